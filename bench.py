@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""Benchmark of the stereo hot path (BASELINE.json metric: pairs/sec at 375x1242, D=228).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A step is one pass of the hot path over one batch of synthetic KITTI-shaped
+stereo pairs: normalise + pad, both trunk forwards (base_model_ws_9, ckpt-1000
+weights), fused correlation + WTA over D=228 and the left-right check
+(BASELINE.json configs[1]: 64 pairs per GPU per step).  Pairs are independent, so
+ranks shard the batch with no data-path collective (weak scaling).
+
+`value`  - device-resident throughput: inputs already in HBM, CUDA events on the
+           stream the kernels run on, max over ranks.
+`e2e`    - the same step through the host-pointer C-ABI call `stereo_pairs` with
+           pinned host buffers: H2D of the images and D2H of the maps inside the
+           timed region.
+`--impl reference` times the CPU restatement of the reference's own TF2 CPU path
+(oracle/, torch-CPU conv + the per-disparity numpy loop of inference.py:143-150)
+on this box's host cores; TensorFlow itself is not installable here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W, D = 375, 1242, 228
+PAIRS_PER_GPU = 64
+DISTINCT_PAIRS = 4
+GOLDEN_CKPT = os.path.join(ROOT, "tests", "golden", "new_checkpoint")
+METRIC = "pairs/sec at 375x1242, D=228 (base_model_ws_9 trunk + fused correlation/WTA + LR check)"
+UNIT = "pairs/s"
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                if out.returncode == 0 and out.stdout.strip():
+                    self.rows.append([c.strip() for c in out.stdout.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for name, v in zip(names, r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]),
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def synthetic_batch(n_pairs: int):
+    from stereo_matching_b200 import synth
+    base = [synth.make_pair(1000 + i, H, W, D) for i in range(min(DISTINCT_PAIRS, n_pairs))]
+    idx = [i % len(base) for i in range(n_pairs)]
+    left = np.stack([base[i][0] for i in idx])
+    right = np.stack([base[i][1] for i in idx])
+    gt = np.stack([base[i][2] for i in idx])
+    return left, right, gt
+
+
+# ---------------------------------------------------------------------------------------------
+def cpu_pair_seconds(rows: int, threads: int | None, repeats: int = 1):
+    """Time the oracle (CPU restatement of inference.py:109-183) on the first
+    `rows` image rows of synthetic pair 1000.  Rows are independent in the
+    reference (only the 9x9 receptive field couples them), so this is a bounded
+    sample of the full-size workload."""
+    import torch
+    from oracle import stereo_oracle as so
+    from stereo_matching_b200 import checkpoint, synth
+    if threads:
+        torch.set_num_threads(threads)
+    layers = checkpoint.load_net_weights(GOLDEN_CKPT)
+    l, r, _ = synth.make_pair(1000, H, W, D)
+    l, r = l[:rows], r[:rows]
+    times = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        so.infer_pair(l, r, layers, "win9_dep9", 9, D, np.float32)
+        times.append(time.perf_counter() - t0)
+    return times, torch.get_num_threads()
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    rows = args.cpu_rows
+    total = args.steps + args.warmup
+    times, cores = cpu_pair_seconds(rows, None, repeats=total)
+    timed = times[args.warmup:]
+    sec = float(np.sum(timed))
+    pairs = (rows / H) * len(timed)
+    value = pairs / sec
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sec / len(timed),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"oracle/stereo_oracle.infer_pair fp32 on the first {rows} of {H} rows of one "
+                                   f"{H}x{W} pair, D={D}, per step; pairs/s scaled by rows/{H}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, world):
+    return {"workload": f"configs[1]: base_model_ws_9, {args.pairs} synthetic {H}x{W} pairs per GPU per step, "
+                        f"fused correlation+WTA, D={D}, ckpt-1000 weights",
+            "pairs_per_gpu": args.pairs, "height": H, "width": W, "disp_range": D,
+            "precision": args.precision, "parallelism": f"batch-sharded x{world}, no collective",
+            "l2": "inputs and per-pair activations (>= 480 MB per pair) exceed the 126 MB L2; no explicit flush"}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from stereo_matching_b200 import _lib
+    from stereo_matching_b200.models.model import base_model_ws_9
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    prec = {"fp32": _lib.PREC_FP32, "bf16x3": _lib.PREC_BF16X3, "bf16": _lib.PREC_BF16}[args.precision]
+
+    model = base_model_ws_9((None, None, 3), device=local_rank, precision=prec)
+    model.load_checkpoint(GOLDEN_CKPT, verbose=False)
+    ctx = model.context
+    n = args.pairs
+    left, right, gt = synthetic_batch(n)
+
+    stream = torch.cuda.Stream()
+    ctx.set_stream(stream.cuda_stream)
+    dev = torch.device("cuda", local_rank)
+    d_left = torch.from_numpy(left).to(dev)
+    d_right = torch.from_numpy(right).to(dev)
+    d_ld = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
+    d_rd = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
+    d_out = torch.empty((n, H, W), dtype=torch.uint8, device=dev)
+
+    def step_dev():
+        ctx.pairs_dev(model.net, d_left.data_ptr(), d_right.data_ptr(), n, H, W, D, prec,
+                      d_ld.data_ptr(), d_rd.data_ptr(), d_out.data_ptr())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing -------------------------------------------------------------
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step_dev()
+        barrier()
+        ctx.profile_enable(True)
+        launches0 = ctx.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local_rank) as clocks:
+            ev0.record(stream)
+            for _ in range(args.steps):
+                step_dev()
+            ev1.record(stream)
+            barrier()
+        ms = max_over_ranks(ev0.elapsed_time(ev1))
+        launches = ctx.launch_count - launches0
+        prof = ctx.profile_read()
+        ctx.profile_enable(False)
+    value = world * n * args.steps / (ms / 1e3)
+
+    # sanity of the result that was just timed (rank 0): GT recovered on pair 0
+    ld0 = d_ld[0].cpu().numpy()
+    from stereo_matching_b200.metric import three_pixel_error
+    err0 = three_pixel_error(ld0.astype(np.int64), gt[0])
+
+    # ---- end to end through the host-pointer C ABI ---------------------------------------------
+    e2e_pairs = min(n, args.e2e_pairs)
+    p_left = torch.from_numpy(left[:e2e_pairs]).pin_memory()
+    p_right = torch.from_numpy(right[:e2e_pairs]).pin_memory()
+    p_ld = torch.empty((e2e_pairs, H, W), dtype=torch.uint8).pin_memory()
+    p_rd = torch.empty((e2e_pairs, H, W), dtype=torch.uint8).pin_memory()
+    p_out = torch.empty((e2e_pairs, H, W), dtype=torch.uint8).pin_memory()
+    lib = _lib.load()
+
+    def step_host():
+        _lib.check(lib.stereo_pairs(ctx._h, model.net, p_left.data_ptr(), p_right.data_ptr(), e2e_pairs, H, W, D,
+                                    prec, p_ld.data_ptr(), p_rd.data_ptr(), p_out.data_ptr(), None, None))
+
+    reps = max(1, (n // e2e_pairs))
+    for _ in range(min(args.warmup, 3)):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for _ in range(reps):
+            step_host()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = world * e2e_pairs * reps * args.steps / e2e_s
+    assert np.array_equal(p_ld[0].numpy(), ld0), "host and device entry points disagree"
+
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant kernel class ---------------------------------------------------
+    pk = peaks()
+    conv_ms, conv_launches = prof["conv"]
+    # 3x3 64->64 layers 2..4 of base_model_ws_9 on the two padded images of a pair
+    flops_per_pair = sum(2.0 * 9 * 64 * 64 * (H + 8 - 2 * k) * (W + 8 - 2 * k) * 2 for k in (2, 3, 4))
+    conv_tflops = flops_per_pair * n * args.steps / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+    step_ms_sum = sum(v[0] for v in prof.values())
+    shares = {k: (v[0] / step_ms_sum if step_ms_sum > 0 else 0.0) for k, v in prof.items()}
+    roofline = {"kernel": "conv3x3_64_64 (trunk layers 2-4)", "bound": "tensor", "achieved": conv_tflops,
+                "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": conv_tflops / pk["bf16_tflops_sustained"], "traffic": None,
+                "peak_source": pk["source"] + " bf16 dense, sustained",
+                "avg_launch_ms": conv_ms / conv_launches if conv_launches else None,
+                "share_of_step": shares.get("conv"),
+                "note": "algorithmic FLOPs (2*9*64*64 per output pixel) / CUDA-event time of the kernel class"}
+    corr_ms, corr_launches = prof["corr"]
+    corr_bytes = 2.0 * H * W * 64 * 4 + 2.0 * H * W      # read two feature maps, write two uint8 maps
+    extra = {"kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+             "kernel_share": shares,
+             "corr_fused": {"gdisp_evals_per_s": 2.0 * H * W * D * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None,
+                            "algorithmic_gbs": corr_bytes * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None},
+             "three_px_error_pair0": err0}
+
+    # ---- CPU baseline (oracle port) on a bounded sample --------------------------------------------
+    cpu = None
+    if not args.no_cpu_baseline:
+        times, cores = cpu_pair_seconds(args.cpu_rows, None, repeats=1)
+        cpu_value = (args.cpu_rows / H) / times[0]
+        cpu = {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"oracle/stereo_oracle.infer_pair fp32 (torch-CPU conv + per-disparity numpy loop) on the "
+                         f"first {args.cpu_rows} of {H} rows of one pair, D={D}: {times[0]:.1f} s"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (fp32 accumulate)", "bf16": "bf16"}[args.precision],
+        "data": "synthetic", "config": workload_config(args, world),
+        "e2e": {"value": e2e_value, "unit": UNIT,
+                "h2d_bytes_per_step": int(2 * e2e_pairs * reps * H * W * 3),
+                "d2h_bytes_per_step": int(3 * e2e_pairs * reps * H * W)},
+        "gpu_launches": int(launches),
+        "clocks": clocks.summary(),
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "extra": extra,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "bf16x3", "bf16"])
+    ap.add_argument("--e2e-pairs", type=int, default=64, help="pairs per host-pointer call in the e2e leg")
+    ap.add_argument("--cpu-rows", type=int, default=96, help="image rows of the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

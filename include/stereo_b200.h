@@ -1,0 +1,157 @@
+/*
+ * stereo_b200.h - C ABI of libstereo_b200.so, the sm_100a implementation of the
+ * Luo/Schwing/Urtasun stereo hot path of datvuthanh/Stereo-Matching.
+ *
+ * The reference has no FFI of its own: its hot path is Python calling TensorFlow
+ * ops (inference.py) and Lua calling the external mc-cnn CUDA library
+ * (post.lua / smooth/nyu.lua).  Each entry point below names the reference
+ * lines it replaces.  The Python package `stereo_matching_b200` binds these
+ * with ctypes and mirrors the reference's own surface on top (see
+ * INTEGRATION.md).
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative STEREO_E_* code on
+ *     failure; stereo_last_error() returns a message for the calling thread.
+ *     Nothing throws across the boundary.
+ *   - a stereo_ctx is bound to one CUDA device and one stream.  It is not
+ *     thread-safe; use one context per GPU / host thread.
+ *   - functions without a suffix take HOST pointers, copy in and out and
+ *     return after the result is in the caller's buffer.  `_dev` variants take
+ *     DEVICE pointers on the context's device, enqueue work on the context's
+ *     stream and return without synchronising (call stereo_sync).
+ *   - images are NHWC, volumes are [n][H][W][D] float32 with D fastest, exactly
+ *     the layout inference.py writes to its .bin files (inference.py:210-231).
+ */
+#ifndef STEREO_B200_H
+#define STEREO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct stereo_ctx stereo_ctx;
+
+enum {
+    STEREO_OK = 0,
+    STEREO_E_INVALID = -1, /* bad argument (null pointer, non-positive size, unknown enum) */
+    STEREO_E_CUDA = -2,    /* a CUDA runtime call or kernel failed */
+    STEREO_E_STATE = -3,   /* weights for the requested net have not been set */
+    STEREO_E_NOMEM = -4,   /* device allocation failed */
+    STEREO_E_LIMIT = -5    /* a size exceeds what a kernel supports */
+};
+
+/* net_type of inference.py:46,81-84 */
+enum { STEREO_NET_WIN9 = 0 /* base_model_ws_9 */, STEREO_NET_WIN37 = 1 /* base_model */ };
+
+/* arithmetic of the trunk / correlation contractions */
+enum {
+    STEREO_PREC_FP32 = 0,   /* fp32 FMA on CUDA cores */
+    STEREO_PREC_BF16X3 = 1, /* tcgen05 tensor cores, 3-pass bf16 split, fp32 accumulate (parity mode) */
+    STEREO_PREC_BF16 = 2    /* tcgen05 tensor cores, single bf16 pass (does not meet the 1e-4 gate) */
+};
+
+const char *stereo_last_error(void);
+int stereo_version(void);
+
+/* One context per GPU.  Replaces the implicit TF / torch7 device state. */
+int stereo_create(int device, stereo_ctx **out);
+int stereo_destroy(stereo_ctx *ctx);
+/* Run on a caller-owned cudaStream_t (pass NULL to go back to the context's own stream). */
+int stereo_set_stream(stereo_ctx *ctx, void *cuda_stream);
+int stereo_sync(stereo_ctx *ctx);
+/* Number of kernels this context has launched since creation (bench bookkeeping). */
+int64_t stereo_launch_count(const stereo_ctx *ctx);
+
+/* Weights of one trunk, replacing `ckpt.restore(manager.latest_checkpoint)`
+ * (inference.py:88-91).  `packed` holds, for every conv layer in order, the
+ * kernel in HWIO order [k][k][Cin][Cout] followed by the bias [Cout]; the
+ * inference-mode BatchNormalization of models/model.py has already been folded
+ * into them by the host (stereo_matching_b200/models/model.py).
+ * WIN9: 4 layers 3x3, 3->64->64->64->64.  WIN37: 9 layers 5x5,
+ * 3->32->32->32->64->64->64->64->64->64. */
+int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_floats);
+
+/* inference.py:109-133: per image (x - mean) / std over all pixels and
+ * channels (population std, float64), zero padded by (patch-1)/2 on each side.
+ * rgb: uint8 [n][h][w][3] -> out: float32 [n][h+patch-1][w+patch-1][3]. */
+int stereo_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch,
+                         float *out);
+int stereo_normalize_pad_dev(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch,
+                             float *out);
+
+/* `model(x, training=False)` of inference.py:136-137 / models/model.py:5-41.
+ * in: float32 [n][h][w][3] -> out: float32 [n][h-8][w-8][64] (WIN9) or
+ * [n][h-36][w-36][64] (WIN37). */
+int stereo_trunk(stereo_ctx *ctx, int net, const float *nhwc_in, int n, int h, int w,
+                 float *nhwc_out, int precision);
+int stereo_trunk_dev(stereo_ctx *ctx, int net, const float *nhwc_in, int n, int h, int w,
+                     float *nhwc_out, int precision);
+
+/* The disparity loop of inference.py:139-150, materialised.
+ * lmap, rmap: float32 [n][h][w][c];  left_vol, right_vol: float32 [n][h][w][D]
+ *   left [y][x][d] = <L[y][x], R[y][x-d]>  for x >= d,   else exactly 0
+ *   right[y][x][d] = <L[y][x+d], R[y][x]>  for x+d < w,  else exactly 0 */
+int stereo_cost_volume(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w,
+                       int c, int D, float *left_vol, float *right_vol, int precision);
+int stereo_cost_volume_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h,
+                           int w, int c, int D, float *left_vol, float *right_vol, int precision);
+
+/* tf.argmax(cost_volume, axis=2) -> uint8 of inference.py:169-183: arg max over
+ * all D slots (zero-filled ones included), lowest index wins ties.
+ * With take_min != 0 it is the `vol:min(2)` of post.lua:159,178,226.
+ * vol: float32 [n][h][w][D] -> disp: uint8 [n][h][w]. */
+int stereo_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min,
+               uint8_t *disp);
+int stereo_wta_dev(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min,
+                   uint8_t *disp);
+
+/* inference.py:139-183 without ever writing the volumes: correlation and WTA
+ * fused.  lmap, rmap: float32 [n][h][w][c] -> left_disp, right_disp: uint8 [n][h][w]. */
+int stereo_corr_wta(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w,
+                    int c, int D, uint8_t *left_disp, uint8_t *right_disp, int precision);
+int stereo_corr_wta_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w,
+                        int c, int D, uint8_t *left_disp, uint8_t *right_disp, int precision);
+
+/* Left-right consistency check = adcensus.outlier_detection (smooth/nyu.lua:95):
+ * 0 match, 1 occlusion, 2 mismatch.  d0, d1: uint8 [n][h][w] -> outlier uint8 [n][h][w]. */
+int stereo_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w,
+                    int D, uint8_t *outlier);
+int stereo_lr_check_dev(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w,
+                        int D, uint8_t *outlier);
+
+/* One iteration of the per-pair loop inference.py:99-183 for n pairs: normalise,
+ * pad, both trunk forwards, fused correlation + WTA, LR check.
+ * left_rgb, right_rgb: uint8 [n][h][w][3];  outputs uint8 [n][h][w];
+ * lr_outlier may be NULL.  If left_vol/right_vol are non-NULL the volumes
+ * (float32 [n][h][w][D]) are materialised as well, as inference.py:210-231 writes them. */
+int stereo_pairs(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n,
+                 int h, int w, int D, int precision, uint8_t *left_disp, uint8_t *right_disp,
+                 uint8_t *lr_outlier, float *left_vol, float *right_vol);
+int stereo_pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb,
+                     int n, int h, int w, int D, int precision, uint8_t *left_disp,
+                     uint8_t *right_disp, uint8_t *lr_outlier, float *left_vol, float *right_vol);
+
+/* Per-kernel timing with CUDA events recorded on the context's stream around every
+ * launch of a kernel class (no counterpart in the reference, which only prints
+ * torch.tic()/toc() wall times, post.lua:100-235).  Enabling resets the counters;
+ * reading synchronises the stream. */
+enum {
+    STEREO_K_PREP = 0,       /* image sums + LUT + normalise/pad */
+    STEREO_K_CONV_FIRST = 1, /* first trunk layer (Cin = 3) */
+    STEREO_K_CONV = 2,       /* remaining trunk layers */
+    STEREO_K_CORR = 3,       /* correlation (+ fused WTA) */
+    STEREO_K_WTA = 4,        /* standalone arg max / arg min over D */
+    STEREO_K_LR = 5,         /* left-right consistency */
+    STEREO_K_COUNT = 6
+};
+int stereo_profile_enable(stereo_ctx *ctx, int on);
+int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches);
+const char *stereo_profile_name(int kernel_class);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STEREO_B200_H */

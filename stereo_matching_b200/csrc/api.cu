@@ -1,0 +1,529 @@
+// C ABI of libstereo_b200.so: context management, argument checking, host<->device
+// staging for the host-pointer entry points, and the per-pair pipeline.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "common.cuh"
+
+namespace stereo {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+int DevBuf::reserve(size_t want)
+{
+    if (want <= bytes) return STEREO_OK;
+    if (ptr) {
+        cudaFree(ptr);
+        ptr = nullptr;
+        bytes = 0;
+    }
+    size_t rounded = (want + 255) & ~(size_t)255;
+    cudaError_t err = cudaMalloc(&ptr, rounded);
+    if (err != cudaSuccess) {
+        ptr = nullptr;
+        (void)cudaGetLastError();
+        set_error("cudaMalloc(%zu bytes) failed: %s", rounded, cudaGetErrorString(err));
+        return STEREO_E_NOMEM;
+    }
+    bytes = rounded;
+    return STEREO_OK;
+}
+
+void DevBuf::release()
+{
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    bytes = 0;
+}
+
+NetDesc net_desc(int net)
+{
+    NetDesc d;
+    auto add = [&](int ks, int cin, int cout, int relu) {
+        LayerDesc &L = d.layer[d.n_layers++];
+        L.ks = ks; L.cin = cin; L.cout = cout; L.relu = relu;
+        L.w_off = d.n_floats;
+        d.n_floats += (size_t)ks * ks * cin * cout;
+        L.b_off = d.n_floats;
+        d.n_floats += cout;
+        d.shrink += ks - 1;
+    };
+    if (net == STEREO_NET_WIN9) {
+        // models/model.py:30-41
+        add(3, 3, 64, 1); add(3, 64, 64, 1); add(3, 64, 64, 1); add(3, 64, 64, 0);
+    } else if (net == STEREO_NET_WIN37) {
+        // models/model.py:5-28 (the dead conv8/bn8 pair at :21-22 is not in the graph)
+        add(5, 3, 32, 1); add(5, 32, 32, 1); add(5, 32, 32, 1); add(5, 32, 64, 1);
+        add(5, 64, 64, 1); add(5, 64, 64, 1); add(5, 64, 64, 1); add(5, 64, 64, 1); add(5, 64, 64, 0);
+    }
+    return d;
+}
+
+static int check_ctx(stereo_ctx *ctx)
+{
+    if (!ctx) {
+        set_error("null context");
+        return STEREO_E_INVALID;
+    }
+    STEREO_CUDA_CHECK(cudaSetDevice(ctx->device));
+    return STEREO_OK;
+}
+
+static int check_dims(int n, int h, int w)
+{
+    STEREO_REQUIRE(n > 0 && h > 0 && w > 0, "n, h, w must be positive (got %d, %d, %d)", n, h, w);
+    return STEREO_OK;
+}
+
+static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision)
+{
+    STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
+    if (!ctx->has_weights[net]) {
+        set_error("weights for net %d have not been set (call stereo_set_weights first)", net);
+        return STEREO_E_STATE;
+    }
+    STEREO_REQUIRE(precision == STEREO_PREC_FP32, "precision mode %d is not available in this build", precision);
+    NetDesc nd = net_desc(net);
+    STEREO_REQUIRE(h > nd.shrink && w > nd.shrink, "input %dx%d is too small for a receptive field of %d", h, w,
+                   nd.shrink + 1);
+    const float *wts = ctx->weights[net].as<float>();
+    size_t max_act = 0;
+    {
+        int ch = h, cw = w;
+        for (int l = 0; l + 1 < nd.n_layers; ++l) {
+            ch -= nd.layer[l].ks - 1;
+            cw -= nd.layer[l].ks - 1;
+            size_t b = sizeof(float) * (size_t)n * ch * cw * nd.layer[l].cout;
+            if (b > max_act) max_act = b;
+        }
+    }
+    STEREO_TRY(ctx->act[0].reserve(max_act));
+    STEREO_TRY(ctx->act[1].reserve(max_act));
+    const float *cur = in;
+    int ch = h, cw = w;
+    for (int l = 0; l < nd.n_layers; ++l) {
+        float *dst = (l + 1 == nd.n_layers) ? out : ctx->act[l & 1].as<float>();
+        STEREO_TRY(launch_conv_ffma(ctx, nd.layer[l], wts, cur, n, ch, cw, dst));
+        ch -= nd.layer[l].ks - 1;
+        cw -= nd.layer[l].ks - 1;
+        cur = dst;
+    }
+    return STEREO_OK;
+}
+
+static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h,
+                     int w, int D, int precision, uint8_t *left_disp, uint8_t *right_disp, uint8_t *lr_outlier,
+                     float *left_vol, float *right_vol)
+{
+    STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
+    STEREO_REQUIRE(D > 0, "disp_range must be positive, got %d", D);
+    STEREO_REQUIRE(left_rgb && right_rgb && left_disp && right_disp, "null image or disparity pointer");
+    NetDesc nd = net_desc(net);
+    const int patch = nd.shrink + 1;
+    const int hp = h + nd.shrink, wp = w + nd.shrink;
+    const size_t pad_img = (size_t)hp * wp * 3;
+    const size_t feat_img = (size_t)h * w * 64;
+    STEREO_TRY(ctx->padded.reserve(sizeof(float) * 2 * pad_img));
+    STEREO_TRY(ctx->feat.reserve(sizeof(float) * 2 * feat_img));
+    float *padded = ctx->padded.as<float>();
+    float *feat = ctx->feat.as<float>();
+    const size_t img_bytes = (size_t)h * w * 3;
+    const size_t map = (size_t)h * w;
+    for (int i = 0; i < n; ++i) {
+        // left and right of one pair go through the trunk as a batch of two
+        STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
+        STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
+        STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, feat, precision));
+        float *lv = left_vol ? left_vol + i * map * D : nullptr;
+        float *rv = right_vol ? right_vol + i * map * D : nullptr;
+        STEREO_TRY(launch_corr_ffma(ctx, feat, feat + feat_img, 1, h, w, 64, D, lv, rv, left_disp + i * map,
+                                    right_disp + i * map));
+    }
+    if (lr_outlier) STEREO_TRY(launch_lr_check(ctx, left_disp, right_disp, n, h, w, D, lr_outlier));
+    return STEREO_OK;
+}
+
+// ---- host staging helpers ----
+static int h2d(stereo_ctx *ctx, DevBuf &buf, const void *src, size_t bytes)
+{
+    STEREO_TRY(buf.reserve(bytes));
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(buf.ptr, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return STEREO_OK;
+}
+
+static int d2h(stereo_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return STEREO_OK;
+}
+
+static int finish(stereo_ctx *ctx)
+{
+    STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    return STEREO_OK;
+}
+
+}  // namespace stereo
+
+using namespace stereo;
+
+extern "C" {
+
+const char *stereo_last_error(void) { return g_error; }
+
+int stereo_version(void) { return 100; }
+
+int stereo_create(int device, stereo_ctx **out)
+{
+    STEREO_REQUIRE(out != nullptr, "null output pointer");
+    *out = nullptr;
+    int count = 0;
+    STEREO_CUDA_CHECK(cudaGetDeviceCount(&count));
+    STEREO_REQUIRE(device >= 0 && device < count, "device %d out of range (%d visible)", device, count);
+    STEREO_CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    STEREO_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+        return STEREO_E_INVALID;
+    }
+    stereo_ctx *ctx = new (std::nothrow) stereo_ctx();
+    if (!ctx) {
+        set_error("out of host memory");
+        return STEREO_E_NOMEM;
+    }
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    cudaError_t err = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+    if (err != cudaSuccess) {
+        set_error("cudaStreamCreate failed: %s", cudaGetErrorString(err));
+        delete ctx;
+        return STEREO_E_CUDA;
+    }
+    ctx->stream = ctx->own_stream;
+    *out = ctx;
+    return STEREO_OK;
+}
+
+int stereo_destroy(stereo_ctx *ctx)
+{
+    if (!ctx) return STEREO_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *bufs[] = {&ctx->weights[0], &ctx->weights[1], &ctx->wsplit[0], &ctx->wsplit[1], &ctx->stats,
+                      &ctx->padded, &ctx->act[0], &ctx->act[1], &ctx->feat, &ctx->stage_in[0], &ctx->stage_in[1],
+                      &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
+                      &ctx->stage_vol[1]};
+    for (DevBuf *b : bufs) b->release();
+    if (ctx->prof.start) {
+        for (int i = 0; i < Profiler::kMaxPairs; ++i) {
+            cudaEventDestroy(ctx->prof.start[i]);
+            cudaEventDestroy(ctx->prof.stop[i]);
+        }
+        delete[] ctx->prof.start;
+        delete[] ctx->prof.stop;
+        delete[] ctx->prof.cls;
+    }
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+    return STEREO_OK;
+}
+
+int stereo_set_stream(stereo_ctx *ctx, void *cuda_stream)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+    return STEREO_OK;
+}
+
+int stereo_sync(stereo_ctx *ctx)
+{
+    STEREO_TRY(check_ctx(ctx));
+    return finish(ctx);
+}
+
+int64_t stereo_launch_count(const stereo_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int stereo_profile_enable(stereo_ctx *ctx, int on)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    Profiler &p = ctx->prof;
+    if (on && !p.start) {
+        p.start = new (std::nothrow) cudaEvent_t[Profiler::kMaxPairs];
+        p.stop = new (std::nothrow) cudaEvent_t[Profiler::kMaxPairs];
+        p.cls = new (std::nothrow) int[Profiler::kMaxPairs];
+        if (!p.start || !p.stop || !p.cls) {
+            set_error("out of host memory");
+            return STEREO_E_NOMEM;
+        }
+        for (int i = 0; i < Profiler::kMaxPairs; ++i) {
+            STEREO_CUDA_CHECK(cudaEventCreate(&p.start[i]));
+            STEREO_CUDA_CHECK(cudaEventCreate(&p.stop[i]));
+        }
+    }
+    p.on = on != 0;
+    p.used = 0;
+    for (int k = 0; k < STEREO_K_COUNT; ++k) p.launches[k] = 0;
+    return STEREO_OK;
+}
+
+int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(kernel_class >= 0 && kernel_class < STEREO_K_COUNT && total_ms && launches, "bad argument");
+    STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    Profiler &p = ctx->prof;
+    double sum = 0.0;
+    int64_t timed = 0;
+    for (int i = 0; i < p.used; ++i) {
+        if (p.cls[i] != kernel_class) continue;
+        float ms = 0.f;
+        STEREO_CUDA_CHECK(cudaEventElapsedTime(&ms, p.start[i], p.stop[i]));
+        sum += ms;
+        ++timed;
+    }
+    // launches beyond the event pool are extrapolated from the timed ones
+    int64_t all = p.launches[kernel_class];
+    *total_ms = timed > 0 ? sum * ((double)all / (double)timed) : 0.0;
+    *launches = all;
+    return STEREO_OK;
+}
+
+const char *stereo_profile_name(int kernel_class)
+{
+    static const char *names[STEREO_K_COUNT] = {"prep", "conv_first", "conv", "corr", "wta", "lr_check"};
+    return kernel_class >= 0 && kernel_class < STEREO_K_COUNT ? names[kernel_class] : "?";
+}
+
+int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_floats)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
+    STEREO_REQUIRE(packed != nullptr, "null weight pointer");
+    NetDesc nd = net_desc(net);
+    STEREO_REQUIRE(n_floats == nd.n_floats, "net %d expects %zu packed floats, got %zu", net, nd.n_floats, n_floats);
+    STEREO_TRY(ctx->weights[net].reserve(sizeof(float) * n_floats));
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(ctx->weights[net].ptr, packed, sizeof(float) * n_floats,
+                                      cudaMemcpyHostToDevice, ctx->stream));
+    STEREO_TRY(finish(ctx));
+    ctx->has_weights[net] = true;
+    return STEREO_OK;
+}
+
+int stereo_normalize_pad_dev(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(rgb && out, "null pointer");
+    return launch_normalize_pad(ctx, rgb, n, h, w, patch, out);
+}
+
+int stereo_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(rgb && out, "null pointer");
+    STEREO_REQUIRE(patch >= 1 && (patch & 1), "patch size must be odd and positive, got %d", patch);
+    size_t in_b = (size_t)n * h * w * 3;
+    size_t out_b = sizeof(float) * (size_t)n * (h + patch - 1) * (w + patch - 1) * 3;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], rgb, in_b));
+    STEREO_TRY(ctx->stage_vol[0].reserve(out_b));
+    STEREO_TRY(launch_normalize_pad(ctx, ctx->stage_in[0].as<uint8_t>(), n, h, w, patch, ctx->stage_vol[0].as<float>()));
+    STEREO_TRY(d2h(ctx, out, ctx->stage_vol[0].ptr, out_b));
+    return finish(ctx);
+}
+
+int stereo_trunk_dev(stereo_ctx *ctx, int net, const float *nhwc_in, int n, int h, int w, float *nhwc_out,
+                     int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(nhwc_in && nhwc_out, "null pointer");
+    return trunk_dev(ctx, net, nhwc_in, n, h, w, nhwc_out, precision);
+}
+
+int stereo_trunk(stereo_ctx *ctx, int net, const float *nhwc_in, int n, int h, int w, float *nhwc_out,
+                 int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(nhwc_in && nhwc_out, "null pointer");
+    STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
+    NetDesc nd = net_desc(net);
+    STEREO_REQUIRE(h > nd.shrink && w > nd.shrink, "input %dx%d is too small for a receptive field of %d", h, w,
+                   nd.shrink + 1);
+    size_t in_b = sizeof(float) * (size_t)n * h * w * 3;
+    size_t out_b = sizeof(float) * (size_t)n * (h - nd.shrink) * (w - nd.shrink) * 64;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], nhwc_in, in_b));
+    STEREO_TRY(ctx->stage_vol[0].reserve(out_b));
+    STEREO_TRY(trunk_dev(ctx, net, ctx->stage_in[0].as<float>(), n, h, w, ctx->stage_vol[0].as<float>(), precision));
+    STEREO_TRY(d2h(ctx, nhwc_out, ctx->stage_vol[0].ptr, out_b));
+    return finish(ctx);
+}
+
+static int corr_args(int n, int h, int w, int c, int D, int precision)
+{
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(c > 0 && D > 0, "channels and disp_range must be positive (got %d, %d)", c, D);
+    STEREO_REQUIRE(precision == STEREO_PREC_FP32, "precision mode %d is not available in this build", precision);
+    return STEREO_OK;
+}
+
+int stereo_cost_volume_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
+                           int D, float *left_vol, float *right_vol, int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(corr_args(n, h, w, c, D, precision));
+    STEREO_REQUIRE(lmap && rmap && left_vol && right_vol, "null pointer");
+    return launch_corr_ffma(ctx, lmap, rmap, n, h, w, c, D, left_vol, right_vol, nullptr, nullptr);
+}
+
+int stereo_cost_volume(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
+                       float *left_vol, float *right_vol, int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(corr_args(n, h, w, c, D, precision));
+    STEREO_REQUIRE(lmap && rmap && left_vol && right_vol, "null pointer");
+    size_t map_b = sizeof(float) * (size_t)n * h * w * c;
+    size_t vol_b = sizeof(float) * (size_t)n * h * w * D;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], lmap, map_b));
+    STEREO_TRY(h2d(ctx, ctx->stage_in[1], rmap, map_b));
+    STEREO_TRY(ctx->stage_vol[0].reserve(vol_b));
+    STEREO_TRY(ctx->stage_vol[1].reserve(vol_b));
+    STEREO_TRY(launch_corr_ffma(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D,
+                                ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(), nullptr, nullptr));
+    STEREO_TRY(d2h(ctx, left_vol, ctx->stage_vol[0].ptr, vol_b));
+    STEREO_TRY(d2h(ctx, right_vol, ctx->stage_vol[1].ptr, vol_b));
+    return finish(ctx);
+}
+
+int stereo_wta_dev(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(D > 0 && vol && disp, "bad argument");
+    return launch_wta(ctx, vol, n, h, w, D, take_min, disp);
+}
+
+int stereo_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(D > 0 && vol && disp, "bad argument");
+    size_t vol_b = sizeof(float) * (size_t)n * h * w * D;
+    size_t map_b = (size_t)n * h * w;
+    STEREO_TRY(h2d(ctx, ctx->stage_vol[0], vol, vol_b));
+    STEREO_TRY(ctx->stage_out[0].reserve(map_b));
+    STEREO_TRY(launch_wta(ctx, ctx->stage_vol[0].as<float>(), n, h, w, D, take_min, ctx->stage_out[0].as<uint8_t>()));
+    STEREO_TRY(d2h(ctx, disp, ctx->stage_out[0].ptr, map_b));
+    return finish(ctx);
+}
+
+int stereo_corr_wta_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
+                        uint8_t *left_disp, uint8_t *right_disp, int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(corr_args(n, h, w, c, D, precision));
+    STEREO_REQUIRE(lmap && rmap && left_disp && right_disp, "null pointer");
+    return launch_corr_ffma(ctx, lmap, rmap, n, h, w, c, D, nullptr, nullptr, left_disp, right_disp);
+}
+
+int stereo_corr_wta(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
+                    uint8_t *left_disp, uint8_t *right_disp, int precision)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(corr_args(n, h, w, c, D, precision));
+    STEREO_REQUIRE(lmap && rmap && left_disp && right_disp, "null pointer");
+    size_t map_b = sizeof(float) * (size_t)n * h * w * c;
+    size_t out_b = (size_t)n * h * w;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], lmap, map_b));
+    STEREO_TRY(h2d(ctx, ctx->stage_in[1], rmap, map_b));
+    STEREO_TRY(ctx->stage_out[0].reserve(out_b));
+    STEREO_TRY(ctx->stage_out[1].reserve(out_b));
+    STEREO_TRY(launch_corr_ffma(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D,
+                                nullptr, nullptr, ctx->stage_out[0].as<uint8_t>(), ctx->stage_out[1].as<uint8_t>()));
+    STEREO_TRY(d2h(ctx, left_disp, ctx->stage_out[0].ptr, out_b));
+    STEREO_TRY(d2h(ctx, right_disp, ctx->stage_out[1].ptr, out_b));
+    return finish(ctx);
+}
+
+int stereo_lr_check_dev(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
+                        uint8_t *outlier)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(D > 0 && d0 && d1 && outlier, "bad argument");
+    return launch_lr_check(ctx, d0, d1, n, h, w, D, outlier);
+}
+
+int stereo_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
+                    uint8_t *outlier)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(D > 0 && d0 && d1 && outlier, "bad argument");
+    size_t b = (size_t)n * h * w;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], d0, b));
+    STEREO_TRY(h2d(ctx, ctx->stage_in[1], d1, b));
+    STEREO_TRY(ctx->stage_out[0].reserve(b));
+    STEREO_TRY(launch_lr_check(ctx, ctx->stage_in[0].as<uint8_t>(), ctx->stage_in[1].as<uint8_t>(), n, h, w, D,
+                               ctx->stage_out[0].as<uint8_t>()));
+    STEREO_TRY(d2h(ctx, outlier, ctx->stage_out[0].ptr, b));
+    return finish(ctx);
+}
+
+int stereo_pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h,
+                     int w, int D, int precision, uint8_t *left_disp, uint8_t *right_disp, uint8_t *lr_outlier,
+                     float *left_vol, float *right_vol)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    return pairs_dev(ctx, net, left_rgb, right_rgb, n, h, w, D, precision, left_disp, right_disp, lr_outlier,
+                     left_vol, right_vol);
+}
+
+int stereo_pairs(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h, int w,
+                 int D, int precision, uint8_t *left_disp, uint8_t *right_disp, uint8_t *lr_outlier,
+                 float *left_vol, float *right_vol)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_dims(n, h, w));
+    STEREO_REQUIRE(left_rgb && right_rgb && left_disp && right_disp, "null image or disparity pointer");
+    STEREO_REQUIRE((left_vol == nullptr) == (right_vol == nullptr), "left and right volumes must be given together");
+    size_t img_b = (size_t)n * h * w * 3, map_b = (size_t)n * h * w;
+    size_t vol_b = sizeof(float) * (size_t)n * h * w * D;
+    STEREO_TRY(h2d(ctx, ctx->stage_in[0], left_rgb, img_b));
+    STEREO_TRY(h2d(ctx, ctx->stage_in[1], right_rgb, img_b));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->stage_out[i].reserve(map_b));
+    if (left_vol) {
+        STEREO_TRY(ctx->stage_vol[0].reserve(vol_b));
+        STEREO_TRY(ctx->stage_vol[1].reserve(vol_b));
+    }
+    STEREO_TRY(pairs_dev(ctx, net, ctx->stage_in[0].as<uint8_t>(), ctx->stage_in[1].as<uint8_t>(), n, h, w, D,
+                         precision, ctx->stage_out[0].as<uint8_t>(), ctx->stage_out[1].as<uint8_t>(),
+                         lr_outlier ? ctx->stage_out[2].as<uint8_t>() : nullptr,
+                         left_vol ? ctx->stage_vol[0].as<float>() : nullptr,
+                         left_vol ? ctx->stage_vol[1].as<float>() : nullptr));
+    STEREO_TRY(d2h(ctx, left_disp, ctx->stage_out[0].ptr, map_b));
+    STEREO_TRY(d2h(ctx, right_disp, ctx->stage_out[1].ptr, map_b));
+    if (lr_outlier) STEREO_TRY(d2h(ctx, lr_outlier, ctx->stage_out[2].ptr, map_b));
+    if (left_vol) {
+        STEREO_TRY(d2h(ctx, left_vol, ctx->stage_vol[0].ptr, vol_b));
+        STEREO_TRY(d2h(ctx, right_vol, ctx->stage_vol[1].ptr, vol_b));
+    }
+    return finish(ctx);
+}
+
+}  // extern "C"

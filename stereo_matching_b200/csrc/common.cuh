@@ -1,0 +1,128 @@
+// Shared declarations of libstereo_b200.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/stereo_b200.h"
+
+namespace stereo {
+
+void set_error(const char *fmt, ...);
+
+#define STEREO_CUDA_CHECK(expr)                                                              \
+    do {                                                                                     \
+        cudaError_t err__ = (expr);                                                          \
+        if (err__ != cudaSuccess) {                                                          \
+            stereo::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(err__),     \
+                              __FILE__, __LINE__);                                           \
+            return err__ == cudaErrorMemoryAllocation ? STEREO_E_NOMEM : STEREO_E_CUDA;      \
+        }                                                                                    \
+    } while (0)
+
+#define STEREO_TRY(expr)              \
+    do {                              \
+        int rc__ = (expr);            \
+        if (rc__ != STEREO_OK) return rc__; \
+    } while (0)
+
+#define STEREO_REQUIRE(cond, ...)          \
+    do {                                   \
+        if (!(cond)) {                     \
+            stereo::set_error(__VA_ARGS__); \
+            return STEREO_E_INVALID;       \
+        }                                  \
+    } while (0)
+
+// Device buffer that only ever grows; owned by a context.
+struct DevBuf {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+    int reserve(size_t want);
+    void release();
+    template <typename T> T *as() const { return static_cast<T *>(ptr); }
+};
+
+constexpr int kMaxLayers = 9;
+
+struct LayerDesc {
+    int ks, cin, cout, relu;
+    size_t w_off, b_off;  // float offsets into the packed weight buffer
+};
+
+struct NetDesc {
+    int n_layers = 0;
+    int shrink = 0;  // total border lost by the valid convolutions
+    LayerDesc layer[kMaxLayers];
+    size_t n_floats = 0;
+};
+
+NetDesc net_desc(int net);
+
+// CUDA-event timing of kernel classes (stereo_profile_*).
+struct Profiler {
+    static constexpr int kMaxPairs = 8192;
+    bool on = false;
+    int used = 0;
+    cudaEvent_t *start = nullptr, *stop = nullptr;
+    int *cls = nullptr;
+    int64_t launches[STEREO_K_COUNT] = {};
+};
+
+}  // namespace stereo
+
+struct stereo_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    int64_t launches = 0;
+    stereo::Profiler prof;
+    bool has_weights[2] = {false, false};
+    stereo::DevBuf weights[2];   // packed fp32, layout of stereo_set_weights
+    stereo::DevBuf wsplit[2];    // tensor-core operand images of the weights (bf16 hi/lo)
+    stereo::DevBuf stats;        // per-image u64 sums + 256-entry LUTs
+    stereo::DevBuf padded;       // normalised, padded images
+    stereo::DevBuf act[2];       // ping-pong activations
+    stereo::DevBuf feat;         // trunk outputs of one pair
+    stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
+    stereo::DevBuf stage_out[3];
+    stereo::DevBuf stage_vol[2];
+};
+
+namespace stereo {
+
+// Brackets the launches issued during its lifetime with a start/stop event pair.
+struct ProfScope {
+    stereo_ctx *ctx;
+    int slot = -1;
+    ProfScope(stereo_ctx *c, int kernel_class) : ctx(c)
+    {
+        Profiler &p = ctx->prof;
+        if (!p.on) return;
+        p.launches[kernel_class] += 1;
+        if (p.used >= Profiler::kMaxPairs) return;
+        slot = p.used++;
+        p.cls[slot] = kernel_class;
+        cudaEventRecord(p.start[slot], ctx->stream);
+    }
+    ~ProfScope()
+    {
+        if (slot >= 0) cudaEventRecord(ctx->prof.stop[slot], ctx->stream);
+    }
+};
+
+// prep.cu
+int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out);
+// conv_ffma.cu
+int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in,
+                     int n, int h_in, int w_in, float *out);
+// corr.cu
+int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
+                     int D, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp);
+int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp);
+int launch_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
+                    uint8_t *outlier);
+
+}  // namespace stereo

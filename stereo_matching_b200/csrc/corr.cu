@@ -1,0 +1,251 @@
+// Left/right correlation cost volumes and winner-take-all
+// (/root/reference/inference.py:139-183), fp32 on CUDA cores.
+//
+//   left [y][x][d] = <L[y][x], R[y][x-d]>   (x >= d,    else exactly 0)
+//   right[y][x][d] = <L[y][x+d], R[y][x]>   (x+d < w,   else exactly 0)
+//
+// Both volumes are the same banded Gram matrix of one image row, indexed two
+// ways.  One CTA handles 64 consecutive x of one row of one side: it stages the
+// 64 "own" feature vectors and the 64+D-1 candidate vectors of the other view
+// transposed in shared memory, forms the 64 x (64+D-1) product block with 8x8
+// register tiles (one 32-column slab per warp), parks it in shared memory and
+// then either streams the band out as [x][d] rows (coalesced, D fastest - the
+// .bin layout of inference.py:210-231) or reduces it to the arg max per pixel
+// without ever touching HBM (fused correlation + WTA).
+#include "common.cuh"
+
+namespace stereo {
+
+constexpr int kCorrTX = 64;   // pixels per CTA
+constexpr int kPA = 68;       // pitch of the transposed own-feature tile
+
+__device__ __forceinline__ void stage_transposed(const float *__restrict__ row, int w, int c, int xstart,
+                                                 int ncols, float *dst, int pitch, int tid, int nthreads)
+{
+    // item -> (x_lo = it % 8, quad = (it / 8) % (c/4), x_hi): each pixel's 4 quads are
+    // contiguous in global memory, the 8 x of a lane group hit distinct banks.
+    int q4 = c >> 2;
+    int items = ((ncols + 7) >> 3) * 8 * q4;
+    for (int it = tid; it < items; it += nthreads) {
+        int xl = it & 7;
+        int q = (it >> 3) % q4;
+        int xh = (it >> 3) / q4;
+        int u = xh * 8 + xl;
+        if (u >= ncols) continue;
+        int gx = xstart + u;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (gx >= 0 && gx < w) v = __ldg(reinterpret_cast<const float4 *>(row + (size_t)gx * c) + q);
+        float *p = dst + (q * 4) * pitch + u;
+        p[0] = v.x;
+        p[pitch] = v.y;
+        p[2 * pitch] = v.z;
+        p[3 * pitch] = v.w;
+    }
+}
+
+template <bool WRITE_VOL, bool WRITE_WTA>
+__global__ __launch_bounds__(512, 1) void corr_ffma_kernel(const float *__restrict__ lmap,
+                                                            const float *__restrict__ rmap, int h, int w,
+                                                            int c, int D, int pb, float *__restrict__ left_vol,
+                                                            float *__restrict__ right_vol,
+                                                            uint8_t *__restrict__ left_disp,
+                                                            uint8_t *__restrict__ right_disp)
+{
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, nthreads = blockDim.x;
+    const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
+    const int side = blockIdx.z & 1, img = blockIdx.z >> 1;
+    const int y = blockIdx.y, x0 = blockIdx.x * kCorrTX;
+    const int nb = kCorrTX + D - 1;
+    const size_t row_off = ((size_t)img * h + y) * w * c;
+    const float *own = (side == 0 ? lmap : rmap) + row_off;
+    const float *oth = (side == 0 ? rmap : lmap) + row_off;
+    const int wstart = side == 0 ? x0 - (D - 1) : x0;
+
+    float *at = smem;                // [c][kPA]
+    float *bt = smem + c * kPA;      // [c][pb]
+    stage_transposed(own, w, c, x0, kCorrTX, at, kPA, tid, nthreads);
+    stage_transposed(oth, w, c, wstart, nb, bt, pb, tid, nthreads);
+    __syncthreads();
+
+    const int a = lane >> 2, b = lane & 3;
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    {
+        const float *ap = at + 4 * a;
+        const float *bp = bt + 32 * warp + 4 * b;
+#pragma unroll 4
+        for (int k = 0; k < c; ++k) {
+            float4 a0 = *reinterpret_cast<const float4 *>(ap + k * kPA);
+            float4 a1 = *reinterpret_cast<const float4 *>(ap + k * kPA + 32);
+            float4 b0 = *reinterpret_cast<const float4 *>(bp + k * pb);
+            float4 b1 = *reinterpret_cast<const float4 *>(bp + k * pb + 16);
+            float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+    }
+    __syncthreads();   // operands are dead: reuse the space for the product block
+
+    float *ss = smem;  // [64][pb]
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        int xi = (i < 4 ? 4 * a + i : 32 + 4 * a + (i - 4));
+        float *p = ss + xi * pb + 32 * warp + 4 * b;
+        *reinterpret_cast<float4 *>(p) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        *reinterpret_cast<float4 *>(p + 16) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+    }
+    __syncthreads();
+
+    // band extraction: left d = xi + D-1 - u, right d = u - xi
+    for (int xi = warp; xi < kCorrTX; xi += nwarps) {
+        int x = x0 + xi;
+        if (x >= w) break;
+        const float *srow = ss + xi * pb;
+        size_t pix = ((size_t)img * h + y) * w + x;
+        float best = 0.f;
+        int best_d = 0x7fffffff;
+        for (int d = lane; d < D; d += 32) {
+            int u = side == 0 ? xi + D - 1 - d : xi + d;
+            float v = srow[u];
+            if (WRITE_VOL) {
+                float *vol = side == 0 ? left_vol : right_vol;
+                vol[pix * D + d] = v;
+            }
+            if (WRITE_WTA) {
+                if (best_d == 0x7fffffff || v > best) { best = v; best_d = d; }
+            }
+        }
+        if (WRITE_WTA) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                float ov = __shfl_xor_sync(0xffffffffu, best, o);
+                int od = __shfl_xor_sync(0xffffffffu, best_d, o);
+                if (od != 0x7fffffff && (best_d == 0x7fffffff || ov > best || (ov == best && od < best_d))) {
+                    best = ov;
+                    best_d = od;
+                }
+            }
+            if (lane == 0) (side == 0 ? left_disp : right_disp)[pix] = (uint8_t)(best_d & 255);
+        }
+    }
+}
+
+int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
+                     int D, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp)
+{
+    STEREO_REQUIRE(c >= 4 && c % 4 == 0, "feature channels must be a positive multiple of 4, got %d", c);
+    int nb = kCorrTX + D - 1;
+    int nwarps = (nb + 31) / 32;
+    int pb = nwarps * 32 + 4;
+    size_t smem = sizeof(float) * (size_t)c * (kPA + pb);
+    size_t smem_prod = sizeof(float) * (size_t)kCorrTX * pb;
+    if (smem_prod > smem) smem = smem_prod;
+    if (nwarps > 16 || smem > 227 * 1024) {
+        set_error("disp_range %d with %d channels exceeds the correlation kernel's tile (needs %zu B shared memory)",
+                  D, c, smem);
+        return STEREO_E_LIMIT;
+    }
+    bool vol = left_vol != nullptr, wta = left_disp != nullptr;
+    STEREO_REQUIRE(vol || wta, "nothing to compute");
+    STEREO_REQUIRE((left_vol == nullptr) == (right_vol == nullptr) && (left_disp == nullptr) == (right_disp == nullptr),
+                   "left and right outputs must be given together");
+    dim3 grid((w + kCorrTX - 1) / kCorrTX, h, 2 * n);
+    auto launch = [&](auto kern) -> int {
+        STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ProfScope prof(ctx, STEREO_K_CORR);
+        kern<<<grid, nwarps * 32, smem, ctx->stream>>>(lmap, rmap, h, w, c, D, pb, left_vol, right_vol,
+                                                      left_disp, right_disp);
+        ctx->launches += 1;
+        STEREO_CUDA_CHECK(cudaGetLastError());
+        return STEREO_OK;
+    };
+    if (vol && wta) return launch(corr_ffma_kernel<true, true>);
+    if (vol) return launch(corr_ffma_kernel<true, false>);
+    return launch(corr_ffma_kernel<false, true>);
+}
+
+// ---- standalone WTA over a materialised volume (inference.py:169-183; post.lua argmin) ----
+// one warp per pixel, coalesced reads along D, shuffle arg-reduction, lowest index wins ties
+__global__ void wta_kernel(const float *__restrict__ vol, size_t npix, int D, int take_min,
+                           uint8_t *__restrict__ disp)
+{
+    int lane = threadIdx.x & 31;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t nwarp = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t p = warp; p < npix; p += nwarp) {
+        const float *row = vol + p * D;
+        float best = 0.f;
+        int best_d = 0x7fffffff;
+        for (int d = lane; d < D; d += 32) {
+            float v = __ldg(row + d);
+            if (take_min) v = -v;
+            if (best_d == 0x7fffffff || v > best) { best = v; best_d = d; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            int od = __shfl_xor_sync(0xffffffffu, best_d, o);
+            if (od != 0x7fffffff && (best_d == 0x7fffffff || ov > best || (ov == best && od < best_d))) {
+                best = ov;
+                best_d = od;
+            }
+        }
+        if (lane == 0) disp[p] = (uint8_t)(best_d & 255);
+    }
+}
+
+int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp)
+{
+    size_t npix = (size_t)n * h * w;
+    int blocks = (int)((npix + 7) / 8);
+    int cap = ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    ProfScope prof(ctx, STEREO_K_WTA);
+    wta_kernel<<<blocks, 256, 0, ctx->stream>>>(vol, npix, D, take_min, disp);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ---- left-right consistency (adcensus.outlier_detection, smooth/nyu.lua:95) ----
+__global__ void lr_check_kernel(const uint8_t *__restrict__ d0, const uint8_t *__restrict__ d1, size_t total,
+                                int w, int D, uint8_t *__restrict__ outlier)
+{
+    size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= total) return;
+    int x = (int)(id % w);
+    int d0i = d0[id];
+    uint8_t res;
+    if (x - d0i < 0) {
+        res = 1;
+    } else if (fabsf((float)d0i - (float)d1[id - d0i]) < 1.1f) {
+        res = 0;
+    } else {
+        res = 1;
+        int dmax = D < x + 1 ? D : x + 1;
+        for (int d = 0; d < dmax; ++d) {
+            if (fabsf((float)d - (float)d1[id - d]) < 1.1f) { res = 2; break; }
+        }
+    }
+    outlier[id] = res;
+}
+
+int launch_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
+                    uint8_t *outlier)
+{
+    size_t total = (size_t)n * h * w;
+    ProfScope prof(ctx, STEREO_K_LR);
+    lr_check_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(d0, d1, total, w, D, outlier);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo

@@ -1,0 +1,217 @@
+"""GPU parity tests of the inference path (T1-T5), all through the C ABI
+(`stereo_matching_b200._lib` is a plain ctypes binding of include/stereo_b200.h).
+
+Gates (BASELINE.json north_star): fp32 cost volume within 1e-4 of the float64
+oracle relative to max|ref|; WTA maps bit-exact except at float ties,
+>= 99.9 % agreement; 3-px error within 0.05 percentage points.
+"""
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+from oracle import post_oracle as po
+from oracle import stereo_oracle as so
+from stereo_matching_b200 import _lib, synth
+from stereo_matching_b200.models.model import base_model, base_model_ws_9
+
+pytestmark = pytest.mark.gpu
+
+COST_TOL = 1e-4      # north star: max|a-b| / max|b|
+WTA_AGREE = 0.999
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    return _lib.Context(0)
+
+
+@pytest.fixture(scope="module")
+def ws9(ws9_layers):
+    m = base_model_ws_9((None, None, 3))
+    m.set_layers(ws9_layers)
+    return m
+
+
+def rel_err(a, b):
+    return float(np.abs(a.astype(np.float64) - b).max() / np.abs(b).max())
+
+
+@pytest.mark.parametrize("shape,patch", [((7, 9), 9), ((33, 70), 9), ((20, 31), 37), ((375, 1242), 9)])
+def test_normalize_pad(ctx, shape, patch):
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, shape + (3,), dtype=np.uint8)
+    ref = so.normalize_and_pad(img, patch)
+    out = ctx.normalize_pad(img, patch)
+    assert out.shape == ref.shape
+    pad = (patch - 1) // 2
+    assert np.all(out[0, :pad] == 0) and np.all(out[0, :, :pad] == 0)
+    np.testing.assert_array_max_ulp(out, ref, maxulp=1)
+
+
+@pytest.mark.parametrize("hw", [(12, 14), (24, 50), (41, 77), (9, 9)])
+def test_trunk_ws9_vs_oracle(ws9, ws9_layers, hw):
+    rng = np.random.default_rng(hw[0])
+    x = rng.standard_normal((2,) + hw + (3,)).astype(np.float32)
+    ref = so.trunk_forward(x, ws9_layers, "win9_dep9", np.float64)
+    out = ws9(x, training=False)
+    assert out.shape == ref.shape == (2, hw[0] - 8, hw[1] - 8, 64)
+    assert rel_err(out, ref) < 1e-5
+
+
+def test_trunk_win37_vs_oracle():
+    layers = synth.make_base_model_weights()
+    m = base_model((None, None, 3))
+    m.set_layers(layers)
+    x = np.random.default_rng(3).standard_normal((1, 45, 60, 3)).astype(np.float32)
+    ref = so.trunk_forward(x, layers, "win37_dep9", np.float64)
+    out = m(x, training=False)
+    assert out.shape == ref.shape == (1, 9, 24, 64)
+    assert rel_err(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("h,w,D", [(3, 10, 6), (4, 70, 12), (2, 64, 64), (3, 129, 201), (2, 300, 228), (2, 20, 33)])
+def test_cost_volume_vs_oracle(ctx, h, w, D):
+    rng = np.random.default_rng(w)
+    L = rng.standard_normal((1, h, w, 64)).astype(np.float32)
+    R = rng.standard_normal((1, h, w, 64)).astype(np.float32)
+    lref, rref = so.cost_volumes(L, R, D, np.float64)
+    lv, rv = ctx.cost_volume(L, R, D)
+    assert rel_err(lv[0], lref) < COST_TOL and rel_err(rv[0], rref) < COST_TOL
+    # the unwritten slots of inference.py:140-141 are exactly zero
+    xs = np.arange(w)[:, None]
+    ds = np.arange(D)[None, :]
+    assert np.all(lv[0][:, xs < ds] == 0)
+    assert np.all(rv[0][:, xs + ds >= w] == 0)
+    # both volumes hold the same numbers (inference.py:149-150)
+    for d in range(0, min(D, w), max(D // 5, 1)):
+        assert np.array_equal(lv[0][:, d:, d], rv[0][:, :w - d, d])
+
+
+def test_wta_matches_numpy_argmax(ctx):
+    rng = np.random.default_rng(0)
+    vol = rng.standard_normal((2, 5, 37, 201)).astype(np.float32)
+    vol[0, 0, 0] = 0.0                    # all ties -> index 0
+    vol[0, 0, 1] = -1.0
+    vol[0, 0, 1, 7] = vol[0, 0, 1, 150] = 3.0   # tie -> lowest index
+    assert np.array_equal(ctx.wta(vol), np.argmax(vol, axis=3).astype(np.uint8))
+    assert np.array_equal(ctx.wta(vol, take_min=True), np.argmin(vol, axis=3).astype(np.uint8))
+
+
+def test_wta_selects_zero_filled_slot_when_all_scores_negative(ctx):
+    L = np.ones((1, 1, 5, 4), np.float32)
+    R = -np.ones((1, 1, 5, 4), np.float32)
+    ld, rd = ctx.corr_wta(L, R, 4)
+    lref, rref = so.cost_volumes(L, R, 4)
+    assert np.array_equal(ld[0], so.wta(lref)) and np.array_equal(rd[0], so.wta(rref))
+    assert list(ld[0, 0]) == [1, 2, 3, 0, 0]
+
+
+@pytest.mark.parametrize("h,w,D", [(6, 150, 64), (3, 200, 228), (2, 90, 201)])
+def test_fused_corr_wta_equals_wta_of_volume(ctx, h, w, D):
+    rng = np.random.default_rng(D)
+    L = rng.standard_normal((2, h, w, 64)).astype(np.float32)
+    R = rng.standard_normal((2, h, w, 64)).astype(np.float32)
+    lv, rv = ctx.cost_volume(L, R, D)
+    ld, rd = ctx.corr_wta(L, R, D)
+    assert np.array_equal(ld, np.argmax(lv, axis=3).astype(np.uint8))
+    assert np.array_equal(rd, np.argmax(rv, axis=3).astype(np.uint8))
+    assert np.array_equal(ld, ctx.wta(lv)) and np.array_equal(rd, ctx.wta(rv))
+
+
+def test_lr_check_bit_exact_on_reference_pngs(ctx, golden_dir):
+    """K5 through the CUDA kernel: results/outlier of the reference."""
+    root = os.path.join(golden_dir, "results")
+    for i in ("000002", "000169", "000192"):
+        l = cv2.imread(os.path.join(root, "nyu_cost_img_2", "%s_10.png" % i), 0)
+        r = cv2.imread(os.path.join(root, "right_nyu_cost_img_2", "%s_10.png" % i), 0)
+        o = cv2.imread(os.path.join(root, "outlier", "%s_10.png" % i), 0)
+        out = ctx.lr_check(l, r, 201)[0]
+        assert np.array_equal(out * 127, o), i
+        assert np.array_equal(out, po.outlier_detection(l.astype(np.float32), r.astype(np.float32), 201).astype(np.uint8))
+
+
+def test_pair_end_to_end_vs_oracle(ctx, ws9, ws9_layers):
+    D = 64
+    l, r, gt = synth.make_pair(1003, 96, 320, D)
+    ref = so.infer_pair(l, r, ws9_layers, "win9_dep9", 9, D, np.float64)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, volumes=True)
+    assert rel_err(out["left_cost"][0], ref["left_cost"]) < COST_TOL
+    assert rel_err(out["right_cost"][0], ref["right_cost"]) < COST_TOL
+    assert (out["left_disp"][0] == ref["left_disp"]).mean() >= WTA_AGREE
+    assert (out["right_disp"][0] == ref["right_disp"]).mean() >= WTA_AGREE
+    e_ref = so.three_pixel_error(ref["left_disp"], gt)
+    e_out = so.three_pixel_error(out["left_disp"][0], gt)
+    assert abs(e_ref - e_out) <= 0.0005            # 0.05 percentage points
+    ref_out = po.outlier_detection(out["left_disp"][0].astype(np.float32), out["right_disp"][0].astype(np.float32), D)
+    assert np.array_equal(out["outlier"][0], ref_out.astype(np.uint8))
+    # fused path (no volumes) gives the same maps
+    out2 = ctx.pairs(_lib.NET_WIN9, l, r, D, volumes=False)
+    assert np.array_equal(out2["left_disp"], out["left_disp"]) and np.array_equal(out2["right_disp"], out["right_disp"])
+
+
+def test_batch_of_pairs_equals_single_pairs(ctx, ws9):
+    D = 40
+    pairs = [synth.make_pair(1100 + i, 30, 100, D) for i in range(3)]
+    L = np.stack([p[0] for p in pairs])
+    R = np.stack([p[1] for p in pairs])
+    out = ctx.pairs(_lib.NET_WIN9, L, R, D)
+    for i in range(3):
+        one = ctx.pairs(_lib.NET_WIN9, L[i], R[i], D)
+        assert np.array_equal(out["left_disp"][i], one["left_disp"][0])
+        assert np.array_equal(out["right_disp"][i], one["right_disp"][0])
+        assert np.array_equal(out["outlier"][i], one["outlier"][0])
+
+
+def test_full_size_properties(ctx, ws9):
+    """BASELINE config 1 (375x1242, D=228) through size-independent properties:
+    the two volumes are the same band indexed two ways, invalid slots are exactly
+    zero, fused WTA equals WTA of the materialised volume, GT recovered."""
+    D = 228
+    l, r, gt = synth.make_pair(1000, 375, 1242, D)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, volumes=True)
+    lv, rv = out["left_cost"][0], out["right_cost"][0]
+    w = 1242
+    for d in (0, 1, 57, 113, 200, 227):
+        assert np.array_equal(lv[:, d:, d], rv[:, :w - d, d])
+        assert np.all(lv[:, :d, d] == 0) and np.all(rv[:, w - d:, d] == 0)
+    assert np.array_equal(out["left_disp"][0], np.argmax(lv, axis=2).astype(np.uint8))
+    assert np.array_equal(out["right_disp"][0], np.argmax(rv, axis=2).astype(np.uint8))
+    fused = ctx.pairs(_lib.NET_WIN9, l, r, D, volumes=False)
+    assert np.array_equal(fused["left_disp"], out["left_disp"])
+    assert so.three_pixel_error(out["left_disp"][0], gt) < 0.2
+    # the float64 oracle on a strip of 8 rows (its padded input rows are 100..115)
+    lp, rp = so.normalize_and_pad(l, 9), so.normalize_and_pad(r, 9)
+    layers = ws9.layers
+    lm = so.trunk_forward(lp[:, 100:116], layers, "win9_dep9", np.float64)
+    rm = so.trunk_forward(rp[:, 100:116], layers, "win9_dep9", np.float64)
+    lref, rref = so.cost_volumes(lm, rm, D, np.float64)
+    assert rel_err(lv[100:108], lref) < COST_TOL and rel_err(rv[100:108], rref) < COST_TOL
+    assert (out["left_disp"][0][100:108] == so.wta(lref)).mean() >= WTA_AGREE
+
+
+def test_error_behaviour(ctx, ws9):
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.cost_volume(np.zeros((1, 2, 8, 64), np.float32), np.zeros((1, 2, 8, 64), np.float32), 0)
+    assert e.value.code == -1
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.cost_volume(np.zeros((1, 2, 8, 6), np.float32), np.zeros((1, 2, 8, 6), np.float32), 4)
+    assert e.value.code == -1
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.cost_volume(np.zeros((1, 1, 8, 64), np.float32), np.zeros((1, 1, 8, 64), np.float32), 2000)
+    assert e.value.code == -5
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.trunk(_lib.NET_WIN9, np.zeros((1, 8, 30, 3), np.float32))
+    assert e.value.code == -1
+    fresh = _lib.Context(0)
+    with pytest.raises(_lib.StereoError) as e:
+        fresh.trunk(_lib.NET_WIN37, np.zeros((1, 40, 40, 3), np.float32))
+    assert e.value.code == -3
+    with pytest.raises(_lib.StereoError):
+        fresh.set_weights(_lib.NET_WIN9, np.zeros(10, np.float32))
+    fresh.close()
+    with pytest.raises(ValueError):
+        ws9(np.zeros((1, 8, 8, 3), np.float32))
+    with pytest.raises(NotImplementedError):
+        ws9(np.zeros((1, 20, 20, 3), np.float32), training=True)
