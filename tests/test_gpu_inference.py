@@ -23,15 +23,16 @@ WTA_AGREE = 0.999
 
 
 @pytest.fixture(scope="module")
-def ctx():
-    return _lib.Context(0)
-
-
-@pytest.fixture(scope="module")
 def ws9(ws9_layers):
     m = base_model_ws_9((None, None, 3))
     m.set_layers(ws9_layers)
     return m
+
+
+@pytest.fixture(scope="module")
+def ctx(ws9):
+    # the context that holds the ckpt-1000 weights
+    return ws9.context
 
 
 def rel_err(a, b):
