@@ -134,6 +134,60 @@ int stereo_pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
                      int n, int h, int w, int D, int precision, uint8_t *left_disp,
                      uint8_t *right_disp, uint8_t *lr_outlier, float *left_vol, float *right_vol);
 
+/* ---- post.lua / smooth/nyu.lua ------------------------------------------------------------
+ * The reference reaches these kernels through the external mc-cnn library
+ * (smooth/init.lua:6).  All volumes here are float32 [h][w][D] (the .bin layout); the
+ * reference's [1][D][h][w] views are a host-side transpose away. */
+typedef struct stereo_post_params {
+    int L1;          /* smooth/nyu.lua:3  cross arm length limit */
+    float tau1;      /* :4  cross intensity threshold */
+    int sgm_i;       /* :7  SGM sweeps */
+    float pi1, pi2, tau_so, alpha1, sgm_q1, sgm_q2; /* :9-14 */
+    int occlusion, subpixel, median, bilateral;     /* :17-20 */
+    float blur_sigma, blur_t;                       /* :21-22 */
+    int nyu_cost_agg_1, sgm, nyu_cost_agg_2, post;  /* post.lua:37-40 */
+} stereo_post_params;
+/* the constants of smooth/nyu.lua:3-22 and the option defaults of post.lua:10-49 */
+int stereo_post_default_params(stereo_post_params *p);
+
+/* post.lua:91-94: byte image -> (x - mean) / std with torch's unbiased std. u8 [h][w] -> f32 [h][w] */
+int stereo_guide_image(stereo_ctx *ctx, const uint8_t *img, int h, int w, float *out);
+
+/* smooth.nyu.cross_agg(l_img, r_img, left_vol, right_vol, iter), smooth/nyu.lua:24-45
+ * (adcensus.cross + adcensus.cbca).  Guide images f32 [h][w]; volumes updated in place. */
+int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img, float *left_vol,
+                         float *right_vol, int h, int w, int D, int iters, const stereo_post_params *p);
+
+/* smooth.nyu.sgm(l_img, r_img, vol, direction), smooth/nyu.lua:47-75 (adcensus.sgm2, 4 paths,
+ * result = accumulated path costs / 4).  direction -1 for the left volume, +1 for the right. */
+int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, float *vol, int h, int w,
+                   int D, int direction, const stereo_post_params *p);
+
+/* smooth.nyu.post(disp, left_vol), smooth/nyu.lua:91-115: outlier_detection,
+ * interpolate_occlusion, interpolate_mismatch, subpixel_enchancement, median2d(5),
+ * mean2d(gaussian(blur_sigma), blur_t).  disp maps f32 [h][w] (0-based disparities);
+ * final f32 [h][w]; outlier f32 [h][w] in {0,1,2}. */
+int stereo_nyu_post(stereo_ctx *ctx, const float *disp_left, const float *disp_right,
+                    const float *left_vol, int h, int w, int D, const stereo_post_params *p,
+                    float *final_disp, float *outlier);
+
+/* post.lua:146-147 `vol:std()`: unbiased std over the whole volume. */
+int stereo_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *std_out);
+
+/* The loop body of post.lua:78-243 for one pair: CBCA -> /std -> negate -> SGM -> CBCA ->
+ * LR check, occlusion / mismatch fill, sub-pixel, median, bilateral.  Inputs are what
+ * inference.py wrote: the two volumes and the two uint8 WTA maps, which post.lua loads as its
+ * guide images (post.lua:91-92).  stages[8] receive the uint8 maps post.lua saves, in order:
+ * nyu_cost_img, right_nyu_cost_img, nyu_sgm_img, right_nyu_sgm_img, nyu_cost_img_2,
+ * right_nyu_cost_img_2, nyu_post, outlier (x127); any entry may be NULL.  final_disp
+ * (optional) receives the float map before the :byte() truncation of post.lua:238. */
+int stereo_post(stereo_ctx *ctx, const float *left_cost, const float *right_cost,
+                const uint8_t *left_disp, const uint8_t *right_disp, int h, int w, int D,
+                const stereo_post_params *p, uint8_t *const stages[8], float *final_disp);
+int stereo_post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_cost,
+                    const uint8_t *left_disp, const uint8_t *right_disp, int h, int w, int D,
+                    const stereo_post_params *p, uint8_t *const stages[8], float *final_disp);
+
 /* Per-kernel timing with CUDA events recorded on the context's stream around every
  * launch of a kernel class (no counterpart in the reference, which only prints
  * torch.tic()/toc() wall times, post.lua:100-235).  Enabling resets the counters;
@@ -145,7 +199,11 @@ enum {
     STEREO_K_CORR = 3,       /* correlation (+ fused WTA) */
     STEREO_K_WTA = 4,        /* standalone arg max / arg min over D */
     STEREO_K_LR = 5,         /* left-right consistency */
-    STEREO_K_COUNT = 6
+    STEREO_K_CBCA = 6,       /* cross-based cost aggregation */
+    STEREO_K_VOLSTD = 7,     /* whole-volume std + scaling */
+    STEREO_K_SGM = 8,        /* semi-global matching, all four paths */
+    STEREO_K_POST_MAPS = 9,  /* guide image, cross arms and the per-pixel post kernels */
+    STEREO_K_COUNT = 10
 };
 int stereo_profile_enable(stereo_ctx *ctx, int on);
 int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches);

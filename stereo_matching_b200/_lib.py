@@ -22,6 +22,22 @@ _c_ctx = ctypes.c_void_p
 _i = ctypes.c_int
 _p = ctypes.c_void_p
 
+
+
+class PostParams(ctypes.Structure):
+    """stereo_post_params: smooth/nyu.lua:3-22 constants + post.lua:37-40 options."""
+    _fields_ = [("L1", _i), ("tau1", ctypes.c_float), ("sgm_i", _i),
+                ("pi1", ctypes.c_float), ("pi2", ctypes.c_float), ("tau_so", ctypes.c_float),
+                ("alpha1", ctypes.c_float), ("sgm_q1", ctypes.c_float), ("sgm_q2", ctypes.c_float),
+                ("occlusion", _i), ("subpixel", _i), ("median", _i), ("bilateral", _i),
+                ("blur_sigma", ctypes.c_float), ("blur_t", ctypes.c_float),
+                ("nyu_cost_agg_1", _i), ("sgm", _i), ("nyu_cost_agg_2", _i), ("post", _i)]
+
+
+_pp = ctypes.POINTER(PostParams)
+STAGE_NAMES = ("nyu_cost_img", "right_nyu_cost_img", "nyu_sgm_img", "right_nyu_sgm_img",
+               "nyu_cost_img_2", "right_nyu_cost_img_2", "nyu_post", "outlier")
+
 # name -> argtypes (restype int unless listed in _RESTYPES); kept in one place so that
 # tests can check that every symbol the header declares is exported and bound
 SIGNATURES = {
@@ -47,13 +63,21 @@ SIGNATURES = {
     "stereo_lr_check_dev": [_c_ctx, _p, _p, _i, _i, _i, _i, _p],
     "stereo_pairs": [_c_ctx, _i, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p],
     "stereo_pairs_dev": [_c_ctx, _i, _p, _p, _i, _i, _i, _i, _i, _p, _p, _p, _p, _p],
+    "stereo_post_default_params": [_pp],
+    "stereo_guide_image": [_c_ctx, _p, _i, _i, _p],
+    "stereo_nyu_cross_agg": [_c_ctx, _p, _p, _p, _p, _i, _i, _i, _i, _pp],
+    "stereo_nyu_sgm": [_c_ctx, _p, _p, _p, _i, _i, _i, _i, _pp],
+    "stereo_nyu_post": [_c_ctx, _p, _p, _p, _i, _i, _i, _pp, _p, _p],
+    "stereo_volume_std": [_c_ctx, _p, ctypes.c_size_t, _p],
+    "stereo_post": [_c_ctx, _p, _p, _p, _p, _i, _i, _i, _pp, ctypes.POINTER(_p), _p],
+    "stereo_post_dev": [_c_ctx, _p, _p, _p, _p, _i, _i, _i, _pp, ctypes.POINTER(_p), _p],
     "stereo_profile_enable": [_c_ctx, _i],
     "stereo_profile_read": [_c_ctx, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
     "stereo_profile_name": [_i],
 }
 _RESTYPES = {"stereo_last_error": ctypes.c_char_p, "stereo_launch_count": ctypes.c_int64,
              "stereo_profile_name": ctypes.c_char_p}
-KERNEL_CLASSES = 6
+KERNEL_CLASSES = 10
 
 _lib = None
 
@@ -100,6 +124,12 @@ def _ptr(a):
 def _arr(a, dtype):
     a = np.ascontiguousarray(a, dtype=dtype)
     return a
+
+
+def default_post_params() -> PostParams:
+    p = PostParams()
+    check(load().stereo_post_default_params(ctypes.byref(p)))
+    return p
 
 
 class Context:
@@ -238,6 +268,71 @@ class Context:
                                      out["right_disp"].ctypes.data, _ptr(out.get("outlier")),
                                      _ptr(out.get("left_cost")), _ptr(out.get("right_cost"))))
         return out
+
+    # -- post chain (post.lua / smooth/nyu.lua); volumes are [h][w][D] float32 --
+    def guide_image(self, img_u8: np.ndarray) -> np.ndarray:
+        img = _arr(img_u8, np.uint8)
+        h, w = img.shape
+        out = np.empty((h, w), np.float32)
+        check(self._lib.stereo_guide_image(self._h, img.ctypes.data, h, w, out.ctypes.data))
+        return out
+
+    def volume_std(self, vol: np.ndarray) -> float:
+        vol = _arr(vol, np.float32)
+        out = np.empty(1, np.float32)
+        check(self._lib.stereo_volume_std(self._h, vol.ctypes.data, vol.size, out.ctypes.data))
+        return out[0]
+
+    def nyu_cross_agg(self, l_img, r_img, left_vol, right_vol, iters: int, params: "PostParams | None" = None):
+        params = params or default_post_params()
+        l_img, r_img = _arr(l_img, np.float32), _arr(r_img, np.float32)
+        lv, rv = np.array(left_vol, np.float32, order="C"), np.array(right_vol, np.float32, order="C")
+        h, w, d = lv.shape
+        check(self._lib.stereo_nyu_cross_agg(self._h, l_img.ctypes.data, r_img.ctypes.data, lv.ctypes.data,
+                                             rv.ctypes.data, h, w, d, int(iters), ctypes.byref(params)))
+        return lv, rv
+
+    def nyu_sgm(self, l_img, r_img, vol, direction: int, params: "PostParams | None" = None):
+        params = params or default_post_params()
+        l_img, r_img = _arr(l_img, np.float32), _arr(r_img, np.float32)
+        v = np.array(vol, np.float32, order="C")
+        h, w, d = v.shape
+        check(self._lib.stereo_nyu_sgm(self._h, l_img.ctypes.data, r_img.ctypes.data, v.ctypes.data, h, w, d,
+                                       int(direction), ctypes.byref(params)))
+        return v
+
+    def nyu_post(self, disp_left, disp_right, left_vol, params: "PostParams | None" = None):
+        params = params or default_post_params()
+        d0, d1 = _arr(disp_left, np.float32), _arr(disp_right, np.float32)
+        v = _arr(left_vol, np.float32)
+        h, w, d = v.shape
+        final = np.empty((h, w), np.float32)
+        outlier = np.empty((h, w), np.float32)
+        check(self._lib.stereo_nyu_post(self._h, d0.ctypes.data, d1.ctypes.data, v.ctypes.data, h, w, d,
+                                        ctypes.byref(params), final.ctypes.data, outlier.ctypes.data))
+        return final, outlier
+
+    def post(self, left_cost, right_cost, left_disp, right_disp, params: "PostParams | None" = None):
+        """post.lua:78-243 for one pair -> {stage name: uint8 map} + 'nyu_post_float'."""
+        params = params or default_post_params()
+        lv, rv = _arr(left_cost, np.float32), _arr(right_cost, np.float32)
+        ld, rd = _arr(left_disp, np.uint8), _arr(right_disp, np.uint8)
+        h, w, d = lv.shape
+        stages = {n: np.empty((h, w), np.uint8) for n in STAGE_NAMES}
+        ptrs = (_p * 8)(*[stages[n].ctypes.data for n in STAGE_NAMES])
+        final = np.empty((h, w), np.float32)
+        check(self._lib.stereo_post(self._h, lv.ctypes.data, rv.ctypes.data, ld.ctypes.data, rd.ctypes.data,
+                                    h, w, d, ctypes.byref(params), ptrs, final.ctypes.data))
+        stages["nyu_post_float"] = final
+        return stages
+
+    def post_dev(self, left_cost, right_cost, left_disp, right_disp, h, w, disp_range, stage_ptrs,
+                 final=None, params: "PostParams | None" = None):
+        params = params or default_post_params()
+        ptrs = (_p * 8)(*[(_ptr(s) if s is not None else None) for s in stage_ptrs])
+        check(self._lib.stereo_post_dev(self._h, _ptr(left_cost), _ptr(right_cost), _ptr(left_disp),
+                                        _ptr(right_disp), h, w, int(disp_range), ctypes.byref(params), ptrs,
+                                        _ptr(final)))
 
     # -- device-pointer entry points (raw addresses; asynchronous) --
     def pairs_dev(self, net, left_rgb, right_rgb, n, h, w, disp_range, precision, left_disp, right_disp,

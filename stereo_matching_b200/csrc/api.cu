@@ -69,7 +69,7 @@ NetDesc net_desc(int net)
     return d;
 }
 
-static int check_ctx(stereo_ctx *ctx)
+int check_ctx(stereo_ctx *ctx)
 {
     if (!ctx) {
         set_error("null context");
@@ -167,7 +167,7 @@ static int d2h(stereo_ctx *ctx, void *dst, const void *src, size_t bytes)
     return STEREO_OK;
 }
 
-static int finish(stereo_ctx *ctx)
+int finish(stereo_ctx *ctx)
 {
     STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     return STEREO_OK;
@@ -223,7 +223,8 @@ int stereo_destroy(stereo_ctx *ctx)
     DevBuf *bufs[] = {&ctx->weights[0], &ctx->weights[1], &ctx->wsplit[0], &ctx->wsplit[1], &ctx->stats,
                       &ctx->padded, &ctx->act[0], &ctx->act[1], &ctx->feat, &ctx->stage_in[0], &ctx->stage_in[1],
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
-                      &ctx->stage_vol[1]};
+                      &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2],
+                      &ctx->post_maps};
     for (DevBuf *b : bufs) b->release();
     if (ctx->prof.start) {
         for (int i = 0; i < Profiler::kMaxPairs; ++i) {
@@ -303,7 +304,8 @@ int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int
 
 const char *stereo_profile_name(int kernel_class)
 {
-    static const char *names[STEREO_K_COUNT] = {"prep", "conv_first", "conv", "corr", "wta", "lr_check"};
+    static const char *names[STEREO_K_COUNT] = {"prep", "conv_first", "conv", "corr", "wta", "lr_check",
+                                                "cbca", "volume_std", "sgm", "post_maps"};
     return kernel_class >= 0 && kernel_class < STEREO_K_COUNT ? names[kernel_class] : "?";
 }
 

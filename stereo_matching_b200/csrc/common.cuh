@@ -89,6 +89,9 @@ struct stereo_ctx {
     stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
     stereo::DevBuf stage_out[3];
     stereo::DevBuf stage_vol[2];
+    stereo::DevBuf scratch;      // per-block partials of the volume reduction
+    stereo::DevBuf post_vol[3];  // working volumes of the post chain
+    stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
 };
 
 namespace stereo {
@@ -124,5 +127,28 @@ int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int 
 int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp);
 int launch_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
                     uint8_t *outlier);
+// post.cu
+struct SgmParams {
+    float pi1, pi2, tau_so, alpha1, q1, q2;
+};
+int launch_guide(stereo_ctx *ctx, const uint8_t *img, int h, int w, float *out);
+int launch_cross(stereo_ctx *ctx, const float *img, int h, int w, int L1, float tau1, short *arms);
+int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
+                int D, int direction);
+int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result);
+int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
+int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,
+               int h, int w, int D, const SgmParams &p, int direction);
+int launch_outlier(stereo_ctx *ctx, const float *d0, const float *d1, int h, int w, int disp_max, float *outlier);
+int launch_interpolate(stereo_ctx *ctx, const float *d0, const float *outlier, int h, int w, float *tmp, float *out);
+int launch_subpixel(stereo_ctx *ctx, const float *d0, const float *vol, int h, int w, int disp_max, float *out);
+int launch_median(stereo_ctx *ctx, const float *img, int h, int w, int kernel_size, float *out);
+int launch_mean2d(stereo_ctx *ctx, const float *img, const float *kernel, int h, int w, int radius, float alpha2,
+                  float *out);
+int launch_u8_to_float(stereo_ctx *ctx, const uint8_t *in, int n, float *out);
+int launch_float_to_u8(stereo_ctx *ctx, const float *in, int n, float scale, uint8_t *out);
+// api.cu helpers shared with post_api.cu
+int check_ctx(stereo_ctx *ctx);
+int finish(stereo_ctx *ctx);
 
 }  // namespace stereo

@@ -1,0 +1,653 @@
+// The post-processing chain of /root/reference/post.lua + smooth/nyu.lua, i.e. the
+// mc-cnn "adcensus" kernels the reference loads from an external library
+// (smooth/init.lua:6), rebuilt for sm_100a.
+//
+// Layout decision: the reference shuttles every volume between [H][W][D] (files,
+// SGM) and [D][H][W] (CBCA, arg-min) with three permute+clone copies per volume
+// (post.lua:119-120, nyu.lua:52,64).  Here every kernel works on [H][W][D] with
+// D fastest - warps run along D, so CBCA gathers, SGM scanline steps and the
+// arg-min all read 128-byte lines - and no transpose is ever made.
+//
+// Arithmetic follows the restated CUDA original operation for operation (same
+// fp32 operations in the same order) so that results match oracle/post_oracle.c
+// bit for bit; the only place where nvcc's FMA contraction is part of the
+// original's arithmetic (mean2d) uses an explicit fmaf, everything else is
+// compiled without contraction.
+#include "common.cuh"
+
+namespace stereo {
+
+// ------------------------------------------------------------------------------------------
+// P0  guide image: byte image -> float, subtract mean, divide by the unbiased std
+//     (post.lua:91-94).  256 possible values -> exact histogram, float64 moments, LUT.
+// ------------------------------------------------------------------------------------------
+struct GuideStats {
+    unsigned long long hist[256];
+    float lut[256];
+};
+
+__global__ void guide_hist_kernel(const uint8_t *__restrict__ img, size_t n, GuideStats *st)
+{
+    __shared__ unsigned int sh[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        atomicAdd(&sh[img[i]], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += blockDim.x)
+        if (sh[i]) atomicAdd(&st->hist[i], (unsigned long long)sh[i]);
+}
+
+__global__ void guide_lut_kernel(GuideStats *st, double n)
+{
+    __shared__ double red[256];
+    int v = threadIdx.x;
+    double cnt = (double)st->hist[v];
+    red[v] = cnt * (double)v;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (v < s) red[v] += red[v + s];
+        __syncthreads();
+    }
+    float mean = (float)(red[0] / n);
+    __syncthreads();
+    float shifted = __fadd_rn((float)v, -mean);          // x:add(-mean) in fp32
+    red[v] = cnt * (double)shifted;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (v < s) red[v] += red[v + s];
+        __syncthreads();
+    }
+    double m2 = red[0] / n;                               // mean of the shifted image (about 0)
+    __syncthreads();
+    red[v] = cnt * ((double)shifted - m2) * ((double)shifted - m2);
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (v < s) red[v] += red[v + s];
+        __syncthreads();
+    }
+    float sd = (float)sqrt(red[0] / (n - 1.0));           // torch :std() is unbiased
+    st->lut[v] = __fdiv_rn(shifted, sd);
+}
+
+__global__ void guide_apply_kernel(const uint8_t *__restrict__ img, size_t n, const GuideStats *__restrict__ st,
+                                   float *__restrict__ out)
+{
+    __shared__ float lut[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = st->lut[i];
+    __syncthreads();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = lut[img[i]];
+}
+
+int launch_guide(stereo_ctx *ctx, const uint8_t *img, int h, int w, float *out)
+{
+    STEREO_TRY(ctx->stats.reserve(sizeof(GuideStats)));
+    GuideStats *st = ctx->stats.as<GuideStats>();
+    size_t n = (size_t)h * w;
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    STEREO_CUDA_CHECK(cudaMemsetAsync(st, 0, sizeof(GuideStats), ctx->stream));
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > ctx->sm_count * 4) blocks = ctx->sm_count * 4;
+    guide_hist_kernel<<<blocks, 256, 0, ctx->stream>>>(img, n, st);
+    guide_lut_kernel<<<1, 256, 0, ctx->stream>>>(st, (double)n);
+    guide_apply_kernel<<<blocks, 256, 0, ctx->stream>>>(img, n, st, out);
+    ctx->launches += 3;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// P1  adcensus.cross (nyu.lua:33-34): four arms per pixel, exclusive end coordinate.
+//     arms[a][y][x], a = 0 left, 1 right, 2 up, 3 down, stored as int16.
+// ------------------------------------------------------------------------------------------
+__global__ void cross_kernel(const float *__restrict__ img, int h, int w, int L1, float tau1,
+                             short *__restrict__ arms)
+{
+    size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t hw = (size_t)h * w;
+    if (id >= 4 * hw) return;
+    int arm = (int)(id / hw);
+    int rem = (int)(id % hw);
+    int x = rem % w, y = rem / w;
+    int dx = 0, dy = 0;
+    if (arm == 0) dx = -1;
+    else if (arm == 1) dx = 1;
+    else if (arm == 2) dy = -1;
+    else dy = 1;
+    float centre = img[rem];
+    int xx = x + dx, yy = y + dy;
+    for (;; xx += dx, yy += dy) {
+        if (xx < 0 || xx >= w || yy < 0 || yy >= h) break;
+        int dist = max(abs(xx - x), abs(yy - y));
+        if (dist == 1) continue;
+        if (fabsf(centre - img[yy * w + xx]) >= tau1) break;
+        if (dist >= L1) break;
+    }
+    arms[id] = (short)(dy == 0 ? xx : yy);
+}
+
+int launch_cross(stereo_ctx *ctx, const float *img, int h, int w, int L1, float tau1, short *arms)
+{
+    size_t total = 4 * (size_t)h * w;
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    cross_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(img, h, w, L1, tau1, arms);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// P2  adcensus.cbca (nyu.lua:37,39) on [H][W][D].  One warp per (pixel, 32 disparities):
+//     the pixel's own arms are warp-uniform, the matched pixel's arms vary per lane; the
+//     loops run over the own-arm window and each lane predicates on its intersection.
+//     Summation order (rows ascending, columns ascending) is that of the original.
+// ------------------------------------------------------------------------------------------
+__global__ __launch_bounds__(256) void cbca_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+                                                   const float *__restrict__ vol, float *__restrict__ out,
+                                                   int h, int w, int D, int direction)
+{
+    const int lane = threadIdx.x & 31;
+    const int chunks = (D + 31) >> 5;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t hw = (size_t)h * w;
+    if (warp >= hw * chunks) return;
+    int chunk = (int)(warp % chunks);
+    size_t pix = warp / chunks;
+    int x = (int)(pix % w), y = (int)(pix / w);
+    int d = chunk * 32 + lane;
+    if (d >= D) return;
+    size_t id = pix * D + d;
+    int xm = x + d * direction;
+    if (xm < 0 || xm >= w) {
+        out[id] = vol[id];
+        return;
+    }
+    const short *a0 = x0c, *a1 = x1c;
+    int up0 = a0[2 * hw + pix], down0 = a0[3 * hw + pix];
+    int yy_s = max(up0, (int)a1[2 * hw + (size_t)y * w + xm]);
+    int yy_t = min(down0, (int)a1[3 * hw + (size_t)y * w + xm]);
+    float sum = 0.f;
+    int cnt = 0;
+    const int shift = d * direction;
+    for (int yy = yy_s + 1; yy < yy_t; ++yy) {
+        size_t rp = (size_t)yy * w;
+        int xx_s = max((int)a0[rp + x], (int)a1[rp + xm] - shift);
+        int xx_t = min((int)a0[hw + rp + x], (int)a1[hw + rp + xm] - shift);
+        const float *vrow = vol + rp * D + d;
+        for (int xx = xx_s + 1; xx < xx_t; ++xx) {
+            sum = __fadd_rn(sum, vrow[(size_t)xx * D]);
+            ++cnt;
+        }
+    }
+    out[id] = __fdiv_rn(sum, (float)cnt);
+}
+
+int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
+                int D, int direction)
+{
+    size_t warps = (size_t)h * w * ((D + 31) / 32);
+    size_t blocks = (warps + 7) / 8;
+    ProfScope prof(ctx, STEREO_K_CBCA);
+    cbca_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(x0c, x1c, vol, out, h, w, D, direction);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// post.lua:146-147  vol / vol:std()  - unbiased std over the whole volume (zero band
+// included).  Two-stage float64 reduction through a scratch array of per-block partials;
+// the partials are combined in a fixed order, so the result is deterministic.
+// result[0] = std (float), result[1] = mean (float)
+// ------------------------------------------------------------------------------------------
+__global__ void volume_moments_kernel(const float *__restrict__ vol, size_t n, double *__restrict__ partial)
+{
+    double s = 0.0, ss = 0.0;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        double v = (double)vol[i];
+        s += v;
+        ss += v * v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_down_sync(0xffffffffu, s, o);
+        ss += __shfl_down_sync(0xffffffffu, ss, o);
+    }
+    __shared__ double sh[2][32];
+    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sh[0][warp] = s; sh[1][warp] = ss; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += sh[0][i]; b += sh[1][i]; }
+        partial[2 * blockIdx.x] = a;
+        partial[2 * blockIdx.x + 1] = b;
+    }
+}
+
+__global__ void volume_std_final_kernel(const double *__restrict__ partial, int nblocks, double n,
+                                        float *__restrict__ result)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double s = 0.0, ss = 0.0;
+    for (int i = 0; i < nblocks; ++i) { s += partial[2 * i]; ss += partial[2 * i + 1]; }
+    double mean = s / n;
+    double var = (ss - s * mean) / (n - 1.0);
+    result[0] = (float)sqrt(var > 0.0 ? var : 0.0);
+    result[1] = (float)mean;
+}
+
+constexpr int kStdBlocks = 1184;   // 148 SMs x 8
+
+int launch_volume_std_with(stereo_ctx *ctx, const float *vol, size_t n, double *partial, float *result)
+{
+    ProfScope prof(ctx, STEREO_K_VOLSTD);
+    volume_moments_kernel<<<kStdBlocks, 256, 0, ctx->stream>>>(vol, n, partial);
+    volume_std_final_kernel<<<1, 32, 0, ctx->stream>>>(partial, kStdBlocks, (double)n, result);
+    ctx->launches += 2;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result)
+{
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * kStdBlocks));
+    return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>(), result);
+}
+
+// elementwise helpers of post.lua:146-153 and nyu.lua:61,64
+__global__ void scale_kernel(const float *__restrict__ in, size_t n, const float *__restrict__ stdp, int mode,
+                             float *__restrict__ out)
+{
+    // mode 0: x / std   mode 1: -(x / std)   mode 2: x / 4
+    float sd = mode == 2 ? 4.f : stdp[0];
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        float v = __fdiv_rn(in[i], sd);
+        out[i] = mode == 1 ? __fmul_rn(v, -1.f) : v;
+    }
+}
+
+int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out)
+{
+    ProfScope prof(ctx, STEREO_K_VOLSTD);
+    scale_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(in, n, stdp, mode, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// P3  adcensus.sgm2 (nyu.lua:59-60): 4-path semi-global matching with intensity-adaptive
+//     penalties.  The original launches one kernel per scanline STEP (2W+2H launches per
+//     volume); here one CTA owns a whole scanline and walks it: thread = disparity, the
+//     previous step's path costs live in shared memory (double buffered, one barrier per
+//     step), the block minimum is a shuffle reduction, and the next step's costs are
+//     prefetched while the current step is computed.
+//     in:  C[h][w][D] cost (optionally C = -(raw / std) applied on the fly)
+//     out: accumulates the path cost; with `first` the kernel writes instead of adding and
+//          with `last` it writes (acc + Lr) / 4, fusing nyu.lua:61,64.
+// ------------------------------------------------------------------------------------------
+template <int SD>
+__global__ __launch_bounds__(512) void sgm_path_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
+                                                       const float *__restrict__ vol,
+                                                       const float *__restrict__ stdp, float *__restrict__ out,
+                                                       int h, int w, int D, SgmParams p, int direction,
+                                                       int first, int last)
+{
+    extern __shared__ float sm[];
+    const int d = threadIdx.x;
+    const int nt = blockDim.x;
+    const int nwarp = nt >> 5;
+    float *prev_s = sm;                 // [2][nt + 2] with a guard element on both sides
+    float *wmin_s = sm + 2 * (nt + 2);  // [2][32]
+    const bool active = d < D;
+
+    constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
+    constexpr int dy = SD == 2 ? 1 : (SD == 3 ? -1 : 0);
+    const int line = blockIdx.x;
+    const int steps = dy == 0 ? w : h;
+    int x = dy == 0 ? (SD == 0 ? 0 : w - 1) : line;
+    int y = dy == 0 ? line : (SD == 2 ? 0 : h - 1);
+
+    const float sd = stdp ? stdp[0] : 1.f;
+    auto load_cost = [&](int yy, int xx) -> float {
+        if (!active) return 0.f;
+        float v = vol[((size_t)yy * w + xx) * D + d];
+        if (stdp) v = __fmul_rn(__fdiv_rn(v, sd), -1.f);   // post.lua:146,152: (x / std) * -1
+        return v;
+    };
+    // penalties (the three cases of the original, with and without the alpha1 division)
+    const float P1a = p.pi1, P2a = p.pi2;
+    const float P1b = __fdiv_rn(p.pi1, __fmul_rn(p.q1, p.q2)), P2b = __fdiv_rn(p.pi2, __fmul_rn(p.q1, p.q2));
+    const float P1c = __fdiv_rn(p.pi1, p.q1), P2c = __fdiv_rn(p.pi2, p.q1);
+
+    // Costs (and, for the accumulating passes, the running sums) are fetched a whole
+    // group of steps ahead so that enough loads are in flight to cover HBM latency.
+    constexpr int PF = 8;
+    auto load_acc = [&](int yy, int xx) -> float {
+        return (active && !first) ? out[((size_t)yy * w + xx) * D + d] : 0.f;
+    };
+    float cbuf[PF], obuf[PF];
+#pragma unroll
+    for (int i = 0; i < PF; ++i) {
+        bool ok = i < steps;
+        cbuf[i] = ok ? load_cost(y + i * dy, x + i * dx) : 0.f;
+        obuf[i] = ok ? load_acc(y + i * dy, x + i * dx) : 0.f;
+    }
+    float i1_prev = 0.f;     // x1 at the matched pixel of the previous step
+    int buf = 0;
+    for (int g = 0; g < steps; g += PF) {
+        float cn[PF], on[PF];
+#pragma unroll
+        for (int i = 0; i < PF; ++i) {
+            bool ok = g + PF + i < steps;
+            cn[i] = ok ? load_cost(y + (PF + i) * dy, x + (PF + i) * dx) : 0.f;
+            on[i] = ok ? load_acc(y + (PF + i) * dy, x + (PF + i) * dx) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < PF; ++i) {
+            const int step = g + i;
+            if (step >= steps) break;
+            const float cost = cbuf[i];
+            const int xx = x + d * direction;
+            const bool xx_ok = active && xx >= 0 && xx < w;
+            float i1_cur = xx_ok ? x1[(size_t)y * w + xx] : 0.f;
+            float val;
+            if (step == 0) {
+                val = cost;
+            } else {
+                const float *pv = prev_s + buf * (nt + 2) + 1;
+                float pmin = wmin_s[buf * 32];
+                for (int k = 1; k < nwarp; ++k) pmin = fminf(pmin, wmin_s[buf * 32 + k]);
+                float D1 = fabsf(x0[(size_t)y * w + x] - x0[(size_t)(y - dy) * w + (x - dx)]);
+                float D2;
+                // the matched pixel of the previous step is (xx - dx, y - dy); its x1 value
+                // was kept in a register
+                if (!xx_ok || xx - dx < 0 || xx - dx >= w) D2 = 10.f;
+                else D2 = fabsf(i1_cur - i1_prev);
+                float P1, P2;
+                if (D1 < p.tau_so && D2 < p.tau_so) { P1 = P1a; P2 = P2a; }
+                else if (D1 > p.tau_so && D2 > p.tau_so) { P1 = P1b; P2 = P2b; }
+                else { P1 = P1c; P2 = P2c; }
+                float c = fminf(pv[d], __fadd_rn(pmin, P2));
+                if (d - 1 >= 0) c = fminf(c, __fadd_rn(pv[d - 1], SD == 2 ? __fdiv_rn(P1, p.alpha1) : P1));
+                if (d + 1 < D) c = fminf(c, __fadd_rn(pv[d + 1], SD == 3 ? __fdiv_rn(P1, p.alpha1) : P1));
+                val = __fadd_rn(__fadd_rn(cost, c), -pmin);
+            }
+            if (active) {
+                size_t o = ((size_t)y * w + x) * D + d;
+                float acc = first ? val : __fadd_rn(obuf[i], val);
+                out[o] = last ? __fdiv_rn(acc, 4.f) : acc;
+            }
+            // publish this step's path costs for the next one
+            buf ^= 1;
+            prev_s[buf * (nt + 2) + 1 + d] = val;
+            float m = active ? val : 3.402823466e38f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if ((d & 31) == 0) wmin_s[buf * 32 + (d >> 5)] = m;
+            __syncthreads();
+            i1_prev = i1_cur;
+            x += dx;
+            y += dy;
+        }
+#pragma unroll
+        for (int i = 0; i < PF; ++i) { cbuf[i] = cn[i]; obuf[i] = on[i]; }
+    }
+}
+
+int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,
+               int h, int w, int D, const SgmParams &p, int direction)
+{
+    int nt = (D + 31) / 32 * 32;
+    if (nt > 512) {
+        set_error("SGM supports disp_range <= 512 (one thread per disparity), got %d", D);
+        return STEREO_E_LIMIT;
+    }
+    size_t smem = sizeof(float) * (2 * (nt + 2) + 64);
+    ProfScope prof(ctx, STEREO_K_SGM);
+    sgm_path_kernel<0><<<h, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 1, 0);
+    sgm_path_kernel<1><<<h, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
+    sgm_path_kernel<2><<<w, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
+    sgm_path_kernel<3><<<w, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 1);
+    ctx->launches += 4;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// P5-P9  per-pixel map kernels (nyu.lua:91-115)
+// ------------------------------------------------------------------------------------------
+__global__ void outlier_kernel(const float *__restrict__ d0, const float *__restrict__ d1, int total, int w,
+                               int disp_max, float *__restrict__ outlier)
+{
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= total) return;
+    int x = id % w;
+    int d0i = (int)d0[id];
+    float res;
+    if (x - d0i < 0) {
+        res = 1.f;
+    } else if (fabsf(d0[id] - d1[id - d0i]) < 1.1f) {
+        res = 0.f;
+    } else {
+        res = 1.f;
+        for (int d = 0; d < disp_max; ++d)
+            if (x - d >= 0 && fabsf((float)d - d1[id - d]) < 1.1f) { res = 2.f; break; }
+    }
+    outlier[id] = res;
+}
+
+__global__ void interpolate_occlusion_kernel(const float *__restrict__ d0, const float *__restrict__ outlier,
+                                             int total, int w, float *__restrict__ out)
+{
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= total) return;
+    if (outlier[id] != 1.f) { out[id] = d0[id]; return; }
+    int x = id % w;
+    int dx = 0;
+    while (x + dx >= 0 && outlier[id + dx] != 0.f) --dx;
+    if (x + dx < 0) {
+        dx = 0;
+        while (x + dx < w && outlier[id + dx] != 0.f) ++dx;
+    }
+    out[id] = x + dx < w ? d0[id + dx] : d0[id];
+}
+
+__device__ __forceinline__ void insertion_sort(float *v, int n)
+{
+    for (int i = 1; i < n; ++i) {
+        float t = v[i];
+        int j = i - 1;
+        while (j >= 0 && v[j] > t) { v[j + 1] = v[j]; --j; }
+        v[j + 1] = t;
+    }
+}
+
+__global__ void interpolate_mismatch_kernel(const float *__restrict__ d0, const float *__restrict__ outlier,
+                                            int h, int w, float *__restrict__ out)
+{
+    const float dirs[32] = {0.f, 1.f, -0.5f, 1.f, -1.f, 1.f, -1.f, 0.5f, -1.f, 0.f, -1.f, -0.5f, -1.f, -1.f, -0.5f, -1.f,
+                            0.f, -1.f, 0.5f, -1.f, 1.f, -1.f, 1.f, -0.5f, 1.f, 0.f, 1.f, 0.5f, 1.f, 1.f, 0.5f, 1.f};
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= h * w) return;
+    if (outlier[id] != 2.f) { out[id] = d0[id]; return; }
+    float vals[16];
+    int n = 0;
+    int x = id % w, y = id / w;
+    for (int k = 0; k < 16; ++k) {
+        float ddx = dirs[2 * k], ddy = dirs[2 * k + 1];
+        float xx = (float)x, yy = (float)y;
+        int xi = (int)roundf(xx), yi = (int)roundf(yy);
+        while (0 <= yi && yi < h && 0 <= xi && xi < w && outlier[yi * w + xi] == 2.f) {
+            xx = __fadd_rn(xx, ddx);
+            yy = __fadd_rn(yy, ddy);
+            xi = (int)roundf(xx);
+            yi = (int)roundf(yy);
+        }
+        if (0 <= yi && yi < h && 0 <= xi && xi < w) vals[n++] = d0[yi * w + xi];
+    }
+    if (n == 0) { out[id] = d0[id]; return; }
+    insertion_sort(vals, n);
+    out[id] = vals[n / 2];
+}
+
+__global__ void subpixel_kernel(const float *__restrict__ d0, const float *__restrict__ vol, int total,
+                                int disp_max, float *__restrict__ out)
+{
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= total) return;
+    int d = (int)d0[id];
+    float res = (float)d;
+    if (1 <= d && d < disp_max - 1) {
+        const float *c = vol + (size_t)id * disp_max + d;      // [H][W][D] layout
+        float cn = c[-1], cz = c[0], cp = c[1];
+        float denom = __fmul_rn(2.f, __fadd_rn(__fadd_rn(cp, cn), -__fmul_rn(2.f, cz)));
+        if (denom > 1e-5f) {
+            float t = __fdiv_rn(__fadd_rn(cp, -cn), denom);
+            t = t < -1.f ? -1.f : (t > 1.f ? 1.f : t);
+            res = __fadd_rn((float)d, -t);
+        }
+    }
+    out[id] = res;
+}
+
+__global__ void median2d_kernel(const float *__restrict__ img, int h, int w, int radius, float *__restrict__ out)
+{
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= h * w) return;
+    int x = id % w, y = id / w;
+    float xs[11 * 11];
+    int n = 0;
+    for (int xx = x - radius; xx <= x + radius; ++xx)
+        for (int yy = y - radius; yy <= y + radius; ++yy)
+            if (0 <= xx && xx < w && 0 <= yy && yy < h) xs[n++] = img[yy * w + xx];
+    insertion_sort(xs, n);
+    out[id] = xs[n / 2];
+}
+
+// mean2d: 16 x 16 pixel tile + halo staged in shared memory; taps walk columns then rows
+// like the original so that the fp32 sums associate identically.
+constexpr int kBlurTile = 16;
+
+__global__ void mean2d_kernel(const float *__restrict__ img, const float *__restrict__ kernel, int h, int w,
+                              int radius, float alpha2, float *__restrict__ out)
+{
+    extern __shared__ float sm[];
+    const int side = kBlurTile + 2 * radius;
+    const int ksz = 2 * radius + 1;
+    float *tile = sm;                  // [side][side + 1], NaN outside the image
+    float *ker = sm + side * (side + 1);
+    const int x0 = blockIdx.x * kBlurTile - radius, y0 = blockIdx.y * kBlurTile - radius;
+    for (int i = threadIdx.y * kBlurTile + threadIdx.x; i < side * side; i += kBlurTile * kBlurTile) {
+        int ty = i / side, tx = i % side;
+        int gx = x0 + tx, gy = y0 + ty;
+        tile[ty * (side + 1) + tx] = (gx >= 0 && gx < w && gy >= 0 && gy < h) ? img[gy * w + gx] : __int_as_float(0x7fc00000);
+    }
+    for (int i = threadIdx.y * kBlurTile + threadIdx.x; i < ksz * ksz; i += kBlurTile * kBlurTile) ker[i] = kernel[i];
+    __syncthreads();
+    int x = blockIdx.x * kBlurTile + threadIdx.x, y = blockIdx.y * kBlurTile + threadIdx.y;
+    if (x >= w || y >= h) return;
+    float centre = tile[(threadIdx.y + radius) * (side + 1) + threadIdx.x + radius];
+    float sum = 0.f, cnt = 0.f;
+    int i = 0;
+    for (int ox = 0; ox < ksz; ++ox)
+        for (int oy = 0; oy < ksz; ++oy, ++i) {
+            float v = tile[(threadIdx.y + oy) * (side + 1) + threadIdx.x + ox];
+            if (fabsf(v - centre) < alpha2) {        // false for the NaN padding
+                sum = fmaf(v, ker[i], sum);          // the original is built with -fmad=true
+                cnt = __fadd_rn(cnt, ker[i]);
+            }
+        }
+    out[y * w + x] = __fdiv_rn(sum, cnt);
+}
+
+__global__ void u8_to_float_kernel(const uint8_t *__restrict__ in, int n, float *__restrict__ out)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (float)in[i];
+}
+
+__global__ void float_to_u8_kernel(const float *__restrict__ in, int n, float scale, uint8_t *__restrict__ out)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (uint8_t)(int)__fmul_rn(in[i], scale);     // :byte() truncation
+}
+
+static inline unsigned blocks_for(int n) { return (unsigned)((n + 255) / 256); }
+
+int launch_outlier(stereo_ctx *ctx, const float *d0, const float *d1, int h, int w, int disp_max, float *outlier)
+{
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    outlier_kernel<<<blocks_for(h * w), 256, 0, ctx->stream>>>(d0, d1, h * w, w, disp_max, outlier);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_interpolate(stereo_ctx *ctx, const float *d0, const float *outlier, int h, int w, float *tmp, float *out)
+{
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    interpolate_occlusion_kernel<<<blocks_for(h * w), 256, 0, ctx->stream>>>(d0, outlier, h * w, w, tmp);
+    interpolate_mismatch_kernel<<<blocks_for(h * w), 256, 0, ctx->stream>>>(tmp, outlier, h, w, out);
+    ctx->launches += 2;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_subpixel(stereo_ctx *ctx, const float *d0, const float *vol, int h, int w, int disp_max, float *out)
+{
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    subpixel_kernel<<<blocks_for(h * w), 256, 0, ctx->stream>>>(d0, vol, h * w, disp_max, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_median(stereo_ctx *ctx, const float *img, int h, int w, int kernel_size, float *out)
+{
+    STEREO_REQUIRE(kernel_size >= 1 && kernel_size <= 11, "median kernel size must be in [1, 11], got %d", kernel_size);
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    median2d_kernel<<<blocks_for(h * w), 256, 0, ctx->stream>>>(img, h, w, kernel_size / 2, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_mean2d(stereo_ctx *ctx, const float *img, const float *kernel, int h, int w, int radius, float alpha2,
+                  float *out)
+{
+    int side = kBlurTile + 2 * radius, ksz = 2 * radius + 1;
+    size_t smem = sizeof(float) * ((size_t)side * (side + 1) + (size_t)ksz * ksz);
+    if (smem > 200 * 1024) {
+        set_error("bilateral radius %d needs %zu B of shared memory", radius, smem);
+        return STEREO_E_LIMIT;
+    }
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(mean2d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((w + kBlurTile - 1) / kBlurTile, (h + kBlurTile - 1) / kBlurTile);
+    ProfScope prof(ctx, STEREO_K_POST_MAPS);
+    mean2d_kernel<<<grid, dim3(kBlurTile, kBlurTile), smem, ctx->stream>>>(img, kernel, h, w, radius, alpha2, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_u8_to_float(stereo_ctx *ctx, const uint8_t *in, int n, float *out)
+{
+    u8_to_float_kernel<<<blocks_for(n), 256, 0, ctx->stream>>>(in, n, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_float_to_u8(stereo_ctx *ctx, const float *in, int n, float scale, uint8_t *out)
+{
+    float_to_u8_kernel<<<blocks_for(n), 256, 0, ctx->stream>>>(in, n, scale, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo

@@ -1,0 +1,374 @@
+// Entry points of the post chain (post.lua + smooth/nyu.lua): parameter defaults, the
+// three smooth.nyu.* functions as host-pointer calls, and the whole per-pair pipeline.
+#include <cmath>
+#include <vector>
+
+#include "common.cuh"
+
+namespace stereo {
+
+static int check_params(const stereo_post_params *p, int h, int w, int D)
+{
+    STEREO_REQUIRE(p != nullptr, "null post parameters");
+    STEREO_REQUIRE(h > 0 && w > 0 && D > 0, "h, w, D must be positive (got %d, %d, %d)", h, w, D);
+    STEREO_REQUIRE(p->L1 >= 1 && p->sgm_i >= 1, "L1 and sgm_i must be >= 1");
+    STEREO_REQUIRE(w < 32768 && h < 32768, "image dimensions must fit the int16 arm encoding");
+    return STEREO_OK;
+}
+
+static SgmParams sgm_params(const stereo_post_params *p)
+{
+    return SgmParams{p->pi1, p->pi2, p->tau_so, p->alpha1, p->sgm_q1, p->sgm_q2};
+}
+
+// smooth/nyu.lua:77-89 gaussian(sigma): double arithmetic, stored as float (:cuda())
+static std::vector<float> gaussian_kernel(float sigma, int *radius)
+{
+    int kr = (int)std::ceil((double)sigma * 3.0);
+    int ks = 2 * kr + 1;
+    std::vector<float> k((size_t)ks * ks);
+    double s = (double)sigma;
+    for (int i = 0; i < ks; ++i)
+        for (int j = 0; j < ks; ++j) {
+            double y = i - kr, x = j - kr;
+            k[(size_t)i * ks + j] = (float)std::exp(-(x * x + y * y) / (2.0 * s * s));
+        }
+    *radius = kr;
+    return k;
+}
+
+// Carve the small per-pair buffers out of one allocation.
+struct PostMaps {
+    float *guide_l, *guide_r, *d0, *d1, *t0, *t1, *outlier, *stdp, *gauss;
+    short *arms_l, *arms_r;
+    uint8_t *u8a, *u8b;
+};
+
+static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
+{
+    size_t hw = (size_t)h * w;
+    size_t hw4 = (hw + 3) & ~(size_t)3;
+    size_t g4 = ((size_t)gauss_n + 3) & ~(size_t)3;
+    size_t bytes = sizeof(float) * (7 * hw4 + 4 + g4) + sizeof(short) * 8 * hw4 + 2 * hw4;
+    STEREO_TRY(ctx->post_maps.reserve(bytes));
+    float *f = ctx->post_maps.as<float>();
+    m->guide_l = f; f += hw4;
+    m->guide_r = f; f += hw4;
+    m->d0 = f; f += hw4;
+    m->d1 = f; f += hw4;
+    m->t0 = f; f += hw4;
+    m->t1 = f; f += hw4;
+    m->outlier = f; f += hw4;
+    m->stdp = f; f += 4;
+    m->gauss = f; f += g4;
+    short *s = reinterpret_cast<short *>(f);
+    m->arms_l = s; s += 4 * hw4;
+    m->arms_r = s; s += 4 * hw4;
+    uint8_t *u = reinterpret_cast<uint8_t *>(s);
+    m->u8a = u; u += hw4;
+    m->u8b = u;
+    return STEREO_OK;
+}
+
+// nyu.lua:91-115 on device maps
+static int nyu_post_dev(stereo_ctx *ctx, PostMaps &m, const float *left_vol, int h, int w, int D,
+                        const stereo_post_params *p, float **final_out)
+{
+    STEREO_TRY(launch_outlier(ctx, m.d0, m.d1, h, w, D, m.outlier));
+    float *cur = m.d0, *other = m.t0;
+    if (p->occlusion == 1) {
+        STEREO_TRY(launch_interpolate(ctx, cur, m.outlier, h, w, m.t1, other));
+        std::swap(cur, other);
+    }
+    if (p->subpixel == 1) {
+        STEREO_TRY(launch_subpixel(ctx, cur, left_vol, h, w, D, other));
+        std::swap(cur, other);
+    }
+    if (p->median == 1) {
+        STEREO_TRY(launch_median(ctx, cur, h, w, 5, other));
+        std::swap(cur, other);
+    }
+    if (p->bilateral == 1) {
+        int radius = 0;
+        std::vector<float> k = gaussian_kernel(p->blur_sigma, &radius);
+        STEREO_CUDA_CHECK(cudaMemcpyAsync(m.gauss, k.data(), sizeof(float) * k.size(), cudaMemcpyHostToDevice,
+                                          ctx->stream));
+        // the host vector must outlive the copy
+        STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+        STEREO_TRY(launch_mean2d(ctx, cur, m.gauss, h, w, radius, p->blur_t, other));
+        std::swap(cur, other);
+    }
+    *final_out = cur;
+    return STEREO_OK;
+}
+
+static int gauss_count(const stereo_post_params *p)
+{
+    int kr = (int)std::ceil((double)p->blur_sigma * 3.0);
+    return (2 * kr + 1) * (2 * kr + 1);
+}
+
+static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_cost, const uint8_t *left_disp,
+                    const uint8_t *right_disp, int h, int w, int D, const stereo_post_params *p,
+                    uint8_t *const stages[8], float *final_disp)
+{
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(left_cost && right_cost && left_disp && right_disp && stages, "null pointer");
+    STEREO_REQUIRE(D <= 256, "the post chain keeps disparity maps as bytes like post.lua (:byte()); D=%d > 256", D);
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    PostMaps m;
+    STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    STEREO_TRY(launch_guide(ctx, left_disp, h, w, m.guide_l));
+    STEREO_TRY(launch_guide(ctx, right_disp, h, w, m.guide_r));
+    STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
+    STEREO_TRY(launch_cross(ctx, m.guide_r, h, w, p->L1, p->tau1, m.arms_r));
+    const SgmParams sp = sgm_params(p);
+
+    // Three working volumes.  Every stage reads `cur` and writes a free buffer; the buffer it
+    // read goes back to the free list unless it is the caller's (read-only) input.  The left
+    // result keeps one buffer (sub-pixel refinement needs it), the right side uses the other two.
+    std::vector<float *> pool = {ctx->post_vol[0].as<float>(), ctx->post_vol[1].as<float>(),
+                                 ctx->post_vol[2].as<float>()};
+    const float *left_final = nullptr;
+    for (int side = 0; side < 2; ++side) {
+        const int direction = side == 0 ? -1 : 1;
+        const float *input = side == 0 ? left_cost : right_cost;
+        const float *cur = input;
+        auto advance = [&](float *dst) {
+            if (cur != input) pool.push_back(const_cast<float *>(cur));
+            cur = dst;
+        };
+        auto take = [&]() {
+            float *dst = pool.back();
+            pool.pop_back();
+            return dst;
+        };
+        // nyu_cost_agg_1 (post.lua:116-133); both volumes are called with (x0c, x1c), nyu.lua:37,39
+        for (int i = 0; i < p->nyu_cost_agg_1; ++i) {
+            float *dst = take();
+            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, cur, dst, h, w, D, direction));
+            advance(dst);
+        }
+        if (p->nyu_cost_agg_1 > 0 && stages[side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
+        // post.lua:146-147: lu = lu / lu:std()  (fused into the SGM cost load when SGM runs)
+        float *stdp = m.stdp + side * 2;
+        STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp));
+        if (p->sgm == 1) {
+            // post.lua:152-155 + nyu.lua:47-75
+            for (int it = 0; it < p->sgm_i; ++it) {
+                float *dst = take();
+                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, it == 0 ? stdp : nullptr, dst, h, w, D, sp,
+                                      direction));
+                advance(dst);
+            }
+            if (stages[2 + side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[2 + side]));
+        } else {
+            float *dst = take();
+            STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 0, dst));
+            advance(dst);
+        }
+        // nyu_cost_agg_2 (post.lua:171-186)
+        for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
+            float *dst = take();
+            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, cur, dst, h, w, D, direction));
+            advance(dst);
+        }
+        if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
+            STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[4 + side]));
+        // post.lua:226-229: disp = argmin - 1 (0-based here)
+        STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, side == 0 ? m.u8a : m.u8b));
+        if (side == 0) left_final = cur;       // stays out of the pool
+        else if (cur != input) pool.push_back(const_cast<float *>(cur));
+    }
+    if (p->post == 1) {
+        STEREO_TRY(launch_u8_to_float(ctx, m.u8a, (int)hw, m.d0));
+        STEREO_TRY(launch_u8_to_float(ctx, m.u8b, (int)hw, m.d1));
+        float *fin = nullptr;
+        STEREO_TRY(nyu_post_dev(ctx, m, left_final, h, w, D, p, &fin));
+        if (stages[6]) STEREO_TRY(launch_float_to_u8(ctx, fin, (int)hw, 1.f, stages[6]));
+        if (stages[7]) STEREO_TRY(launch_float_to_u8(ctx, m.outlier, (int)hw, 127.f, stages[7]));
+        if (final_disp)
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(final_disp, fin, sizeof(float) * hw, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return STEREO_OK;
+}
+
+static int to_dev(stereo_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return STEREO_OK;
+}
+
+static int to_host(stereo_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return STEREO_OK;
+}
+
+}  // namespace stereo
+
+using namespace stereo;
+
+extern "C" {
+
+int stereo_post_default_params(stereo_post_params *p)
+{
+    STEREO_REQUIRE(p != nullptr, "null pointer");
+    p->L1 = 5;
+    p->tau1 = 0.03f;
+    p->sgm_i = 1;
+    p->pi1 = 2.3f;
+    p->pi2 = 24.25f;
+    p->tau_so = 0.08f;
+    p->alpha1 = 1.75f;
+    p->sgm_q1 = 3.f;
+    p->sgm_q2 = 2.f;
+    p->occlusion = 1;
+    p->subpixel = 1;
+    p->median = 1;
+    p->bilateral = 1;
+    p->blur_sigma = 5.99f;
+    p->blur_t = 5.f;
+    p->nyu_cost_agg_1 = 1;
+    p->sgm = 1;
+    p->nyu_cost_agg_2 = 1;
+    p->post = 1;
+    return STEREO_OK;
+}
+
+int stereo_guide_image(stereo_ctx *ctx, const uint8_t *img, int h, int w, float *out)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(img && out && h > 0 && w > 0, "bad argument");
+    size_t hw = (size_t)h * w;
+    STEREO_TRY(ctx->stage_in[0].reserve(hw));
+    STEREO_TRY(ctx->stage_vol[0].reserve(sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, ctx->stage_in[0].ptr, img, hw));
+    STEREO_TRY(launch_guide(ctx, ctx->stage_in[0].as<uint8_t>(), h, w, ctx->stage_vol[0].as<float>()));
+    STEREO_TRY(to_host(ctx, out, ctx->stage_vol[0].ptr, sizeof(float) * hw));
+    return finish(ctx);
+}
+
+int stereo_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *std_out)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(vol && std_out && n > 1, "bad argument");
+    STEREO_TRY(ctx->stage_vol[0].reserve(sizeof(float) * n));
+    STEREO_TRY(ctx->stage_out[0].reserve(16));
+    STEREO_TRY(to_dev(ctx, ctx->stage_vol[0].ptr, vol, sizeof(float) * n));
+    STEREO_TRY(launch_volume_std(ctx, ctx->stage_vol[0].as<float>(), n, ctx->stage_out[0].as<float>()));
+    STEREO_TRY(to_host(ctx, std_out, ctx->stage_out[0].ptr, sizeof(float)));
+    return finish(ctx);
+}
+
+int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img, float *left_vol, float *right_vol,
+                         int h, int w, int D, int iters, const stereo_post_params *p)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(l_img && r_img && left_vol && right_vol && iters >= 0, "bad argument");
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    PostMaps m;
+    STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
+    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
+    STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
+    STEREO_TRY(launch_cross(ctx, m.guide_r, h, w, p->L1, p->tau1, m.arms_r));
+    for (int side = 0; side < 2; ++side) {
+        float *host = side == 0 ? left_vol : right_vol;
+        float *a = ctx->post_vol[0].as<float>(), *b = ctx->post_vol[1].as<float>();
+        STEREO_TRY(to_dev(ctx, a, host, sizeof(float) * nvox));
+        for (int i = 0; i < iters; ++i) {
+            // both calls pass (x0c, x1c), nyu.lua:37,39
+            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, a, b, h, w, D, side == 0 ? -1 : 1));
+            std::swap(a, b);
+        }
+        STEREO_TRY(to_host(ctx, host, a, sizeof(float) * nvox));
+        STEREO_TRY(finish(ctx));
+    }
+    return STEREO_OK;
+}
+
+int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, float *vol, int h, int w, int D,
+                   int direction, const stereo_post_params *p)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(l_img && r_img && vol && (direction == -1 || direction == 1), "bad argument");
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    PostMaps m;
+    STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
+    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
+    float *a = ctx->post_vol[0].as<float>(), *b = ctx->post_vol[1].as<float>();
+    STEREO_TRY(to_dev(ctx, a, vol, sizeof(float) * nvox));
+    const SgmParams sp = sgm_params(p);
+    for (int it = 0; it < p->sgm_i; ++it) {
+        STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, a, nullptr, b, h, w, D, sp, direction));
+        std::swap(a, b);
+    }
+    STEREO_TRY(to_host(ctx, vol, a, sizeof(float) * nvox));
+    return finish(ctx);
+}
+
+int stereo_nyu_post(stereo_ctx *ctx, const float *disp_left, const float *disp_right, const float *left_vol, int h,
+                    int w, int D, const stereo_post_params *p, float *final_disp, float *outlier)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(disp_left && disp_right && left_vol && final_disp && outlier, "null pointer");
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    PostMaps m;
+    STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
+    STEREO_TRY(ctx->post_vol[0].reserve(sizeof(float) * nvox));
+    STEREO_TRY(to_dev(ctx, m.d0, disp_left, sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, m.d1, disp_right, sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, ctx->post_vol[0].ptr, left_vol, sizeof(float) * nvox));
+    float *fin = nullptr;
+    STEREO_TRY(nyu_post_dev(ctx, m, ctx->post_vol[0].as<float>(), h, w, D, p, &fin));
+    STEREO_TRY(to_host(ctx, final_disp, fin, sizeof(float) * hw));
+    STEREO_TRY(to_host(ctx, outlier, m.outlier, sizeof(float) * hw));
+    return finish(ctx);
+}
+
+int stereo_post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_cost, const uint8_t *left_disp,
+                    const uint8_t *right_disp, int h, int w, int D, const stereo_post_params *p,
+                    uint8_t *const stages[8], float *final_disp)
+{
+    STEREO_TRY(check_ctx(ctx));
+    return post_dev(ctx, left_cost, right_cost, left_disp, right_disp, h, w, D, p, stages, final_disp);
+}
+
+int stereo_post(stereo_ctx *ctx, const float *left_cost, const float *right_cost, const uint8_t *left_disp,
+                const uint8_t *right_disp, int h, int w, int D, const stereo_post_params *p,
+                uint8_t *const stages[8], float *final_disp)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(left_cost && right_cost && left_disp && right_disp && stages, "null pointer");
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    STEREO_TRY(ctx->stage_vol[0].reserve(sizeof(float) * nvox));
+    STEREO_TRY(ctx->stage_vol[1].reserve(sizeof(float) * nvox));
+    STEREO_TRY(ctx->stage_in[0].reserve(hw));
+    STEREO_TRY(ctx->stage_in[1].reserve(hw));
+    STEREO_TRY(ctx->stage_out[0].reserve(8 * hw));
+    STEREO_TRY(ctx->stage_out[1].reserve(sizeof(float) * hw));
+    STEREO_TRY(to_dev(ctx, ctx->stage_vol[0].ptr, left_cost, sizeof(float) * nvox));
+    STEREO_TRY(to_dev(ctx, ctx->stage_vol[1].ptr, right_cost, sizeof(float) * nvox));
+    STEREO_TRY(to_dev(ctx, ctx->stage_in[0].ptr, left_disp, hw));
+    STEREO_TRY(to_dev(ctx, ctx->stage_in[1].ptr, right_disp, hw));
+    uint8_t *dstages[8];
+    for (int i = 0; i < 8; ++i) dstages[i] = stages[i] ? ctx->stage_out[0].as<uint8_t>() + i * hw : nullptr;
+    STEREO_TRY(post_dev(ctx, ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(),
+                        ctx->stage_in[0].as<uint8_t>(), ctx->stage_in[1].as<uint8_t>(), h, w, D, p, dstages,
+                        final_disp ? ctx->stage_out[1].as<float>() : nullptr));
+    for (int i = 0; i < 8; ++i)
+        if (stages[i]) STEREO_TRY(to_host(ctx, stages[i], dstages[i], hw));
+    if (final_disp) STEREO_TRY(to_host(ctx, final_disp, ctx->stage_out[1].ptr, sizeof(float) * hw));
+    return finish(ctx);
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+"""GPU parity tests of the post chain (P0-P9) through the C ABI, against
+oracle/post_oracle.{c,py}.  The CUDA kernels perform the same fp32 operations in
+the same order as the restated original, so per-kernel results are required to
+be bit-identical; the whole-volume std (a float64 reduction in a different
+order) is allowed 1 ulp, and chain outputs that depend on it are compared at
+1e-5 / 99.9 %."""
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+from oracle import post_oracle as po
+from oracle import stereo_oracle as so
+from stereo_matching_b200 import _lib, synth
+from stereo_matching_b200.models.model import base_model_ws_9
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx(ws9_layers):
+    m = base_model_ws_9((None, None, 3))
+    m.set_layers(ws9_layers)
+    return m.context
+
+
+@pytest.fixture(scope="module")
+def scene(ctx):
+    """One synthetic pair through the GPU inference path: volumes + WTA maps."""
+    D = 48
+    l, r, gt = synth.make_pair(1007, 70, 230, D)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, volumes=True)
+    return {"D": D, "gt": gt, "lv": out["left_cost"][0], "rv": out["right_cost"][0],
+            "ld": out["left_disp"][0], "rd": out["right_disp"][0]}
+
+
+def test_guide_image(ctx, scene, golden_dir):
+    for img in (scene["ld"], cv2.imread(os.path.join(golden_dir, "results", "left_disp", "left_000002_10.png"), 0)):
+        ref = po.normalise_guide(img)
+        out = ctx.guide_image(img)
+        np.testing.assert_array_max_ulp(out, ref, maxulp=1)
+
+
+def test_volume_std(ctx, scene):
+    ref = po.volume_std(scene["lv"])
+    out = ctx.volume_std(scene["lv"])
+    np.testing.assert_array_max_ulp(np.float32(out), np.float32(ref), maxulp=1)
+
+
+@pytest.mark.parametrize("iters", [1, 2])
+def test_cross_agg_bit_exact(ctx, scene, iters):
+    l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
+    lu = np.ascontiguousarray(np.transpose(scene["lv"], (2, 0, 1)))
+    ru = np.ascontiguousarray(np.transpose(scene["rv"], (2, 0, 1)))
+    lref, rref = po.nyu_cross_agg(l_img, r_img, lu, ru, iters)
+    lv, rv = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], iters)
+    assert np.array_equal(np.transpose(lv, (2, 0, 1)), lref)
+    assert np.array_equal(np.transpose(rv, (2, 0, 1)), rref)
+
+
+@pytest.mark.parametrize("direction", [-1, 1])
+def test_sgm_bit_exact(ctx, scene, direction):
+    l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
+    vol = scene["lv"] if direction == -1 else scene["rv"]
+    vol = (vol / po.volume_std(vol)) * np.float32(-1)
+    ref = po.nyu_sgm(l_img, r_img, np.ascontiguousarray(np.transpose(vol, (2, 0, 1))), direction)
+    out = ctx.nyu_sgm(l_img, r_img, vol, direction)
+    assert np.array_equal(np.transpose(out, (2, 0, 1)), ref)
+
+
+@pytest.mark.parametrize("D", [33, 201])
+def test_sgm_ragged_disparity_ranges(ctx, D):
+    rng = np.random.default_rng(D)
+    h, w = 6, 40
+    l_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    r_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    vol = rng.standard_normal((h, w, D)).astype(np.float32)
+    for direction in (-1, 1):
+        ref = po.nyu_sgm(l_img, r_img, np.ascontiguousarray(np.transpose(vol, (2, 0, 1))), direction)
+        out = ctx.nyu_sgm(l_img, r_img, vol, direction)
+        assert np.array_equal(np.transpose(out, (2, 0, 1)), ref)
+
+
+def test_nyu_post_bit_exact_on_reference_maps(ctx, golden_dir):
+    """The shipped CA2 maps of image 000002 through LR check, fills, median and
+    bilateral (sub-pixel needs a volume: a synthetic one is used, identical on
+    both sides)."""
+    root = os.path.join(golden_dir, "results")
+    l = cv2.imread(os.path.join(root, "nyu_cost_img_2", "000169_10.png"), 0).astype(np.float32)[:120]
+    r = cv2.imread(os.path.join(root, "right_nyu_cost_img_2", "000169_10.png"), 0).astype(np.float32)[:120]
+    h, w = l.shape
+    D = 201
+    vol = np.random.default_rng(0).random((h, w, D)).astype(np.float32)
+    fin, outl = ctx.nyu_post(l, r, vol)
+    fref, oref = po.nyu_post([l, r], np.ascontiguousarray(np.transpose(vol, (2, 0, 1))))
+    assert np.array_equal(outl, oref)
+    assert np.array_equal(fin, fref)
+    ref_png = cv2.imread(os.path.join(root, "outlier", "000169_10.png"), 0)[:120]
+    # rows cut at 120: the LR check only looks along rows, so the crop is still pinned by K5
+    assert np.array_equal((outl * 127).astype(np.uint8), ref_png)
+
+
+def test_full_chain_vs_oracle(ctx, scene):
+    D = scene["D"]
+    ref = po.post_chain(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
+    out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
+    # before the global std everything is bit exact
+    assert np.array_equal(out["nyu_cost_img"], ref["nyu_cost_img"])
+    assert np.array_equal(out["right_nyu_cost_img"], ref["right_nyu_cost_img"])
+    for name in ("nyu_sgm_img", "right_nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2", "outlier"):
+        assert (out[name] == ref[name]).mean() >= 0.999, name
+    diff = np.abs(out["nyu_post_float"] - ref["nyu_post_float"])
+    assert (diff <= 1e-3).mean() >= 0.999
+    assert (out["nyu_post"] == ref["nyu_post"]).mean() >= 0.999
+    e_ref = so.three_pixel_error(ref["nyu_post"], scene["gt"])
+    e_out = so.three_pixel_error(out["nyu_post"], scene["gt"])
+    assert abs(e_ref - e_out) <= 0.0005
+    assert e_out < so.three_pixel_error(scene["ld"], scene["gt"])
+
+
+def test_post_error_behaviour(ctx, scene):
+    p = _lib.default_post_params()
+    assert (p.L1, p.sgm_i, p.nyu_cost_agg_1, p.post) == (5, 1, 1, 1)
+    assert p.pi1 == pytest.approx(2.3) and p.blur_sigma == pytest.approx(5.99)
+    big = np.zeros((2, 4, 300), np.float32)
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.post(big, big, np.zeros((2, 4), np.uint8), np.zeros((2, 4), np.uint8))
+    assert e.value.code == -1
+    with pytest.raises(_lib.StereoError) as e:
+        ctx.nyu_sgm(np.zeros((2, 4), np.float32), np.zeros((2, 4), np.float32), np.zeros((2, 4, 600), np.float32), -1)
+    assert e.value.code == -5
+
+
+def test_lua_surface_mirror(ctx, scene):
+    """smooth.nyu.cross_agg / sgm / post with the reference's [1,D,H,W] layout."""
+    from stereo_matching_b200 import post as post_mod
+    l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
+    lu = np.ascontiguousarray(np.transpose(scene["lv"], (2, 0, 1)))[None]
+    ru = np.ascontiguousarray(np.transpose(scene["rv"], (2, 0, 1)))[None]
+    h, w = l_img.shape
+    lo, ro = post_mod.nyu.cross_agg(l_img.reshape(1, 1, h, w), r_img.reshape(1, 1, h, w), lu, ru, 1)
+    lref, rref = po.nyu_cross_agg(l_img, r_img, lu[0], ru[0], 1)
+    assert lo.shape == lu.shape and np.array_equal(lo[0], lref) and np.array_equal(ro[0], rref)
