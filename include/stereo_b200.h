@@ -144,7 +144,8 @@ typedef struct stereo_post_params {
     int sgm_i;       /* :7  SGM sweeps */
     float pi1, pi2, tau_so, alpha1, sgm_q1, sgm_q2; /* :9-14 */
     int occlusion, subpixel, median, bilateral;     /* :17-20 */
-    float blur_sigma, blur_t;                       /* :21-22 */
+    double blur_sigma;                              /* :21  (a Lua double; the Gaussian of nyu.lua:77-89 is built in double) */
+    float blur_t;                                   /* :22 */
     int nyu_cost_agg_1, sgm, nyu_cost_agg_2, post;  /* post.lua:37-40 */
 } stereo_post_params;
 /* the constants of smooth/nyu.lua:3-22 and the option defaults of post.lua:10-49 */

@@ -92,11 +92,34 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         set_error("weights for net %d have not been set (call stereo_set_weights first)", net);
         return STEREO_E_STATE;
     }
-    STEREO_REQUIRE(precision == STEREO_PREC_FP32, "precision mode %d is not available in this build", precision);
+    STEREO_REQUIRE(precision == STEREO_PREC_FP32 || precision == STEREO_PREC_BF16X3 || precision == STEREO_PREC_BF16,
+                   "unknown precision mode %d", precision);
     NetDesc nd = net_desc(net);
     STEREO_REQUIRE(h > nd.shrink && w > nd.shrink, "input %dx%d is too small for a receptive field of %d", h, w,
                    nd.shrink + 1);
     const float *wts = ctx->weights[net].as<float>();
+    if (precision != STEREO_PREC_FP32) {
+        STEREO_REQUIRE(net == STEREO_NET_WIN9,
+                       "the tensor-core trunk is built for base_model_ws_9 (3x3, 64 channels); use STEREO_PREC_FP32 for base_model");
+        // layer 1 on CUDA cores (K = 27) writing chunk-planar bf16 (hi, lo); layers 2-4 on tcgen05
+        const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
+        const int wp = tc_pitch(w - 2);
+        const size_t plane_elems = (size_t)n * (h - 2) * 8 * wp * 8;
+        STEREO_TRY(ctx->act[0].reserve(2 * plane_elems * 2));
+        STEREO_TRY(ctx->act[1].reserve(2 * plane_elems * 2));
+        uint16_t *a_hi = ctx->act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
+        uint16_t *b_hi = ctx->act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
+        const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>();
+        const size_t wl = tc_weight_image_elems();
+        STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
+        STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 2, w - 2, wp, wimg, wts + nd.layer[1].b_off, b_hi, b_lo, wp,
+                                  nullptr, 1, planes));
+        STEREO_TRY(launch_conv_tc(ctx, b_hi, b_lo, n, h - 4, w - 4, wp, wimg + wl, wts + nd.layer[2].b_off, a_hi, a_lo,
+                                  wp, nullptr, 1, planes));
+        STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 6, w - 6, wp, wimg + 2 * wl, wts + nd.layer[3].b_off, nullptr,
+                                  nullptr, wp, out, 0, planes));
+        return STEREO_OK;
+    }
     size_t max_act = 0;
     {
         int ch = h, cw = w;
@@ -319,6 +342,14 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
     STEREO_TRY(ctx->weights[net].reserve(sizeof(float) * n_floats));
     STEREO_CUDA_CHECK(cudaMemcpyAsync(ctx->weights[net].ptr, packed, sizeof(float) * n_floats,
                                       cudaMemcpyHostToDevice, ctx->stream));
+    if (net == STEREO_NET_WIN9) {
+        // UMMA B-operand images (bf16 hi/lo) of the three 64->64 layers
+        const size_t wl = tc_weight_image_elems();
+        STEREO_TRY(ctx->wsplit[net].reserve(3 * wl * 2));
+        for (int l = 1; l < 4; ++l)
+            STEREO_TRY(launch_weight_images(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
+                                            ctx->wsplit[net].as<uint16_t>() + (l - 1) * wl));
+    }
     STEREO_TRY(finish(ctx));
     ctx->has_weights[net] = true;
     return STEREO_OK;

@@ -121,6 +121,15 @@ int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int 
 // conv_ffma.cu
 int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in,
                      int n, int h_in, int w_in, float *out);
+int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in, int n,
+                            int h_in, int w_in, void *out_hi, void *out_lo, int wp_out);
+// conv_tc.cu
+size_t tc_weight_image_elems();
+int tc_pitch(int w);
+int launch_weight_images(stereo_ctx *ctx, const float *layer_w, void *img);
+int launch_conv_tc(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
+                   const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
+                   int relu, int planes);
 // corr.cu
 int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
                      int D, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp);

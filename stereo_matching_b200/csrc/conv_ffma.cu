@@ -7,6 +7,8 @@
 // staged in shared memory channel-planar ([c][row][col]) so that a thread reads
 // the 8+KS-1 consecutive pixels of one patch row with vector loads and reuses
 // them for the KS horizontal taps.  Each thread owns 8 pixels x COUT/8 channels.
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace stereo {
@@ -29,7 +31,8 @@ __global__ __launch_bounds__(256, 2) void conv_ffma_kernel(const float *__restri
                                                            const float *__restrict__ wgt,
                                                            const float *__restrict__ bias,
                                                            float *__restrict__ out, int h_in, int w_in,
-                                                           int relu)
+                                                           int relu, __nv_bfloat16 *__restrict__ out_hi,
+                                                           __nv_bfloat16 *__restrict__ out_lo, int wp_out)
 {
     using S = ConvSmem<KS, CK>;
     constexpr int CPT = COUT / 8;          // output channels per thread (4 or 8)
@@ -149,6 +152,29 @@ __global__ __launch_bounds__(256, 2) void conv_ffma_kernel(const float *__restri
             v[o] = acc[j][o] + b[o];
             if (relu) v[o] = fmaxf(v[o], 0.f);
         }
+        if (out_hi != nullptr) {
+            // chunk-planar bf16 (hi, lo) for the tensor-core layers: [img][y][c/8][x][c%8]
+            if constexpr (COUT == 64) {
+#pragma unroll
+                for (int g = 0; g < 2; ++g) {
+                    uint32_t hi[2], lo[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        float a0 = v[4 * g + 2 * e], a1 = v[4 * g + 2 * e + 1];
+                        __nv_bfloat16 h0 = __float2bfloat16_rn(a0), h1 = __float2bfloat16_rn(a1);
+                        __nv_bfloat16 l0 = __float2bfloat16_rn(a0 - __bfloat162float(h0));
+                        __nv_bfloat16 l1 = __float2bfloat16_rn(a1 - __bfloat162float(h1));
+                        hi[e] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                        lo[e] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+                    }
+                    int cc = 4 * g + (cg >> 1);
+                    size_t off = ((((size_t)blockIdx.z * h_out + gy) * 8 + cc) * wp_out + gx) * 8 + (cg & 1) * 4;
+                    *reinterpret_cast<uint2 *>(out_hi + off) = make_uint2(hi[0], hi[1]);
+                    if (out_lo != nullptr) *reinterpret_cast<uint2 *>(out_lo + off) = make_uint2(lo[0], lo[1]);
+                }
+            }
+            continue;
+        }
         float *p = orow + (size_t)gx * COUT + cg * 4;
         *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
         if constexpr (CPT == 8) *reinterpret_cast<float4 *>(p + 32) = make_float4(v[4], v[5], v[6], v[7]);
@@ -157,7 +183,8 @@ __global__ __launch_bounds__(256, 2) void conv_ffma_kernel(const float *__restri
 
 template <int KS, int CIN, int COUT, int CK>
 static int launch_one(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in, int n,
-                      int h_in, int w_in, float *out)
+                      int h_in, int w_in, float *out, void *out_hi = nullptr, void *out_lo = nullptr,
+                      int wp_out = 0)
 {
     using S = ConvSmem<KS, CK>;
     constexpr size_t smem = sizeof(float) * (CK * S::PLANE + KS * KS * CK * COUT);
@@ -167,7 +194,9 @@ static int launch_one(stereo_ctx *ctx, const LayerDesc &L, const float *weights,
     int h_out = h_in - KS + 1, w_out = w_in - KS + 1;
     dim3 grid((w_out + kTW - 1) / kTW, (h_out + kTH - 1) / kTH, n);
     ProfScope prof(ctx, CIN == 3 ? STEREO_K_CONV_FIRST : STEREO_K_CONV);
-    kern<<<grid, 256, smem, ctx->stream>>>(in, weights + L.w_off, weights + L.b_off, out, h_in, w_in, L.relu);
+    kern<<<grid, 256, smem, ctx->stream>>>(in, weights + L.w_off, weights + L.b_off, out, h_in, w_in, L.relu,
+                                           static_cast<__nv_bfloat16 *>(out_hi), static_cast<__nv_bfloat16 *>(out_lo),
+                                           wp_out);
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
@@ -185,6 +214,14 @@ int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, 
     if (L.ks == 5 && L.cin == 64 && L.cout == 64) return launch_one<5, 64, 64, 8>(ctx, L, weights, in, n, h_in, w_in, out);
     set_error("no fp32 convolution kernel for ks=%d cin=%d cout=%d", L.ks, L.cin, L.cout);
     return STEREO_E_INVALID;
+}
+
+// First layer of base_model_ws_9 with the output written as chunk-planar bf16 (hi, lo)
+int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in, int n,
+                            int h_in, int w_in, void *out_hi, void *out_lo, int wp_out)
+{
+    STEREO_REQUIRE(L.ks == 3 && L.cin == 3 && L.cout == 64, "split output is only built for the 3x3 3->64 layer");
+    return launch_one<3, 3, 64, 3>(ctx, L, weights, in, n, h_in, w_in, nullptr, out_hi, out_lo, wp_out);
 }
 
 }  // namespace stereo

@@ -1,0 +1,367 @@
+// Siamese trunk on the 5th-generation tensor cores: 3x3 / 64->64 'valid' convolution as an
+// implicit GEMM with tcgen05.mma, accumulators in TMEM, operands staged in shared memory by
+// TMA bulk copies (/root/reference/models/model.py:33-39, layers 2-4 of base_model_ws_9).
+//
+// Precision.  Single-pass bf16 operands miss the 1e-4 cost-volume gate on the ckpt-1000
+// weights, so activations and weights are kept as a bf16 (hi, lo) pair
+// with x ~= hi + lo and each product is formed as hi*hi + hi*lo + lo*hi in the fp32 TMEM
+// accumulator (STEREO_PREC_BF16X3).  STEREO_PREC_BF16 issues only the hi*hi pass.
+//
+// Data layout.  Activations live in HBM "chunk-planar": [image][y][c/8][x][c%8] bf16, one
+// plane for hi and one for lo.  For a fixed (y, c/8) a run of pixels is contiguous, 16 bytes
+// per pixel - exactly one row of a no-swizzle K-major UMMA core matrix.  A CTA stages an
+// input row as [plane][c/8][130 px][16 B]; the A operand of tap (ky, kx) is then the same
+// tile with the start address advanced by kx*16 bytes (ky picks the ring slot), SBO = 128 B,
+// LBO = 130*16 B.  No im2col copy is ever made and every input row is fetched once per CTA.
+//
+// Work split.  A CTA owns a strip of 128 output pixels x 32 output channels and walks down
+// `rows_per_cta` output rows: M = 128 pixels, N = 32 channels, K = 9 taps x 64 channels.
+// The 32-channel half of the weights (9 taps x hi/lo x 4 KB = 72 KB) stays resident in shared
+// memory, input rows stream through a 4-slot ring, and two 32-column TMEM accumulators
+// alternate between the MMA issuer and the epilogue warps.
+//
+// Warp roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
+// allocator, warps 4-7 = epilogue (TMEM -> registers -> bias/ReLU -> hi/lo split -> HBM).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace stereo {
+
+namespace tc {
+
+constexpr int kStripW = 128;               // output pixels per CTA row (UMMA M)
+constexpr int kPW = kStripW + 2;           // input pixels per staged row
+constexpr int kNHalf = 32;                 // output channels per CTA (UMMA N)
+constexpr int kRunBytes = kPW * 16;        // one (plane, channel-chunk) run of a staged row
+constexpr int kPlaneBytes = 8 * kRunBytes; // 8 channel chunks
+constexpr int kSlotBytes = 2 * kPlaneBytes;
+constexpr int kSlots = 4;
+constexpr int kWTapBytes = 8 * kNHalf * 16;            // one tap, one plane: [kc][n][8] bf16
+constexpr int kWBytes = 9 * 2 * kWTapBytes;            // 73,728
+constexpr int kSmemBars = kWBytes + kSlots * kSlotBytes;
+constexpr int kSmemTotal = kSmemBars + 16 * 8 + 16;
+constexpr uint32_t kTmemCols = 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol error traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (done) return;
+    }
+    __trap();
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], bf16 operands, fp32 accumulate, issued by one thread
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major, no-swizzle shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+// start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout_type=0 [61,64)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    return (uint64_t)((addr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+// kind::f16 instruction descriptor: D=f32 (bit 4), A=B=bf16 (bits 7, 10), K-major A and B,
+// N>>3 at [17,23), M>>4 at [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n)
+{
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+struct Params {
+    const __nv_bfloat16 *in_hi, *in_lo;   // chunk-planar [img][h_in][8][wp_in][8]
+    int h_in, w_in, wp_in;
+    const __nv_bfloat16 *wimg;            // [nh][tap][plane][kc][n][8] for this layer
+    const float *bias;                    // [64]
+    __nv_bfloat16 *out_hi, *out_lo;       // chunk-planar [img][h_out][8][wp_out][8] (or null)
+    int wp_out;
+    float *out_f32;                       // NHWC [img][h_out][w_out][64] (or null)
+    int relu, planes, rows_per_cta;
+};
+
+__global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int h_out = p.h_in - 2, w_out = p.w_in - 2;
+    const int x0 = blockIdx.x * kStripW;
+    const int y0 = blockIdx.y * p.rows_per_cta;
+    const int rows_out = min(p.rows_per_cta, h_out - y0);
+    const int img = blockIdx.z >> 1, nh = blockIdx.z & 1;
+    const int rows_in = rows_out + 2;
+
+    const uint32_t s_w = smem_u32(smem);
+    const uint32_t s_rows = s_w + kWBytes;
+    const uint32_t s_bar = s_w + kSmemBars;
+    const uint32_t bar_full = s_bar;              // [4]
+    const uint32_t bar_empty = s_bar + 32;        // [4]
+    const uint32_t bar_w = s_bar + 64;            // [1]
+    const uint32_t bar_acc_full = s_bar + 72;     // [2]
+    const uint32_t bar_acc_empty = s_bar + 88;    // [2]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSmemBars + 16 * 8);
+
+    if (tid == 0) {
+        for (int i = 0; i < kSlots; ++i) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, 1);
+        }
+        mbar_init(bar_w, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(bar_acc_full + 8 * i, 1);
+            mbar_init(bar_acc_empty + 8 * i, 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---- TMA producer: weights once, then the input rows through the ring ----
+            const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(p.wimg) + (size_t)nh * kWBytes;
+            mbar_expect_tx(bar_w, 9u * p.planes * kWTapBytes);
+            for (int tap = 0; tap < 9; ++tap)
+                bulk_g2s(s_w + tap * 2 * kWTapBytes, wsrc + (size_t)tap * 2 * kWTapBytes, p.planes * kWTapBytes, bar_w);
+            const size_t row_elems = (size_t)8 * p.wp_in * 8;     // bf16 elements per image row
+            for (int r = 0; r < rows_in; ++r) {
+                const int slot = r & (kSlots - 1);
+                mbar_wait(bar_empty + 8 * slot, ((r >> 2) & 1) ^ 1);
+                mbar_expect_tx(bar_full + 8 * slot, (uint32_t)p.planes * kPlaneBytes);
+                const size_t row_off = ((size_t)img * p.h_in + (y0 + r)) * row_elems + (size_t)x0 * 8;
+                for (int pl = 0; pl < p.planes; ++pl) {
+                    const __nv_bfloat16 *src = (pl == 0 ? p.in_hi : p.in_lo) + row_off;
+                    const uint32_t dst = s_rows + slot * kSlotBytes + pl * kPlaneBytes;
+                    for (int cc = 0; cc < 8; ++cc)
+                        bulk_g2s(dst + cc * kRunBytes, src + (size_t)cc * p.wp_in * 8, kRunBytes, bar_full + 8 * slot);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---- MMA issuer ----
+            constexpr uint32_t idesc = make_idesc(kStripW, kNHalf);
+            mbar_wait(bar_w, 0);
+            for (int j = 0; j < rows_out; ++j) {
+                const int b = j & 1;
+                mbar_wait(bar_acc_empty + 8 * b, ((j >> 1) & 1) ^ 1);
+                if (j == 0) {
+                    mbar_wait(bar_full + 0, 0);
+                    mbar_wait(bar_full + 8, 0);
+                }
+                mbar_wait(bar_full + 8 * ((j + 2) & 3), ((j + 2) >> 2) & 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)b * kNHalf;
+                uint32_t acc = 0;
+                // (activation plane, weight plane): lo*hi and hi*lo first, hi*hi last
+                const int n_combo = p.planes == 2 ? 3 : 1;
+                for (int combo = 0; combo < n_combo; ++combo) {
+                    const int apl = (n_combo == 3 && combo == 0) ? 1 : 0;
+                    const int wpl = (n_combo == 3 && combo == 1) ? 1 : 0;
+#pragma unroll 1
+                    for (int ky = 0; ky < 3; ++ky) {
+                        const uint32_t a_row = s_rows + ((j + ky) & 3) * kSlotBytes + apl * kPlaneBytes;
+#pragma unroll
+                        for (int kx = 0; kx < 3; ++kx) {
+                            const uint32_t b_tap = s_w + (ky * 3 + kx) * 2 * kWTapBytes + wpl * kWTapBytes;
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) {
+                                uint64_t ad = smem_desc(a_row + 2 * ks * kRunBytes + kx * 16, kRunBytes, 128);
+                                uint64_t bd = smem_desc(b_tap + 2 * ks * (kNHalf * 16), kNHalf * 16, 128);
+                                umma_bf16(tmem_d, ad, bd, idesc, acc);
+                                acc = 1;
+                            }
+                        }
+                    }
+                }
+                tc_commit(bar_empty + 8 * (j & 3));      // input row j is no longer needed
+                tc_commit(bar_acc_full + 8 * b);         // accumulator b is complete
+            }
+            // rows j+1, j+2 of the last step are never released through the ring; nothing waits on them
+        }
+    } else if (warp >= 4) {
+        // ---- epilogue: TMEM -> registers -> bias / ReLU -> (hi, lo) or fp32 -> HBM ----
+        const int q = warp & 3;                      // TMEM lane quarter this warp may touch
+        const int px = x0 + q * 32 + lane;
+        float bias[kNHalf];
+#pragma unroll
+        for (int i = 0; i < kNHalf; ++i) bias[i] = __ldg(p.bias + nh * kNHalf + i);
+        for (int j = 0; j < rows_out; ++j) {
+            const int b = j & 1;
+            mbar_wait(bar_acc_full + 8 * b, (j >> 1) & 1);
+            tc_fence_after();
+            uint32_t v[kNHalf];
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)b * kNHalf;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]),
+                  "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]),
+                  "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_acc_empty + 8 * b);    // the accumulator may be overwritten
+
+            const int y = y0 + j;
+            if (px < w_out) {
+                float f[kNHalf];
+#pragma unroll
+                for (int i = 0; i < kNHalf; ++i) {
+                    f[i] = __uint_as_float(v[i]) + bias[i];
+                    if (p.relu) f[i] = fmaxf(f[i], 0.f);
+                }
+                if (p.out_f32) {
+                    float4 *dst = reinterpret_cast<float4 *>(p.out_f32 + (((size_t)img * h_out + y) * w_out + px) * 64 +
+                                                             nh * kNHalf);
+#pragma unroll
+                    for (int i = 0; i < kNHalf / 4; ++i) dst[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < kNHalf / 8; ++c) {
+                        uint32_t hi[4], lo[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            float a0 = f[8 * c + 2 * e], a1 = f[8 * c + 2 * e + 1];
+                            __nv_bfloat16 h0 = __float2bfloat16_rn(a0), h1 = __float2bfloat16_rn(a1);
+                            __nv_bfloat16 l0 = __float2bfloat16_rn(a0 - __bfloat162float(h0));
+                            __nv_bfloat16 l1 = __float2bfloat16_rn(a1 - __bfloat162float(h1));
+                            hi[e] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                            lo[e] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+                        }
+                        const size_t off = ((((size_t)img * h_out + y) * 8 + (nh * 4 + c)) * p.wp_out + px) * 8;
+                        *reinterpret_cast<uint4 *>(p.out_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                        if (p.planes == 2)
+                            *reinterpret_cast<uint4 *>(p.out_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    }
+}
+
+// fp32 packed weights (one 3x3 64->64 layer: [tap][cin][cout] + bias) -> UMMA B operand images
+// [nh][tap][plane][kc][n][8] bf16 with plane 0 = hi, plane 1 = lo
+__global__ void weight_image_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ img)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;      // over [nh][tap][kc][n][k8]
+    if (i >= 2 * 9 * 8 * 32 * 8) return;
+    int k8 = i & 7, n = (i >> 3) & 31, kc = (i >> 8) & 7, tap = (i >> 11) % 9, nh = (i >> 11) / 9;
+    float v = w[((size_t)tap * 64 + kc * 8 + k8) * 64 + nh * 32 + n];
+    __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+    size_t base = (((size_t)nh * 9 + tap) * 2) * (8 * 32 * 8) + ((size_t)kc * 32 + n) * 8 + k8;
+    img[base] = hi;
+    img[base + 8 * 32 * 8] = lo;
+}
+
+}  // namespace tc
+
+size_t tc_weight_image_elems() { return (size_t)2 * 9 * 2 * 8 * 32 * 8; }   // per layer
+
+int launch_weight_images(stereo_ctx *ctx, const float *layer_w, void *img)
+{
+    tc::weight_image_kernel<<<(2 * 9 * 8 * 32 * 8 + 255) / 256, 256, 0, ctx->stream>>>(
+        layer_w, static_cast<__nv_bfloat16 *>(img));
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int tc_pitch(int w) { return (w + tc::kStripW - 1) / tc::kStripW * tc::kStripW + 8; }
+
+int launch_conv_tc(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
+                   const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
+                   int relu, int planes)
+{
+    STEREO_REQUIRE(h_in >= 3 && w_in >= 3, "input %dx%d smaller than the 3x3 kernel", h_in, w_in);
+    const int h_out = h_in - 2, w_out = w_in - 2;
+    const int strips = (w_out + tc::kStripW - 1) / tc::kStripW;
+    STEREO_REQUIRE(wp_in >= strips * tc::kStripW + 2, "activation pitch %d too small for %d strips", wp_in, strips);
+    tc::Params p;
+    p.in_hi = static_cast<const __nv_bfloat16 *>(in_hi);
+    p.in_lo = static_cast<const __nv_bfloat16 *>(in_lo);
+    p.h_in = h_in; p.w_in = w_in; p.wp_in = wp_in;
+    p.wimg = static_cast<const __nv_bfloat16 *>(wimg);
+    p.bias = bias;
+    p.out_hi = static_cast<__nv_bfloat16 *>(out_hi);
+    p.out_lo = static_cast<__nv_bfloat16 *>(out_lo);
+    p.wp_out = wp_out;
+    p.out_f32 = out_f32;
+    p.relu = relu; p.planes = planes;
+    // enough row segments for a few waves of 1 CTA/SM, few enough to amortise weights + halo rows
+    int column_ctas = strips * 2 * n;
+    int segs = (ctx->sm_count * 3 + column_ctas - 1) / column_ctas;
+    int rows = (h_out + segs - 1) / segs;
+    if (rows < 8) rows = 8;
+    p.rows_per_cta = rows;
+    segs = (h_out + rows - 1) / rows;
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(tc::conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           tc::kSmemTotal));
+    ProfScope prof(ctx, STEREO_K_CONV);
+    tc::conv3x3_tc_kernel<<<dim3(strips, segs, 2 * n), 256, tc::kSmemTotal, ctx->stream>>>(p);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo

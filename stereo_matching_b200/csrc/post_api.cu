@@ -22,12 +22,12 @@ static SgmParams sgm_params(const stereo_post_params *p)
 }
 
 // smooth/nyu.lua:77-89 gaussian(sigma): double arithmetic, stored as float (:cuda())
-static std::vector<float> gaussian_kernel(float sigma, int *radius)
+static std::vector<float> gaussian_kernel(double sigma, int *radius)
 {
-    int kr = (int)std::ceil((double)sigma * 3.0);
+    int kr = (int)std::ceil(sigma * 3.0);
     int ks = 2 * kr + 1;
     std::vector<float> k((size_t)ks * ks);
-    double s = (double)sigma;
+    double s = sigma;
     for (int i = 0; i < ks; ++i)
         for (int j = 0; j < ks; ++j) {
             double y = i - kr, x = j - kr;
@@ -104,7 +104,7 @@ static int nyu_post_dev(stereo_ctx *ctx, PostMaps &m, const float *left_vol, int
 
 static int gauss_count(const stereo_post_params *p)
 {
-    int kr = (int)std::ceil((double)p->blur_sigma * 3.0);
+    int kr = (int)std::ceil(p->blur_sigma * 3.0);
     return (2 * kr + 1) * (2 * kr + 1);
 }
 
@@ -228,7 +228,7 @@ int stereo_post_default_params(stereo_post_params *p)
     p->subpixel = 1;
     p->median = 1;
     p->bilateral = 1;
-    p->blur_sigma = 5.99f;
+    p->blur_sigma = 5.99;
     p->blur_t = 5.f;
     p->nyu_cost_agg_1 = 1;
     p->sgm = 1;

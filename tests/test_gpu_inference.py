@@ -216,3 +216,49 @@ def test_error_behaviour(ctx, ws9):
         ws9(np.zeros((1, 8, 8, 3), np.float32))
     with pytest.raises(NotImplementedError):
         ws9(np.zeros((1, 20, 20, 3), np.float32), training=True)
+
+
+# ---- tensor-core trunk (tcgen05 / TMEM), STEREO_PREC_BF16X3 and STEREO_PREC_BF16 ----------------
+BF16X3_TOL = 2e-5     # 3-pass bf16 split: SURVEY section 7 measured 5.6e-6 on ckpt-1000
+BF16_TOL = 2e-2       # single bf16 pass: its own, much looser tolerance (does NOT meet the 1e-4 gate)
+
+
+@pytest.mark.parametrize("hw", [(12, 14), (24, 50), (20, 300), (75, 140), (11, 139)])
+def test_trunk_tensor_core_bf16x3_vs_oracle(ctx, ws9_layers, hw):
+    rng = np.random.default_rng(hw[1])
+    x = rng.standard_normal((2,) + hw + (3,)).astype(np.float32)
+    ref = so.trunk_forward(x, ws9_layers, "win9_dep9", np.float64)
+    out = ctx.trunk(_lib.NET_WIN9, x, _lib.PREC_BF16X3)
+    assert out.shape == ref.shape
+    assert rel_err(out, ref) < BF16X3_TOL
+    fp32 = ctx.trunk(_lib.NET_WIN9, x, _lib.PREC_FP32)
+    assert rel_err(out, fp32.astype(np.float64)) < BF16X3_TOL
+
+
+def test_trunk_tensor_core_bf16_reports_its_own_tolerance(ctx, ws9_layers):
+    x = np.random.default_rng(9).standard_normal((1, 40, 150, 3)).astype(np.float32)
+    ref = so.trunk_forward(x, ws9_layers, "win9_dep9", np.float64)
+    out = ctx.trunk(_lib.NET_WIN9, x, _lib.PREC_BF16)
+    err = rel_err(out, ref)
+    assert 1e-5 < err < BF16_TOL        # clearly worse than the split, clearly not garbage
+
+
+def test_pair_end_to_end_tensor_core(ctx, ws9_layers):
+    D = 64
+    l, r, gt = synth.make_pair(1003, 96, 320, D)
+    ref = so.infer_pair(l, r, ws9_layers, "win9_dep9", 9, D, np.float64)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    assert rel_err(out["left_cost"][0], ref["left_cost"]) < COST_TOL
+    assert rel_err(out["right_cost"][0], ref["right_cost"]) < COST_TOL
+    assert (out["left_disp"][0] == ref["left_disp"]).mean() >= WTA_AGREE
+    assert (out["right_disp"][0] == ref["right_disp"]).mean() >= WTA_AGREE
+    assert abs(so.three_pixel_error(ref["left_disp"], gt) - so.three_pixel_error(out["left_disp"][0], gt)) <= 0.0005
+
+
+def test_tensor_core_trunk_rejects_base_model(ctx):
+    layers = synth.make_base_model_weights()
+    m = base_model((None, None, 3), precision=_lib.PREC_BF16X3)
+    m.set_layers(layers)
+    with pytest.raises(_lib.StereoError) as e:
+        m(np.zeros((1, 45, 60, 3), np.float32))
+    assert e.value.code == -1
