@@ -85,7 +85,14 @@ static int check_dims(int n, int h, int w)
     return STEREO_OK;
 }
 
-static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision)
+// Planar (hi, lo) feature output of the tensor-core trunk, consumed by the tensor-core correlation.
+struct PlanarOut {
+    uint16_t *hi = nullptr, *lo = nullptr;   // already offset by the left margin
+    int wf = 0;
+};
+
+static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision,
+                     const PlanarOut *planar = nullptr)
 {
     STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
     if (!ctx->has_weights[net]) {
@@ -116,8 +123,12 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
                                   nullptr, 1, planes));
         STEREO_TRY(launch_conv_tc(ctx, b_hi, b_lo, n, h - 4, w - 4, wp, wimg + wl, wts + nd.layer[2].b_off, a_hi, a_lo,
                                   wp, nullptr, 1, planes));
-        STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 6, w - 6, wp, wimg + 2 * wl, wts + nd.layer[3].b_off, nullptr,
-                                  nullptr, wp, out, 0, planes));
+        if (planar)
+            STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 6, w - 6, wp, wimg + 2 * wl, wts + nd.layer[3].b_off,
+                                      planar->hi, planar->lo, planar->wf, nullptr, 0, planes));
+        else
+            STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 6, w - 6, wp, wimg + 2 * wl, wts + nd.layer[3].b_off,
+                                      nullptr, nullptr, wp, out, 0, planes));
         return STEREO_OK;
     }
     size_t max_act = 0;
@@ -144,6 +155,50 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
     return STEREO_OK;
 }
 
+// Chunk-planar bf16 feature buffers with zero margins: [plane][side][n][h][8][wf][8].
+struct PlanarFeat {
+    uint16_t *l_hi, *l_lo, *r_hi, *r_lo;
+    int wf, ml;
+};
+
+static int ensure_planar(stereo_ctx *ctx, int n, int h, int w, int D, PlanarFeat *f)
+{
+    corr_tc_geometry(w, D, &f->wf, &f->ml);
+    const size_t side_elems = (size_t)n * h * 8 * f->wf * 8;
+    const size_t bytes = 4 * side_elems * sizeof(uint16_t);
+    const bool grown = bytes > ctx->featp.bytes;
+    STEREO_TRY(ctx->featp.reserve(bytes));
+    const int geom[5] = {n, h, w, f->wf, f->ml};
+    bool same = !grown;
+    for (int i = 0; i < 5; ++i) same = same && ctx->featp_geom[i] == geom[i];
+    if (!same) {
+        // margins must read as exact zeros (the zero-filled slots of inference.py:140-141)
+        STEREO_CUDA_CHECK(cudaMemsetAsync(ctx->featp.ptr, 0, ctx->featp.bytes, ctx->stream));
+        for (int i = 0; i < 5; ++i) ctx->featp_geom[i] = geom[i];
+    }
+    uint16_t *base = ctx->featp.as<uint16_t>();
+    f->l_hi = base;
+    f->r_hi = base + side_elems;
+    f->l_lo = base + 2 * side_elems;
+    f->r_lo = base + 3 * side_elems;
+    return STEREO_OK;
+}
+
+// Correlation from caller-provided fp32 NHWC feature maps.
+static int corr_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
+                    int precision, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp)
+{
+    if (precision == STEREO_PREC_FP32 || c != 64 || D > corr_tc_max_disp())
+        return launch_corr_ffma(ctx, lmap, rmap, n, h, w, c, D, left_vol, right_vol, left_disp, right_disp);
+    PlanarFeat f;
+    STEREO_TRY(ensure_planar(ctx, n, h, w, D, &f));
+    const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
+    STEREO_TRY(launch_nhwc_to_planar(ctx, lmap, n, h, w, f.wf, f.ml, f.l_hi, planes == 2 ? f.l_lo : nullptr));
+    STEREO_TRY(launch_nhwc_to_planar(ctx, rmap, n, h, w, f.wf, f.ml, f.r_hi, planes == 2 ? f.r_lo : nullptr));
+    return launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, n, h, w, f.wf, f.ml, D, planes, left_vol, right_vol,
+                          left_disp, right_disp);
+}
+
 static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h,
                      int w, int D, int precision, uint8_t *left_disp, uint8_t *right_disp, uint8_t *lr_outlier,
                      float *left_vol, float *right_vol)
@@ -162,15 +217,31 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     float *feat = ctx->feat.as<float>();
     const size_t img_bytes = (size_t)h * w * 3;
     const size_t map = (size_t)h * w;
+    const bool tc_corr = precision != STEREO_PREC_FP32 && net == STEREO_NET_WIN9 && D <= corr_tc_max_disp();
+    PlanarFeat pf;
+    if (tc_corr) STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf));
     for (int i = 0; i < n; ++i) {
         // left and right of one pair go through the trunk as a batch of two
         STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
         STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
-        STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, feat, precision));
         float *lv = left_vol ? left_vol + i * map * D : nullptr;
         float *rv = right_vol ? right_vol + i * map * D : nullptr;
-        STEREO_TRY(launch_corr_ffma(ctx, feat, feat + feat_img, 1, h, w, 64, D, lv, rv, left_disp + i * map,
-                                    right_disp + i * map));
+        if (tc_corr) {
+            // the trunk's last layer writes the chunk-planar bf16 features the correlation reads
+            // (image 0 = left, image 1 = right are adjacent sides of one plane)
+            PlanarOut po;
+            po.hi = pf.l_hi + (size_t)pf.ml * 8;
+            po.lo = pf.l_lo + (size_t)pf.ml * 8;
+            po.wf = pf.wf;
+            const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
+            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po));
+            STEREO_TRY(launch_corr_tc(ctx, pf.l_hi, pf.l_lo, pf.r_hi, pf.r_lo, 1, h, w, pf.wf, pf.ml, D, planes, lv, rv,
+                                      left_disp + i * map, right_disp + i * map));
+        } else {
+            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, feat, precision));
+            STEREO_TRY(corr_dev(ctx, feat, feat + feat_img, 1, h, w, 64, D, precision, lv, rv, left_disp + i * map,
+                                right_disp + i * map));
+        }
     }
     if (lr_outlier) STEREO_TRY(launch_lr_check(ctx, left_disp, right_disp, n, h, w, D, lr_outlier));
     return STEREO_OK;
@@ -247,7 +318,7 @@ int stereo_destroy(stereo_ctx *ctx)
                       &ctx->padded, &ctx->act[0], &ctx->act[1], &ctx->feat, &ctx->stage_in[0], &ctx->stage_in[1],
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
                       &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2],
-                      &ctx->post_maps};
+                      &ctx->post_maps, &ctx->featp};
     for (DevBuf *b : bufs) b->release();
     if (ctx->prof.start) {
         for (int i = 0; i < Profiler::kMaxPairs; ++i) {
@@ -410,7 +481,8 @@ static int corr_args(int n, int h, int w, int c, int D, int precision)
 {
     STEREO_TRY(check_dims(n, h, w));
     STEREO_REQUIRE(c > 0 && D > 0, "channels and disp_range must be positive (got %d, %d)", c, D);
-    STEREO_REQUIRE(precision == STEREO_PREC_FP32, "precision mode %d is not available in this build", precision);
+    STEREO_REQUIRE(precision == STEREO_PREC_FP32 || precision == STEREO_PREC_BF16X3 || precision == STEREO_PREC_BF16,
+                   "unknown precision mode %d", precision);
     return STEREO_OK;
 }
 
@@ -420,7 +492,7 @@ int stereo_cost_volume_dev(stereo_ctx *ctx, const float *lmap, const float *rmap
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(corr_args(n, h, w, c, D, precision));
     STEREO_REQUIRE(lmap && rmap && left_vol && right_vol, "null pointer");
-    return launch_corr_ffma(ctx, lmap, rmap, n, h, w, c, D, left_vol, right_vol, nullptr, nullptr);
+    return corr_dev(ctx, lmap, rmap, n, h, w, c, D, precision, left_vol, right_vol, nullptr, nullptr);
 }
 
 int stereo_cost_volume(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
@@ -435,8 +507,8 @@ int stereo_cost_volume(stereo_ctx *ctx, const float *lmap, const float *rmap, in
     STEREO_TRY(h2d(ctx, ctx->stage_in[1], rmap, map_b));
     STEREO_TRY(ctx->stage_vol[0].reserve(vol_b));
     STEREO_TRY(ctx->stage_vol[1].reserve(vol_b));
-    STEREO_TRY(launch_corr_ffma(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D,
-                                ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(), nullptr, nullptr));
+    STEREO_TRY(corr_dev(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D, precision,
+                        ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(), nullptr, nullptr));
     STEREO_TRY(d2h(ctx, left_vol, ctx->stage_vol[0].ptr, vol_b));
     STEREO_TRY(d2h(ctx, right_vol, ctx->stage_vol[1].ptr, vol_b));
     return finish(ctx);
@@ -470,7 +542,7 @@ int stereo_corr_wta_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, i
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(corr_args(n, h, w, c, D, precision));
     STEREO_REQUIRE(lmap && rmap && left_disp && right_disp, "null pointer");
-    return launch_corr_ffma(ctx, lmap, rmap, n, h, w, c, D, nullptr, nullptr, left_disp, right_disp);
+    return corr_dev(ctx, lmap, rmap, n, h, w, c, D, precision, nullptr, nullptr, left_disp, right_disp);
 }
 
 int stereo_corr_wta(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c, int D,
@@ -485,8 +557,8 @@ int stereo_corr_wta(stereo_ctx *ctx, const float *lmap, const float *rmap, int n
     STEREO_TRY(h2d(ctx, ctx->stage_in[1], rmap, map_b));
     STEREO_TRY(ctx->stage_out[0].reserve(out_b));
     STEREO_TRY(ctx->stage_out[1].reserve(out_b));
-    STEREO_TRY(launch_corr_ffma(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D,
-                                nullptr, nullptr, ctx->stage_out[0].as<uint8_t>(), ctx->stage_out[1].as<uint8_t>()));
+    STEREO_TRY(corr_dev(ctx, ctx->stage_in[0].as<float>(), ctx->stage_in[1].as<float>(), n, h, w, c, D, precision,
+                        nullptr, nullptr, ctx->stage_out[0].as<uint8_t>(), ctx->stage_out[1].as<uint8_t>()));
     STEREO_TRY(d2h(ctx, left_disp, ctx->stage_out[0].ptr, out_b));
     STEREO_TRY(d2h(ctx, right_disp, ctx->stage_out[1].ptr, out_b));
     return finish(ctx);

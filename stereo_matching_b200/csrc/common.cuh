@@ -89,6 +89,8 @@ struct stereo_ctx {
     stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
     stereo::DevBuf stage_out[3];
     stereo::DevBuf stage_vol[2];
+    stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
+    int featp_geom[5] = {0, 0, 0, 0, 0};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
     stereo::DevBuf post_vol[3];  // working volumes of the post chain
     stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
@@ -130,6 +132,13 @@ int launch_weight_images(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv_tc(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
                    const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
                    int relu, int planes);
+// corr_tc.cu
+int corr_tc_max_disp();
+void corr_tc_geometry(int w, int D, int *wf, int *ml);
+int launch_nhwc_to_planar(stereo_ctx *ctx, const float *in, int n, int h, int w, int wf, int ml, void *hi, void *lo);
+int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
+                   int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
+                   uint8_t *left_disp, uint8_t *right_disp);
 // corr.cu
 int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
                      int D, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp);

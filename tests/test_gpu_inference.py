@@ -262,3 +262,62 @@ def test_tensor_core_trunk_rejects_base_model(ctx):
     with pytest.raises(_lib.StereoError) as e:
         m(np.zeros((1, 45, 60, 3), np.float32))
     assert e.value.code == -1
+
+
+# ---- tensor-core correlation (tcgen05), STEREO_PREC_BF16X3 ---------------------------------------
+@pytest.mark.parametrize("h,w,D", [(3, 10, 6), (2, 300, 228), (3, 129, 201), (2, 20, 33), (2, 150, 257), (4, 260, 64)])
+def test_cost_volume_tensor_core_vs_oracle(ctx, h, w, D):
+    rng = np.random.default_rng(w + D)
+    L = rng.standard_normal((2, h, w, 64)).astype(np.float32)
+    R = rng.standard_normal((2, h, w, 64)).astype(np.float32)
+    lv, rv = ctx.cost_volume(L, R, D, _lib.PREC_BF16X3)
+    for i in range(2):
+        lref, rref = so.cost_volumes(L[i:i + 1], R[i:i + 1], D, np.float64)
+        assert rel_err(lv[i], lref) < COST_TOL and rel_err(rv[i], rref) < COST_TOL
+    xs = np.arange(w)[:, None]
+    ds = np.arange(D)[None, :]
+    assert np.all(lv[0][:, xs < ds] == 0)            # zero-filled slots are exact zeros
+    assert np.all(rv[0][:, xs + ds >= w] == 0)
+    scale = np.abs(lv).max()
+    for d in range(0, min(D, w), max(D // 5, 1)):
+        assert np.abs(lv[0][:, d:, d] - rv[0][:, :w - d, d]).max() <= 1e-6 * scale
+    # fused WTA sees exactly the values that the materialising variant stores
+    ld, rd = ctx.corr_wta(L, R, D, _lib.PREC_BF16X3)
+    assert np.array_equal(ld, np.argmax(lv, axis=3).astype(np.uint8))
+    assert np.array_equal(rd, np.argmax(rv, axis=3).astype(np.uint8))
+
+
+def test_tensor_core_wta_zero_fill_and_ties(ctx):
+    L = np.ones((1, 1, 5, 64), np.float32)
+    R = -np.ones((1, 1, 5, 64), np.float32)
+    ld, rd = ctx.corr_wta(L, R, 4, _lib.PREC_BF16X3)
+    lref, rref = so.cost_volumes(L, R, 4)
+    assert np.array_equal(ld[0], so.wta(lref)) and np.array_equal(rd[0], so.wta(rref))
+    Z = np.zeros((1, 2, 140, 64), np.float32)      # all ties -> disparity 0 everywhere
+    ld, rd = ctx.corr_wta(Z, Z, 100, _lib.PREC_BF16X3)
+    assert not ld.any() and not rd.any()
+
+
+def test_tensor_core_correlation_falls_back_to_cuda_cores_for_wide_ranges(ctx):
+    rng = np.random.default_rng(1)
+    L = rng.standard_normal((1, 1, 400, 64)).astype(np.float32)
+    R = rng.standard_normal((1, 1, 400, 64)).astype(np.float32)
+    lv, rv = ctx.cost_volume(L, R, 300, _lib.PREC_BF16X3)      # D > 257: fp32 CUDA-core kernel
+    lref, rref = so.cost_volumes(L, R, 300, np.float64)
+    assert rel_err(lv[0], lref) < 1e-5 and rel_err(rv[0], rref) < 1e-5
+
+
+def test_full_size_tensor_core_pipeline(ctx):
+    """375x1242, D=228 through trunk + correlation on the tensor cores vs the fp32 CUDA-core path."""
+    D = 228
+    l, r, gt = synth.make_pair(1001, 375, 1242, D)
+    a = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_FP32, volumes=True)
+    b = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    assert rel_err(b["left_cost"][0], a["left_cost"][0].astype(np.float64)) < COST_TOL
+    assert rel_err(b["right_cost"][0], a["right_cost"][0].astype(np.float64)) < COST_TOL
+    assert (a["left_disp"] == b["left_disp"]).mean() >= WTA_AGREE
+    assert (a["right_disp"] == b["right_disp"]).mean() >= WTA_AGREE
+    assert np.array_equal(b["left_disp"][0], np.argmax(b["left_cost"][0], axis=2).astype(np.uint8))
+    c = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=False)
+    assert np.array_equal(c["left_disp"], b["left_disp"]) and np.array_equal(c["right_disp"], b["right_disp"])
+    assert abs(so.three_pixel_error(a["left_disp"][0], gt) - so.three_pixel_error(b["left_disp"][0], gt)) <= 0.0005
