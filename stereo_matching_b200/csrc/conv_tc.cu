@@ -42,7 +42,8 @@ constexpr int kWTapBytes = 8 * kNHalf * 16;            // one tap, one plane: [k
 constexpr int kWBytes = 9 * 2 * kWTapBytes;            // 73,728
 constexpr int kSmemBars = kWBytes + kSlots * kSlotBytes;
 constexpr int kSmemTotal = kSmemBars + 16 * 8 + 16;
-constexpr uint32_t kTmemCols = 64;
+constexpr int kIssuers = 2;
+constexpr uint32_t kTmemCols = 128;             // 2 buffers x kIssuers partial accumulators x 32 columns
 
 struct Params {
     const __nv_bfloat16 *in_hi, *in_lo;   // chunk-planar [img][h_in][8][wp_in][8]
@@ -79,11 +80,11 @@ __global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
     if (tid == 0) {
         for (int i = 0; i < kSlots; ++i) {
             mbar_init(bar_full + 8 * i, 1);
-            mbar_init(bar_empty + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, kIssuers);
         }
         mbar_init(bar_w, 1);
         for (int i = 0; i < 2; ++i) {
-            mbar_init(bar_acc_full + 8 * i, 1);
+            mbar_init(bar_acc_full + 8 * i, kIssuers);
             mbar_init(bar_acc_empty + 8 * i, 4);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -119,10 +120,15 @@ __global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == 2) {
         if (lane == 0) {
-            // ---- MMA issuer ----
+            // ---- MMA issuers: the K loop (operand-split combination x tap) is dealt out to
+            // kIssuers threads, each accumulating into its own TMEM block; the epilogue adds the
+            // partial sums.  One thread alone cannot issue 108 small MMAs per row fast enough.
+            const int issuer = warp - 1;
             constexpr uint32_t idesc = make_idesc(kStripW, kNHalf);
+            const uint32_t a_hi = desc_hi(128), b_hi = desc_hi(128);
+            const int n_units = (p.planes == 2 ? 3 : 1) * 9;
             mbar_wait(bar_w, 0);
             for (int j = 0; j < rows_out; ++j) {
                 const int b = j & 1;
@@ -133,31 +139,28 @@ __global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
                 }
                 mbar_wait(bar_full + 8 * ((j + 2) & 3), ((j + 2) >> 2) & 1);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + (uint32_t)b * kNHalf;
+                const uint32_t tmem_d = tmem_base + (uint32_t)(b * kIssuers + issuer) * kNHalf;
                 uint32_t acc = 0;
-                // (activation plane, weight plane): lo*hi and hi*lo first, hi*hi last
-                const int n_combo = p.planes == 2 ? 3 : 1;
-                for (int combo = 0; combo < n_combo; ++combo) {
-                    const int apl = (n_combo == 3 && combo == 0) ? 1 : 0;
-                    const int wpl = (n_combo == 3 && combo == 1) ? 1 : 0;
 #pragma unroll 1
-                    for (int ky = 0; ky < 3; ++ky) {
-                        const uint32_t a_row = s_rows + ((j + ky) & 3) * kSlotBytes + apl * kPlaneBytes;
+                for (int u = issuer; u < n_units; u += kIssuers) {
+                    // (activation plane, weight plane): lo*hi, hi*lo, then hi*hi
+                    const int combo = u / 9, tap = u - combo * 9;
+                    const int ky = tap / 3, kx = tap - ky * 3;
+                    const int apl = (p.planes == 2 && combo == 0) ? 1 : 0;
+                    const int wpl = (p.planes == 2 && combo == 1) ? 1 : 0;
+                    // descriptor lo words; the K steps add compile-time constants (all offsets are
+                    // multiples of 16 bytes and stay below 2^18, so the address field never carries)
+                    const uint32_t a_lo = desc_lo(s_rows + ((j + ky) & 3) * kSlotBytes + apl * kPlaneBytes + kx * 16, kRunBytes);
+                    const uint32_t b_lo = desc_lo(s_w + tap * 2 * kWTapBytes + wpl * kWTapBytes, kNHalf * 16);
 #pragma unroll
-                        for (int kx = 0; kx < 3; ++kx) {
-                            const uint32_t b_tap = s_w + (ky * 3 + kx) * 2 * kWTapBytes + wpl * kWTapBytes;
-#pragma unroll
-                            for (int ks = 0; ks < 4; ++ks) {
-                                uint64_t ad = smem_desc(a_row + 2 * ks * kRunBytes + kx * 16, kRunBytes, 128);
-                                uint64_t bd = smem_desc(b_tap + 2 * ks * (kNHalf * 16), kNHalf * 16, 128);
-                                umma_bf16(tmem_d, ad, bd, idesc, acc);
-                                acc = 1;
-                            }
-                        }
+                    for (int ks = 0; ks < 4; ++ks) {
+                        umma_bf16_parts(tmem_d, a_lo + ((2 * ks * kRunBytes) >> 4), a_hi,
+                                        b_lo + ((2 * ks * (kNHalf * 16)) >> 4), b_hi, idesc, acc);
+                        acc = 1;
                     }
                 }
-                tc_commit(bar_empty + 8 * (j & 3));      // input row j is no longer needed
-                tc_commit(bar_acc_full + 8 * b);         // accumulator b is complete
+                tc_commit(bar_empty + 8 * (j & 3));      // this issuer no longer needs input row j
+                tc_commit(bar_acc_full + 8 * b);         // this issuer's partial accumulator is complete
             }
             // rows j+1, j+2 of the last step are never released through the ring; nothing waits on them
         }
@@ -172,19 +175,10 @@ __global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
             const int b = j & 1;
             mbar_wait(bar_acc_full + 8 * b, (j >> 1) & 1);
             tc_fence_after();
-            uint32_t v[kNHalf];
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)b * kNHalf;
-            asm volatile(
-                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]),
-                  "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]),
-                  "=r"(v[30]), "=r"(v[31])
-                : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            uint32_t v[kNHalf], v2[kNHalf];
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(b * kIssuers) * kNHalf;
+            tmem_ld_32x32(taddr, v);
+            tmem_ld_32x32(taddr + kNHalf, v2);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_acc_empty + 8 * b);    // the accumulator may be overwritten
@@ -194,7 +188,7 @@ __global__ __launch_bounds__(256, 1) void conv3x3_tc_kernel(Params p)
                 float f[kNHalf];
 #pragma unroll
                 for (int i = 0; i < kNHalf; ++i) {
-                    f[i] = __uint_as_float(v[i]) + bias[i];
+                    f[i] = (__uint_as_float(v[i]) + __uint_as_float(v2[i])) + bias[i];
                     if (p.relu) f[i] = fmaxf(f[i], 0.f);
                 }
                 if (p.out_f32) {
