@@ -175,6 +175,23 @@ int stereo_nyu_post(stereo_ctx *ctx, const float *disp_left, const float *disp_r
 /* post.lua:146-147 `vol:std()`: unbiased std over the whole volume. */
 int stereo_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *std_out);
 
+/* No counterpart in the reference.  The unbiased std of `stereo_volume_std` for callers that
+ * cannot allocate device memory: a loop that fixes its memory map at start-up and bans later
+ * cudaMalloc calls (they stall the device and can fail under fragmentation), or a host whose
+ * own pool already holds all of HBM.  This call allocates nothing - no cudaMalloc, no
+ * cudaFree, no library allocator: the per-block partial sums go to a 64 KB array built into
+ * the library (resident on every GPU that loads it until exit).
+ *   vol, result : DEVICE pointers on the current device; result receives 2 floats,
+ *                 result[0] = std (unbiased), result[1] = mean.  Work is enqueued on
+ *                 `cuda_stream` (a cudaStream_t, NULL = default stream) and not synchronised.
+ *   n           : 2 <= n <= 268,435,456 elements; larger inputs are refused with
+ *                 STEREO_E_LIMIT (use stereo_volume_std).
+ * The first call on each device looks up the array's device address (that device must be
+ * current); make that first call before any stream capture begins.  All calls share the one
+ * array: two calls whose kernels overlap on the GPU (different streams, no ordering) race on
+ * it and give wrong results - serialise them.  Nothing needs clearing between calls. */
+int stereo_volume_std_static(const float *vol, size_t n, float *result, void *cuda_stream);
+
 /* The loop body of post.lua:78-243 for one pair: CBCA -> /std -> negate -> SGM -> CBCA ->
  * LR check, occlusion / mismatch fill, sub-pixel, median, bilateral.  Inputs are what
  * inference.py wrote: the two volumes and the two uint8 WTA maps, which post.lua loads as its

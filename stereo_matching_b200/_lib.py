@@ -69,6 +69,7 @@ SIGNATURES = {
     "stereo_nyu_sgm": [_c_ctx, _p, _p, _p, _i, _i, _i, _i, _pp],
     "stereo_nyu_post": [_c_ctx, _p, _p, _p, _i, _i, _i, _pp, _p, _p],
     "stereo_volume_std": [_c_ctx, _p, ctypes.c_size_t, _p],
+    "stereo_volume_std_static": [_p, ctypes.c_size_t, _p, _p],
     "stereo_post": [_c_ctx, _p, _p, _p, _p, _i, _i, _i, _pp, ctypes.POINTER(_p), _p],
     "stereo_post_dev": [_c_ctx, _p, _p, _p, _p, _i, _i, _i, _pp, ctypes.POINTER(_p), _p],
     "stereo_profile_enable": [_c_ctx, _i],

@@ -257,6 +257,63 @@ int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result
     return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>(), result);
 }
 
+// ------------------------------------------------------------------------------------------
+// stereo_volume_std_static: the same reduction for callers that must not allocate.
+//
+// Who that is: a perception loop that carves up device memory once at start-up and forbids
+// any later cudaMalloc (it synchronises the whole device and may fail once memory is
+// fragmented), or a host process whose own pool already owns all of HBM, so that an
+// allocation made behind its back by this library would simply fail.  For them the per-block
+// partial sums live in a fixed array that is part of the library image; every GPU that loads
+// the library carries these 64 KB until the process exits.
+// ------------------------------------------------------------------------------------------
+constexpr int kStaticStdMaxBlocks = 4096;
+constexpr size_t kStaticStdElemsPerBlock = 65536;     // so at most 268,435,456 elements (1 GiB of fp32)
+static __device__ __align__(256) double g_static_std_scratch[2 * kStaticStdMaxBlocks];
+
+// In host code `g_static_std_scratch` is only a handle for the symbol, not a device address;
+// the address is looked up once per device and kept here.
+constexpr int kMaxDevices = 64;
+static double *g_static_std_addr[kMaxDevices] = {};
+
+}  // namespace stereo
+
+extern "C" int stereo_volume_std_static(const float *vol, size_t n, float *result, void *cuda_stream)
+{
+    using namespace stereo;
+    STEREO_REQUIRE(vol != nullptr && result != nullptr, "null pointer");
+    STEREO_REQUIRE(n >= 2, "the unbiased std needs at least 2 elements, got %zu", n);
+    const size_t max_n = (size_t)kStaticStdMaxBlocks * kStaticStdElemsPerBlock;
+    if (n > max_n) {
+        set_error("stereo_volume_std_static handles at most %zu elements (its scratch array is fixed at %d partial "
+                  "sums); got %zu - use stereo_volume_std",
+                  max_n, kStaticStdMaxBlocks, n);
+        return STEREO_E_LIMIT;
+    }
+    int dev = -1;
+    STEREO_CUDA_CHECK(cudaGetDevice(&dev));
+    STEREO_REQUIRE(dev >= 0 && dev < kMaxDevices, "device index %d is beyond the %d this entry point tracks", dev,
+                   kMaxDevices);
+    if (g_static_std_addr[dev] == nullptr) {
+        // first call on this device (with it current): resolve the symbol to a device pointer
+        double *addr = nullptr;
+        STEREO_CUDA_CHECK(cudaGetSymbolAddress((void **)&addr, g_static_std_scratch));
+        STEREO_REQUIRE(addr != nullptr, "cudaGetSymbolAddress returned a null address");
+        g_static_std_addr[dev] = addr;
+    }
+    double *scratch = g_static_std_addr[dev];
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    const int nblocks = (int)((n + kStaticStdElemsPerBlock - 1) / kStaticStdElemsPerBlock);
+    // Nothing has to be cleared: block b writes slots 2b and 2b+1 before the final kernel reads
+    // exactly the first 2*nblocks slots, so whatever the previous call left behind is never read.
+    volume_moments_kernel<<<nblocks, 256, 0, stream>>>(vol, n, scratch);
+    volume_std_final_kernel<<<1, 32, 0, stream>>>(scratch, nblocks, (double)n, result);
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+namespace stereo {
+
 // elementwise helpers of post.lua:146-153 and nyu.lua:61,64
 __global__ void scale_kernel(const float *__restrict__ in, size_t n, const float *__restrict__ stdp, int mode,
                              float *__restrict__ out)
