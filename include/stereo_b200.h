@@ -147,6 +147,8 @@ typedef struct stereo_post_params {
     double blur_sigma;                              /* :21  (a Lua double; the Gaussian of nyu.lua:77-89 is built in double) */
     float blur_t;                                   /* :22 */
     int nyu_cost_agg_1, sgm, nyu_cost_agg_2, post;  /* post.lua:37-40 */
+    int cbca_exact;  /* 0: separable CBCA (row sums first; same sum, last-bit differences);
+                        1: the original's strictly sequential summation order (slower) */
 } stereo_post_params;
 /* the constants of smooth/nyu.lua:3-22 and the option defaults of post.lua:10-49 */
 int stereo_post_default_params(stereo_post_params *p);

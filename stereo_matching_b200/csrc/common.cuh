@@ -92,7 +92,8 @@ struct stereo_ctx {
     stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
     int featp_geom[5] = {0, 0, 0, 0, 0};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
-    stereo::DevBuf post_vol[3];  // working volumes of the post chain
+    stereo::DevBuf post_vol[4];  // working volumes of the post chain
+    stereo::DevBuf post_cnt;     // row-segment lengths of the separable CBCA (uint8 per voxel)
     stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
 };
 
@@ -153,6 +154,8 @@ int launch_guide(stereo_ctx *ctx, const uint8_t *img, int h, int w, float *out);
 int launch_cross(stereo_ctx *ctx, const float *img, int h, int w, int L1, float tau1, short *arms);
 int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
                 int D, int direction);
+int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
+                          uint8_t *hcnt, float *out, int h, int w, int D, int direction);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,

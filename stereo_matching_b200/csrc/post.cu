@@ -195,6 +195,91 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
     return STEREO_OK;
 }
 
+// Separable form of the same aggregation.  The support region of (y, x, d) is a union of row
+// segments: rows yy between the vertical arm ends, and on row yy the segment fixed by the arms
+// at (yy, x) and (yy, x + d*dir) - which depends on (yy, x, d) only.  So
+//   hsum[yy][x][d] = sum over that segment,  hcnt = its length            (horizontal pass)
+//   out[y][x][d]   = sum_yy hsum[yy][x][d] / sum_yy hcnt[yy][x][d]        (vertical pass)
+// is the same sum with <= 9 + 9 instead of <= 81 loads per voxel.  Mathematically identical to
+// cbca_kernel; the fp32 additions associate per row first, so results differ from the
+// original's strictly sequential order in the last bits (tests bound it at 2e-6 relative).
+__global__ __launch_bounds__(256) void cbca_h_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+                                                     const float *__restrict__ vol, float *__restrict__ hsum,
+                                                     uint8_t *__restrict__ hcnt, int h, int w, int D, int direction)
+{
+    const int lane = threadIdx.x & 31;
+    const int chunks = (D + 31) >> 5;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t hw = (size_t)h * w;
+    if (warp >= hw * chunks) return;
+    int chunk = (int)(warp % chunks);
+    size_t pix = warp / chunks;
+    int x = (int)(pix % w);
+    int d = chunk * 32 + lane;
+    if (d >= D) return;
+    size_t id = pix * D + d;
+    int xm = x + d * direction;
+    if (xm < 0 || xm >= w) {           // copied through by the vertical pass
+        hsum[id] = vol[id];
+        hcnt[id] = 0;
+        return;
+    }
+    const int shift = d * direction;
+    size_t rowpix = pix - x;
+    int xx_s = max((int)x0c[pix], (int)x1c[rowpix + xm] - shift);
+    int xx_t = min((int)x0c[hw + pix], (int)x1c[hw + rowpix + xm] - shift);
+    const float *vrow = vol + rowpix * D + d;
+    float sum = 0.f;
+    for (int xx = xx_s + 1; xx < xx_t; ++xx) sum = __fadd_rn(sum, vrow[(size_t)xx * D]);
+    hsum[id] = sum;
+    hcnt[id] = (uint8_t)(xx_t - xx_s - 1);
+}
+
+__global__ __launch_bounds__(256) void cbca_v_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+                                                     const float *__restrict__ hsum, const uint8_t *__restrict__ hcnt,
+                                                     float *__restrict__ out, int h, int w, int D, int direction)
+{
+    const int lane = threadIdx.x & 31;
+    const int chunks = (D + 31) >> 5;
+    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    size_t hw = (size_t)h * w;
+    if (warp >= hw * chunks) return;
+    int chunk = (int)(warp % chunks);
+    size_t pix = warp / chunks;
+    int x = (int)(pix % w), y = (int)(pix / w);
+    int d = chunk * 32 + lane;
+    if (d >= D) return;
+    size_t id = pix * D + d;
+    int xm = x + d * direction;
+    if (xm < 0 || xm >= w) {
+        out[id] = hsum[id];
+        return;
+    }
+    int yy_s = max((int)x0c[2 * hw + pix], (int)x1c[2 * hw + (size_t)y * w + xm]);
+    int yy_t = min((int)x0c[3 * hw + pix], (int)x1c[3 * hw + (size_t)y * w + xm]);
+    const size_t col = (size_t)x * D + d, pitch = (size_t)w * D;
+    float sum = 0.f;
+    int cnt = 0;
+    for (int yy = yy_s + 1; yy < yy_t; ++yy) {
+        sum = __fadd_rn(sum, hsum[yy * pitch + col]);
+        cnt += hcnt[yy * pitch + col];
+    }
+    out[id] = __fdiv_rn(sum, (float)cnt);
+}
+
+int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
+                          uint8_t *hcnt, float *out, int h, int w, int D, int direction)
+{
+    size_t warps = (size_t)h * w * ((D + 31) / 32);
+    size_t blocks = (warps + 7) / 8;
+    ProfScope prof(ctx, STEREO_K_CBCA);
+    cbca_h_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
+    cbca_v_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
+    ctx->launches += 2;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 // ------------------------------------------------------------------------------------------
 // post.lua:146-147  vol / vol:std()  - unbiased std over the whole volume (zero band
 // included).  Two-stage float64 reduction through a scratch array of per-block partials;
@@ -338,140 +423,187 @@ int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, 
 // ------------------------------------------------------------------------------------------
 // P3  adcensus.sgm2 (nyu.lua:59-60): 4-path semi-global matching with intensity-adaptive
 //     penalties.  The original launches one kernel per scanline STEP (2W+2H launches per
-//     volume); here one CTA owns a whole scanline and walks it: thread = disparity, the
-//     previous step's path costs live in shared memory (double buffered, one barrier per
-//     step), the block minimum is a shuffle reduction, and the next step's costs are
-//     prefetched while the current step is computed.
-//     in:  C[h][w][D] cost (optionally C = -(raw / std) applied on the fly)
+//     volume) with one thread per disparity.  Here one WARP owns a whole scanline and walks
+//     it: each lane keeps KPL consecutive disparities of the previous step's path costs in
+//     registers, the neighbours d-1 / d+1 across lanes come from two shuffles, the minimum
+//     over D from a shuffle reduction - no shared memory and no block barrier on the
+//     serial chain - and the costs (and running sums) of the next PF steps are already in
+//     flight as 16-byte loads when a step is computed.
+//     in:  C[h][w][D] cost (optionally C = -(raw / std) applied on the fly, post.lua:146,152)
 //     out: accumulates the path cost; with `first` the kernel writes instead of adding and
 //          with `last` it writes (acc + Lr) / 4, fusing nyu.lua:61,64.
+//     Arithmetic per voxel is that of the original, operation for operation.
 // ------------------------------------------------------------------------------------------
-template <int SD>
-__global__ __launch_bounds__(512) void sgm_path_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
-                                                       const float *__restrict__ vol,
-                                                       const float *__restrict__ stdp, float *__restrict__ out,
-                                                       int h, int w, int D, SgmParams p, int direction,
-                                                       int first, int last)
+template <int SD, int KPL, int PF, bool VEC>
+__global__ __launch_bounds__(32) void sgm_warp_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
+                                                      const float *__restrict__ vol,
+                                                      const float *__restrict__ stdp, float *__restrict__ out,
+                                                      int h, int w, int D, SgmParams p, int direction, int first,
+                                                      int last)
 {
-    extern __shared__ float sm[];
-    const int d = threadIdx.x;
-    const int nt = blockDim.x;
-    const int nwarp = nt >> 5;
-    float *prev_s = sm;                 // [2][nt + 2] with a guard element on both sides
-    float *wmin_s = sm + 2 * (nt + 2);  // [2][32]
-    const bool active = d < D;
-
     constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
     constexpr int dy = SD == 2 ? 1 : (SD == 3 ? -1 : 0);
+    const int lane = threadIdx.x;
     const int line = blockIdx.x;
     const int steps = dy == 0 ? w : h;
     int x = dy == 0 ? (SD == 0 ? 0 : w - 1) : line;
     int y = dy == 0 ? line : (SD == 2 ? 0 : h - 1);
-
+    const int d0 = lane * KPL;
     const float sd = stdp ? stdp[0] : 1.f;
-    auto load_cost = [&](int yy, int xx) -> float {
-        if (!active) return 0.f;
-        float v = vol[((size_t)yy * w + xx) * D + d];
-        if (stdp) v = __fmul_rn(__fdiv_rn(v, sd), -1.f);   // post.lua:146,152: (x / std) * -1
-        return v;
-    };
-    // penalties (the three cases of the original, with and without the alpha1 division)
+    const float kBig = 3.402823466e38f;
+
+    // the three penalty cases of the original, with and without the alpha1 division
     const float P1a = p.pi1, P2a = p.pi2;
     const float P1b = __fdiv_rn(p.pi1, __fmul_rn(p.q1, p.q2)), P2b = __fdiv_rn(p.pi2, __fmul_rn(p.q1, p.q2));
     const float P1c = __fdiv_rn(p.pi1, p.q1), P2c = __fdiv_rn(p.pi2, p.q1);
+    // "P1 / alpha1" applies to the d-1 term on the downward path and to the d+1 term on the upward one
+    const float P1a_m = SD == 2 ? __fdiv_rn(P1a, p.alpha1) : P1a, P1a_p = SD == 3 ? __fdiv_rn(P1a, p.alpha1) : P1a;
+    const float P1b_m = SD == 2 ? __fdiv_rn(P1b, p.alpha1) : P1b, P1b_p = SD == 3 ? __fdiv_rn(P1b, p.alpha1) : P1b;
+    const float P1c_m = SD == 2 ? __fdiv_rn(P1c, p.alpha1) : P1c, P1c_p = SD == 3 ? __fdiv_rn(P1c, p.alpha1) : P1c;
 
-    // Costs (and, for the accumulating passes, the running sums) are fetched a whole
-    // group of steps ahead so that enough loads are in flight to cover HBM latency.
-    constexpr int PF = 8;
-    auto load_acc = [&](int yy, int xx) -> float {
-        return (active && !first) ? out[((size_t)yy * w + xx) * D + d] : 0.f;
+    const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;     // floats between consecutive steps
+    const float *cptr = vol + ((size_t)y * w + x) * D + d0;
+    float *optr = out + ((size_t)y * w + x) * D + d0;
+
+    auto load_row = [&](const float *src, float (&dst)[KPL], bool scale) {
+        if (VEC) {
+#pragma unroll
+            for (int j = 0; j < KPL / 4; ++j) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (d0 + 4 * j < D) v = __ldg(reinterpret_cast<const float4 *>(src) + j);
+                dst[4 * j] = v.x; dst[4 * j + 1] = v.y; dst[4 * j + 2] = v.z; dst[4 * j + 3] = v.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) dst[k] = d0 + k < D ? __ldg(src + k) : 0.f;
+        }
+        if (scale) {
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) dst[k] = __fmul_rn(__fdiv_rn(dst[k], sd), -1.f);   // (x / std) * -1
+        }
     };
-    float cbuf[PF], obuf[PF];
+
+    float cbuf[PF][KPL], obuf[PF][KPL];
 #pragma unroll
     for (int i = 0; i < PF; ++i) {
-        bool ok = i < steps;
-        cbuf[i] = ok ? load_cost(y + i * dy, x + i * dx) : 0.f;
-        obuf[i] = ok ? load_acc(y + i * dy, x + i * dx) : 0.f;
-    }
-    float i1_prev = 0.f;     // x1 at the matched pixel of the previous step
-    int buf = 0;
-    for (int g = 0; g < steps; g += PF) {
-        float cn[PF], on[PF];
-#pragma unroll
-        for (int i = 0; i < PF; ++i) {
-            bool ok = g + PF + i < steps;
-            cn[i] = ok ? load_cost(y + (PF + i) * dy, x + (PF + i) * dx) : 0.f;
-            on[i] = ok ? load_acc(y + (PF + i) * dy, x + (PF + i) * dx) : 0.f;
+        if (i < steps) {
+            load_row(cptr + i * vstride, cbuf[i], stdp != nullptr);
+            if (!first) load_row(optr + i * vstride, obuf[i], false);
         }
+    }
+
+    float prev[KPL], i1p[KPL];
+#pragma unroll
+    for (int k = 0; k < KPL; ++k) { prev[k] = 0.f; i1p[k] = 0.f; }
+
+    for (int g = 0; g < steps; g += PF) {
 #pragma unroll
         for (int i = 0; i < PF; ++i) {
             const int step = g + i;
             if (step >= steps) break;
-            const float cost = cbuf[i];
-            const int xx = x + d * direction;
-            const bool xx_ok = active && xx >= 0 && xx < w;
-            float i1_cur = xx_ok ? x1[(size_t)y * w + xx] : 0.f;
-            float val;
-            if (step == 0) {
-                val = cost;
-            } else {
-                const float *pv = prev_s + buf * (nt + 2) + 1;
-                float pmin = wmin_s[buf * 32];
-                for (int k = 1; k < nwarp; ++k) pmin = fminf(pmin, wmin_s[buf * 32 + k]);
-                float D1 = fabsf(x0[(size_t)y * w + x] - x0[(size_t)(y - dy) * w + (x - dx)]);
-                float D2;
-                // the matched pixel of the previous step is (xx - dx, y - dy); its x1 value
-                // was kept in a register
-                if (!xx_ok || xx - dx < 0 || xx - dx >= w) D2 = 10.f;
-                else D2 = fabsf(i1_cur - i1_prev);
-                float P1, P2;
-                if (D1 < p.tau_so && D2 < p.tau_so) { P1 = P1a; P2 = P2a; }
-                else if (D1 > p.tau_so && D2 > p.tau_so) { P1 = P1b; P2 = P2b; }
-                else { P1 = P1c; P2 = P2c; }
-                float c = fminf(pv[d], __fadd_rn(pmin, P2));
-                if (d - 1 >= 0) c = fminf(c, __fadd_rn(pv[d - 1], SD == 2 ? __fdiv_rn(P1, p.alpha1) : P1));
-                if (d + 1 < D) c = fminf(c, __fadd_rn(pv[d + 1], SD == 3 ? __fdiv_rn(P1, p.alpha1) : P1));
-                val = __fadd_rn(__fadd_rn(cost, c), -pmin);
-            }
-            if (active) {
-                size_t o = ((size_t)y * w + x) * D + d;
-                float acc = first ? val : __fadd_rn(obuf[i], val);
-                out[o] = last ? __fdiv_rn(acc, 4.f) : acc;
-            }
-            // publish this step's path costs for the next one
-            buf ^= 1;
-            prev_s[buf * (nt + 2) + 1 + d] = val;
-            float m = active ? val : 3.402823466e38f;
+            // guide values at the matched pixels of this step (L1-resident rows)
+            float i1c[KPL];
+            const float *g1 = x1 + (size_t)y * w + x;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) m = fminf(m, __shfl_xor_sync(0xffffffffu, m, o));
-            if ((d & 31) == 0) wmin_s[buf * 32 + (d >> 5)] = m;
-            __syncthreads();
-            i1_prev = i1_cur;
+            for (int k = 0; k < KPL; ++k) {
+                const int xx = x + (d0 + k) * direction;
+                i1c[k] = (xx >= 0 && xx < w) ? __ldg(g1 + (d0 + k) * direction) : 0.f;
+            }
+            float val[KPL];
+            if (step == 0) {
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) val[k] = cbuf[i][k];
+            } else {
+                float pmin = kBig;
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) pmin = fminf(pmin, d0 + k < D ? prev[k] : kBig);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) pmin = fminf(pmin, __shfl_xor_sync(0xffffffffu, pmin, o));
+                const float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
+                const float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
+                const float D1 = fabsf(__ldg(x0 + (size_t)y * w + x) - __ldg(x0 + (size_t)(y - dy) * w + (x - dx)));
+                const bool d1_lt = D1 < p.tau_so, d1_gt = D1 > p.tau_so;
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) {
+                    const int d = d0 + k;
+                    const int xx = x + d * direction;
+                    // the matched pixel of the previous step is (xx - dx, y - dy); its x1 value is i1p[k]
+                    float D2;
+                    if (xx < 0 || xx >= w || xx - dx < 0 || xx - dx >= w) D2 = 10.f;
+                    else D2 = fabsf(i1c[k] - i1p[k]);
+                    float P1m, P1p, P2;
+                    if (d1_lt && D2 < p.tau_so) { P1m = P1a_m; P1p = P1a_p; P2 = P2a; }
+                    else if (d1_gt && D2 > p.tau_so) { P1m = P1b_m; P1p = P1b_p; P2 = P2b; }
+                    else { P1m = P1c_m; P1p = P1c_p; P2 = P2c; }
+                    float c = fminf(prev[k], __fadd_rn(pmin, P2));
+                    const float pm = k > 0 ? prev[k > 0 ? k - 1 : 0] : below;
+                    const float pp = k < KPL - 1 ? prev[k < KPL - 1 ? k + 1 : 0] : above;
+                    if (d - 1 >= 0) c = fminf(c, __fadd_rn(pm, P1m));
+                    if (d + 1 < D) c = fminf(c, __fadd_rn(pp, P1p));
+                    val[k] = __fadd_rn(__fadd_rn(cbuf[i][k], c), -pmin);
+                }
+            }
+            // accumulate into the output volume
+            float res[KPL];
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) {
+                float acc = first ? val[k] : __fadd_rn(obuf[i][k], val[k]);
+                res[k] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
+            }
+            if (VEC) {
+#pragma unroll
+                for (int j = 0; j < KPL / 4; ++j)
+                    if (d0 + 4 * j < D)
+                        reinterpret_cast<float4 *>(optr)[j] = make_float4(res[4 * j], res[4 * j + 1], res[4 * j + 2], res[4 * j + 3]);
+            } else {
+#pragma unroll
+                for (int k = 0; k < KPL; ++k)
+                    if (d0 + k < D) optr[k] = res[k];
+            }
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) { prev[k] = val[k]; i1p[k] = i1c[k]; }
+            // refill this ring slot with the step PF ahead
+            if (step + PF < steps) {
+                load_row(cptr + (ptrdiff_t)PF * vstride, cbuf[i], stdp != nullptr);
+                if (!first) load_row(optr + (ptrdiff_t)PF * vstride, obuf[i], false);
+            }
+            cptr += vstride;
+            optr += vstride;
             x += dx;
             y += dy;
         }
-#pragma unroll
-        for (int i = 0; i < PF; ++i) { cbuf[i] = cn[i]; obuf[i] = on[i]; }
     }
+}
+
+template <int KPL, int PF, bool VEC>
+static int launch_sgm_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp,
+                        float *out, int h, int w, int D, const SgmParams &p, int direction)
+{
+    sgm_warp_kernel<0, KPL, PF, VEC><<<h, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 1, 0);
+    sgm_warp_kernel<1, KPL, PF, VEC><<<h, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
+    sgm_warp_kernel<2, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
+    sgm_warp_kernel<3, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 1);
+    ctx->launches += 4;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
 }
 
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,
                int h, int w, int D, const SgmParams &p, int direction)
 {
-    int nt = (D + 31) / 32 * 32;
-    if (nt > 512) {
-        set_error("SGM supports disp_range <= 512 (one thread per disparity), got %d", D);
+    if (D > 512) {
+        set_error("SGM supports disp_range <= 512 (16 disparities per lane), got %d", D);
         return STEREO_E_LIMIT;
     }
-    size_t smem = sizeof(float) * (2 * (nt + 2) + 64);
+    // 16-byte loads need every [x][d] row to start 16-byte aligned
+    const bool vec = D % 4 == 0 && ((uintptr_t)vol % 16 == 0) && ((uintptr_t)out % 16 == 0);
     ProfScope prof(ctx, STEREO_K_SGM);
-    sgm_path_kernel<0><<<h, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 1, 0);
-    sgm_path_kernel<1><<<h, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
-    sgm_path_kernel<2><<<w, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
-    sgm_path_kernel<3><<<w, nt, smem, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 1);
-    ctx->launches += 4;
-    STEREO_CUDA_CHECK(cudaGetLastError());
-    return STEREO_OK;
+    if (D <= 128) return vec ? launch_sgm_t<4, 4, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
+                             : launch_sgm_t<4, 4, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
+    if (D <= 256) return vec ? launch_sgm_t<8, 4, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
+                             : launch_sgm_t<8, 4, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
+    return vec ? launch_sgm_t<16, 2, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
+               : launch_sgm_t<16, 2, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
 }
 
 // ------------------------------------------------------------------------------------------

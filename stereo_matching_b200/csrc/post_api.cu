@@ -70,6 +70,15 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
     return STEREO_OK;
 }
 
+// one adcensus.cbca call in either summation order; `tmp` is a spare volume for the separable form
+static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
+                    float *tmp, float *out, int h, int w, int D, int direction)
+{
+    if (p->cbca_exact) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
+    STEREO_TRY(ctx->post_cnt.reserve((size_t)h * w * D));
+    return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt.as<uint8_t>(), out, h, w, D, direction);
+}
+
 // nyu.lua:91-115 on device maps
 static int nyu_post_dev(stereo_ctx *ctx, PostMaps &m, const float *left_vol, int h, int w, int D,
                         const stereo_post_params *p, float **final_out)
@@ -118,7 +127,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
-    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 4; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
     STEREO_TRY(launch_guide(ctx, left_disp, h, w, m.guide_l));
     STEREO_TRY(launch_guide(ctx, right_disp, h, w, m.guide_r));
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
@@ -129,7 +138,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     // read goes back to the free list unless it is the caller's (read-only) input.  The left
     // result keeps one buffer (sub-pixel refinement needs it), the right side uses the other two.
     std::vector<float *> pool = {ctx->post_vol[0].as<float>(), ctx->post_vol[1].as<float>(),
-                                 ctx->post_vol[2].as<float>()};
+                                 ctx->post_vol[2].as<float>(), ctx->post_vol[3].as<float>()};
     const float *left_final = nullptr;
     for (int side = 0; side < 2; ++side) {
         const int direction = side == 0 ? -1 : 1;
@@ -147,7 +156,9 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         // nyu_cost_agg_1 (post.lua:116-133); both volumes are called with (x0c, x1c), nyu.lua:37,39
         for (int i = 0; i < p->nyu_cost_agg_1; ++i) {
             float *dst = take();
-            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, cur, dst, h, w, D, direction));
+            float *tmp = take();
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction));
+            pool.push_back(tmp);
             advance(dst);
         }
         if (p->nyu_cost_agg_1 > 0 && stages[side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
@@ -171,7 +182,9 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         // nyu_cost_agg_2 (post.lua:171-186)
         for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
             float *dst = take();
-            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, cur, dst, h, w, D, direction));
+            float *tmp = take();
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction));
+            pool.push_back(tmp);
             advance(dst);
         }
         if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
@@ -234,6 +247,7 @@ int stereo_post_default_params(stereo_post_params *p)
     p->sgm = 1;
     p->nyu_cost_agg_2 = 1;
     p->post = 1;
+    p->cbca_exact = 0;
     return STEREO_OK;
 }
 
@@ -271,7 +285,7 @@ int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
-    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
     STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
     STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
@@ -282,7 +296,8 @@ int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img
         STEREO_TRY(to_dev(ctx, a, host, sizeof(float) * nvox));
         for (int i = 0; i < iters; ++i) {
             // both calls pass (x0c, x1c), nyu.lua:37,39
-            STEREO_TRY(launch_cbca(ctx, m.arms_l, m.arms_r, a, b, h, w, D, side == 0 ? -1 : 1));
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, a, ctx->post_vol[2].as<float>(), b, h, w, D,
+                                side == 0 ? -1 : 1));
             std::swap(a, b);
         }
         STEREO_TRY(to_host(ctx, host, a, sizeof(float) * nvox));

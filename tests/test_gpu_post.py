@@ -48,15 +48,37 @@ def test_volume_std(ctx, scene):
     np.testing.assert_array_max_ulp(np.float32(out), np.float32(ref), maxulp=1)
 
 
+def exact_params():
+    p = _lib.default_post_params()
+    p.cbca_exact = 1          # the original's strictly sequential summation order
+    return p
+
+
 @pytest.mark.parametrize("iters", [1, 2])
 def test_cross_agg_bit_exact(ctx, scene, iters):
     l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
     lu = np.ascontiguousarray(np.transpose(scene["lv"], (2, 0, 1)))
     ru = np.ascontiguousarray(np.transpose(scene["rv"], (2, 0, 1)))
     lref, rref = po.nyu_cross_agg(l_img, r_img, lu, ru, iters)
-    lv, rv = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], iters)
+    lv, rv = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], iters, exact_params())
     assert np.array_equal(np.transpose(lv, (2, 0, 1)), lref)
     assert np.array_equal(np.transpose(rv, (2, 0, 1)), rref)
+
+
+CBCA_SEPARABLE_TOL = 2e-6     # max|a-b| / max|b|: same sum, row sums associated first
+
+
+@pytest.mark.parametrize("iters", [1, 2])
+def test_cross_agg_separable_within_tolerance(ctx, scene, iters):
+    l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
+    lu = np.ascontiguousarray(np.transpose(scene["lv"], (2, 0, 1)))
+    ru = np.ascontiguousarray(np.transpose(scene["rv"], (2, 0, 1)))
+    lref, rref = po.nyu_cross_agg(l_img, r_img, lu, ru, iters)
+    lv, rv = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], iters)      # default: separable
+    for out, ref in ((lv, lref), (rv, rref)):
+        out = np.transpose(out, (2, 0, 1))
+        assert np.abs(out - ref).max() / np.abs(ref).max() < CBCA_SEPARABLE_TOL
+        assert (np.argmax(out, axis=0) == np.argmax(ref, axis=0)).mean() >= 0.999
 
 
 @pytest.mark.parametrize("direction", [-1, 1])
@@ -101,13 +123,20 @@ def test_nyu_post_bit_exact_on_reference_maps(ctx, golden_dir):
     assert np.array_equal((outl * 127).astype(np.uint8), ref_png)
 
 
-def test_full_chain_vs_oracle(ctx, scene):
+@pytest.mark.parametrize("exact", [1, 0])
+def test_full_chain_vs_oracle(ctx, scene, exact):
     D = scene["D"]
     ref = po.post_chain(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
-    out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
-    # before the global std everything is bit exact
-    assert np.array_equal(out["nyu_cost_img"], ref["nyu_cost_img"])
-    assert np.array_equal(out["right_nyu_cost_img"], ref["right_nyu_cost_img"])
+    params = _lib.default_post_params()
+    params.cbca_exact = exact
+    out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"], params)
+    if exact:
+        # before the global std everything is bit exact
+        assert np.array_equal(out["nyu_cost_img"], ref["nyu_cost_img"])
+        assert np.array_equal(out["right_nyu_cost_img"], ref["right_nyu_cost_img"])
+    else:
+        assert (out["nyu_cost_img"] == ref["nyu_cost_img"]).mean() >= 0.999
+        assert (out["right_nyu_cost_img"] == ref["right_nyu_cost_img"]).mean() >= 0.999
     for name in ("nyu_sgm_img", "right_nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2", "outlier"):
         assert (out[name] == ref[name]).mean() >= 0.999, name
     diff = np.abs(out["nyu_post_float"] - ref["nyu_post_float"])
@@ -139,6 +168,8 @@ def test_lua_surface_mirror(ctx, scene):
     lu = np.ascontiguousarray(np.transpose(scene["lv"], (2, 0, 1)))[None]
     ru = np.ascontiguousarray(np.transpose(scene["rv"], (2, 0, 1)))[None]
     h, w = l_img.shape
+    post_mod.nyu.params.cbca_exact = 1
     lo, ro = post_mod.nyu.cross_agg(l_img.reshape(1, 1, h, w), r_img.reshape(1, 1, h, w), lu, ru, 1)
+    post_mod.nyu.params.cbca_exact = 0
     lref, rref = po.nyu_cross_agg(l_img, r_img, lu[0], ru[0], 1)
     assert lo.shape == lu.shape and np.array_equal(lo[0], lref) and np.array_equal(ro[0], rref)
