@@ -158,7 +158,7 @@ int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, c
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
-int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,
+int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction);
 int launch_outlier(stereo_ctx *ctx, const float *d0, const float *d1, int h, int w, int disp_max, float *outlier);
 int launch_interpolate(stereo_ctx *ctx, const float *d0, const float *outlier, int h, int w, float *tmp, float *out);

@@ -203,66 +203,57 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
 // is the same sum with <= 9 + 9 instead of <= 81 loads per voxel.  Mathematically identical to
 // cbca_kernel; the fp32 additions associate per row first, so results differ from the
 // original's strictly sequential order in the last bits (tests bound it at 2e-6 relative).
-__global__ __launch_bounds__(256) void cbca_h_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+// block = one pixel (blockIdx.x = x, blockIdx.y = y), thread = disparity: no index decoding
+__global__ __launch_bounds__(512) void cbca_h_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
                                                      const float *__restrict__ vol, float *__restrict__ hsum,
                                                      uint8_t *__restrict__ hcnt, int h, int w, int D, int direction)
 {
-    const int lane = threadIdx.x & 31;
-    const int chunks = (D + 31) >> 5;
-    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    size_t hw = (size_t)h * w;
-    if (warp >= hw * chunks) return;
-    int chunk = (int)(warp % chunks);
-    size_t pix = warp / chunks;
-    int x = (int)(pix % w);
-    int d = chunk * 32 + lane;
+    const int d = threadIdx.x;
     if (d >= D) return;
-    size_t id = pix * D + d;
-    int xm = x + d * direction;
+    const int x = blockIdx.x, y = blockIdx.y;
+    const int hw = h * w;
+    const int rowpix = y * w, pix = rowpix + x;
+    const int id = pix * D + d;
+    const int shift = d * direction;
+    const int xm = x + shift;
     if (xm < 0 || xm >= w) {           // copied through by the vertical pass
         hsum[id] = vol[id];
         hcnt[id] = 0;
         return;
     }
-    const int shift = d * direction;
-    size_t rowpix = pix - x;
-    int xx_s = max((int)x0c[pix], (int)x1c[rowpix + xm] - shift);
-    int xx_t = min((int)x0c[hw + pix], (int)x1c[hw + rowpix + xm] - shift);
-    const float *vrow = vol + rowpix * D + d;
+    const int xx_s = max((int)x0c[pix], (int)x1c[rowpix + xm] - shift);
+    const int xx_t = min((int)x0c[hw + pix], (int)x1c[hw + rowpix + xm] - shift);
+    const float *vp = vol + (rowpix + xx_s + 1) * D + d;
     float sum = 0.f;
-    for (int xx = xx_s + 1; xx < xx_t; ++xx) sum = __fadd_rn(sum, vrow[(size_t)xx * D]);
+    for (int n = xx_t - xx_s - 1; n > 0; --n, vp += D) sum = __fadd_rn(sum, *vp);
     hsum[id] = sum;
     hcnt[id] = (uint8_t)(xx_t - xx_s - 1);
 }
 
-__global__ __launch_bounds__(256) void cbca_v_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+__global__ __launch_bounds__(512) void cbca_v_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
                                                      const float *__restrict__ hsum, const uint8_t *__restrict__ hcnt,
                                                      float *__restrict__ out, int h, int w, int D, int direction)
 {
-    const int lane = threadIdx.x & 31;
-    const int chunks = (D + 31) >> 5;
-    size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    size_t hw = (size_t)h * w;
-    if (warp >= hw * chunks) return;
-    int chunk = (int)(warp % chunks);
-    size_t pix = warp / chunks;
-    int x = (int)(pix % w), y = (int)(pix / w);
-    int d = chunk * 32 + lane;
+    const int d = threadIdx.x;
     if (d >= D) return;
-    size_t id = pix * D + d;
-    int xm = x + d * direction;
+    const int x = blockIdx.x, y = blockIdx.y;
+    const int hw = h * w;
+    const int pix = y * w + x;
+    const int id = pix * D + d;
+    const int xm = x + d * direction;
     if (xm < 0 || xm >= w) {
         out[id] = hsum[id];
         return;
     }
-    int yy_s = max((int)x0c[2 * hw + pix], (int)x1c[2 * hw + (size_t)y * w + xm]);
-    int yy_t = min((int)x0c[3 * hw + pix], (int)x1c[3 * hw + (size_t)y * w + xm]);
-    const size_t col = (size_t)x * D + d, pitch = (size_t)w * D;
+    const int yy_s = max((int)x0c[2 * hw + pix], (int)x1c[2 * hw + y * w + xm]);
+    const int yy_t = min((int)x0c[3 * hw + pix], (int)x1c[3 * hw + y * w + xm]);
+    const int pitch = w * D;
+    int off = ((yy_s + 1) * w + x) * D + d;
     float sum = 0.f;
     int cnt = 0;
-    for (int yy = yy_s + 1; yy < yy_t; ++yy) {
-        sum = __fadd_rn(sum, hsum[yy * pitch + col]);
-        cnt += hcnt[yy * pitch + col];
+    for (int n = yy_t - yy_s - 1; n > 0; --n, off += pitch) {
+        sum = __fadd_rn(sum, hsum[off]);
+        cnt += hcnt[off];
     }
     out[id] = __fdiv_rn(sum, (float)cnt);
 }
@@ -270,11 +261,12 @@ __global__ __launch_bounds__(256) void cbca_v_kernel(const short *__restrict__ x
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction)
 {
-    size_t warps = (size_t)h * w * ((D + 31) / 32);
-    size_t blocks = (warps + 7) / 8;
+    STEREO_REQUIRE((size_t)h * w * D < (size_t)1 << 31, "volume too large for 32-bit indexing");
+    STEREO_REQUIRE(D <= 512, "separable CBCA runs one thread per disparity: D <= 512, got %d", D);
+    const int nt = (D + 31) / 32 * 32;
     ProfScope prof(ctx, STEREO_K_CBCA);
-    cbca_h_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
-    cbca_v_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
+    cbca_h_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
+    cbca_v_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
     ctx->launches += 2;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
@@ -429,72 +421,78 @@ int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, 
 //     over D from a shuffle reduction - no shared memory and no block barrier on the
 //     serial chain - and the costs (and running sums) of the next PF steps are already in
 //     flight as 16-byte loads when a step is computed.
-//     in:  C[h][w][D] cost (optionally C = -(raw / std) applied on the fly, post.lua:146,152)
-//     out: accumulates the path cost; with `first` the kernel writes instead of adding and
-//          with `last` it writes (acc + Lr) / 4, fusing nyu.lua:61,64.
+//
+//     Three launches per volume: the two horizontal paths run concurrently in one grid and
+//     write their path costs to two buffers (a = left->right, b = right->left); the downward
+//     pass writes (a + b) + Lr into a; the upward pass writes ((a + Lr) / 4) - the order of
+//     additions of the original's `out +=`, and the division of nyu.lua:61,64.
+//     The input is the cost volume C = -(raw / std) (post.lua:146,152), scaled beforehand.
 //     Arithmetic per voxel is that of the original, operation for operation.
 // ------------------------------------------------------------------------------------------
-template <int SD, int KPL, int PF, bool VEC>
-__global__ __launch_bounds__(32) void sgm_warp_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
-                                                      const float *__restrict__ vol,
-                                                      const float *__restrict__ stdp, float *__restrict__ out,
-                                                      int h, int w, int D, SgmParams p, int direction, int first,
-                                                      int last)
+template <int SD, int KPL, int PF, bool VEC, int NACC>
+__device__ __forceinline__ void sgm_scan(const float *__restrict__ x0, const float *__restrict__ x1,
+                                         const float *__restrict__ cvol, const float *acc_a, const float *acc_b,
+                                         float *outp, int h, int w, int D, const SgmParams &p, int direction,
+                                         int line, int last)
 {
     constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
     constexpr int dy = SD == 2 ? 1 : (SD == 3 ? -1 : 0);
-    const int lane = threadIdx.x;
-    const int line = blockIdx.x;
+    const int lane = threadIdx.x & 31;
     const int steps = dy == 0 ? w : h;
     int x = dy == 0 ? (SD == 0 ? 0 : w - 1) : line;
     int y = dy == 0 ? line : (SD == 2 ? 0 : h - 1);
     const int d0 = lane * KPL;
-    const float sd = stdp ? stdp[0] : 1.f;
-    const float kBig = 3.402823466e38f;
+    const float kBig = 3.0e38f;          // stands for "no such disparity": never the minimum, kBig + P == kBig
+    const float tau = p.tau_so;
 
-    // the three penalty cases of the original, with and without the alpha1 division
+    // the three penalty cases of the original; "P1 / alpha1" applies to the d-1 term on the
+    // downward path and to the d+1 term on the upward one
     const float P1a = p.pi1, P2a = p.pi2;
     const float P1b = __fdiv_rn(p.pi1, __fmul_rn(p.q1, p.q2)), P2b = __fdiv_rn(p.pi2, __fmul_rn(p.q1, p.q2));
     const float P1c = __fdiv_rn(p.pi1, p.q1), P2c = __fdiv_rn(p.pi2, p.q1);
-    // "P1 / alpha1" applies to the d-1 term on the downward path and to the d+1 term on the upward one
     const float P1a_m = SD == 2 ? __fdiv_rn(P1a, p.alpha1) : P1a, P1a_p = SD == 3 ? __fdiv_rn(P1a, p.alpha1) : P1a;
     const float P1b_m = SD == 2 ? __fdiv_rn(P1b, p.alpha1) : P1b, P1b_p = SD == 3 ? __fdiv_rn(P1b, p.alpha1) : P1b;
     const float P1c_m = SD == 2 ? __fdiv_rn(P1c, p.alpha1) : P1c, P1c_p = SD == 3 ? __fdiv_rn(P1c, p.alpha1) : P1c;
 
     const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;     // floats between consecutive steps
-    const float *cptr = vol + ((size_t)y * w + x) * D + d0;
-    float *optr = out + ((size_t)y * w + x) * D + d0;
+    const size_t base = ((size_t)y * w + x) * D + d0;
+    const float *cptr = cvol + base;
+    const float *aptr = NACC >= 1 ? acc_a + base : nullptr;
+    const float *bptr = NACC >= 2 ? acc_b + base : nullptr;
+    float *optr = outp + base;
 
-    auto load_row = [&](const float *src, float (&dst)[KPL], bool scale) {
+    bool valid[KPL];
+#pragma unroll
+    for (int k = 0; k < KPL; ++k) valid[k] = d0 + k < D;
+
+    auto load_row = [&](const float *src, float (&dst)[KPL]) {
         if (VEC) {
 #pragma unroll
             for (int j = 0; j < KPL / 4; ++j) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (d0 + 4 * j < D) v = __ldg(reinterpret_cast<const float4 *>(src) + j);
+                if (valid[4 * j]) v = __ldg(reinterpret_cast<const float4 *>(src) + j);
                 dst[4 * j] = v.x; dst[4 * j + 1] = v.y; dst[4 * j + 2] = v.z; dst[4 * j + 3] = v.w;
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < KPL; ++k) dst[k] = d0 + k < D ? __ldg(src + k) : 0.f;
-        }
-        if (scale) {
-#pragma unroll
-            for (int k = 0; k < KPL; ++k) dst[k] = __fmul_rn(__fdiv_rn(dst[k], sd), -1.f);   // (x / std) * -1
+            for (int k = 0; k < KPL; ++k) dst[k] = valid[k] ? __ldg(src + k) : 0.f;
         }
     };
 
-    float cbuf[PF][KPL], obuf[PF][KPL];
+    float cbuf[PF][KPL], abuf[NACC >= 1 ? PF : 1][KPL], bbuf[NACC >= 2 ? PF : 1][KPL];
 #pragma unroll
     for (int i = 0; i < PF; ++i) {
         if (i < steps) {
-            load_row(cptr + i * vstride, cbuf[i], stdp != nullptr);
-            if (!first) load_row(optr + i * vstride, obuf[i], false);
+            load_row(cptr + i * vstride, cbuf[i]);
+            if (NACC >= 1) load_row(aptr + i * vstride, abuf[i]);
+            if (NACC >= 2) load_row(bptr + i * vstride, bbuf[i]);
         }
     }
 
     float prev[KPL], i1p[KPL];
 #pragma unroll
-    for (int k = 0; k < KPL; ++k) { prev[k] = 0.f; i1p[k] = 0.f; }
+    for (int k = 0; k < KPL; ++k) { prev[k] = kBig; i1p[k] = 0.f; }
+    const bool has_below = lane > 0, has_above = d0 + KPL < D;
 
     for (int g = 0; g < steps; g += PF) {
 #pragma unroll
@@ -503,71 +501,79 @@ __global__ __launch_bounds__(32) void sgm_warp_kernel(const float *__restrict__ 
             if (step >= steps) break;
             // guide values at the matched pixels of this step (L1-resident rows)
             float i1c[KPL];
-            const float *g1 = x1 + (size_t)y * w + x;
+            const float *g1 = x1 + (size_t)y * w;
+            const int xx0 = x + d0 * direction;
 #pragma unroll
             for (int k = 0; k < KPL; ++k) {
-                const int xx = x + (d0 + k) * direction;
-                i1c[k] = (xx >= 0 && xx < w) ? __ldg(g1 + (d0 + k) * direction) : 0.f;
+                const int xx = xx0 + k * direction;
+                i1c[k] = (unsigned)xx < (unsigned)w ? __ldg(g1 + xx) : 0.f;
             }
             float val[KPL];
             if (step == 0) {
 #pragma unroll
-                for (int k = 0; k < KPL; ++k) val[k] = cbuf[i][k];
+                for (int k = 0; k < KPL; ++k) val[k] = valid[k] ? cbuf[i][k] : kBig;
             } else {
-                float pmin = kBig;
+                float pmin = prev[0];
 #pragma unroll
-                for (int k = 0; k < KPL; ++k) pmin = fminf(pmin, d0 + k < D ? prev[k] : kBig);
+                for (int k = 1; k < KPL; ++k) pmin = fminf(pmin, prev[k]);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) pmin = fminf(pmin, __shfl_xor_sync(0xffffffffu, pmin, o));
-                const float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
-                const float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
+                float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
+                float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
+                below = has_below ? below : kBig;
+                above = has_above ? above : kBig;
                 const float D1 = fabsf(__ldg(x0 + (size_t)y * w + x) - __ldg(x0 + (size_t)(y - dy) * w + (x - dx)));
-                const bool d1_lt = D1 < p.tau_so, d1_gt = D1 > p.tau_so;
+                // D1 is the same for the whole scanline step: pick the candidate penalty set once
+                const bool d1_lt = D1 < tau, d1_gt = D1 > tau;
+                const float P2x = d1_lt ? P2a : P2b, P1mx = d1_lt ? P1a_m : P1b_m, P1px = d1_lt ? P1a_p : P1b_p;
+                const float pmin_p2x = __fadd_rn(pmin, P2x), pmin_p2c = __fadd_rn(pmin, P2c);
 #pragma unroll
                 for (int k = 0; k < KPL; ++k) {
-                    const int d = d0 + k;
-                    const int xx = x + d * direction;
+                    const int xx = xx0 + k * direction;
                     // the matched pixel of the previous step is (xx - dx, y - dy); its x1 value is i1p[k]
-                    float D2;
-                    if (xx < 0 || xx >= w || xx - dx < 0 || xx - dx >= w) D2 = 10.f;
-                    else D2 = fabsf(i1c[k] - i1p[k]);
-                    float P1m, P1p, P2;
-                    if (d1_lt && D2 < p.tau_so) { P1m = P1a_m; P1p = P1a_p; P2 = P2a; }
-                    else if (d1_gt && D2 > p.tau_so) { P1m = P1b_m; P1p = P1b_p; P2 = P2b; }
-                    else { P1m = P1c_m; P1p = P1c_p; P2 = P2c; }
-                    float c = fminf(prev[k], __fadd_rn(pmin, P2));
+                    const bool inside = (unsigned)xx < (unsigned)w && (dx == 0 || (unsigned)(xx - dx) < (unsigned)w);
+                    const float D2 = inside ? fabsf(i1c[k] - i1p[k]) : 10.f;
+                    const bool both = d1_lt ? (D2 < tau) : (d1_gt && D2 > tau);
+                    const float P1m = both ? P1mx : P1c_m, P1p = both ? P1px : P1c_p;
+                    float c = fminf(prev[k], both ? pmin_p2x : pmin_p2c);
                     const float pm = k > 0 ? prev[k > 0 ? k - 1 : 0] : below;
                     const float pp = k < KPL - 1 ? prev[k < KPL - 1 ? k + 1 : 0] : above;
-                    if (d - 1 >= 0) c = fminf(c, __fadd_rn(pm, P1m));
-                    if (d + 1 < D) c = fminf(c, __fadd_rn(pp, P1p));
-                    val[k] = __fadd_rn(__fadd_rn(cbuf[i][k], c), -pmin);
+                    c = fminf(c, __fadd_rn(pm, P1m));
+                    c = fminf(c, __fadd_rn(pp, P1p));
+                    const float v = __fadd_rn(__fadd_rn(cbuf[i][k], c), -pmin);
+                    val[k] = valid[k] ? v : kBig;
                 }
             }
             // accumulate into the output volume
             float res[KPL];
 #pragma unroll
             for (int k = 0; k < KPL; ++k) {
-                float acc = first ? val[k] : __fadd_rn(obuf[i][k], val[k]);
+                float acc = val[k];
+                if (NACC == 1) acc = __fadd_rn(abuf[i][k], val[k]);
+                if (NACC == 2) acc = __fadd_rn(__fadd_rn(abuf[i][k], bbuf[i][k]), val[k]);
                 res[k] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
             }
             if (VEC) {
 #pragma unroll
                 for (int j = 0; j < KPL / 4; ++j)
-                    if (d0 + 4 * j < D)
+                    if (valid[4 * j])
                         reinterpret_cast<float4 *>(optr)[j] = make_float4(res[4 * j], res[4 * j + 1], res[4 * j + 2], res[4 * j + 3]);
             } else {
 #pragma unroll
                 for (int k = 0; k < KPL; ++k)
-                    if (d0 + k < D) optr[k] = res[k];
+                    if (valid[k]) optr[k] = res[k];
             }
 #pragma unroll
             for (int k = 0; k < KPL; ++k) { prev[k] = val[k]; i1p[k] = i1c[k]; }
             // refill this ring slot with the step PF ahead
             if (step + PF < steps) {
-                load_row(cptr + (ptrdiff_t)PF * vstride, cbuf[i], stdp != nullptr);
-                if (!first) load_row(optr + (ptrdiff_t)PF * vstride, obuf[i], false);
+                load_row(cptr + (ptrdiff_t)PF * vstride, cbuf[i]);
+                if (NACC >= 1) load_row(aptr + (ptrdiff_t)PF * vstride, abuf[i]);
+                if (NACC >= 2) load_row(bptr + (ptrdiff_t)PF * vstride, bbuf[i]);
             }
             cptr += vstride;
+            if (NACC >= 1) aptr += vstride;
+            if (NACC >= 2) bptr += vstride;
             optr += vstride;
             x += dx;
             y += dy;
@@ -575,20 +581,39 @@ __global__ __launch_bounds__(32) void sgm_warp_kernel(const float *__restrict__ 
     }
 }
 
+// both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
 template <int KPL, int PF, bool VEC>
-static int launch_sgm_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp,
-                        float *out, int h, int w, int D, const SgmParams &p, int direction)
+__global__ __launch_bounds__(32) void sgm_h_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
+                                                   const float *__restrict__ cvol, float *out_a, float *out_b, int h,
+                                                   int w, int D, SgmParams p, int direction)
 {
-    sgm_warp_kernel<0, KPL, PF, VEC><<<h, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 1, 0);
-    sgm_warp_kernel<1, KPL, PF, VEC><<<h, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
-    sgm_warp_kernel<2, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 0);
-    sgm_warp_kernel<3, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, vol, stdp, out, h, w, D, p, direction, 0, 1);
-    ctx->launches += 4;
+    if (blockIdx.y == 0) sgm_scan<0, KPL, PF, VEC, 0>(x0, x1, cvol, nullptr, nullptr, out_a, h, w, D, p, direction, blockIdx.x, 0);
+    else sgm_scan<1, KPL, PF, VEC, 0>(x0, x1, cvol, nullptr, nullptr, out_b, h, w, D, p, direction, blockIdx.x, 0);
+}
+
+template <int SD, int KPL, int PF, bool VEC>
+__global__ __launch_bounds__(32) void sgm_v_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
+                                                   const float *__restrict__ cvol, float *out_a, const float *out_b,
+                                                   int h, int w, int D, SgmParams p, int direction)
+{
+    if (SD == 2) sgm_scan<2, KPL, PF, VEC, 2>(x0, x1, cvol, out_a, out_b, out_a, h, w, D, p, direction, blockIdx.x, 0);
+    else sgm_scan<3, KPL, PF, VEC, 1>(x0, x1, cvol, out_a, nullptr, out_a, h, w, D, p, direction, blockIdx.x, 1);
+}
+
+template <int KPL, int PF, bool VEC>
+static int launch_sgm_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a,
+                        float *out_b, int h, int w, int D, const SgmParams &p, int direction)
+{
+    sgm_h_kernel<KPL, PF, VEC><<<dim3(h, 2), 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
+    sgm_v_kernel<2, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
+    sgm_v_kernel<3, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
+    ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
 }
 
-int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *vol, const float *stdp, float *out,
+// cvol: pre-scaled costs; out: result; scratch: one more volume (the right->left path costs)
+int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction)
 {
     if (D > 512) {
@@ -596,14 +621,15 @@ int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *v
         return STEREO_E_LIMIT;
     }
     // 16-byte loads need every [x][d] row to start 16-byte aligned
-    const bool vec = D % 4 == 0 && ((uintptr_t)vol % 16 == 0) && ((uintptr_t)out % 16 == 0);
+    const bool vec = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+                     ((uintptr_t)scratch % 16 == 0);
     ProfScope prof(ctx, STEREO_K_SGM);
-    if (D <= 128) return vec ? launch_sgm_t<4, 4, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
-                             : launch_sgm_t<4, 4, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
-    if (D <= 256) return vec ? launch_sgm_t<8, 4, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
-                             : launch_sgm_t<8, 4, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
-    return vec ? launch_sgm_t<16, 2, true>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction)
-               : launch_sgm_t<16, 2, false>(ctx, x0, x1, vol, stdp, out, h, w, D, p, direction);
+    if (D <= 128) return vec ? launch_sgm_t<4, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
+                             : launch_sgm_t<4, 4, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
+    if (D <= 256) return vec ? launch_sgm_t<8, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
+                             : launch_sgm_t<8, 4, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
+    return vec ? launch_sgm_t<16, 2, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
+               : launch_sgm_t<16, 2, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
 }
 
 // ------------------------------------------------------------------------------------------

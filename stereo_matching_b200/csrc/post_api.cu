@@ -74,7 +74,7 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
                     float *tmp, float *out, int h, int w, int D, int direction)
 {
-    if (p->cbca_exact) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
+    if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
     STEREO_TRY(ctx->post_cnt.reserve((size_t)h * w * D));
     return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt.as<uint8_t>(), out, h, w, D, direction);
 }
@@ -167,10 +167,16 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp));
         if (p->sgm == 1) {
             // post.lua:152-155 + nyu.lua:47-75
+            {   // post.lua:146,152: lu = (lu / lu:std()) * -1
+                float *dst = take();
+                STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 1, dst));
+                advance(dst);
+            }
             for (int it = 0; it < p->sgm_i; ++it) {
                 float *dst = take();
-                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, it == 0 ? stdp : nullptr, dst, h, w, D, sp,
-                                      direction));
+                float *tmp = take();
+                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction));
+                pool.push_back(tmp);
                 advance(dst);
             }
             if (stages[2 + side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[2 + side]));
@@ -315,14 +321,14 @@ int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, floa
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
-    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
     STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
     STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
     float *a = ctx->post_vol[0].as<float>(), *b = ctx->post_vol[1].as<float>();
     STEREO_TRY(to_dev(ctx, a, vol, sizeof(float) * nvox));
     const SgmParams sp = sgm_params(p);
     for (int it = 0; it < p->sgm_i; ++it) {
-        STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, a, nullptr, b, h, w, D, sp, direction));
+        STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, a, b, ctx->post_vol[2].as<float>(), h, w, D, sp, direction));
         std::swap(a, b);
     }
     STEREO_TRY(to_host(ctx, vol, a, sizeof(float) * nvox));
