@@ -155,7 +155,7 @@ int launch_cross(stereo_ctx *ctx, const float *img, int h, int w, int L1, float 
 int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
                 int D, int direction);
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
-                          uint8_t *hcnt, float *out, int h, int w, int D, int direction);
+                          uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,

@@ -258,15 +258,114 @@ __global__ __launch_bounds__(512) void cbca_v_kernel(const short *__restrict__ x
     out[id] = __fdiv_rn(sum, (float)cnt);
 }
 
+// Register-blocked versions for arm lengths up to L1 = 5 (windows of at most 9): a thread owns
+// one disparity of FOUR neighbouring pixels, loads the 12 values their windows cover once and
+// forms the four sums from registers (same ascending order of additions as above).
+constexpr int kCbR = 4;                  // window half width = L1 - 1
+constexpr int kCbB = 4;                  // pixels per thread
+constexpr int kCbN = kCbB + 2 * kCbR;    // values loaded
+
+__global__ __launch_bounds__(512) void cbca_h4_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+                                                      const float *__restrict__ vol, float *__restrict__ hsum,
+                                                      uint8_t *__restrict__ hcnt, int h, int w, int D, int direction)
+{
+    const int d = threadIdx.x;
+    if (d >= D) return;
+    const int xb = blockIdx.x * kCbB, y = blockIdx.y;
+    const int hw = h * w, rowpix = y * w;
+    const int shift = d * direction;
+    float v[kCbN];
+#pragma unroll
+    for (int j = 0; j < kCbN; ++j) {
+        const int col = xb - kCbR + j;
+        v[j] = (col >= 0 && col < w) ? vol[(rowpix + col) * D + d] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < kCbB; ++i) {
+        const int x = xb + i;
+        if (x >= w) break;
+        const int pix = rowpix + x, id = pix * D + d;
+        const int xm = x + shift;
+        if (xm < 0 || xm >= w) {
+            hsum[id] = v[kCbR + i];
+            hcnt[id] = 0;
+            continue;
+        }
+        const int xx_s = max((int)x0c[pix], (int)x1c[rowpix + xm] - shift);
+        const int xx_t = min((int)x0c[hw + pix], (int)x1c[hw + rowpix + xm] - shift);
+        float sum = 0.f;
+#pragma unroll
+        for (int j = i; j <= i + 2 * kCbR; ++j) {       // columns x-R .. x+R
+            const int col = xb - kCbR + j;
+            if (col > xx_s && col < xx_t) sum = __fadd_rn(sum, v[j]);
+        }
+        hsum[id] = sum;
+        hcnt[id] = (uint8_t)(xx_t - xx_s - 1);
+    }
+}
+
+__global__ __launch_bounds__(512) void cbca_v4_kernel(const short *__restrict__ x0c, const short *__restrict__ x1c,
+                                                      const float *__restrict__ hsum, const uint8_t *__restrict__ hcnt,
+                                                      float *__restrict__ out, int h, int w, int D, int direction)
+{
+    const int d = threadIdx.x;
+    if (d >= D) return;
+    const int x = blockIdx.x, yb = blockIdx.y * kCbB;
+    const int hw = h * w;
+    const int xm = x + d * direction;
+    if (xm < 0 || xm >= w) {
+#pragma unroll
+        for (int i = 0; i < kCbB; ++i) {
+            const int y = yb + i;
+            if (y < h) out[(y * w + x) * D + d] = hsum[(y * w + x) * D + d];
+        }
+        return;
+    }
+    float v[kCbN];
+    int c[kCbN];
+#pragma unroll
+    for (int j = 0; j < kCbN; ++j) {
+        const int row = yb - kCbR + j;
+        const bool in = row >= 0 && row < h;
+        const int off = (row * w + x) * D + d;
+        v[j] = in ? hsum[off] : 0.f;
+        c[j] = in ? (int)hcnt[off] : 0;
+    }
+#pragma unroll
+    for (int i = 0; i < kCbB; ++i) {
+        const int y = yb + i;
+        if (y >= h) break;
+        const int pix = y * w + x;
+        const int yy_s = max((int)x0c[2 * hw + pix], (int)x1c[2 * hw + y * w + xm]);
+        const int yy_t = min((int)x0c[3 * hw + pix], (int)x1c[3 * hw + y * w + xm]);
+        float sum = 0.f;
+        int cnt = 0;
+#pragma unroll
+        for (int j = i; j <= i + 2 * kCbR; ++j) {       // rows y-R .. y+R
+            const int row = yb - kCbR + j;
+            if (row > yy_s && row < yy_t) {
+                sum = __fadd_rn(sum, v[j]);
+                cnt += c[j];
+            }
+        }
+        out[pix * D + d] = __fdiv_rn(sum, (float)cnt);
+    }
+}
+
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
-                          uint8_t *hcnt, float *out, int h, int w, int D, int direction)
+                          uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1)
 {
     STEREO_REQUIRE((size_t)h * w * D < (size_t)1 << 31, "volume too large for 32-bit indexing");
     STEREO_REQUIRE(D <= 512, "separable CBCA runs one thread per disparity: D <= 512, got %d", D);
     const int nt = (D + 31) / 32 * 32;
     ProfScope prof(ctx, STEREO_K_CBCA);
-    cbca_h_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
-    cbca_v_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
+    if (L1 - 1 <= kCbR) {
+        cbca_h4_kernel<<<dim3((w + kCbB - 1) / kCbB, h), nt, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
+        cbca_v4_kernel<<<dim3(w, (h + kCbB - 1) / kCbB), nt, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
+    } else {
+        cbca_h_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, vol, hsum, hcnt, h, w, D, direction);
+        cbca_v_kernel<<<dim3(w, h), nt, 0, ctx->stream>>>(x0c, x1c, hsum, hcnt, out, h, w, D, direction);
+    }
     ctx->launches += 2;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;

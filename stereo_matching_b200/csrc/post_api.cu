@@ -76,7 +76,7 @@ static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x
 {
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
     STEREO_TRY(ctx->post_cnt.reserve((size_t)h * w * D));
-    return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt.as<uint8_t>(), out, h, w, D, direction);
+    return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt.as<uint8_t>(), out, h, w, D, direction, p->L1);
 }
 
 // nyu.lua:91-115 on device maps
