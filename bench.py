@@ -313,6 +313,50 @@ def run_b200(args):
              "other_rooflines": {k: v for k, v in rooflines.items() if k != dominant},
              "three_px_error_pair0": err0}
 
+    # ---- BASELINE.json configs[3]: the post.lua chain on one pair, device resident (secondary numbers) ------
+    if not args.no_post:
+        with torch.cuda.stream(stream):
+            d_lv = torch.empty((H, W, D), dtype=torch.float32, device=dev)
+            d_rv = torch.empty((H, W, D), dtype=torch.float32, device=dev)
+            ctx.pairs_dev(model.net, d_left.data_ptr(), d_right.data_ptr(), 1, H, W, D, prec,
+                          d_ld.data_ptr(), d_rd.data_ptr(), None, d_lv.data_ptr(), d_rv.data_ptr())
+            d_stages = torch.empty((8, H, W), dtype=torch.uint8, device=dev)
+            stage_ptrs = [d_stages[i].data_ptr() for i in range(8)]
+
+            def post_once():
+                ctx.post_dev(d_lv.data_ptr(), d_rv.data_ptr(), d_ld.data_ptr(), d_rd.data_ptr(), H, W, D, stage_ptrs)
+
+            post_once()
+            torch.cuda.synchronize()
+            reps = 3
+            ctx.profile_enable(True)
+            pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            pe0.record(stream)
+            for _ in range(reps):
+                post_once()
+            pe1.record(stream)
+            torch.cuda.synchronize()
+            post_ms = pe0.elapsed_time(pe1) / reps
+            pprof = ctx.profile_read()
+            ctx.profile_enable(False)
+        vol_bytes = 4.0 * H * W * D
+        hbm = pk["hbm_gbs"]
+
+        def gbs(cls, algorithmic_bytes_per_launch_group, groups):
+            ms_, cnt = pprof[cls]
+            return algorithmic_bytes_per_launch_group * groups * reps / (ms_ / 1e3) / 1e9 if ms_ > 0 else None
+
+        post_final = d_stages[6].cpu().numpy()
+        extra["post_chain"] = {
+            "workload": "configs[3] (4-path SGM as in the reference): CBCA -> SGM -> CBCA -> LR/fill/subpixel/median/bilateral, one pair",
+            "ms_per_pair": post_ms, "pairs_per_s": 1e3 / post_ms,
+            "kernel_ms_per_pair": {k: v[0] / reps for k, v in pprof.items() if v[1]},
+            "note": "left and right chains overlap on two streams, so the per-class times sum to more than ms_per_pair",
+            "cbca_gbs_algorithmic": gbs("cbca", 2 * vol_bytes, 4), "sgm_gbs_algorithmic": gbs("sgm", 2 * vol_bytes, 2),
+            "wta_gbs": gbs("wta", vol_bytes, 8), "hbm_peak_gbs": hbm,
+            "three_px_error_pair0_after_post": three_pixel_error(post_final.astype(np.int64), gt[0]),
+        }
+
     # ---- CPU baseline (oracle port) on a bounded sample --------------------------------------------
     cpu = None
     if not args.no_cpu_baseline:
@@ -354,6 +398,7 @@ def main():
     ap.add_argument("--e2e-pairs", type=int, default=64, help="pairs per host-pointer call in the e2e leg")
     ap.add_argument("--cpu-rows", type=int, default=96, help="image rows of the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-post", action="store_true", help="skip the secondary post-chain measurement")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -317,7 +317,8 @@ int stereo_destroy(stereo_ctx *ctx)
     DevBuf *bufs[] = {&ctx->weights[0], &ctx->weights[1], &ctx->wsplit[0], &ctx->wsplit[1], &ctx->stats,
                       &ctx->padded, &ctx->act[0], &ctx->act[1], &ctx->feat, &ctx->stage_in[0], &ctx->stage_in[1],
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
-                      &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2], &ctx->post_vol[3], &ctx->post_cnt,
+                      &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2], &ctx->post_vol[3], &ctx->post_vol[4], &ctx->post_vol[5], &ctx->post_vol[6], &ctx->post_vol[7],
+                      &ctx->post_cnt[0], &ctx->post_cnt[1],
                       &ctx->post_maps, &ctx->featp};
     for (DevBuf *b : bufs) b->release();
     if (ctx->prof.start) {
@@ -329,6 +330,9 @@ int stereo_destroy(stereo_ctx *ctx)
         delete[] ctx->prof.stop;
         delete[] ctx->prof.cls;
     }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return STEREO_OK;

@@ -92,8 +92,10 @@ struct stereo_ctx {
     stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
     int featp_geom[5] = {0, 0, 0, 0, 0};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
-    stereo::DevBuf post_vol[4];  // working volumes of the post chain
-    stereo::DevBuf post_cnt;     // row-segment lengths of the separable CBCA (uint8 per voxel)
+    stereo::DevBuf post_vol[8];  // working volumes of the post chain: 4 per side (the sides run on two streams)
+    stereo::DevBuf post_cnt[2];  // row-segment lengths of the separable CBCA (uint8 per voxel), per side
+    cudaStream_t aux_stream = nullptr;   // second stream of the post chain
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
 };
 
@@ -156,7 +158,7 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
                 int D, int direction);
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
-int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result);
+int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction);

@@ -427,10 +427,11 @@ int launch_volume_std_with(stereo_ctx *ctx, const float *vol, size_t n, double *
     return STEREO_OK;
 }
 
-int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result)
+// `slot` (0 or 1) selects one of two partial-sum areas so that two streams can reduce at once
+int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot)
 {
-    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * kStdBlocks));
-    return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>(), result);
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * kStdBlocks));
+    return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>() + (slot ? 2 * kStdBlocks : 0), result);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -72,12 +72,21 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 
 // one adcensus.cbca call in either summation order; `tmp` is a spare volume for the separable form
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
-                    float *tmp, float *out, int h, int w, int D, int direction)
+                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
 {
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
-    STEREO_TRY(ctx->post_cnt.reserve((size_t)h * w * D));
-    return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt.as<uint8_t>(), out, h, w, D, direction, p->L1);
+    STEREO_TRY(ctx->post_cnt[slot].reserve((size_t)h * w * D));
+    return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt[slot].as<uint8_t>(), out, h, w, D, direction,
+                                 p->L1);
 }
+
+// Runs the launches issued during its lifetime on another stream.
+struct StreamSwap {
+    stereo_ctx *ctx;
+    cudaStream_t saved;
+    StreamSwap(stereo_ctx *c, cudaStream_t s) : ctx(c), saved(c->stream) { c->stream = s; }
+    ~StreamSwap() { ctx->stream = saved; }
+};
 
 // nyu.lua:91-115 on device maps
 static int nyu_post_dev(stereo_ctx *ctx, PostMaps &m, const float *left_vol, int h, int w, int D,
@@ -127,20 +136,34 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
-    for (int i = 0; i < 4; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream
+    // section would serialise it
+    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * 1184));
+    if (!ctx->aux_stream) {
+        STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+        STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+        STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    }
     STEREO_TRY(launch_guide(ctx, left_disp, h, w, m.guide_l));
     STEREO_TRY(launch_guide(ctx, right_disp, h, w, m.guide_r));
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
     STEREO_TRY(launch_cross(ctx, m.guide_r, h, w, p->L1, p->tau1, m.arms_r));
     const SgmParams sp = sgm_params(p);
 
-    // Three working volumes.  Every stage reads `cur` and writes a free buffer; the buffer it
-    // read goes back to the free list unless it is the caller's (read-only) input.  The left
-    // result keeps one buffer (sub-pixel refinement needs it), the right side uses the other two.
-    std::vector<float *> pool = {ctx->post_vol[0].as<float>(), ctx->post_vol[1].as<float>(),
-                                 ctx->post_vol[2].as<float>(), ctx->post_vol[3].as<float>()};
+    // The left and the right volume are independent until smooth.nyu.post: the left chain is
+    // issued on the context's stream, the right chain on a second stream (the scanline kernels
+    // of SGM leave most of the machine idle on their own).  Four working volumes per side: every
+    // stage reads `cur` and writes a free buffer; the buffer it read goes back to the free list
+    // unless it is the caller's (read-only) input.
+    STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
     const float *left_final = nullptr;
     for (int side = 0; side < 2; ++side) {
+        StreamSwap swap(ctx, side == 0 ? ctx->stream : ctx->aux_stream);
+        std::vector<float *> pool;
+        for (int i = 0; i < 4; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
         const int direction = side == 0 ? -1 : 1;
         const float *input = side == 0 ? left_cost : right_cost;
         const float *cur = input;
@@ -157,14 +180,14 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         for (int i = 0; i < p->nyu_cost_agg_1; ++i) {
             float *dst = take();
             float *tmp = take();
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction));
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
             pool.push_back(tmp);
             advance(dst);
         }
         if (p->nyu_cost_agg_1 > 0 && stages[side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
         // post.lua:146-147: lu = lu / lu:std()  (fused into the SGM cost load when SGM runs)
         float *stdp = m.stdp + side * 2;
-        STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp));
+        STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
         if (p->sgm == 1) {
             // post.lua:152-155 + nyu.lua:47-75
             {   // post.lua:146,152: lu = (lu / lu:std()) * -1
@@ -189,7 +212,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
             float *dst = take();
             float *tmp = take();
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction));
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
             pool.push_back(tmp);
             advance(dst);
         }
@@ -197,9 +220,10 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[4 + side]));
         // post.lua:226-229: disp = argmin - 1 (0-based here)
         STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, side == 0 ? m.u8a : m.u8b));
-        if (side == 0) left_final = cur;       // stays out of the pool
-        else if (cur != input) pool.push_back(const_cast<float *>(cur));
+        if (side == 0) left_final = cur;
+        else STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->stream));      // still the second stream here
     }
+    STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     if (p->post == 1) {
         STEREO_TRY(launch_u8_to_float(ctx, m.u8a, (int)hw, m.d0));
         STEREO_TRY(launch_u8_to_float(ctx, m.u8b, (int)hw, m.d1));
