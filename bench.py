@@ -313,11 +313,50 @@ def run_b200(args):
              "other_rooflines": {k: v for k, v in rooflines.items() if k != dominant},
              "three_px_error_pair0": err0}
 
-    # ---- BASELINE.json configs[3]: the post.lua chain on one pair, device resident (secondary numbers) ------
+    # ---- BASELINE.json metric, second half: "cost-volume GB/s vs HBM peak" (configs[0] shape: one pair,
+    #      left + right volumes materialised in the reference's [H][W][D] layout, then standalone WTA) ----------
     if not args.no_post:
         with torch.cuda.stream(stream):
             d_lv = torch.empty((H, W, D), dtype=torch.float32, device=dev)
             d_rv = torch.empty((H, W, D), dtype=torch.float32, device=dev)
+            d_feat = torch.empty((2, H, W, 64), dtype=torch.float32, device=dev)
+            d_pad = torch.empty((2, H + 8, W + 8, 3), dtype=torch.float32, device=dev)
+            ctx.normalize_pad_dev(d_left.data_ptr(), 1, H, W, 9, d_pad[0].data_ptr())
+            ctx.normalize_pad_dev(d_right.data_ptr(), 1, H, W, 9, d_pad[1].data_ptr())
+            ctx.trunk_dev(model.net, d_pad.data_ptr(), 2, H + 8, W + 8, d_feat.data_ptr(), prec)
+
+            def vol_once():
+                ctx.cost_volume_dev(d_feat[0].data_ptr(), d_feat[1].data_ptr(), 1, H, W, 64, D,
+                                    d_lv.data_ptr(), d_rv.data_ptr(), prec)
+                ctx.wta_dev(d_lv.data_ptr(), 1, H, W, D, False, d_ld.data_ptr())
+                ctx.wta_dev(d_rv.data_ptr(), 1, H, W, D, False, d_rd.data_ptr())
+
+            vol_once()
+            torch.cuda.synchronize()
+            reps = 5
+            ctx.profile_enable(True)
+            for _ in range(reps):
+                vol_once()
+            vprof = ctx.profile_read()
+            ctx.profile_enable(False)
+        vol_bytes = 4.0 * H * W * D
+        feat_bytes = 4.0 * H * W * 64
+        corr_ms_v = vprof["corr"][0] / reps          # includes the fp32 -> planar bf16 feature conversion
+        wta_ms_v = vprof["wta"][0] / reps
+        extra["cost_volume"] = {
+            "workload": "configs[0] shape: one pair, left+right volumes materialised [H][W][D] fp32, then standalone WTA",
+            "materialise_ms": corr_ms_v,
+            "materialise_gbs": (2 * feat_bytes + 2 * vol_bytes) / (corr_ms_v / 1e3) / 1e9,
+            "materialise_frac_of_hbm": (2 * feat_bytes + 2 * vol_bytes) / (corr_ms_v / 1e3) / 1e9 / pk["hbm_gbs"],
+            "wta_ms": wta_ms_v, "wta_gbs": (2 * vol_bytes + 2 * H * W) / (wta_ms_v / 1e3) / 1e9,
+            "wta_frac_of_hbm": (2 * vol_bytes + 2 * H * W) / (wta_ms_v / 1e3) / 1e9 / pk["hbm_gbs"],
+            "algorithmic_bytes": {"materialise": 2 * feat_bytes + 2 * vol_bytes, "wta": 2 * vol_bytes + 2 * H * W},
+        }
+        del d_feat, d_pad
+
+    # ---- BASELINE.json configs[3]: the post.lua chain on one pair, device resident (secondary numbers) ------
+    if not args.no_post:
+        with torch.cuda.stream(stream):
             ctx.pairs_dev(model.net, d_left.data_ptr(), d_right.data_ptr(), 1, H, W, D, prec,
                           d_ld.data_ptr(), d_rd.data_ptr(), None, d_lv.data_ptr(), d_rv.data_ptr())
             d_stages = torch.empty((8, H, W), dtype=torch.uint8, device=dev)

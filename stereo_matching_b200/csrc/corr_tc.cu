@@ -33,8 +33,11 @@ constexpr int kWinN = 384;
 constexpr int kARun = kTileM * 16, kAPlane = 8 * kARun;      // 16 KB per plane
 constexpr int kBRun = kWinN * 16, kBPlane = 8 * kBRun;       // 48 KB per plane
 constexpr int kSmemA = 0, kSmemB = 2 * kAPlane;
-constexpr int kSmemStage = kSmemB + 2 * kBPlane;             // 4 warps x [32][33] floats
-constexpr int kSmemBars = kSmemStage + 4 * 32 * 33 * 4;
+constexpr int kSmemStage = kSmemB + 2 * kBPlane;             // one [32][33] float block per epilogue warp
+constexpr int kEpiWarps = 8;                                 // two per TMEM lane quarter
+constexpr int kChunksPerWarp = (kWinN / 32) / (kEpiWarps / 4);
+constexpr int kSmemWta = kSmemStage + kEpiWarps * 32 * 33 * 4;   // [2 tiles][2 halves][128] (value, d)
+constexpr int kSmemBars = kSmemWta + 2 * 2 * 128 * 8;
 constexpr int kSmemTotal = kSmemBars + 64;
 constexpr uint32_t kTmemCols = 512;
 
@@ -46,18 +49,20 @@ struct Params {
     int tiles_x, ntiles;
 };
 
+// One epilogue warp drains `kChunksPerWarp` 32-column chunks of its 32 TMEM lanes.
 template <int SIDE, bool VOL, bool WTA>
 __device__ __forceinline__ void drain_tile(const Params &p, uint32_t tmem_row, float *stage, int lane, int q,
-                                           int img, int y, int x0)
+                                           int c_begin, int img, int y, int x0, float &best, int &best_d)
 {
     const int xi = q * 32 + lane;
     const int D = p.D;
-    float best = -INFINITY;
-    int best_d = 0;
+    best = -INFINITY;
+    best_d = 0x7fffffff;
     float *vol = SIDE == 0 ? p.left_vol : p.right_vol;
     const size_t row_pix = ((size_t)img * p.h + y) * p.w;
+    const int rows_ok = min(32, p.w - (x0 + q * 32));            // rows of this warp that are inside the image
 #pragma unroll 1
-    for (int c = 0; c < kWinN / 32; ++c) {
+    for (int c = c_begin; c < c_begin + kChunksPerWarp; ++c) {
         uint32_t v[32];
         tc::tmem_ld_32x32(tmem_row + c * 32, v);
         if (WTA) {
@@ -77,25 +82,29 @@ __device__ __forceinline__ void drain_tile(const Params &p, uint32_t tmem_row, f
 #pragma unroll
             for (int i = 0; i < 32; ++i) stage[lane * 33 + i] = __uint_as_float(v[i]);
             __syncwarp();
-            const int u = c * 32 + lane;
-#pragma unroll 4
-            for (int r = 0; r < 32; ++r) {
-                const int xr = q * 32 + r;
-                const int x = x0 + xr;
-                const int d = SIDE == 0 ? xr + D - 1 - u : u - xr;
-                if (x < p.w && (unsigned)d < (unsigned)D) vol[(row_pix + x) * D + d] = stage[r * 33 + lane];
+            // row r of the block goes to out[x0 + q*32 + r][d00 +- r]: one 128-byte run per warp store
+            const int d00 = SIDE == 0 ? q * 32 + D - 1 - (c * 32 + lane) : (c * 32 + lane) - q * 32;
+            const int dstep = SIDE == 0 ? 1 : -1;
+            float *dst = vol + (row_pix + x0 + q * 32) * D + d00;
+            const int stride = D + dstep;
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 8) {
+                float t[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t[j] = stage[(r0 + j) * 33 + lane];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int r = r0 + j;
+                    if (r < rows_ok && (unsigned)(d00 + dstep * r) < (unsigned)D) dst[(size_t)r * stride] = t[j];
+                }
             }
             __syncwarp();
         }
     }
-    if (WTA) {
-        const int x = x0 + xi;
-        if (x < p.w) (SIDE == 0 ? p.left_disp : p.right_disp)[row_pix + x] = (uint8_t)(best_d & 255);
-    }
 }
 
 template <bool VOL, bool WTA>
-__global__ __launch_bounds__(256, 1) void corr_tc_kernel(Params p)
+__global__ __launch_bounds__(128 + 32 * kEpiWarps, 1) void corr_tc_kernel(Params p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -109,7 +118,7 @@ __global__ __launch_bounds__(256, 1) void corr_tc_kernel(Params p)
         tc::mbar_init(bar_full, 1);
         tc::mbar_init(bar_empty, 1);
         tc::mbar_init(bar_acc_full, 1);
-        tc::mbar_init(bar_acc_empty, 4);
+        tc::mbar_init(bar_acc_empty, kEpiWarps);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -192,9 +201,11 @@ __global__ __launch_bounds__(256, 1) void corr_tc_kernel(Params p)
             }
         }
     } else if (warp >= 4) {
-        // ---- epilogue ----
+        // ---- epilogue: 8 warps, warp (q, half) drains columns [half*192, half*192+192) of lanes 32q.. ----
         const int q = warp & 3;
-        float *stage = reinterpret_cast<float *>(smem + kSmemStage) + q * 32 * 33;
+        const int half = (warp - 4) >> 2;
+        float *stage = reinterpret_cast<float *>(smem + kSmemStage) + (warp - 4) * 32 * 33;
+        float2 *wta_s = reinterpret_cast<float2 *>(smem + kSmemWta);
         const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16);
         int k = 0;
         for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x, ++k) {
@@ -202,11 +213,27 @@ __global__ __launch_bounds__(256, 1) void corr_tc_kernel(Params p)
             decode(t, img, side, y, x0);
             tc::mbar_wait(bar_acc_full, k & 1);
             tc::tc_fence_after();
-            if (side == 0) drain_tile<0, VOL, WTA>(p, tmem_row, stage, lane, q, img, y, x0);
-            else drain_tile<1, VOL, WTA>(p, tmem_row, stage, lane, q, img, y, x0);
+            float best;
+            int best_d;
+            if (side == 0) drain_tile<0, VOL, WTA>(p, tmem_row, stage, lane, q, half * kChunksPerWarp, img, y, x0, best, best_d);
+            else drain_tile<1, VOL, WTA>(p, tmem_row, stage, lane, q, half * kChunksPerWarp, img, y, x0, best, best_d);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(bar_acc_empty);
+            if (WTA) {
+                // merge the two halves of each row: larger value wins, equal values -> lower disparity
+                float2 *slot = wta_s + (k & 1) * 256;
+                slot[half * 128 + q * 32 + lane] = make_float2(best, __int_as_float(best_d));
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                if (half == 0) {
+                    const float2 o = slot[128 + q * 32 + lane];
+                    const int od = __float_as_int(o.y);
+                    if (o.x > best || (o.x == best && od < best_d)) best_d = od;
+                    const int x = x0 + q * 32 + lane;
+                    if (x < p.w)
+                        (side == 0 ? p.left_disp : p.right_disp)[((size_t)img * p.h + y) * p.w + x] = (uint8_t)(best_d & 255);
+                }
+            }
         }
     }
 
@@ -284,7 +311,7 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
     auto launch = [&](auto kern) -> int {
         STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tcc::kSmemTotal));
         ProfScope prof(ctx, STEREO_K_CORR);
-        kern<<<grid, 256, tcc::kSmemTotal, ctx->stream>>>(p);
+        kern<<<grid, 128 + 32 * tcc::kEpiWarps, tcc::kSmemTotal, ctx->stream>>>(p);
         ctx->launches += 1;
         STEREO_CUDA_CHECK(cudaGetLastError());
         return STEREO_OK;
