@@ -321,3 +321,13 @@ def test_full_size_tensor_core_pipeline(ctx):
     c = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=False)
     assert np.array_equal(c["left_disp"], b["left_disp"]) and np.array_equal(c["right_disp"], b["right_disp"])
     assert abs(so.three_pixel_error(a["left_disp"][0], gt) - so.three_pixel_error(b["left_disp"][0], gt)) <= 0.0005
+
+
+@pytest.mark.parametrize("D", [4, 64, 228, 256])
+def test_wta_vector_path_matches_numpy(ctx, D):
+    rng = np.random.default_rng(D)
+    vol = rng.standard_normal((1, 7, 53, D)).astype(np.float32)
+    vol[0, 0, 0] = 0.0
+    vol[0, 0, 1, D // 3] = vol[0, 0, 1, D - 1] = 9.0        # tie -> lowest index
+    assert np.array_equal(ctx.wta(vol), np.argmax(vol, axis=3).astype(np.uint8))
+    assert np.array_equal(ctx.wta(vol, take_min=True), np.argmin(vol, axis=3).astype(np.uint8))
