@@ -34,10 +34,12 @@ constexpr int kARun = kTileM * 16, kAPlane = 8 * kARun;      // 16 KB per plane
 constexpr int kBRun = kWinN * 16, kBPlane = 8 * kBRun;       // 48 KB per plane
 constexpr int kSmemA = 0, kSmemB = 2 * kAPlane;
 constexpr int kSmemStage = kSmemB + 2 * kBPlane;             // one [32][33] float block per epilogue warp
-constexpr int kEpiWarps = 8;                                 // two per TMEM lane quarter
-constexpr int kChunksPerWarp = (kWinN / 32) / (kEpiWarps / 4);
-constexpr int kSmemWta = kSmemStage + kEpiWarps * 32 * 33 * 4;   // [2 tiles][2 halves][128] (value, d)
-constexpr int kSmemBars = kSmemWta + 2 * 2 * 128 * 8;
+constexpr int kEpiWarps = 16;                                // four per TMEM lane quarter
+constexpr int kParts = kEpiWarps / 4;                        // column parts of a tile row
+constexpr int kStagePitch = 36;                              // floats; 16-byte stores, conflict-free both ways
+constexpr int kChunksPerWarp = (kWinN / 32) / kParts;
+constexpr int kSmemWta = kSmemStage + kEpiWarps * 32 * kStagePitch * 4;   // [2 tiles][kParts][128] (value, d)
+constexpr int kSmemBars = kSmemWta + 2 * kParts * 128 * 8;
 constexpr int kSmemTotal = kSmemBars + 64;
 constexpr uint32_t kTmemCols = 512;
 
@@ -80,22 +82,27 @@ __device__ __forceinline__ void drain_tile(const Params &p, uint32_t tmem_row, f
         }
         if (VOL) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) stage[lane * 33 + i] = __uint_as_float(v[i]);
+            for (int i = 0; i < 8; ++i)
+                reinterpret_cast<uint4 *>(stage + lane * kStagePitch)[i] = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
             __syncwarp();
-            // row r of the block goes to out[x0 + q*32 + r][d00 +- r]: one 128-byte run per warp store
+            // row r of the block goes to out[x0 + q*32 + r][d00 +- r]: one 128-byte run per warp store.
+            // Offsets are 32-bit and advance by a constant per row (one image row of a volume is < 2^31 floats).
             const int d00 = SIDE == 0 ? q * 32 + D - 1 - (c * 32 + lane) : (c * 32 + lane) - q * 32;
             const int dstep = SIDE == 0 ? 1 : -1;
-            float *dst = vol + (row_pix + x0 + q * 32) * D + d00;
             const int stride = D + dstep;
+            float *rowbase = vol + row_pix * D;
+            int off = (x0 + q * 32) * D + d00;
+            int dd = d00;
 #pragma unroll 1
             for (int r0 = 0; r0 < 32; r0 += 8) {
                 float t[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) t[j] = stage[(r0 + j) * 33 + lane];
+                for (int j = 0; j < 8; ++j) t[j] = stage[(r0 + j) * kStagePitch + lane];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const int r = r0 + j;
-                    if (r < rows_ok && (unsigned)(d00 + dstep * r) < (unsigned)D) dst[(size_t)r * stride] = t[j];
+                    if (r0 + j < rows_ok && (unsigned)dd < (unsigned)D) rowbase[off] = t[j];
+                    off += stride;
+                    dd += dstep;
                 }
             }
             __syncwarp();
@@ -111,14 +118,16 @@ __global__ __launch_bounds__(128 + 32 * kEpiWarps, 1) void corr_tc_kernel(Params
     const uint32_t s_base = tc::smem_u32(smem);
     const uint32_t s_a = s_base + kSmemA, s_b = s_base + kSmemB;
     const uint32_t bar_full = s_base + kSmemBars, bar_empty = bar_full + 8;
-    const uint32_t bar_acc_full = bar_full + 16, bar_acc_empty = bar_full + 24;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSmemBars + 32);
+    const uint32_t bar_acc_full = bar_full + 16, bar_acc_empty = bar_full + 32;     // [2] each
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSmemBars + 48);
 
     if (tid == 0) {
         tc::mbar_init(bar_full, 1);
         tc::mbar_init(bar_empty, 1);
-        tc::mbar_init(bar_acc_full, 1);
-        tc::mbar_init(bar_acc_empty, kEpiWarps);
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(bar_acc_full + 8 * i, 1);
+            tc::mbar_init(bar_acc_empty + 8 * i, kEpiWarps / 2);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -168,18 +177,19 @@ __global__ __launch_bounds__(128 + 32 * kEpiWarps, 1) void corr_tc_kernel(Params
     } else if (warp == 1) {
         if (lane == 0) {
             // ---- MMA issuer ----
-            constexpr uint32_t idesc256 = tc::make_idesc(kTileM, 256);
-            constexpr uint32_t idesc128 = tc::make_idesc(kTileM, 128);
+            constexpr uint32_t idesc_half = tc::make_idesc(kTileM, kWinN / 2);
             const int n_combo = p.planes == 2 ? 3 : 1;
             int k = 0;
             for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x, ++k) {
                 int img, side, y, x0;
                 decode(t, img, side, y, x0);
                 tc::mbar_wait(bar_full, k & 1);
-                tc::mbar_wait(bar_acc_empty, (k & 1) ^ 1);
-                tc::tc_fence_after();
+                // two column blocks of 192 with their own full/empty barriers: block 1 of this tile
+                // is computed while block 0 is drained, block 0 of the next tile while block 1 is
 #pragma unroll 1
                 for (int nb = 0; nb < 2; ++nb) {
+                    tc::mbar_wait(bar_acc_empty + 8 * nb, (k & 1) ^ 1);
+                    tc::tc_fence_after();
                     uint32_t acc = 0;
                     for (int combo = 0; combo < n_combo; ++combo) {
                         // L_lo*R_hi, then L_hi*R_lo, then L_hi*R_hi on both sides, so that the left
@@ -190,28 +200,29 @@ __global__ __launch_bounds__(128 + 32 * kEpiWarps, 1) void corr_tc_kernel(Params
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
                             uint64_t ad = tc::smem_desc(s_a + apl * kAPlane + 2 * ks * kARun, kARun, 128);
-                            uint64_t bd = tc::smem_desc(s_b + bpl * kBPlane + 2 * ks * kBRun + nb * 256 * 16, kBRun, 128);
-                            tc::umma_bf16(tmem_base + nb * 256, ad, bd, nb == 0 ? idesc256 : idesc128, acc);
+                            uint64_t bd = tc::smem_desc(s_b + bpl * kBPlane + 2 * ks * kBRun + nb * (kWinN / 2) * 16, kBRun, 128);
+                            tc::umma_bf16(tmem_base + nb * (kWinN / 2), ad, bd, idesc_half, acc);
                             acc = 1;
                         }
                     }
+                    tc::tc_commit(bar_acc_full + 8 * nb);     // this column block is complete
                 }
                 tc::tc_commit(bar_empty);        // operands may be overwritten
-                tc::tc_commit(bar_acc_full);     // accumulators complete
             }
         }
     } else if (warp >= 4) {
-        // ---- epilogue: 8 warps, warp (q, half) drains columns [half*192, half*192+192) of lanes 32q.. ----
+        // ---- epilogue: warp (q, part) drains kChunksPerWarp 32-column chunks of TMEM lanes 32q.. ----
         const int q = warp & 3;
-        const int half = (warp - 4) >> 2;
-        float *stage = reinterpret_cast<float *>(smem + kSmemStage) + (warp - 4) * 32 * 33;
+        const int half = (warp - 4) >> 2;            // column part of this warp
+        float *stage = reinterpret_cast<float *>(smem + kSmemStage) + (warp - 4) * 32 * kStagePitch;
         float2 *wta_s = reinterpret_cast<float2 *>(smem + kSmemWta);
         const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16);
         int k = 0;
         for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x, ++k) {
             int img, side, y, x0;
             decode(t, img, side, y, x0);
-            tc::mbar_wait(bar_acc_full, k & 1);
+            const int nb = half / (kParts / 2);          // column block this warp drains
+            tc::mbar_wait(bar_acc_full + 8 * nb, k & 1);
             tc::tc_fence_after();
             float best;
             int best_d;
@@ -219,16 +230,19 @@ __global__ __launch_bounds__(128 + 32 * kEpiWarps, 1) void corr_tc_kernel(Params
             else drain_tile<1, VOL, WTA>(p, tmem_row, stage, lane, q, half * kChunksPerWarp, img, y, x0, best, best_d);
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(bar_acc_empty);
+            if (lane == 0) tc::mbar_arrive(bar_acc_empty + 8 * nb);
             if (WTA) {
                 // merge the two halves of each row: larger value wins, equal values -> lower disparity
-                float2 *slot = wta_s + (k & 1) * 256;
+                float2 *slot = wta_s + (k & 1) * (kParts * 128);
                 slot[half * 128 + q * 32 + lane] = make_float2(best, __int_as_float(best_d));
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
                 if (half == 0) {
-                    const float2 o = slot[128 + q * 32 + lane];
-                    const int od = __float_as_int(o.y);
-                    if (o.x > best || (o.x == best && od < best_d)) best_d = od;
+#pragma unroll
+                    for (int part = 1; part < kParts; ++part) {
+                        const float2 o = slot[part * 128 + q * 32 + lane];
+                        const int od = __float_as_int(o.y);
+                        if (o.x > best || (o.x == best && od < best_d)) { best = o.x; best_d = od; }
+                    }
                     const int x = x0 + q * 32 + lane;
                     if (x < p.w)
                         (side == 0 ? p.left_disp : p.right_disp)[((size_t)img * p.h + y) * p.w + x] = (uint8_t)(best_d & 255);
@@ -281,7 +295,7 @@ void corr_tc_geometry(int w, int D, int *wf, int *ml)
 
 int launch_nhwc_to_planar(stereo_ctx *ctx, const float *in, int n, int h, int w, int wf, int ml, void *hi, void *lo)
 {
-    ProfScope prof(ctx, STEREO_K_CORR);
+    ProfScope prof(ctx, STEREO_K_PREP);      // layout conversion, not part of the correlation kernel's time
     tcc::nhwc_to_planar_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(
         in, n, h, w, wf, ml, static_cast<__nv_bfloat16 *>(hi), static_cast<__nv_bfloat16 *>(lo));
     ctx->launches += 1;
