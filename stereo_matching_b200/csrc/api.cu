@@ -91,8 +91,11 @@ struct PlanarOut {
     int wf = 0;
 };
 
+// `u8_left`/`u8_right` (tensor-core path, n == 2 only): the original uint8 images of one pair; layer 1
+// is then computed straight from them (their ImageStats must be in ctx->stats) and `in` is not read.
 static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision,
-                     const PlanarOut *planar = nullptr)
+                     const PlanarOut *planar = nullptr, const uint8_t *u8_left = nullptr,
+                     const uint8_t *u8_right = nullptr)
 {
     STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
     if (!ctx->has_weights[net]) {
@@ -118,7 +121,11 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         uint16_t *b_hi = ctx->act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
         const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>();
         const size_t wl = tc_weight_image_elems();
-        STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
+        if (u8_left)
+            STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host, a_hi,
+                                           planes == 2 ? a_lo : nullptr, wp));
+        else
+            STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
         STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 2, w - 2, wp, wimg, wts + nd.layer[1].b_off, b_hi, b_lo, wp,
                                   nullptr, 1, planes));
         STEREO_TRY(launch_conv_tc(ctx, b_hi, b_lo, n, h - 4, w - 4, wp, wimg + wl, wts + nd.layer[2].b_off, a_hi, a_lo,
@@ -222,8 +229,13 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     if (tc_corr) STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf));
     for (int i = 0; i < n; ++i) {
         // left and right of one pair go through the trunk as a batch of two
-        STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
-        STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
+        if (tc_corr) {
+            // tensor-core path: only the image statistics; layer 1 reads the uint8 images itself
+            STEREO_TRY(launch_image_stats(ctx, left_rgb + i * img_bytes, right_rgb + i * img_bytes, h, w));
+        } else {
+            STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
+            STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
+        }
         float *lv = left_vol ? left_vol + i * map * D : nullptr;
         float *rv = right_vol ? right_vol + i * map * D : nullptr;
         if (tc_corr) {
@@ -234,7 +246,8 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             po.lo = pf.l_lo + (size_t)pf.ml * 8;
             po.wf = pf.wf;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
-            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po));
+            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po, left_rgb + i * img_bytes,
+                                 right_rgb + i * img_bytes));
             STEREO_TRY(launch_corr_tc(ctx, pf.l_hi, pf.l_lo, pf.r_hi, pf.r_lo, 1, h, w, pf.wf, pf.ml, D, planes, lv, rv,
                                       left_disp + i * map, right_disp + i * map));
         } else {
@@ -418,6 +431,8 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
     STEREO_CUDA_CHECK(cudaMemcpyAsync(ctx->weights[net].ptr, packed, sizeof(float) * n_floats,
                                       cudaMemcpyHostToDevice, ctx->stream));
     if (net == STEREO_NET_WIN9) {
+        memcpy(ctx->conv1_host.w, packed + nd.layer[0].w_off, sizeof(ctx->conv1_host.w));
+        memcpy(ctx->conv1_host.b, packed + nd.layer[0].b_off, sizeof(ctx->conv1_host.b));
         // UMMA B-operand images (bf16 hi/lo) of the three 64->64 layers
         const size_t wl = tc_weight_image_elems();
         STEREO_TRY(ctx->wsplit[net].reserve(3 * wl * 2));

@@ -60,6 +60,19 @@ struct NetDesc {
 
 NetDesc net_desc(int net);
 
+// exact integer moments of a uint8 image and the 256-entry normalisation table built from them
+struct ImageStats {
+    unsigned long long sum;
+    unsigned long long sumsq;
+    float lut[256];
+};
+
+// first-layer weights of base_model_ws_9 as they are passed to conv1_direct_kernel (by value)
+struct Conv1Weights {
+    float w[27 * 64];   // [ky][kx][cin][cout]
+    float b[64];
+};
+
 // CUDA-event timing of kernel classes (stereo_profile_*).
 struct Profiler {
     static constexpr int kMaxPairs = 8192;
@@ -89,6 +102,7 @@ struct stereo_ctx {
     stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
     stereo::DevBuf stage_out[3];
     stereo::DevBuf stage_vol[2];
+    stereo::Conv1Weights conv1_host;   // host copy of the ws9 first layer (kernel-parameter weights)
     stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
     int featp_geom[5] = {0, 0, 0, 0, 0};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
@@ -123,6 +137,10 @@ struct ProfScope {
 
 // prep.cu
 int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out);
+int launch_image_stats(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w);
+// conv1_direct.cu
+int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
+                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out);
 // conv_ffma.cu
 int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in,
                      int n, int h_in, int w_in, float *out);

@@ -9,12 +9,6 @@
 
 namespace stereo {
 
-struct ImageStats {
-    unsigned long long sum;
-    unsigned long long sumsq;
-    float lut[256];
-};
-
 __global__ void image_sums_kernel(const uint8_t *__restrict__ rgb, size_t per_image, ImageStats *stats)
 {
     const uint8_t *img = rgb + (size_t)blockIdx.y * per_image;
@@ -108,6 +102,25 @@ __global__ void normalize_pad_kernel(const uint8_t *__restrict__ rgb, const Imag
         if (x >= 0 && x < w && y >= 0 && y < h) v = lut[src[((size_t)y * w + x) * 3 + c]];
         dst[i] = v;
     }
+}
+
+// sums + LUT of two separately stored images (left, right of one pair) into ctx->stats[0..1]
+int launch_image_stats(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w)
+{
+    STEREO_TRY(ctx->stats.reserve(sizeof(ImageStats) * 2));
+    ImageStats *stats = ctx->stats.as<ImageStats>();
+    ProfScope prof(ctx, STEREO_K_PREP);
+    STEREO_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(ImageStats) * 2, ctx->stream));
+    size_t per_image = (size_t)h * w * 3;
+    int bx = (int)((per_image / 16 + 255) / 256);
+    if (bx > ctx->sm_count * 2) bx = ctx->sm_count * 2;
+    if (bx < 1) bx = 1;
+    image_sums_kernel<<<dim3(bx, 1), 256, 0, ctx->stream>>>(img0, per_image, stats);
+    image_sums_kernel<<<dim3(bx, 1), 256, 0, ctx->stream>>>(img1, per_image, stats + 1);
+    build_lut_kernel<<<2, 256, 0, ctx->stream>>>(stats, (double)per_image);
+    ctx->launches += 3;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
 }
 
 int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out)
