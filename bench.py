@@ -120,8 +120,8 @@ def cpu_pair_seconds(rows: int, threads: int | None, repeats: int = 1):
     import torch
     from oracle import stereo_oracle as so
     from stereo_matching_b200 import checkpoint, synth
-    if threads:
-        torch.set_num_threads(threads)
+    # torchrun exports OMP_NUM_THREADS=1; the CPU baseline is meant to use every host core
+    torch.set_num_threads(threads or os.cpu_count() or 1)
     layers = checkpoint.load_net_weights(GOLDEN_CKPT)
     l, r, _ = synth.make_pair(1000, H, W, D)
     l, r = l[:rows], r[:rows]
@@ -412,8 +412,8 @@ def run_b200(args):
         "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (fp32 accumulate)", "bf16": "bf16"}[args.precision],
         "data": "synthetic", "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": UNIT,
-                "h2d_bytes_per_step": int(2 * e2e_pairs * reps * H * W * 3),
-                "d2h_bytes_per_step": int(3 * e2e_pairs * reps * H * W)},
+                "h2d_bytes_per_step": int(world * 2 * e2e_pairs * reps * H * W * 3),
+                "d2h_bytes_per_step": int(world * 3 * e2e_pairs * reps * H * W)},
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
         "roofline": roofline,
