@@ -149,6 +149,11 @@ int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *we
 // conv_tc.cu
 size_t tc_weight_image_elems();
 int tc_pitch(int w);
+int tc2_pitch(int w);
+int launch_weight_images2(stereo_ctx *ctx, const float *layer_w, void *img);
+int launch_conv_tc2(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
+                    const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
+                    int relu, int planes);
 int launch_weight_images(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv_tc(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
                    const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
