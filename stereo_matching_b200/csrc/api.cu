@@ -85,15 +85,16 @@ static int check_dims(int n, int h, int w)
     return STEREO_OK;
 }
 
-// STEREO_CONV_2CTA=0 selects the single-CTA tensor-core convolution (conv_tc.cu) instead of the
-// CTA-pair kernel (conv_tc2.cu); read once.
-static bool conv_pair_mode()
+// Which tensor-core convolution runs trunk layers 2-4.  STEREO_CONV_KERNEL=1: single CTA
+// (conv_tc.cu), 2: CTA pair, one output row at a time (conv_tc2.cu), 3 (default): CTA pair,
+// row-streaming N = 192 (conv_tc3.cu).  Read once.
+static int conv_kernel_mode()
 {
-    static const bool on = [] {
-        const char *e = getenv("STEREO_CONV_2CTA");
-        return !(e && e[0] == '0');
+    static const int mode = [] {
+        const char *e = getenv("STEREO_CONV_KERNEL");
+        return (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 3;
     }();
-    return on;
+    return mode;
 }
 
 // Planar (hi, lo) feature output of the tensor-core trunk, consumed by the tensor-core correlation.
@@ -124,16 +125,17 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
                        "the tensor-core trunk is built for base_model_ws_9 (3x3, 64 channels); use STEREO_PREC_FP32 for base_model");
         // layer 1 on CUDA cores (K = 27) writing chunk-planar bf16 (hi, lo); layers 2-4 on tcgen05
         const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
-        const bool pair = conv_pair_mode();
-        const int wp = pair ? tc2_pitch(w - 2) : tc_pitch(w - 2);
+        const int mode = conv_kernel_mode();
+        const int wp = mode >= 2 ? tc2_pitch(w - 2) : tc_pitch(w - 2);
         const size_t plane_elems = (size_t)n * (h - 2) * 8 * wp * 8;
         STEREO_TRY(ctx->act[0].reserve(2 * plane_elems * 2));
         STEREO_TRY(ctx->act[1].reserve(2 * plane_elems * 2));
         uint16_t *a_hi = ctx->act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
         uint16_t *b_hi = ctx->act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
-        const size_t wl = tc_weight_image_elems();
-        const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (pair ? 3 * wl : 0);
-        auto launch_conv_tc = pair ? launch_conv_tc2 : stereo::launch_conv_tc;
+        size_t wl = tc_weight_image_elems();
+        if (mode == 3) wl = tc3_weight_image_elems();
+        const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (mode == 1 ? 0 : (mode == 2 ? 3 : 6) * tc_weight_image_elems());
+        auto launch_conv_tc = mode == 3 ? launch_conv_tc3 : (mode == 2 ? launch_conv_tc2 : stereo::launch_conv_tc);
         if (u8_left)
             STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host, a_hi,
                                            planes == 2 ? a_lo : nullptr, wp));
@@ -448,13 +450,16 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
         memcpy(ctx->conv1_host.b, packed + nd.layer[0].b_off, sizeof(ctx->conv1_host.b));
         // UMMA B-operand images (bf16 hi/lo) of the three 64->64 layers
         const size_t wl = tc_weight_image_elems();
-        // (single-CTA layout first, then the per-CTA halves of the 2-CTA kernel)
-        STEREO_TRY(ctx->wsplit[net].reserve(6 * wl * 2));
+        // (single-CTA layout first, then the per-CTA halves of the two CTA-pair kernels)
+        const size_t wl3 = tc3_weight_image_elems();
+        STEREO_TRY(ctx->wsplit[net].reserve((6 * wl + 3 * wl3) * 2));
         for (int l = 1; l < 4; ++l) {
             STEREO_TRY(launch_weight_images(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
                                             ctx->wsplit[net].as<uint16_t>() + (l - 1) * wl));
             STEREO_TRY(launch_weight_images2(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
                                              ctx->wsplit[net].as<uint16_t>() + (l + 2) * wl));
+            STEREO_TRY(launch_weight_images3(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
+                                             ctx->wsplit[net].as<uint16_t>() + 6 * wl + (l - 1) * wl3));
         }
     }
     STEREO_TRY(finish(ctx));

@@ -150,6 +150,14 @@ int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *we
 size_t tc_weight_image_elems();
 int tc_pitch(int w);
 int tc2_pitch(int w);
+int corr_sweep_margin();
+int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
+                      int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
+size_t tc3_weight_image_elems();
+int launch_weight_images3(stereo_ctx *ctx, const float *layer_w, void *img);
+int launch_conv_tc3(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
+                    const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
+                    int relu, int planes);
 int launch_weight_images2(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv_tc2(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
                     const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,

@@ -1,0 +1,329 @@
+// Fused correlation + WTA, sweeping along image rows (/root/reference/inference.py:139-183).
+//
+// corr_tc.cu treats every 128-pixel tile on its own and reloads the whole 384-column candidate
+// window (128 KB of operands per tile): it is bound by that reload, which cannot overlap the MMAs
+// because only one operand set fits into shared memory.  Neighbouring tiles of one image row share
+// two thirds of their window, so here a CTA sweeps along a row: the candidates live in a ring of
+// four 128-pixel blocks, every tile adds ONE new block (and its own 128 pixels, double-buffered),
+// i.e. 64 KB per tile, loaded by TMA two tiles ahead of the MMAs.
+//
+//   left  sweep: own = L block k, candidates = R blocks k-2, k-1, k,   d = xi + 256 - u
+//   right sweep: own = R block k, candidates = L blocks k,   k+1, k+2, d = u - xi
+//   (xi = pixel inside the own block, u = column inside the 384-wide window)
+//
+// Per tile the issuer runs three M=128 x N=128 accumulations (one per candidate block, K = 64,
+// bf16 hi/lo split = 12 MMAs each) into a ring of four 128-column tensor-memory blocks; 16 epilogue
+// warps drain each block as soon as its MMAs commit (one 32-column chunk per warp, chunks outside
+// the disparity band skipped), keep the running arg max in registers and merge the four column
+// parts through shared memory at the end of the tile.  The volume never exists.
+#include <cuda_bf16.h>
+
+#include <cstdlib>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace stereo {
+
+namespace tcs {
+
+constexpr int kBlk = 128;                       // pixels per block
+constexpr int kRun = kBlk * 16;                 // one channel chunk: 2 KB
+constexpr int kPlane = 8 * kRun;                // 16 KB
+constexpr int kBlock = 2 * kPlane;              // hi + lo: 32 KB
+constexpr int kASlots = 3, kBSlots = 4, kAccBlocks = 4;
+constexpr int kSmemA = 0;
+constexpr int kSmemB = kSmemA + kASlots * kBlock;
+constexpr int kSmemWtaV = kSmemB + kBSlots * kBlock;         // [3 parts][128] best value of column parts 1-3
+constexpr int kSmemWtaD = kSmemWtaV + 3 * 128 * 4;           // [3 parts][128] its disparity (16 bit)
+constexpr int kSmemBars = kSmemWtaD + 3 * 128 * 2;
+constexpr int kSmemTotal = kSmemBars + 256;
+static_assert(kSmemTotal <= 232448, "shared memory budget of one CTA");
+constexpr int kEpiWarps = 16;
+constexpr int kThreads = 128 + 32 * kEpiWarps;
+constexpr uint32_t kTmemCols = 512;
+constexpr int kMargin = 256;                    // zero columns the feature rows need left of pixel 0
+
+struct Params {
+    const __nv_bfloat16 *l_hi, *l_lo, *r_hi, *r_lo;   // [n][h][8][wf][8], pixel x at column ml + x
+    int n, h, w, wf, ml, D, planes;
+    uint8_t *left_disp, *right_disp;                   // [n][h][w]
+    int nb, tps, segs, nitems;                         // blocks per row, tiles per segment, segments per row
+};
+
+struct Item {
+    int img, side, y, k0, k1;
+};
+
+__device__ __forceinline__ Item decode(const Params &p, int item)
+{
+    Item it;
+    // left and right sweep of one row are neighbouring items: they run at the same time on
+    // neighbouring CTAs and the second reader of every feature block finds it in L2
+    const int seg = item % p.segs;
+    int rest = item / p.segs;
+    it.side = rest & 1;
+    rest >>= 1;
+    it.y = rest % p.h;
+    it.img = rest / p.h;
+    it.k0 = seg * p.tps;
+    it.k1 = min(p.nb, it.k0 + p.tps);
+    return it;
+}
+
+__global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t s_base = tc::smem_u32(smem);
+    const uint32_t s_a = s_base + kSmemA, s_b = s_base + kSmemB;
+    const uint32_t bar_a_full = s_base + kSmemBars;          // [3]
+    const uint32_t bar_a_empty = bar_a_full + 24;            // [3]
+    const uint32_t bar_b_full = bar_a_full + 48;             // [4]
+    const uint32_t bar_b_empty = bar_a_full + 80;            // [4]
+    const uint32_t bar_acc_full = bar_a_full + 112;          // [4]
+    const uint32_t bar_acc_empty = bar_a_full + 144;         // [4]
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSmemBars + 176);
+
+    if (tid == 0) {
+        for (int i = 0; i < kASlots; ++i) {
+            tc::mbar_init(bar_a_full + 8 * i, 1);
+            tc::mbar_init(bar_a_empty + 8 * i, 1);
+        }
+        for (int i = 0; i < 4; ++i) {
+            tc::mbar_init(bar_b_full + 8 * i, 1);
+            tc::mbar_init(bar_b_empty + 8 * i, 1);
+            tc::mbar_init(bar_acc_full + 8 * i, 1);
+            tc::mbar_init(bar_acc_empty + 8 * i, kEpiWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)),
+                     "r"(kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const size_t img_elems = (size_t)p.h * 8 * p.wf * 8;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---- TMA producer: candidate blocks two tiles ahead, own blocks one tile ahead ----
+            uint32_t E = 0, T = 0;                   // running candidate-block and tile counters
+            for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+                const Item it = decode(p, item);
+                const size_t row0 = (size_t)it.img * img_elems + (size_t)it.y * 8 * p.wf * 8;
+                const __nv_bfloat16 *own[2] = {it.side == 0 ? p.l_hi : p.r_hi, it.side == 0 ? p.l_lo : p.r_lo};
+                const __nv_bfloat16 *oth[2] = {it.side == 0 ? p.r_hi : p.l_hi, it.side == 0 ? p.r_lo : p.l_lo};
+                auto load_block = [&](uint32_t dst, const __nv_bfloat16 *const *src, int col, uint32_t bar) {
+                    tc::mbar_expect_tx(bar, (uint32_t)p.planes * kPlane);
+                    for (int pl = 0; pl < p.planes; ++pl)
+                        for (int cc = 0; cc < 8; ++cc)
+                            tc::bulk_g2s(dst + pl * kPlane + cc * kRun,
+                                         src[pl] + row0 + ((size_t)cc * p.wf + col) * 8, kRun, bar);
+                };
+                auto load_entry = [&](int j) {       // j-th candidate block of this row
+                    const uint32_t slot = E % kBSlots, ph = (E / kBSlots) & 1;
+                    ++E;
+                    tc::mbar_wait(bar_b_empty + 8 * slot, ph ^ 1);
+                    load_block(s_b + slot * kBlock, oth, p.ml + kBlk * (it.side == 0 ? j - 2 : j), bar_b_full + 8 * slot);
+                };
+                auto load_own = [&](int k) {
+                    const uint32_t slot = T % kASlots, ph = (T / kASlots) & 1;
+                    ++T;
+                    tc::mbar_wait(bar_a_empty + 8 * slot, ph ^ 1);
+                    load_block(s_a + slot * kBlock, own, p.ml + kBlk * k, bar_a_full + 8 * slot);
+                };
+                load_own(it.k0);
+                load_entry(it.k0);
+                load_entry(it.k0 + 1);
+                for (int k = it.k0; k < it.k1; ++k) {
+                    load_entry(k + 2);
+                    if (k + 1 < it.k1) load_own(k + 1);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ---- MMA issuer ----
+            constexpr uint32_t idesc = tc::make_idesc(kBlk, kBlk);
+            const uint32_t d_hi = tc::desc_hi(128);
+            const int n_combo = p.planes == 2 ? 3 : 1;
+            uint32_t E0 = 0, T = 0, G = 0;           // first candidate block of the item, tiles, accumulator blocks
+            for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+                const Item it = decode(p, item);
+                // L_lo*R_hi, then L_hi*R_lo, then L_hi*R_hi on both sides: the left and the right
+                // volume accumulate the same terms in the same order
+                const int lo_first = it.side == 0 ? 0 : 1;
+                for (int k = it.k0; k < it.k1; ++k) {
+                    const uint32_t as = T % kASlots;
+                    tc::mbar_wait(bar_a_full + 8 * as, (T / kASlots) & 1);
+                    const uint32_t e_first = E0 + (uint32_t)(k - it.k0);
+#pragma unroll 1
+                    for (int o = 0; o < 3; ++o) {
+                        const uint32_t e = e_first + o, bs = e % kBSlots;
+                        if (k == it.k0 || o == 2) tc::mbar_wait(bar_b_full + 8 * bs, (e / kBSlots) & 1);
+                        const uint32_t ab = G % kAccBlocks;
+                        tc::mbar_wait(bar_acc_empty + 8 * ab, ((G / kAccBlocks) & 1) ^ 1);
+                        ++G;
+                        tc::tc_fence_after();
+                        uint32_t acc = 0;
+                        for (int combo = 0; combo < n_combo; ++combo) {
+                            const int apl = (n_combo == 3 && combo == lo_first) ? 1 : 0;
+                            const int bpl = (n_combo == 3 && combo == 1 - lo_first) ? 1 : 0;
+                            const uint32_t a_lo = tc::desc_lo(s_a + as * kBlock + apl * kPlane, kRun);
+                            const uint32_t b_lo = tc::desc_lo(s_b + bs * kBlock + bpl * kPlane, kRun);
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks) {
+                                tc::umma_bf16_parts(tmem_base + ab * kBlk, a_lo + ((2 * ks * kRun) >> 4), d_hi,
+                                                    b_lo + ((2 * ks * kRun) >> 4), d_hi, idesc, acc);
+                                acc = 1;
+                            }
+                        }
+                        tc::tc_commit(bar_acc_full + 8 * ab);
+                        // the oldest candidate block has had its last use (at the end of a row all three have)
+                        if (o == 0 || k == it.k1 - 1) tc::tc_commit(bar_b_empty + 8 * bs);
+                    }
+                    tc::tc_commit(bar_a_empty + 8 * as);
+                    ++T;
+                }
+                E0 += (uint32_t)(it.k1 - it.k0) + 2;
+            }
+        }
+    } else if (warp >= 4) {
+        // ---- epilogue: warp (q, part) drains columns 32*part.. of every accumulator block, lanes 32q.. ----
+        const int q = warp & 3, part = (warp - 4) >> 2;
+        const int xi = q * 32 + lane;
+        const int D = p.D;
+        float *wta_v = reinterpret_cast<float *>(smem + kSmemWtaV);
+        uint16_t *wta_d = reinterpret_cast<uint16_t *>(smem + kSmemWtaD);
+        uint32_t T = 0, G = 0;
+        for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
+            const Item it = decode(p, item);
+            for (int k = it.k0; k < it.k1; ++k, ++T) {
+                float best = -INFINITY;
+                int best_d = 0x7fffffff;
+#pragma unroll 1
+                for (int o = 0; o < 3; ++o, ++G) {
+                    const uint32_t ab = G % kAccBlocks;
+                    tc::mbar_wait(bar_acc_full + 8 * ab, (G / kAccBlocks) & 1);
+                    tc::tc_fence_after();
+                    const int u0 = 128 * o + 32 * part;                  // first window column of this chunk
+                    // disparities this warp can see in the chunk (warp-uniform): skip it when none is in [0, D)
+                    const int dlo = it.side == 0 ? 32 * q + kMargin - u0 - 31 : u0 - 32 * q - 31;
+                    if (dlo + 62 >= 0 && dlo <= D - 1) {
+                        uint32_t v[32];
+                        tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
+                        if (it.side == 0) {
+                            // d falls as u rises, so ">=" keeps the lowest d among equals
+                            const int dbase = xi + kMargin - u0;
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const int d = dbase - i;
+                                const float f = __uint_as_float(v[i]);
+                                const bool take = (unsigned)d < (unsigned)D && f >= best;
+                                best = take ? f : best;
+                                best_d = take ? d : best_d;
+                            }
+                        } else {
+                            const int dbase = u0 - xi;
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const int d = dbase + i;
+                                const float f = __uint_as_float(v[i]);
+                                const bool take = (unsigned)d < (unsigned)D && f > best;
+                                best = take ? f : best;
+                                best_d = take ? d : best_d;
+                            }
+                        }
+                    }
+                    tc::tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(bar_acc_empty + 8 * ab);
+                }
+                // merge the four column parts of each row: larger value wins, equal values -> lower disparity.
+                // Barrier 1: parts 1-3 have written; barrier 2: part 0 has read (so the buffer can be rewritten).
+                if (part != 0) {
+                    if (T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                    wta_v[(part - 1) * 128 + xi] = best;
+                    wta_d[(part - 1) * 128 + xi] = (uint16_t)(best_d == 0x7fffffff ? 0xffff : best_d);
+                    asm volatile("bar.arrive 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                } else {
+                    asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+#pragma unroll
+                    for (int pt = 0; pt < 3; ++pt) {
+                        const float ov = wta_v[pt * 128 + xi];
+                        const int od = wta_d[pt * 128 + xi];
+                        if (ov > best || (ov == best && od < best_d)) { best = ov; best_d = od; }
+                    }
+                    asm volatile("bar.arrive 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                    const int x = kBlk * k + xi;
+                    if (x < p.w)
+                        (it.side == 0 ? p.left_disp : p.right_disp)[((size_t)it.img * p.h + it.y) * p.w + x] =
+                            (uint8_t)(best_d & 255);
+                }
+            }
+        }
+        if (part != 0 && T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+    }
+
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc::tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    }
+}
+
+}  // namespace tcs
+
+int corr_sweep_margin() { return tcs::kMargin; }
+
+int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
+                      int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp)
+{
+    const int nb = (w + tcs::kBlk - 1) / tcs::kBlk;
+    STEREO_REQUIRE(D >= 1 && D - 1 <= tcs::kMargin, "row-sweep correlation supports disp_range <= %d, got %d",
+                   tcs::kMargin + 1, D);
+    STEREO_REQUIRE(ml >= tcs::kMargin && wf >= ml + tcs::kBlk * (nb + 2), "feature margins too small");
+    tcs::Params p;
+    p.l_hi = static_cast<const __nv_bfloat16 *>(l_hi);
+    p.l_lo = static_cast<const __nv_bfloat16 *>(l_lo);
+    p.r_hi = static_cast<const __nv_bfloat16 *>(r_hi);
+    p.r_lo = static_cast<const __nv_bfloat16 *>(r_lo);
+    p.n = n; p.h = h; p.w = w; p.wf = wf; p.ml = ml; p.D = D; p.planes = planes;
+    p.left_disp = left_disp; p.right_disp = right_disp;
+    p.nb = nb;
+    // rows may be cut into segments when that balances the persistent CTAs better: cost model =
+    // rounds x (tiles per segment + half a tile of pipeline fill)
+    const int rows = n * 2 * h;
+    int best_segs = 1;
+    double best_cost = 1e30;
+    for (int segs = 1; segs <= 4 && segs <= nb; ++segs) {
+        const int tps = (nb + segs - 1) / segs;
+        const int real_segs = (nb + tps - 1) / tps;
+        const long items = (long)rows * real_segs;
+        const double cost = (double)((items + ctx->sm_count - 1) / ctx->sm_count) * (tps + 0.5);
+        if (cost < best_cost) { best_cost = cost; best_segs = real_segs; }
+    }
+    if (const char *e = getenv("STEREO_CORR_SEGS")) {      // tuning override
+        const int v = atoi(e);
+        if (v >= 1 && v <= nb) best_segs = v;
+    }
+    p.tps = (nb + best_segs - 1) / best_segs;
+    p.segs = (nb + p.tps - 1) / p.tps;
+    p.nitems = rows * p.segs;
+    const int grid = p.nitems < ctx->sm_count ? p.nitems : ctx->sm_count;
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(tcs::corr_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           tcs::kSmemTotal));
+    ProfScope prof(ctx, STEREO_K_CORR);
+    tcs::corr_sweep_kernel<<<grid, tcs::kThreads, tcs::kSmemTotal, ctx->stream>>>(p);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo

@@ -289,8 +289,12 @@ int corr_tc_max_disp() { return tcc::kWinN - tcc::kTileM + 1; }
 
 void corr_tc_geometry(int w, int D, int *wf, int *ml)
 {
-    *ml = (D - 1 + 7) / 8 * 8;
-    *wf = *ml + w + tcc::kWinN;
+    // left margin: what the row-sweep kernel wants (corr_sweep.cu), or D-1 rounded up if that is more;
+    // right margin: a whole candidate window past the last 128-pixel block
+    const int need = (D - 1 + 7) / 8 * 8;
+    *ml = need > corr_sweep_margin() ? need : corr_sweep_margin();
+    const int nb = (w + tcc::kTileM - 1) / tcc::kTileM;
+    *wf = *ml + nb * tcc::kTileM + (tcc::kWinN - tcc::kTileM);
 }
 
 int launch_nhwc_to_planar(stereo_ctx *ctx, const float *in, int n, int h, int w, int wf, int ml, void *hi, void *lo)
@@ -309,9 +313,14 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
 {
     STEREO_REQUIRE(D >= 1 && D <= corr_tc_max_disp(), "tensor-core correlation supports disp_range <= %d, got %d",
                    corr_tc_max_disp(), D);
-    STEREO_REQUIRE(ml >= D - 1 && wf >= ml + w + tcc::kWinN, "feature margins too small");
+    STEREO_REQUIRE(ml >= D - 1 && wf >= ml + (w + tcc::kTileM - 1) / tcc::kTileM * tcc::kTileM + tcc::kWinN - tcc::kTileM,
+                   "feature margins too small");
     bool vol = left_vol != nullptr, wta = left_disp != nullptr;
     STEREO_REQUIRE(vol || wta, "nothing to compute");
+    // fused WTA only: the row-sweep kernel (STEREO_CORR_KERNEL=1 keeps the per-tile kernel below)
+    static const bool sweep = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return !(e && e[0] == '1'); }();
+    if (!vol && sweep && ml >= corr_sweep_margin())
+        return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
     tcc::Params p;
     p.l_hi = static_cast<const __nv_bfloat16 *>(l_hi);
     p.l_lo = static_cast<const __nv_bfloat16 *>(l_lo);
