@@ -286,16 +286,18 @@ def run_b200(args):
     corr_tflops = band_flops_pair * n * args.steps / (corr_ms / 1e3) / 1e12 if corr_ms > 0 else 0.0
     corr_bytes = 2.0 * H * W * 64 * 4 + 2.0 * H * W      # fp32-equivalent feature bytes in, two uint8 maps out
     rooflines = {
-        "conv": {"kernel": ("conv3x3_tc_kernel (tcgen05, trunk layers 2-4)" if args.precision != "fp32"
+        "conv": {"kernel": ("conv3x3_tc3_kernel (tcgen05 cta_group::2, M=256 x N=192, trunk layers 2-4)" if args.precision != "fp32"
                             else "conv_ffma_kernel<3,64,64> (trunk layers 2-4)"),
                  "bound": "tensor", "achieved": conv_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
                  "frac": conv_tflops / tensor_peak, "traffic": None,
                  "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
                  "avg_launch_ms": conv_ms / conv_launches if conv_launches else None,
                  "share_of_step": shares.get("conv"), "mma_passes": split,
+                 "executed_frac": split * conv_tflops / tensor_peak,
                  "note": "algorithmic FLOPs (2*9*64*64 per output pixel, counted once whatever the operand split) / "
-                         "CUDA-event time of the kernel class; the tensor pipe executes mma_passes x these FLOPs"},
-        "corr": {"kernel": ("corr_tc_kernel<fused WTA> (tcgen05)" if args.precision != "fp32"
+                         "CUDA-event time of the kernel class; the tensor pipe executes mma_passes x these FLOPs "
+                         "(executed_frac = that rate / peak; ncu: profiles/)"},
+        "corr": {"kernel": ("corr_sweep_kernel (tcgen05, fused WTA)" if args.precision != "fp32"
                             else "corr_ffma_kernel<fused WTA>"),
                  "bound": "tensor", "achieved": corr_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
                  "frac": corr_tflops / tensor_peak, "traffic": None,

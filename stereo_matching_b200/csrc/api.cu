@@ -136,9 +136,13 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         if (mode == 3) wl = tc3_weight_image_elems();
         const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (mode == 1 ? 0 : (mode == 2 ? 3 : 6) * tc_weight_image_elems());
         auto launch_conv_tc = mode == 3 ? launch_conv_tc3 : (mode == 2 ? launch_conv_tc2 : stereo::launch_conv_tc);
-        if (u8_left)
-            STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host, a_hi,
-                                           planes == 2 ? a_lo : nullptr, wp));
+        if (u8_left) {
+            // STEREO_CONV1_KERNEL=1: CUDA-core layer 1 (conv1_direct.cu); default: tensor cores (conv1_tc.cu)
+            static const bool direct = [] { const char *e = getenv("STEREO_CONV1_KERNEL"); return e && e[0] == '1'; }();
+            auto launch_conv1 = direct ? launch_conv1_direct : launch_conv1_tc;
+            STEREO_TRY(launch_conv1(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host, a_hi,
+                                    planes == 2 ? a_lo : nullptr, wp));
+        }
         else
             STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
         STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 2, w - 2, wp, wimg, wts + nd.layer[1].b_off, b_hi, b_lo, wp,

@@ -141,6 +141,8 @@ int launch_image_stats(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1
 // conv1_direct.cu
 int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
                         const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out);
+int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
+                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out);
 // conv_ffma.cu
 int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in,
                      int n, int h_in, int w_in, float *out);
@@ -151,6 +153,9 @@ size_t tc_weight_image_elems();
 int tc_pitch(int w);
 int tc2_pitch(int w);
 int corr_sweep_margin();
+int corr_sweep2_row_cols(int w);
+int launch_corr_sweep2(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
+                       int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                       int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
 size_t tc3_weight_image_elems();

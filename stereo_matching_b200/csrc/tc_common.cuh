@@ -116,6 +116,42 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// One lane of a converged warp (elect.sync): wrapping each tcgen05 / bulk-copy instruction in
+// `if (elect_one())` inside warp-uniform control flow lets ptxas emit the instruction once, without
+// the per-lane loop it adds when the whole code path is entered by a single thread.
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "elect.sync _|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+// A operand from tensor memory ("TS" form): rows = lanes, two bf16 per 32-bit column, 8 columns per K=16
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t b_hi,
+                                             uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// shared memory -> tensor memory: 128 rows x 32 bytes (one K=16 slab of a K-major bf16 operand) into
+// 128 lanes x 8 columns; executes in issue order with the MMAs of the same thread
+__device__ __forceinline__ void tmem_cp_128x256b(uint32_t taddr, uint32_t d_lo, uint32_t d_hi)
+{
+    asm volatile(
+        "{\n\t.reg .b64 ds;\n\t"
+        "mov.b64 ds, {%1, %2};\n\t"
+        "tcgen05.cp.cta_group::1.128x256b [%0], ds;\n\t}"
+        ::"r"(taddr), "r"(d_lo), "r"(d_hi)
+        : "memory");
+}
 // ---- CTA-pair (cta_group::2) helpers ----
 __device__ __forceinline__ uint32_t cluster_rank()
 {
