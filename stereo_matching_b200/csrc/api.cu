@@ -139,9 +139,14 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         if (u8_left) {
             // STEREO_CONV1_KERNEL=1: CUDA-core layer 1 (conv1_direct.cu); default: tensor cores (conv1_tc.cu)
             static const bool direct = [] { const char *e = getenv("STEREO_CONV1_KERNEL"); return e && e[0] == '1'; }();
-            auto launch_conv1 = direct ? launch_conv1_direct : launch_conv1_tc;
-            STEREO_TRY(launch_conv1(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host, a_hi,
-                                    planes == 2 ? a_lo : nullptr, wp));
+            if (direct)
+                STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host,
+                                               a_hi, planes == 2 ? a_lo : nullptr, wp));
+            else
+                STEREO_TRY(launch_conv1_tc(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink,
+                                           ctx->wsplit[net].as<uint16_t>() + 6 * tc_weight_image_elems() +
+                                               3 * tc3_weight_image_elems(),
+                                           wts + nd.layer[0].b_off, a_hi, planes == 2 ? a_lo : nullptr, wp));
         }
         else
             STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
@@ -456,7 +461,9 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
         const size_t wl = tc_weight_image_elems();
         // (single-CTA layout first, then the per-CTA halves of the two CTA-pair kernels)
         const size_t wl3 = tc3_weight_image_elems();
-        STEREO_TRY(ctx->wsplit[net].reserve((6 * wl + 3 * wl3) * 2));
+        STEREO_TRY(ctx->wsplit[net].reserve((6 * wl + 3 * wl3 + conv1_tc_weight_image_elems()) * 2));
+        STEREO_TRY(launch_conv1_weight_image(ctx, ctx->weights[net].as<float>() + nd.layer[0].w_off,
+                                             ctx->wsplit[net].as<uint16_t>() + 6 * wl + 3 * wl3));
         for (int l = 1; l < 4; ++l) {
             STEREO_TRY(launch_weight_images(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
                                             ctx->wsplit[net].as<uint16_t>() + (l - 1) * wl));

@@ -46,10 +46,11 @@ constexpr uint32_t kTmemCols = 256;
 constexpr int kEpiWarps = 8, kBuildWarps = 5;
 constexpr int kThreads = 128 + 32 * (kEpiWarps + kBuildWarps);
 
-__global__ __launch_bounds__(kThreads, 1) void conv1_tc_kernel(const uint8_t *__restrict__ img0,
+__global__ __launch_bounds__(kThreads, 2) void conv1_tc_kernel(const uint8_t *__restrict__ img0,
                                                               const uint8_t *__restrict__ img1,
                                                               const ImageStats *__restrict__ stats, int h, int w,
-                                                              const __grid_constant__ Conv1Weights cw,
+                                                              const __nv_bfloat16 *__restrict__ wimg,
+                                                              const float *__restrict__ bias,
                                                               __nv_bfloat16 *__restrict__ out_hi,
                                                               __nv_bfloat16 *__restrict__ out_lo, int wp_out,
                                                               int rows_per_cta)
@@ -86,21 +87,9 @@ __global__ __launch_bounds__(kThreads, 1) void conv1_tc_kernel(const uint8_t *__
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int i = tid; i < 256; i += kThreads) s_lut[i] = stats[im].lut[i];
-    if (tid < 64) s_bias[tid] = cw.b[tid];
-    {
-        __nv_bfloat16 *s_wb = reinterpret_cast<__nv_bfloat16 *>(smem + kSmemW);
-        for (int i = tid; i < 3 * 2 * 64 * 8; i += kThreads) {       // over [kx][chunk][n][k8]
-            const int k8 = i & 7, n = (i >> 3) & 63, ch = (i >> 9) & 1, kx = i >> 10;
-            const int k = ch * 8 + k8;                               // 0..15; k = 3 ky + c for k < 9
-            float v = 0.f;
-            if (k < 9) v = cw.w[(((k / 3) * 3 + kx) * 3 + (k % 3)) * 64 + n];
-            const __nv_bfloat16 hi = __float2bfloat16_rn(v);
-            const __nv_bfloat16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
-            const int off = (kx * 2 + ch) * 64 * 8 + n * 8 + k8;
-            s_wb[off] = hi;
-            s_wb[3 * (kWTap / 2) + off] = lo;
-        }
-    }
+    if (tid < 64) s_bias[tid] = __ldg(bias + tid);
+    for (int i = tid; i < 6 * kWTap / 16; i += kThreads)
+        reinterpret_cast<uint4 *>(smem + kSmemW)[i] = __ldg(reinterpret_cast<const uint4 *>(wimg) + i);
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"(kTmemCols));
@@ -175,25 +164,33 @@ __global__ __launch_bounds__(kThreads, 1) void conv1_tc_kernel(const uint8_t *__
         const bool active = col < kPW;
         const int xi = x0 + col - kPad;                              // image column
         const bool x_in = active && xi >= 0 && xi < w;
-        // normalised (hi, lo) bf16 of the three colours of one padded-image row at this column, packed
-        // as hi0|hi1, hi2|0, lo0|lo1, lo2|0
-        auto load_row = [&](int yp, uint32_t (&o)[4]) {
+        // raw bytes of one padded-image row at this column (0xffffffff = outside the image), fetched one
+        // row ahead of their use so that the load latency overlaps the previous row's work
+        auto fetch = [&](int yp) -> uint32_t {
             const int yi = yp - kPad;
+            if (!(x_in && yi >= 0 && yi < h)) return 0xffffffffu;
+            const uint8_t *px = img + ((size_t)yi * w + xi) * 3;
+            return (uint32_t)px[0] | ((uint32_t)px[1] << 8) | ((uint32_t)px[2] << 16);
+        };
+        // normalised (hi, lo) bf16 of the three colours, packed as hi0|hi1, hi2|0, lo0|lo1, lo2|0
+        auto convert = [&](uint32_t raw, uint32_t (&o)[4]) {
             float f0 = 0.f, f1 = 0.f, f2 = 0.f;
-            if (x_in && yi >= 0 && yi < h) {
-                const uint8_t *px = img + ((size_t)yi * w + xi) * 3;
-                f0 = s_lut[px[0]];
-                f1 = s_lut[px[1]];
-                f2 = s_lut[px[2]];
+            if (raw != 0xffffffffu) {
+                f0 = s_lut[raw & 255];
+                f1 = s_lut[(raw >> 8) & 255];
+                f2 = s_lut[(raw >> 16) & 255];
             }
             split_bf16x2(f0, f1, o[0], o[2]);
             split_bf16x2(f2, 0.f, o[1], o[3]);
         };
         uint32_t r0[4], r1[4], r2[4];
-        load_row(y0, r0);
-        load_row(y0 + 1, r1);
+        convert(fetch(y0), r0);
+        convert(fetch(y0 + 1), r1);
+        uint32_t raw_next = fetch(y0 + 2);
         for (int r = 0; r < rows; ++r) {
-            load_row(y0 + r + 2, r2);
+            const uint32_t raw = raw_next;
+            raw_next = fetch(y0 + r + 3);
+            convert(raw, r2);
             const uint32_t as = r % kASlots;
             mbar_wait(bar_a_empty + 8 * as, ((r / kASlots) & 1) ^ 1);
             if (active) {
@@ -229,10 +226,35 @@ __global__ __launch_bounds__(kThreads, 1) void conv1_tc_kernel(const uint8_t *__
     }
 }
 
+// [plane][kx][k/8][n][8] bf16 operand images of the 27x64 weights, k = 3 ky + c (zero for k >= 9)
+__global__ void conv1_weight_image_kernel(const float *__restrict__ w, __nv_bfloat16 *__restrict__ img)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;             // over [kx][chunk][n][k8]
+    if (i >= 3 * 2 * 64 * 8) return;
+    const int k8 = i & 7, n = (i >> 3) & 63, ch = (i >> 9) & 1, kx = i >> 10;
+    const int k = ch * 8 + k8;
+    float v = 0.f;
+    if (k < 9) v = w[(((k / 3) * 3 + kx) * 3 + (k % 3)) * 64 + n];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+    img[i] = hi;
+    img[3 * 2 * 64 * 8 + i] = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+
 }  // namespace c1
 
-int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w, const Conv1Weights &cw,
-                    void *out_hi, void *out_lo, int wp_out)
+size_t conv1_tc_weight_image_elems() { return (size_t)2 * 3 * 2 * 64 * 8; }
+
+int launch_conv1_weight_image(stereo_ctx *ctx, const float *layer_w, void *img)
+{
+    c1::conv1_weight_image_kernel<<<(3 * 2 * 64 * 8 + 255) / 256, 256, 0, ctx->stream>>>(
+        layer_w, static_cast<__nv_bfloat16 *>(img));
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w, const void *wimg,
+                    const float *bias, void *out_hi, void *out_lo, int wp_out)
 {
     const int h1 = h + 2 * c1::kPad - 2, w1 = w + 2 * c1::kPad - 2;
     const int strips = (w1 + c1::kStripW - 1) / c1::kStripW;
@@ -246,7 +268,8 @@ int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, i
                                            c1::kSmemTotal));
     ProfScope prof(ctx, STEREO_K_CONV_FIRST);
     c1::conv1_tc_kernel<<<grid, c1::kThreads, c1::kSmemTotal, ctx->stream>>>(
-        img0, img1, ctx->stats.as<ImageStats>(), h, w, cw, static_cast<__nv_bfloat16 *>(out_hi),
+        img0, img1, ctx->stats.as<ImageStats>(), h, w, static_cast<const __nv_bfloat16 *>(wimg), bias,
+        static_cast<__nv_bfloat16 *>(out_hi),
         static_cast<__nv_bfloat16 *>(out_lo), wp_out, rows);
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
