@@ -107,7 +107,7 @@ struct PlanarOut {
 // is then computed straight from them (their ImageStats must be in ctx->stats) and `in` is not read.
 static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision,
                      const PlanarOut *planar = nullptr, const uint8_t *u8_left = nullptr,
-                     const uint8_t *u8_right = nullptr)
+                     const uint8_t *u8_right = nullptr, int stats_off = 0)
 {
     STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
     if (!ctx->has_weights[net]) {
@@ -141,12 +141,12 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
             static const bool direct = [] { const char *e = getenv("STEREO_CONV1_KERNEL"); return e && e[0] == '1'; }();
             if (direct)
                 STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host,
-                                               a_hi, planes == 2 ? a_lo : nullptr, wp));
+                                               a_hi, planes == 2 ? a_lo : nullptr, wp, stats_off));
             else
                 STEREO_TRY(launch_conv1_tc(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink,
                                            ctx->wsplit[net].as<uint16_t>() + 6 * tc_weight_image_elems() +
                                                3 * tc3_weight_image_elems(),
-                                           wts + nd.layer[0].b_off, a_hi, planes == 2 ? a_lo : nullptr, wp));
+                                           wts + nd.layer[0].b_off, a_hi, planes == 2 ? a_lo : nullptr, wp, stats_off));
         }
         else
             STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
@@ -250,13 +250,14 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     const size_t map = (size_t)h * w;
     const bool tc_corr = precision != STEREO_PREC_FP32 && net == STEREO_NET_WIN9 && D <= corr_tc_max_disp();
     PlanarFeat pf;
-    if (tc_corr) STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf));
+    if (tc_corr) {
+        STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf));
+        // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
+        STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
+    }
     for (int i = 0; i < n; ++i) {
         // left and right of one pair go through the trunk as a batch of two
-        if (tc_corr) {
-            // tensor-core path: only the image statistics; layer 1 reads the uint8 images itself
-            STEREO_TRY(launch_image_stats(ctx, left_rgb + i * img_bytes, right_rgb + i * img_bytes, h, w));
-        } else {
+        if (!tc_corr) {
             STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
             STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
         }
@@ -271,7 +272,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             po.wf = pf.wf;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
             STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po, left_rgb + i * img_bytes,
-                                 right_rgb + i * img_bytes));
+                                 right_rgb + i * img_bytes, 2 * i));
             STEREO_TRY(launch_corr_tc(ctx, pf.l_hi, pf.l_lo, pf.r_hi, pf.r_lo, 1, h, w, pf.wf, pf.ml, D, planes, lv, rv,
                                       left_disp + i * map, right_disp + i * map));
         } else {

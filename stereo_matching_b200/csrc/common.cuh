@@ -137,14 +137,14 @@ struct ProfScope {
 
 // prep.cu
 int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out);
-int launch_image_stats(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w);
+int launch_pair_stats(stereo_ctx *ctx, const uint8_t *left, const uint8_t *right, int n, int h, int w);
 // conv1_direct.cu
 int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
-                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out);
+                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out, int stats_off);
 size_t conv1_tc_weight_image_elems();
 int launch_conv1_weight_image(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w, const void *wimg,
-                    const float *bias, void *out_hi, void *out_lo, int wp_out);
+                    const float *bias, void *out_hi, void *out_lo, int wp_out, int stats_off);
 // conv_ffma.cu
 int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in,
                      int n, int h_in, int w_in, float *out);

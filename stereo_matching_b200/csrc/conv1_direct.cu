@@ -81,7 +81,7 @@ __global__ __launch_bounds__(128, 3) void conv1_direct_kernel(const uint8_t *__r
 }
 
 int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
-                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out)
+                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out, int stats_off)
 {
     const int h1 = h + 2 * kC1Pad - 2, w1o = w + 2 * kC1Pad - 2;
     // 3 CTAs fit on an SM (168 registers): size the row segments so that the grid is one full wave
@@ -92,7 +92,7 @@ int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img
     if (rows < 4) rows = 4;
     dim3 grid(strips, (h1 + rows - 1) / rows, 2);
     ProfScope prof(ctx, STEREO_K_CONV_FIRST);
-    conv1_direct_kernel<<<grid, 128, 0, ctx->stream>>>(img0, img1, ctx->stats.as<ImageStats>(), h, w, cw,
+    conv1_direct_kernel<<<grid, 128, 0, ctx->stream>>>(img0, img1, ctx->stats.as<ImageStats>() + stats_off, h, w, cw,
                                                        static_cast<__nv_bfloat16 *>(out_hi),
                                                        static_cast<__nv_bfloat16 *>(out_lo), wp_out, rows);
     ctx->launches += 1;

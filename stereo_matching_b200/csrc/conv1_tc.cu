@@ -254,7 +254,7 @@ int launch_conv1_weight_image(stereo_ctx *ctx, const float *layer_w, void *img)
 }
 
 int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w, const void *wimg,
-                    const float *bias, void *out_hi, void *out_lo, int wp_out)
+                    const float *bias, void *out_hi, void *out_lo, int wp_out, int stats_off)
 {
     const int h1 = h + 2 * c1::kPad - 2, w1 = w + 2 * c1::kPad - 2;
     const int strips = (w1 + c1::kStripW - 1) / c1::kStripW;
@@ -268,7 +268,7 @@ int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, i
                                            c1::kSmemTotal));
     ProfScope prof(ctx, STEREO_K_CONV_FIRST);
     c1::conv1_tc_kernel<<<grid, c1::kThreads, c1::kSmemTotal, ctx->stream>>>(
-        img0, img1, ctx->stats.as<ImageStats>(), h, w, static_cast<const __nv_bfloat16 *>(wimg), bias,
+        img0, img1, ctx->stats.as<ImageStats>() + stats_off, h, w, static_cast<const __nv_bfloat16 *>(wimg), bias,
         static_cast<__nv_bfloat16 *>(out_hi),
         static_cast<__nv_bfloat16 *>(out_lo), wp_out, rows);
     ctx->launches += 1;

@@ -271,34 +271,47 @@ int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, in
 }
 
 // ---- left-right consistency (adcensus.outlier_detection, smooth/nyu.lua:95) ----
-__global__ void lr_check_kernel(const uint8_t *__restrict__ d0, const uint8_t *__restrict__ d1, size_t total,
-                                int w, int D, uint8_t *__restrict__ outlier)
+// The reference searches, for every inconsistent left pixel x, all d in [0, min(D, x+1)) for a right
+// pixel x-d whose disparity is within 1 of d (-> "mismatch", else "occlusion").  Seen from the right
+// image that is a scatter: right pixel x' with disparity v explains the left positions x'+d for
+// d in {v-1, v, v+1} and 0 <= d < D.  One CTA per image row marks those positions in shared memory
+// (3 stores per pixel instead of a D-step search per pixel), then classifies the row.
+constexpr int kLrMaxW = 8192;
+
+__global__ __launch_bounds__(256) void lr_check_kernel(const uint8_t *__restrict__ d0, const uint8_t *__restrict__ d1,
+                                                       int w, int D, uint8_t *__restrict__ outlier)
 {
-    size_t id = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (id >= total) return;
-    int x = (int)(id % w);
-    int d0i = d0[id];
-    uint8_t res;
-    if (x - d0i < 0) {
-        res = 1;
-    } else if (fabsf((float)d0i - (float)d1[id - d0i]) < 1.1f) {
-        res = 0;
-    } else {
-        res = 1;
-        int dmax = D < x + 1 ? D : x + 1;
-        for (int d = 0; d < dmax; ++d) {
-            if (fabsf((float)d - (float)d1[id - d]) < 1.1f) { res = 2; break; }
-        }
+    __shared__ uint8_t s_d1[kLrMaxW];
+    __shared__ uint8_t s_mark[kLrMaxW];
+    const size_t row = (size_t)blockIdx.x * w;
+    for (int x = threadIdx.x; x < w; x += blockDim.x) {
+        s_d1[x] = d1[row + x];
+        s_mark[x] = 0;
     }
-    outlier[id] = res;
+    __syncthreads();
+    for (int x = threadIdx.x; x < w; x += blockDim.x) {
+        const int v = s_d1[x];
+#pragma unroll
+        for (int d = v - 1; d <= v + 1; ++d)
+            if (d >= 0 && d < D && x + d < w) s_mark[x + d] = 1;
+    }
+    __syncthreads();
+    for (int x = threadIdx.x; x < w; x += blockDim.x) {
+        const int d0i = d0[row + x];
+        uint8_t res;
+        if (x - d0i < 0) res = 1;
+        else if (abs(d0i - (int)s_d1[x - d0i]) <= 1) res = 0;
+        else res = s_mark[x] ? 2 : 1;
+        outlier[row + x] = res;
+    }
 }
 
 int launch_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
                     uint8_t *outlier)
 {
-    size_t total = (size_t)n * h * w;
+    STEREO_REQUIRE(w <= kLrMaxW, "image width %d exceeds the LR-check row buffer (%d)", w, kLrMaxW);
     ProfScope prof(ctx, STEREO_K_LR);
-    lr_check_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(d0, d1, total, w, D, outlier);
+    lr_check_kernel<<<(unsigned)(n * h), 256, 0, ctx->stream>>>(d0, d1, w, D, outlier);
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;

@@ -9,7 +9,8 @@
 
 namespace stereo {
 
-__global__ void image_sums_kernel(const uint8_t *__restrict__ rgb, size_t per_image, ImageStats *stats)
+__global__ void image_sums_kernel(const uint8_t *__restrict__ rgb, size_t per_image, ImageStats *stats,
+                                  int stat_stride = 1)
 {
     const uint8_t *img = rgb + (size_t)blockIdx.y * per_image;
     unsigned long long s = 0, ss = 0;
@@ -61,8 +62,8 @@ __global__ void image_sums_kernel(const uint8_t *__restrict__ rgb, size_t per_im
             ss += __shfl_down_sync(0xffffffffu, ss, o);
         }
         if (lane == 0) {
-            atomicAdd(&stats[blockIdx.y].sum, s);
-            atomicAdd(&stats[blockIdx.y].sumsq, ss);
+            atomicAdd(&stats[blockIdx.y * stat_stride].sum, s);
+            atomicAdd(&stats[blockIdx.y * stat_stride].sumsq, ss);
         }
     }
 }
@@ -104,20 +105,22 @@ __global__ void normalize_pad_kernel(const uint8_t *__restrict__ rgb, const Imag
     }
 }
 
-// sums + LUT of two separately stored images (left, right of one pair) into ctx->stats[0..1]
-int launch_image_stats(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w)
+// sums + LUT of n pairs whose left and right images are stored in two separate arrays, into
+// ctx->stats[2i] (left of pair i) and ctx->stats[2i + 1] (right): three launches for the whole batch
+int launch_pair_stats(stereo_ctx *ctx, const uint8_t *left, const uint8_t *right, int n, int h, int w)
 {
-    STEREO_TRY(ctx->stats.reserve(sizeof(ImageStats) * 2));
+    STEREO_TRY(ctx->stats.reserve(sizeof(ImageStats) * 2 * (size_t)n));
     ImageStats *stats = ctx->stats.as<ImageStats>();
     ProfScope prof(ctx, STEREO_K_PREP);
-    STEREO_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(ImageStats) * 2, ctx->stream));
+    STEREO_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(ImageStats) * 2 * (size_t)n, ctx->stream));
     size_t per_image = (size_t)h * w * 3;
     int bx = (int)((per_image / 16 + 255) / 256);
-    if (bx > ctx->sm_count * 2) bx = ctx->sm_count * 2;
+    const int cap = n >= 8 ? 32 : ctx->sm_count * 2;
+    if (bx > cap) bx = cap;
     if (bx < 1) bx = 1;
-    image_sums_kernel<<<dim3(bx, 1), 256, 0, ctx->stream>>>(img0, per_image, stats);
-    image_sums_kernel<<<dim3(bx, 1), 256, 0, ctx->stream>>>(img1, per_image, stats + 1);
-    build_lut_kernel<<<2, 256, 0, ctx->stream>>>(stats, (double)per_image);
+    image_sums_kernel<<<dim3(bx, n), 256, 0, ctx->stream>>>(left, per_image, stats, 2);
+    image_sums_kernel<<<dim3(bx, n), 256, 0, ctx->stream>>>(right, per_image, stats + 1, 2);
+    build_lut_kernel<<<2 * n, 256, 0, ctx->stream>>>(stats, (double)per_image);
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
