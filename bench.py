@@ -263,6 +263,8 @@ def run_b200(args):
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = world * e2e_pairs * reps * args.steps / e2e_s
     assert np.array_equal(p_ld[0].numpy(), ld0), "host and device entry points disagree"
+    e2e_h2d = int(world * 2 * e2e_pairs * reps * H * W * 3)      # uint8 left + right images of every pair
+    e2e_d2h = int(world * 3 * e2e_pairs * reps * H * W)          # two disparity maps + the LR-check labels
 
     if world > 1:
         dist.barrier()
@@ -289,7 +291,13 @@ def run_b200(args):
         "conv": {"kernel": ("conv3x3_tc3_kernel (tcgen05 cta_group::2, M=256 x N=192, trunk layers 2-4)" if args.precision != "fp32"
                             else "conv_ffma_kernel<3,64,64> (trunk layers 2-4)"),
                  "bound": "tensor", "achieved": conv_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
-                 "frac": conv_tflops / tensor_peak, "traffic": None,
+                 "frac": conv_tflops / tensor_peak,
+                 # dram__bytes_read.sum + dram__bytes_write.sum per launch of conv3x3_tc3_kernel at 375x1242
+                 # (ncu --set full, profiles/r01_ncu_summary.md: 267.4 MB + 191.9 MB); algorithmic bytes per
+                 # launch are the bf16 (hi, lo) activations in and out, 2 x 2 x 2 x 64 x 2 B per pixel
+                 "traffic": (459.3e6 if (args.precision != "fp32" and (H, W) == (375, 1242)) else None),
+                 "algorithmic_bytes_per_launch": 2.0 * 2 * 64 * 2 * 2 * (H + 5) * (W + 5),
+                 "tensor_pipe_active_ncu": 0.85 if args.precision == "bf16x3" else None,
                  "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
                  "avg_launch_ms": conv_ms / conv_launches if conv_launches else None,
                  "share_of_step": shares.get("conv"), "mma_passes": split,
@@ -414,8 +422,7 @@ def run_b200(args):
         "vs_baseline": None, "dtype": {"fp32": "f32", "bf16x3": "bf16x3 (fp32 accumulate)", "bf16": "bf16"}[args.precision],
         "data": "synthetic", "config": workload_config(args, world),
         "e2e": {"value": e2e_value, "unit": UNIT,
-                "h2d_bytes_per_step": int(world * 2 * e2e_pairs * reps * H * W * 3),
-                "d2h_bytes_per_step": int(world * 3 * e2e_pairs * reps * H * W)},
+                "h2d_bytes_per_step": e2e_h2d, "d2h_bytes_per_step": e2e_d2h},
         "gpu_launches": int(launches),
         "clocks": clocks.summary(),
         "roofline": roofline,
