@@ -371,6 +371,12 @@ int stereo_destroy(stereo_ctx *ctx)
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
+    for (int i = 0; i < 16; ++i) {
+        if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+        if (ctx->ev_out[i]) cudaEventDestroy(ctx->ev_out[i]);
+    }
+    if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+    if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return STEREO_OK;
@@ -662,6 +668,53 @@ int stereo_pairs(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_
     STEREO_REQUIRE((left_vol == nullptr) == (right_vol == nullptr), "left and right volumes must be given together");
     size_t img_b = (size_t)n * h * w * 3, map_b = (size_t)n * h * w;
     size_t vol_b = sizeof(float) * (size_t)n * h * w * D;
+    if (!left_vol && n > 1) {
+        // Maps only: cut the batch into up to 16 chunks and run upload, compute and download of neighbouring
+        // chunks at the same time (copy engines on their own streams, ordered by events).  The staging
+        // buffers hold the whole batch, so chunks never alias.
+        STEREO_TRY(ctx->stage_in[0].reserve(img_b));
+        STEREO_TRY(ctx->stage_in[1].reserve(img_b));
+        for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->stage_out[i].reserve(map_b));
+        if (!ctx->copy_in) {
+            STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+            STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+            for (int i = 0; i < 16; ++i) {
+                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_out[i], cudaEventDisableTiming));
+            }
+        }
+        const int chunk = (n + 15) / 16;
+        const size_t img1 = (size_t)h * w * 3, map1 = (size_t)h * w;
+        uint8_t *d_l = ctx->stage_in[0].as<uint8_t>(), *d_r = ctx->stage_in[1].as<uint8_t>();
+        uint8_t *d_ld = ctx->stage_out[0].as<uint8_t>(), *d_rd = ctx->stage_out[1].as<uint8_t>();
+        uint8_t *d_lr = ctx->stage_out[2].as<uint8_t>();
+        // uploads start once everything queued on the compute stream so far (which may still read the
+        // staging buffers) is done
+        STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_out[0], ctx->stream));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->copy_in, ctx->ev_out[0], 0));
+        int k = 0;
+        for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
+            const int m = n - i0 < chunk ? n - i0 : chunk;
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(d_l + i0 * img1, left_rgb + i0 * img1, m * img1, cudaMemcpyHostToDevice, ctx->copy_in));
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(d_r + i0 * img1, right_rgb + i0 * img1, m * img1, cudaMemcpyHostToDevice, ctx->copy_in));
+            STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_in[k], ctx->copy_in));
+        }
+        k = 0;
+        for (int i0 = 0; i0 < n; i0 += chunk, ++k) {
+            const int m = n - i0 < chunk ? n - i0 : chunk;
+            STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_in[k], 0));
+            STEREO_TRY(pairs_dev(ctx, net, d_l + i0 * img1, d_r + i0 * img1, m, h, w, D, precision, d_ld + i0 * map1,
+                                 d_rd + i0 * map1, lr_outlier ? d_lr + i0 * map1 : nullptr, nullptr, nullptr));
+            STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_out[k], ctx->stream));
+            STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->copy_out, ctx->ev_out[k], 0));
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(left_disp + i0 * map1, d_ld + i0 * map1, m * map1, cudaMemcpyDeviceToHost, ctx->copy_out));
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(right_disp + i0 * map1, d_rd + i0 * map1, m * map1, cudaMemcpyDeviceToHost, ctx->copy_out));
+            if (lr_outlier)
+                STEREO_CUDA_CHECK(cudaMemcpyAsync(lr_outlier + i0 * map1, d_lr + i0 * map1, m * map1, cudaMemcpyDeviceToHost, ctx->copy_out));
+        }
+        STEREO_CUDA_CHECK(cudaStreamSynchronize(ctx->copy_out));
+        return finish(ctx);
+    }
     STEREO_TRY(h2d(ctx, ctx->stage_in[0], left_rgb, img_b));
     STEREO_TRY(h2d(ctx, ctx->stage_in[1], right_rgb, img_b));
     for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->stage_out[i].reserve(map_b));

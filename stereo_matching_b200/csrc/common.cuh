@@ -111,6 +111,9 @@ struct stereo_ctx {
     cudaStream_t aux_stream = nullptr;   // second stream of the post chain
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
+    // host-pointer stereo_pairs: H2D and D2H run on their own streams, chunk by chunk, under the compute
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in[16] = {}, ev_out[16] = {};
 };
 
 namespace stereo {
