@@ -218,7 +218,6 @@ def run_b200(args):
         for _ in range(args.warmup):
             step_dev()
         barrier()
-        ctx.profile_enable(True)
         launches0 = ctx.launch_count
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         with ClockSampler(local_rank) as clocks:
@@ -229,6 +228,18 @@ def run_b200(args):
             barrier()
         ms = max_over_ranks(ev0.elapsed_time(ev1))
         launches = ctx.launch_count - launches0
+        # Kernel-class durations for the rooflines: the same K steps once more with the library's event
+        # profiling on.  While it is on the library runs the pairs one after the other on one stream (in the
+        # timed region above two pairs are in flight on two streams and their kernels share the GPU), so
+        # every kernel is timed alone, on the stream it is launched on.
+        ctx.profile_enable(True)
+        pev0, pev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pev0.record(stream)
+        for _ in range(args.steps):
+            step_dev()
+        pev1.record(stream)
+        barrier()
+        serial_ms = pev0.elapsed_time(pev1)
         prof = ctx.profile_read()
         ctx.profile_enable(False)
     value = world * n * args.steps / (ms / 1e3)
@@ -321,6 +332,10 @@ def run_b200(args):
     extra = {"kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items() if v[1]},
              "kernel_share": {k: v for k, v in shares.items() if v},
              "other_rooflines": {k: v for k, v in rooflines.items() if k != dominant},
+             "serial_ms_per_step": serial_ms / args.steps,
+             "note": "kernel_ms_per_step / kernel_share / rooflines come from a second pass of the same K steps with "
+                     "kernel-class event timing on, in which pairs run one at a time (serial_ms_per_step); the "
+                     "headline value is the first pass, where two pairs are in flight on two streams",
              "three_px_error_pair0": err0}
 
     # ---- BASELINE.json metric, second half: "cost-volume GB/s vs HBM peak" (configs[0] shape: one pair,

@@ -107,7 +107,7 @@ struct PlanarOut {
 // is then computed straight from them (their ImageStats must be in ctx->stats) and `in` is not read.
 static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, int w, float *out, int precision,
                      const PlanarOut *planar = nullptr, const uint8_t *u8_left = nullptr,
-                     const uint8_t *u8_right = nullptr, int stats_off = 0)
+                     const uint8_t *u8_right = nullptr, int stats_off = 0, int lane = 0)
 {
     STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
     if (!ctx->has_weights[net]) {
@@ -128,10 +128,11 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         const int mode = conv_kernel_mode();
         const int wp = mode >= 2 ? tc2_pitch(w - 2) : tc_pitch(w - 2);
         const size_t plane_elems = (size_t)n * (h - 2) * 8 * wp * 8;
-        STEREO_TRY(ctx->act[0].reserve(2 * plane_elems * 2));
-        STEREO_TRY(ctx->act[1].reserve(2 * plane_elems * 2));
-        uint16_t *a_hi = ctx->act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
-        uint16_t *b_hi = ctx->act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
+        DevBuf *act = lane ? ctx->act_b : ctx->act;
+        STEREO_TRY(act[0].reserve(2 * plane_elems * 2));
+        STEREO_TRY(act[1].reserve(2 * plane_elems * 2));
+        uint16_t *a_hi = act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
+        uint16_t *b_hi = act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
         size_t wl = tc_weight_image_elems();
         if (mode == 3) wl = tc3_weight_image_elems();
         const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (mode == 1 ? 0 : (mode == 2 ? 3 : 6) * tc_weight_image_elems());
@@ -192,22 +193,24 @@ struct PlanarFeat {
     int wf, ml;
 };
 
-static int ensure_planar(stereo_ctx *ctx, int n, int h, int w, int D, PlanarFeat *f)
+static int ensure_planar(stereo_ctx *ctx, int n, int h, int w, int D, PlanarFeat *f, int lane = 0)
 {
+    DevBuf &buf = lane ? ctx->featp_b : ctx->featp;
+    int *cached = lane ? ctx->featp_b_geom : ctx->featp_geom;
     corr_tc_geometry(w, D, &f->wf, &f->ml);
     const size_t side_elems = (size_t)n * h * 8 * f->wf * 8;
     const size_t bytes = 4 * side_elems * sizeof(uint16_t);
-    const bool grown = bytes > ctx->featp.bytes;
-    STEREO_TRY(ctx->featp.reserve(bytes));
+    const bool grown = bytes > buf.bytes;
+    STEREO_TRY(buf.reserve(bytes));
     const int geom[5] = {n, h, w, f->wf, f->ml};
     bool same = !grown;
-    for (int i = 0; i < 5; ++i) same = same && ctx->featp_geom[i] == geom[i];
+    for (int i = 0; i < 5; ++i) same = same && cached[i] == geom[i];
     if (!same) {
         // margins must read as exact zeros (the zero-filled slots of inference.py:140-141)
-        STEREO_CUDA_CHECK(cudaMemsetAsync(ctx->featp.ptr, 0, ctx->featp.bytes, ctx->stream));
-        for (int i = 0; i < 5; ++i) ctx->featp_geom[i] = geom[i];
+        STEREO_CUDA_CHECK(cudaMemsetAsync(buf.ptr, 0, buf.bytes, ctx->stream));
+        for (int i = 0; i < 5; ++i) cached[i] = geom[i];
     }
-    uint16_t *base = ctx->featp.as<uint16_t>();
+    uint16_t *base = buf.as<uint16_t>();
     f->l_hi = base;
     f->r_hi = base + side_elems;
     f->l_lo = base + 2 * side_elems;
@@ -249,13 +252,37 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     const size_t img_bytes = (size_t)h * w * 3;
     const size_t map = (size_t)h * w;
     const bool tc_corr = precision != STEREO_PREC_FP32 && net == STEREO_NET_WIN9 && D <= corr_tc_max_disp();
-    PlanarFeat pf;
+    PlanarFeat pf[2];
+    // (kernel-class profiling wants every kernel alone on the GPU: one lane while it is on)
+    const int lanes = (tc_corr && n > 1 && !ctx->prof.on) ? 2 : 1;
+    cudaStream_t lane_stream[2] = {ctx->stream, ctx->stream};
     if (tc_corr) {
-        STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf));
         // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
         STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
+        STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[0], 0));
+        if (lanes == 2) {
+            // Pairs alternate between two streams with their own activation and feature buffers: the first
+            // CTAs of one pair's next kernel fill the SMs that the tail of the other pair's kernel leaves idle.
+            if (!ctx->aux_stream) STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+            if (!ctx->ev_fork) {
+                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+            }
+            STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[1], 1));
+            lane_stream[1] = ctx->aux_stream;
+            STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+            STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+        }
     }
+    struct LaneStream {                      // launches go to ctx->stream: point it at the lane's stream
+        stereo_ctx *ctx;
+        cudaStream_t saved;
+        LaneStream(stereo_ctx *c, cudaStream_t s) : ctx(c), saved(c->stream) { c->stream = s; }
+        ~LaneStream() { ctx->stream = saved; }
+    };
     for (int i = 0; i < n; ++i) {
+        const int lane = lanes == 2 ? (i & 1) : 0;
+        LaneStream on_lane(ctx, lane_stream[lane]);
         // left and right of one pair go through the trunk as a batch of two
         if (!tc_corr) {
             STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
@@ -266,20 +293,25 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
         if (tc_corr) {
             // the trunk's last layer writes the chunk-planar bf16 features the correlation reads
             // (image 0 = left, image 1 = right are adjacent sides of one plane)
+            const PlanarFeat &f = pf[lane];
             PlanarOut po;
-            po.hi = pf.l_hi + (size_t)pf.ml * 8;
-            po.lo = pf.l_lo + (size_t)pf.ml * 8;
-            po.wf = pf.wf;
+            po.hi = f.l_hi + (size_t)f.ml * 8;
+            po.lo = f.l_lo + (size_t)f.ml * 8;
+            po.wf = f.wf;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
             STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po, left_rgb + i * img_bytes,
-                                 right_rgb + i * img_bytes, 2 * i));
-            STEREO_TRY(launch_corr_tc(ctx, pf.l_hi, pf.l_lo, pf.r_hi, pf.r_lo, 1, h, w, pf.wf, pf.ml, D, planes, lv, rv,
+                                 right_rgb + i * img_bytes, 2 * i, lane));
+            STEREO_TRY(launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, 1, h, w, f.wf, f.ml, D, planes, lv, rv,
                                       left_disp + i * map, right_disp + i * map));
         } else {
             STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, feat, precision));
             STEREO_TRY(corr_dev(ctx, feat, feat + feat_img, 1, h, w, 64, D, precision, lv, rv, left_disp + i * map,
                                 right_disp + i * map));
         }
+    }
+    if (lanes == 2) {
+        STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     }
     if (lr_outlier) STEREO_TRY(launch_lr_check(ctx, left_disp, right_disp, n, h, w, D, lr_outlier));
     return STEREO_OK;
@@ -357,7 +389,7 @@ int stereo_destroy(stereo_ctx *ctx)
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
                       &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2], &ctx->post_vol[3], &ctx->post_vol[4], &ctx->post_vol[5], &ctx->post_vol[6], &ctx->post_vol[7],
                       &ctx->post_cnt[0], &ctx->post_cnt[1],
-                      &ctx->post_maps, &ctx->featp};
+                      &ctx->post_maps, &ctx->featp, &ctx->featp_b, &ctx->act_b[0], &ctx->act_b[1]};
     for (DevBuf *b : bufs) b->release();
     if (ctx->prof.start) {
         for (int i = 0; i < Profiler::kMaxPairs; ++i) {
