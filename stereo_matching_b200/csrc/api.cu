@@ -128,7 +128,7 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
         const int mode = conv_kernel_mode();
         const int wp = mode >= 2 ? tc2_pitch(w - 2) : tc_pitch(w - 2);
         const size_t plane_elems = (size_t)n * (h - 2) * 8 * wp * 8;
-        DevBuf *act = lane ? ctx->act_b : ctx->act;
+        DevBuf *act = lane ? ctx->act_b + 2 * (lane - 1) : ctx->act;
         STEREO_TRY(act[0].reserve(2 * plane_elems * 2));
         STEREO_TRY(act[1].reserve(2 * plane_elems * 2));
         uint16_t *a_hi = act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
@@ -195,8 +195,8 @@ struct PlanarFeat {
 
 static int ensure_planar(stereo_ctx *ctx, int n, int h, int w, int D, PlanarFeat *f, int lane = 0)
 {
-    DevBuf &buf = lane ? ctx->featp_b : ctx->featp;
-    int *cached = lane ? ctx->featp_b_geom : ctx->featp_geom;
+    DevBuf &buf = lane ? ctx->featp_b[lane - 1] : ctx->featp;
+    int *cached = lane ? ctx->featp_b_geom[lane - 1] : ctx->featp_geom;
     corr_tc_geometry(w, D, &f->wf, &f->ml);
     const size_t side_elems = (size_t)n * h * 8 * f->wf * 8;
     const size_t bytes = 4 * side_elems * sizeof(uint16_t);
@@ -252,26 +252,37 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     const size_t img_bytes = (size_t)h * w * 3;
     const size_t map = (size_t)h * w;
     const bool tc_corr = precision != STEREO_PREC_FP32 && net == STEREO_NET_WIN9 && D <= corr_tc_max_disp();
-    PlanarFeat pf[2];
-    // (kernel-class profiling wants every kernel alone on the GPU: one lane while it is on)
-    const int lanes = (tc_corr && n > 1 && !ctx->prof.on) ? 2 : 1;
-    cudaStream_t lane_stream[2] = {ctx->stream, ctx->stream};
+    PlanarFeat pf[4];
+    // Pairs alternate between up to four streams ("lanes") with their own activation and feature buffers: the
+    // first CTAs of one pair's next kernel fill the SMs that the tail of another pair's kernel leaves idle, and
+    // launch gaps disappear.  Kernel-class profiling wants every kernel alone on the GPU: one lane while it is on.
+    static const int max_lanes = [] { const char *e = getenv("STEREO_PAIR_LANES"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
+    int lanes = (tc_corr && !ctx->prof.on) ? max_lanes : 1;
+    if (lanes > n) lanes = n;
+    cudaStream_t lane_stream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (tc_corr) {
         // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
         STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
         STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[0], 0));
-        if (lanes == 2) {
-            // Pairs alternate between two streams with their own activation and feature buffers: the first
-            // CTAs of one pair's next kernel fill the SMs that the tail of the other pair's kernel leaves idle.
-            if (!ctx->aux_stream) STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
-            if (!ctx->ev_fork) {
-                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-                STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-            }
-            STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[1], 1));
-            lane_stream[1] = ctx->aux_stream;
+        if (lanes > 1) {
+            if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+            if (!ctx->ev_join) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
             STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, ctx->stream));
-            STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+            for (int l = 1; l < lanes; ++l) {
+                if (!ctx->lane_streams[l - 1]) {
+                    STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->lane_streams[l - 1], cudaStreamNonBlocking));
+                    STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->lane_join[l - 1], cudaEventDisableTiming));
+                }
+                lane_stream[l] = ctx->lane_streams[l - 1];
+                STEREO_CUDA_CHECK(cudaStreamWaitEvent(lane_stream[l], ctx->ev_fork, 0));
+            }
+            for (int l = 1; l < lanes; ++l) {
+                cudaStream_t saved = ctx->stream;
+                ctx->stream = lane_stream[l];                   // the first-use memset of the margins goes to the lane
+                int rc = ensure_planar(ctx, 1, h, w, D, &pf[l], l);
+                ctx->stream = saved;
+                STEREO_TRY(rc);
+            }
         }
     }
     struct LaneStream {                      // launches go to ctx->stream: point it at the lane's stream
@@ -281,7 +292,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
         ~LaneStream() { ctx->stream = saved; }
     };
     for (int i = 0; i < n; ++i) {
-        const int lane = lanes == 2 ? (i & 1) : 0;
+        const int lane = i % lanes;
         LaneStream on_lane(ctx, lane_stream[lane]);
         // left and right of one pair go through the trunk as a batch of two
         if (!tc_corr) {
@@ -309,9 +320,9 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
                                 right_disp + i * map));
         }
     }
-    if (lanes == 2) {
-        STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->aux_stream));
-        STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    for (int l = 1; l < lanes; ++l) {
+        STEREO_CUDA_CHECK(cudaEventRecord(ctx->lane_join[l - 1], lane_stream[l]));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->lane_join[l - 1], 0));
     }
     if (lr_outlier) STEREO_TRY(launch_lr_check(ctx, left_disp, right_disp, n, h, w, D, lr_outlier));
     return STEREO_OK;
@@ -389,7 +400,8 @@ int stereo_destroy(stereo_ctx *ctx)
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
                       &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2], &ctx->post_vol[3], &ctx->post_vol[4], &ctx->post_vol[5], &ctx->post_vol[6], &ctx->post_vol[7],
                       &ctx->post_cnt[0], &ctx->post_cnt[1],
-                      &ctx->post_maps, &ctx->featp, &ctx->featp_b, &ctx->act_b[0], &ctx->act_b[1]};
+                      &ctx->post_maps, &ctx->featp, &ctx->featp_b[0], &ctx->featp_b[1], &ctx->featp_b[2], &ctx->act_b[0],
+                      &ctx->act_b[1], &ctx->act_b[2], &ctx->act_b[3], &ctx->act_b[4], &ctx->act_b[5]};
     for (DevBuf *b : bufs) b->release();
     if (ctx->prof.start) {
         for (int i = 0; i < Profiler::kMaxPairs; ++i) {
@@ -406,6 +418,10 @@ int stereo_destroy(stereo_ctx *ctx)
     for (int i = 0; i < 16; ++i) {
         if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
         if (ctx->ev_out[i]) cudaEventDestroy(ctx->ev_out[i]);
+    }
+    for (int i = 0; i < 3; ++i) {
+        if (ctx->lane_join[i]) cudaEventDestroy(ctx->lane_join[i]);
+        if (ctx->lane_streams[i]) cudaStreamDestroy(ctx->lane_streams[i]);
     }
     if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
     if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);

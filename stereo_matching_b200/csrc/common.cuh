@@ -98,7 +98,7 @@ struct stereo_ctx {
     stereo::DevBuf stats;        // per-image u64 sums + 256-entry LUTs
     stereo::DevBuf padded;       // normalised, padded images
     stereo::DevBuf act[2];       // ping-pong activations
-    stereo::DevBuf act_b[2];     // the same for the second lane of stereo_pairs (pairs alternate between two streams)
+    stereo::DevBuf act_b[6];     // the same for lanes 1..3 of stereo_pairs (pairs alternate between streams)
     stereo::DevBuf feat;         // trunk outputs of one pair
     stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
     stereo::DevBuf stage_out[3];
@@ -106,8 +106,10 @@ struct stereo_ctx {
     stereo::Conv1Weights conv1_host;   // host copy of the ws9 first layer (kernel-parameter weights)
     stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
     int featp_geom[5] = {0, 0, 0, 0, 0};
-    stereo::DevBuf featp_b;      // second lane
-    int featp_b_geom[5] = {0, 0, 0, 0, 0};
+    stereo::DevBuf featp_b[3];   // lanes 1..3
+    int featp_b_geom[3][5] = {};
+    cudaStream_t lane_streams[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t lane_join[3] = {nullptr, nullptr, nullptr};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
     stereo::DevBuf post_vol[8];  // working volumes of the post chain: 4 per side (the sides run on two streams)
     stereo::DevBuf post_cnt[2];  // row-segment lengths of the separable CBCA (uint8 per voxel), per side
