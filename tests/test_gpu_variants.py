@@ -1,0 +1,76 @@
+"""Every selectable kernel variant of the fused path against the oracle.
+
+The library picks its kernels once per process from environment variables (STEREO_CONV_KERNEL,
+STEREO_CONV1_KERNEL, STEREO_CORR_KERNEL, STEREO_PAIR_LANES), so each variant runs in
+its own interpreter: a batch of three synthetic pairs through `stereo_pairs` (fused correlation + WTA,
+LR check), maps written to an .npz.  Gates as in test_gpu_inference.py: >= 99.9 % of the WTA pixels
+equal to the float64 oracle's, LR labels consistent with the maps.
+"""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import post_oracle as po
+from oracle import stereo_oracle as so
+from stereo_matching_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+H, W, D, N = 96, 400, 64, 3
+WTA_AGREE = 0.999
+
+CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib, checkpoint, synth
+from stereo_matching_b200.models.model import base_model_ws_9
+H, W, D, N = (int(v) for v in sys.argv[3:7])
+m = base_model_ws_9((None, None, 3))
+m.set_layers(checkpoint.load_net_weights(os.path.join(sys.argv[1], "tests", "golden", "new_checkpoint")))
+pairs = [synth.make_pair(2000 + i, H, W, D) for i in range(N)]
+left = np.stack([p[0] for p in pairs]); right = np.stack([p[1] for p in pairs])
+out = m.context.pairs(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3, volumes=False, lr_check=True)
+np.savez(sys.argv[2], left=out["left_disp"], right=out["right_disp"], lr=out["outlier"])
+"""
+
+VARIANTS = [
+    {},                                       # defaults: conv_tc3, conv1_tc, corr_sweep, two lanes
+    {"STEREO_CONV_KERNEL": "1"},
+    {"STEREO_CONV_KERNEL": "2"},
+    {"STEREO_CONV1_KERNEL": "1"},
+    {"STEREO_CORR_KERNEL": "1"},
+    {"STEREO_CORR_KERNEL": "3"},
+    {"STEREO_PAIR_LANES": "1"},
+    {"STEREO_PAIR_LANES": "4"},
+]
+
+
+@pytest.fixture(scope="module")
+def reference_maps(ws9_layers):
+    refs = []
+    for i in range(N):
+        l, r, _ = synth.make_pair(2000 + i, H, W, D)
+        refs.append(so.infer_pair(l, r, ws9_layers, "win9_dep9", 9, D, np.float64))
+    return refs
+
+
+@pytest.mark.parametrize("env", VARIANTS, ids=lambda e: ",".join(f"{k[7:]}={v}" for k, v in e.items()) or "default")
+def test_variant_matches_oracle(env, reference_maps, tmp_path):
+    out = tmp_path / "maps.npz"
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, "-c", CHILD, ROOT, str(out), str(H), str(W), str(D), str(N)], env=e,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = np.load(out)
+    for i, ref in enumerate(reference_maps):
+        assert (got["left"][i] == ref["left_disp"]).mean() >= WTA_AGREE
+        assert (got["right"][i] == ref["right_disp"]).mean() >= WTA_AGREE
+        # the labels are an exact integer function of the two maps the same call returned
+        lab = po.outlier_detection(got["left"][i].astype(np.float32), got["right"][i].astype(np.float32), D)
+        assert np.array_equal(got["lr"][i], lab.astype(np.uint8))
