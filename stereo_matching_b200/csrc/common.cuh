@@ -167,7 +167,8 @@ int corr_sweep2_row_cols(int w);
 int launch_corr_sweep2(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                        int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
-                      int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
+                      int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
+                      uint8_t *left_disp, uint8_t *right_disp);
 size_t tc3_weight_image_elems();
 int launch_weight_images3(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv_tc3(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,

@@ -31,14 +31,22 @@ constexpr int kBlk = 128;                       // pixels per block
 constexpr int kRun = kBlk * 16;                 // one channel chunk: 2 KB
 constexpr int kPlane = 8 * kRun;                // 16 KB
 constexpr int kBlock = 2 * kPlane;              // hi + lo: 32 KB
-constexpr int kASlots = 3, kBSlots = 4, kAccBlocks = 4;
-constexpr int kSmemA = 0;
-constexpr int kSmemB = kSmemA + kASlots * kBlock;
-constexpr int kSmemWtaV = kSmemB + kBSlots * kBlock;         // [3 parts][128] best value of column parts 1-3
-constexpr int kSmemWtaD = kSmemWtaV + 3 * 128 * 4;           // [3 parts][128] its disparity (16 bit)
-constexpr int kSmemBars = kSmemWtaD + 3 * 128 * 2;
-constexpr int kSmemTotal = kSmemBars + 256;
-static_assert(kSmemTotal <= 232448, "shared memory budget of one CTA");
+constexpr int kBSlots = 4, kAccBlocks = 4;
+constexpr int kStageRows = 8, kStagePitch = 36;  // materialising epilogue: [8 rows][32 + 4] floats per warp
+// Shared-memory layout.  The materialising variant gives up one of the three own-block slots for the
+// staging buffers in which the epilogue warps transpose 8x32 blocks before they store them.
+template <bool VOL>
+struct Layout {
+    static constexpr int kASlots = VOL ? 2 : 3;
+    static constexpr int kA = 0;
+    static constexpr int kB = kA + kASlots * kBlock;
+    static constexpr int kWtaV = kB + kBSlots * kBlock;          // [3 parts][128] best value of column parts 1-3
+    static constexpr int kWtaD = kWtaV + 3 * 128 * 4;            // [3 parts][128] its disparity (16 bit)
+    static constexpr int kStage = kWtaD + 3 * 128 * 2;
+    static constexpr int kBars = kStage + (VOL ? 16 * kStageRows * kStagePitch * 4 : 0);
+    static constexpr int kTotal = kBars + 256;
+    static_assert(kTotal <= 232448, "shared memory budget of one CTA");
+};
 constexpr int kEpiWarps = 16;
 constexpr int kThreads = 128 + 32 * kEpiWarps;
 constexpr uint32_t kTmemCols = 512;
@@ -47,7 +55,8 @@ constexpr int kMargin = 256;                    // zero columns the feature rows
 struct Params {
     const __nv_bfloat16 *l_hi, *l_lo, *r_hi, *r_lo;   // [n][h][8][wf][8], pixel x at column ml + x
     int n, h, w, wf, ml, D, planes;
-    uint8_t *left_disp, *right_disp;                   // [n][h][w]
+    uint8_t *left_disp, *right_disp;                   // [n][h][w] or null
+    float *left_vol, *right_vol;                       // [n][h][w][D] or null
     int nb, tps, segs, nitems;                         // blocks per row, tiles per segment, segments per row
 };
 
@@ -71,19 +80,22 @@ __device__ __forceinline__ Item decode(const Params &p, int item)
     return it;
 }
 
+template <bool VOL, bool WTA>
 __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
 {
+    using L = Layout<VOL>;
+    constexpr int kASlots = L::kASlots;
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t s_base = tc::smem_u32(smem);
-    const uint32_t s_a = s_base + kSmemA, s_b = s_base + kSmemB;
-    const uint32_t bar_a_full = s_base + kSmemBars;          // [3]
+    const uint32_t s_a = s_base + L::kA, s_b = s_base + L::kB;
+    const uint32_t bar_a_full = s_base + L::kBars;          // [3]
     const uint32_t bar_a_empty = bar_a_full + 24;            // [3]
     const uint32_t bar_b_full = bar_a_full + 48;             // [4]
     const uint32_t bar_b_empty = bar_a_full + 80;            // [4]
     const uint32_t bar_acc_full = bar_a_full + 112;          // [4]
     const uint32_t bar_acc_empty = bar_a_full + 144;         // [4]
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + kSmemBars + 176);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + L::kBars + 176);
 
     if (tid == 0) {
         for (int i = 0; i < kASlots; ++i) {
@@ -198,8 +210,9 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
         const int q = warp & 3, part = (warp - 4) >> 2;
         const int xi = q * 32 + lane;
         const int D = p.D;
-        float *wta_v = reinterpret_cast<float *>(smem + kSmemWtaV);
-        uint16_t *wta_d = reinterpret_cast<uint16_t *>(smem + kSmemWtaD);
+        float *wta_v = reinterpret_cast<float *>(smem + L::kWtaV);
+        uint16_t *wta_d = reinterpret_cast<uint16_t *>(smem + L::kWtaD);
+        float *stage = reinterpret_cast<float *>(smem + L::kStage) + (warp - 4) * kStageRows * kStagePitch;
         uint32_t T = 0, G = 0;
         for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
             const Item it = decode(p, item);
@@ -217,26 +230,61 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                     if (dlo + 62 >= 0 && dlo <= D - 1) {
                         uint32_t v[32];
                         tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
-                        if (it.side == 0) {
-                            // d falls as u rises, so ">=" keeps the lowest d among equals
-                            const int dbase = xi + kMargin - u0;
+                        if (WTA) {
+                            if (it.side == 0) {
+                                // d falls as u rises, so ">=" keeps the lowest d among equals
+                                const int dbase = xi + kMargin - u0;
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                const int d = dbase - i;
-                                const float f = __uint_as_float(v[i]);
-                                const bool take = (unsigned)d < (unsigned)D && f >= best;
-                                best = take ? f : best;
-                                best_d = take ? d : best_d;
+                                for (int i = 0; i < 32; ++i) {
+                                    const int d = dbase - i;
+                                    const float f = __uint_as_float(v[i]);
+                                    const bool take = (unsigned)d < (unsigned)D && f >= best;
+                                    best = take ? f : best;
+                                    best_d = take ? d : best_d;
+                                }
+                            } else {
+                                const int dbase = u0 - xi;
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) {
+                                    const int d = dbase + i;
+                                    const float f = __uint_as_float(v[i]);
+                                    const bool take = (unsigned)d < (unsigned)D && f > best;
+                                    best = take ? f : best;
+                                    best_d = take ? d : best_d;
+                                }
                             }
-                        } else {
-                            const int dbase = u0 - xi;
+                        }
+                        if (VOL) {
+                            // Eight rows at a time go through the warp's staging block, so that every warp store
+                            // is one 128-byte run of a [x][d] output row: row r of the chunk is pixel
+                            // x0 + 32q + r, its column j is disparity d00 + r - j (left) or d00 - r + j (right).
+                            float *vol = it.side == 0 ? p.left_vol : p.right_vol;
+                            float *rowbase = vol + (((size_t)it.img * p.h + it.y) * p.w) * (size_t)D;
+                            const int xq = kBlk * k + q * 32;
+                            const int dstep = it.side == 0 ? 1 : -1;
+                            const int stride = D + dstep;                   // 32-bit offsets: a row of a volume is < 2^31 floats
+                            int dd = it.side == 0 ? q * 32 + kMargin - (u0 + lane) : (u0 + lane) - q * 32;   // row 0
+                            int off = xq * D + dd;
+                            const int rows_ok = min(32, p.w - xq);
+#pragma unroll 1
+                            for (int r0 = 0; r0 < 32; r0 += kStageRows) {
+                                if (lane >= r0 && lane < r0 + kStageRows) {
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                const int d = dbase + i;
-                                const float f = __uint_as_float(v[i]);
-                                const bool take = (unsigned)d < (unsigned)D && f > best;
-                                best = take ? f : best;
-                                best_d = take ? d : best_d;
+                                    for (int i = 0; i < 8; ++i)
+                                        reinterpret_cast<uint4 *>(stage + (lane - r0) * kStagePitch)[i] =
+                                            make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                                }
+                                __syncwarp();
+                                float t[kStageRows];
+#pragma unroll
+                                for (int j = 0; j < kStageRows; ++j) t[j] = stage[j * kStagePitch + lane];
+#pragma unroll
+                                for (int j = 0; j < kStageRows; ++j) {
+                                    if (r0 + j < rows_ok && (unsigned)dd < (unsigned)D) rowbase[off] = t[j];
+                                    off += stride;
+                                    dd += dstep;
+                                }
+                                __syncwarp();
                             }
                         }
                     }
@@ -244,6 +292,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                     __syncwarp();
                     if (lane == 0) tc::mbar_arrive(bar_acc_empty + 8 * ab);
                 }
+                if (!WTA) continue;
                 // merge the four column parts of each row: larger value wins, equal values -> lower disparity.
                 // Barrier 1: parts 1-3 have written; barrier 2: part 0 has read (so the buffer can be rewritten).
                 if (part != 0) {
@@ -267,7 +316,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                 }
             }
         }
-        if (part != 0 && T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        if (WTA && part != 0 && T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
     }
 
     tc::tc_fence_before();
@@ -283,7 +332,8 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
 int corr_sweep_margin() { return tcs::kMargin; }
 
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
-                      int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp)
+                      int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
+                      uint8_t *left_disp, uint8_t *right_disp)
 {
     const int nb = (w + tcs::kBlk - 1) / tcs::kBlk;
     STEREO_REQUIRE(D >= 1 && D - 1 <= tcs::kMargin, "row-sweep correlation supports disp_range <= %d, got %d",
@@ -296,6 +346,7 @@ int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const
     p.r_lo = static_cast<const __nv_bfloat16 *>(r_lo);
     p.n = n; p.h = h; p.w = w; p.wf = wf; p.ml = ml; p.D = D; p.planes = planes;
     p.left_disp = left_disp; p.right_disp = right_disp;
+    p.left_vol = left_vol; p.right_vol = right_vol;
     p.nb = nb;
     // rows may be cut into segments when that balances the persistent CTAs better: cost model =
     // rounds x (tiles per segment + half a tile of pipeline fill)
@@ -317,12 +368,18 @@ int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const
     p.segs = (nb + p.tps - 1) / p.tps;
     p.nitems = rows * p.segs;
     const int grid = p.nitems < ctx->sm_count ? p.nitems : ctx->sm_count;
-    STEREO_CUDA_CHECK(cudaFuncSetAttribute(tcs::corr_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           tcs::kSmemTotal));
-    ProfScope prof(ctx, STEREO_K_CORR);
-    tcs::corr_sweep_kernel<<<grid, tcs::kThreads, tcs::kSmemTotal, ctx->stream>>>(p);
-    ctx->launches += 1;
-    STEREO_CUDA_CHECK(cudaGetLastError());
+    const bool vol = left_vol != nullptr, wta = left_disp != nullptr;
+    auto launch = [&](auto kern, int smem_bytes) -> int {
+        STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        ProfScope prof(ctx, STEREO_K_CORR);
+        kern<<<grid, tcs::kThreads, smem_bytes, ctx->stream>>>(p);
+        ctx->launches += 1;
+        STEREO_CUDA_CHECK(cudaGetLastError());
+        return STEREO_OK;
+    };
+    if (vol && wta) return launch(tcs::corr_sweep_kernel<true, true>, tcs::Layout<true>::kTotal);
+    if (vol) return launch(tcs::corr_sweep_kernel<true, false>, tcs::Layout<true>::kTotal);
+    STEREO_TRY(launch(tcs::corr_sweep_kernel<false, true>, tcs::Layout<false>::kTotal));
     return STEREO_OK;
 }
 

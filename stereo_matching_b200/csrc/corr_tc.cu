@@ -322,8 +322,9 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
     // (STEREO_CORR_KERNEL=3: CTA-pair row sweep, corr_sweep2.cu - measured slower so far, see DESIGN.md;
     //  default 2: single-CTA row sweep, corr_sweep.cu)
     static const int mode = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 2; }();
-    if (!vol && mode == 2 && ml >= corr_sweep_margin())
-        return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
+    if (mode == 2 && ml >= corr_sweep_margin())
+        return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_vol, right_vol, left_disp,
+                                 right_disp);
     if (!vol && mode == 3 && ml >= corr_sweep_margin() && wf >= ml + corr_sweep2_row_cols(w))
         return launch_corr_sweep2(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
     tcc::Params p;
