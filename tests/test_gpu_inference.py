@@ -331,3 +331,29 @@ def test_wta_vector_path_matches_numpy(ctx, D):
     vol[0, 0, 1, D // 3] = vol[0, 0, 1, D - 1] = 9.0        # tie -> lowest index
     assert np.array_equal(ctx.wta(vol), np.argmax(vol, axis=3).astype(np.uint8))
     assert np.array_equal(ctx.wta(vol, take_min=True), np.argmin(vol, axis=3).astype(np.uint8))
+
+
+@pytest.mark.parametrize("h,w,D", [(374, 1238, 201), (376, 1241, 228), (375, 1242, 201)])
+def test_kitti_sizes_tensor_core(ctx, ws9, h, w, D):
+    """The three image sizes of the shipped results (K8), reference-default and benchmark disparity ranges,
+    through the tensor-core kernels: band symmetry, exact zero fill, fused WTA == WTA of the materialised
+    volume, and the float64 oracle on a strip of rows."""
+    l, r, gt = synth.make_pair(3000 + h, h, w, D)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    lv, rv = out["left_cost"][0], out["right_cost"][0]
+    for d in (0, 1, D // 2, D - 1):
+        assert np.array_equal(lv[:, d:, d], rv[:, :w - d, d])
+        assert np.all(lv[:, :d, d] == 0) and np.all(rv[:, w - d:, d] == 0)
+    assert np.array_equal(out["left_disp"][0], np.argmax(lv, axis=2).astype(np.uint8))
+    assert np.array_equal(out["right_disp"][0], np.argmax(rv, axis=2).astype(np.uint8))
+    fused = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=False)
+    assert np.array_equal(fused["left_disp"], out["left_disp"]) and np.array_equal(fused["right_disp"], out["right_disp"])
+    lab = po.outlier_detection(fused["left_disp"][0].astype(np.float32), fused["right_disp"][0].astype(np.float32), D)
+    assert np.array_equal(fused["outlier"][0], lab.astype(np.uint8))
+    y0 = h - 8                                   # the last 8 rows: bottom padding included
+    lp, rp = so.normalize_and_pad(l, 9), so.normalize_and_pad(r, 9)
+    lm = so.trunk_forward(lp[:, y0:y0 + 16], ws9.layers, "win9_dep9", np.float64)
+    rm = so.trunk_forward(rp[:, y0:y0 + 16], ws9.layers, "win9_dep9", np.float64)
+    lref, rref = so.cost_volumes(lm, rm, D, np.float64)
+    assert rel_err(lv[y0:], lref) < COST_TOL and rel_err(rv[y0:], rref) < COST_TOL
+    assert (out["left_disp"][0][y0:] == so.wta(lref)).mean() >= WTA_AGREE
