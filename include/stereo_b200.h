@@ -229,6 +229,35 @@ int stereo_profile_enable(stereo_ctx *ctx, int on);
 int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches);
 const char *stereo_profile_name(int kernel_class);
 
+/* ---------------------------------------------------------------------------------------------
+ * Patch training.  Replaces the body of the training loop of
+ * /root/reference/train.py:92-112: model(lpatch, training=True), model(rpatch, training=True),
+ * map_inner_product (train.py:11-17), softmax cross-entropy (train.py:106), tape.gradient and
+ * optimizer.apply_gradients with tf.keras.optimizers.Adam (train.py:80,109-112).
+ * Parameters are one flat fp32 array in the order of Keras' trainable_variables: per layer kernel
+ * [k][k][Cin][Cout], bias, gamma, beta; the moving statistics (mean, variance per layer) are a second
+ * array.  A trainer belongs to the context it was created on and uses its stream.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct stereo_trainer stereo_trainer;
+int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, stereo_trainer **out);
+int stereo_train_destroy(stereo_trainer *tr);
+size_t stereo_train_param_count(const stereo_trainer *tr);
+size_t stereo_train_stat_count(const stereo_trainer *tr);
+int stereo_train_patch_size(const stereo_trainer *tr);
+/* host arrays; adam_m / adam_v may be null (zeros) */
+int stereo_train_set_state(stereo_trainer *tr, const float *params, const float *stats, const float *adam_m,
+                           const float *adam_v, long long step);
+int stereo_train_get_state(stereo_trainer *tr, float *params, float *stats, float *adam_m, float *adam_v,
+                           long long *step);
+/* left [B][p][p][3], right [B][p][p+D-1][3], targets [B][D]: host fp32.  loss = batch mean; correct3 = number of
+ * patches with |argmax(logits) - argmax(targets)| <= 3 (train.py:117-119); grads_out (host, may be null). */
+int stereo_train_forward_backward(stereo_trainer *tr, const float *left, const float *right, const float *targets,
+                                  float *loss, int *correct3, float *grads_out);
+/* device address of the flat gradient array, for an in-place all-reduce between ranks */
+int stereo_train_grads_dev(stereo_trainer *tr, float **grads);
+/* one Adam step with the stored gradients (or grads_dev, a device array, if not null) */
+int stereo_train_apply(stereo_trainer *tr, const float *grads_dev, float lr);
+
 #ifdef __cplusplus
 }
 #endif

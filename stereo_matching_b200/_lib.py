@@ -75,9 +75,20 @@ SIGNATURES = {
     "stereo_profile_enable": [_c_ctx, _i],
     "stereo_profile_read": [_c_ctx, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
     "stereo_profile_name": [_i],
+    "stereo_train_create": [_c_ctx, _i, _i, _i, ctypes.POINTER(ctypes.c_void_p)],
+    "stereo_train_destroy": [_p],
+    "stereo_train_param_count": [_p],
+    "stereo_train_stat_count": [_p],
+    "stereo_train_patch_size": [_p],
+    "stereo_train_set_state": [_p, _p, _p, _p, _p, ctypes.c_longlong],
+    "stereo_train_get_state": [_p, _p, _p, _p, _p, ctypes.POINTER(ctypes.c_longlong)],
+    "stereo_train_forward_backward": [_p, _p, _p, _p, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(_i), _p],
+    "stereo_train_grads_dev": [_p, ctypes.POINTER(ctypes.c_void_p)],
+    "stereo_train_apply": [_p, _p, ctypes.c_float],
 }
 _RESTYPES = {"stereo_last_error": ctypes.c_char_p, "stereo_launch_count": ctypes.c_int64,
-             "stereo_profile_name": ctypes.c_char_p}
+             "stereo_profile_name": ctypes.c_char_p,
+             "stereo_train_param_count": ctypes.c_size_t, "stereo_train_stat_count": ctypes.c_size_t}
 KERNEL_CLASSES = 10
 
 _lib = None
@@ -361,3 +372,69 @@ class Context:
 
     def lr_check_dev(self, d0, d1, n, h, w, disp_range, outlier):
         check(self._lib.stereo_lr_check_dev(self._h, _ptr(d0), _ptr(d1), n, h, w, int(disp_range), _ptr(outlier)))
+
+
+class Trainer:
+    """One `stereo_trainer`: patch training of a trunk on the context's GPU (reference train.py:92-112).
+
+    `params` / `stats` are flat float32 arrays: per layer kernel [k][k][Cin][Cout], bias, gamma, beta
+    (Keras' trainable_variables order), and per layer moving mean, moving variance."""
+
+    def __init__(self, ctx: "Context", net: int, batch: int, disp_range: int):
+        self._lib = load()
+        self.ctx = ctx
+        h = ctypes.c_void_p()
+        check(self._lib.stereo_train_create(ctx._h, int(net), int(batch), int(disp_range), ctypes.byref(h)))
+        self._h = h
+        self.batch, self.disp_range = int(batch), int(disp_range)
+        self.n_params = int(self._lib.stereo_train_param_count(h))
+        self.n_stats = int(self._lib.stereo_train_stat_count(h))
+        self.patch = int(self._lib.stereo_train_patch_size(h))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.stereo_train_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_state(self, params, stats, adam_m=None, adam_v=None, step: int = 0):
+        params, stats = _arr(params, np.float32), _arr(stats, np.float32)
+        if params.size != self.n_params or stats.size != self.n_stats:
+            raise ValueError(f"expected {self.n_params} parameters and {self.n_stats} statistics")
+        m = None if adam_m is None else _arr(adam_m, np.float32)
+        v = None if adam_v is None else _arr(adam_v, np.float32)
+        check(self._lib.stereo_train_set_state(self._h, params.ctypes.data, stats.ctypes.data, _ptr(m), _ptr(v), int(step)))
+
+    def get_state(self):
+        out = {"params": np.empty(self.n_params, np.float32), "stats": np.empty(self.n_stats, np.float32),
+               "adam_m": np.empty(self.n_params, np.float32), "adam_v": np.empty(self.n_params, np.float32)}
+        step = ctypes.c_longlong(0)
+        check(self._lib.stereo_train_get_state(self._h, out["params"].ctypes.data, out["stats"].ctypes.data,
+                                               out["adam_m"].ctypes.data, out["adam_v"].ctypes.data, ctypes.byref(step)))
+        out["step"] = int(step.value)
+        return out
+
+    def forward_backward(self, left, right, targets, want_grads: bool = False):
+        left, right, targets = _arr(left, np.float32), _arr(right, np.float32), _arr(targets, np.float32)
+        p, B, D = self.patch, self.batch, self.disp_range
+        if left.shape != (B, p, p, 3) or right.shape != (B, p, p + D - 1, 3) or targets.shape != (B, D):
+            raise ValueError(f"expected left {(B, p, p, 3)}, right {(B, p, p + D - 1, 3)}, targets {(B, D)}")
+        loss, correct = ctypes.c_float(0), ctypes.c_int(0)
+        grads = np.empty(self.n_params, np.float32) if want_grads else None
+        check(self._lib.stereo_train_forward_backward(self._h, left.ctypes.data, right.ctypes.data, targets.ctypes.data,
+                                                      ctypes.byref(loss), ctypes.byref(correct), _ptr(grads)))
+        return float(loss.value), int(correct.value), grads
+
+    def grads_dev(self) -> int:
+        """Device address of the flat gradient array (for an in-place all-reduce)."""
+        ptr = ctypes.c_void_p()
+        check(self._lib.stereo_train_grads_dev(self._h, ctypes.byref(ptr)))
+        return int(ptr.value)
+
+    def apply(self, lr: float, grads_dev=None):
+        check(self._lib.stereo_train_apply(self._h, _ptr(grads_dev), float(lr)))

@@ -1,0 +1,612 @@
+// Patch training of the Siamese trunk on the device (/root/reference/train.py:92-112, models/model.py,
+// data_handler.py:75-85): forward of both towers in training mode (conv 'valid' -> ReLU -> BatchNorm
+// with batch statistics), inner product of the left feature with the D right features, softmax
+// cross-entropy against the soft 5-tap labels, backward through both towers (shared weights, gradients
+// summed), Adam.  SURVEY.md section 8(f) rank 1.
+//
+// Everything is fp32 on the CUDA cores: the tensors are small (B = 128 patches of 9 x 9 and 9 x 209) and
+// the step is latency-, not throughput-bound; channel reductions (BatchNorm statistics, weight gradients)
+// accumulate in double.  The gradient buffer is one flat device array in the order of Keras'
+// `trainable_variables` (per layer: kernel [k][k][Cin][Cout], bias, gamma, beta), so that data-parallel
+// training is ONE all-reduce over it (113 088 floats for base_model_ws_9).
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+
+namespace stereo {
+
+constexpr float kBnEps = 1e-3f;        // Keras BatchNormalization default (models/model.py)
+constexpr float kBnMomentum = 0.99f;   // Keras default
+
+struct TrainLayer {
+    int ks, cin, cout, relu;
+    size_t w_off, b_off, g_off, be_off;     // offsets into the flat parameter / gradient arrays
+    size_t mean_off, var_off;               // offsets into the moving statistics
+};
+
+// activations of one tower that the backward pass needs
+struct Tower {
+    DevBuf x[kMaxLayers + 1];      // x[l] = input of layer l (x[0] = patches), x[L] = features
+    DevBuf a[kMaxLayers];          // conv + bias (+ ReLU) output, before BatchNorm
+    DevBuf bn[kMaxLayers];         // per channel: batch mean, inverse std  (2 * cout floats)
+    int h[kMaxLayers + 1], w[kMaxLayers + 1];
+};
+
+}  // namespace stereo
+
+struct stereo_trainer {
+    stereo_ctx *ctx = nullptr;
+    int net = 0, batch = 0, D = 0, patch = 0, n_layers = 0;
+    stereo::TrainLayer layer[stereo::kMaxLayers];
+    size_t n_params = 0, n_stats = 0;
+    stereo::DevBuf params, grads, adam_m, adam_v, stats;
+    stereo::DevBuf red;            // double scratch for reductions (>= max(n_params, 4 * 64))
+    stereo::DevBuf d_act[2];       // ping-pong gradient wrt activations
+    stereo::DevBuf logits, dlogits, loss_buf, targets;
+    stereo::DevBuf dfeat[2];       // gradient wrt the left / right feature tensors
+    stereo::Tower tower[2];
+    long long step = 0;
+};
+
+namespace stereo {
+
+// ------------------------------------------------------------------------------------------
+// forward kernels
+// ------------------------------------------------------------------------------------------
+// out[p][co] = bias[co] + sum_{ky,kx,ci} in[(y+ky, x+kx)][ci] * w[ky][kx][ci][co]   (+ ReLU)
+__global__ void train_conv_fwd_kernel(const float *__restrict__ in, const float *__restrict__ w,
+                                      const float *__restrict__ bias, int n, int h, int wd, int ks, int cin, int cout,
+                                      int relu, float *__restrict__ out)
+{
+    const int ho = h - ks + 1, wo = wd - ks + 1;
+    const size_t total = (size_t)n * ho * wo * cout;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int co = (int)(i % cout);
+        size_t p = i / cout;
+        const int x = (int)(p % wo);
+        p /= wo;
+        const int y = (int)(p % ho), b = (int)(p / ho);
+        float acc = bias[co];
+        for (int ky = 0; ky < ks; ++ky)
+            for (int kx = 0; kx < ks; ++kx) {
+                const float *ip = in + (((size_t)b * h + y + ky) * wd + x + kx) * cin;
+                const float *wp = w + ((size_t)(ky * ks + kx) * cin) * cout + co;
+                for (int ci = 0; ci < cin; ++ci) acc = fmaf(ip[ci], wp[(size_t)ci * cout], acc);
+            }
+        out[i] = relu ? fmaxf(acc, 0.f) : acc;
+    }
+}
+
+// per-channel sum and sum of squares (double) of a [m][c] array; red[0..c) += sum, red[c..2c) += sumsq
+__global__ void train_channel_moments_kernel(const float *__restrict__ a, size_t m, int c, double *__restrict__ red)
+{
+    // blockDim.x = c * rows_per_block; thread (r, ch)
+    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
+    double s = 0.0, ss = 0.0;
+    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) {
+        const double v = (double)a[p * c + ch];
+        s += v;
+        ss += v * v;
+    }
+    atomicAdd(red + ch, s);
+    atomicAdd(red + c + ch, ss);
+}
+
+// batch mean / biased variance -> (mean, invstd); moving statistics as Keras updates them
+__global__ void train_bn_finalize_kernel(const double *__restrict__ red, double m, int c, float *__restrict__ bn,
+                                         float *__restrict__ moving_mean, float *__restrict__ moving_var)
+{
+    const int ch = threadIdx.x;
+    if (ch >= c) return;
+    const double mean = red[ch] / m;
+    double var = red[c + ch] / m - mean * mean;
+    if (var < 0.0) var = 0.0;
+    bn[ch] = (float)mean;
+    bn[c + ch] = (float)(1.0 / sqrt(var + (double)kBnEps));
+    moving_mean[ch] = moving_mean[ch] * kBnMomentum + (float)mean * (1.f - kBnMomentum);
+    moving_var[ch] = moving_var[ch] * kBnMomentum + (float)var * (1.f - kBnMomentum);
+}
+
+__global__ void train_bn_apply_kernel(const float *__restrict__ a, size_t total, int c, const float *__restrict__ bn,
+                                      const float *__restrict__ gamma, const float *__restrict__ beta,
+                                      float *__restrict__ y)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int ch = (int)(i % c);
+        y[i] = gamma[ch] * ((a[i] - bn[ch]) * bn[c + ch]) + beta[ch];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// loss: logits[b][d] = <L[b], R[b][d]>, softmax cross-entropy with soft labels (train.py:11-17,106)
+// one block per patch pair; writes dlogits = (softmax - t) / B, loss_b, |argmax - argmax(t)| <= 3
+// ------------------------------------------------------------------------------------------
+__global__ void train_loss_kernel(const float *__restrict__ lf, const float *__restrict__ rf,
+                                  const float *__restrict__ targets, int D, int c, int batch,
+                                  float *__restrict__ logits, float *__restrict__ dlogits, float *__restrict__ loss_out)
+{
+    extern __shared__ float sh[];        // [D] logits, then reduction scratch
+    float *lg = sh, *scr = sh + ((D + 1) & ~1);      // 8-byte aligned: reused as double scratch
+    const int b = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const float *l = lf + (size_t)b * c;
+    for (int d = tid; d < D; d += nt) {
+        const float *r = rf + ((size_t)b * D + d) * c;
+        float acc = 0.f;
+        for (int k = 0; k < c; ++k) acc = fmaf(l[k], r[k], acc);
+        lg[d] = acc;
+        logits[(size_t)b * D + d] = acc;
+    }
+    __syncthreads();
+    // max, argmax (lowest index), label argmax
+    float mx = -INFINITY;
+    int am = 0x7fffffff;
+    float tmx = -INFINITY;
+    int tam = 0x7fffffff;
+    for (int d = tid; d < D; d += nt) {
+        if (lg[d] > mx) { mx = lg[d]; am = d; }
+        const float t = targets[(size_t)b * D + d];
+        if (t > tmx) { tmx = t; tam = d; }
+    }
+    float *s_v = scr, *s_t = scr + nt;
+    int *s_i = reinterpret_cast<int *>(scr + 2 * nt), *s_ti = reinterpret_cast<int *>(scr + 3 * nt);
+    s_v[tid] = mx; s_i[tid] = am; s_t[tid] = tmx; s_ti[tid] = tam;
+    __syncthreads();
+    for (int o = nt / 2; o > 0; o >>= 1) {
+        if (tid < o) {
+            if (s_v[tid + o] > s_v[tid] || (s_v[tid + o] == s_v[tid] && s_i[tid + o] < s_i[tid])) { s_v[tid] = s_v[tid + o]; s_i[tid] = s_i[tid + o]; }
+            if (s_t[tid + o] > s_t[tid] || (s_t[tid + o] == s_t[tid] && s_ti[tid + o] < s_ti[tid])) { s_t[tid] = s_t[tid + o]; s_ti[tid] = s_ti[tid + o]; }
+        }
+        __syncthreads();
+    }
+    mx = s_v[0];
+    const int pred = s_i[0], label = s_ti[0];
+    __syncthreads();
+    // sum of exp, sum of t * (x - max)
+    double se = 0.0, st = 0.0, tsum = 0.0;
+    for (int d = tid; d < D; d += nt) {
+        const float z = lg[d] - mx;
+        se += exp((double)z);
+        const double t = (double)targets[(size_t)b * D + d];
+        st += t * (double)z;
+        tsum += t;
+    }
+    double *s_d = reinterpret_cast<double *>(scr);
+    s_d[tid] = se; s_d[nt + tid] = st; s_d[2 * nt + tid] = tsum;
+    __syncthreads();
+    for (int o = nt / 2; o > 0; o >>= 1) {
+        if (tid < o) { s_d[tid] += s_d[tid + o]; s_d[nt + tid] += s_d[nt + tid + o]; s_d[2 * nt + tid] += s_d[2 * nt + tid + o]; }
+        __syncthreads();
+    }
+    se = s_d[0]; st = s_d[nt]; tsum = s_d[2 * nt];
+    const double lse = log(se);
+    for (int d = tid; d < D; d += nt) {
+        const double sm = exp((double)(lg[d] - mx)) / se;
+        dlogits[(size_t)b * D + d] = (float)((sm * tsum - (double)targets[(size_t)b * D + d]) / (double)batch);
+    }
+    if (tid == 0) {
+        loss_out[2 * b] = (float)(tsum * lse - st);                // -sum t * log softmax
+        loss_out[2 * b + 1] = abs(pred - label) <= 3 ? 1.f : 0.f;  // train.py:117-119
+    }
+}
+
+// dL[b][k] = sum_d dlogits[b][d] * R[b][d][k];  dR[b][d][k] = dlogits[b][d] * L[b][k]
+__global__ void train_loss_bwd_kernel(const float *__restrict__ lf, const float *__restrict__ rf,
+                                      const float *__restrict__ dlogits, int D, int c, float *__restrict__ dl,
+                                      float *__restrict__ dr)
+{
+    const int b = blockIdx.x, k = threadIdx.x;
+    if (k >= c) return;
+    const float lk = lf[(size_t)b * c + k];
+    float acc = 0.f;
+    for (int d = 0; d < D; ++d) {
+        const float g = dlogits[(size_t)b * D + d];
+        acc = fmaf(g, rf[((size_t)b * D + d) * c + k], acc);
+        dr[((size_t)b * D + d) * c + k] = g * lk;
+    }
+    dl[(size_t)b * c + k] = acc;
+}
+
+// ------------------------------------------------------------------------------------------
+// backward kernels
+// ------------------------------------------------------------------------------------------
+// BatchNorm backward, reduction part: red[ch] += sum dy, red[c + ch] += sum dy * xhat
+__global__ void train_bn_bwd_reduce_kernel(const float *__restrict__ dy, const float *__restrict__ a, size_t m, int c,
+                                           const float *__restrict__ bn, double *__restrict__ red)
+{
+    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
+    const float mean = bn[ch], invstd = bn[c + ch];
+    double s = 0.0, sx = 0.0;
+    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) {
+        const float g = dy[p * c + ch];
+        s += (double)g;
+        sx += (double)g * (double)((a[p * c + ch] - mean) * invstd);
+    }
+    atomicAdd(red + ch, s);
+    atomicAdd(red + c + ch, sx);
+}
+
+// dgamma += red[c + ch], dbeta += red[ch];
+// da = gamma * invstd * (dy - dbeta / M - xhat * dgamma / M), then through the ReLU (a > 0) if the layer has one
+__global__ void train_bn_bwd_apply_kernel(const float *__restrict__ dy, const float *__restrict__ a, size_t total, int c,
+                                          double m, const float *__restrict__ bn, const float *__restrict__ gamma,
+                                          const double *__restrict__ red, int relu, float *__restrict__ dz)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int ch = (int)(i % c);
+        const float av = a[i];
+        const float xhat = (av - bn[ch]) * bn[c + ch];
+        const float db = (float)(red[ch] / m), dg = (float)(red[c + ch] / m);
+        float g = gamma[ch] * bn[c + ch] * (dy[i] - db - xhat * dg);
+        if (relu && !(av > 0.f)) g = 0.f;
+        dz[i] = g;
+    }
+}
+
+__global__ void train_accumulate_kernel(const double *__restrict__ red, int n, float *__restrict__ dst)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += (float)red[i];
+}
+
+// dW[t][ci][co] += sum_p x[p + t][ci] * dz[p][co];  grid = (taps * cin, chunks), block = cout threads
+__global__ void train_conv_bwd_w_kernel(const float *__restrict__ x, const float *__restrict__ dz, int n, int h, int wd,
+                                        int ks, int cin, int cout, double *__restrict__ red_w)
+{
+    const int ho = h - ks + 1, wo = wd - ks + 1;
+    const int t = blockIdx.x / cin, ci = blockIdx.x % cin;
+    const int ky = t / ks, kx = t % ks, co = threadIdx.x;
+    const size_t m = (size_t)n * ho * wo;
+    const size_t chunk = (m + gridDim.y - 1) / gridDim.y;
+    const size_t p0 = (size_t)blockIdx.y * chunk, p1 = p0 + chunk < m ? p0 + chunk : m;
+    double acc = 0.0;
+    float part = 0.f;
+    int cnt = 0;
+    for (size_t p = p0; p < p1; ++p) {
+        const int xo = (int)(p % wo);
+        const size_t q = p / wo;
+        const int yo = (int)(q % ho), b = (int)(q / ho);
+        const float xv = x[(((size_t)b * h + yo + ky) * wd + xo + kx) * cin + ci];
+        part = fmaf(xv, dz[p * cout + co], part);
+        if (++cnt == 256) { acc += (double)part; part = 0.f; cnt = 0; }
+    }
+    acc += (double)part;
+    atomicAdd(red_w + ((size_t)t * cin + ci) * cout + co, acc);
+}
+
+// db[co] += sum_p dz[p][co]
+__global__ void train_bias_bwd_kernel(const float *__restrict__ dz, size_t m, int c, double *__restrict__ red)
+{
+    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
+    double s = 0.0;
+    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) s += (double)dz[p * c + ch];
+    atomicAdd(red + ch, s);
+}
+
+// dx[b][yy][xx][ci] = sum_{ky,kx,co} dz[b][yy - ky][xx - kx][co] * w[ky][kx][ci][co]
+__global__ void train_conv_bwd_x_kernel(const float *__restrict__ dz, const float *__restrict__ w, int n, int h, int wd,
+                                        int ks, int cin, int cout, float *__restrict__ dx)
+{
+    const int ho = h - ks + 1, wo = wd - ks + 1;
+    const size_t total = (size_t)n * h * wd * cin;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % cin);
+        size_t p = i / cin;
+        const int xx = (int)(p % wd);
+        p /= wd;
+        const int yy = (int)(p % h), b = (int)(p / h);
+        float acc = 0.f;
+        for (int ky = 0; ky < ks; ++ky) {
+            const int yo = yy - ky;
+            if (yo < 0 || yo >= ho) continue;
+            for (int kx = 0; kx < ks; ++kx) {
+                const int xo = xx - kx;
+                if (xo < 0 || xo >= wo) continue;
+                const float *g = dz + (((size_t)b * ho + yo) * wo + xo) * cout;
+                const float *wp = w + ((size_t)(ky * ks + kx) * cin + ci) * cout;
+                for (int co = 0; co < cout; ++co) acc = fmaf(g[co], wp[co], acc);
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
+// Adam as tf.keras.optimizers.Adam applies it (train.py:80,112): lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t)
+__global__ void train_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
+                                  float *__restrict__ v, size_t n, float lr_t, float b1, float b2, float eps)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= lr_t * mi / (sqrtf(vi) + eps);
+}
+
+__global__ void train_reduce_loss_kernel(const float *__restrict__ per_pair, int batch, float *__restrict__ out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double s = 0.0, c = 0.0;
+    for (int b = 0; b < batch; ++b) { s += (double)per_pair[2 * b]; c += (double)per_pair[2 * b + 1]; }
+    out[0] = (float)(s / batch);
+    out[1] = (float)c;
+}
+
+static inline unsigned grid_for(size_t total, int block, int cap)
+{
+    size_t g = (total + block - 1) / block;
+    return (unsigned)(g < 1 ? 1 : (g > (size_t)cap ? (size_t)cap : g));
+}
+
+// ------------------------------------------------------------------------------------------
+// one tower forward (training mode) and backward
+// ------------------------------------------------------------------------------------------
+static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, int h, int w)
+{
+    stereo_ctx *ctx = tr->ctx;
+    const float *P = tr->params.as<float>();
+    float *S = tr->stats.as<float>();
+    double *red = tr->red.as<double>();
+    const int n = tr->batch;
+    tw.h[0] = h; tw.w[0] = w;
+    const float *cur = patches;
+    for (int l = 0; l < tr->n_layers; ++l) {
+        const TrainLayer &L = tr->layer[l];
+        const int ho = tw.h[l] - L.ks + 1, wo = tw.w[l] - L.ks + 1;
+        tw.h[l + 1] = ho; tw.w[l + 1] = wo;
+        const size_t m = (size_t)n * ho * wo, total = m * L.cout;
+        STEREO_TRY(tw.a[l].reserve(total * sizeof(float)));
+        STEREO_TRY(tw.x[l + 1].reserve(total * sizeof(float)));
+        STEREO_TRY(tw.bn[l].reserve(2 * L.cout * sizeof(float)));
+        train_conv_fwd_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+            cur, P + L.w_off, P + L.b_off, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, L.relu, tw.a[l].as<float>());
+        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
+        const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
+        train_channel_moments_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(
+            tw.a[l].as<float>(), m, L.cout, red);
+        train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>(),
+                                                                S + L.mean_off, S + L.var_off);
+        train_bn_apply_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+            tw.a[l].as<float>(), total, L.cout, tw.bn[l].as<float>(), P + L.g_off, P + L.be_off, tw.x[l + 1].as<float>());
+        ctx->launches += 4;
+        cur = tw.x[l + 1].as<float>();
+    }
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// dfeat: gradient wrt the tower's output (same shape as x[L]); gradients are ADDED to tr->grads
+static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, const float *dfeat)
+{
+    stereo_ctx *ctx = tr->ctx;
+    const float *P = tr->params.as<float>();
+    float *G = tr->grads.as<float>();
+    double *red = tr->red.as<double>();
+    const int n = tr->batch;
+    const float *dy = dfeat;
+    for (int l = tr->n_layers - 1; l >= 0; --l) {
+        const TrainLayer &L = tr->layer[l];
+        const int ho = tw.h[l + 1], wo = tw.w[l + 1];
+        const size_t m = (size_t)n * ho * wo, total = m * L.cout;
+        const float *a = tw.a[l].as<float>();
+        const float *xin = l == 0 ? patches : tw.x[l].as<float>();
+        float *dz = tr->d_act[0].as<float>();                 // gradient wrt conv output (after the ReLU mask)
+        // BatchNorm: dgamma, dbeta, da
+        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
+        const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
+        train_bn_bwd_reduce_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(
+            dy, a, m, L.cout, tw.bn[l].as<float>(), red);
+        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red, L.cout, G + L.be_off);
+        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + L.cout, L.cout, G + L.g_off);
+        train_bn_bwd_apply_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+            dy, a, total, L.cout, (double)m, tw.bn[l].as<float>(), P + L.g_off, red, L.relu, dz);
+        // conv: dW, db (double accumulation), then dx for the layer below
+        const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
+        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (wn + L.cout) * sizeof(double), ctx->stream));
+        int chunks = (int)((m + 4095) / 4096);
+        if (chunks > 64) chunks = 64;
+        if (chunks < 1) chunks = 1;
+        train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks * L.cin, chunks), L.cout, 0, ctx->stream>>>(
+            xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
+        train_bias_bwd_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(dz, m, L.cout, red + wn);
+        train_accumulate_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(red, (int)wn, G + L.w_off);
+        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + wn, L.cout, G + L.b_off);
+        ctx->launches += 8;
+        if (l > 0) {
+            float *dx = tr->d_act[1].as<float>();
+            const size_t tin = (size_t)n * tw.h[l] * tw.w[l] * L.cin;
+            train_conv_bwd_x_kernel<<<grid_for(tin, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+                dz, P + L.w_off, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, dx);
+            ctx->launches += 1;
+            dy = dx;          // d_act[1] carries the gradient down; d_act[0] is rewritten as the next dz
+        }
+    }
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo
+
+using namespace stereo;
+
+extern "C" {
+
+int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, stereo_trainer **out)
+{
+    STEREO_REQUIRE(ctx != nullptr && out != nullptr, "null pointer");
+    STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
+    STEREO_REQUIRE(batch >= 2 && disp_range >= 5 && (disp_range & 1), "need batch >= 2 and an odd disp_range >= 5 (got %d, %d)",
+                   batch, disp_range);
+    STEREO_CUDA_CHECK(cudaSetDevice(ctx->device));
+    stereo_trainer *tr = new stereo_trainer();
+    tr->ctx = ctx;
+    tr->net = net;
+    tr->batch = batch;
+    tr->D = disp_range;
+    const NetDesc nd = net_desc(net);
+    tr->n_layers = nd.n_layers;
+    tr->patch = nd.shrink + 1;
+    size_t po = 0, so = 0;
+    for (int l = 0; l < nd.n_layers; ++l) {
+        TrainLayer &L = tr->layer[l];
+        L.ks = nd.layer[l].ks; L.cin = nd.layer[l].cin; L.cout = nd.layer[l].cout; L.relu = nd.layer[l].relu;
+        L.w_off = po; po += (size_t)L.ks * L.ks * L.cin * L.cout;
+        L.b_off = po; po += L.cout;
+        L.g_off = po; po += L.cout;
+        L.be_off = po; po += L.cout;
+        L.mean_off = so; so += L.cout;
+        L.var_off = so; so += L.cout;
+    }
+    tr->n_params = po;
+    tr->n_stats = so;
+    int rc = STEREO_OK;
+    auto need = [&](DevBuf &b, size_t bytes) { if (rc == STEREO_OK) rc = b.reserve(bytes); };
+    need(tr->params, po * sizeof(float));
+    need(tr->grads, po * sizeof(float));
+    need(tr->adam_m, po * sizeof(float));
+    need(tr->adam_v, po * sizeof(float));
+    need(tr->stats, so * sizeof(float));
+    need(tr->red, (po + 1024) * sizeof(double));
+    const size_t pw = (size_t)tr->patch + disp_range - 1;
+    const size_t act = (size_t)batch * (tr->patch - nd.layer[0].ks + 1) * (pw - nd.layer[0].ks + 1) * 64;
+    need(tr->d_act[0], act * sizeof(float));
+    need(tr->d_act[1], act * sizeof(float));
+    need(tr->logits, (size_t)batch * disp_range * sizeof(float));
+    need(tr->dlogits, (size_t)batch * disp_range * sizeof(float));
+    need(tr->targets, (size_t)batch * disp_range * sizeof(float));
+    need(tr->loss_buf, ((size_t)2 * batch + 2) * sizeof(float));
+    need(tr->tower[0].x[0], (size_t)batch * tr->patch * tr->patch * 3 * sizeof(float));
+    need(tr->tower[1].x[0], (size_t)batch * tr->patch * pw * 3 * sizeof(float));
+    if (rc != STEREO_OK) { delete tr; return rc; }
+    cudaMemsetAsync(tr->adam_m.ptr, 0, po * sizeof(float), ctx->stream);
+    cudaMemsetAsync(tr->adam_v.ptr, 0, po * sizeof(float), ctx->stream);
+    cudaMemsetAsync(tr->params.ptr, 0, po * sizeof(float), ctx->stream);
+    cudaMemsetAsync(tr->stats.ptr, 0, so * sizeof(float), ctx->stream);
+    STEREO_TRY(finish(ctx));
+    *out = tr;
+    return STEREO_OK;
+}
+
+int stereo_train_destroy(stereo_trainer *tr)
+{
+    if (!tr) return STEREO_OK;
+    cudaSetDevice(tr->ctx->device);
+    cudaStreamSynchronize(tr->ctx->stream);
+    DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
+                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1]};
+    for (DevBuf *b : bufs) b->release();
+    for (int t = 0; t < 2; ++t) {
+        for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();
+        for (int l = 0; l < kMaxLayers; ++l) { tr->tower[t].a[l].release(); tr->tower[t].bn[l].release(); }
+    }
+    delete tr;
+    return STEREO_OK;
+}
+
+size_t stereo_train_param_count(const stereo_trainer *tr) { return tr ? tr->n_params : 0; }
+size_t stereo_train_stat_count(const stereo_trainer *tr) { return tr ? tr->n_stats : 0; }
+int stereo_train_patch_size(const stereo_trainer *tr) { return tr ? tr->patch : 0; }
+
+int stereo_train_set_state(stereo_trainer *tr, const float *params, const float *stats, const float *adam_m,
+                           const float *adam_v, long long step)
+{
+    STEREO_REQUIRE(tr && params && stats, "null pointer");
+    cudaStream_t s = tr->ctx->stream;
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->params.ptr, params, tr->n_params * sizeof(float), cudaMemcpyHostToDevice, s));
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->stats.ptr, stats, tr->n_stats * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (adam_m) STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->adam_m.ptr, adam_m, tr->n_params * sizeof(float), cudaMemcpyHostToDevice, s));
+    else STEREO_CUDA_CHECK(cudaMemsetAsync(tr->adam_m.ptr, 0, tr->n_params * sizeof(float), s));
+    if (adam_v) STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->adam_v.ptr, adam_v, tr->n_params * sizeof(float), cudaMemcpyHostToDevice, s));
+    else STEREO_CUDA_CHECK(cudaMemsetAsync(tr->adam_v.ptr, 0, tr->n_params * sizeof(float), s));
+    tr->step = step;
+    return finish(tr->ctx);
+}
+
+int stereo_train_get_state(stereo_trainer *tr, float *params, float *stats, float *adam_m, float *adam_v, long long *step)
+{
+    STEREO_REQUIRE(tr != nullptr, "null pointer");
+    cudaStream_t s = tr->ctx->stream;
+    if (params) STEREO_CUDA_CHECK(cudaMemcpyAsync(params, tr->params.ptr, tr->n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (stats) STEREO_CUDA_CHECK(cudaMemcpyAsync(stats, tr->stats.ptr, tr->n_stats * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (adam_m) STEREO_CUDA_CHECK(cudaMemcpyAsync(adam_m, tr->adam_m.ptr, tr->n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (adam_v) STEREO_CUDA_CHECK(cudaMemcpyAsync(adam_v, tr->adam_v.ptr, tr->n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (step) *step = tr->step;
+    return finish(tr->ctx);
+}
+
+// Device address of the flat gradient array (n_params floats): a data-parallel host all-reduces it in
+// place between stereo_train_forward_backward and stereo_train_apply.
+int stereo_train_grads_dev(stereo_trainer *tr, float **grads)
+{
+    STEREO_REQUIRE(tr && grads, "null pointer");
+    *grads = tr->grads.as<float>();
+    return STEREO_OK;
+}
+
+// Host pointers: left [B][p][p][3], right [B][p][p + D - 1][3], targets [B][D] (fp32, already normalised
+// patches as data_handler.py:60-85 produces them).  Computes loss (mean over the batch), the number of
+// patches whose arg max is within 3 of the label's (train.py:117-119) and the gradients (kept on the device;
+// copied to `grads_out` if not null).  Moving BatchNorm statistics are updated by both tower passes.
+int stereo_train_forward_backward(stereo_trainer *tr, const float *left, const float *right, const float *targets,
+                                  float *loss, int *correct3, float *grads_out)
+{
+    STEREO_REQUIRE(tr && left && right && targets, "null pointer");
+    stereo_ctx *ctx = tr->ctx;
+    STEREO_CUDA_CHECK(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const int B = tr->batch, D = tr->D, p = tr->patch, pw = p + D - 1;
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->tower[0].x[0].ptr, left, (size_t)B * p * p * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->tower[1].x[0].ptr, right, (size_t)B * p * pw * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->targets.ptr, targets, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, s));
+    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->grads.ptr, 0, tr->n_params * sizeof(float), s));
+    STEREO_TRY(tower_forward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), p, p));
+    STEREO_TRY(tower_forward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), p, pw));
+    const int L = tr->n_layers, c = tr->layer[L - 1].cout;
+    STEREO_REQUIRE(tr->tower[0].h[L] == 1 && tr->tower[0].w[L] == 1 && tr->tower[1].h[L] == 1 && tr->tower[1].w[L] == D,
+                   "unexpected feature shape");
+    const float *lf = tr->tower[0].x[L].as<float>(), *rf = tr->tower[1].x[L].as<float>();
+    const int nt = 256;
+    const size_t sh = (((size_t)D + 1) & ~(size_t)1) * sizeof(float) + 6 * nt * sizeof(float);
+    train_loss_kernel<<<B, nt, sh, s>>>(lf, rf, tr->targets.as<float>(), D, c, B, tr->logits.as<float>(),
+                                        tr->dlogits.as<float>(), tr->loss_buf.as<float>());
+    train_reduce_loss_kernel<<<1, 32, 0, s>>>(tr->loss_buf.as<float>(), B, tr->loss_buf.as<float>() + 2 * B);
+    DevBuf &dl = tr->dfeat[0], &dr = tr->dfeat[1];
+    STEREO_TRY(dl.reserve((size_t)B * c * sizeof(float)));
+    STEREO_TRY(dr.reserve((size_t)B * D * c * sizeof(float)));
+    train_loss_bwd_kernel<<<B, c, 0, s>>>(lf, rf, tr->dlogits.as<float>(), D, c, dl.as<float>(), dr.as<float>());
+    ctx->launches += 3;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    STEREO_TRY(tower_backward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), dr.as<float>()));
+    STEREO_TRY(tower_backward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), dl.as<float>()));
+    float host[2] = {0.f, 0.f};
+    STEREO_CUDA_CHECK(cudaMemcpyAsync(host, tr->loss_buf.as<float>() + 2 * B, sizeof(host), cudaMemcpyDeviceToHost, s));
+    if (grads_out)
+        STEREO_CUDA_CHECK(cudaMemcpyAsync(grads_out, tr->grads.ptr, tr->n_params * sizeof(float), cudaMemcpyDeviceToHost, s));
+    STEREO_TRY(finish(ctx));
+    if (loss) *loss = host[0];
+    if (correct3) *correct3 = (int)(host[1] + 0.5f);
+    return STEREO_OK;
+}
+
+// One Adam step (beta1 0.9, beta2 0.999, epsilon 1e-7: tf.keras.optimizers.Adam defaults, train.py:80) with the
+// gradients of the last forward_backward call (or `grads_dev`, a device array, if not null).
+int stereo_train_apply(stereo_trainer *tr, const float *grads_dev, float lr)
+{
+    STEREO_REQUIRE(tr != nullptr, "null pointer");
+    stereo_ctx *ctx = tr->ctx;
+    STEREO_CUDA_CHECK(cudaSetDevice(ctx->device));
+    tr->step += 1;
+    const double b1 = 0.9, b2 = 0.999;
+    const float lr_t = (float)((double)lr * sqrt(1.0 - pow(b2, (double)tr->step)) / (1.0 - pow(b1, (double)tr->step)));
+    const float *g = grads_dev ? grads_dev : tr->grads.as<float>();
+    train_adam_kernel<<<(unsigned)((tr->n_params + 255) / 256), 256, 0, ctx->stream>>>(
+        tr->params.as<float>(), g, tr->adam_m.as<float>(), tr->adam_v.as<float>(), tr->n_params, lr_t, (float)b1, (float)b2, 1e-7f);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return finish(ctx);
+}
+
+}  // extern "C"

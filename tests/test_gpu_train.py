@@ -1,0 +1,106 @@
+"""GPU parity of the training step (csrc/train.cu through the C ABI) against oracle/train_oracle.py
+(float64 torch autograd).  Tolerances: loss 1e-5 relative, gradients 2e-4 of the largest gradient entry
+(fp32 forward/backward with double channel reductions), Adam trajectories 1e-4 after several steps."""
+import numpy as np
+import pytest
+
+from oracle import train_oracle as to
+from stereo_matching_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = _lib.Context(0)
+    yield c
+    c.close()
+
+
+def _batch(rng, B, D, p=9):
+    return (rng.standard_normal((B, p, p, 3)).astype(np.float32),
+            rng.standard_normal((B, p, p + D - 1, 3)).astype(np.float32), to.soft_labels(B, D))
+
+
+@pytest.mark.parametrize("B,D", [(4, 7), (16, 33), (128, 201)])
+def test_forward_backward_matches_oracle(ctx, B, D):
+    rng = np.random.default_rng(B)
+    params, stats = to.init_params("win9_dep9", seed=B)
+    params = (params + 0.05 * rng.standard_normal(params.size)).astype(np.float32)
+    left, right, targets = _batch(rng, B, D)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+    assert tr.n_params == 113088 and tr.patch == 9
+    tr.set_state(params, stats)
+    loss, correct, grads = tr.forward_backward(left, right, targets, want_grads=True)
+    ref_stats = stats.copy()
+    rloss, rcorrect, rgrads, _ = to.forward_backward(params.astype(np.float64), ref_stats, left, right, targets)
+    assert abs(loss - rloss) <= 1e-5 * max(1.0, abs(rloss))
+    assert correct == rcorrect
+    assert np.abs(grads - rgrads).max() <= 2e-4 * np.abs(rgrads).max()
+    layers, _, _ = to.param_layout("win9_dep9")
+    for d in layers:                                            # every parameter group on its own scale
+        for k in ("kernel", "bias", "gamma", "beta"):
+            ref = rgrads[d[k]]
+            # (the bias of the last layer feeds straight into BatchNorm: its true gradient is zero and what is
+            #  left is fp32 round-off, hence the absolute term)
+            assert np.abs(grads[d[k]] - ref).max() <= 5e-4 * np.abs(ref).max() + 2e-5 * np.abs(rgrads).max(), k
+    st = tr.get_state()
+    assert np.allclose(st["stats"], ref_stats, rtol=1e-4, atol=1e-6)      # moving mean / variance (two passes)
+    tr.close()
+
+
+def test_adam_trajectory_matches_oracle(ctx):
+    B, D = 16, 21
+    rng = np.random.default_rng(7)
+    params, stats = to.init_params("win9_dep9", seed=9)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+    tr.set_state(params, stats)
+    p64, m, v = params.astype(np.float64), np.zeros(params.size), np.zeros(params.size)
+    rstats = stats.copy()
+    losses = []
+    solid = np.ones(params.size, bool)      # entries whose gradient is well above fp32 round-off at every step
+    for step in range(1, 6):
+        left, right, targets = _batch(rng, B, D)
+        loss, _, _ = tr.forward_backward(left, right, targets)
+        tr.apply(to.learning_rate(step))
+        rloss, _, g, _ = to.forward_backward(p64, rstats, left, right, targets)
+        solid &= np.abs(g) > 1e-3 * np.abs(g).max()
+        p64, m, v = to.adam_step(p64, g, m, v, step, to.learning_rate(step))
+        losses.append((loss, rloss))
+    for loss, rloss in losses:
+        assert abs(loss - rloss) <= 2e-4 * max(1.0, abs(rloss))
+    st = tr.get_state()
+    assert st["step"] == 5
+    # Adam moves a parameter by ~lr per step whatever the size of its gradient, so entries whose true gradient
+    # is (near) zero - e.g. a bias that feeds straight into BatchNorm - random-walk on round-off in any
+    # implementation; the trajectories are compared where the gradient is solid
+    assert solid.mean() > 0.5
+    assert np.abs(st["params"] - p64)[solid].max() <= 2e-4 * np.abs(p64).max()
+    tr.close()
+
+
+def test_loss_decreases_on_a_fixed_batch(ctx):
+    """Overfitting one batch: the loss must fall (end-to-end sanity of sign conventions)."""
+    B, D = 32, 41
+    rng = np.random.default_rng(3)
+    params, stats = to.init_params("win9_dep9", seed=4)
+    left, right, targets = _batch(rng, B, D)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+    tr.set_state(params, stats)
+    first = last = None
+    for step in range(30):
+        loss, _, _ = tr.forward_backward(left, right, targets)
+        tr.apply(1e-3)
+        first = loss if first is None else first
+        last = loss
+    assert last < 0.5 * first
+    tr.close()
+
+
+def test_error_behaviour(ctx):
+    with pytest.raises(_lib.StereoError):
+        _lib.Trainer(ctx, _lib.NET_WIN9, 8, 200)                # even disparity range has no centre label
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, 4, 7)
+    with pytest.raises(ValueError):
+        tr.forward_backward(np.zeros((4, 9, 9, 3), np.float32), np.zeros((4, 9, 9, 3), np.float32), np.zeros((4, 7), np.float32))
+    tr.close()
