@@ -46,6 +46,7 @@ struct stereo_trainer {
     stereo::DevBuf d_act[2];       // ping-pong gradient wrt activations
     stereo::DevBuf logits, dlogits, loss_buf, targets;
     stereo::DevBuf dfeat[2];       // gradient wrt the left / right feature tensors
+    stereo::DevBuf d_pad, w_flip, zero_bias;   // backward-data as a forward convolution: padded dz, flipped weights
     stereo::Tower tower[2];
     long long step = 0;
 };
@@ -250,29 +251,55 @@ __global__ void train_accumulate_kernel(const double *__restrict__ red, int n, f
     if (i < n) dst[i] += (float)red[i];
 }
 
-// dW[t][ci][co] += sum_p x[p + t][ci] * dz[p][co];  grid = (taps * cin, chunks), block = cout threads
-__global__ void train_conv_bwd_w_kernel(const float *__restrict__ x, const float *__restrict__ dz, int n, int h, int wd,
-                                        int ks, int cin, int cout, double *__restrict__ red_w)
+// dW[t][ci][co] += sum_p x[p + t][ci] * dz[p][co].  A shared-memory GEMM per tap: grid = (taps, position
+// chunks), 256 threads, every thread a 4 x 4 block of the (<= 64 x 64) [ci][co] tile; the positions of a chunk
+// are accumulated in fp32 (<= kBwdChunk terms), the chunks in double (atomics).
+constexpr int kBwdChunk = 2048;
+__global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__restrict__ x, const float *__restrict__ dz,
+                                                               int n, int h, int wd, int ks, int cin, int cout,
+                                                               double *__restrict__ red_w)
 {
+    __shared__ float xs[32][65], ds[32][65];
     const int ho = h - ks + 1, wo = wd - ks + 1;
-    const int t = blockIdx.x / cin, ci = blockIdx.x % cin;
-    const int ky = t / ks, kx = t % ks, co = threadIdx.x;
+    const int t = blockIdx.x, ky = t / ks, kx = t % ks;
     const size_t m = (size_t)n * ho * wo;
-    const size_t chunk = (m + gridDim.y - 1) / gridDim.y;
-    const size_t p0 = (size_t)blockIdx.y * chunk, p1 = p0 + chunk < m ? p0 + chunk : m;
-    double acc = 0.0;
-    float part = 0.f;
-    int cnt = 0;
-    for (size_t p = p0; p < p1; ++p) {
-        const int xo = (int)(p % wo);
-        const size_t q = p / wo;
-        const int yo = (int)(q % ho), b = (int)(q / ho);
-        const float xv = x[(((size_t)b * h + yo + ky) * wd + xo + kx) * cin + ci];
-        part = fmaf(xv, dz[p * cout + co], part);
-        if (++cnt == 256) { acc += (double)part; part = 0.f; cnt = 0; }
+    const size_t p0 = (size_t)blockIdx.y * kBwdChunk, p1 = p0 + kBwdChunk < m ? p0 + kBwdChunk : m;
+    const int tid = threadIdx.x, ci0 = (tid >> 4) * 4, co0 = (tid & 15) * 4;
+    float acc[4][4] = {};
+    for (size_t pb = p0; pb < p1; pb += 32) {
+        for (int e = tid; e < 32 * 64; e += 256) {
+            const int pp = e >> 6, c = e & 63;
+            const size_t p = pb + pp;
+            float xv = 0.f, dv = 0.f;
+            if (p < p1) {
+                const int xo = (int)(p % wo);
+                const size_t q = p / wo;
+                const int yo = (int)(q % ho), b = (int)(q / ho);
+                if (c < cin) xv = x[(((size_t)b * h + yo + ky) * wd + xo + kx) * cin + c];
+                if (c < cout) dv = dz[p * cout + c];
+            }
+            xs[pp][c] = xv;
+            ds[pp][c] = dv;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int pp = 0; pp < 32; ++pp) {
+            float a[4], bv[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { a[i] = xs[pp][ci0 + i]; bv[i] = ds[pp][co0 + i]; }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
     }
-    acc += (double)part;
-    atomicAdd(red_w + ((size_t)t * cin + ci) * cout + co, acc);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (ci0 + i < cin && co0 + j < cout)
+                atomicAdd(red_w + ((size_t)t * cin + ci0 + i) * cout + co0 + j, (double)acc[i][j]);
 }
 
 // db[co] += sum_p dz[p][co]
@@ -284,32 +311,35 @@ __global__ void train_bias_bwd_kernel(const float *__restrict__ dz, size_t m, in
     atomicAdd(red + ch, s);
 }
 
-// dx[b][yy][xx][ci] = sum_{ky,kx,co} dz[b][yy - ky][xx - kx][co] * w[ky][kx][ci][co]
-__global__ void train_conv_bwd_x_kernel(const float *__restrict__ dz, const float *__restrict__ w, int n, int h, int wd,
-                                        int ks, int cin, int cout, float *__restrict__ dx)
+// dx[b][yy][xx][ci] = sum_{ky,kx,co} dz[b][yy - ky][xx - kx][co] * w[ky][kx][ci][co] is the 'valid' convolution of
+// dz, zero-padded by ks - 1 on every side, with the flipped and transposed weights
+// w'[ky'][kx'][co][ci] = w[ks-1-ky'][ks-1-kx'][ci][co]: it runs through train_conv_fwd_kernel.
+__global__ void train_pad_kernel(const float *__restrict__ dz, int n, int ho, int wo, int c, int pad,
+                                 float *__restrict__ out)
 {
-    const int ho = h - ks + 1, wo = wd - ks + 1;
-    const size_t total = (size_t)n * h * wd * cin;
+    const int hp = ho + 2 * pad, wp = wo + 2 * pad;
+    const size_t total = (size_t)n * hp * wp * c;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int ci = (int)(i % cin);
-        size_t p = i / cin;
-        const int xx = (int)(p % wd);
-        p /= wd;
-        const int yy = (int)(p % h), b = (int)(p / h);
-        float acc = 0.f;
-        for (int ky = 0; ky < ks; ++ky) {
-            const int yo = yy - ky;
-            if (yo < 0 || yo >= ho) continue;
-            for (int kx = 0; kx < ks; ++kx) {
-                const int xo = xx - kx;
-                if (xo < 0 || xo >= wo) continue;
-                const float *g = dz + (((size_t)b * ho + yo) * wo + xo) * cout;
-                const float *wp = w + ((size_t)(ky * ks + kx) * cin + ci) * cout;
-                for (int co = 0; co < cout; ++co) acc = fmaf(g[co], wp[co], acc);
-            }
-        }
-        dx[i] = acc;
+        const int ch = (int)(i % c);
+        size_t p = i / c;
+        const int x = (int)(p % wp) - pad;
+        p /= wp;
+        const int y = (int)(p % hp) - pad, b = (int)(p / hp);
+        out[i] = (x >= 0 && x < wo && y >= 0 && y < ho) ? dz[(((size_t)b * ho + y) * wo + x) * c + ch] : 0.f;
     }
+}
+
+__global__ void train_flip_weights_kernel(const float *__restrict__ w, int ks, int cin, int cout, float *__restrict__ wt)
+{
+    const int total = ks * ks * cin * cout;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int ci = i % cin;
+    int r = i / cin;
+    const int co = r % cout;
+    r /= cout;
+    const int kx = r % ks, ky = r / ks;
+    wt[i] = w[(((size_t)(ks - 1 - ky) * ks + (ks - 1 - kx)) * cin + ci) * cout + co];
 }
 
 // Adam as tf.keras.optimizers.Adam applies it (train.py:80,112): lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t)
@@ -406,10 +436,8 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         // conv: dW, db (double accumulation), then dx for the layer below
         const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (wn + L.cout) * sizeof(double), ctx->stream));
-        int chunks = (int)((m + 4095) / 4096);
-        if (chunks > 64) chunks = 64;
-        if (chunks < 1) chunks = 1;
-        train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks * L.cin, chunks), L.cout, 0, ctx->stream>>>(
+        const int chunks = (int)((m + kBwdChunk - 1) / kBwdChunk);
+        train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks, chunks), 256, 0, ctx->stream>>>(
             xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
         train_bias_bwd_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(dz, m, L.cout, red + wn);
         train_accumulate_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(red, (int)wn, G + L.w_off);
@@ -418,9 +446,17 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         if (l > 0) {
             float *dx = tr->d_act[1].as<float>();
             const size_t tin = (size_t)n * tw.h[l] * tw.w[l] * L.cin;
-            train_conv_bwd_x_kernel<<<grid_for(tin, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-                dz, P + L.w_off, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, dx);
-            ctx->launches += 1;
+            const int pad = L.ks - 1, hp = ho + 2 * pad, wp = wo + 2 * pad;
+            const size_t tpad = (size_t)n * hp * wp * L.cout;
+            STEREO_TRY(tr->d_pad.reserve(tpad * sizeof(float)));
+            STEREO_TRY(tr->w_flip.reserve(wn * sizeof(float)));
+            train_pad_kernel<<<grid_for(tpad, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(dz, n, ho, wo, L.cout, pad,
+                                                                                             tr->d_pad.as<float>());
+            train_flip_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(P + L.w_off, L.ks, L.cin, L.cout,
+                                                                                            tr->w_flip.as<float>());
+            train_conv_fwd_kernel<<<grid_for(tin, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+                tr->d_pad.as<float>(), tr->w_flip.as<float>(), tr->zero_bias.as<float>(), n, hp, wp, L.ks, L.cout, L.cin, 0, dx);
+            ctx->launches += 3;
             dy = dx;          // d_act[1] carries the gradient down; d_act[0] is rewritten as the next dz
         }
     }
@@ -478,6 +514,7 @@ int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, ste
     need(tr->dlogits, (size_t)batch * disp_range * sizeof(float));
     need(tr->targets, (size_t)batch * disp_range * sizeof(float));
     need(tr->loss_buf, ((size_t)2 * batch + 2) * sizeof(float));
+    need(tr->zero_bias, 64 * sizeof(float));
     need(tr->tower[0].x[0], (size_t)batch * tr->patch * tr->patch * 3 * sizeof(float));
     need(tr->tower[1].x[0], (size_t)batch * tr->patch * pw * 3 * sizeof(float));
     if (rc != STEREO_OK) { delete tr; return rc; }
@@ -485,6 +522,7 @@ int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, ste
     cudaMemsetAsync(tr->adam_v.ptr, 0, po * sizeof(float), ctx->stream);
     cudaMemsetAsync(tr->params.ptr, 0, po * sizeof(float), ctx->stream);
     cudaMemsetAsync(tr->stats.ptr, 0, so * sizeof(float), ctx->stream);
+    cudaMemsetAsync(tr->zero_bias.ptr, 0, 64 * sizeof(float), ctx->stream);
     STEREO_TRY(finish(ctx));
     *out = tr;
     return STEREO_OK;
@@ -496,7 +534,7 @@ int stereo_train_destroy(stereo_trainer *tr)
     cudaSetDevice(tr->ctx->device);
     cudaStreamSynchronize(tr->ctx->stream);
     DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
-                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1]};
+                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias};
     for (DevBuf *b : bufs) b->release();
     for (int t = 0; t < 2; ++t) {
         for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();
