@@ -107,3 +107,36 @@ def test_error_behaviour(ctx):
     with pytest.raises(ValueError):
         tr.forward_backward(np.zeros((4, 9, 9, 3), np.float32), np.zeros((4, 9, 9, 3), np.float32), np.zeros((4, 7), np.float32))
     tr.close()
+
+
+def test_trained_checkpoint_feeds_the_inference_path(ctx, tmp_path):
+    """train -> TensorBundle with the reference's keys -> `load_checkpoint` -> disparity maps: a hundred steps on
+    synthetic patches must already beat the untrained trunk on a synthetic pair."""
+    from stereo_matching_b200 import synth, train
+    from stereo_matching_b200.metric import three_pixel_error
+    from stereo_matching_b200.models.model import base_model_ws_9
+    B, D = 64, 41
+    data = train.SyntheticPatches(1, 9, D, B, seed=2, height=160, width=480)
+    params, stats = train.init_state("win9_dep9", seed=6)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+    tr.set_state(params, stats)
+    l, r, gt = synth.make_pair(7001, 120, 360, D)
+
+    def error_of(p, s, name):
+        train.save_checkpoint(str(tmp_path / name), "win9_dep9", 100, p, s)
+        m = base_model_ws_9((None, None, 3))
+        m.load_checkpoint(str(tmp_path / name), verbose=False)
+        out = m.context.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, lr_check=False)
+        return three_pixel_error(out["left_disp"][0].astype(np.int64), gt)
+
+    before = error_of(params, stats, "init")
+    hits = 0
+    for step in range(1, 101):
+        loss, correct, _ = tr.forward_backward(*data.next_batch())
+        tr.apply(train.learning_rate(step))
+        hits += correct if step > 80 else 0
+    st = tr.get_state()
+    after = error_of(st["params"], st["stats"], "trained")
+    assert hits / (20 * B) > 0.8                      # train.py:117-119 accuracy on the last 20 batches
+    assert after < before and after < 0.25
+    tr.close()
