@@ -140,3 +140,23 @@ def test_trained_checkpoint_feeds_the_inference_path(ctx, tmp_path):
     assert hits / (20 * B) > 0.8                      # train.py:117-119 accuracy on the last 20 batches
     assert after < before and after < 0.25
     tr.close()
+
+
+def test_base_model_forward_backward_matches_oracle(ctx):
+    """win37_dep9 (nine 5x5 layers, 32/64 channels, 37x37 patches) through the same kernels."""
+    B, D = 4, 5
+    rng = np.random.default_rng(37)
+    params, stats = to.init_params("win37_dep9", seed=37)
+    params = (params + 0.02 * rng.standard_normal(params.size)).astype(np.float32)
+    left, right, targets = _batch(rng, B, D, p=37)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN37, B, D)
+    assert tr.patch == 37 and tr.n_params == to.param_layout("win37_dep9")[1]
+    tr.set_state(params, stats)
+    loss, correct, grads = tr.forward_backward(left, right, targets, want_grads=True)
+    ref_stats = stats.copy()
+    rloss, rcorrect, rgrads, _ = to.forward_backward(params.astype(np.float64), ref_stats, left, right, targets,
+                                                     net="win37_dep9")
+    assert abs(loss - rloss) <= 1e-5 * max(1.0, abs(rloss)) and correct == rcorrect
+    assert np.abs(grads - rgrads).max() <= 5e-4 * np.abs(rgrads).max()
+    assert np.allclose(tr.get_state()["stats"], ref_stats, rtol=1e-4, atol=1e-6)
+    tr.close()
