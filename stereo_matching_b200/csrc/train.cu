@@ -10,6 +10,7 @@
 // `trainable_variables` (per layer: kernel [k][k][Cin][Cout], bias, gamma, beta), so that data-parallel
 // training is ONE all-reduce over it (113 088 floats for base_model_ws_9).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -371,6 +372,29 @@ static inline unsigned grid_for(size_t total, int block, int cap)
     return (unsigned)(g < 1 ? 1 : (g > (size_t)cap ? (size_t)cap : g));
 }
 
+// 'valid' convolution + bias (+ ReLU): the tiled fp32 kernels of the inference path (conv_ffma.cu) where one is
+// instantiated for the shape, the plain kernel above otherwise.  `wbase + w_off` = kernel, `wbase + b_off` = bias.
+static int train_conv(stereo_ctx *ctx, int ks, int cin, int cout, int relu, const float *wbase, size_t w_off,
+                      size_t b_off, const float *in, int n, int h, int w, float *out)
+{
+    const bool tiled = (ks == 3 && cout == 64 && (cin == 3 || cin == 64)) ||
+                       (ks == 5 && ((cin == 3 && cout == 32) || (cin == 32 && cout == 32) || (cin == 32 && cout == 64) ||
+                                    (cin == 64 && cout == 64)));
+    // (STEREO_TRAIN_CONV=plain forces the plain kernel: used to tell round-off from a bug)
+    static const bool plain = [] { const char *e = getenv("STEREO_TRAIN_CONV"); return e && e[0] == 'p'; }();
+    if (tiled && !plain) {
+        LayerDesc L;
+        L.ks = ks; L.cin = cin; L.cout = cout; L.relu = relu; L.w_off = w_off; L.b_off = b_off;
+        return launch_conv_ffma(ctx, L, wbase, in, n, h, w, out);
+    }
+    const size_t total = (size_t)n * (h - ks + 1) * (w - ks + 1) * cout;
+    train_conv_fwd_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
+        in, wbase + w_off, wbase + b_off, n, h, w, ks, cin, cout, relu, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 // ------------------------------------------------------------------------------------------
 // one tower forward (training mode) and backward
 // ------------------------------------------------------------------------------------------
@@ -391,8 +415,8 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         STEREO_TRY(tw.a[l].reserve(total * sizeof(float)));
         STEREO_TRY(tw.x[l + 1].reserve(total * sizeof(float)));
         STEREO_TRY(tw.bn[l].reserve(2 * L.cout * sizeof(float)));
-        train_conv_fwd_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-            cur, P + L.w_off, P + L.b_off, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, L.relu, tw.a[l].as<float>());
+        STEREO_TRY(train_conv(ctx, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
+                              tw.a[l].as<float>()));
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
         const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
         train_channel_moments_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(
@@ -401,7 +425,7 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
                                                                 S + L.mean_off, S + L.var_off);
         train_bn_apply_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
             tw.a[l].as<float>(), total, L.cout, tw.bn[l].as<float>(), P + L.g_off, P + L.be_off, tw.x[l + 1].as<float>());
-        ctx->launches += 4;
+        ctx->launches += 3;
         cur = tw.x[l + 1].as<float>();
     }
     STEREO_CUDA_CHECK(cudaGetLastError());
@@ -445,18 +469,17 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         ctx->launches += 8;
         if (l > 0) {
             float *dx = tr->d_act[1].as<float>();
-            const size_t tin = (size_t)n * tw.h[l] * tw.w[l] * L.cin;
             const int pad = L.ks - 1, hp = ho + 2 * pad, wp = wo + 2 * pad;
             const size_t tpad = (size_t)n * hp * wp * L.cout;
             STEREO_TRY(tr->d_pad.reserve(tpad * sizeof(float)));
-            STEREO_TRY(tr->w_flip.reserve(wn * sizeof(float)));
+            STEREO_TRY(tr->w_flip.reserve((wn + 64) * sizeof(float)));     // flipped kernel, then a zero bias
             train_pad_kernel<<<grid_for(tpad, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(dz, n, ho, wo, L.cout, pad,
                                                                                              tr->d_pad.as<float>());
             train_flip_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(P + L.w_off, L.ks, L.cin, L.cout,
                                                                                             tr->w_flip.as<float>());
-            train_conv_fwd_kernel<<<grid_for(tin, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-                tr->d_pad.as<float>(), tr->w_flip.as<float>(), tr->zero_bias.as<float>(), n, hp, wp, L.ks, L.cout, L.cin, 0, dx);
-            ctx->launches += 3;
+            STEREO_CUDA_CHECK(cudaMemsetAsync(tr->w_flip.as<float>() + wn, 0, 64 * sizeof(float), ctx->stream));
+            STEREO_TRY(train_conv(ctx, L.ks, L.cout, L.cin, 0, tr->w_flip.as<float>(), 0, wn, tr->d_pad.as<float>(), n, hp, wp, dx));
+            ctx->launches += 2;
             dy = dx;          // d_act[1] carries the gradient down; d_act[0] is rewritten as the next dz
         }
     }
