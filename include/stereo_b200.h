@@ -229,6 +229,13 @@ int stereo_profile_enable(stereo_ctx *ctx, int on);
 int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches);
 const char *stereo_profile_name(int kernel_class);
 
+/* post.lua:98-115,188-204 (options cost_agg, cost_agg_2, cost_w, cost_h): `iters` passes of
+ * nn.SpatialAveragePooling(kw, kh, 1, 1, (kw-1)/2, (kh-1)/2) with setCountExcludePad() over every disparity plane of
+ * a [h][w][D] volume.  The device variant needs a scratch volume when iters > 1. */
+int stereo_box_agg(stereo_ctx *ctx, const float *vol, int h, int w, int D, int kw, int kh, int iters, float *out);
+int stereo_box_agg_dev(stereo_ctx *ctx, const float *vol, int h, int w, int D, int kw, int kh, int iters, float *out,
+                       float *scratch);
+
 /* ---------------------------------------------------------------------------------------------
  * Patch training.  Replaces the body of the training loop of
  * /root/reference/train.py:92-112: model(lpatch, training=True), model(rpatch, training=True),

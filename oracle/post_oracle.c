@@ -327,3 +327,30 @@ int oracle_num_threads(void)
     return 1;
 #endif
 }
+
+/* post.lua:98-115,188-204  nn.SpatialAveragePooling(cost_w, cost_h, 1, 1, pad_w, pad_h) with
+ * setCountExcludePad(), applied to every disparity plane (torch7 THCUNN AvePoolForward: window clipped to the
+ * image, values summed row by row in fp32, divided by the number of in-image taps).
+ * Layout here [H][W][D] (D fastest), like every volume of this oracle. */
+void oracle_box_agg(const float *in, float *out, int H, int W, int D, int kw, int kh)
+{
+    const int pw = (kw - 1) / 2, ph = (kh - 1) / 2;
+#pragma omp parallel for
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            int y0 = y - ph, x0 = x - pw, y1 = y0 + kh, x1 = x0 + kw;
+            if (y1 > H + ph) y1 = H + ph;
+            if (x1 > W + pw) x1 = W + pw;
+            if (y0 < 0) y0 = 0;
+            if (x0 < 0) x0 = 0;
+            if (y1 > H) y1 = H;
+            if (x1 > W) x1 = W;
+            const float cnt = (float)((y1 - y0) * (x1 - x0));
+            for (int d = 0; d < D; ++d) {
+                float s = 0.f;
+                for (int yy = y0; yy < y1; ++yy)
+                    for (int xx = x0; xx < x1; ++xx) s += in[((size_t)yy * W + xx) * D + d];
+                out[((size_t)y * W + x) * D + d] = s / cnt;
+            }
+        }
+}

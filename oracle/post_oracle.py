@@ -237,3 +237,14 @@ def post_chain(left_cost_hwd, right_cost_hwd, left_disp_u8, right_disp_u8,
     stages["left_vol"] = lu
     stages["right_vol"] = ru
     return stages
+
+
+def box_agg(vol, kw=5, kh=5, iters=1):
+    """post.lua:98-106,188-203: `iters` passes of the count-exclude-pad average pooling; vol is [H][W][D]."""
+    cur = _f32(vol)
+    h, w, d = cur.shape
+    for _ in range(int(iters)):
+        out = np.empty_like(cur)
+        lib().oracle_box_agg(_fp(cur), _fp(out), h, w, d, int(kw), int(kh))
+        cur = out
+    return cur

@@ -75,6 +75,8 @@ SIGNATURES = {
     "stereo_profile_enable": [_c_ctx, _i],
     "stereo_profile_read": [_c_ctx, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
     "stereo_profile_name": [_i],
+    "stereo_box_agg": [_c_ctx, _p, _i, _i, _i, _i, _i, _i, _p],
+    "stereo_box_agg_dev": [_c_ctx, _p, _i, _i, _i, _i, _i, _i, _p, _p],
     "stereo_train_create": [_c_ctx, _i, _i, _i, ctypes.POINTER(ctypes.c_void_p)],
     "stereo_train_destroy": [_p],
     "stereo_train_param_count": [_p],
@@ -287,6 +289,13 @@ class Context:
         h, w = img.shape
         out = np.empty((h, w), np.float32)
         check(self._lib.stereo_guide_image(self._h, img.ctypes.data, h, w, out.ctypes.data))
+        return out
+
+    def box_agg(self, vol: np.ndarray, kw: int = 5, kh: int = 5, iters: int = 1) -> np.ndarray:
+        vol = _arr(vol, np.float32)
+        h, w, d = vol.shape
+        out = np.empty_like(vol)
+        check(self._lib.stereo_box_agg(self._h, vol.ctypes.data, h, w, d, int(kw), int(kh), int(iters), out.ctypes.data))
         return out
 
     def volume_std(self, vol: np.ndarray) -> float:

@@ -206,6 +206,7 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
+int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction);

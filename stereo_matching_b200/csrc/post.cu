@@ -733,6 +733,38 @@ int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *c
 }
 
 // ------------------------------------------------------------------------------------------
+// post.lua:98-115,188-204  optional box aggregation: nn.SpatialAveragePooling(cost_w, cost_h, 1, 1, pad)
+// with setCountExcludePad() on every disparity plane.  One thread per voxel (d fastest, so the <= kw*kh loads
+// of a warp are contiguous runs), same summation order as the original (row by row), sum / in-image taps.
+// ------------------------------------------------------------------------------------------
+__global__ void box_agg_kernel(const float *__restrict__ in, int h, int w, int D, int kw, int kh,
+                               float *__restrict__ out)
+{
+    const size_t total = (size_t)h * w * D;
+    const int pw = (kw - 1) / 2, ph = (kh - 1) / 2;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int d = (int)(i % D);
+        const size_t p = i / D;
+        const int x = (int)(p % w), y = (int)(p / w);
+        const int y0 = max(y - ph, 0), x0 = max(x - pw, 0);
+        const int y1 = min(min(y - ph + kh, h + ph), h), x1 = min(min(x - pw + kw, w + pw), w);
+        float s = 0.f;
+        for (int yy = y0; yy < y1; ++yy)
+            for (int xx = x0; xx < x1; ++xx) s = __fadd_rn(s, in[((size_t)yy * w + xx) * D + d]);
+        out[i] = __fdiv_rn(s, (float)((y1 - y0) * (x1 - x0)));
+    }
+}
+
+int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out)
+{
+    ProfScope prof(ctx, STEREO_K_CBCA);
+    box_agg_kernel<<<ctx->sm_count * 16, 256, 0, ctx->stream>>>(in, h, w, D, kw, kh, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // P5-P9  per-pixel map kernels (nyu.lua:91-115)
 // ------------------------------------------------------------------------------------------
 __global__ void outlier_kernel(const float *__restrict__ d0, const float *__restrict__ d1, int total, int w,

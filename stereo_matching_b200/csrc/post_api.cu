@@ -306,6 +306,39 @@ int stereo_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *std_ou
     return finish(ctx);
 }
 
+int stereo_box_agg_dev(stereo_ctx *ctx, const float *vol, int h, int w, int D, int kw, int kh, int iters, float *out,
+                       float *scratch)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(vol && out && h > 0 && w > 0 && D > 0, "bad argument");
+    STEREO_REQUIRE(kw >= 1 && kh >= 1 && (kw & 1) && (kh & 1) && iters >= 1, "window %dx%d must be odd and positive, iters >= 1",
+                   kw, kh);
+    STEREO_REQUIRE(iters == 1 || scratch, "more than one pass needs a scratch volume");
+    // passes ping-pong between `out` and `scratch` so that the last one lands in `out`
+    const float *src = vol;
+    for (int i = 0; i < iters; ++i) {
+        float *dst = ((iters - 1 - i) & 1) ? scratch : out;
+        STEREO_TRY(launch_box_agg(ctx, src, h, w, D, kw, kh, dst));
+        src = dst;
+    }
+    return STEREO_OK;
+}
+
+int stereo_box_agg(stereo_ctx *ctx, const float *vol, int h, int w, int D, int kw, int kh, int iters, float *out)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(vol && out && h > 0 && w > 0 && D > 0, "bad argument");
+    const size_t bytes = sizeof(float) * (size_t)h * w * D;
+    STEREO_TRY(ctx->stage_vol[0].reserve(bytes));
+    STEREO_TRY(ctx->stage_vol[1].reserve(bytes));
+    STEREO_TRY(ctx->post_vol[0].reserve(bytes));
+    STEREO_TRY(to_dev(ctx, ctx->stage_vol[0].ptr, vol, bytes));
+    STEREO_TRY(stereo_box_agg_dev(ctx, ctx->stage_vol[0].as<float>(), h, w, D, kw, kh, iters, ctx->stage_vol[1].as<float>(),
+                                  ctx->post_vol[0].as<float>()));
+    STEREO_TRY(to_host(ctx, out, ctx->stage_vol[1].ptr, bytes));
+    return finish(ctx);
+}
+
 int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img, float *left_vol, float *right_vol,
                          int h, int w, int D, int iters, const stereo_post_params *p)
 {

@@ -91,14 +91,61 @@ def build_parser():
     p.add_argument("--cost_agg", type=int, default=0)
     p.add_argument("--cost_agg_2", type=int, default=0)
     p.add_argument("--confLoc", type=int, default=0)
+    p.add_argument("--cost_w", type=int, default=5)
+    p.add_argument("--cost_h", type=int, default=5)
+    p.add_argument("--thres", type=float, default=23)
     p.add_argument("--in_dir", default=None, help="where left_cost/ etc. live (default: --saveDir, like post.lua's ./results)")
     return p
 
 
+def run_staged(ctx, opt, params, unary, right_unary, l_u8, r_u8):
+    """post.lua:95-243 stage by stage through the separate entry points - the path taken when one of the
+    options that post.lua leaves off by default is set: `cost_agg` / `cost_agg_2` (box aggregation,
+    post.lua:98-115,188-221) or `confLoc` (score threshold, post.lua:108-110,139-142).  Volumes are [H][W][D];
+    every arithmetic step is the device kernel of the fused pipeline or the same fp32 operation in numpy."""
+    l_img, r_img = ctx.guide_image(l_u8), ctx.guide_image(r_u8)           # post.lua:91-94
+    st = {}
+    lu, ru = np.asarray(unary, np.float32), np.asarray(right_unary, np.float32)
+    if opt.cost_agg > 0:                                                   # post.lua:98-115
+        cost_vol = ctx.box_agg(lu, opt.cost_w, opt.cost_h, opt.cost_agg)
+        pred = ctx.wta(cost_vol)[0]
+        if opt.confLoc == 1:
+            pred = np.where(cost_vol.max(axis=2) < np.float32(opt.thres), 255, pred).astype(np.uint8)   # (256 - 1):byte()
+        st["cost_img"] = pred
+        if opt.nyu_cost_agg_1 <= 0:
+            lu = cost_vol                                                  # post.lua:134 (the right volume stays raw)
+    if opt.nyu_cost_agg_1 > 0:                                             # post.lua:116-132
+        lu, ru = ctx.nyu_cross_agg(l_img, r_img, lu, ru, opt.nyu_cost_agg_1, params)
+        st["nyu_cost_img"], st["right_nyu_cost_img"] = ctx.wta(lu)[0], ctx.wta(ru)[0]
+    if opt.confLoc == 1:                                                   # post.lua:139-142
+        lu = np.where(lu < np.float32(opt.thres), np.float32(0), lu)
+        ru = np.where(ru < np.float32(opt.thres), np.float32(0), ru)
+    lu = (lu / np.float32(ctx.volume_std(lu))).astype(np.float32)         # post.lua:146-147
+    ru = (ru / np.float32(ctx.volume_std(ru))).astype(np.float32)
+    if opt.sgm == 1:                                                       # post.lua:149-166
+        lu = ctx.nyu_sgm(l_img, r_img, lu * np.float32(-1), -1, params)
+        ru = ctx.nyu_sgm(l_img, r_img, ru * np.float32(-1), 1, params)
+        st["nyu_sgm_img"], st["right_nyu_sgm_img"] = ctx.wta(lu, take_min=True)[0], ctx.wta(ru, take_min=True)[0]
+    if opt.cost_agg_2 > 0:                                                 # post.lua:188-221
+        lu = ctx.box_agg(lu, opt.cost_w, opt.cost_h, opt.cost_agg_2)
+        ru = ctx.box_agg(ru, opt.cost_w, opt.cost_h, opt.cost_agg_2)
+        st["post_cost_img"] = ctx.wta(lu, take_min=True)[0]
+        st["right_post_cost_img"] = ctx.wta(ru)[0]                         # `ru:max(1)` in the original (post.lua:214)
+    if opt.nyu_cost_agg_2 > 0:                                             # post.lua:168-185
+        lu, ru = ctx.nyu_cross_agg(l_img, r_img, lu, ru, opt.nyu_cost_agg_2, params)
+        st["nyu_cost_img_2"], st["right_nyu_cost_img_2"] = ctx.wta(lu, take_min=True)[0], ctx.wta(ru, take_min=True)[0]
+    if opt.post == 1:                                                      # post.lua:223-242
+        d0 = ctx.wta(lu, take_min=True)[0].astype(np.float32)
+        d1 = ctx.wta(ru, take_min=True)[0].astype(np.float32)
+        final, outlier = ctx.nyu_post(d0, d1, lu, params)
+        st["nyu_post"] = final.astype(np.uint8)                            # :byte() truncation
+        st["outlier"] = (outlier * 127).astype(np.uint8)
+        st["nyu_post_float"] = final
+    return st
+
+
 def run(opt) -> int:
     import cv2
-    if opt.cost_agg or opt.cost_agg_2 or opt.confLoc:
-        raise SystemExit("cost_agg / cost_agg_2 / confLoc are off by default in post.lua and are not implemented")
     in_dir = opt.in_dir or opt.saveDir
     ctx = default_context(opt.gpuid)
     params = _lib.default_post_params()
@@ -122,8 +169,17 @@ def run(opt) -> int:
         r_img = cv2.imread(os.path.join(in_dir, "right_disp", "right_%06d_10.png" % file_id), cv2.IMREAD_GRAYSCALE)
         if opt.postprocess != 1:
             continue
-        stages = ctx.post(unary, right_unary, l_img, r_img, params)
+        if opt.cost_agg or opt.cost_agg_2 or opt.confLoc:
+            stages = run_staged(ctx, opt, params, unary, right_unary, l_img, r_img)     # non-default branches
+        else:
+            stages = ctx.post(unary, right_unary, l_img, r_img, params)
+        for name in ("cost_img", "post_cost_img", "right_post_cost_img"):
+            if name in stages:
+                os.makedirs(os.path.join(opt.saveDir, name), exist_ok=True)
+                cv2.imwrite(os.path.join(opt.saveDir, name, "%06d_10.png" % file_id), stages[name])
         for name in _lib.STAGE_NAMES:
+            if name not in stages:
+                continue
             skip = (name.endswith("nyu_cost_img") and not opt.nyu_cost_agg_1) or \
                    ("sgm" in name and not opt.sgm) or (name.endswith("_2") and not opt.nyu_cost_agg_2) or \
                    (name in ("nyu_post", "outlier") and not opt.post)

@@ -173,3 +173,34 @@ def test_lua_surface_mirror(ctx, scene):
     post_mod.nyu.params.cbca_exact = 0
     lref, rref = po.nyu_cross_agg(l_img, r_img, lu[0], ru[0], 1)
     assert lo.shape == lu.shape and np.array_equal(lo[0], lref) and np.array_equal(ro[0], rref)
+
+
+@pytest.mark.parametrize("h,w,D,kw,kh,iters", [(13, 17, 6, 5, 5, 1), (24, 40, 33, 5, 5, 2), (9, 31, 64, 3, 7, 3), (60, 90, 201, 5, 5, 1)])
+def test_box_agg_bit_exact(ctx, h, w, D, kw, kh, iters):
+    rng = np.random.default_rng(h * w)
+    vol = rng.standard_normal((h, w, D)).astype(np.float32)
+    assert np.array_equal(ctx.box_agg(vol, kw, kh, iters), po.box_agg(vol, kw, kh, iters))
+
+
+def test_staged_post_path_equals_fused_pipeline_and_runs_the_optional_branches(ctx):
+    """post.py's staged path (taken for cost_agg / cost_agg_2 / confLoc) with those options off must reproduce the
+    fused `stereo_post` stage PNGs bit for bit; with them on it must produce the extra stage images."""
+    from stereo_matching_b200 import post as bpost
+    h, w, D = 40, 96, 33
+    rng = np.random.default_rng(5)
+    lv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    rv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    ld, rd = ctx.wta(lv)[0], ctx.wta(rv)[0]
+    params = _lib.default_post_params()
+    opt = bpost.build_parser().parse_args([])
+    fused = ctx.post(lv, rv, ld, rd, params)
+    staged = bpost.run_staged(ctx, opt, params, lv, rv, ld, rd)
+    for name in _lib.STAGE_NAMES:
+        assert np.array_equal(fused[name], staged[name]), name
+    opt = bpost.build_parser().parse_args(["--cost_agg", "1", "--cost_agg_2", "2", "--confLoc", "1", "--thres", "23"])
+    extra = bpost.run_staged(ctx, opt, params, lv, rv, ld, rd)
+    for name in ("cost_img", "post_cost_img", "right_post_cost_img", "nyu_post", "outlier"):
+        assert extra[name].shape == (h, w) and extra[name].dtype == np.uint8
+    agg = po.box_agg(lv, 5, 5, 1)
+    ref = np.where(agg.max(axis=2) < 23, 255, agg.argmax(axis=2)).astype(np.uint8)
+    assert np.array_equal(extra["cost_img"], ref)

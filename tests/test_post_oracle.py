@@ -127,3 +127,21 @@ def test_full_chain_runs_and_improves(ws9_layers):
     e1 = so.three_pixel_error(st["nyu_post"], gt)
     assert e1 < e0
     assert set(np.unique(st["outlier"])) <= {0, 127, 254}
+
+
+def test_box_agg_is_count_exclude_pad_average_pooling():
+    """post.lua:98-106: nn.SpatialAveragePooling(5, 5, 1, 1, 2, 2):setCountExcludePad() == torch avg_pool2d with
+    count_include_pad=False (independent implementation; summation order differs, hence allclose)."""
+    import torch
+    rng = np.random.default_rng(11)
+    vol = rng.standard_normal((13, 17, 6)).astype(np.float32)
+    for kw, kh in ((5, 5), (3, 7), (1, 1)):
+        got = po.box_agg(vol, kw, kh)
+        ref = torch.nn.functional.avg_pool2d(torch.tensor(vol).permute(2, 0, 1)[None], (kh, kw), 1, ((kh - 1) // 2, (kw - 1) // 2),
+                                             count_include_pad=False)[0].permute(1, 2, 0).numpy()
+        assert np.allclose(got, ref, rtol=1e-5, atol=1e-6)
+    assert np.array_equal(po.box_agg(vol, 1, 1), vol)
+    twice = po.box_agg(vol, 5, 5, iters=2)
+    assert np.array_equal(twice, po.box_agg(po.box_agg(vol, 5, 5), 5, 5))
+    const = np.full((9, 9, 3), 2.5, np.float32)
+    assert np.array_equal(po.box_agg(const, 5, 5, iters=3), const)        # borders divide by the in-image count
