@@ -167,3 +167,19 @@ def test_base_model_forward_backward_matches_oracle(ctx):
     assert err.max() <= 2e-3 and np.quantile(err, 0.999) <= 1e-4
     assert np.allclose(tr.get_state()["stats"], ref_stats, rtol=1e-4, atol=1e-6)
     tr.close()
+
+
+def test_evaluate_mirror_counts_three_pixel_hits(ctx, ws9_layers):
+    """evaluate.py on synthetic validation patches with the shipped ckpt-1000 weights: the trained network puts
+    most patches within 3 of the label, and the count equals a direct numpy restatement."""
+    from stereo_matching_b200 import evaluate as bev, train
+    from stereo_matching_b200.models.model import base_model_ws_9
+    m = base_model_ws_9((None, None, 3))
+    m.set_layers(ws9_layers)
+    data = train.SyntheticPatches(1, 9, 41, 96, seed=5, height=160, width=480)
+    lp, rp, t = data.next_batch()
+    acc = bev.evaluate(m, lp, rp, t, eval_size=40, verbose=False)
+    lf, rf = m(lp, training=False), m(rp, training=False)
+    pred = np.argmax(np.einsum("nc,ndc->nd", lf[:, 0, 0], rf[:, 0]), axis=1)
+    assert acc == pytest.approx(100.0 * np.mean(np.abs(pred - 20) <= 3))
+    assert acc > 80.0
