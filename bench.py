@@ -425,6 +425,33 @@ def run_b200(args):
             "three_px_error_pair0_after_post": three_pixel_error(post_final.astype(np.int64), gt[0]),
         }
 
+    # ---- secondary: configs[4]-style patch training step, rank 0 only ------------------
+    if not args.no_post and rank == 0:
+        try:
+            from stereo_matching_b200 import train as b200train
+            tB, tD = 128, 201
+            tctx = _lib.Context(local_rank)
+            tr = _lib.Trainer(tctx, _lib.NET_WIN9, tB, tD)
+            tr.set_state(*b200train.init_state("win9_dep9", 0))
+            trng = np.random.default_rng(0)
+            tl = trng.standard_normal((tB, 9, 9, 3)).astype(np.float32)
+            trr = trng.standard_normal((tB, 9, 9 + tD - 1, 3)).astype(np.float32)
+            tt = b200train.soft_labels(tB, tD)
+            for i in range(3):
+                tr.forward_backward(tl, trr, tt)
+                tr.apply(1e-3)
+            t0 = time.perf_counter()
+            for i in range(10):
+                tloss, _, _ = tr.forward_backward(tl, trr, tt)
+                tr.apply(1e-3)
+            tms = (time.perf_counter() - t0) / 10 * 1e3
+            extra["training_step"] = {"workload": f"base_model_ws_9 patch training, B={tB}, D={tD}, host patches in / loss out",
+                                      "ms_per_step": tms, "patches_per_s": tB / tms * 1e3, "loss": tloss}
+            tr.close()
+            tctx.close()
+        except Exception as e:          # secondary measurement: never fail the bench line
+            extra["training_step"] = {"error": repr(e)}
+
     # ---- CPU baseline (oracle port) on a bounded sample --------------------------------------------
     cpu = None
     if not args.no_cpu_baseline:
