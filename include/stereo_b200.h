@@ -229,6 +229,17 @@ int stereo_profile_enable(stereo_ctx *ctx, int on);
 int stereo_profile_read(stereo_ctx *ctx, int kernel_class, double *total_ms, int64_t *launches);
 const char *stereo_profile_name(int kernel_class);
 
+/* inference.py (trunk, both cost volumes, WTA) and post.lua (CBCA, SGM, CBCA, LR check, fills, sub-pixel, median,
+ * bilateral) back to back for n pairs; the volumes stay on the device (the reference passes them through
+ * left_cost/*.bin and right_cost/*.bin, inference.py:210-231 -> post.lua:89-90).  nyu_post [n][h][w] uint8 is
+ * post.lua:238's image; outlier (labels * 127, post.lua:241) and left_wta (inference.py:202) may be null. */
+int stereo_pairs_post(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h, int w,
+                      int disp_range, int precision, const stereo_post_params *params, uint8_t *nyu_post,
+                      uint8_t *outlier, uint8_t *left_wta);
+int stereo_pairs_post_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h,
+                          int w, int disp_range, int precision, const stereo_post_params *params, uint8_t *nyu_post,
+                          uint8_t *outlier, uint8_t *left_wta);
+
 /* post.lua:98-115,188-204 (options cost_agg, cost_agg_2, cost_w, cost_h): `iters` passes of
  * nn.SpatialAveragePooling(kw, kh, 1, 1, (kw-1)/2, (kh-1)/2) with setCountExcludePad() over every disparity plane of
  * a [h][w][D] volume.  The device variant needs a scratch volume when iters > 1. */

@@ -75,6 +75,8 @@ SIGNATURES = {
     "stereo_profile_enable": [_c_ctx, _i],
     "stereo_profile_read": [_c_ctx, _i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)],
     "stereo_profile_name": [_i],
+    "stereo_pairs_post": [_c_ctx, _i, _p, _p, _i, _i, _i, _i, _i, _pp, _p, _p, _p],
+    "stereo_pairs_post_dev": [_c_ctx, _i, _p, _p, _i, _i, _i, _i, _i, _pp, _p, _p, _p],
     "stereo_box_agg": [_c_ctx, _p, _i, _i, _i, _i, _i, _i, _p],
     "stereo_box_agg_dev": [_c_ctx, _p, _i, _i, _i, _i, _i, _i, _p, _p],
     "stereo_train_create": [_c_ctx, _i, _i, _i, ctypes.POINTER(ctypes.c_void_p)],
@@ -347,6 +349,20 @@ class Context:
         stages["nyu_post_float"] = final
         return stages
 
+    def pairs_post(self, net: int, left_rgb, right_rgb, disp_range: int, precision: int = PREC_FP32,
+                   params: "PostParams | None" = None):
+        """inference.py + post.lua for a batch of pairs, volumes kept on the device -> final maps."""
+        params = params or default_post_params()
+        left_rgb, right_rgb = _arr(left_rgb, np.uint8), _arr(right_rgb, np.uint8)
+        if left_rgb.ndim == 3:
+            left_rgb, right_rgb = left_rgb[None], right_rgb[None]
+        n, h, w, _ = left_rgb.shape
+        out = {k: np.empty((n, h, w), np.uint8) for k in ("nyu_post", "outlier", "left_disp")}
+        check(self._lib.stereo_pairs_post(self._h, int(net), left_rgb.ctypes.data, right_rgb.ctypes.data, n, h, w,
+                                          int(disp_range), int(precision), ctypes.byref(params), out["nyu_post"].ctypes.data,
+                                          out["outlier"].ctypes.data, out["left_disp"].ctypes.data))
+        return out
+
     def post_dev(self, left_cost, right_cost, left_disp, right_disp, h, w, disp_range, stage_ptrs,
                  final=None, params: "PostParams | None" = None):
         params = params or default_post_params()
@@ -361,6 +377,12 @@ class Context:
         check(self._lib.stereo_pairs_dev(self._h, int(net), _ptr(left_rgb), _ptr(right_rgb), n, h, w,
                                          int(disp_range), int(precision), _ptr(left_disp), _ptr(right_disp),
                                          _ptr(outlier), _ptr(left_vol), _ptr(right_vol)))
+
+    def pairs_post_dev(self, net, left_rgb, right_rgb, n, h, w, disp_range, precision, params, nyu_post, outlier=None,
+                       left_wta=None):
+        check(self._lib.stereo_pairs_post_dev(self._h, int(net), _ptr(left_rgb), _ptr(right_rgb), n, h, w, int(disp_range),
+                                              int(precision), ctypes.byref(params), _ptr(nyu_post), _ptr(outlier),
+                                              _ptr(left_wta)))
 
     def normalize_pad_dev(self, rgb, n, h, w, patch, out):
         check(self._lib.stereo_normalize_pad_dev(self._h, _ptr(rgb), n, h, w, int(patch), _ptr(out)))

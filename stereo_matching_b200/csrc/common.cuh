@@ -116,6 +116,7 @@ struct stereo_ctx {
     cudaStream_t aux_stream = nullptr;   // second stream of the post chain
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     stereo::DevBuf post_maps;    // guide images, arms, float maps, std scalars
+    stereo::DevBuf pp_maps;      // stereo_pairs_post: WTA maps and stage images of the pair in flight
     // host-pointer stereo_pairs: H2D and D2H run on their own streams, chunk by chunk, under the compute
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[16] = {}, ev_out[16] = {};

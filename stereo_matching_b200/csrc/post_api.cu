@@ -420,6 +420,61 @@ int stereo_post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     return post_dev(ctx, left_cost, right_cost, left_disp, right_disp, h, w, D, p, stages, final_disp);
 }
 
+// inference.py and post.lua back to back on the device: the two cost volumes are materialised into library
+// buffers, post-processed and never leave the GPU, so the reference's 850 MB of .bin files per pair
+// (inference.py:210-231 -> post.lua:89-90) become an optional export.
+// Device pointers.  nyu_post [n][h][w] uint8 (post.lua:238 `:byte()`), outlier and left_wta may be null.
+int stereo_pairs_post_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h,
+                          int w, int D, int precision, const stereo_post_params *p, uint8_t *nyu_post,
+                          uint8_t *outlier, uint8_t *left_wta)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_TRY(check_params(p, h, w, D));
+    STEREO_REQUIRE(left_rgb && right_rgb && nyu_post && n > 0, "bad argument");
+    const size_t hw = (size_t)h * w, nvox = hw * D;
+    STEREO_TRY(ctx->stage_vol[0].reserve(sizeof(float) * nvox));
+    STEREO_TRY(ctx->stage_vol[1].reserve(sizeof(float) * nvox));
+    STEREO_TRY(ctx->pp_maps.reserve(10 * hw));
+    uint8_t *maps = ctx->pp_maps.as<uint8_t>();          // [0] left WTA, [1] right WTA, [2..9] the eight stage images
+    for (int i = 0; i < n; ++i) {
+        STEREO_TRY(stereo_pairs_dev(ctx, net, left_rgb + (size_t)i * hw * 3, right_rgb + (size_t)i * hw * 3, 1, h, w, D,
+                                    precision, maps, maps + hw, nullptr, ctx->stage_vol[0].as<float>(),
+                                    ctx->stage_vol[1].as<float>()));
+        uint8_t *stages[8];
+        for (int k = 0; k < 8; ++k) stages[k] = maps + (2 + k) * hw;
+        stages[6] = nyu_post + (size_t)i * hw;                                   // "nyu_post"
+        if (outlier) stages[7] = outlier + (size_t)i * hw;                      // "outlier" (label * 127)
+        STEREO_TRY(post_dev(ctx, ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(), maps, maps + hw, h, w, D, p,
+                            stages, nullptr));
+        if (left_wta)
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(left_wta + (size_t)i * hw, maps, hw, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return STEREO_OK;
+}
+
+// The same with host pointers.
+int stereo_pairs_post(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const uint8_t *right_rgb, int n, int h, int w,
+                      int D, int precision, const stereo_post_params *p, uint8_t *nyu_post, uint8_t *outlier,
+                      uint8_t *left_wta)
+{
+    STEREO_TRY(check_ctx(ctx));
+    STEREO_REQUIRE(left_rgb && right_rgb && nyu_post && n > 0 && h > 0 && w > 0, "bad argument");
+    const size_t hw = (size_t)h * w, img_b = (size_t)n * hw * 3, map_b = (size_t)n * hw;
+    STEREO_TRY(ctx->stage_in[0].reserve(img_b));
+    STEREO_TRY(ctx->stage_in[1].reserve(img_b));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->stage_out[i].reserve(map_b));
+    STEREO_TRY(to_dev(ctx, ctx->stage_in[0].ptr, left_rgb, img_b));
+    STEREO_TRY(to_dev(ctx, ctx->stage_in[1].ptr, right_rgb, img_b));
+    STEREO_TRY(stereo_pairs_post_dev(ctx, net, ctx->stage_in[0].as<uint8_t>(), ctx->stage_in[1].as<uint8_t>(), n, h, w, D,
+                                     precision, p, ctx->stage_out[0].as<uint8_t>(),
+                                     outlier ? ctx->stage_out[1].as<uint8_t>() : nullptr,
+                                     left_wta ? ctx->stage_out[2].as<uint8_t>() : nullptr));
+    STEREO_TRY(to_host(ctx, nyu_post, ctx->stage_out[0].ptr, map_b));
+    if (outlier) STEREO_TRY(to_host(ctx, outlier, ctx->stage_out[1].ptr, map_b));
+    if (left_wta) STEREO_TRY(to_host(ctx, left_wta, ctx->stage_out[2].ptr, map_b));
+    return finish(ctx);
+}
+
 int stereo_post(stereo_ctx *ctx, const float *left_cost, const float *right_cost, const uint8_t *left_disp,
                 const uint8_t *right_disp, int h, int w, int D, const stereo_post_params *p,
                 uint8_t *const stages[8], float *final_disp)

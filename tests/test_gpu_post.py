@@ -204,3 +204,22 @@ def test_staged_post_path_equals_fused_pipeline_and_runs_the_optional_branches(c
     agg = po.box_agg(lv, 5, 5, 1)
     ref = np.where(agg.max(axis=2) < 23, 255, agg.argmax(axis=2)).astype(np.uint8)
     assert np.array_equal(extra["cost_img"], ref)
+
+
+def test_pairs_post_equals_inference_then_post(ctx):
+    """`stereo_pairs_post` (volumes never leave the device) == `stereo_pairs` with exported volumes followed by
+    `stereo_post` on them, bit for bit, for a batch of two pairs."""
+    D, h, w = 64, 72, 200
+    pairs = [synth.make_pair(4100 + i, h, w, D) for i in range(2)]
+    left = np.stack([p[0] for p in pairs])
+    right = np.stack([p[1] for p in pairs])
+    fused = ctx.pairs_post(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3)
+    ref = ctx.pairs(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3, volumes=True)
+    for i in range(2):
+        st = ctx.post(ref["left_cost"][i], ref["right_cost"][i], ref["left_disp"][i], ref["right_disp"][i])
+        assert np.array_equal(fused["nyu_post"][i], st["nyu_post"])
+        assert np.array_equal(fused["outlier"][i], st["outlier"])
+        assert np.array_equal(fused["left_disp"][i], ref["left_disp"][i])
+    from stereo_matching_b200.metric import three_pixel_error
+    gt = pairs[0][2]
+    assert three_pixel_error(fused["nyu_post"][0].astype(np.int64), gt) <= three_pixel_error(ref["left_disp"][0].astype(np.int64), gt)
