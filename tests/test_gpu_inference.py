@@ -357,3 +357,35 @@ def test_kitti_sizes_tensor_core(ctx, ws9, h, w, D):
     lref, rref = so.cost_volumes(lm, rm, D, np.float64)
     assert rel_err(lv[y0:], lref) < COST_TOL and rel_err(rv[y0:], rref) < COST_TOL
     assert (out["left_disp"][0][y0:] == so.wta(lref)).mean() >= WTA_AGREE
+
+
+def test_two_contexts_on_one_gpu_are_independent(ws9_layers):
+    """One context per thread is the threading model: two contexts driven from two threads at the
+    same time give the results of a single one."""
+    import threading
+    D = 33
+    pairs = [synth.make_pair(5200 + i, 60, 180, D) for i in range(4)]
+    left = np.stack([p[0] for p in pairs])
+    right = np.stack([p[1] for p in pairs])
+    models = []
+    for _ in range(2):
+        m = base_model_ws_9((None, None, 3))
+        m._ctx = _lib.Context(0)                      # a context of its own instead of the shared default
+        m.set_layers(ws9_layers)
+        models.append(m)
+    ref = models[0].context.pairs(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3)
+    outs = [None, None]
+
+    def work(k):
+        for _ in range(3):
+            outs[k] = models[k].context.pairs(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3)
+
+    threads = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for k in range(2):
+        for name in ("left_disp", "right_disp", "outlier"):
+            assert np.array_equal(outs[k][name], ref[name]), (k, name)
+        models[k].context.close()
