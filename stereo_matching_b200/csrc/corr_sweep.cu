@@ -159,12 +159,13 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ---- MMA issuer ----
+        {
+            // ---- MMA issuer: the whole warp runs the loop (converged), one elected lane issues ----
             constexpr uint32_t idesc = tc::make_idesc(kBlk, kBlk);
             const uint32_t d_hi = tc::desc_hi(128);
-            const int n_combo = p.planes == 2 ? 3 : 1;
+            const int n_mma = p.planes == 2 ? 12 : 4;
             uint32_t E0 = 0, T = 0, G = 0;           // first candidate block of the item, tiles, accumulator blocks
+            bool prewaited = false;                  // barriers of the coming block already waited for
             for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
                 const Item it = decode(p, item);
                 // L_lo*R_hi, then L_hi*R_lo, then L_hi*R_hi on both sides: the left and the right
@@ -175,31 +176,45 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                     tc::mbar_wait(bar_a_full + 8 * as, (T / kASlots) & 1);
                     const uint32_t e_first = E0 + (uint32_t)(k - it.k0);
 #pragma unroll 1
-                    for (int o = 0; o < 3; ++o) {
+                    for (int o = 0; o < 3; ++o, ++G) {
                         const uint32_t e = e_first + o, bs = e % kBSlots;
-                        if (k == it.k0 || o == 2) tc::mbar_wait(bar_b_full + 8 * bs, (e / kBSlots) & 1);
                         const uint32_t ab = G % kAccBlocks;
-                        tc::mbar_wait(bar_acc_empty + 8 * ab, ((G / kAccBlocks) & 1) ^ 1);
-                        ++G;
+                        if (!prewaited) {
+                            if (k == it.k0 || o == 2) tc::mbar_wait(bar_b_full + 8 * bs, (e / kBSlots) & 1);
+                            tc::mbar_wait(bar_acc_empty + 8 * ab, ((G / kAccBlocks) & 1) ^ 1);
+                        }
+                        prewaited = false;
                         tc::tc_fence_after();
-                        uint32_t acc = 0;
-                        for (int combo = 0; combo < n_combo; ++combo) {
-                            const int apl = (n_combo == 3 && combo == lo_first) ? 1 : 0;
-                            const int bpl = (n_combo == 3 && combo == 1 - lo_first) ? 1 : 0;
-                            const uint32_t a_lo = tc::desc_lo(s_a + as * kBlock + apl * kPlane, kRun);
-                            const uint32_t b_lo = tc::desc_lo(s_b + bs * kBlock + bpl * kPlane, kRun);
 #pragma unroll
-                            for (int ks = 0; ks < 4; ++ks) {
-                                tc::umma_bf16_parts(tmem_base + ab * kBlk, a_lo + ((2 * ks * kRun) >> 4), d_hi,
-                                                    b_lo + ((2 * ks * kRun) >> 4), d_hi, idesc, acc);
-                                acc = 1;
+                        for (int m = 0; m < 12; ++m) {
+                            if (m < n_mma) {
+                                const int combo = m >> 2, ks = m & 3;
+                                const int apl = (n_mma == 12 && combo == lo_first) ? 1 : 0;
+                                const int bpl = (n_mma == 12 && combo == 1 - lo_first) ? 1 : 0;
+                                const uint32_t a_lo = tc::desc_lo(s_a + as * kBlock + apl * kPlane, kRun);
+                                const uint32_t b_lo = tc::desc_lo(s_b + bs * kBlock + bpl * kPlane, kRun);
+                                if (tc::elect_one())
+                                    tc::umma_bf16_parts(tmem_base + ab * kBlk, a_lo + ((2 * ks * kRun) >> 4), d_hi,
+                                                        b_lo + ((2 * ks * kRun) >> 4), d_hi, idesc, m > 0);
+                            }
+                            // With the last MMAs of the block still to issue and several queued in the tensor pipe,
+                            // wait for what the next block of this tile needs: its accumulator and its candidates.
+                            if (m == 8 && o < 2) {
+                                if (k == it.k0 || o == 1) {
+                                    const uint32_t en = e + 1;
+                                    tc::mbar_wait(bar_b_full + 8 * (en % kBSlots), (en / kBSlots) & 1);
+                                }
+                                tc::mbar_wait(bar_acc_empty + 8 * ((G + 1) % kAccBlocks), (((G + 1) / kAccBlocks) & 1) ^ 1);
+                                prewaited = true;
                             }
                         }
-                        tc::tc_commit(bar_acc_full + 8 * ab);
-                        // the oldest candidate block has had its last use (at the end of a row all three have)
-                        if (o == 0 || k == it.k1 - 1) tc::tc_commit(bar_b_empty + 8 * bs);
+                        if (tc::elect_one()) {
+                            tc::tc_commit(bar_acc_full + 8 * ab);
+                            // the oldest candidate block has had its last use (at the end of a row all three have)
+                            if (o == 0 || k == it.k1 - 1) tc::tc_commit(bar_b_empty + 8 * bs);
+                        }
                     }
-                    tc::tc_commit(bar_a_empty + 8 * as);
+                    if (tc::elect_one()) tc::tc_commit(bar_a_empty + 8 * as);
                     ++T;
                 }
                 E0 += (uint32_t)(it.k1 - it.k0) + 2;
