@@ -389,3 +389,17 @@ def test_two_contexts_on_one_gpu_are_independent(ws9_layers):
         for name in ("left_disp", "right_disp", "outlier"):
             assert np.array_equal(outs[k][name], ref[name]), (k, name)
         models[k].context.close()
+
+
+def test_batched_tensor_core_pairs_with_volumes_equal_single_pairs(ctx):
+    """Pairs of a batch run on alternating streams with their own buffers: with the volumes exported too, every
+    pair must equal the same pair processed alone."""
+    D = 40
+    pairs = [synth.make_pair(5300 + i, 50, 300, D) for i in range(3)]
+    left = np.stack([p[0] for p in pairs])
+    right = np.stack([p[1] for p in pairs])
+    batch = ctx.pairs(_lib.NET_WIN9, left, right, D, precision=_lib.PREC_BF16X3, volumes=True)
+    for i in range(3):
+        one = ctx.pairs(_lib.NET_WIN9, left[i], right[i], D, precision=_lib.PREC_BF16X3, volumes=True)
+        for name in ("left_disp", "right_disp", "outlier", "left_cost", "right_cost"):
+            assert np.array_equal(batch[name][i], one[name][0]), (i, name)
