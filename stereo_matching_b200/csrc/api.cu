@@ -121,8 +121,44 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
                    nd.shrink + 1);
     const float *wts = ctx->weights[net].as<float>();
     if (precision != STEREO_PREC_FP32) {
-        STEREO_REQUIRE(net == STEREO_NET_WIN9,
-                       "the tensor-core trunk is built for base_model_ws_9 (3x3, 64 channels); use STEREO_PREC_FP32 for base_model");
+        if (net == STEREO_NET_WIN37) {
+            // base_model: layer 1 (K = 75) on the CUDA cores in fp32, converted to chunk-planar bf16 (hi, lo);
+            // layers 2-9 on tcgen05 with all weights streamed (conv_tcg.cu)
+            STEREO_REQUIRE(in != nullptr, "base_model takes the normalised, padded fp32 image");
+            const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
+            const int h1 = h - 4, w1 = w - 4;
+            const int wp = tcg_pitch(w1);
+            const size_t plane_elems = (size_t)n * h1 * 8 * wp * 8;            // up to 64 channels
+            DevBuf *act = lane ? ctx->act_b + 2 * (lane - 1) : ctx->act;
+            STEREO_TRY(act[0].reserve(2 * plane_elems * 2));
+            STEREO_TRY(act[1].reserve(2 * plane_elems * 2));
+            STEREO_TRY(ctx->feat.reserve(sizeof(float) * (size_t)n * h1 * w1 * 32));
+            uint16_t *buf_hi[2] = {act[0].as<uint16_t>(), act[1].as<uint16_t>()};
+            uint16_t *buf_lo[2] = {buf_hi[0] + plane_elems, buf_hi[1] + plane_elems};
+            STEREO_TRY(launch_conv_ffma(ctx, nd.layer[0], wts, in, n, h, w, ctx->feat.as<float>()));
+            STEREO_TRY(launch_nhwc_to_planar_g(ctx, ctx->feat.as<float>(), n, h1, w1, 32, wp, buf_hi[0],
+                                               planes == 2 ? buf_lo[0] : nullptr));
+            const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>();
+            int ch = h1, cw = w1, cur = 0;
+            for (int l = 1; l < nd.n_layers; ++l) {
+                const LayerDesc &L = nd.layer[l];
+                const bool last = l + 1 == nd.n_layers;
+                void *o_hi = buf_hi[cur ^ 1], *o_lo = buf_lo[cur ^ 1];
+                int o_wp = wp;
+                float *o_f32 = nullptr;
+                if (last) {
+                    if (planar) { o_hi = planar->hi; o_lo = planar->lo; o_wp = planar->wf; }
+                    else { o_hi = nullptr; o_lo = nullptr; o_f32 = out; }
+                }
+                STEREO_TRY(launch_conv_tcg(ctx, L.ks, L.cin, L.cout, buf_hi[cur], buf_lo[cur], n, ch, cw, wp, wimg,
+                                           wts + L.b_off, o_hi, o_lo, o_wp, o_f32, L.relu, planes));
+                wimg += tcg_weight_image_elems(L.ks, L.cin, L.cout);
+                ch -= L.ks - 1;
+                cw -= L.ks - 1;
+                cur ^= 1;
+            }
+            return STEREO_OK;
+        }
         // layer 1 on CUDA cores (K = 27) writing chunk-planar bf16 (hi, lo); layers 2-4 on tcgen05
         const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
         const int mode = conv_kernel_mode();
@@ -251,18 +287,19 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     float *feat = ctx->feat.as<float>();
     const size_t img_bytes = (size_t)h * w * 3;
     const size_t map = (size_t)h * w;
-    const bool tc_corr = precision != STEREO_PREC_FP32 && net == STEREO_NET_WIN9 && D <= corr_tc_max_disp();
+    const bool tc_corr = precision != STEREO_PREC_FP32 && D <= corr_tc_max_disp();
+    const bool from_u8 = tc_corr && net == STEREO_NET_WIN9;      // layer 1 reads the uint8 images itself
     PlanarFeat pf[4];
     // Pairs alternate between up to four streams ("lanes") with their own activation and feature buffers: the
     // first CTAs of one pair's next kernel fill the SMs that the tail of another pair's kernel leaves idle, and
     // launch gaps disappear.  Kernel-class profiling wants every kernel alone on the GPU: one lane while it is on.
     static const int max_lanes = [] { const char *e = getenv("STEREO_PAIR_LANES"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
-    int lanes = (tc_corr && !ctx->prof.on) ? max_lanes : 1;
+    int lanes = (from_u8 && !ctx->prof.on) ? max_lanes : 1;
     if (lanes > n) lanes = n;
     cudaStream_t lane_stream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (tc_corr) {
         // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
-        STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
+        if (from_u8) STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
         STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[0], 0));
         if (lanes > 1) {
             if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
@@ -295,7 +332,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
         const int lane = i % lanes;
         LaneStream on_lane(ctx, lane_stream[lane]);
         // left and right of one pair go through the trunk as a batch of two
-        if (!tc_corr) {
+        if (!from_u8) {
             STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
             STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
         }
@@ -310,8 +347,9 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             po.lo = f.l_lo + (size_t)f.ml * 8;
             po.wf = f.wf;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
-            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po, left_rgb + i * img_bytes,
-                                 right_rgb + i * img_bytes, 2 * i, lane));
+            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po,
+                                 from_u8 ? left_rgb + i * img_bytes : nullptr, from_u8 ? right_rgb + i * img_bytes : nullptr,
+                                 2 * i, lane));
             STEREO_TRY(launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, 1, h, w, f.wf, f.ml, D, planes, lv, rv,
                                       left_disp + i * map, right_disp + i * map));
         } else {
@@ -526,6 +564,19 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
                                              ctx->wsplit[net].as<uint16_t>() + (l + 2) * wl));
             STEREO_TRY(launch_weight_images3(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
                                              ctx->wsplit[net].as<uint16_t>() + 6 * wl + (l - 1) * wl3));
+        }
+    }
+    if (net == STEREO_NET_WIN37) {
+        // streaming units of conv_tcg.cu for layers 2-9, one after the other
+        size_t total = 0;
+        for (int l = 1; l < nd.n_layers; ++l) total += tcg_weight_image_elems(nd.layer[l].ks, nd.layer[l].cin, nd.layer[l].cout);
+        STEREO_TRY(ctx->wsplit[net].reserve(total * 2));
+        size_t off = 0;
+        for (int l = 1; l < nd.n_layers; ++l) {
+            const LayerDesc &L = nd.layer[l];
+            STEREO_TRY(launch_weight_image_g(ctx, ctx->weights[net].as<float>() + L.w_off, L.ks, L.cin, L.cout,
+                                             ctx->wsplit[net].as<uint16_t>() + off));
+            off += tcg_weight_image_elems(L.ks, L.cin, L.cout);
         }
     }
     STEREO_TRY(finish(ctx));

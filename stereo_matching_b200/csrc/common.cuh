@@ -163,6 +163,13 @@ int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *we
 size_t tc_weight_image_elems();
 int tc_pitch(int w);
 int tc2_pitch(int w);
+size_t tcg_weight_image_elems(int ks, int cin, int cout);
+int tcg_pitch(int w);
+int launch_weight_image_g(stereo_ctx *ctx, const float *layer_w, int ks, int cin, int cout, void *img);
+int launch_nhwc_to_planar_g(stereo_ctx *ctx, const float *in, int n, int h, int w, int c, int wp, void *hi, void *lo);
+int launch_conv_tcg(stereo_ctx *ctx, int ks, int cin, int cout, const void *in_hi, const void *in_lo, int n, int h_in,
+                    int w_in, int wp_in, const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out,
+                    float *out_f32, int relu, int planes);
 int corr_sweep_margin();
 int corr_sweep2_row_cols(int w);
 int launch_corr_sweep2(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,

@@ -255,13 +255,49 @@ def test_pair_end_to_end_tensor_core(ctx, ws9_layers):
     assert abs(so.three_pixel_error(ref["left_disp"], gt) - so.three_pixel_error(out["left_disp"][0], gt)) <= 0.0005
 
 
-def test_tensor_core_trunk_rejects_base_model(ctx):
+@pytest.fixture(scope="module")
+def base_layers(ctx):
     layers = synth.make_base_model_weights()
-    m = base_model((None, None, 3), precision=_lib.PREC_BF16X3)
-    m.set_layers(layers)
-    with pytest.raises(_lib.StereoError) as e:
-        m(np.zeros((1, 45, 60, 3), np.float32))
-    assert e.value.code == -1
+    m = base_model((None, None, 3))
+    m.set_layers(layers)              # loads STEREO_NET_WIN37 weights into the shared context
+    return layers
+
+
+# nine 5x5 layers with K = 800-1600 per output (ws9: four 3x3 layers, K = 576): the dropped lo*lo terms of the
+# split add up to ~3e-5 of max|ref| on the features; the cost volume gate (1e-4) is checked further down
+BASE_BF16X3_TOL = 6e-5
+
+
+@pytest.mark.parametrize("hw", [(45, 60), (37, 37), (40, 200), (52, 300)])
+def test_base_model_trunk_tensor_core_bf16x3_vs_oracle(ctx, base_layers, hw):
+    """base_model (5x5, 32/64 channels, models/model.py:5-28) through conv_tcg: layers 2-9 on tcgen05."""
+    x = np.random.default_rng(hw[1]).standard_normal((2,) + hw + (3,)).astype(np.float32)
+    ref = so.trunk_forward(x, base_layers, "win37_dep9", np.float64)
+    out = ctx.trunk(_lib.NET_WIN37, x, _lib.PREC_BF16X3)
+    assert out.shape == ref.shape == (2, hw[0] - 36, hw[1] - 36, 64)
+    assert rel_err(out, ref) < BASE_BF16X3_TOL
+    fp32 = ctx.trunk(_lib.NET_WIN37, x, _lib.PREC_FP32)
+    assert rel_err(out, fp32.astype(np.float64)) < BASE_BF16X3_TOL
+
+
+def test_base_model_trunk_tensor_core_bf16_reports_its_own_tolerance(ctx, base_layers):
+    x = np.random.default_rng(4).standard_normal((1, 45, 170, 3)).astype(np.float32)
+    ref = so.trunk_forward(x, base_layers, "win37_dep9", np.float64)
+    err = rel_err(ctx.trunk(_lib.NET_WIN37, x, _lib.PREC_BF16), ref)
+    assert 1e-5 < err < BF16_TOL
+
+
+def test_base_model_pair_end_to_end_tensor_core(ctx, base_layers):
+    D = 48
+    l, r, gt = synth.make_pair(1007, 40, 200, D)
+    ref = so.infer_pair(l, r, base_layers, "win37_dep9", 37, D, np.float64)
+    out = ctx.pairs(_lib.NET_WIN37, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    assert rel_err(out["left_cost"][0], ref["left_cost"]) < COST_TOL
+    assert rel_err(out["right_cost"][0], ref["right_cost"]) < COST_TOL
+    assert (out["left_disp"][0] == ref["left_disp"]).mean() >= WTA_AGREE
+    assert (out["right_disp"][0] == ref["right_disp"]).mean() >= WTA_AGREE
+    fp32 = ctx.pairs(_lib.NET_WIN37, l, r, D, precision=_lib.PREC_FP32)
+    assert (out["left_disp"][0] == fp32["left_disp"][0]).mean() >= WTA_AGREE
 
 
 # ---- tensor-core correlation (tcgen05), STEREO_PREC_BF16X3 ---------------------------------------
