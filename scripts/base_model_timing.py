@@ -25,6 +25,10 @@ def main():
         for _ in range(reps):
             ctx.pairs(_lib.NET_WIN37, l, r, D, precision=prec)
         out[name + "_ms_per_pair"] = (time.perf_counter() - t0) / reps * 1e3
+        ctx.profile_enable(True)
+        ctx.pairs(_lib.NET_WIN37, l, r, D, precision=prec)
+        out[name + "_kernel_ms"] = {k: round(v[0], 4) for k, v in ctx.profile_read().items() if v[1]}
+        ctx.profile_enable(False)
     print(json.dumps(out))
 
 

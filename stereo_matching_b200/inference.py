@@ -57,20 +57,35 @@ def build_parser():
 
 
 def _read_kitti(flags, file_id):
+    """(left, right) uint8 [h,w,3] and the uint8 ground truth (or None).
+
+    kitti2015: image_2 / image_3 in RGB order (scipy.misc.imread, inference.py:102-103), GT = cv2 GRAYSCALE of the
+    16-bit disp_noc_0 PNG, i.e. its high byte (inference.py:104).
+    kitti2012: grey image_0 / image_1 (inference.py:105-107).  The reference normalises the grey image and
+    assigns it into its 3-channel padded array (inference.py:129-130), which broadcasts the one channel into
+    all three; replicating the uint8 grey values gives the same mean, std and tower input.  The reference never
+    reads a ground truth in this mode (its metric line then fails on an undefined name); here `disp_noc/` is
+    used when it exists and the error is reported as nan when it does not."""
     import cv2
-    l = cv2.imread("%s/image_2/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_COLOR)
-    r = cv2.imread("%s/image_3/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_COLOR)
-    gt = cv2.imread("%s/disp_noc_0/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_GRAYSCALE)
-    if l is None or r is None or gt is None:
-        raise FileNotFoundError("KITTI files for id %06d not found under %s" % (file_id, flags.data_root))
-    # scipy.misc.imread returns RGB (inference.py:102-103)
-    return l[:, :, ::-1].copy(), r[:, :, ::-1].copy(), gt
+    if flags.data_version == "kitti2015":
+        l = cv2.imread("%s/image_2/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_COLOR)
+        r = cv2.imread("%s/image_3/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_COLOR)
+        gt = cv2.imread("%s/disp_noc_0/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_GRAYSCALE)
+        if l is None or r is None or gt is None:
+            raise FileNotFoundError("KITTI files for id %06d not found under %s" % (file_id, flags.data_root))
+        return l[:, :, ::-1].copy(), r[:, :, ::-1].copy(), gt
+    l = cv2.imread("%s/image_0/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_GRAYSCALE)
+    r = cv2.imread("%s/image_1/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_GRAYSCALE)
+    if l is None or r is None:
+        raise FileNotFoundError("KITTI 2012 files for id %06d not found under %s" % (file_id, flags.data_root))
+    gt = cv2.imread("%s/disp_noc/%06d_10.png" % (flags.data_root, file_id), cv2.IMREAD_GRAYSCALE)
+    return np.repeat(l[:, :, None], 3, axis=2), np.repeat(r[:, :, None], 3, axis=2), gt
 
 
 def run(flags) -> float:
     import cv2
-    if flags.data_version != "kitti2015":
-        raise SystemExit("only data_version=kitti2015 (3-channel input) is supported")
+    if flags.data_version not in ("kitti2015", "kitti2012"):
+        raise SystemExit("data_version should be either kitti2012 or kitti2015")
     if flags.net_type == "win37_dep9":
         model = base_model((None, None, 3), device=flags.device)
     else:
@@ -102,12 +117,16 @@ def run(flags) -> float:
         out = ctx.pairs(model.net, linput, rinput, flags.disp_range, model.precision,
                         lr_check=False, volumes=not flags.no_bin)
         left_image_int, right_image_int = out["left_disp"][0], out["right_disp"][0]
-        error_id = three_pixel_error(left_image_int.astype(np.int64), disp_targets)
+        if disp_targets is None:
+            error_id = float("nan")
+        else:
+            error_id = three_pixel_error(left_image_int.astype(np.int64), disp_targets)
         error += error_id
         print(("%06d" % file_id) + "_10" + "\t" + ("%f" % error_id))
         cv2.imwrite("%s/left_disp/left_%06d_10.png" % (flags.out_dir, file_id), left_image_int)
         cv2.imwrite("%s/right_disp/right_%06d_10.png" % (flags.out_dir, file_id), right_image_int)
-        cv2.imwrite("%s/gt/true_%06d_10.png" % (flags.out_dir, file_id), disp_targets)
+        if disp_targets is not None:
+            cv2.imwrite("%s/gt/true_%06d_10.png" % (flags.out_dir, file_id), disp_targets)
         if not flags.no_bin:
             h, w = left_image_int.shape
             out["left_cost"][0].tofile(os.path.join(flags.out_dir, "left_cost", bin_name("left", file_id, h, w, flags.disp_range)))

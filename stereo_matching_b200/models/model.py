@@ -114,7 +114,8 @@ class StereoTrunk:
     # -- forward --
     def __call__(self, x, training: bool = False):
         if training:
-            raise NotImplementedError("training=True (batch-statistics BatchNorm) is not part of the inference path")
+            raise NotImplementedError("training=True (batch-statistics BatchNorm, train.py:100-101) runs through "
+                                      "stereo_matching_b200.train / _lib.Trainer, which owns the device state")
         if self.layers is None:
             raise RuntimeError("weights not set: call load_checkpoint(model_dir) or set_layers(layers) first")
         x = np.asarray(x)

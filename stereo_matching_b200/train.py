@@ -190,11 +190,19 @@ def main(argv=None):
     ap.add_argument("--net_type", default="win9_dep9", choices=sorted(NETS))
     ap.add_argument("--patch_size", type=int, default=9)
     ap.add_argument("--disp_range", type=int, default=201)
-    ap.add_argument("--synthetic", type=int, default=4, help="number of synthetic pairs to sample patches from")
+    ap.add_argument("--eval_size", type=int, default=200)
+    ap.add_argument("--num_tr_img", type=int, default=160)
+    ap.add_argument("--num_val_img", type=int, default=40)
+    ap.add_argument("--num_val_loc", type=int, default=5000)
+    ap.add_argument("--phase", default="train")
+    ap.add_argument("--synthetic", type=int, default=4,
+                    help="number of synthetic pairs to sample patches from; 0 = KITTI through data_handler.Data_handler")
     ap.add_argument("--seed", type=int, default=123)
     args = ap.parse_args(argv)
     if args.data_version != "kitti2015":
-        ap.error("only the 3-channel kitti2015 mode is built (train.py:57-58)")
+        # the reference builds the towers with 3 input channels whatever the data version (train.py:67-70), so its
+        # own kitti2012 training stops at the first tower call; nothing to mirror
+        ap.error("training takes the 3-channel kitti2015 data (the reference's towers are (None, None, 3), train.py:67-70)")
 
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
@@ -223,7 +231,14 @@ def main(argv=None):
         if rank == 0:
             print("Initializing from scratch.")
     tr.set_state(params, stats, step=step)
-    data = SyntheticPatches(args.synthetic, args.patch_size, args.disp_range, args.batch_size, seed=args.seed + rank)
+    if args.synthetic > 0:
+        data = SyntheticPatches(args.synthetic, args.patch_size, args.disp_range, args.batch_size, seed=args.seed + rank)
+    else:
+        from .data_handler import Data_handler
+        np.random.seed(args.seed + rank)                       # train.py:43 (rank 0 = the reference's order)
+        data = Data_handler(args.data_version, args.data_root, args.util_root, args.num_tr_img, args.num_val_img,
+                            args.num_val_loc, args.batch_size, args.patch_size, args.disp_range,
+                            val_npy="val.npy" if rank == 0 else "")
     gview = DeviceGradView(tr, local_rank).tensor if world > 1 else None
 
     acc_total = 0

@@ -183,3 +183,36 @@ def test_evaluate_mirror_counts_three_pixel_hits(ctx, ws9_layers):
     pred = np.argmax(np.einsum("nc,ndc->nd", lf[:, 0, 0], rf[:, 0]), axis=1)
     assert acc == pytest.approx(100.0 * np.mean(np.abs(pred - 20) <= 3))
     assert acc > 80.0
+
+
+def test_real_data_loop_preprocess_train_inference(tmp_path, monkeypatch, capsys):
+    """The reference's workflow on a KITTI-shaped tree: location files (preprocess), `train.py` through
+    Data_handler (which writes val.npy), then `inference.py` on the validation ids with the checkpoint the
+    training wrote; kitti2012 (grey) mode of inference.py runs on the same tree."""
+    import kitti_tree
+    from stereo_matching_b200 import checkpoint, inference, train
+    tree = kitti_tree.build(tmp_path / "kitti")
+    monkeypatch.chdir(tmp_path)                       # val.npy goes to the working directory (data_handler.py:114)
+    common = ["--data_root", tree["root"], "--patch_size", "9", "--disp_range", str(2 * kitti_tree.HR + 1),
+              "--model_dir", str(tmp_path / "ckpt")]
+    rc = train.main(common + ["--synthetic", "0", "--util_root", tree["util"], "--num_tr_img", str(kitti_tree.TR),
+                              "--num_val_img", str(kitti_tree.VAL), "--num_val_loc", "64", "--batch_size", "32",
+                              "--num_iter", "100", "--max_epoch", "1"])
+    assert rc == 0
+    out = capsys.readouterr().out
+    assert "Saved checkpoint for step 100" in out and "Epoch 1 finished" in out
+    # tf.train.CheckpointManager numbers its saves (one per 100 steps): the first one is ckpt-1
+    assert checkpoint.latest_checkpoint(str(tmp_path / "ckpt")).endswith("ckpt-1")
+    val_ids = np.load(tmp_path / "val.npy")
+    assert 1 <= len(val_ids) <= kitti_tree.VAL
+    for version in ("kitti2015", "kitti2012"):
+        res = tmp_path / ("results_" + version)
+        inference.main(common + ["--data_version", version, "--out_dir", str(res), "--num_val_img", str(len(val_ids))])
+        text = capsys.readouterr().out
+        mean = float(text.split("Mean Error:")[1].split()[0])
+        # colour: ground truth read from disp_noc_0; grey: the tree has no disp_noc/, the error is reported as nan
+        assert (0.0 <= mean < 0.9) if version == "kitti2015" else np.isnan(mean)
+        for fid in val_ids:
+            assert (res / "left_disp" / ("left_%06d_10.png" % fid)).exists()
+            name = "left_%06d_10_%d_%d_%d.bin" % (fid, kitti_tree.H, kitti_tree.W, 2 * kitti_tree.HR + 1)
+            assert (res / "left_cost" / name).stat().st_size == kitti_tree.H * kitti_tree.W * (2 * kitti_tree.HR + 1) * 4
