@@ -112,6 +112,7 @@ struct stereo_ctx {
     cudaEvent_t lane_join[3] = {nullptr, nullptr, nullptr};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
     stereo::DevBuf post_vol[8];  // working volumes of the post chain: 4 per side (the sides run on two streams)
+    stereo::DevBuf sgm_aux[2];   // classified guide differences of the SGM ring kernels, per side
     stereo::DevBuf post_cnt[2];  // row-segment lengths of the separable CBCA (uint8 per voxel), per side
     cudaStream_t aux_stream = nullptr;   // second stream of the post chain
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -216,6 +217,10 @@ int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, c
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
 int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
+// sgm_ring.cu
+bool sgm_ring_usable(const float *cvol, const float *out, const float *scratch, int D);
+int launch_sgm_ring(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
+                    int h, int w, int D, const SgmParams &p, int direction);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction);
 int launch_outlier(stereo_ctx *ctx, const float *d0, const float *d1, int h, int w, int disp_max, float *outlier);

@@ -724,6 +724,10 @@ int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *c
     const bool vec = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                      ((uintptr_t)scratch % 16 == 0);
     ProfScope prof(ctx, STEREO_K_SGM);
+    // default: the shared-memory ring kernels (sgm_ring.cu); STEREO_SGM_KERNEL=1 keeps the register-prefetch ones
+    static const bool ring = [] { const char *e = getenv("STEREO_SGM_KERNEL"); return !(e && atoi(e) == 1); }();
+    if (ring && sgm_ring_usable(cvol, out, scratch, D))
+        return launch_sgm_ring(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
     if (D <= 128) return vec ? launch_sgm_t<4, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
                              : launch_sgm_t<4, 4, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
     if (D <= 256) return vec ? launch_sgm_t<8, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)

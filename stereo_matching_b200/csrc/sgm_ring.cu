@@ -1,0 +1,332 @@
+// adcensus.sgm2 (smooth/nyu.lua:59-60) with the volumes streamed through shared memory by bulk copies.
+//
+// The register-prefetch kernels in post.cu (one warp per scanline, every lane loading its own 32 bytes of each
+// step) move 2.0-2.6 TB/s: each warp asks DRAM for one 912-byte row per step, 1 500-3 700 independent streams at a
+// time.  Here a CTA of NW scanline warps plus one producer warp pulls LARGE contiguous granules into a ring of
+// shared-memory stages with cp.async.bulk (completion on an mbarrier), so that a request covers
+//   horizontal paths: G consecutive steps of one scanline  (G x D floats, contiguous along x),
+//   vertical paths:   one step of NW adjacent scanlines    (NW x D floats, contiguous along x),
+// The penalty case of every (pixel, disparity) depends on the two guide images only: sgm_prep_kernel classifies
+// D1 and D2 against tau once per call into byte images (`want` per pixel and path, `code` per matched pixel and
+// path, padded so that no range check is left), and a step reads 8 bytes per lane one step ahead instead of
+// gathering and comparing guide values.  The path-cost arithmetic is the original's, operation for operation
+// (sgm_step_coded() in sgm_step.cuh): results are bit-identical to the register-prefetch kernels.
+// Needs D % 4 == 0 and 16-byte aligned volumes (bulk copies); launch_sgm() falls back to post.cu otherwise.
+#include <algorithm>
+
+#include "common.cuh"
+#include "sgm_step.cuh"
+#include "tc_common.cuh"
+
+namespace stereo {
+using namespace tc;
+
+namespace {
+
+constexpr int kMaxStages = 8;
+
+// Byte images of sgm_prep_kernel: want[path][h][w], code[path][h][pitch] with pitch = w + 2 * pad
+struct SgmAux {
+    const uint8_t *want, *code;
+    int pad, pitch;
+};
+
+template <int SD, int NACC, int KPL, int NW, int DIR>
+__device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__restrict__ cvol, const float *acc_a,
+                                              const float *acc_b, float *outp, int h, int w, int D, const SgmParams &p,
+                                              int last, int G, int S, int group)
+{
+    constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
+    constexpr int dy = SD == 2 ? 1 : (SD == 3 ? -1 : 0);
+    constexpr bool kH = dy == 0;
+    constexpr int kArrays = 1 + NACC;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int steps = kH ? w : h;
+    const int n_lines = kH ? h : w;
+    const int line0 = group * NW;
+    const int lines_here = min(NW, n_lines - line0);
+    const int n_stages = (steps + G - 1) / G;
+    const uint32_t array_bytes = (uint32_t)NW * G * D * 4;            // one array of one stage
+    const uint32_t stage_bytes = kArrays * array_bytes;
+    const uint32_t s_data = smem_u32(smem);
+    const uint32_t s_bar = s_data + (uint32_t)S * stage_bytes;
+    const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < S; ++i) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, (uint32_t)lines_here);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (warp == NW) {
+        // ---- producer: one lane issues the bulk copies of every stage ----
+        if (lane != 0) return;
+        const float *src[3] = {cvol, acc_a, acc_b};
+        for (int t = 0; t < n_stages; ++t) {
+            const int s = t % S;
+            mbar_wait(bar_empty + 8 * s, ((t / S) & 1) ^ 1);
+            const int g_here = min(G, steps - t * G);
+            const uint32_t dst0 = s_data + (uint32_t)s * stage_bytes;
+            if (kH) {
+                // per scanline: g_here consecutive pixels; the right-to-left path walks its granule backwards
+                const uint32_t bytes = (uint32_t)g_here * D * 4;
+                mbar_expect_tx(bar_full + 8 * s, bytes * lines_here * kArrays);
+                const int x_lo = SD == 0 ? t * G : w - t * G - g_here;
+                for (int a = 0; a < kArrays; ++a)
+                    for (int q = 0; q < lines_here; ++q)
+                        bulk_g2s(dst0 + a * array_bytes + (uint32_t)q * G * D * 4,
+                                 src[a] + ((size_t)(line0 + q) * w + x_lo) * D, bytes, bar_full + 8 * s);
+            } else {
+                // per step: the lines_here adjacent pixels of one image row
+                const uint32_t bytes = (uint32_t)lines_here * D * 4;
+                mbar_expect_tx(bar_full + 8 * s, bytes * g_here * kArrays);
+                for (int a = 0; a < kArrays; ++a)
+                    for (int i = 0; i < g_here; ++i) {
+                        const int y = SD == 2 ? t * G + i : h - 1 - (t * G + i);
+                        bulk_g2s(dst0 + a * array_bytes + (uint32_t)i * NW * D * 4, src[a] + ((size_t)y * w + line0) * D,
+                                 bytes, bar_full + 8 * s);
+                    }
+            }
+        }
+        return;
+    }
+    if (warp >= lines_here) return;
+
+    // ---- consumers: one warp per scanline, KPL consecutive disparities per lane ----
+    const int line = line0 + warp;
+    const int x = kH ? (SD == 0 ? 0 : w - 1) : line;
+    const int y = kH ? line : (SD == 2 ? 0 : h - 1);
+    const int d0 = lane * KPL;
+    const SgmPenalties<SD> pen(p);
+    bool valid4[KPL / 4];
+#pragma unroll
+    for (int j = 0; j < KPL / 4; ++j) valid4[j] = d0 + 4 * j < D;      // D % 4 == 0: whole float4s
+    const bool has_below = lane > 0, has_above = d0 + KPL < D;
+
+    // classified guide differences of the NEXT step (bytes; one step ahead of their use)
+    const uint8_t *cptr = aux.code + ((size_t)SD * h + y) * aux.pitch + aux.pad + x + d0 * DIR;
+    const uint8_t *wptr = aux.want + ((size_t)SD * h + y) * w + x;
+    const ptrdiff_t cstep = (ptrdiff_t)dy * aux.pitch + dx, wstep = (ptrdiff_t)dy * w + dx;
+    int code_n[KPL], want_n = 3;
+#pragma unroll
+    for (int k = 0; k < KPL; ++k) code_n[k] = 0;
+
+    float prev[KPL];
+#pragma unroll
+    for (int k = 0; k < KPL; ++k) prev[k] = kSgmBig;
+    float *optr = outp + ((size_t)y * w + x) * D + d0;
+    const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;
+
+    int step = 0;
+    for (int t = 0; t < n_stages; ++t) {
+        const int s = t % S;
+        const int g_here = min(G, steps - t * G);
+        mbar_wait(bar_full + 8 * s, (t / S) & 1);
+        const uint8_t *stage = smem + (size_t)s * stage_bytes;
+        for (int i = 0; i < g_here; ++i, ++step) {
+            int code[KPL];
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) code[k] = code_n[k];
+            const int want = want_n;
+            if (step + 1 < steps) {
+                cptr += cstep;
+                wptr += wstep;
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) code_n[k] = __ldg(cptr + k * DIR);
+                want_n = __ldg(wptr);
+            }
+            // costs (and running sums) of this step from the stage
+            const int pos = kH ? (SD == 0 ? i : g_here - 1 - i) : i;
+            const uint32_t row = kH ? (uint32_t)(warp * G + pos) : (uint32_t)(i * NW + warp);
+            const uint8_t *src = stage + ((size_t)row * D + d0) * 4;
+            float c[KPL], a[NACC >= 1 ? KPL : 1], b[NACC >= 2 ? KPL : 1];
+#pragma unroll
+            for (int j = 0; j < KPL / 4; ++j) {
+                if (valid4[j]) {
+                    const float4 v = *reinterpret_cast<const float4 *>(src + 16 * j);
+                    c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
+                    if (NACC >= 1) {
+                        const float4 u = *reinterpret_cast<const float4 *>(src + array_bytes + 16 * j);
+                        a[4 * j] = u.x; a[4 * j + 1] = u.y; a[4 * j + 2] = u.z; a[4 * j + 3] = u.w;
+                    }
+                    if (NACC >= 2) {
+                        const float4 u = *reinterpret_cast<const float4 *>(src + 2 * array_bytes + 16 * j);
+                        b[4 * j] = u.x; b[4 * j + 1] = u.y; b[4 * j + 2] = u.z; b[4 * j + 3] = u.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        c[4 * j + e] = kSgmBig;           // stays kSgmBig through the step: "no such disparity"
+                        if (NACC >= 1) a[4 * j + e] = 0.f;
+                        if (NACC >= 2) b[4 * j + e] = 0.f;
+                    }
+                }
+            }
+            float val[KPL];
+            if (step == 0) {
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) val[k] = c[k];
+            } else {
+                sgm_step_coded<SD, KPL>(pen, want, c, prev, code, has_below, has_above, val);
+            }
+#pragma unroll
+            for (int j = 0; j < KPL / 4; ++j) {
+                if (valid4[j]) {
+                    float r[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float acc = val[4 * j + e];
+                        if (NACC == 1) acc = __fadd_rn(a[4 * j + e], acc);
+                        if (NACC == 2) acc = __fadd_rn(__fadd_rn(a[4 * j + e], b[4 * j + e]), acc);
+                        r[e] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
+                    }
+                    reinterpret_cast<float4 *>(optr)[j] = make_float4(r[0], r[1], r[2], r[3]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) prev[k] = val[k];
+            optr += vstride;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+    }
+}
+
+// Classifies the guide differences of the four paths (0: left->right, 1: right->left, 2: down, 3: up) against tau
+// with the original's comparisons: D1 = |x0(p) - x0(p - r)|, D2 = |x1(q) - x1(q - r)| with q = (xx, y) the matched
+// pixel, 10 where q or q - r (horizontally) is outside the image.  Rows / columns whose predecessor lies outside
+// (the first step of a path) are never read.
+__global__ void sgm_prep_kernel(const float *__restrict__ x0, const float *__restrict__ x1, int h, int w, float tau,
+                                int pad, int pitch, uint8_t *__restrict__ want, uint8_t *__restrict__ code)
+{
+    const size_t total = (size_t)h * pitch;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+        const int y = (int)(idx / pitch), xx = (int)(idx % pitch) - pad;
+#pragma unroll
+        for (int sd = 0; sd < 4; ++sd) {
+            const int dx = sd == 0 ? 1 : (sd == 1 ? -1 : 0), dy = sd == 2 ? 1 : (sd == 3 ? -1 : 0);
+            const int yp = y - dy, xp = xx - dx;
+            const bool row_ok = (unsigned)yp < (unsigned)h;
+            const bool inside = (unsigned)xx < (unsigned)w && (unsigned)xp < (unsigned)w && row_ok;
+            const float D2 = inside ? fabsf(x1[(size_t)y * w + xx] - x1[(size_t)yp * w + xp]) : 10.f;
+            code[((size_t)sd * h + y) * pitch + xx + pad] = D2 < tau ? 1 : (D2 > tau ? 2 : 0);
+            if ((unsigned)xx < (unsigned)w) {
+                const float D1 = inside ? fabsf(x0[(size_t)y * w + xx] - x0[(size_t)yp * w + xp]) : 0.f;
+                want[((size_t)sd * h + y) * w + xx] = D1 < tau ? 1 : (D1 > tau ? 2 : 3);
+            }
+        }
+    }
+}
+
+// both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
+template <int KPL, int NW, int DIR>
+__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
+                                                                   float *out_a, float *out_b, int h, int w, int D,
+                                                                   SgmParams p, int G, int S)
+{
+    if (blockIdx.y == 0)
+        sgm_ring_scan<0, 0, KPL, NW, DIR>(aux, cvol, nullptr, nullptr, out_a, h, w, D, p, 0, G, S, blockIdx.x);
+    else
+        sgm_ring_scan<1, 0, KPL, NW, DIR>(aux, cvol, nullptr, nullptr, out_b, h, w, D, p, 0, G, S, blockIdx.x);
+}
+
+// SD 2: a <- (a + b) + Lr (downward); SD 3: a <- (a + Lr) / 4 (upward)
+template <int SD, int KPL, int NW, int DIR>
+__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
+                                                                   float *out_a, const float *out_b, int h, int w, int D,
+                                                                   SgmParams p, int G, int S)
+{
+    if (SD == 2)
+        sgm_ring_scan<2, 2, KPL, NW, DIR>(aux, cvol, out_a, out_b, out_a, h, w, D, p, 0, G, S, blockIdx.x);
+    else
+        sgm_ring_scan<3, 1, KPL, NW, DIR>(aux, cvol, out_a, nullptr, out_a, h, w, D, p, 1, G, S, blockIdx.x);
+}
+
+struct RingShape {
+    int G, S;
+    size_t smem;
+};
+
+// stages of about `stage_target` bytes, as many as fit into `budget` (2..kMaxStages)
+RingShape ring_shape(int arrays, int nw, int D, bool horizontal, size_t stage_target, size_t budget)
+{
+    const size_t unit = (size_t)arrays * nw * D * 4;          // one step of the CTA's scanlines
+    int G = horizontal ? (int)std::max<size_t>(1, stage_target / unit) : 1;
+    if (!horizontal && 2 * unit <= stage_target) G = 2;
+    G = std::min(G, 16);
+    int S = (int)std::min<size_t>(kMaxStages, budget / (unit * G));
+    while (S < 2 && G > 1) {
+        G /= 2;
+        S = (int)std::min<size_t>(kMaxStages, budget / (unit * G));
+    }
+    return {G, S, (size_t)S * unit * G + 2 * 8 * kMaxStages};
+}
+
+template <int KPL, int NW, int DIR>
+int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a, float *out_b,
+                  int h, int w, int D, const SgmParams &p)
+{
+    const RingShape sh_h = ring_shape(1, NW, D, true, 32 * 1024, 96 * 1024);
+    const RingShape sh_v2 = ring_shape(3, NW, D, false, 24 * 1024, 72 * 1024);
+    const RingShape sh_v3 = ring_shape(2, NW, D, false, 16 * 1024, 72 * 1024);
+    if (sh_h.S < 2 || sh_v2.S < 2 || sh_v3.S < 2) {
+        set_error("sgm ring: disp_range %d does not fit the shared-memory stages", D);
+        return STEREO_E_LIMIT;
+    }
+    // classified guide differences, one set per side (the two sides of the post chain run on two streams)
+    SgmAux aux;
+    aux.pad = 32 * KPL + 4;
+    aux.pitch = w + 2 * aux.pad;
+    DevBuf &buf = ctx->sgm_aux[DIR > 0];
+    const size_t want_bytes = (size_t)4 * h * w, code_bytes = (size_t)4 * h * aux.pitch;
+    STEREO_TRY(buf.reserve(want_bytes + code_bytes));
+    uint8_t *want = buf.as<uint8_t>(), *code = want + want_bytes;
+    aux.want = want;
+    aux.code = code;
+    sgm_prep_kernel<<<std::min<size_t>(((size_t)h * aux.pitch + 255) / 256, 148 * 8), 256, 0, ctx->stream>>>(
+        x0, x1, h, w, p.tau_so, aux.pad, aux.pitch, want, code);
+
+    auto kh = sgm_ring_h_kernel<KPL, NW, DIR>;
+    auto kv2 = sgm_ring_v_kernel<2, KPL, NW, DIR>;
+    auto kv3 = sgm_ring_v_kernel<3, KPL, NW, DIR>;
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(kh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_h.smem));
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v2.smem));
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v3.smem));
+    const int threads = (NW + 1) * 32;
+    kh<<<dim3((h + NW - 1) / NW, 2), threads, sh_h.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_h.G, sh_h.S);
+    kv2<<<(w + NW - 1) / NW, threads, sh_v2.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v2.G, sh_v2.S);
+    kv3<<<(w + NW - 1) / NW, threads, sh_v3.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v3.G, sh_v3.S);
+    ctx->launches += 4;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+template <int DIR>
+int launch_ring_dir(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
+                    int h, int w, int D, const SgmParams &p)
+{
+    if (D <= 128) return launch_ring_t<4, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    if (D <= 256) return launch_ring_t<8, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    return launch_ring_t<16, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+}
+
+}  // namespace
+
+bool sgm_ring_usable(const float *cvol, const float *out, const float *scratch, int D)
+{
+    return D % 4 == 0 && D <= 512 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+           ((uintptr_t)scratch % 16 == 0);
+}
+
+int launch_sgm_ring(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
+                    int h, int w, int D, const SgmParams &p, int direction)
+{
+    return direction > 0 ? launch_ring_dir<1>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
+                         : launch_ring_dir<-1>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+}
+
+}  // namespace stereo

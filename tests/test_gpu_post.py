@@ -91,10 +91,12 @@ def test_sgm_bit_exact(ctx, scene, direction):
     assert np.array_equal(np.transpose(out, (2, 0, 1)), ref)
 
 
-@pytest.mark.parametrize("D", [33, 201])
-def test_sgm_ragged_disparity_ranges(ctx, D):
+@pytest.mark.parametrize("D,h,w", [(33, 6, 40), (201, 6, 40), (228, 9, 45), (132, 7, 70), (260, 5, 41), (64, 13, 37),
+                                   (4, 5, 9), (512, 3, 18)])
+def test_sgm_ragged_disparity_ranges(ctx, D, h, w):
+    """D % 4 != 0 runs the register-prefetch kernels, the rest the shared-memory ring kernels (sgm_ring.cu):
+    scanline counts that do not fill the last CTA, stages cut short at the end of a scanline."""
     rng = np.random.default_rng(D)
-    h, w = 6, 40
     l_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
     r_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
     vol = rng.standard_normal((h, w, D)).astype(np.float32)
