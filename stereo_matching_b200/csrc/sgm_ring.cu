@@ -11,7 +11,8 @@
 // path, padded so that no range check is left), and a step reads 8 bytes per lane one step ahead instead of
 // gathering and comparing guide values.  The path-cost arithmetic is the original's, operation for operation
 // (sgm_step_coded() in sgm_step.cuh): results are bit-identical to the register-prefetch kernels.
-// Needs D % 4 == 0 and 16-byte aligned volumes (bulk copies); launch_sgm() falls back to post.cu otherwise.
+// D % 4 != 0 or volumes that are not 16-byte aligned take the same kernels: the bulk copies then fetch the
+// 16-byte aligned superset of each run and the lanes read 4-byte words.
 #include <algorithm>
 
 #include "common.cuh"
@@ -31,7 +32,20 @@ struct SgmAux {
     int pad, pitch;
 };
 
-template <int SD, int NACC, int KPL, int NW, int DIR>
+// Shared-memory layout of one stage: per array (costs, running sums) a row of SLOTS, one per bulk copy:
+//   horizontal: slot = scanline of the CTA, holding G consecutive steps   (G * D floats)
+//   vertical:   slot = step of the stage, holding the NW scanlines        (NW * D floats)
+// Aligned volumes (D % 4 == 0, 16-byte aligned pointers): a slot is exactly its floats, read with 16-byte loads.
+// Otherwise (e.g. the reference's default D = 201) the bulk copy fetches the 16-byte aligned superset of the run
+// into a slot 32 bytes larger, the run starts `phase` = (address mod 16) bytes into the slot, and the lanes read
+// 4-byte words.  The superset reaches at most 12 bytes before / after the run, inside the volume's allocation
+// granule.
+__host__ __device__ inline uint32_t ring_slot_bytes(bool aligned, uint32_t run_floats)
+{
+    return aligned ? run_floats * 4 : ((run_floats * 4 + 15) & ~15u) + 32;
+}
+
+template <int SD, int NACC, int KPL, int NW, int DIR, bool ALIGNED>
 __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__restrict__ cvol, const float *acc_a,
                                               const float *acc_b, float *outp, int h, int w, int D, const SgmParams &p,
                                               int last, int G, int S, int group)
@@ -47,11 +61,13 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     const int line0 = group * NW;
     const int lines_here = min(NW, n_lines - line0);
     const int n_stages = (steps + G - 1) / G;
-    const uint32_t array_bytes = (uint32_t)NW * G * D * 4;            // one array of one stage
+    const uint32_t slot_bytes = ring_slot_bytes(ALIGNED, (uint32_t)(kH ? G : NW) * D);
+    const uint32_t array_bytes = (uint32_t)(kH ? NW : G) * slot_bytes;  // one array of one stage
     const uint32_t stage_bytes = kArrays * array_bytes;
     const uint32_t s_data = smem_u32(smem);
     const uint32_t s_bar = s_data + (uint32_t)S * stage_bytes;
     const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages;
+    const float *src[3] = {cvol, acc_a, acc_b};
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < S; ++i) {
@@ -62,33 +78,36 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     }
     __syncthreads();
 
+    // global element offset of the run that fills slot `k` of stage `t`
+    auto run_start = [&](int t, int k, int g_here) -> size_t {
+        if (kH) {       // scanline line0 + k, g_here consecutive pixels; the right-to-left path walks them backwards
+            const int x_lo = SD == 0 ? t * G : w - t * G - g_here;
+            return ((size_t)(line0 + k) * w + x_lo) * D;
+        }
+        const int y = SD == 2 ? t * G + k : h - 1 - (t * G + k);      // step k of the stage: one image row
+        return ((size_t)y * w + line0) * D;
+    };
+
     if (warp == NW) {
         // ---- producer: one lane issues the bulk copies of every stage ----
         if (lane != 0) return;
-        const float *src[3] = {cvol, acc_a, acc_b};
         for (int t = 0; t < n_stages; ++t) {
             const int s = t % S;
             mbar_wait(bar_empty + 8 * s, ((t / S) & 1) ^ 1);
             const int g_here = min(G, steps - t * G);
+            const int n_slots = kH ? lines_here : g_here;
+            const uint32_t run_bytes = (uint32_t)(kH ? g_here : lines_here) * D * 4;
             const uint32_t dst0 = s_data + (uint32_t)s * stage_bytes;
-            if (kH) {
-                // per scanline: g_here consecutive pixels; the right-to-left path walks its granule backwards
-                const uint32_t bytes = (uint32_t)g_here * D * 4;
-                mbar_expect_tx(bar_full + 8 * s, bytes * lines_here * kArrays);
-                const int x_lo = SD == 0 ? t * G : w - t * G - g_here;
+            uint32_t total = 0;
+            for (int pass = 0; pass < 2; ++pass) {          // pass 0 adds up the bytes, pass 1 issues the copies
+                if (pass == 1) mbar_expect_tx(bar_full + 8 * s, total);
                 for (int a = 0; a < kArrays; ++a)
-                    for (int q = 0; q < lines_here; ++q)
-                        bulk_g2s(dst0 + a * array_bytes + (uint32_t)q * G * D * 4,
-                                 src[a] + ((size_t)(line0 + q) * w + x_lo) * D, bytes, bar_full + 8 * s);
-            } else {
-                // per step: the lines_here adjacent pixels of one image row
-                const uint32_t bytes = (uint32_t)lines_here * D * 4;
-                mbar_expect_tx(bar_full + 8 * s, bytes * g_here * kArrays);
-                for (int a = 0; a < kArrays; ++a)
-                    for (int i = 0; i < g_here; ++i) {
-                        const int y = SD == 2 ? t * G + i : h - 1 - (t * G + i);
-                        bulk_g2s(dst0 + a * array_bytes + (uint32_t)i * NW * D * 4, src[a] + ((size_t)y * w + line0) * D,
-                                 bytes, bar_full + 8 * s);
+                    for (int k = 0; k < n_slots; ++k) {
+                        const uintptr_t from = (uintptr_t)(src[a] + run_start(t, k, g_here));
+                        const uintptr_t lo = ALIGNED ? from : from & ~(uintptr_t)15;
+                        const uint32_t len = ALIGNED ? run_bytes : (uint32_t)(((from + run_bytes + 15) & ~(uintptr_t)15) - lo);
+                        if (pass == 0) total += len;
+                        else bulk_g2s(dst0 + a * array_bytes + (uint32_t)k * slot_bytes, (const void *)lo, len, bar_full + 8 * s);
                     }
             }
         }
@@ -104,7 +123,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     const SgmPenalties<SD> pen(p);
     bool valid4[KPL / 4];
 #pragma unroll
-    for (int j = 0; j < KPL / 4; ++j) valid4[j] = d0 + 4 * j < D;      // D % 4 == 0: whole float4s
+    for (int j = 0; j < KPL / 4; ++j) valid4[j] = d0 + 4 * j < D;      // whole float4s when D % 4 == 0
     const bool has_below = lane > 0, has_above = d0 + KPL < D;
 
     // classified guide differences of the NEXT step (bytes; one step ahead of their use)
@@ -140,30 +159,45 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                 want_n = __ldg(wptr);
             }
             // costs (and running sums) of this step from the stage
-            const int pos = kH ? (SD == 0 ? i : g_here - 1 - i) : i;
-            const uint32_t row = kH ? (uint32_t)(warp * G + pos) : (uint32_t)(i * NW + warp);
-            const uint8_t *src = stage + ((size_t)row * D + d0) * 4;
+            const int slot = kH ? warp : i;
+            const int inner = kH ? (SD == 0 ? i : g_here - 1 - i) : warp;        // run-relative pixel
+            const uint8_t *base = stage + (uint32_t)slot * slot_bytes + ((uint32_t)inner * D + d0) * 4;
             float c[KPL], a[NACC >= 1 ? KPL : 1], b[NACC >= 2 ? KPL : 1];
+            if (ALIGNED) {
 #pragma unroll
-            for (int j = 0; j < KPL / 4; ++j) {
-                if (valid4[j]) {
-                    const float4 v = *reinterpret_cast<const float4 *>(src + 16 * j);
-                    c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
-                    if (NACC >= 1) {
-                        const float4 u = *reinterpret_cast<const float4 *>(src + array_bytes + 16 * j);
-                        a[4 * j] = u.x; a[4 * j + 1] = u.y; a[4 * j + 2] = u.z; a[4 * j + 3] = u.w;
-                    }
-                    if (NACC >= 2) {
-                        const float4 u = *reinterpret_cast<const float4 *>(src + 2 * array_bytes + 16 * j);
-                        b[4 * j] = u.x; b[4 * j + 1] = u.y; b[4 * j + 2] = u.z; b[4 * j + 3] = u.w;
-                    }
-                } else {
+                for (int j = 0; j < KPL / 4; ++j) {
+                    if (valid4[j]) {
+                        const float4 v = *reinterpret_cast<const float4 *>(base + 16 * j);
+                        c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
+                        if (NACC >= 1) {
+                            const float4 u = *reinterpret_cast<const float4 *>(base + array_bytes + 16 * j);
+                            a[4 * j] = u.x; a[4 * j + 1] = u.y; a[4 * j + 2] = u.z; a[4 * j + 3] = u.w;
+                        }
+                        if (NACC >= 2) {
+                            const float4 u = *reinterpret_cast<const float4 *>(base + 2 * array_bytes + 16 * j);
+                            b[4 * j] = u.x; b[4 * j + 1] = u.y; b[4 * j + 2] = u.z; b[4 * j + 3] = u.w;
+                        }
+                    } else {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        c[4 * j + e] = kSgmBig;           // stays kSgmBig through the step: "no such disparity"
-                        if (NACC >= 1) a[4 * j + e] = 0.f;
-                        if (NACC >= 2) b[4 * j + e] = 0.f;
+                        for (int e = 0; e < 4; ++e) {
+                            c[4 * j + e] = kSgmBig;           // stays kSgmBig through the step: "no such disparity"
+                            if (NACC >= 1) a[4 * j + e] = 0.f;
+                            if (NACC >= 2) b[4 * j + e] = 0.f;
+                        }
                     }
+                }
+            } else {
+                // the run sits `phase` bytes into its slot (per array: the volumes need not share an alignment)
+                const size_t e0 = run_start(t, slot, g_here);
+                uint32_t ph[kArrays];
+#pragma unroll
+                for (int q = 0; q < kArrays; ++q) ph[q] = (uint32_t)((uintptr_t)(src[q] + e0) & 15) + q * array_bytes;
+#pragma unroll
+                for (int k = 0; k < KPL; ++k) {
+                    const bool ok = d0 + k < D;
+                    c[k] = ok ? *reinterpret_cast<const float *>(base + ph[0] + 4 * k) : kSgmBig;
+                    if (NACC >= 1) a[k] = ok ? *reinterpret_cast<const float *>(base + ph[NACC >= 1 ? 1 : 0] + 4 * k) : 0.f;
+                    if (NACC >= 2) b[k] = ok ? *reinterpret_cast<const float *>(base + ph[NACC >= 2 ? 2 : 0] + 4 * k) : 0.f;
                 }
             }
             float val[KPL];
@@ -184,7 +218,13 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                         if (NACC == 2) acc = __fadd_rn(__fadd_rn(a[4 * j + e], b[4 * j + e]), acc);
                         r[e] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
                     }
-                    reinterpret_cast<float4 *>(optr)[j] = make_float4(r[0], r[1], r[2], r[3]);
+                    if (ALIGNED) {
+                        reinterpret_cast<float4 *>(optr)[j] = make_float4(r[0], r[1], r[2], r[3]);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (d0 + 4 * j + e < D) optr[4 * j + e] = r[e];
+                    }
                 }
             }
 #pragma unroll
@@ -223,27 +263,27 @@ __global__ void sgm_prep_kernel(const float *__restrict__ x0, const float *__res
 }
 
 // both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
-template <int KPL, int NW, int DIR>
+template <int KPL, int NW, int DIR, bool ALIGNED>
 __global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
     if (blockIdx.y == 0)
-        sgm_ring_scan<0, 0, KPL, NW, DIR>(aux, cvol, nullptr, nullptr, out_a, h, w, D, p, 0, G, S, blockIdx.x);
+        sgm_ring_scan<0, 0, KPL, NW, DIR, ALIGNED>(aux, cvol, nullptr, nullptr, out_a, h, w, D, p, 0, G, S, blockIdx.x);
     else
-        sgm_ring_scan<1, 0, KPL, NW, DIR>(aux, cvol, nullptr, nullptr, out_b, h, w, D, p, 0, G, S, blockIdx.x);
+        sgm_ring_scan<1, 0, KPL, NW, DIR, ALIGNED>(aux, cvol, nullptr, nullptr, out_b, h, w, D, p, 0, G, S, blockIdx.x);
 }
 
 // SD 2: a <- (a + b) + Lr (downward); SD 3: a <- (a + Lr) / 4 (upward)
-template <int SD, int KPL, int NW, int DIR>
+template <int SD, int KPL, int NW, int DIR, bool ALIGNED>
 __global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, const float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
     if (SD == 2)
-        sgm_ring_scan<2, 2, KPL, NW, DIR>(aux, cvol, out_a, out_b, out_a, h, w, D, p, 0, G, S, blockIdx.x);
+        sgm_ring_scan<2, 2, KPL, NW, DIR, ALIGNED>(aux, cvol, out_a, out_b, out_a, h, w, D, p, 0, G, S, blockIdx.x);
     else
-        sgm_ring_scan<3, 1, KPL, NW, DIR>(aux, cvol, out_a, nullptr, out_a, h, w, D, p, 1, G, S, blockIdx.x);
+        sgm_ring_scan<3, 1, KPL, NW, DIR, ALIGNED>(aux, cvol, out_a, nullptr, out_a, h, w, D, p, 1, G, S, blockIdx.x);
 }
 
 struct RingShape {
@@ -252,27 +292,29 @@ struct RingShape {
 };
 
 // stages of about `stage_target` bytes, as many as fit into `budget` (2..kMaxStages)
-RingShape ring_shape(int arrays, int nw, int D, bool horizontal, size_t stage_target, size_t budget)
+RingShape ring_shape(int arrays, int nw, int D, bool horizontal, bool aligned, size_t stage_target, size_t budget)
 {
-    const size_t unit = (size_t)arrays * nw * D * 4;          // one step of the CTA's scanlines
-    int G = horizontal ? (int)std::max<size_t>(1, stage_target / unit) : 1;
-    if (!horizontal && 2 * unit <= stage_target) G = 2;
-    G = std::min(G, 16);
-    int S = (int)std::min<size_t>(kMaxStages, budget / (unit * G));
+    auto stage = [&](int G) {
+        return horizontal ? (size_t)arrays * nw * ring_slot_bytes(aligned, (uint32_t)G * D)
+                          : (size_t)arrays * G * ring_slot_bytes(aligned, (uint32_t)nw * D);
+    };
+    int G = horizontal ? 16 : 2;
+    while (G > 1 && stage(G) > stage_target) G = horizontal ? G - 1 : 1;
+    int S = (int)std::min<size_t>(kMaxStages, budget / stage(G));
     while (S < 2 && G > 1) {
-        G /= 2;
-        S = (int)std::min<size_t>(kMaxStages, budget / (unit * G));
+        --G;
+        S = (int)std::min<size_t>(kMaxStages, budget / stage(G));
     }
-    return {G, S, (size_t)S * unit * G + 2 * 8 * kMaxStages};
+    return {G, S, (size_t)S * stage(G) + 2 * 8 * kMaxStages};
 }
 
-template <int KPL, int NW, int DIR>
+template <int KPL, int NW, int DIR, bool ALIGNED>
 int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a, float *out_b,
                   int h, int w, int D, const SgmParams &p)
 {
-    const RingShape sh_h = ring_shape(1, NW, D, true, 32 * 1024, 96 * 1024);
-    const RingShape sh_v2 = ring_shape(3, NW, D, false, 24 * 1024, 72 * 1024);
-    const RingShape sh_v3 = ring_shape(2, NW, D, false, 16 * 1024, 72 * 1024);
+    const RingShape sh_h = ring_shape(1, NW, D, true, ALIGNED, 32 * 1024, 96 * 1024);
+    const RingShape sh_v2 = ring_shape(3, NW, D, false, ALIGNED, 24 * 1024, 72 * 1024);
+    const RingShape sh_v3 = ring_shape(2, NW, D, false, ALIGNED, 16 * 1024, 72 * 1024);
     if (sh_h.S < 2 || sh_v2.S < 2 || sh_v3.S < 2) {
         set_error("sgm ring: disp_range %d does not fit the shared-memory stages", D);
         return STEREO_E_LIMIT;
@@ -290,9 +332,9 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     sgm_prep_kernel<<<std::min<size_t>(((size_t)h * aux.pitch + 255) / 256, 148 * 8), 256, 0, ctx->stream>>>(
         x0, x1, h, w, p.tau_so, aux.pad, aux.pitch, want, code);
 
-    auto kh = sgm_ring_h_kernel<KPL, NW, DIR>;
-    auto kv2 = sgm_ring_v_kernel<2, KPL, NW, DIR>;
-    auto kv3 = sgm_ring_v_kernel<3, KPL, NW, DIR>;
+    auto kh = sgm_ring_h_kernel<KPL, NW, DIR, ALIGNED>;
+    auto kv2 = sgm_ring_v_kernel<2, KPL, NW, DIR, ALIGNED>;
+    auto kv3 = sgm_ring_v_kernel<3, KPL, NW, DIR, ALIGNED>;
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_h.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v2.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v3.smem));
@@ -305,28 +347,34 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     return STEREO_OK;
 }
 
-template <int DIR>
+template <int DIR, bool ALIGNED>
 int launch_ring_dir(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                     int h, int w, int D, const SgmParams &p)
 {
-    if (D <= 128) return launch_ring_t<4, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
-    if (D <= 256) return launch_ring_t<8, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
-    return launch_ring_t<16, 4, DIR>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    if (D <= 128) return launch_ring_t<4, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    if (D <= 256) return launch_ring_t<8, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    return launch_ring_t<16, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
 }
 
 }  // namespace
 
 bool sgm_ring_usable(const float *cvol, const float *out, const float *scratch, int D)
 {
-    return D % 4 == 0 && D <= 512 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
-           ((uintptr_t)scratch % 16 == 0);
+    (void)cvol; (void)out; (void)scratch;
+    return D <= 512;
 }
 
 int launch_sgm_ring(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                     int h, int w, int D, const SgmParams &p, int direction)
 {
-    return direction > 0 ? launch_ring_dir<1>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
-                         : launch_ring_dir<-1>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    // bulk copies and 16-byte accesses need every [x][d] row to start 16-byte aligned
+    const bool aligned = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
+                         ((uintptr_t)scratch % 16 == 0);
+    if (aligned)
+        return direction > 0 ? launch_ring_dir<1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
+                             : launch_ring_dir<-1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    return direction > 0 ? launch_ring_dir<1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
+                         : launch_ring_dir<-1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
 }
 
 }  // namespace stereo

@@ -74,3 +74,39 @@ def test_variant_matches_oracle(env, reference_maps, tmp_path):
         # the labels are an exact integer function of the two maps the same call returned
         lab = po.outlier_detection(got["left"][i].astype(np.float32), got["right"][i].astype(np.float32), D)
         assert np.array_equal(got["lr"][i], lab.astype(np.uint8))
+
+
+SGM_CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib
+ctx = _lib.Context(0)
+out = {}
+for D, h, w in ((228, 21, 150), (201, 10, 77), (48, 33, 61)):
+    rng = np.random.default_rng(D)
+    l_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    r_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    vol = rng.standard_normal((h, w, D)).astype(np.float32)
+    for direction in (-1, 1):
+        out["%d_%d" % (D, direction)] = ctx.nyu_sgm(l_img, r_img, vol, direction)
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_sgm_kernel_families_agree_bit_for_bit(tmp_path):
+    """STEREO_SGM_KERNEL=1 (register prefetch, post.cu) against the default shared-memory ring kernels
+    (sgm_ring.cu; aligned bulk-copy and unaligned cp.async variants); the ring kernels are checked against the C
+    restatement in test_gpu_post.py."""
+    maps = {}
+    for name, env in (("ring", {}), ("regs", {"STEREO_SGM_KERNEL": "1"})):
+        e = dict(os.environ)
+        e.update(env)
+        out = tmp_path / (name + ".npz")
+        r = subprocess.run([sys.executable, "-c", SGM_CHILD, ROOT, str(out)], env=e, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        maps[name] = np.load(out)
+    assert sorted(maps["ring"].files) == sorted(maps["regs"].files) and len(maps["ring"].files) == 6
+    for k in maps["ring"].files:
+        assert np.array_equal(maps["ring"][k], maps["regs"][k]), k
