@@ -437,7 +437,7 @@ int stereo_destroy(stereo_ctx *ctx)
                       &ctx->padded, &ctx->act[0], &ctx->act[1], &ctx->feat, &ctx->stage_in[0], &ctx->stage_in[1],
                       &ctx->stage_out[0], &ctx->stage_out[1], &ctx->stage_out[2], &ctx->stage_vol[0],
                       &ctx->stage_vol[1], &ctx->scratch, &ctx->post_vol[0], &ctx->post_vol[1], &ctx->post_vol[2], &ctx->post_vol[3], &ctx->post_vol[4], &ctx->post_vol[5], &ctx->post_vol[6], &ctx->post_vol[7],
-                      &ctx->post_cnt[0], &ctx->post_cnt[1], &ctx->sgm_aux[0], &ctx->sgm_aux[1],
+                      &ctx->post_cnt[0], &ctx->post_cnt[1], &ctx->sgm_aux[0], &ctx->sgm_aux[1], &ctx->cbca_rec[0], &ctx->cbca_rec[1],
                       &ctx->post_maps, &ctx->pp_maps, &ctx->featp, &ctx->featp_b[0], &ctx->featp_b[1], &ctx->featp_b[2], &ctx->act_b[0],
                       &ctx->act_b[1], &ctx->act_b[2], &ctx->act_b[3], &ctx->act_b[4], &ctx->act_b[5]};
     for (DevBuf *b : bufs) b->release();

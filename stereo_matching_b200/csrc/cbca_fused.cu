@@ -1,0 +1,164 @@
+// adcensus.cbca (smooth/nyu.lua:37-40) in ONE pass over the volume, for arm lengths up to L1 = 5.
+//
+// The separable form in post.cu writes the row-segment sums (hsum, fp32) and lengths (hcnt, uint8) of every voxel
+// to HBM and reads them back nine rows at a time: 1.84 GB of DRAM traffic and ~260 instructions per voxel for
+// 0.85 GB of algorithmic bytes.  Here a thread owns one disparity of FOUR neighbouring pixels and walks down a band
+// of image rows: for every row it forms the four row-segment sums from 12 loaded costs (as cbca_h4_kernel does) and
+// keeps the last nine rows of (sum, length) in registers; the output of row y - 4 is the sum over the rows its
+// vertical arms admit (as cbca_v4_kernel does).  Same additions in the same order as the two-pass kernels, so the
+// results are bit-identical to them; nothing but the volume is read and nothing but the result written.
+//
+// Arms are repacked once per call into one 32-bit record per pixel holding the four exclusive arm ends RELATIVE to
+// the pixel (left <= -1, right >= 1, up <= -1, down >= 1 as int8): the matched pixel's horizontal arms
+// "x1c[xm] - d*dir - x" are then simply its relative arms, and one load fetches all four.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace stereo {
+
+namespace {
+
+constexpr int kFR = 4;                   // window half width = L1 - 1
+constexpr int kFB = 4;                   // pixels per thread
+constexpr int kFN = kFB + 2 * kFR;       // costs loaded per row
+constexpr int kFW = 2 * kFR + 1;         // rows kept
+
+__global__ void cbca_pack_arms_kernel(const short *__restrict__ arms, int h, int w, int pitch, uint32_t *__restrict__ rec)
+{
+    const int total = h * pitch;
+    const int hw = h * w;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int y = idx / pitch, x = idx - y * pitch;
+        uint32_t r = 0x01ff01ffu;                            // padding columns: empty arms (-1, 1, -1, 1)
+        if (x < w) {
+            const int pix = y * w + x;
+            // exclusive ends lie beyond the pixel: the pixel itself always belongs to its support region
+            const int l = min(-1, max(-127, arms[pix] - x)), rt = max(1, min(127, arms[hw + pix] - x));
+            const int u = min(-1, max(-127, arms[2 * hw + pix] - y)), dn = max(1, min(127, arms[3 * hw + pix] - y));
+            r = (uint32_t)(l & 0xff) | ((uint32_t)(rt & 0xff) << 8) | ((uint32_t)(u & 0xff) << 16) | ((uint32_t)(dn & 0xff) << 24);
+        }
+        rec[idx] = r;
+    }
+}
+
+__device__ __forceinline__ int rec_byte(uint32_t r, int i) { return (int)(int8_t)(r >> (8 * i)); }
+
+__global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
+                                                         int pitch, const float *__restrict__ vol, float *__restrict__ out,
+                                                         int h, int w, int D, int direction, int rows_per_band)
+{
+    const int d = threadIdx.x;
+    if (d >= D) return;
+    const int xb = blockIdx.x * kFB;
+    const int y0 = blockIdx.y * rows_per_band, y1 = min(h, y0 + rows_per_band);
+    const int shift = d * direction;
+
+    int offs[kFN];                           // element offsets of the 12 columns inside a row (clamped: loads stay in the row)
+#pragma unroll
+    for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * D + d;
+    bool pix_ok[kFB], match_ok[kFB];
+    int xm[kFB];
+#pragma unroll
+    for (int i = 0; i < kFB; ++i) {
+        const int x = xb + i;
+        pix_ok[i] = x < w;
+        match_ok[i] = (unsigned)(x + shift) < (unsigned)w;
+        xm[i] = min(max(x + shift, 0), w - 1);
+    }
+
+    float hs[kFW][kFB];
+    int hc[kFW][kFB];
+#pragma unroll
+    for (int u = 0; u < kFW; ++u)
+#pragma unroll
+        for (int i = 0; i < kFB; ++i) { hs[u][i] = 0.f; hc[u][i] = 0; }
+    const int row_elems = w * D;
+
+    for (int base = y0 - kFR; base < y1 + kFR; base += kFW) {
+#pragma unroll
+        for (int u = 0; u < kFW; ++u) {
+            const int r = base + u;
+            if (r >= y1 + kFR) break;
+            if (r >= 0 && r < h) {
+                // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
+                const float *vrow = vol + (size_t)r * row_elems;
+                float v[kFN];
+#pragma unroll
+                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vrow + offs[j]);
+                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (size_t)r * pitch + xb);
+                const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
+                const uint32_t *m_row = rec1 + (size_t)r * pitch;
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) {
+                    const uint32_t m = __ldg(m_row + xm[i]);
+                    const int rs = max(rec_byte(own_r[i], 0), rec_byte(m, 0));
+                    const int rt = min(rec_byte(own_r[i], 1), rec_byte(m, 1));
+                    float sum = 0.f;
+#pragma unroll
+                    for (int jj = -kFR; jj <= kFR; ++jj) {       // columns x-R .. x+R, ascending
+                        const bool in = jj < 0 ? jj > rs : (jj > 0 ? jj < rt : true);
+                        sum = in ? __fadd_rn(sum, v[kFR + i + jj]) : sum;
+                    }
+                    // unmatched disparities are copied through: keep the cost itself, length 0
+                    hs[u][i] = match_ok[i] ? sum : v[kFR + i];
+                    hc[u][i] = match_ok[i] ? rt - rs - 1 : 0;
+                }
+            }
+            const int y = r - kFR;
+            if (y >= y0 && y < y1) {
+                // ---- output row y: rows y-R .. y+R sit in slots u+1 .. u+9 (mod 9) (cbca_v4_kernel) ----
+                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (size_t)y * pitch + xb);
+                const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
+                const uint32_t *m_row = rec1 + (size_t)y * pitch;
+                float *orow = out + (size_t)y * row_elems;
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) {
+                    if (!pix_ok[i]) continue;
+                    const uint32_t m = __ldg(m_row + xm[i]);
+                    const int us = max(rec_byte(own_r[i], 2), rec_byte(m, 2));
+                    const int ud = min(rec_byte(own_r[i], 3), rec_byte(m, 3));
+                    float sum = 0.f;
+                    int cnt = 0;
+#pragma unroll
+                    for (int jj = -kFR; jj <= kFR; ++jj) {       // rows y-R .. y+R, ascending
+                        const int slot = (u + 1 + jj + kFR) % kFW;
+                        const bool in = jj < 0 ? jj > us : (jj > 0 ? jj < ud : true);
+                        sum = in ? __fadd_rn(sum, hs[slot][i]) : sum;
+                        cnt = in ? cnt + hc[slot][i] : cnt;
+                    }
+                    const float centre = hs[(u + 1 + kFR) % kFW][i];
+                    orow[offs[kFR + i]] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
+                }
+            }
+        }
+    }
+}
+
+}  // namespace
+
+// x0c / x1c: int16 arms [4][h][w] of the two views; rec: scratch for 2 * h * pitch records
+int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
+                      int D, int direction, int L1)
+{
+    STEREO_REQUIRE((size_t)h * w * D < (size_t)1 << 31, "volume too large for 32-bit indexing");
+    STEREO_REQUIRE(D <= 256 && L1 - 1 <= kFR, "fused CBCA: D <= 256 and L1 <= %d, got D=%d L1=%d", kFR + 1, D, L1);
+    const int pitch = (w + 3) / 4 * 4 + 4;
+    DevBuf &buf = ctx->cbca_rec[direction > 0];
+    STEREO_TRY(buf.reserve((size_t)2 * h * pitch * sizeof(uint32_t)));
+    uint32_t *rec0 = buf.as<uint32_t>(), *rec1 = rec0 + (size_t)h * pitch;
+    ProfScope prof(ctx, STEREO_K_CBCA);
+    const int pack_blocks = std::min((h * pitch + 255) / 256, 148 * 8);
+    cbca_pack_arms_kernel<<<pack_blocks, 256, 0, ctx->stream>>>(x0c, h, w, pitch, rec0);
+    cbca_pack_arms_kernel<<<pack_blocks, 256, 0, ctx->stream>>>(x1c, h, w, pitch, rec1);
+    const int nt = (D + 31) / 32 * 32;
+    const int bands = std::max(1, (h + 62) / 63);
+    const int rows_per_band = (h + bands - 1) / bands;
+    cbca_fused_kernel<<<dim3((w + kFB - 1) / kFB, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D,
+                                                                                direction, rows_per_band);
+    ctx->launches += 3;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
+}  // namespace stereo

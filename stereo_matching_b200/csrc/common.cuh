@@ -112,6 +112,7 @@ struct stereo_ctx {
     cudaEvent_t lane_join[3] = {nullptr, nullptr, nullptr};
     stereo::DevBuf scratch;      // per-block partials of the volume reduction
     stereo::DevBuf post_vol[8];  // working volumes of the post chain: 4 per side (the sides run on two streams)
+    stereo::DevBuf cbca_rec[2];  // packed relative arms of the fused CBCA kernel, per side
     stereo::DevBuf sgm_aux[2];   // classified guide differences of the SGM ring kernels, per side
     stereo::DevBuf post_cnt[2];  // row-segment lengths of the separable CBCA (uint8 per voxel), per side
     cudaStream_t aux_stream = nullptr;   // second stream of the post chain
@@ -214,6 +215,9 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
                 int D, int direction);
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
+// cbca_fused.cu
+int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
+                      int D, int direction, int L1);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
 int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);

@@ -75,6 +75,9 @@ static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x
                     float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
 {
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
+    // default: one fused pass (cbca_fused.cu); STEREO_CBCA_KERNEL=1 keeps the two-pass separable kernels
+    static const bool fused = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return !(e && atoi(e) == 1); }();
+    if (fused && D <= 256 && p->L1 <= 5) return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1);
     STEREO_TRY(ctx->post_cnt[slot].reserve((size_t)h * w * D));
     return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt[slot].as<uint8_t>(), out, h, w, D, direction,
                                  p->L1);

@@ -90,16 +90,23 @@ for D, h, w in ((228, 21, 150), (201, 10, 77), (48, 33, 61)):
     vol = rng.standard_normal((h, w, D)).astype(np.float32)
     for direction in (-1, 1):
         out["%d_%d" % (D, direction)] = ctx.nyu_sgm(l_img, r_img, vol, direction)
+    # cross-based aggregation on piecewise-constant guides (arms of every length), two iterations
+    gl = np.repeat(np.repeat(rng.standard_normal((h // 3 + 1, w // 5 + 1)), 3, 0), 5, 1)[:h, :w].astype(np.float32) * 0.05
+    gr = np.roll(gl, -3, axis=1)
+    vol2 = rng.standard_normal((h, w, D)).astype(np.float32)
+    lv, rv = ctx.nyu_cross_agg(gl, gr, vol, vol2, 2)
+    out["cbca_l_%d" % D], out["cbca_r_%d" % D] = lv, rv
 np.savez(sys.argv[2], **out)
 """
 
 
-def test_sgm_kernel_families_agree_bit_for_bit(tmp_path):
+def test_post_kernel_families_agree_bit_for_bit(tmp_path):
     """STEREO_SGM_KERNEL=1 (register prefetch, post.cu) against the default shared-memory ring kernels
-    (sgm_ring.cu; aligned bulk-copy and unaligned cp.async variants); the ring kernels are checked against the C
-    restatement in test_gpu_post.py."""
+    (sgm_ring.cu; aligned and unaligned volumes), and STEREO_CBCA_KERNEL=1 (two-pass separable CBCA, post.cu)
+    against the default fused pass (cbca_fused.cu): same additions in the same order, so the bits must agree.  The
+    defaults are checked against the C restatement in test_gpu_post.py."""
     maps = {}
-    for name, env in (("ring", {}), ("regs", {"STEREO_SGM_KERNEL": "1"})):
+    for name, env in (("ring", {}), ("regs", {"STEREO_SGM_KERNEL": "1", "STEREO_CBCA_KERNEL": "1"})):
         e = dict(os.environ)
         e.update(env)
         out = tmp_path / (name + ".npz")
@@ -107,6 +114,6 @@ def test_sgm_kernel_families_agree_bit_for_bit(tmp_path):
                            timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         maps[name] = np.load(out)
-    assert sorted(maps["ring"].files) == sorted(maps["regs"].files) and len(maps["ring"].files) == 6
+    assert sorted(maps["ring"].files) == sorted(maps["regs"].files) and len(maps["ring"].files) == 12
     for k in maps["ring"].files:
         assert np.array_equal(maps["ring"][k], maps["regs"][k]), k
