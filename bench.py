@@ -469,6 +469,44 @@ def run_b200(args):
         except Exception as e:          # secondary measurement: never fail the bench line
             extra["training_step"] = {"error": repr(e)}
 
+    # ---- secondary: configs[2]-style base_model (win37) pairs: tensor-core trunk + fused correlation + LR check ----
+    if not args.no_post and rank == 0:
+        try:
+            from stereo_matching_b200 import synth as b200synth
+            from stereo_matching_b200.models.model import base_model as make_base_model
+            bm = make_base_model((None, None, 3), device=local_rank, precision=prec)
+            bm.set_layers(b200synth.make_base_model_weights())
+            bctx = bm.context
+            bctx.set_stream(stream.cuda_stream)
+            nb = min(n, 8)
+            with torch.cuda.stream(stream):
+                d_bo = torch.empty((nb, H, W), dtype=torch.uint8, device=dev)
+
+                def base_once():
+                    bctx.pairs_dev(bm.net, d_left.data_ptr(), d_right.data_ptr(), nb, H, W, D, prec,
+                                   d_ld.data_ptr(), d_rd.data_ptr(), d_bo.data_ptr(), None, None)
+
+                base_once()
+                torch.cuda.synchronize()
+                bctx.profile_enable(True)
+                be0, be1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                be0.record(stream)
+                base_once()
+                be1.record(stream)
+                torch.cuda.synchronize()
+                bprof = bctx.profile_read()
+                bctx.profile_enable(False)
+            bms = be0.elapsed_time(be1) / nb
+            conv_ms = bprof["conv"][0] / nb
+            extra["base_model"] = {
+                "workload": f"base_model (nine 5x5 layers, 37x37 receptive field), {nb} pairs, fused correlation + WTA + LR check",
+                "ms_per_pair": bms, "pairs_per_s": 1e3 / bms, "conv_ms_per_pair": conv_ms,
+                "conv_tflops_algorithmic": 1191.75e9 / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else None,
+                "note": "layers 2-9 on tcgen05 (conv_tcg.cu), 1 191.75 GFLOP per pair counted once; seeded synthetic weights "
+                        "(the reference ships none for base_model)"}
+        except Exception as e:          # secondary measurement: never fail the bench line
+            extra["base_model"] = {"error": repr(e)}
+
     # ---- CPU baseline (oracle port) on a bounded sample --------------------------------------------
     cpu = None
     if not args.no_cpu_baseline:

@@ -8,9 +8,11 @@
 // vertical arms admit (as cbca_v4_kernel does).  Same additions in the same order as the two-pass kernels, so the
 // results are bit-identical to them; nothing but the volume is read and nothing but the result written.
 //
-// Arms are repacked once per call into one 32-bit record per pixel holding the four exclusive arm ends RELATIVE to
-// the pixel (left <= -1, right >= 1, up <= -1, down >= 1 as int8): the matched pixel's horizontal arms
-// "x1c[xm] - d*dir - x" are then simply its relative arms, and one load fetches all four.
+// Arms are repacked once per call into one 32-bit record per pixel: bit b of byte 0 says whether the pixel's
+// horizontal arms reach column offset -4..-1, +1..+4 (b = 0..7), byte 1 the same for row offsets.  Relative to the
+// pixel, the matched pixel's arms "x1c[xm] - d*dir - x" are simply ITS relative arms, so the intersection of the two
+// support intervals is the bitwise AND of two records, the segment length a population count, and every
+// conditional addition one bit test - no arm arithmetic is left in the inner loops.
 #include <algorithm>
 
 #include "common.cuh"
@@ -24,25 +26,44 @@ constexpr int kFB = 4;                   // pixels per thread
 constexpr int kFN = kFB + 2 * kFR;       // costs loaded per row
 constexpr int kFW = 2 * kFR + 1;         // rows kept
 
+// bit of offset jj (-4..-1, 1..4) inside a mask byte
+__host__ __device__ constexpr uint32_t off_bit(int jj) { return 1u << (jj < 0 ? jj + kFR : jj + kFR - 1); }
+
 __global__ void cbca_pack_arms_kernel(const short *__restrict__ arms, int h, int w, int pitch, uint32_t *__restrict__ rec)
 {
     const int total = h * pitch;
     const int hw = h * w;
     for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
         const int y = idx / pitch, x = idx - y * pitch;
-        uint32_t r = 0x01ff01ffu;                            // padding columns: empty arms (-1, 1, -1, 1)
+        uint32_t r = 0;                                      // padding columns: the pixel alone
         if (x < w) {
             const int pix = y * w + x;
-            // exclusive ends lie beyond the pixel: the pixel itself always belongs to its support region
-            const int l = min(-1, max(-127, arms[pix] - x)), rt = max(1, min(127, arms[hw + pix] - x));
-            const int u = min(-1, max(-127, arms[2 * hw + pix] - y)), dn = max(1, min(127, arms[3 * hw + pix] - y));
-            r = (uint32_t)(l & 0xff) | ((uint32_t)(rt & 0xff) << 8) | ((uint32_t)(u & 0xff) << 16) | ((uint32_t)(dn & 0xff) << 24);
+            // exclusive arm ends relative to the pixel: offsets strictly between them belong to the support region
+            const int l = arms[pix] - x, rt = arms[hw + pix] - x, u = arms[2 * hw + pix] - y, dn = arms[3 * hw + pix] - y;
+#pragma unroll
+            for (int k = 1; k <= kFR; ++k) {
+                if (-k > l) r |= off_bit(-k);
+                if (k < rt) r |= off_bit(k);
+                if (-k > u) r |= off_bit(-k) << 8;
+                if (k < dn) r |= off_bit(k) << 8;
+            }
         }
         rec[idx] = r;
     }
 }
 
-__device__ __forceinline__ int rec_byte(uint32_t r, int i) { return (int)(int8_t)(r >> (8 * i)); }
+// sum += v if (mask & bit): one bit test and one predicated add
+__device__ __forceinline__ void add_if(float &sum, float v, uint32_t mask, uint32_t bit)
+{
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\tand.b32 t, %2, %3;\n\tsetp.ne.u32 p, t, 0;\n\t@p add.rn.f32 %0, %0, %1;\n\t}"
+        : "+f"(sum) : "f"(v), "r"(mask), "r"(bit));
+}
+__device__ __forceinline__ void add_if(float &sum, int &cnt, float v, int c, uint32_t mask, uint32_t bit)
+{
+    asm("{\n\t.reg .pred p;\n\t.reg .b32 t;\n\tand.b32 t, %4, %5;\n\tsetp.ne.u32 p, t, 0;\n\t@p add.rn.f32 %0, %0, %2;\n\t"
+        "@p add.s32 %1, %1, %3;\n\t}"
+        : "+f"(sum), "+r"(cnt) : "f"(v), "r"(c), "r"(mask), "r"(bit));
+}
 
 __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                          int pitch, const float *__restrict__ vol, float *__restrict__ out,
@@ -82,53 +103,50 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
             if (r >= y1 + kFR) break;
             if (r >= 0 && r < h) {
                 // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
-                const float *vrow = vol + (size_t)r * row_elems;
+                const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
                 float v[kFN];
 #pragma unroll
-                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vrow + offs[j]);
-                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (size_t)r * pitch + xb);
+                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (rbase + xb));
                 const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
-                const uint32_t *m_row = rec1 + (size_t)r * pitch;
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
-                    const uint32_t m = __ldg(m_row + xm[i]);
-                    const int rs = max(rec_byte(own_r[i], 0), rec_byte(m, 0));
-                    const int rt = min(rec_byte(own_r[i], 1), rec_byte(m, 1));
+                    const uint32_t cm = own_r[i] & __ldg(rec1 + (rbase + xm[i]));   // both arms reach the column
                     float sum = 0.f;
 #pragma unroll
-                    for (int jj = -kFR; jj <= kFR; ++jj) {       // columns x-R .. x+R, ascending
-                        const bool in = jj < 0 ? jj > rs : (jj > 0 ? jj < rt : true);
-                        sum = in ? __fadd_rn(sum, v[kFR + i + jj]) : sum;
+                    for (int jj = -kFR; jj <= kFR; ++jj) {           // columns x-R .. x+R, ascending
+                        if (jj == 0) sum = __fadd_rn(sum, v[kFR + i]);
+                        else add_if(sum, v[kFR + i + jj], cm, off_bit(jj));
                     }
                     // unmatched disparities are copied through: keep the cost itself, length 0
                     hs[u][i] = match_ok[i] ? sum : v[kFR + i];
-                    hc[u][i] = match_ok[i] ? rt - rs - 1 : 0;
+                    hc[u][i] = match_ok[i] ? __popc(cm & 0xffu) + 1 : 0;
                 }
             }
             const int y = r - kFR;
             if (y >= y0 && y < y1) {
                 // ---- output row y: rows y-R .. y+R sit in slots u+1 .. u+9 (mod 9) (cbca_v4_kernel) ----
-                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (size_t)y * pitch + xb);
+                const int rbase = y * pitch, obase = y * row_elems;
+                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (rbase + xb));
                 const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
-                const uint32_t *m_row = rec1 + (size_t)y * pitch;
-                float *orow = out + (size_t)y * row_elems;
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
                     if (!pix_ok[i]) continue;
-                    const uint32_t m = __ldg(m_row + xm[i]);
-                    const int us = max(rec_byte(own_r[i], 2), rec_byte(m, 2));
-                    const int ud = min(rec_byte(own_r[i], 3), rec_byte(m, 3));
+                    const uint32_t cm = (own_r[i] & __ldg(rec1 + (rbase + xm[i]))) >> 8;   // both arms reach the row
                     float sum = 0.f;
                     int cnt = 0;
 #pragma unroll
-                    for (int jj = -kFR; jj <= kFR; ++jj) {       // rows y-R .. y+R, ascending
+                    for (int jj = -kFR; jj <= kFR; ++jj) {           // rows y-R .. y+R, ascending
                         const int slot = (u + 1 + jj + kFR) % kFW;
-                        const bool in = jj < 0 ? jj > us : (jj > 0 ? jj < ud : true);
-                        sum = in ? __fadd_rn(sum, hs[slot][i]) : sum;
-                        cnt = in ? cnt + hc[slot][i] : cnt;
+                        if (jj == 0) {
+                            sum = __fadd_rn(sum, hs[slot][i]);
+                            cnt += hc[slot][i];
+                        } else {
+                            add_if(sum, cnt, hs[slot][i], hc[slot][i], cm, off_bit(jj));
+                        }
                     }
                     const float centre = hs[(u + 1 + kFR) % kFW][i];
-                    orow[offs[kFR + i]] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
+                    out[obase + offs[kFR + i]] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
                 }
             }
         }
