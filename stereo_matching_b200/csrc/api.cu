@@ -138,7 +138,11 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
             STEREO_TRY(launch_conv_ffma(ctx, nd.layer[0], wts, in, n, h, w, ctx->feat.as<float>()));
             STEREO_TRY(launch_nhwc_to_planar_g(ctx, ctx->feat.as<float>(), n, h1, w1, 32, wp, buf_hi[0],
                                                planes == 2 ? buf_lo[0] : nullptr));
-            const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>();
+            // STEREO_CONV5_KERNEL=1: conv_tcg.cu (one MMA per tap); default: conv_tcr.cu (each input row once)
+            static const bool per_tap = [] { const char *e = getenv("STEREO_CONV5_KERNEL"); return e && atoi(e) == 1; }();
+            size_t img_total = 0;
+            for (int l = 1; l < nd.n_layers; ++l) img_total += tcg_weight_image_elems(nd.layer[l].ks, nd.layer[l].cin, nd.layer[l].cout);
+            const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (per_tap ? 0 : img_total);
             int ch = h1, cw = w1, cur = 0;
             for (int l = 1; l < nd.n_layers; ++l) {
                 const LayerDesc &L = nd.layer[l];
@@ -150,8 +154,9 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
                     if (planar) { o_hi = planar->hi; o_lo = planar->lo; o_wp = planar->wf; }
                     else { o_hi = nullptr; o_lo = nullptr; o_f32 = out; }
                 }
-                STEREO_TRY(launch_conv_tcg(ctx, L.ks, L.cin, L.cout, buf_hi[cur], buf_lo[cur], n, ch, cw, wp, wimg,
-                                           wts + L.b_off, o_hi, o_lo, o_wp, o_f32, L.relu, planes));
+                STEREO_TRY((per_tap ? launch_conv_tcg : launch_conv_tcr)(ctx, L.ks, L.cin, L.cout, buf_hi[cur], buf_lo[cur], n, ch,
+                                                                         cw, wp, wimg, wts + L.b_off, o_hi, o_lo, o_wp,
+                                                                         o_f32, L.relu, planes));
                 wimg += tcg_weight_image_elems(L.ks, L.cin, L.cout);
                 ch -= L.ks - 1;
                 cw -= L.ks - 1;
@@ -570,12 +575,15 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
         // streaming units of conv_tcg.cu for layers 2-9, one after the other
         size_t total = 0;
         for (int l = 1; l < nd.n_layers; ++l) total += tcg_weight_image_elems(nd.layer[l].ks, nd.layer[l].cin, nd.layer[l].cout);
-        STEREO_TRY(ctx->wsplit[net].reserve(total * 2));
+        // two images of the same size: per-tap units (conv_tcg.cu), then per-kx units (conv_tcr.cu)
+        STEREO_TRY(ctx->wsplit[net].reserve(2 * total * 2));
         size_t off = 0;
         for (int l = 1; l < nd.n_layers; ++l) {
             const LayerDesc &L = nd.layer[l];
             STEREO_TRY(launch_weight_image_g(ctx, ctx->weights[net].as<float>() + L.w_off, L.ks, L.cin, L.cout,
                                              ctx->wsplit[net].as<uint16_t>() + off));
+            STEREO_TRY(launch_weight_image_r(ctx, ctx->weights[net].as<float>() + L.w_off, L.ks, L.cin, L.cout,
+                                             ctx->wsplit[net].as<uint16_t>() + total + off));
             off += tcg_weight_image_elems(L.ks, L.cin, L.cout);
         }
     }

@@ -172,6 +172,11 @@ int launch_nhwc_to_planar_g(stereo_ctx *ctx, const float *in, int n, int h, int 
 int launch_conv_tcg(stereo_ctx *ctx, int ks, int cin, int cout, const void *in_hi, const void *in_lo, int n, int h_in,
                     int w_in, int wp_in, const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out,
                     float *out_f32, int relu, int planes);
+// conv_tcr.cu (every input row multiplied once; same contract, its own weight image)
+int launch_weight_image_r(stereo_ctx *ctx, const float *layer_w, int ks, int cin, int cout, void *img);
+int launch_conv_tcr(stereo_ctx *ctx, int ks, int cin, int cout, const void *in_hi, const void *in_lo, int n, int h_in,
+                    int w_in, int wp_in, const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out,
+                    float *out_f32, int relu, int planes);
 int corr_sweep_margin();
 int corr_sweep2_row_cols(int w);
 int launch_corr_sweep2(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
