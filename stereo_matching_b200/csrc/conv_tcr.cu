@@ -11,12 +11,11 @@
 // the epilogue drains a finished block, writes zeros back (tcgen05.st) and releases it.
 //
 // Weights stream from L2 through a three-stage ring, one (kx, plane) unit [kc][KS*Cout][8] (40 KB for 64 -> 64) at
-// a time, ten units per input row = 400 KB per 128 output pixels: the L2 -> SM path would bound the kernel, so the
-// CTAs that work on the left and on the right image of a pair (same strip, same rows, same weights) form a cluster
-// of two, each fetches half of every unit and multicasts it into both shared memories, and a ring stage is refilled
-// when both issuers have committed their MMAs on it (multicast tcgen05.commit).  Input rows (chunk-planar bf16
-// hi / lo planes) pass through a ring of three slots and are read for exactly one row of MMAs.  Arithmetic and layouts are those of conv_tcg.cu (hi*hi + lo*hi + hi*lo
-// into fp32), so are the results up to the order of the fp32 accumulation.
+// a time, ten units per input row = 400 KB per 128 output pixels; sharing the units between the CTAs of the left and
+// the right image through a cluster halved that L2 traffic and changed nothing measurable (2.67 against 2.69 ms per
+// pair), so every CTA streams its own.  Input rows (chunk-planar bf16 hi / lo planes) pass through a ring of three
+// slots and are read for exactly one row of MMAs.  Arithmetic and layouts are those of conv_tcg.cu (hi*hi + lo*hi +
+// hi*lo into fp32), so are the results up to the order of the fp32 accumulation.
 //
 // Warp roles: warp 0 = TMA producer of the input rows, warp 3 = TMA producer of the weight ring, warp 1 = MMA
 // issuer (whole warp, one elected lane issues), warp 2 allocates tensor memory, warps 4-7 = epilogue.
@@ -65,12 +64,10 @@ struct Cfg {
     static_assert(CIN % 16 == 0 && COUT % 32 == 0 && COUT <= 64 && kNB > KS, "channel counts of base_model");
 };
 
-template <int KS, int CIN, int COUT, int CS>
+template <int KS, int CIN, int COUT>
 __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
 {
     using C = Cfg<KS, CIN, COUT>;
-    constexpr uint16_t kClusterMask = (uint16_t)((1u << CS) - 1);
-    static_assert(C::kUnitBytes % (16 * CS) == 0, "a weight unit splits into CS bulk copies");
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int h_out = p.h_in - (KS - 1), w_out = p.w_in - (KS - 1);
@@ -99,7 +96,7 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
         }
         for (int i = 0; i < kWStages; ++i) {
             mbar_init(bar_w_full + 8 * i, 1);
-            mbar_init(bar_w_empty + 8 * i, CS);           // every issuer of the cluster has consumed the stage
+            mbar_init(bar_w_empty + 8 * i, 1);
         }
         for (int i = 0; i < C::kNB; ++i) {
             mbar_init(bar_acc_full + 8 * i, 1);
@@ -115,7 +112,6 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (CS > 1) cluster_sync_all();                      // peers multicast into this CTA: its barriers must exist
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
@@ -139,8 +135,6 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
         if (lane == 0) {
             // ---- TMA producer: weight units in the issuer's order: per input row (kx 0, hi), (kx 0, lo), (kx 1, hi), ... ----
             const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(p.wimg);
-            constexpr uint32_t kPart = C::kUnitBytes / CS;      // this CTA's share of a unit
-            const uint32_t part_off = (CS > 1 ? cluster_rank() : 0u) * kPart;
             uint32_t u = 0;
             for (int r = 0; r < rows_in; ++r)
                 for (int kx = 0; kx < KS; ++kx)
@@ -148,10 +142,8 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
                         const uint32_t st = u % kWStages;
                         mbar_wait(bar_w_empty + 8 * st, ((u / kWStages) & 1) ^ 1);
                         mbar_expect_tx(bar_w_full + 8 * st, C::kUnitBytes);
-                        const uint8_t *src = wsrc + ((size_t)kx * 2 + pl) * C::kUnitBytes + part_off;
-                        const uint32_t dst = s_w + st * C::kUnitBytes + part_off;
-                        if (CS > 1) bulk_g2s_multicast(dst, src, kPart, bar_w_full + 8 * st, kClusterMask);
-                        else bulk_g2s(dst, src, kPart, bar_w_full + 8 * st);
+                        bulk_g2s(s_w + st * C::kUnitBytes, wsrc + ((size_t)kx * 2 + pl) * C::kUnitBytes, C::kUnitBytes,
+                                 bar_w_full + 8 * st);
                     }
         }
     } else if (warp == 1) {
@@ -202,10 +194,7 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
                             if (two_runs && elect_one()) umma_bf16_parts(tmem_d1, a_k, d_hi, b_k + boff1, d_hi, idesc1, 1u);
                         }
                     }
-                    if (elect_one()) {
-                        if (CS > 1) tc_commit_multicast(bar_w_empty + 8 * st, kClusterMask);
-                        else tc_commit(bar_w_empty + 8 * st);
-                    }
+                    if (elect_one()) tc_commit(bar_w_empty + 8 * st);
                 }
             }
             if (elect_one()) {
@@ -277,7 +266,6 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
     }
-    if (CS > 1) cluster_sync_all();                      // no CTA leaves while a peer may still signal its barriers
 }
 
 // fp32 packed weights ([tap = ky*KS + kx][cin][cout]) -> streaming units [kx][plane][kc][n][8] bf16 with
@@ -316,31 +304,10 @@ int launch_weight_image_r(stereo_ctx *ctx, const float *layer_w, int ks, int cin
     return STEREO_OK;
 }
 
-template <int KS, int CIN, int COUT, int CS>
-static int launch_tcr_cs(stereo_ctx *ctx, tcr::Params &p, int n, int strips, int segs)
-{
-    using C = tcr::Cfg<KS, CIN, COUT>;
-    auto kernel = tcr::conv_tcr_kernel<KS, CIN, COUT, CS>;
-    STEREO_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemTotal));
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(strips, segs, n);
-    cfg.blockDim = dim3(256);
-    cfg.dynamicSmemBytes = C::kSmemTotal;
-    cfg.stream = ctx->stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 1;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = CS;                       // the images of a batch share strip, rows and weights
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    STEREO_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, p));
-    return STEREO_OK;
-}
-
 template <int KS, int CIN, int COUT>
 static int launch_tcr(stereo_ctx *ctx, tcr::Params &p, int n)
 {
+    using C = tcr::Cfg<KS, CIN, COUT>;
     const int h_out = p.h_in - (KS - 1), w_out = p.w_in - (KS - 1);
     const int strips = (w_out + tcr::kStripW - 1) / tcr::kStripW;
     STEREO_REQUIRE(p.wp_in >= strips * tcr::kStripW + KS - 1, "activation pitch %d too small for %d strips", p.wp_in, strips);
@@ -351,9 +318,10 @@ static int launch_tcr(stereo_ctx *ctx, tcr::Params &p, int n)
     if (rows < 8) rows = 8;
     p.rows_per_cta = rows;
     segs = (h_out + rows - 1) / rows;
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(tcr::conv_tcr_kernel<KS, CIN, COUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           C::kSmemTotal));
     ProfScope prof(ctx, STEREO_K_CONV);
-    if (n % 2 == 0) STEREO_TRY((launch_tcr_cs<KS, CIN, COUT, 2>(ctx, p, n, strips, segs)));
-    else STEREO_TRY((launch_tcr_cs<KS, CIN, COUT, 1>(ctx, p, n, strips, segs)));
+    tcr::conv_tcr_kernel<KS, CIN, COUT><<<dim3(strips, segs, n), 256, C::kSmemTotal, ctx->stream>>>(p);
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;

@@ -173,21 +173,6 @@ __device__ __forceinline__ void mbar_arrive_remote(uint32_t local_bar, uint32_t 
         ::"r"(local_bar), "r"(rank)
         : "memory");
 }
-// bulk copy delivered to the same shared-memory offset (and mbarrier) in every CTA of `mask`
-__device__ __forceinline__ void bulk_g2s_multicast(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint16_t mask)
-{
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
-        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(mask)
-        : "memory");
-}
-// commit of this CTA's MMAs (cta_group::1), delivered to the barrier at this offset in every CTA of `mask`
-__device__ __forceinline__ void tc_commit_multicast(uint32_t bar, uint16_t mask)
-{
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"(mask)
-                 : "memory");
-}
 // commit of the pair's MMAs, delivered to the barrier at this offset in both CTAs
 __device__ __forceinline__ void tc_commit_pair(uint32_t bar)
 {

@@ -117,3 +117,41 @@ def test_post_kernel_families_agree_bit_for_bit(tmp_path):
     assert sorted(maps["ring"].files) == sorted(maps["regs"].files) and len(maps["ring"].files) == 12
     for k in maps["ring"].files:
         assert np.array_equal(maps["ring"][k], maps["regs"][k]), k
+
+
+BASE_CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib, synth
+from stereo_matching_b200.models.model import base_model
+m = base_model((None, None, 3))
+m.set_layers(synth.make_base_model_weights())
+x = np.random.default_rng(11).standard_normal((2, 52, 300, 3)).astype(np.float32)
+np.savez(sys.argv[2], pair=m.context.trunk(_lib.NET_WIN37, x, _lib.PREC_BF16X3),
+         single=m.context.trunk(_lib.NET_WIN37, x[:1], _lib.PREC_BF16X3))
+"""
+
+
+def test_base_model_conv_kernel_families_agree(tmp_path):
+    """STEREO_CONV5_KERNEL=1 (conv_tcg.cu, one MMA per tap) against the default conv_tcr.cu (each input row
+    once): same products, different order of the fp32 accumulation, so equal within the tolerance of the split;
+    both are checked against the float64 oracle."""
+    from oracle import stereo_oracle as so
+    outs = {}
+    for name, env in (("row_once", {}), ("per_tap", {"STEREO_CONV5_KERNEL": "1"})):
+        e = dict(os.environ)
+        e.update(env)
+        out = tmp_path / (name + ".npz")
+        r = subprocess.run([sys.executable, "-c", BASE_CHILD, ROOT, str(out)], env=e, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[name] = np.load(out)
+    a, b = outs["row_once"], outs["per_tap"]
+    assert np.abs(a["pair"] - b["pair"]).max() / np.abs(b["pair"]).max() < 2e-5
+    assert np.array_equal(a["single"][0], a["pair"][0])          # the batch size does not change an image's result
+    layers = synth.make_base_model_weights()
+    x = np.random.default_rng(11).standard_normal((2, 52, 300, 3)).astype(np.float32)
+    ref = so.trunk_forward(x, layers, "win37_dep9", np.float64)
+    for k in ("row_once", "per_tap"):
+        assert np.abs(outs[k]["pair"] - ref).max() / np.abs(ref).max() < 6e-5
