@@ -502,7 +502,7 @@ def run_b200(args):
                 "workload": f"base_model (nine 5x5 layers, 37x37 receptive field), {nb} pairs, fused correlation + WTA + LR check",
                 "ms_per_pair": bms, "pairs_per_s": 1e3 / bms, "conv_ms_per_pair": conv_ms,
                 "conv_tflops_algorithmic": 1191.75e9 / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else None,
-                "note": "layers 2-9 on tcgen05 (conv_tcg.cu), 1 191.75 GFLOP per pair counted once; seeded synthetic weights "
+                "note": "layers 2-9 on tcgen05 (conv_tcr.cu), 1 191.75 GFLOP per pair counted once; seeded synthetic weights "
                         "(the reference ships none for base_model)"}
         except Exception as e:          # secondary measurement: never fail the bench line
             extra["base_model"] = {"error": repr(e)}
