@@ -68,6 +68,10 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     const uint32_t s_bar = s_data + (uint32_t)S * stage_bytes;
     const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages;
     const float *src[3] = {cvol, acc_a, acc_b};
+    // unaligned volumes: results leave through a per-warp staging row (two of them, used alternately) so that a
+    // warp store is a 128-byte run instead of 32 words 32 bytes apart
+    const int Dp = (D + 3) & ~3;
+    float *stg_rows = reinterpret_cast<float *>(smem + (size_t)S * stage_bytes + 2 * 8 * kMaxStages) + (size_t)warp * 2 * Dp;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < S; ++i) {
@@ -137,15 +141,30 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     float prev[KPL];
 #pragma unroll
     for (int k = 0; k < KPL; ++k) prev[k] = kSgmBig;
-    float *optr = outp + ((size_t)y * w + x) * D + d0;
+    float *optr = outp + ((size_t)y * w + x) * D + (ALIGNED ? d0 : 0);
     const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;
 
+    // unaligned volumes: running slot-relative byte offsets (see the gather below).  Horizontal paths move one pixel
+    // (D floats) inside the run per step; vertical paths change the run, whose phase moves by (w * D * 4) mod 16.
+    uint32_t o_run[3] = {0, 0, 0}, ph_run[3] = {0, 0, 0};
+    const uint32_t o_step = kH ? (uint32_t)(dx * D * 4) : ((uint32_t)(dy * w * D * 4) & 15u);
     int step = 0;
     for (int t = 0; t < n_stages; ++t) {
         const int s = t % S;
         const int g_here = min(G, steps - t * G);
         mbar_wait(bar_full + 8 * s, (t / S) & 1);
         const uint8_t *stage = smem + (size_t)s * stage_bytes;
+        if (!ALIGNED) {
+            // byte offset of this lane's first float inside its slot at the first step of the stage: the phase of
+            // the run (address mod 16) plus the run-relative position
+            const size_t e0 = run_start(t, kH ? warp : 0, g_here);
+            const int inner0 = kH ? (SD == 0 ? 0 : g_here - 1) : warp;
+#pragma unroll
+            for (int q = 0; q < kArrays; ++q) {
+                ph_run[q] = (uint32_t)((uintptr_t)(src[q] + e0) & 15);
+                o_run[q] = ph_run[q] + ((uint32_t)inner0 * D + d0) * 4;
+            }
+        }
         for (int i = 0; i < g_here; ++i, ++step) {
             int code[KPL];
 #pragma unroll
@@ -162,7 +181,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
             const int slot = kH ? warp : i;
             const int inner = kH ? (SD == 0 ? i : g_here - 1 - i) : warp;        // run-relative pixel
             const uint8_t *base = stage + (uint32_t)slot * slot_bytes + ((uint32_t)inner * D + d0) * 4;
-            float c[KPL], a[NACC >= 1 ? KPL : 1], b[NACC >= 2 ? KPL : 1];
+            float c[KPL], a[KPL], b[KPL];      // a, b: running sums (used when NACC >= 1, 2)
             if (ALIGNED) {
 #pragma unroll
                 for (int j = 0; j < KPL / 4; ++j) {
@@ -187,18 +206,48 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     }
                 }
             } else {
-                // the run sits `phase` bytes into its slot (per array: the volumes need not share an alignment)
-                const size_t e0 = run_start(t, slot, g_here);
-                uint32_t ph[kArrays];
+                // the run sits `phase` bytes into its slot (per array: the volumes need not share an alignment), so a
+                // lane's KPL floats start (phase + row offset) mod 16 bytes into a 16-byte word - the same shift for
+                // every lane.  Read the aligned words that cover them and pick by the (warp-uniform) shift.
+                auto gather = [&](int q, float (&dst)[KPL], float fill) {
+                    const uint32_t o = o_run[q];
+                    const uint8_t *al = stage + q * array_bytes + (uint32_t)slot * slot_bytes + (o & ~15u);
+                    float tq[KPL + 4];
 #pragma unroll
-                for (int q = 0; q < kArrays; ++q) ph[q] = (uint32_t)((uintptr_t)(src[q] + e0) & 15) + q * array_bytes;
+                    for (int j = 0; j < KPL / 4 + 1; ++j) {
+                        const float4 v = *reinterpret_cast<const float4 *>(al + 16 * j);
+                        tq[4 * j] = v.x; tq[4 * j + 1] = v.y; tq[4 * j + 2] = v.z; tq[4 * j + 3] = v.w;
+                    }
+                    const uint32_t sh = (o & 15u) >> 2;
+                    if (sh == 0) {
 #pragma unroll
-                for (int k = 0; k < KPL; ++k) {
-                    const bool ok = d0 + k < D;
-                    c[k] = ok ? *reinterpret_cast<const float *>(base + ph[0] + 4 * k) : kSgmBig;
-                    if (NACC >= 1) a[k] = ok ? *reinterpret_cast<const float *>(base + ph[NACC >= 1 ? 1 : 0] + 4 * k) : 0.f;
-                    if (NACC >= 2) b[k] = ok ? *reinterpret_cast<const float *>(base + ph[NACC >= 2 ? 2 : 0] + 4 * k) : 0.f;
-                }
+                        for (int k = 0; k < KPL; ++k) dst[k] = tq[k];
+                    } else if (sh == 1) {
+#pragma unroll
+                        for (int k = 0; k < KPL; ++k) dst[k] = tq[k + 1];
+                    } else if (sh == 2) {
+#pragma unroll
+                        for (int k = 0; k < KPL; ++k) dst[k] = tq[k + 2];
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < KPL; ++k) dst[k] = tq[k + 3];
+                    }
+                    if (d0 + KPL > D) {                      // only the lanes at the end of the disparity range
+#pragma unroll
+                        for (int k = 0; k < KPL; ++k) dst[k] = d0 + k < D ? dst[k] : fill;
+                    }
+                    // next step: the neighbouring pixel of the run (horizontal) / the next image row (vertical)
+                    if (kH) {
+                        o_run[q] = o + o_step;
+                    } else {
+                        const uint32_t ph = (ph_run[q] + o_step) & 15u;
+                        o_run[q] = o - ph_run[q] + ph;
+                        ph_run[q] = ph;
+                    }
+                };
+                gather(0, c, kSgmBig);
+                if constexpr (NACC >= 1) gather(1, a, 0.f);
+                if constexpr (NACC >= 2) gather(2, b, 0.f);
             }
             float val[KPL];
             if (step == 0) {
@@ -221,11 +270,14 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     if (ALIGNED) {
                         reinterpret_cast<float4 *>(optr)[j] = make_float4(r[0], r[1], r[2], r[3]);
                     } else {
-#pragma unroll
-                        for (int e = 0; e < 4; ++e)
-                            if (d0 + 4 * j + e < D) optr[4 * j + e] = r[e];
+                        *reinterpret_cast<float4 *>(stg_rows + (step & 1) * Dp + d0 + 4 * j) = make_float4(r[0], r[1], r[2], r[3]);
                     }
                 }
+            }
+            if (!ALIGNED) {
+                __syncwarp();
+                const float *row = stg_rows + (step & 1) * Dp;
+                for (int e = lane; e < D; e += 32) optr[e] = row[e];
             }
 #pragma unroll
             for (int k = 0; k < KPL; ++k) prev[k] = val[k];
@@ -305,7 +357,8 @@ RingShape ring_shape(int arrays, int nw, int D, bool horizontal, bool aligned, s
         --G;
         S = (int)std::min<size_t>(kMaxStages, budget / stage(G));
     }
-    return {G, S, (size_t)S * stage(G) + 2 * 8 * kMaxStages};
+    const size_t staging = aligned ? 0 : (size_t)nw * 2 * ((D + 3) & ~3) * 4;      // per-warp output rows
+    return {G, S, (size_t)S * stage(G) + 2 * 8 * kMaxStages + staging};
 }
 
 template <int KPL, int NW, int DIR, bool ALIGNED>
