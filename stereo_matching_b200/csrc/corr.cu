@@ -183,10 +183,23 @@ __global__ void wta_kernel(const float *__restrict__ vol, size_t npix, int D, in
         const float *row = vol + p * D;
         float best = 0.f;
         int best_d = 0x7fffffff;
-        for (int d = lane; d < D; d += 32) {
-            float v = __ldg(row + d);
-            if (take_min) v = -v;
-            if (best_d == 0x7fffffff || v > best) { best = v; best_d = d; }
+        if (D <= 256) {
+            // all of the lane's (up to eight) loads in flight before the first compare
+            float v8[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v8[i] = lane + 32 * i < D ? __ldg(row + lane + 32 * i) : 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int d = lane + 32 * i;
+                const float v = take_min ? -v8[i] : v8[i];
+                if (d < D && (best_d == 0x7fffffff || v > best)) { best = v; best_d = d; }
+            }
+        } else {
+            for (int d = lane; d < D; d += 32) {
+                float v = __ldg(row + d);
+                if (take_min) v = -v;
+                if (best_d == 0x7fffffff || v > best) { best = v; best_d = d; }
+            }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
