@@ -71,6 +71,10 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 }
 
 // one adcensus.cbca call in either summation order; `tmp` is a spare volume for the separable form
+// The SGM ring kernels fetch the 16-byte aligned superset of every run of an unaligned volume (sgm_ring.cu): up to
+// 12 bytes past the last voxel, which this slack keeps inside the allocation whatever its size.
+static constexpr size_t kVolSlack = 256;
+
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
                     float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
 {
@@ -141,7 +145,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
     // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream
     // section would serialise it
-    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
     for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
     STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * 1184));
     if (!ctx->aux_stream) {
@@ -351,7 +355,7 @@ int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
-    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
     STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
     STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
@@ -381,7 +385,7 @@ int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, floa
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, 1, &m));
-    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox));
+    for (int i = 0; i < 3; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
     STEREO_TRY(to_dev(ctx, m.guide_l, l_img, sizeof(float) * hw));
     STEREO_TRY(to_dev(ctx, m.guide_r, r_img, sizeof(float) * hw));
     float *a = ctx->post_vol[0].as<float>(), *b = ctx->post_vol[1].as<float>();
