@@ -56,7 +56,10 @@ struct Cfg {
     static constexpr int kUnitBytes = kChunks * kNAll * 16; // one kx, one plane: [kc][n][8] bf16
     static constexpr int kNB = 512 / COUT;                 // accumulator blocks (output rows in flight)
     static constexpr int kMaxRun = 256 / COUT;             // blocks one MMA may span (N <= 256)
-    static constexpr int kSmemRows = kWStages * kUnitBytes;
+    // all 2 * KS units of a layer stay in shared memory when they fit beside the row slots (32 -> 32: 100 KB);
+    // otherwise they stream through kWStages stages
+    static constexpr bool kResident = 2 * KS * kUnitBytes <= 112 * 1024;
+    static constexpr int kSmemRows = (kResident ? 2 * KS : kWStages) * kUnitBytes;
     static constexpr int kSmemBias = kSmemRows + kSlots * kSlotBytes;
     static constexpr int kSmemBars = kSmemBias + COUT * 4;
     static constexpr int kSmemTotal = kSmemBars + 48 * 8 + 16;
@@ -136,6 +139,12 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
             // ---- TMA producer: weight units in the issuer's order: per input row (kx 0, hi), (kx 0, lo), (kx 1, hi), ... ----
             const uint8_t *wsrc = reinterpret_cast<const uint8_t *>(p.wimg);
             uint32_t u = 0;
+            if (C::kResident) {
+                // the whole weight image once: unit (kx, plane) at its own offset, one barrier
+                mbar_expect_tx(bar_w_full, 2 * KS * C::kUnitBytes);
+                for (int i = 0; i < 2 * KS; ++i)
+                    bulk_g2s(s_w + i * C::kUnitBytes, wsrc + (size_t)i * C::kUnitBytes, C::kUnitBytes, bar_w_full);
+            } else
             for (int r = 0; r < rows_in; ++r)
                 for (int kx = 0; kx < KS; ++kx)
                     for (int pl = 0; pl < p.planes; ++pl, ++u) {
@@ -150,6 +159,7 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
         // ---- MMA issuer: the whole warp runs the loop, one elected lane issues ----
         const uint32_t d_hi = desc_hi(128);
         uint32_t u = 0;                                   // running weight-unit counter
+        if (C::kResident) mbar_wait(bar_w_full, 0);
         for (int r = 0; r < rows_in; ++r) {
             const int slot = r % kSlots;
             // output rows this input row feeds: j = r - ky for the vertical taps that stay inside the band
@@ -179,9 +189,11 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
                 const uint32_t a_base = s_rows + slot * C::kSlotBytes + kx * 16;
                 // unit (kx, hi): A_hi * W_hi, then A_lo * W_hi; unit (kx, lo): A_hi * W_lo
                 for (int pl = 0; pl < p.planes; ++pl, ++u) {
-                    const uint32_t st = u % kWStages;
-                    mbar_wait(bar_w_full + 8 * st, (u / kWStages) & 1);
-                    tc_fence_after();
+                    const uint32_t st = C::kResident ? (uint32_t)(kx * 2 + pl) : u % kWStages;
+                    if (!C::kResident) {
+                        mbar_wait(bar_w_full + 8 * st, (u / kWStages) & 1);
+                        tc_fence_after();
+                    }
                     const uint32_t unit = desc_lo(s_w + st * C::kUnitBytes, C::kNAll * 16);
                     const int n_a = (pl == 0 && p.planes == 2) ? 2 : 1;      // activation planes multiplied with this unit
                     for (int apl = 0; apl < n_a; ++apl) {
@@ -194,7 +206,7 @@ __global__ __launch_bounds__(256, 1) void conv_tcr_kernel(Params p)
                             if (two_runs && elect_one()) umma_bf16_parts(tmem_d1, a_k, d_hi, b_k + boff1, d_hi, idesc1, 1u);
                         }
                     }
-                    if (elect_one()) tc_commit(bar_w_empty + 8 * st);
+                    if (!C::kResident && elect_one()) tc_commit(bar_w_empty + 8 * st);
                 }
             }
             if (elect_one()) {
