@@ -260,34 +260,45 @@ __global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__re
                                                                int n, int h, int wd, int ks, int cin, int cout,
                                                                double *__restrict__ red_w)
 {
-    __shared__ float xs[32][65], ds[32][65];
+    // 32 positions x 64 channels of x (shifted by the tap) and of dz; rows are 256 bytes, so a thread reads its four
+    // input and four output channels as one 16-byte word each (the 16 lanes that share ci0 read the same word)
+    __shared__ __align__(16) float xs[32][64], ds[32][64];
     const int ho = h - ks + 1, wo = wd - ks + 1;
     const int t = blockIdx.x, ky = t / ks, kx = t % ks;
     const size_t m = (size_t)n * ho * wo;
     const size_t p0 = (size_t)blockIdx.y * kBwdChunk, p1 = p0 + kBwdChunk < m ? p0 + kBwdChunk : m;
     const int tid = threadIdx.x, ci0 = (tid >> 4) * 4, co0 = (tid & 15) * 4;
+    // loader role: channel c of positions pb + lp, lp = tid / 64 + 4 i; (b, yo, xo) of the position walk along
+    const int c = tid & 63, lp0 = tid >> 6;
+    size_t pl = p0 + lp0;
+    int xo = (int)(pl % wo);
+    size_t q = pl / wo;
+    int yo = (int)(q % ho), b = (int)(q / ho);
     float acc[4][4] = {};
     for (size_t pb = p0; pb < p1; pb += 32) {
-        for (int e = tid; e < 32 * 64; e += 256) {
-            const int pp = e >> 6, c = e & 63;
-            const size_t p = pb + pp;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int pp = lp0 + 4 * i;
             float xv = 0.f, dv = 0.f;
-            if (p < p1) {
-                const int xo = (int)(p % wo);
-                const size_t q = p / wo;
-                const int yo = (int)(q % ho), b = (int)(q / ho);
+            if (pl < p1) {
                 if (c < cin) xv = x[(((size_t)b * h + yo + ky) * wd + xo + kx) * cin + c];
-                if (c < cout) dv = dz[p * cout + c];
+                if (c < cout) dv = dz[pl * cout + c];
             }
             xs[pp][c] = xv;
             ds[pp][c] = dv;
+            pl += 4;
+            xo += 4;
+            while (xo >= wo) {
+                xo -= wo;
+                if (++yo == ho) { yo = 0; ++b; }
+            }
         }
         __syncthreads();
 #pragma unroll 8
         for (int pp = 0; pp < 32; ++pp) {
-            float a[4], bv[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) { a[i] = xs[pp][ci0 + i]; bv[i] = ds[pp][co0 + i]; }
+            const float4 a4 = *reinterpret_cast<const float4 *>(&xs[pp][ci0]);
+            const float4 b4 = *reinterpret_cast<const float4 *>(&ds[pp][co0]);
+            const float a[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -301,6 +312,63 @@ __global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__re
         for (int j = 0; j < 4; ++j)
             if (ci0 + i < cin && co0 + j < cout)
                 atomicAdd(red_w + ((size_t)t * cin + ci0 + i) * cout + co0 + j, (double)acc[i][j]);
+}
+
+// The same for a first layer (ks * ks * cin <= 32, i.e. 3 input channels): all taps at once.  With r = t * cin + ci
+// the gradient is ONE [r][co] product over the positions, dW[r][co] += sum_p patch[p][r] * dz[p][co]; running it as
+// ks * ks products of 64 x 64 tiles would spend 21 of 22 multiplications on zero padding.
+__global__ __launch_bounds__(256) void train_conv_bwd_w_small_kernel(const float *__restrict__ x, const float *__restrict__ dz,
+                                                                     int n, int h, int wd, int ks, int cin, int cout,
+                                                                     double *__restrict__ red_w)
+{
+    __shared__ __align__(16) float xs[32][32], ds[32][64];
+    const int ho = h - ks + 1, wo = wd - ks + 1, rows = ks * ks * cin;
+    const size_t m = (size_t)n * ho * wo;
+    const size_t p0 = (size_t)blockIdx.x * kBwdChunk, p1 = p0 + kBwdChunk < m ? p0 + kBwdChunk : m;
+    const int tid = threadIdx.x, r0 = (tid >> 4) * 2, co0 = (tid & 15) * 4;
+    // loader roles: dz channel c of positions lp0 + 4 i; patch entry pr of positions pq0 + 8 i
+    const int c = tid & 63, lp0 = tid >> 6;
+    const int pr = tid & 31, pq0 = tid >> 5;
+    const int pt = pr / cin, pci = pr - pt * cin, pky = pt / ks, pkx = pt - pky * ks;
+    float acc[2][4] = {};
+    for (size_t pb = p0; pb < p1; pb += 32) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int pp = lp0 + 4 * i;
+            const size_t p = pb + pp;
+            ds[pp][c] = (p < p1 && c < cout) ? dz[p * cout + c] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int pp = pq0 + 8 * i;
+            const size_t p = pb + pp;
+            float xv = 0.f;
+            if (p < p1 && pr < rows) {
+                const int xo = (int)(p % wo);
+                const size_t q = p / wo;
+                const int yo = (int)(q % ho), b = (int)(q / ho);
+                xv = x[(((size_t)b * h + yo + pky) * wd + xo + pkx) * cin + pci];
+            }
+            xs[pp][pr] = xv;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int pp = 0; pp < 32; ++pp) {
+            const float2 a2 = *reinterpret_cast<const float2 *>(&xs[pp][r0]);
+            const float4 b4 = *reinterpret_cast<const float4 *>(&ds[pp][co0]);
+            const float a[2] = {a2.x, a2.y}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (r0 + i < rows && co0 + j < cout) atomicAdd(red_w + (size_t)(r0 + i) * cout + co0 + j, (double)acc[i][j]);
 }
 
 // db[co] += sum_p dz[p][co]
@@ -461,8 +529,11 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (wn + L.cout) * sizeof(double), ctx->stream));
         const int chunks = (int)((m + kBwdChunk - 1) / kBwdChunk);
-        train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks, chunks), 256, 0, ctx->stream>>>(
-            xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
+        if (L.ks * L.ks * L.cin <= 32 && L.cout <= 64)
+            train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
+        else
+            train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks, chunks), 256, 0, ctx->stream>>>(
+                xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
         train_bias_bwd_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(dz, m, L.cout, red + wn);
         train_accumulate_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(red, (int)wn, G + L.w_off);
         train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + wn, L.cout, G + L.b_off);
