@@ -254,11 +254,11 @@ __global__ void train_accumulate_kernel(const double *__restrict__ red, int n, f
 
 // dW[t][ci][co] += sum_p x[p + t][ci] * dz[p][co].  A shared-memory GEMM per tap: grid = (taps, position
 // chunks), 256 threads, every thread a 4 x 4 block of the (<= 64 x 64) [ci][co] tile; the positions of a chunk
-// are accumulated in fp32 (<= kBwdChunk terms), the chunks in double (atomics).
+// are accumulated in fp32 (<= kBwdChunk terms; the launch picks the chunk), the chunks in double (atomics).
 constexpr int kBwdChunk = 2048;
 __global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__restrict__ x, const float *__restrict__ dz,
                                                                int n, int h, int wd, int ks, int cin, int cout,
-                                                               double *__restrict__ red_w)
+                                                               int chunk, double *__restrict__ red_w)
 {
     // 32 positions x 64 channels of x (shifted by the tap) and of dz; rows are 256 bytes, so a thread reads its four
     // input and four output channels as one 16-byte word each (the 16 lanes that share ci0 read the same word)
@@ -266,7 +266,7 @@ __global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__re
     const int ho = h - ks + 1, wo = wd - ks + 1;
     const int t = blockIdx.x, ky = t / ks, kx = t % ks;
     const size_t m = (size_t)n * ho * wo;
-    const size_t p0 = (size_t)blockIdx.y * kBwdChunk, p1 = p0 + kBwdChunk < m ? p0 + kBwdChunk : m;
+    const size_t p0 = (size_t)blockIdx.y * chunk, p1 = p0 + chunk < m ? p0 + chunk : m;
     const int tid = threadIdx.x, ci0 = (tid >> 4) * 4, co0 = (tid & 15) * 4;
     // loader role: channel c of positions pb + lp, lp = tid / 64 + 4 i; (b, yo, xo) of the position walk along
     const int c = tid & 63, lp0 = tid >> 6;
@@ -319,12 +319,12 @@ __global__ __launch_bounds__(256) void train_conv_bwd_w_kernel(const float *__re
 // ks * ks products of 64 x 64 tiles would spend 21 of 22 multiplications on zero padding.
 __global__ __launch_bounds__(256) void train_conv_bwd_w_small_kernel(const float *__restrict__ x, const float *__restrict__ dz,
                                                                      int n, int h, int wd, int ks, int cin, int cout,
-                                                                     double *__restrict__ red_w)
+                                                                     int chunk, double *__restrict__ red_w)
 {
     __shared__ __align__(16) float xs[32][32], ds[32][64];
     const int ho = h - ks + 1, wo = wd - ks + 1, rows = ks * ks * cin;
     const size_t m = (size_t)n * ho * wo;
-    const size_t p0 = (size_t)blockIdx.x * kBwdChunk, p1 = p0 + kBwdChunk < m ? p0 + kBwdChunk : m;
+    const size_t p0 = (size_t)blockIdx.x * chunk, p1 = p0 + chunk < m ? p0 + chunk : m;
     const int tid = threadIdx.x, r0 = (tid >> 4) * 2, co0 = (tid & 15) * 4;
     // loader roles: dz channel c of positions lp0 + 4 i; patch entry pr of positions pq0 + 8 i
     const int c = tid & 63, lp0 = tid >> 6;
@@ -528,12 +528,19 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         // conv: dW, db (double accumulation), then dx for the layer below
         const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (wn + L.cout) * sizeof(double), ctx->stream));
-        const int chunks = (int)((m + kBwdChunk - 1) / kBwdChunk);
-        if (L.ks * L.ks * L.cin <= 32 && L.cout <= 64)
-            train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
+        // positions per block (accumulated in fp32; the blocks in double): at most kBwdChunk, fewer when that would
+        // leave SMs idle (the left tower, the first layer's single product): about eight blocks per SM
+        const bool small = L.ks * L.ks * L.cin <= 32 && L.cout <= 64;
+        const size_t products = small ? 1 : (size_t)L.ks * L.ks;
+        size_t chunk = (m * products / ((size_t)ctx->sm_count * 8) + 31) / 32 * 32;
+        chunk = chunk < 128 ? 128 : (chunk > (size_t)kBwdChunk ? (size_t)kBwdChunk : chunk);
+        const int chunks = (int)((m + chunk - 1) / chunk);
+        if (small)
+            train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout,
+                                                                           (int)chunk, red);
         else
             train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks, chunks), 256, 0, ctx->stream>>>(
-                xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, red);
+                xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, (int)chunk, red);
         train_bias_bwd_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(dz, m, L.cout, red + wn);
         train_accumulate_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(red, (int)wn, G + L.w_off);
         train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + wn, L.cout, G + L.b_off);
