@@ -1,4 +1,4 @@
-"""Data-parallel training check, run as `torchrun --nproc-per-node N scripts/train_dp_check.py`: every rank
+"""Data-parallel training check, run as `torchrun --nproc-per-node N tests/tools/train_dp_check.py`: every rank
 computes gradients on its own batch, the flat device gradient array is averaged with one NCCL all-reduce
 (through a zero-copy torch view of the library's buffer), every rank applies the same Adam step.  Rank 0 checks
 that all ranks hold bit-identical parameters afterwards and that they match the CPU oracle's step on the
@@ -11,7 +11,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 from oracle import train_oracle as to                                  # noqa: E402
 from stereo_matching_b200 import _lib, train                           # noqa: E402
