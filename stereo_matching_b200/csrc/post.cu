@@ -380,11 +380,37 @@ int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, c
 __global__ void volume_moments_kernel(const float *__restrict__ vol, size_t n, double *__restrict__ partial)
 {
     double s = 0.0, ss = 0.0;
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        double v = (double)vol[i];
-        s += v;
-        ss += v * v;
+    const size_t stride = (size_t)gridDim.x * blockDim.x, tid0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (((uintptr_t)vol & 15) == 0) {
+        // 16-byte loads, two of them in flight per thread, four independent double accumulations
+        const float4 *v4 = reinterpret_cast<const float4 *>(vol);
+        const size_t n4 = n / 4;
+        double s1 = 0.0, ss1 = 0.0, s2 = 0.0, ss2 = 0.0, s3 = 0.0, ss3 = 0.0;
+        size_t i = tid0;
+        for (; i + stride < n4; i += 2 * stride) {
+            const float4 a = __ldg(v4 + i), b = __ldg(v4 + i + stride);
+            const double a0 = a.x, a1 = a.y, a2 = a.z, a3 = a.w, b0 = b.x, b1 = b.y, b2 = b.z, b3 = b.w;
+            s += a0; ss += a0 * a0; s1 += a1; ss1 += a1 * a1; s2 += a2; ss2 += a2 * a2; s3 += a3; ss3 += a3 * a3;
+            s += b0; ss += b0 * b0; s1 += b1; ss1 += b1 * b1; s2 += b2; ss2 += b2 * b2; s3 += b3; ss3 += b3 * b3;
+        }
+        if (i < n4) {
+            const float4 a = __ldg(v4 + i);
+            const double a0 = a.x, a1 = a.y, a2 = a.z, a3 = a.w;
+            s += a0; ss += a0 * a0; s1 += a1; ss1 += a1 * a1; s2 += a2; ss2 += a2 * a2; s3 += a3; ss3 += a3 * a3;
+        }
+        for (size_t k = 4 * n4 + tid0; k < n; k += stride) {          // the last n % 4 elements
+            const double v = (double)vol[k];
+            s += v;
+            ss += v * v;
+        }
+        s = (s + s1) + (s2 + s3);
+        ss = (ss + ss1) + (ss2 + ss3);
+    } else {
+        for (size_t i = tid0; i < n; i += stride) {
+            double v = (double)vol[i];
+            s += v;
+            ss += v * v;
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
