@@ -2,8 +2,8 @@
 //
 // The separable form in post.cu writes the row-segment sums (hsum, fp32) and lengths (hcnt, uint8) of every voxel
 // to HBM and reads them back nine rows at a time: 1.84 GB of DRAM traffic and ~260 instructions per voxel for
-// 0.85 GB of algorithmic bytes.  Here a thread owns one disparity of FOUR neighbouring pixels and walks down a band
-// of image rows: for every row it forms the four row-segment sums from 12 loaded costs (as cbca_h4_kernel does) and
+// 0.85 GB of algorithmic bytes.  Here a thread owns one disparity of TWO neighbouring pixels and walks down a band
+// of image rows: for every row it forms the two row-segment sums from 10 loaded costs (as cbca_h4_kernel does) and
 // keeps the last nine rows of (sum, length) in registers; the output of row y - 4 is the sum over the rows its
 // vertical arms admit (as cbca_v4_kernel does).  Same additions in the same order as the two-pass kernels, so the
 // results are bit-identical to them; nothing but the volume is read and nothing but the result written.
@@ -22,7 +22,7 @@ namespace stereo {
 namespace {
 
 constexpr int kFR = 4;                   // window half width = L1 - 1
-constexpr int kFB = 4;                   // pixels per thread
+constexpr int kFB = 2;                   // pixels per thread (4: 118 registers, two CTAs per SM, slower; 1: slower still)
 constexpr int kFN = kFB + 2 * kFR;       // costs loaded per row
 constexpr int kFW = 2 * kFR + 1;         // rows kept
 
@@ -107,8 +107,9 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                 float v[kFN];
 #pragma unroll
                 for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
-                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (rbase + xb));
-                const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
+                uint32_t own_r[kFB];
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) own_r[i] = __ldg(rec0 + (rbase + xb + i));
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
                     const uint32_t cm = own_r[i] & __ldg(rec1 + (rbase + xm[i]));   // both arms reach the column
@@ -127,8 +128,9 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
             if (y >= y0 && y < y1) {
                 // ---- output row y: rows y-R .. y+R sit in slots u+1 .. u+9 (mod 9) (cbca_v4_kernel) ----
                 const int rbase = y * pitch, obase = y * row_elems;
-                const uint4 own = *reinterpret_cast<const uint4 *>(rec0 + (rbase + xb));
-                const uint32_t own_r[kFB] = {own.x, own.y, own.z, own.w};
+                uint32_t own_r[kFB];
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) own_r[i] = __ldg(rec0 + (rbase + xb + i));
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
                     if (!pix_ok[i]) continue;
