@@ -85,8 +85,15 @@ __device__ __forceinline__ void sgm_step_coded(const SgmPenalties<SD> &pen, int 
     float pmin = prev[0];
 #pragma unroll
     for (int k = 1; k < KPL; ++k) pmin = fminf(pmin, prev[k]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) pmin = fminf(pmin, __shfl_xor_sync(0xffffffffu, pmin, o));
+    // minimum over the warp in one instruction: redux.sync works on integers, and float order is integer order once
+    // the magnitude bits of negative values are flipped (no NaNs here: costs are finite, kSgmBig included)
+    {
+        int key = __float_as_int(pmin);
+        key ^= (key >> 31) & 0x7fffffff;
+        key = __reduce_min_sync(0xffffffffu, key);
+        key ^= (key >> 31) & 0x7fffffff;
+        pmin = __int_as_float(key);
+    }
     float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
     float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
     below = has_below ? below : kSgmBig;
