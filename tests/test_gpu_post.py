@@ -208,10 +208,11 @@ def test_staged_post_path_equals_fused_pipeline_and_runs_the_optional_branches(c
     assert np.array_equal(extra["cost_img"], ref)
 
 
-def test_pairs_post_equals_inference_then_post(ctx):
+@pytest.mark.parametrize("D,h,w", [(64, 72, 200), (201, 41, 263)])
+def test_pairs_post_equals_inference_then_post(ctx, D, h, w):
     """`stereo_pairs_post` (volumes never leave the device) == `stereo_pairs` with exported volumes followed by
-    `stereo_post` on them, bit for bit, for a batch of two pairs."""
-    D, h, w = 64, 72, 200
+    `stereo_post` on them, bit for bit, for a batch of two pairs; also at the reference's default disp_range 201,
+    whose volume rows are not 16-byte aligned (other SGM / WTA code paths), with odd image sizes."""
     pairs = [synth.make_pair(4100 + i, h, w, D) for i in range(2)]
     left = np.stack([p[0] for p in pairs])
     right = np.stack([p[1] for p in pairs])
