@@ -81,6 +81,24 @@ def test_cross_agg_separable_within_tolerance(ctx, scene, iters):
         assert (np.argmax(out, axis=0) == np.argmax(ref, axis=0)).mean() >= 0.999
 
 
+@pytest.mark.parametrize("D,h,w", [(201, 23, 61), (256, 11, 37), (33, 70, 9)])
+def test_cross_agg_fused_random_scenes(ctx, D, h, w):
+    """The fused single-pass CBCA (default for D <= 256) on piecewise-constant guides with arms of every length,
+    image widths that do not fill the last thread's pixels and heights below one band, against the C restatement."""
+    rng = np.random.default_rng(D + h)
+    gl = np.repeat(np.repeat(rng.standard_normal((h // 3 + 1, w // 4 + 1)), 3, 0), 4, 1)[:h, :w].astype(np.float32) * 0.05
+    gr = np.roll(gl, -2, axis=1)
+    lv = rng.standard_normal((h, w, D)).astype(np.float32)
+    rv = rng.standard_normal((h, w, D)).astype(np.float32)
+    lu, ru = (np.ascontiguousarray(np.transpose(v, (2, 0, 1))) for v in (lv, rv))
+    lref, rref = po.nyu_cross_agg(gl, gr, lu, ru, 2)
+    lo, ro = ctx.nyu_cross_agg(gl, gr, lv, rv, 2)
+    for out, ref in ((lo, lref), (ro, rref)):
+        assert np.abs(np.transpose(out, (2, 0, 1)) - ref).max() / np.abs(ref).max() < CBCA_SEPARABLE_TOL
+    le, re_ = ctx.nyu_cross_agg(gl, gr, lv, rv, 2, exact_params())
+    assert np.array_equal(np.transpose(le, (2, 0, 1)), lref) and np.array_equal(np.transpose(re_, (2, 0, 1)), rref)
+
+
 @pytest.mark.parametrize("direction", [-1, 1])
 def test_sgm_bit_exact(ctx, scene, direction):
     l_img, r_img = po.normalise_guide(scene["ld"]), po.normalise_guide(scene["rd"])
