@@ -280,6 +280,16 @@ def test_base_model_trunk_tensor_core_bf16x3_vs_oracle(ctx, base_layers, hw):
     assert rel_err(out, fp32.astype(np.float64)) < BASE_BF16X3_TOL
 
 
+def test_base_model_trunk_tensor_core_many_bands_vs_fp32_path(ctx, base_layers):
+    """A larger input (four 128-pixel strips, a dozen row bands per image) against the fp32 CUDA-core path, which the
+    small cases above tie to the float64 oracle."""
+    x = np.random.default_rng(21).standard_normal((2, 130, 420, 3)).astype(np.float32)
+    fp32 = ctx.trunk(_lib.NET_WIN37, x, _lib.PREC_FP32)
+    out = ctx.trunk(_lib.NET_WIN37, x, _lib.PREC_BF16X3)
+    assert out.shape == fp32.shape == (2, 94, 384, 64)
+    assert rel_err(out, fp32.astype(np.float64)) < BASE_BF16X3_TOL
+
+
 def test_base_model_trunk_tensor_core_bf16_reports_its_own_tolerance(ctx, base_layers):
     x = np.random.default_rng(4).standard_normal((1, 45, 170, 3)).astype(np.float32)
     ref = so.trunk_forward(x, base_layers, "win37_dep9", np.float64)
