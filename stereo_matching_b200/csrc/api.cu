@@ -132,12 +132,10 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
             DevBuf *act = lane ? ctx->act_b + 2 * (lane - 1) : ctx->act;
             STEREO_TRY(act[0].reserve(2 * plane_elems * 2));
             STEREO_TRY(act[1].reserve(2 * plane_elems * 2));
-            STEREO_TRY(ctx->feat.reserve(sizeof(float) * (size_t)n * h1 * w1 * 32));
             uint16_t *buf_hi[2] = {act[0].as<uint16_t>(), act[1].as<uint16_t>()};
             uint16_t *buf_lo[2] = {buf_hi[0] + plane_elems, buf_hi[1] + plane_elems};
-            STEREO_TRY(launch_conv_ffma(ctx, nd.layer[0], wts, in, n, h, w, ctx->feat.as<float>()));
-            STEREO_TRY(launch_nhwc_to_planar_g(ctx, ctx->feat.as<float>(), n, h1, w1, 32, wp, buf_hi[0],
-                                               planes == 2 ? buf_lo[0] : nullptr));
+            // layer 1 writes the chunk-planar (hi, lo) planes itself
+            STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, buf_hi[0], planes == 2 ? buf_lo[0] : nullptr, wp));
             // STEREO_CONV5_KERNEL=1: conv_tcg.cu (one MMA per tap); default: conv_tcr.cu (each input row once)
             static const bool per_tap = [] { const char *e = getenv("STEREO_CONV5_KERNEL"); return e && atoi(e) == 1; }();
             size_t img_total = 0;

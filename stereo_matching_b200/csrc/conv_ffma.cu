@@ -172,6 +172,21 @@ __global__ __launch_bounds__(256, 2) void conv_ffma_kernel(const float *__restri
                     *reinterpret_cast<uint2 *>(out_hi + off) = make_uint2(hi[0], hi[1]);
                     if (out_lo != nullptr) *reinterpret_cast<uint2 *>(out_lo + off) = make_uint2(lo[0], lo[1]);
                 }
+            } else if constexpr (COUT == 32) {
+                // four chunks of eight channels; this thread holds channels 4 cg .. 4 cg + 3
+                uint32_t hi[2], lo[2];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    float a0 = v[2 * e], a1 = v[2 * e + 1];
+                    __nv_bfloat16 h0 = __float2bfloat16_rn(a0), h1 = __float2bfloat16_rn(a1);
+                    __nv_bfloat16 l0 = __float2bfloat16_rn(a0 - __bfloat162float(h0));
+                    __nv_bfloat16 l1 = __float2bfloat16_rn(a1 - __bfloat162float(h1));
+                    hi[e] = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+                    lo[e] = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+                }
+                size_t off = ((((size_t)blockIdx.z * h_out + gy) * 4 + (cg >> 1)) * wp_out + gx) * 8 + (cg & 1) * 4;
+                *reinterpret_cast<uint2 *>(out_hi + off) = make_uint2(hi[0], hi[1]);
+                if (out_lo != nullptr) *reinterpret_cast<uint2 *>(out_lo + off) = make_uint2(lo[0], lo[1]);
             }
             continue;
         }
@@ -216,11 +231,13 @@ int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, 
     return STEREO_E_INVALID;
 }
 
-// First layer of base_model_ws_9 with the output written as chunk-planar bf16 (hi, lo)
+// First layer of base_model_ws_9 / base_model with the output written as chunk-planar bf16 (hi, lo)
 int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in, int n,
                             int h_in, int w_in, void *out_hi, void *out_lo, int wp_out)
 {
-    STEREO_REQUIRE(L.ks == 3 && L.cin == 3 && L.cout == 64, "split output is only built for the 3x3 3->64 layer");
+    if (L.ks == 5 && L.cin == 3 && L.cout == 32)        // first layer of base_model
+        return launch_one<5, 3, 32, 3>(ctx, L, weights, in, n, h_in, w_in, nullptr, out_hi, out_lo, wp_out);
+    STEREO_REQUIRE(L.ks == 3 && L.cin == 3 && L.cout == 64, "split output is only built for the first layers (3x3 3->64, 5x5 3->32)");
     return launch_one<3, 3, 64, 3>(ctx, L, weights, in, n, h_in, w_in, nullptr, out_hi, out_lo, wp_out);
 }
 
