@@ -284,7 +284,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     const int hp = h + nd.shrink, wp = w + nd.shrink;
     const size_t pad_img = (size_t)hp * wp * 3;
     const size_t feat_img = (size_t)h * w * 64;
-    STEREO_TRY(ctx->padded.reserve(sizeof(float) * 2 * pad_img));
+    STEREO_TRY(ctx->padded.reserve(sizeof(float) * 2 * pad_img * 4));      // one padded pair per lane
     STEREO_TRY(ctx->feat.reserve(sizeof(float) * 2 * feat_img));
     float *padded = ctx->padded.as<float>();
     float *feat = ctx->feat.as<float>();
@@ -297,12 +297,12 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     // first CTAs of one pair's next kernel fill the SMs that the tail of another pair's kernel leaves idle, and
     // launch gaps disappear.  Kernel-class profiling wants every kernel alone on the GPU: one lane while it is on.
     static const int max_lanes = [] { const char *e = getenv("STEREO_PAIR_LANES"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
-    int lanes = (from_u8 && !ctx->prof.on) ? max_lanes : 1;
+    int lanes = (tc_corr && !ctx->prof.on) ? max_lanes : 1;
     if (lanes > n) lanes = n;
     cudaStream_t lane_stream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (tc_corr) {
         // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
-        if (from_u8) STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
+        STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
         STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[0], 0));
         if (lanes > 1) {
             if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
@@ -335,9 +335,14 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
         const int lane = i % lanes;
         LaneStream on_lane(ctx, lane_stream[lane]);
         // left and right of one pair go through the trunk as a batch of two
-        if (!from_u8) {
-            STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded));
-            STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded + pad_img));
+        float *padded_lane = padded + (size_t)lane * 2 * pad_img;
+        if (tc_corr && !from_u8) {
+            // base_model: the statistics of all pairs are there already, the lane has its own padded images
+            STEREO_TRY(launch_pad_with_stats(ctx, left_rgb + i * img_bytes, h, w, patch, 2 * i, padded_lane));
+            STEREO_TRY(launch_pad_with_stats(ctx, right_rgb + i * img_bytes, h, w, patch, 2 * i + 1, padded_lane + pad_img));
+        } else if (!from_u8) {
+            STEREO_TRY(launch_normalize_pad(ctx, left_rgb + i * img_bytes, 1, h, w, patch, padded_lane));
+            STEREO_TRY(launch_normalize_pad(ctx, right_rgb + i * img_bytes, 1, h, w, patch, padded_lane + pad_img));
         }
         float *lv = left_vol ? left_vol + i * map * D : nullptr;
         float *rv = right_vol ? right_vol + i * map * D : nullptr;
@@ -350,13 +355,13 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             po.lo = f.l_lo + (size_t)f.ml * 8;
             po.wf = f.wf;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
-            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, nullptr, precision, &po,
+            STEREO_TRY(trunk_dev(ctx, net, padded_lane, 2, hp, wp, nullptr, precision, &po,
                                  from_u8 ? left_rgb + i * img_bytes : nullptr, from_u8 ? right_rgb + i * img_bytes : nullptr,
                                  2 * i, lane));
             STEREO_TRY(launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, 1, h, w, f.wf, f.ml, D, planes, lv, rv,
                                       left_disp + i * map, right_disp + i * map));
         } else {
-            STEREO_TRY(trunk_dev(ctx, net, padded, 2, hp, wp, feat, precision));
+            STEREO_TRY(trunk_dev(ctx, net, padded_lane, 2, hp, wp, feat, precision));
             STEREO_TRY(corr_dev(ctx, feat, feat + feat_img, 1, h, w, 64, D, precision, lv, rv, left_disp + i * map,
                                 right_disp + i * map));
         }

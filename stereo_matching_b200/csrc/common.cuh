@@ -148,6 +148,7 @@ struct ProfScope {
 
 // prep.cu
 int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out);
+int launch_pad_with_stats(stereo_ctx *ctx, const uint8_t *rgb, int h, int w, int patch, int stats_index, float *out);
 int launch_pair_stats(stereo_ctx *ctx, const uint8_t *left, const uint8_t *right, int n, int h, int w);
 // conv1_direct.cu
 int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,

@@ -149,4 +149,19 @@ int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int 
     return STEREO_OK;
 }
 
+// normalise + pad one image with statistics that are already in ctx->stats[stats_index] (launch_pair_stats)
+int launch_pad_with_stats(stereo_ctx *ctx, const uint8_t *rgb, int h, int w, int patch, int stats_index, float *out)
+{
+    STEREO_REQUIRE(patch >= 1 && (patch & 1), "patch size must be odd and positive, got %d", patch);
+    ProfScope prof(ctx, STEREO_K_PREP);
+    const int pad = (patch - 1) / 2;
+    const size_t total = (size_t)(h + 2 * pad) * (w + 2 * pad) * 3;
+    int gx = (int)((total + 255) / 256);
+    if (gx > ctx->sm_count * 8) gx = ctx->sm_count * 8;
+    normalize_pad_kernel<<<dim3(gx, 1), 256, 0, ctx->stream>>>(rgb, ctx->stats.as<ImageStats>() + stats_index, h, w, pad, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 }  // namespace stereo

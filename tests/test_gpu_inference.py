@@ -280,6 +280,19 @@ def test_base_model_trunk_tensor_core_bf16x3_vs_oracle(ctx, base_layers, hw):
     assert rel_err(out, fp32.astype(np.float64)) < BASE_BF16X3_TOL
 
 
+def test_base_model_batched_pairs_equal_single_pairs(ctx, base_layers):
+    """Three pairs in one call alternate over two streams with their own padded images, activations and feature
+    planes: every pair's maps and volumes must be those of a call with that pair alone."""
+    D = 40
+    pairs = [synth.make_pair(1300 + i, 38, 150, D) for i in range(3)]
+    left, right = np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+    both = ctx.pairs(_lib.NET_WIN37, left, right, D, precision=_lib.PREC_BF16X3, volumes=True)
+    for i in range(3):
+        one = ctx.pairs(_lib.NET_WIN37, left[i], right[i], D, precision=_lib.PREC_BF16X3, volumes=True)
+        for k in ("left_disp", "right_disp", "outlier", "left_cost", "right_cost"):
+            assert np.array_equal(both[k][i], one[k][0]), (i, k)
+
+
 def test_base_model_trunk_tensor_core_many_bands_vs_fp32_path(ctx, base_layers):
     """A larger input (four 128-pixel strips, a dozen row bands per image) against the fp32 CUDA-core path, which the
     small cases above tie to the float64 oracle."""
