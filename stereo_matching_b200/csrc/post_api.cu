@@ -223,10 +223,10 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             pool.push_back(tmp);
             advance(dst);
         }
-        if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
-            STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[4 + side]));
-        // post.lua:226-229: disp = argmin - 1 (0-based here)
+        // post.lua:226-229: disp = argmin - 1 (0-based here); the stage image of cross_agg 2 is the same map
         STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, side == 0 ? m.u8a : m.u8b));
+        if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[4 + side], side == 0 ? m.u8a : m.u8b, hw, cudaMemcpyDeviceToDevice, ctx->stream));
         if (side == 0) left_final = cur;
         else STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->stream));      // still the second stream here
     }
@@ -447,8 +447,8 @@ int stereo_pairs_post_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, con
         STEREO_TRY(stereo_pairs_dev(ctx, net, left_rgb + (size_t)i * hw * 3, right_rgb + (size_t)i * hw * 3, 1, h, w, D,
                                     precision, maps, maps + hw, nullptr, ctx->stage_vol[0].as<float>(),
                                     ctx->stage_vol[1].as<float>()));
-        uint8_t *stages[8];
-        for (int k = 0; k < 8; ++k) stages[k] = maps + (2 + k) * hw;
+        // only the final maps are asked for: the six intermediate stage images (one WTA over a volume each) are skipped
+        uint8_t *stages[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
         stages[6] = nyu_post + (size_t)i * hw;                                   // "nyu_post"
         if (outlier) stages[7] = outlier + (size_t)i * hw;                      // "outlier" (label * 127)
         STEREO_TRY(post_dev(ctx, ctx->stage_vol[0].as<float>(), ctx->stage_vol[1].as<float>(), maps, maps + hw, h, w, D, p,
