@@ -46,8 +46,11 @@ def timed(fn, reps):
 
 
 post_ms = timed(lambda: ctx.post_dev(d_lv.data_ptr(), d_rv.data_ptr(), d_ld.data_ptr(), d_rd.data_ptr(), H, W, D, ptrs), 5)
-d_np = torch.empty((1, H, W), dtype=torch.uint8, device=dev)
+d_np = torch.empty((4, H, W), dtype=torch.uint8, device=dev)
 pp = _lib.default_post_params()
 full_ms = timed(lambda: ctx.pairs_post_dev(m.net, d_left.data_ptr(), d_right.data_ptr(), 1, H, W, D, prec, pp,
                                            d_np.data_ptr()), 5)
-print(json.dumps({"D": D, "post_chain_ms": post_ms, "full_pipeline_ms": full_ms}))
+d_l4, d_r4 = d_left.unsqueeze(0).repeat(4, 1, 1, 1).contiguous(), d_right.unsqueeze(0).repeat(4, 1, 1, 1).contiguous()
+full4_ms = timed(lambda: ctx.pairs_post_dev(m.net, d_l4.data_ptr(), d_r4.data_ptr(), 4, H, W, D, prec, pp,
+                                            d_np.data_ptr()), 3) / 4
+print(json.dumps({"D": D, "post_chain_ms": post_ms, "full_pipeline_ms": full_ms, "full_pipeline_ms_batch4": full4_ms}))
