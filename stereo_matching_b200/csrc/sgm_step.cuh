@@ -104,7 +104,8 @@ __device__ __forceinline__ void sgm_step_coded(const SgmPenalties<SD> &pen, int 
 #pragma unroll
     for (int k = 0; k < KPL; ++k) {
         const bool both = code[k] == want;
-        const float P1m = both ? P1mx : pen.P1c_m, P1p = both ? P1px : pen.P1c_p;
+        // on the horizontal paths no alpha1 is applied: P1 is the same for d - 1 and d + 1, one select less
+        const float P1m = both ? P1mx : pen.P1c_m, P1p = SD < 2 ? P1m : (both ? P1px : pen.P1c_p);
         float m = fminf(prev[k], both ? pmin_p2x : pmin_p2c);
         const float pm = k > 0 ? prev[k > 0 ? k - 1 : 0] : below;
         const float pp = k < KPL - 1 ? prev[k < KPL - 1 ? k + 1 : 0] : above;
