@@ -432,9 +432,17 @@ __global__ void volume_moments_kernel(const float *__restrict__ vol, size_t n, d
 __global__ void volume_std_final_kernel(const double *__restrict__ partial, int nblocks, double n,
                                         float *__restrict__ result)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // one warp: lane l adds partials l, l + 32, ... in order, then a fixed shuffle tree - deterministic, and
+    // ~40 dependent loads instead of ~2 400
+    if (blockIdx.x != 0 || threadIdx.x >= 32) return;
     double s = 0.0, ss = 0.0;
-    for (int i = 0; i < nblocks; ++i) { s += partial[2 * i]; ss += partial[2 * i + 1]; }
+    for (int i = threadIdx.x; i < nblocks; i += 32) { s += partial[2 * i]; ss += partial[2 * i + 1]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_down_sync(0xffffffffu, s, o);
+        ss += __shfl_down_sync(0xffffffffu, ss, o);
+    }
+    if (threadIdx.x != 0) return;
     double mean = s / n;
     double var = (ss - s * mean) / (n - 1.0);
     result[0] = (float)sqrt(var > 0.0 ? var : 0.0);
