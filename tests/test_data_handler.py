@@ -156,3 +156,14 @@ def test_inference_reader_kitti2012_replicates_the_grey_channel(kitti):
     raw = kitti["raw"][2]
     assert np.array_equal(gt3, (raw >> 8).astype(np.uint8))                 # cv2 GRAYSCALE of a 16-bit PNG = high byte
     assert np.array_equal(l3[:, :, 1], grey)
+
+
+def test_preprocess_cli_reuses_an_existing_permutation(kitti, tmp_path):
+    """`python -m stereo_matching_b200.preprocess --perm myPerm.bin`: location files regenerated for a given split."""
+    out = tmp_path / "again"
+    rc = preprocess.main(["--data_root", kitti["root"], "--save_dir", str(out), "--tr_num", str(TR), "--val_num", str(VAL),
+                          "--psz", str(PSZ), "--half_range", str(HR), "--n_files", str(N_FILES),
+                          "--perm", os.path.join(kitti["util"], "myPerm.bin")])
+    assert rc == 0
+    for name in ("myPerm.bin", "tr_%d_%d_%d.bin" % (TR, PSZ, HR), "val_%d_%d_%d.bin" % (VAL, PSZ, HR)):
+        assert open(out / name, "rb").read() == open(os.path.join(kitti["util"], name), "rb").read()
