@@ -442,6 +442,23 @@ def run_b200(args):
             "three_px_error_pair0_after_post": three_pixel_error(post_final.astype(np.int64), gt[0]),
         }
 
+    # ---- post chain on the host cores: the C/OpenMP restatement on a bounded sample of the same pair ----
+    if not args.no_post and not args.no_cpu_baseline and rank == 0:
+        try:
+            from oracle import post_oracle as po
+            prow = min(48, H)
+            lv_h, rv_h = d_lv[:prow].cpu().numpy(), d_rv[:prow].cpu().numpy()
+            ld_h, rd_h = d_ld[0, :prow].cpu().numpy(), d_rd[0, :prow].cpu().numpy()
+            t0 = time.perf_counter()
+            po.post_chain(lv_h, rv_h, ld_h, rd_h)
+            psec = time.perf_counter() - t0
+            extra["post_chain"]["cpu_baseline"] = {
+                "value": (prow / H) / psec, "unit": UNIT, "cores": po.num_threads(), "kind": "port",
+                "sample": f"oracle/post_oracle.post_chain (C, OpenMP) on the first {prow} of {H} rows of pair 0's volumes, "
+                          f"D={D}: {psec:.1f} s; pairs/s scaled by rows/{H}"}
+        except Exception as e:          # secondary measurement: never fail the bench line
+            extra["post_chain"]["cpu_baseline"] = {"error": repr(e)}
+
     # ---- secondary: configs[4]-style patch training step, rank 0 only ------------------
     if not args.no_post and rank == 0:
         try:
