@@ -112,7 +112,7 @@ def synthetic_batch(n_pairs: int):
 
 
 # ---------------------------------------------------------------------------------------------
-def cpu_pair_seconds(rows: int, threads: int | None, repeats: int = 1):
+def cpu_pair_seconds(rows: int, threads: int | None, repeats: int = 1, banded: bool = False):
     """Time the oracle (CPU restatement of inference.py:109-183) on the first
     `rows` image rows of synthetic pair 1000.  Rows are independent in the
     reference (only the 9x9 receptive field couples them), so this is a bounded
@@ -128,7 +128,7 @@ def cpu_pair_seconds(rows: int, threads: int | None, repeats: int = 1):
     times = []
     for _ in range(repeats):
         t0 = time.perf_counter()
-        so.infer_pair(l, r, layers, "win9_dep9", 9, D, np.float32)
+        so.infer_pair(l, r, layers, "win9_dep9", 9, D, np.float32, banded=banded)
         times.append(time.perf_counter() - t0)
     return times, torch.get_num_threads()
 
@@ -534,6 +534,12 @@ def run_b200(args):
         cpu = {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"oracle/stereo_oracle.infer_pair fp32 (torch-CPU conv + per-disparity numpy loop) on the "
                          f"first {args.cpu_rows} of {H} rows of one pair, D={D}: {times[0]:.1f} s"}
+        # the "fair" vectorised CPU variant (one banded W x W product per row), labelled separately
+        vt, _ = cpu_pair_seconds(args.cpu_rows, None, repeats=1, banded=True)
+        extra["cpu_baseline_vectorised"] = {
+            "value": (args.cpu_rows / H) / vt[0], "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"the same sample with the cost volumes as one BLAS product per image row "
+                      f"(oracle/stereo_oracle.cost_volumes_banded): {vt[0]:.1f} s; not the reference's loop structure"}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -117,6 +117,29 @@ def cost_volumes(lmap: np.ndarray, rmap: np.ndarray, disp_range: int,
     return left, right
 
 
+def cost_volumes_banded(lmap: np.ndarray, rmap: np.ndarray, disp_range: int, dtype=np.float32):
+    """The same two volumes the "fair" way for a CPU: per image row one W x W product
+    S = L[y] @ R[y].T through BLAS, of which only the band 0 <= xl - xr < D is kept,
+      left [y, x, d] = S[x, x - d],   right[y, x, d] = S[x + d, x].
+    Not the reference's loop structure (inference.py:139-150 runs D element-wise multiply-reduce passes): it is
+    timed beside `cost_volumes` in bench.py and labelled as such.  Unwritten slots stay 0.0."""
+    h, w = lmap.shape[1], lmap.shape[2]
+    left = np.zeros((h, w, disp_range), dtype)
+    right = np.zeros((h, w, disp_range), dtype)
+    d = np.arange(min(disp_range, w))
+    x = np.arange(w)
+    xl, dd = np.meshgrid(x, d, indexing="ij")              # left:  S[x, x - d] where x >= d
+    ok_l = xl >= dd
+    ok_r = xl + dd < w                                     # right: S[x + d, x] where x + d < W
+    lm = lmap[0].astype(dtype, copy=False)
+    rm = rmap[0].astype(dtype, copy=False)
+    for y in range(h):
+        S = lm[y] @ rm[y].T
+        left[y][:, :len(d)][ok_l] = S[xl[ok_l], (xl - dd)[ok_l]]
+        right[y][:, :len(d)][ok_r] = S[(xl + dd)[ok_r], xl[ok_r]]
+    return left, right
+
+
 def wta(volume: np.ndarray) -> np.ndarray:
     """/root/reference/inference.py:169-183: argmax over all D slots (zero-filled
     ones included), first maximum wins, cast to uint8."""
@@ -143,12 +166,14 @@ def volume_bytes(volume: np.ndarray) -> bytes:
 
 
 def infer_pair(left_u8, right_u8, layers, net="win9_dep9", patch_size=9,
-               disp_range=201, dtype=np.float64):
-    """One iteration of the per-pair loop, inference.py:99-183."""
+               disp_range=201, dtype=np.float64, banded=False):
+    """One iteration of the per-pair loop, inference.py:99-183 (`banded`: the cost volumes through
+    `cost_volumes_banded` instead of the reference's D-loop)."""
     l = normalize_and_pad(left_u8, patch_size)
     r = normalize_and_pad(right_u8, patch_size)
     lmap = trunk_forward(l, layers, net, dtype)
     rmap = trunk_forward(r, layers, net, dtype)
-    lv, rv = cost_volumes(lmap, rmap, disp_range, accumulate=dtype)
+    lv, rv = (cost_volumes_banded(lmap, rmap, disp_range, dtype) if banded
+              else cost_volumes(lmap, rmap, disp_range, accumulate=dtype))
     return {"lmap": lmap, "rmap": rmap, "left_cost": lv, "right_cost": rv,
             "left_disp": wta(lv), "right_disp": wta(rv)}

@@ -128,3 +128,15 @@ def test_synthetic_pair_ground_truth_is_consistent():
     # a visible pixel shows the same colour in both views
     assert np.array_equal(l[ys, xs], r[ys, xs - d])
     assert (gt > 0).mean() > 0.5
+
+
+def test_banded_cost_volumes_equal_the_reference_loop():
+    """The vectorised CPU variant bench.py times beside the reference's D-loop gives the same volumes."""
+    rng = np.random.default_rng(5)
+    L = rng.standard_normal((1, 3, 37, 64)).astype(np.float32)
+    R = rng.standard_normal((1, 3, 37, 64)).astype(np.float32)
+    for D in (6, 37, 50):
+        lref, rref = so.cost_volumes(L, R, D, np.float64)
+        lb, rb = so.cost_volumes_banded(L, R, D, np.float64)
+        assert np.allclose(lb, lref, rtol=0, atol=1e-12) and np.allclose(rb, rref, rtol=0, atol=1e-12)
+        assert np.array_equal(lb == 0, lref == 0)
