@@ -134,9 +134,29 @@ static void sgm_step(const float *x0, const float *x1, const float *vol, float *
     }
 }
 
+static void sgm_diagonals(const float *x0, const float *x1, const float *vol, float *out,
+                          int H, int W, int D, float pi1, float pi2, float tau_so, float alpha1,
+                          float q1, float q2, int direction);
+
+/* `paths` = 4: the reference (nyu.lua:59-60).  `paths` = 8 is NOT in the reference: the four
+ * diagonal paths (4: down-right, 5: down-left, 6: up-right, 7: up-left) are added after the
+ * four of the original with the same step (no alpha1 scaling, which the original applies to
+ * the two vertical paths only); the caller divides by 8.  BASELINE.json configs[3] names an
+ * 8-path chain; it is kept apart from every parity figure. */
+void oracle_sgm2_paths(const float *x0, const float *x1, const float *vol, float *out,
+                       int H, int W, int D, float pi1, float pi2, float tau_so, float alpha1,
+                       float q1, float q2, int direction, int paths);
+
 void oracle_sgm2(const float *x0, const float *x1, const float *vol, float *out,
                  int H, int W, int D, float pi1, float pi2, float tau_so, float alpha1,
                  float q1, float q2, int direction)
+{
+    oracle_sgm2_paths(x0, x1, vol, out, H, W, D, pi1, pi2, tau_so, alpha1, q1, q2, direction, 4);
+}
+
+void oracle_sgm2_paths(const float *x0, const float *x1, const float *vol, float *out,
+                       int H, int W, int D, float pi1, float pi2, float tau_so, float alpha1,
+                       float q1, float q2, int direction, int paths)
 {
     /* horizontal paths: scanlines (rows) are independent */
     for (int sd = 0; sd < 2; ++sd) {
@@ -176,6 +196,33 @@ void oracle_sgm2(const float *x0, const float *x1, const float *vol, float *out,
             free(a); free(b);
         }
     }
+    if (paths == 8) sgm_diagonals(x0, x1, vol, out, H, W, D, pi1, pi2, tau_so, alpha1, q1, q2, direction);
+}
+
+/* the four diagonal paths: image rows in path order, the previous row's path costs kept whole */
+static void sgm_diagonals(const float *x0, const float *x1, const float *vol, float *out,
+                          int H, int W, int D, float pi1, float pi2, float tau_so, float alpha1,
+                          float q1, float q2, int direction)
+{
+    float *rows[2];
+    rows[0] = (float *)malloc(sizeof(float) * (size_t)W * D);
+    rows[1] = (float *)malloc(sizeof(float) * (size_t)W * D);
+    for (int sd = 4; sd < 8; ++sd) {
+        int dx = (sd == 4 || sd == 6) ? 1 : -1;
+        int dy = sd < 6 ? 1 : -1;
+        for (int step = 0; step < H; ++step) {
+            int y = dy > 0 ? step : H - 1 - step;
+            const float *prow = rows[(step + 1) & 1];
+            float *crow = rows[step & 1];
+#pragma omp parallel for schedule(static)
+            for (int x = 0; x < W; ++x) {
+                int first = step == 0 || x - dx < 0 || x - dx >= W;
+                sgm_step(x0, x1, vol, out, first ? crow : prow + (size_t)(x - dx) * D, crow + (size_t)x * D,
+                         H, W, D, x, y, dx, dy, sd, direction, pi1, pi2, tau_so, alpha1, q1, q2, first);
+            }
+        }
+    }
+    free(rows[0]); free(rows[1]);
 }
 
 /* nyu.lua:95  adcensus.outlier_detection(d0, d1, outlier, disp_max)

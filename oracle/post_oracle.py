@@ -68,14 +68,14 @@ def cbca(x0c, x1c, vol, direction):
     return out
 
 
-def sgm2(x0, x1, vol_hwd, direction, p=NYU):
+def sgm2(x0, x1, vol_hwd, direction, p=NYU, paths=4):
     vol = _f32(vol_hwd)
     h, w, d = vol.shape
     out = np.zeros_like(vol)
-    lib().oracle_sgm2(_fp(_f32(x0)), _fp(_f32(x1)), _fp(vol), _fp(out), h, w, d,
-                      ctypes.c_float(p["pi1"]), ctypes.c_float(p["pi2"]), ctypes.c_float(p["tau_so"]),
-                      ctypes.c_float(p["alpha1"]), ctypes.c_float(p["sgm_q1"]),
-                      ctypes.c_float(p["sgm_q2"]), int(direction))
+    lib().oracle_sgm2_paths(_fp(_f32(x0)), _fp(_f32(x1)), _fp(vol), _fp(out), h, w, d,
+                            ctypes.c_float(p["pi1"]), ctypes.c_float(p["pi2"]), ctypes.c_float(p["tau_so"]),
+                            ctypes.c_float(p["alpha1"]), ctypes.c_float(p["sgm_q1"]),
+                            ctypes.c_float(p["sgm_q2"]), int(direction), int(paths))
     return out
 
 
@@ -152,14 +152,17 @@ def nyu_cross_agg(l_img, r_img, left_vol, right_vol, iters):
     return left_vol, right_vol
 
 
-def nyu_sgm(l_img, r_img, vol_dhw, direction, p=NYU):
-    """smooth/nyu.lua:47-75: permute to [H,W,D], sgm_i sweeps, result = out / 4."""
+def nyu_sgm(l_img, r_img, vol_dhw, direction, p=NYU, paths=4):
+    """smooth/nyu.lua:47-75: permute to [H,W,D], sgm_i sweeps, result = out / 4.
+    `paths=8` (not in the reference, see oracle_sgm2_paths) adds the four diagonals and divides by 8."""
+    if paths not in (4, 8):
+        raise ValueError("paths must be 4 or 8")
     vol = np.ascontiguousarray(np.transpose(vol_dhw, (1, 2, 0)))
     out = None
     for _ in range(p["sgm_i"]):
-        out = sgm2(l_img, r_img, vol, direction, p)
-        vol = out / np.float32(4)
-    return np.ascontiguousarray(np.transpose(out, (2, 0, 1))) / np.float32(4)
+        out = sgm2(l_img, r_img, vol, direction, p, paths)
+        vol = out / np.float32(paths)
+    return np.ascontiguousarray(np.transpose(out, (2, 0, 1))) / np.float32(paths)
 
 
 def nyu_post(disp, left_vol_dhw, p=NYU):
@@ -197,11 +200,16 @@ def volume_std(vol):
 
 
 def post_chain(left_cost_hwd, right_cost_hwd, left_disp_u8, right_disp_u8,
-               nyu_cost_agg_1=1, sgm=1, nyu_cost_agg_2=1, post=1, p=NYU):
-    """post.lua:78-243 with default options.  Inputs are what inference.py wrote:
-    the two [H,W,D] float32 volumes and the two uint8 WTA maps, which post.lua
-    loads as its guide images (post.lua:91-92).  Returns every stage PNG as a
-    uint8 array plus the final float map."""
+               nyu_cost_agg_1=1, sgm=1, nyu_cost_agg_2=1, post=1, p=NYU,
+               cost_agg=0, cost_agg_2=0, confLoc=0, cost_w=5, cost_h=5, thres=23.0, sgm_paths=4):
+    """post.lua:78-243.  Inputs are what inference.py wrote: the two [H,W,D] float32
+    volumes and the two uint8 WTA maps, which post.lua loads as its guide images
+    (post.lua:91-92).  Returns every stage PNG as a uint8 array plus the final float
+    map.  The optional branches (`cost_agg`, `confLoc`, `cost_agg_2`; off by default in
+    post.lua:37-49) run in post.lua's order: box aggregation of the left volume
+    (:97-115), CBCA 1 (:116-137), threshold (:139-142), std (:146-147), SGM (:149-166),
+    CBCA 2 (:168-186), box aggregation 2 (:188-221), nyu.post (:223-242).
+    `sgm_paths=8` is NOT the reference (its chain is 4-path): see nyu_sgm."""
     stages = {}
     unary = _f32(left_cost_hwd)
     right_unary = _f32(right_cost_hwd)
@@ -209,25 +217,45 @@ def post_chain(left_cost_hwd, right_cost_hwd, left_disp_u8, right_disp_u8,
     right_unary = np.where(np.isnan(right_unary), np.float32(1e38), right_unary)
     l_img = normalise_guide(left_disp_u8)
     r_img = normalise_guide(right_disp_u8)
-    lu = np.ascontiguousarray(np.transpose(unary, (2, 0, 1)))          # post.lua:119-120
-    ru = np.ascontiguousarray(np.transpose(right_unary, (2, 0, 1)))
+    cost_vol = None
+    if cost_agg > 0:                                                     # post.lua:97-115
+        cost_vol = box_agg(unary, cost_w, cost_h, cost_agg)
+        pred = np.argmax(cost_vol, axis=2)
+        if confLoc == 1:
+            pred = np.where(cost_vol.max(axis=2) < np.float32(thres), 255, pred)    # 256 - 1, :byte()
+        stages["cost_img"] = pred.astype(np.uint8)
     if nyu_cost_agg_1 > 0:
+        lu = np.ascontiguousarray(np.transpose(unary, (2, 0, 1)))      # post.lua:119-120
+        ru = np.ascontiguousarray(np.transpose(right_unary, (2, 0, 1)))
         lu, ru = nyu_cross_agg(l_img, r_img, lu, ru, nyu_cost_agg_1)
         stages["nyu_cost_img"] = np.argmax(lu, axis=0).astype(np.uint8)      # post.lua:125-127
         stages["right_nyu_cost_img"] = np.argmax(ru, axis=0).astype(np.uint8)
+    else:
+        # post.lua:134-135 takes cost_vol / right_cost_vol; the latter is never assigned in post.lua, so the
+        # reference only runs this branch for the left volume: the raw right volume stands in here
+        lu = np.ascontiguousarray(np.transpose(cost_vol if cost_vol is not None else unary, (2, 0, 1)))
+        ru = np.ascontiguousarray(np.transpose(right_unary, (2, 0, 1)))
+    if confLoc == 1:                                                     # post.lua:139-142
+        lu = np.where(lu < np.float32(thres), np.float32(0), lu)
+        ru = np.where(ru < np.float32(thres), np.float32(0), ru)
     lu = lu / volume_std(lu)                                             # post.lua:146-147
     ru = ru / volume_std(ru)
     if sgm == 1:
         lu = lu * np.float32(-1)                                         # post.lua:152-153
         ru = ru * np.float32(-1)
-        lu = nyu_sgm(l_img, r_img, lu, -1, p)
-        ru = nyu_sgm(l_img, r_img, ru, 1, p)
+        lu = nyu_sgm(l_img, r_img, lu, -1, p, sgm_paths)
+        ru = nyu_sgm(l_img, r_img, ru, 1, p, sgm_paths)
         stages["nyu_sgm_img"] = np.argmin(lu, axis=0).astype(np.uint8)
         stages["right_nyu_sgm_img"] = np.argmin(ru, axis=0).astype(np.uint8)
-    if nyu_cost_agg_2 > 0:
+    if nyu_cost_agg_2 > 0:                                               # post.lua:168-186
         lu, ru = nyu_cross_agg(l_img, r_img, lu, ru, nyu_cost_agg_2)
         stages["nyu_cost_img_2"] = np.argmin(lu, axis=0).astype(np.uint8)
         stages["right_nyu_cost_img_2"] = np.argmin(ru, axis=0).astype(np.uint8)
+    if cost_agg_2 > 0:                                                   # post.lua:188-221
+        lu = np.ascontiguousarray(np.transpose(box_agg(np.transpose(lu, (1, 2, 0)), cost_w, cost_h, cost_agg_2), (2, 0, 1)))
+        ru = np.ascontiguousarray(np.transpose(box_agg(np.transpose(ru, (1, 2, 0)), cost_w, cost_h, cost_agg_2), (2, 0, 1)))
+        stages["post_cost_img"] = np.argmin(lu, axis=0).astype(np.uint8)
+        stages["right_post_cost_img"] = np.argmax(ru, axis=0).astype(np.uint8)     # `ru:max(1)`, post.lua:214
     if post == 1:
         disp = [np.argmin(lu, axis=0).astype(np.float32), np.argmin(ru, axis=0).astype(np.float32)]
         final, outlier = nyu_post(disp, lu, p)

@@ -15,8 +15,16 @@ dependency of this library, so the on-disk format is parsed here directly:
   {1:dtype 2:shape{2:dim{1:size}} 3:shard_id 4:offset 5:size 6:crc32c}.
 * `<prefix>.data-00000-of-00001` holds the raw little-endian tensors.
 
-`write_bundle` emits the same format (single data block, no compression) so
-that checkpoints written here can be restored by the reference.
+`write_bundle` emits the same format (single data block, no compression).
+`tf.train.Checkpoint.restore` is object-based: it walks the `TrackableObjectGraph`
+stored in the string tensor `_CHECKPOINTABLE_OBJECT_GRAPH` and looks tensors up by
+the `checkpoint_key` of each node, so a bundle without that tensor would be
+restored by NAME (`conv2d/kernel` ...), find nothing and leave the weights at
+their initial values.  `object_graph` builds the graph of
+`tf.train.Checkpoint(step, optimizer, net)` (train.py:80) for a trunk of N
+conv/BN blocks - for base_model_ws_9 byte for byte the one inside the shipped
+ckpt-1000 (tests/test_checkpoint.py) - and `write_bundle` stores `bytes` values as
+scalar DT_STRING tensors the way TensorFlow does.
 """
 from __future__ import annotations
 
@@ -224,9 +232,31 @@ def latest_checkpoint(model_dir: str) -> str | None:
     return None
 
 
+def _string_payload(value: bytes) -> Tuple[bytes, int]:
+    """On-disk bytes of a scalar DT_STRING tensor and the entry's crc32c (tensor_bundle.cc WriteStringTensor):
+    varint length, masked crc32c of the length as a little-endian uint32, the bytes; the entry checksum runs
+    over the FIXED-width length, the length checksum and the bytes (checked against ckpt-1000's object graph)."""
+    n = struct.pack("<I", len(value))
+    len_crc = struct.pack("<I", masked_crc32c(n))
+    return _put_varint(len(value)) + len_crc + value, masked_crc32c(n + len_crc + value)
+
+
+def _read_string(raw: bytes, entry: "BundleEntry", key: str, verify_crc: bool) -> bytes:
+    n, pos = _varint(raw, 0)
+    value = raw[pos + 4:]
+    if len(value) != n:
+        raise CheckpointError(f"{key}: string tensor length mismatch")
+    if verify_crc:
+        payload, crc = _string_payload(value)
+        if payload != raw or crc != entry.crc32c:
+            raise CheckpointError(f"{key}: crc32c mismatch")
+    return value
+
+
 def read_bundle(prefix: str, verify_crc: bool = False,
-                keys_filter=None) -> Dict[str, np.ndarray]:
-    """Read every numeric tensor of a bundle; string tensors are skipped."""
+                keys_filter=None, strings: bool = False) -> Dict[str, np.ndarray]:
+    """Read every numeric tensor of a bundle; scalar string tensors are returned as `bytes` when `strings` is
+    set and skipped otherwise."""
     entries = read_index(prefix + ".index")
     data_path = prefix + ".data-00000-of-00001"
     with open(data_path, "rb") as f:
@@ -234,6 +264,9 @@ def read_bundle(prefix: str, verify_crc: bool = False,
     out: Dict[str, np.ndarray] = {}
     for key, e in entries.items():
         if keys_filter is not None and not keys_filter(key):
+            continue
+        if e.dtype == _DT_STRING and strings and not e.shape:
+            out[key] = _read_string(data[e.offset:e.offset + e.size], e, key, verify_crc)
             continue
         if e.dtype == _DT_STRING or e.dtype not in _DT_NUMPY:
             continue
@@ -316,12 +349,17 @@ def _entry_proto(dtype: int, shape, offset: int, size: int, crc: int) -> bytes:
 
 
 def write_bundle(prefix: str, tensors: Dict[str, np.ndarray]) -> None:
-    """Write {key: ndarray} as a single-shard TensorBundle."""
+    """Write {key: ndarray | bytes} as a single-shard TensorBundle (`bytes` -> scalar string tensor)."""
     data = bytearray()
     entries: List[Tuple[bytes, bytes]] = []
     # BundleHeaderProto{num_shards=1, endianness=LITTLE(0, omitted), version{producer=1}}
     entries.append((b"", b"\x08\x01\x1a\x02\x08\x01"))
     for key in sorted(tensors):
+        if isinstance(tensors[key], (bytes, bytearray)):
+            raw, crc = _string_payload(bytes(tensors[key]))
+            entries.append((key.encode("utf-8"), _entry_proto(_DT_STRING, (), len(data), len(raw), crc)))
+            data += raw
+            continue
         arr = np.asarray(tensors[key], order="C")
         dt = arr.dtype.newbyteorder("<") if arr.dtype.byteorder == ">" else arr.dtype
         if np.dtype(dt) not in _NUMPY_DT:
@@ -348,3 +386,87 @@ def write_bundle(prefix: str, tensors: Dict[str, np.ndarray]) -> None:
         f.write(bytes(out))
     with open(prefix + ".data-00000-of-00001", "wb") as f:
         f.write(bytes(data))
+
+
+# ---- the object graph of tf.train.Checkpoint(step, optimizer, net) ---------------------------------------------
+OBJECT_GRAPH_KEY = "_CHECKPOINTABLE_OBJECT_GRAPH"
+_CONV_VARS = ("kernel", "bias")
+_BN_VARS = ("gamma", "beta", "moving_mean", "moving_variance")
+_ADAM_HYPERS = ("iter", "beta_1", "beta_2", "decay", "learning_rate")
+
+
+def _pb_str(field: int, value: bytes) -> bytes:
+    return _put_varint(field << 3 | 2) + _put_varint(len(value)) + value
+
+
+def _pb_int(field: int, value: int) -> bytes:
+    return _put_varint(field << 3) + _put_varint(value) if value else b""      # proto3: zero is not written
+
+
+def _keras_name(base: str, index: int) -> str:
+    return base if index == 0 else "%s_%d" % (base, index)
+
+
+def object_graph(n_blocks: int, conv_names=None, bn_names=None) -> bytes:
+    """Serialised `TrackableObjectGraph` (tensorflow/core/protobuf/trackable_object_graph.proto) of the
+    reference's `tf.train.Checkpoint(step=..., optimizer=Adam, net=model)` (train.py:78-80) where `model` is a
+    functional Keras model of `n_blocks` Conv2D + BatchNormalization pairs (models/model.py).
+
+    Node numbering and field order follow what TensorFlow wrote into the shipped ckpt-1000: root; net, optimizer,
+    step, save_counter; the InputLayer and the 2*n_blocks layers; the optimizer's hyper-parameters; the layers'
+    variables (a BatchNormalization also tracks an `axis` list wrapper, a node without attributes); then one Adam
+    `m` slot per trainable variable, then the `v` slots.  `conv_names` / `bn_names` are the Keras layer names
+    (`full_name` is informational; restore matches on the graph)."""
+    conv_names = conv_names or [_keras_name("conv2d", i) for i in range(n_blocks)]
+    bn_names = bn_names or [_keras_name("batch_normalization", i) for i in range(n_blocks)]
+    n_layers = 2 * n_blocks
+    nodes = []          # each: {"children": [(id, name)], "attr": (full_name, key) | None, "slots": [(orig, slot, id)]}
+
+    def new_node():
+        nodes.append({"children": [], "attr": None, "slots": []})
+        return len(nodes) - 1
+
+    root, net, opt, step, counter = (new_node() for _ in range(5))
+    nodes[root]["children"] = [(net, "net"), (opt, "optimizer"), (step, "step"), (counter, "save_counter")]
+    nodes[step]["attr"] = ("Variable", "step" + _SUFFIX)
+    nodes[counter]["attr"] = ("save_counter", "save_counter" + _SUFFIX)
+    input_layer = new_node()
+    layer_nodes = [new_node() for _ in range(n_layers)]
+    nodes[net]["children"].append((input_layer, "layer-0"))
+    for k, node in enumerate(layer_nodes):
+        nodes[net]["children"] += [(node, "layer_with_weights-%d" % k), (node, "layer-%d" % (k + 1))]
+    for name in _ADAM_HYPERS:
+        node = new_node()
+        nodes[opt]["children"].append((node, name))
+        nodes[node]["attr"] = ("Adam/" + name, "optimizer/%s%s" % (name, _SUFFIX))
+    trainable = []      # (node id, full name, checkpoint key stem)
+    for k, layer in enumerate(layer_nodes):
+        is_conv = k % 2 == 0
+        lname = conv_names[k // 2] if is_conv else bn_names[k // 2]
+        if not is_conv:
+            nodes[layer]["children"].append((new_node(), "axis"))
+        for var in (_CONV_VARS if is_conv else _BN_VARS):
+            node = new_node()
+            nodes[layer]["children"].append((node, var))
+            stem = "net/layer_with_weights-%d/%s" % (k, var)
+            nodes[node]["attr"] = ("%s/%s" % (lname, var), stem + _SUFFIX)
+            if not var.startswith("moving_"):
+                trainable.append((node, "%s/%s" % (lname, var), stem))
+    for slot in ("m", "v"):
+        for orig, full, stem in trainable:
+            node = new_node()
+            nodes[node]["attr"] = ("Adam/%s/%s" % (full, slot), "%s/.OPTIMIZER_SLOT/optimizer/%s%s" % (stem, slot, _SUFFIX))
+            nodes[opt]["slots"].append((orig, slot, node))
+
+    out = b""
+    for nd in nodes:
+        body = b""
+        for cid, name in nd["children"]:
+            body += _pb_str(1, _pb_int(1, cid) + _pb_str(2, name.encode()))
+        if nd["attr"]:
+            full, key = nd["attr"]
+            body += _pb_str(2, _pb_str(1, b"VARIABLE_VALUE") + _pb_str(2, full.encode()) + _pb_str(3, key.encode()))
+        for orig, slot, sid in nd["slots"]:
+            body += _pb_str(3, _pb_int(1, orig) + _pb_str(2, slot.encode()) + _pb_int(3, sid))
+        out += _pb_str(1, body)
+    return out

@@ -278,6 +278,8 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
 {
     STEREO_REQUIRE(net == STEREO_NET_WIN9 || net == STEREO_NET_WIN37, "unknown net %d", net);
     STEREO_REQUIRE(D > 0, "disp_range must be positive, got %d", D);
+    // inference.py:202-207 writes the maps as 8-bit PNGs; the 3-pixel error of a wrapped map would be meaningless
+    STEREO_REQUIRE(D <= 256, "disparity maps are bytes like the reference's PNGs; disp_range %d > 256", D);
     STEREO_REQUIRE(left_rgb && right_rgb && left_disp && right_disp, "null image or disparity pointer");
     NetDesc nd = net_desc(net);
     const int patch = nd.shrink + 1;
@@ -688,6 +690,7 @@ int stereo_wta_dev(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(check_dims(n, h, w));
     STEREO_REQUIRE(D > 0 && vol && disp, "bad argument");
+    STEREO_REQUIRE(D <= 256, "disparity maps are bytes; disp_range %d > 256", D);
     return launch_wta(ctx, vol, n, h, w, D, take_min, disp);
 }
 
@@ -696,6 +699,7 @@ int stereo_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, in
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(check_dims(n, h, w));
     STEREO_REQUIRE(D > 0 && vol && disp, "bad argument");
+    STEREO_REQUIRE(D <= 256, "disparity maps are bytes; disp_range %d > 256", D);
     size_t vol_b = sizeof(float) * (size_t)n * h * w * D;
     size_t map_b = (size_t)n * h * w;
     STEREO_TRY(h2d(ctx, ctx->stage_vol[0], vol, vol_b));
@@ -711,6 +715,7 @@ int stereo_corr_wta_dev(stereo_ctx *ctx, const float *lmap, const float *rmap, i
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(corr_args(n, h, w, c, D, precision));
     STEREO_REQUIRE(lmap && rmap && left_disp && right_disp, "null pointer");
+    STEREO_REQUIRE(D <= 256, "disparity maps are bytes; disp_range %d > 256", D);
     return corr_dev(ctx, lmap, rmap, n, h, w, c, D, precision, nullptr, nullptr, left_disp, right_disp);
 }
 
@@ -720,6 +725,7 @@ int stereo_corr_wta(stereo_ctx *ctx, const float *lmap, const float *rmap, int n
     STEREO_TRY(check_ctx(ctx));
     STEREO_TRY(corr_args(n, h, w, c, D, precision));
     STEREO_REQUIRE(lmap && rmap && left_disp && right_disp, "null pointer");
+    STEREO_REQUIRE(D <= 256, "disparity maps are bytes; disp_range %d > 256", D);
     size_t map_b = sizeof(float) * (size_t)n * h * w * c;
     size_t out_b = (size_t)n * h * w;
     STEREO_TRY(h2d(ctx, ctx->stage_in[0], lmap, map_b));

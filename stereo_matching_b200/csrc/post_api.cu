@@ -148,11 +148,9 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
     for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
     STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * 1184));
-    if (!ctx->aux_stream) {
-        STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
-        STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-        STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-    }
+    if (!ctx->aux_stream) STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+    if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    if (!ctx->ev_join) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
     STEREO_TRY(launch_guide(ctx, left_disp, h, w, m.guide_l));
     STEREO_TRY(launch_guide(ctx, right_disp, h, w, m.guide_r));
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));

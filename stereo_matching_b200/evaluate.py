@@ -3,8 +3,9 @@
 Validation patches through the trunk in inference mode (`model(x, training=False)`, evaluate.py:80-81), inner
 product of the left feature with the D right features (evaluate.py:11-17,84), arg max, and the share of patches
 whose prediction is within 3 of the label (evaluate.py:86-98).  The trunk runs in the CUDA library; the
-inner product over [N, D, 64] features is one numpy einsum.  Without KITTI, `--synthetic N` draws the
-validation patches from N synthetic pairs.
+inner product over [N, D, 64] features is one numpy einsum.  Like the reference it evaluates the `val_*.bin`
+patches through `Data_handler.evaluate()`; `--synthetic N` draws the validation patches from N generated pairs
+instead (KITTI is not shipped).
 """
 import argparse
 import sys
@@ -50,12 +51,24 @@ def main(argv=None):
     ap.add_argument("--patch_size", type=int, default=37)
     ap.add_argument("--num_val_loc", type=int, default=1000)
     ap.add_argument("--disp_range", type=int, default=201)
-    ap.add_argument("--synthetic", type=int, default=2)
+    ap.add_argument("--num_tr_img", type=int, default=160)
+    ap.add_argument("--num_val_img", type=int, default=40)
+    ap.add_argument("--synthetic", type=int, default=0,
+                    help="0 (default): the val_*.bin patches through data_handler.Data_handler, like the reference; "
+                         "N > 0: validation patches drawn from N generated pairs")
     args = ap.parse_args(argv)
     model = (base_model if args.net_type == "win37_dep9" else base_model_ws_9)((None, None, 3))
     model.load_checkpoint(args.model_dir)
-    data = train.SyntheticPatches(args.synthetic, args.patch_size, args.disp_range, args.num_val_loc, seed=321)
-    lpatch, rpatch, targets = data.next_batch()
+    if args.synthetic > 0:
+        print("NOTICE: evaluating on %d generated pairs, not on KITTI (--synthetic)" % args.synthetic)
+        data = train.SyntheticPatches(args.synthetic, args.patch_size, args.disp_range, args.num_val_loc, seed=321)
+        lpatch, rpatch, targets = data.next_batch()
+    else:
+        from .data_handler import Data_handler
+        np.random.seed(123)                                            # evaluate.py:42
+        dhandler = Data_handler(args.data_version, args.data_root, args.util_root, args.num_tr_img, args.num_val_img,
+                                args.num_val_loc, args.batch_size, args.patch_size, args.disp_range)
+        lpatch, rpatch, targets = dhandler.evaluate()                  # evaluate.py:77
     evaluate(model, lpatch, rpatch, targets, args.eval_size)
     return 0
 

@@ -17,7 +17,7 @@ import os
 
 import numpy as np
 
-from . import _lib, synth
+from . import _lib, shard, synth
 from .metric import three_pixel_error
 from .models.model import base_model, base_model_ws_9
 
@@ -53,7 +53,21 @@ def build_parser():
     p.add_argument("--device", type=int, default=0)
     p.add_argument("--no_bin", action="store_true", help="skip the .bin cost volumes")
     p.add_argument("--val_ids", default="val.npy")
+    p.add_argument("--precision", default="bf16x3", choices=sorted(PRECISIONS),
+                   help="bf16x3 (default): tcgen05 kernels, split-bf16 operands, fp32 accumulate, within the 1e-4 "
+                        "cost-volume gate; fp32: CUDA-core kernels; bf16: single pass, reports its own tolerance")
     return p
+
+
+PRECISIONS = {"fp32": _lib.PREC_FP32, "bf16x3": _lib.PREC_BF16X3, "bf16": _lib.PREC_BF16}
+
+
+def _world():
+    """(rank, world_size, local_rank) from the torchrun environment; (0, 1, None) for a plain `python -m` run."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world <= 1:
+        return 0, 1, None
+    return int(os.environ["RANK"]), world, int(os.environ.get("LOCAL_RANK", os.environ["RANK"]))
 
 
 def _read_kitti(flags, file_id):
@@ -86,10 +100,22 @@ def run(flags) -> float:
     import cv2
     if flags.data_version not in ("kitti2015", "kitti2012"):
         raise SystemExit("data_version should be either kitti2012 or kitti2015")
+    if flags.disp_range > 256:
+        raise SystemExit("--disp_range %d: disparity maps are bytes (the reference writes uint8 PNGs), at most 256"
+                         % flags.disp_range)
+    # launched with torchrun (one process per GPU): the pair list is sharded round-robin over the ranks
+    # (shard.py; the reference's loop, inference.py:99, carries no state between pairs), results meet on rank 0
+    rank, world, local_rank = _world()
+    if world > 1:
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            dist.init_process_group("gloo")          # only the per-pair errors travel; no data-path collective
+        flags.device = local_rank
+    precision = PRECISIONS[flags.precision]
     if flags.net_type == "win37_dep9":
-        model = base_model((None, None, 3), device=flags.device)
+        model = base_model((None, None, 3), device=flags.device, precision=precision)
     else:
-        model = base_model_ws_9((None, None, 3), device=flags.device)
+        model = base_model_ws_9((None, None, 3), device=flags.device, precision=precision)
     if flags.patch_size != model.shrink + 1:
         raise SystemExit("--patch_size %d does not match net_type %s (receptive field %d)"
                          % (flags.patch_size, flags.net_type, model.shrink + 1))
@@ -108,8 +134,10 @@ def run(flags) -> float:
         os.makedirs(os.path.join(flags.out_dir, sub), exist_ok=True)
 
     ctx = model.context
-    error = 0.0
-    for i, file_id in enumerate(file_ids):
+    all_ids = file_ids
+    mine = shard.shard_indices(len(all_ids), rank, world)
+    errors = []
+    for i, file_id in ((k, all_ids[k]) for k in mine):
         if flags.synthetic:
             linput, rinput, disp_targets = synth.make_pair(1000 + file_id, flags.height, flags.width, flags.disp_range)
         else:
@@ -121,7 +149,7 @@ def run(flags) -> float:
             error_id = float("nan")
         else:
             error_id = three_pixel_error(left_image_int.astype(np.int64), disp_targets)
-        error += error_id
+        errors.append(error_id)
         print(("%06d" % file_id) + "_10" + "\t" + ("%f" % error_id))
         cv2.imwrite("%s/left_disp/left_%06d_10.png" % (flags.out_dir, file_id), left_image_int)
         cv2.imwrite("%s/right_disp/right_%06d_10.png" % (flags.out_dir, file_id), right_image_int)
@@ -132,8 +160,11 @@ def run(flags) -> float:
             out["left_cost"][0].tofile(os.path.join(flags.out_dir, "left_cost", bin_name("left", file_id, h, w, flags.disp_range)))
             out["right_cost"][0].tofile(os.path.join(flags.out_dir, "right_cost", bin_name("right", file_id, h, w, flags.disp_range)))
         print("Image %s processed." % (i + 1))
-    mean = error / max(len(file_ids), 1)
-    print("Mean Error: ", mean)
+    # inference.py:236 divides by FLAGS.num_val_img; the synthetic mode by the number of generated pairs
+    n_items = len(all_ids) if flags.synthetic else flags.num_val_img
+    mean = float(sum(shard.gather_results(errors, len(all_ids), rank, world)) / max(n_items, 1))
+    if rank == 0:
+        print("Mean Error: ", mean)
     return mean
 
 

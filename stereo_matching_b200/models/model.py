@@ -75,7 +75,9 @@ def fold_batchnorm(layers: List[Dict[str, np.ndarray]], ks: int, chans: List[int
 class StereoTrunk:
     """Callable stand-in for the Keras `Model` the reference factories return."""
 
-    def __init__(self, name: str, input_shape=(None, None, 3), device: int = 0, precision: int = _lib.PREC_FP32):
+    def __init__(self, name: str, input_shape=(None, None, 3), device: int = 0, precision: int = _lib.PREC_BF16X3):
+        # default: the tcgen05 kernels with split-bf16 operands (meets the 1e-4 cost-volume gate);
+        # precision=_lib.PREC_FP32 selects the CUDA-core fp32 kernels
         if tuple(input_shape)[-1] != 3:
             raise ValueError("the reference trunks take 3-channel input (models/model.py)")
         self.name = name

@@ -126,14 +126,14 @@ def run_staged(ctx, opt, params, unary, right_unary, l_u8, r_u8):
         lu = ctx.nyu_sgm(l_img, r_img, lu * np.float32(-1), -1, params)
         ru = ctx.nyu_sgm(l_img, r_img, ru * np.float32(-1), 1, params)
         st["nyu_sgm_img"], st["right_nyu_sgm_img"] = ctx.wta(lu, take_min=True)[0], ctx.wta(ru, take_min=True)[0]
+    if opt.nyu_cost_agg_2 > 0:                                             # post.lua:168-185
+        lu, ru = ctx.nyu_cross_agg(l_img, r_img, lu, ru, opt.nyu_cost_agg_2, params)
+        st["nyu_cost_img_2"], st["right_nyu_cost_img_2"] = ctx.wta(lu, take_min=True)[0], ctx.wta(ru, take_min=True)[0]
     if opt.cost_agg_2 > 0:                                                 # post.lua:188-221
         lu = ctx.box_agg(lu, opt.cost_w, opt.cost_h, opt.cost_agg_2)
         ru = ctx.box_agg(ru, opt.cost_w, opt.cost_h, opt.cost_agg_2)
         st["post_cost_img"] = ctx.wta(lu, take_min=True)[0]
         st["right_post_cost_img"] = ctx.wta(ru)[0]                         # `ru:max(1)` in the original (post.lua:214)
-    if opt.nyu_cost_agg_2 > 0:                                             # post.lua:168-185
-        lu, ru = ctx.nyu_cross_agg(l_img, r_img, lu, ru, opt.nyu_cost_agg_2, params)
-        st["nyu_cost_img_2"], st["right_nyu_cost_img_2"] = ctx.wta(lu, take_min=True)[0], ctx.wta(ru, take_min=True)[0]
     if opt.post == 1:                                                      # post.lua:223-242
         d0 = ctx.wta(lu, take_min=True)[0].astype(np.float32)
         d1 = ctx.wta(ru, take_min=True)[0].astype(np.float32)

@@ -11,8 +11,12 @@ forward/backward on its own batch, the flat gradient array (113 088 floats for w
 ONE all-reduce (NCCL over NVLink on GPUs) and every rank applies the same Adam step.  As in any data-parallel
 BatchNorm without cross-replica sync, the batch statistics are per rank.
 
-Checkpoints are TensorBundles with the reference's key names (`net/layer_with_weights-k/...`), readable by
-the reference's `tf.train.Checkpoint(...).restore` and by `stereo_matching_b200.checkpoint`.
+Checkpoints are TensorBundles holding what the reference's `tf.train.Checkpoint(step, optimizer, net)` saves,
+under the same keys as the shipped ckpt-1000: the object graph TensorFlow's object-based restore walks (for
+base_model_ws_9 byte for byte the shipped one), the net's variables, Adam's iteration count, hyper-parameters and
+m / v slots, `step`, `save_counter`; at most three are kept (`max_to_keep=3`, train.py:81).  TensorFlow is not
+available here, so "the reference restores them" is checked structurally (same keys, dtypes, shapes and graph
+as ckpt-1000, tests/test_checkpoint.py), not by running `ckpt.restore`.
 """
 import argparse
 import os
@@ -95,18 +99,89 @@ def layers_to_state(net_type: str, layers: List[Dict[str, np.ndarray]]) -> Tuple
     return p, s
 
 
-def save_checkpoint(model_dir: str, net_type: str, step: int, params: np.ndarray, stats: np.ndarray) -> str:
-    """`ckpt-<n>` + the `checkpoint` state file, as tf.train.CheckpointManager names them (train.py:82,121)."""
+def _keras_names(net_type: str):
+    """Keras' automatic layer names.  base_model builds a Conv2D + BatchNormalization pair that never enters the
+    graph (models/model.py:21-22), so its eighth block is conv2d_8 / batch_normalization_8."""
+    n = len(NETS[net_type][2]) - 1
+    idx = list(range(n)) if net_type == "win9_dep9" else [i for i in range(n + 1) if i != 7]
+    return (["conv2d" if i == 0 else "conv2d_%d" % i for i in idx],
+            ["batch_normalization" if i == 0 else "batch_normalization_%d" % i for i in idx])
+
+
+def save_checkpoint(model_dir: str, net_type: str, step: int, params: np.ndarray, stats: np.ndarray,
+                    adam_m: np.ndarray = None, adam_v: np.ndarray = None, lr: float = None,
+                    max_to_keep: int = 3) -> str:
+    """`manager.save()` of train.py:82,121: `ckpt-<n>` + the `checkpoint` state file, at most `max_to_keep`
+    checkpoints kept (tf.train.CheckpointManager(..., max_to_keep=3)).
+
+    The bundle holds what `tf.train.Checkpoint(step, optimizer, net)` saves, under the same keys as the shipped
+    ckpt-1000: the object graph (restore is object-based and needs it), `step` (int32), `save_counter`, the net's
+    variables, Adam's `iter`, hyper-parameters and the `m` / `v` slot of every trainable variable (zeros when the
+    caller has none, e.g. weights exported without an optimizer state)."""
     os.makedirs(model_dir, exist_ok=True)
-    tensors = {"step" + _SUFFIX: np.asarray(step, np.int64)}
+    lay = layout(net_type)[0]
+    counter = step // 100 if step % 100 == 0 else step
+    m = np.zeros_like(params) if adam_m is None else np.asarray(adam_m, np.float32)
+    v = np.zeros_like(params) if adam_v is None else np.asarray(adam_v, np.float32)
+    conv_names, bn_names = _keras_names(net_type)
+    tensors = {checkpoint.OBJECT_GRAPH_KEY: checkpoint.object_graph(len(lay), conv_names, bn_names),
+               "step" + _SUFFIX: np.asarray(step, np.int32),
+               "save_counter" + _SUFFIX: np.asarray(counter, np.int64),
+               "optimizer/iter" + _SUFFIX: np.asarray(step, np.int64),
+               "optimizer/beta_1" + _SUFFIX: np.asarray(0.9, np.float32),
+               "optimizer/beta_2" + _SUFFIX: np.asarray(0.999, np.float32),
+               "optimizer/decay" + _SUFFIX: np.asarray(0.0, np.float32),
+               "optimizer/learning_rate" + _SUFFIX: np.asarray(learning_rate(step) if lr is None else lr, np.float32)}
     for k, layer in enumerate(state_to_layers(net_type, params, stats)):
         for name, arr in layer.items():
             tensors[f"net/layer_with_weights-{k}/{name}{_SUFFIX}"] = arr
-    name = f"ckpt-{step // 100 if step % 100 == 0 else step}"
+    for k, d in enumerate(lay):
+        for layer_k, name in ((2 * k, "kernel"), (2 * k, "bias"), (2 * k + 1, "gamma"), (2 * k + 1, "beta")):
+            shape = d["shape"] if name == "kernel" else (-1,)
+            stem = f"net/layer_with_weights-{layer_k}/{name}/.OPTIMIZER_SLOT/optimizer/"
+            tensors[stem + "m" + _SUFFIX] = m[d[name]].reshape(shape)
+            tensors[stem + "v" + _SUFFIX] = v[d[name]].reshape(shape)
+    name = f"ckpt-{counter}"
     checkpoint.write_bundle(os.path.join(model_dir, name), tensors)
-    with open(os.path.join(model_dir, "checkpoint"), "w") as f:
-        f.write(f'model_checkpoint_path: "{name}"\nall_model_checkpoint_paths: "{name}"\n')
+    # the state file lists every kept checkpoint, oldest first; older ones are deleted (max_to_keep)
+    state = os.path.join(model_dir, "checkpoint")
+    kept = []
+    if os.path.exists(state):
+        with open(state) as f:
+            kept = [ln.split(":", 1)[1].strip().strip('"') for ln in f if ln.startswith("all_model_checkpoint_paths:")]
+    kept = [k for k in kept if k != name] + [name]
+    while max_to_keep and len(kept) > max_to_keep:
+        old = kept.pop(0)
+        for ext in (".index", ".data-00000-of-00001"):
+            try:
+                os.remove(os.path.join(model_dir, old + ext))
+            except OSError:
+                pass
+    with open(state, "w") as f:
+        f.write(f'model_checkpoint_path: "{name}"\n')
+        for k in kept:
+            f.write(f'all_model_checkpoint_paths: "{k}"\n')
     return os.path.join(model_dir, name)
+
+
+def load_checkpoint_state(prefix: str, net_type: str) -> Dict[str, np.ndarray]:
+    """What `ckpt.restore(...)` of train.py:84 brings back: params, stats, Adam slots (None when the bundle has
+    none) and the step."""
+    params, stats = layers_to_state(net_type, checkpoint.load_net_weights(prefix))
+    b = checkpoint.read_bundle(prefix, keys_filter=lambda k: "OPTIMIZER_SLOT" in k or k.startswith("step/"))
+    lay = layout(net_type)[0]
+    m, v = np.zeros_like(params), np.zeros_like(params)
+    found = 0
+    for k, d in enumerate(lay):
+        for layer_k, name in ((2 * k, "kernel"), (2 * k, "bias"), (2 * k + 1, "gamma"), (2 * k + 1, "beta")):
+            stem = f"net/layer_with_weights-{layer_k}/{name}/.OPTIMIZER_SLOT/optimizer/"
+            if stem + "m" + _SUFFIX in b and stem + "v" + _SUFFIX in b:
+                m[d[name]] = np.asarray(b[stem + "m" + _SUFFIX], np.float32).reshape(-1)
+                v[d[name]] = np.asarray(b[stem + "v" + _SUFFIX], np.float32).reshape(-1)
+                found += 1
+    step = int(b.get("step" + _SUFFIX, 0))
+    have = found == 4 * len(lay)
+    return {"params": params, "stats": stats, "adam_m": m if have else None, "adam_v": v if have else None, "step": step}
 
 
 # ---- patches -----------------------------------------------------------------------------------------------
@@ -195,8 +270,9 @@ def main(argv=None):
     ap.add_argument("--num_val_img", type=int, default=40)
     ap.add_argument("--num_val_loc", type=int, default=5000)
     ap.add_argument("--phase", default="train")
-    ap.add_argument("--synthetic", type=int, default=4,
-                    help="number of synthetic pairs to sample patches from; 0 = KITTI through data_handler.Data_handler")
+    ap.add_argument("--synthetic", type=int, default=0,
+                    help="0 (default): KITTI through data_handler.Data_handler, like the reference; N > 0: sample the "
+                         "patches from N generated pairs instead")
     ap.add_argument("--seed", type=int, default=123)
     args = ap.parse_args(argv)
     if args.data_version != "kitti2015":
@@ -219,18 +295,16 @@ def main(argv=None):
     latest = checkpoint.latest_checkpoint(args.model_dir) if os.path.isdir(args.model_dir) else None
     step = 0
     if latest:
-        params, stats = layers_to_state(args.net_type, checkpoint.load_net_weights(latest))
-        try:
-            step = int(checkpoint.read_bundle(latest, keys_filter=lambda k: k == "step" + _SUFFIX)["step" + _SUFFIX])
-        except Exception:
-            step = 0
+        st = load_checkpoint_state(latest, args.net_type)
+        step = st["step"]
+        tr.set_state(st["params"], st["stats"], st["adam_m"], st["adam_v"], step=step)
         if rank == 0:
             print(f"Restored from {latest}")
     else:
         params, stats = init_state(args.net_type, args.seed)
+        tr.set_state(params, stats, step=0)
         if rank == 0:
             print("Initializing from scratch.")
-    tr.set_state(params, stats, step=step)
     if args.synthetic > 0:
         data = SyntheticPatches(args.synthetic, args.patch_size, args.disp_range, args.batch_size, seed=args.seed + rank)
     else:
@@ -257,7 +331,8 @@ def main(argv=None):
             acc += correct
             if step % 100 == 0 and rank == 0:
                 st = tr.get_state()
-                path = save_checkpoint(args.model_dir, args.net_type, step, st["params"], st["stats"])
+                path = save_checkpoint(args.model_dir, args.net_type, step, st["params"], st["stats"],
+                                       st["adam_m"], st["adam_v"])
                 print(f"Saved checkpoint for step {step}: {path}")
                 print("Loss at step: %d: %.6f" % (step, loss))
         if rank == 0:

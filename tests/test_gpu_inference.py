@@ -24,7 +24,8 @@ WTA_AGREE = 0.999
 
 @pytest.fixture(scope="module")
 def ws9(ws9_layers):
-    m = base_model_ws_9((None, None, 3))
+    # the fp32 CUDA-core path on purpose: the tcgen05 path (the default precision) has its own section below
+    m = base_model_ws_9((None, None, 3), precision=_lib.PREC_FP32)
     m.set_layers(ws9_layers)
     return m
 
@@ -63,7 +64,7 @@ def test_trunk_ws9_vs_oracle(ws9, ws9_layers, hw):
 
 def test_trunk_win37_vs_oracle():
     layers = synth.make_base_model_weights()
-    m = base_model((None, None, 3))
+    m = base_model((None, None, 3), precision=_lib.PREC_FP32)
     m.set_layers(layers)
     x = np.random.default_rng(3).standard_normal((1, 45, 60, 3)).astype(np.float32)
     ref = so.trunk_forward(x, layers, "win37_dep9", np.float64)
@@ -303,6 +304,43 @@ def test_base_model_trunk_tensor_core_many_bands_vs_fp32_path(ctx, base_layers):
     assert rel_err(out, fp32.astype(np.float64)) < BASE_BF16X3_TOL
 
 
+def test_base_model_full_size_strip_vs_oracle(ctx, base_layers):
+    """base_model at the benchmark size (375x1242, D = 228, models/model.py:5-28) through the tensor-core kernels:
+    band symmetry and zero fill of the whole volumes, fused WTA == WTA of the materialised volume, and the float64
+    oracle on strips of rows at the top, in the middle and at the bottom of the image (padding rows included)."""
+    D = 228
+    h, w = 375, 1242
+    l, r, gt = synth.make_pair(1000, h, w, D)
+    out = ctx.pairs(_lib.NET_WIN37, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    lv, rv = out["left_cost"][0], out["right_cost"][0]
+    for d in (0, 1, 113, 227):
+        assert np.array_equal(lv[:, d:, d], rv[:, :w - d, d])
+        assert np.all(lv[:, :d, d] == 0) and np.all(rv[:, w - d:, d] == 0)
+    assert np.array_equal(out["left_disp"][0], np.argmax(lv, axis=2).astype(np.uint8))
+    assert np.array_equal(out["right_disp"][0], np.argmax(rv, axis=2).astype(np.uint8))
+    lp, rp = so.normalize_and_pad(l, 37), so.normalize_and_pad(r, 37)
+    rows = 3
+    for y0 in (0, 186, h - rows):
+        lm = so.trunk_forward(lp[:, y0:y0 + rows + 36], base_layers, "win37_dep9", np.float64)
+        rm = so.trunk_forward(rp[:, y0:y0 + rows + 36], base_layers, "win37_dep9", np.float64)
+        lref, rref = so.cost_volumes(lm, rm, D, np.float64)
+        assert rel_err(lv[y0:y0 + rows], lref) < COST_TOL and rel_err(rv[y0:y0 + rows], rref) < COST_TOL, y0
+        assert (out["left_disp"][0][y0:y0 + rows] == so.wta(lref)).mean() >= WTA_AGREE, y0
+
+
+def test_default_precision_is_the_tensor_core_path(ws9_layers):
+    """`base_model_ws_9(...)` without a precision runs the tcgen05 kernels (split bf16, fp32 accumulate)."""
+    m = base_model_ws_9((None, None, 3))
+    assert m.precision == _lib.PREC_BF16X3
+    m.set_layers(ws9_layers)
+    x = np.random.default_rng(8).standard_normal((2, 30, 150, 3)).astype(np.float32)
+    before = m.context.launch_count
+    out = m(x, training=False)
+    assert m.context.launch_count > before
+    assert rel_err(out, so.trunk_forward(x, ws9_layers, "win9_dep9", np.float64)) < 2e-5
+    assert np.array_equal(out, m.context.trunk(_lib.NET_WIN9, x, _lib.PREC_BF16X3))
+
+
 def test_base_model_trunk_tensor_core_bf16_reports_its_own_tolerance(ctx, base_layers):
     x = np.random.default_rng(4).standard_normal((1, 45, 170, 3)).astype(np.float32)
     ref = so.trunk_forward(x, base_layers, "win37_dep9", np.float64)
@@ -340,6 +378,12 @@ def test_cost_volume_tensor_core_vs_oracle(ctx, h, w, D):
     scale = np.abs(lv).max()
     for d in range(0, min(D, w), max(D // 5, 1)):
         assert np.abs(lv[0][:, d:, d] - rv[0][:, :w - d, d]).max() <= 1e-6 * scale
+    if D > 256:
+        # disparity maps are bytes like the reference's PNGs: a wider range is refused, not wrapped
+        with pytest.raises(_lib.StereoError) as e:
+            ctx.corr_wta(L, R, D, _lib.PREC_BF16X3)
+        assert e.value.code == -1
+        return
     # fused WTA sees exactly the values that the materialising variant stores
     ld, rd = ctx.corr_wta(L, R, D, _lib.PREC_BF16X3)
     assert np.array_equal(ld, np.argmax(lv, axis=3).astype(np.uint8))

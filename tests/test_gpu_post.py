@@ -244,3 +244,126 @@ def test_pairs_post_equals_inference_then_post(ctx, D, h, w):
     from stereo_matching_b200.metric import three_pixel_error
     gt = pairs[0][2]
     assert three_pixel_error(fused["nyu_post"][0].astype(np.int64), gt) <= three_pixel_error(ref["left_disp"][0].astype(np.int64), gt)
+
+
+# ---- the benchmark size: 375 x 1242 at D = 228 (BASELINE.json) and at the reference's default D = 201 --------------
+# The ring / band / partition logic of the default kernels (sgm_ring.cu stages over 1 242 steps and 375 scanlines, the
+# row bands of cbca_fused.cu, the unaligned rows of D = 201) against the C restatement at the size they are timed at.
+@pytest.fixture(scope="module", params=[228, 201])
+def full_scene(request, ctx):
+    D = request.param
+    l, r, gt = synth.make_pair(1000, 375, 1242, D)
+    out = ctx.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    sc = {"D": D, "gt": gt, "lv": out["left_cost"][0], "rv": out["right_cost"][0],
+          "ld": out["left_disp"][0], "rd": out["right_disp"][0]}
+    sc["ref"] = po.post_chain(sc["lv"], sc["rv"], sc["ld"], sc["rd"])
+    return sc
+
+
+@pytest.mark.parametrize("exact", [0, 1])
+def test_full_size_chain_vs_oracle(ctx, full_scene, exact):
+    """post.lua:116-243 on one full pair: every stage map and the final float map (gates of test_full_chain_vs_oracle)."""
+    sc, ref = full_scene, full_scene["ref"]
+    params = _lib.default_post_params()
+    params.cbca_exact = exact
+    out = ctx.post(sc["lv"], sc["rv"], sc["ld"], sc["rd"], params)
+    for name in ("nyu_cost_img", "right_nyu_cost_img"):
+        if exact:
+            assert np.array_equal(out[name], ref[name]), name            # before the global std: bit exact
+        else:
+            assert (out[name] == ref[name]).mean() >= 0.999, name
+    for name in ("nyu_sgm_img", "right_nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2", "outlier"):
+        assert (out[name] == ref[name]).mean() >= 0.999, name
+    diff = np.abs(out["nyu_post_float"] - ref["nyu_post_float"])
+    assert (diff <= 1e-3).mean() >= 0.999
+    assert (out["nyu_post"] == ref["nyu_post"]).mean() >= 0.999
+    e_ref = so.three_pixel_error(ref["nyu_post"], sc["gt"])
+    e_out = so.three_pixel_error(out["nyu_post"], sc["gt"])
+    assert abs(e_ref - e_out) <= 0.0005
+    assert e_out < so.three_pixel_error(sc["ld"], sc["gt"])
+
+
+def test_full_size_sgm_bit_exact(ctx, full_scene):
+    """smooth.nyu.sgm alone on the full-size volumes (nyu.lua:47-75), both matching directions, bit for bit."""
+    sc = full_scene
+    l_img, r_img = po.normalise_guide(sc["ld"]), po.normalise_guide(sc["rd"])
+    for direction, vol in ((-1, sc["lv"]), (1, sc["rv"])):
+        vol = (vol / po.volume_std(vol)) * np.float32(-1)
+        ref = po.nyu_sgm(l_img, r_img, np.ascontiguousarray(np.transpose(vol, (2, 0, 1))), direction)
+        out = ctx.nyu_sgm(l_img, r_img, vol, direction)
+        assert np.array_equal(np.transpose(out, (2, 0, 1)), ref), direction
+        del ref, out
+
+
+def test_full_size_cross_agg(ctx, full_scene):
+    """smooth.nyu.cross_agg alone on the full-size volumes (nyu.lua:24-45): the original's summation order bit for
+    bit, the default single-pass kernel within its stated tolerance."""
+    sc = full_scene
+    l_img, r_img = po.normalise_guide(sc["ld"]), po.normalise_guide(sc["rd"])
+    lu = np.ascontiguousarray(np.transpose(sc["lv"], (2, 0, 1)))
+    ru = np.ascontiguousarray(np.transpose(sc["rv"], (2, 0, 1)))
+    lref, rref = po.nyu_cross_agg(l_img, r_img, lu, ru, 1)
+    del lu, ru
+    le, re_ = ctx.nyu_cross_agg(l_img, r_img, sc["lv"], sc["rv"], 1, exact_params())
+    assert np.array_equal(np.transpose(le, (2, 0, 1)), lref) and np.array_equal(np.transpose(re_, (2, 0, 1)), rref)
+    del le, re_
+    lo, ro = ctx.nyu_cross_agg(l_img, r_img, sc["lv"], sc["rv"], 1)
+    for out, ref in ((lo, lref), (ro, rref)):
+        assert np.abs(np.transpose(out, (2, 0, 1)) - ref).max() / np.abs(ref).max() < CBCA_SEPARABLE_TOL
+
+
+def test_cli_workflow_inference_post_cal(tmp_path, capsys, ws9_layers):
+    """The reference's workflow end to end through the three command lines: `inference.py` (maps + .bin volumes,
+    inference.py:202-231) -> `post.lua` (reads them back, post.lua:78-92, writes the stage PNG directories,
+    :124-132,158-166,177-185,237-241) -> `cal.py` (3-pixel error of nyu_post against gt).  The stage PNGs must be
+    those of `ctx.post` on the same volumes, and cal.py's number that of the metric on them."""
+    from stereo_matching_b200 import cal, inference
+    from stereo_matching_b200 import post as bpost
+    from stereo_matching_b200.metric import three_pixel_error
+    res = tmp_path / "results"
+    h, w, D = 60, 200, 40
+    golden = os.path.join(os.path.dirname(__file__), "golden", "new_checkpoint")
+    inference.main(["--model_dir", golden, "--out_dir", str(res), "--synthetic", "2", "--height", str(h),
+                    "--width", str(w), "--disp_range", str(D)])
+    text = capsys.readouterr().out
+    assert "Mean Error:" in text
+    n = bpost.run(bpost.build_parser().parse_args(["--saveDir", str(res), "--disp_range", str(D)]))
+    assert n == 2
+    m = base_model_ws_9((None, None, 3))
+    m.set_layers(ws9_layers)
+    errs = []
+    for fid in (0, 1):
+        l, r, gt = synth.make_pair(1000 + fid, h, w, D)
+        out = m.context.pairs(_lib.NET_WIN9, l, r, D, precision=m.precision, volumes=True)
+        lv = np.fromfile(res / "left_cost" / ("left_%06d_10_%d_%d_%d.bin" % (fid, h, w, D)), "<f4").reshape(h, w, D)
+        assert np.array_equal(lv, out["left_cost"][0])
+        assert np.array_equal(cv2.imread(str(res / "left_disp" / ("left_%06d_10.png" % fid)), 0), out["left_disp"][0])
+        assert np.array_equal(cv2.imread(str(res / "gt" / ("true_%06d_10.png" % fid)), 0), gt)
+        st = m.context.post(out["left_cost"][0], out["right_cost"][0], out["left_disp"][0], out["right_disp"][0])
+        for name in _lib.STAGE_NAMES:
+            png = cv2.imread(str(res / name / ("%06d_10.png" % fid)), cv2.IMREAD_GRAYSCALE)
+            assert png is not None and np.array_equal(png, st[name]), name
+        errs.append(three_pixel_error(st["nyu_post"], gt))
+    mean = cal.run(str(res))
+    assert mean == pytest.approx(np.mean(errs))
+    assert mean <= float(text.split("Mean Error:")[1].split()[0]) + 0.01   # the chain does not lose to the raw WTA maps
+
+
+def test_staged_path_follows_post_lua_order_with_optional_branches(ctx):
+    """post.py's staged path with cost_agg / cost_agg_2 on against the restated post.lua (oracle post_chain with the
+    same options): CBCA 2 runs before the second box aggregation (post.lua:168-186, then :188-221)."""
+    from stereo_matching_b200 import post as bpost
+    h, w, D = 40, 96, 33
+    rng = np.random.default_rng(11)
+    lv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    rv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    ld, rd = ctx.wta(lv)[0], ctx.wta(rv)[0]
+    params = exact_params()
+    opt = bpost.build_parser().parse_args(["--cost_agg", "1", "--cost_agg_2", "2"])
+    out = bpost.run_staged(ctx, opt, params, lv, rv, ld, rd)
+    ref = po.post_chain(lv, rv, ld, rd, cost_agg=1, cost_agg_2=2)
+    for name in ("cost_img", "nyu_cost_img", "right_nyu_cost_img"):
+        assert np.array_equal(out[name], ref[name]), name
+    for name in ("nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2", "post_cost_img", "right_post_cost_img",
+                 "nyu_post", "outlier"):
+        assert (out[name] == ref[name]).mean() >= 0.999, name

@@ -145,3 +145,77 @@ def test_box_agg_is_count_exclude_pad_average_pooling():
     assert np.array_equal(twice, po.box_agg(po.box_agg(vol, 5, 5), 5, 5))
     const = np.full((9, 9, 3), 2.5, np.float32)
     assert np.array_equal(po.box_agg(const, 5, 5, iters=3), const)        # borders divide by the in-image count
+
+
+def _sgm_python(x0, x1, vol, direction, paths, p=po.NYU):
+    """One-pixel-at-a-time Python loops over explicit paths (a second, independent restatement of the recurrence in
+    SURVEY.md section 8(a) P3), float32 operation for operation."""
+    f = np.float32
+    h, w, D = vol.shape
+    out = np.zeros_like(vol)
+    dirs = [(1, 0), (-1, 0), (0, 1), (0, -1), (1, 1), (-1, 1), (1, -1), (-1, -1)][:paths]
+    pi1, pi2, tau, a1, q1, q2 = (f(p[k]) for k in ("pi1", "pi2", "tau_so", "alpha1", "sgm_q1", "sgm_q2"))
+    for sd, (dx, dy) in enumerate(dirs):
+        Lr = np.zeros_like(vol)
+        ys = range(h) if dy >= 0 else range(h - 1, -1, -1)
+        xs = range(w) if dx >= 0 else range(w - 1, -1, -1)
+        for y in ys:
+            for x in xs:
+                px, py = x - dx, y - dy
+                if not (0 <= px < w and 0 <= py < h):
+                    Lr[y, x] = vol[y, x]
+                    continue
+                prev = Lr[py, px]
+                pmin = prev.min()
+                D1 = abs(x0[y, x] - x0[py, px])
+                for d in range(D):
+                    xx = x + d * direction
+                    if xx < 0 or xx >= w or xx - dx < 0 or xx - dx >= w:
+                        D2 = f(10)
+                    else:
+                        D2 = abs(x1[y, xx] - x1[py, xx - dx])
+                    if D1 < tau and D2 < tau:
+                        P1, P2 = pi1, pi2
+                    elif D1 > tau and D2 > tau:
+                        P1, P2 = pi1 / (q1 * q2), pi2 / (q1 * q2)
+                    else:
+                        P1, P2 = pi1 / q1, pi2 / q1
+                    c = min(prev[d], pmin + P2)
+                    if d > 0:
+                        c = min(c, prev[d - 1] + (P1 / a1 if sd == 2 else P1))
+                    if d + 1 < D:
+                        c = min(c, prev[d + 1] + (P1 / a1 if sd == 3 else P1))
+                    Lr[y, x, d] = vol[y, x, d] + c - pmin
+        out = out + Lr
+    return out
+
+
+@pytest.mark.parametrize("paths", [4, 8])
+@pytest.mark.parametrize("direction", [-1, 1])
+def test_sgm_c_restatement_equals_python_loops(paths, direction):
+    """The C restatement (scanline order, OpenMP) against plain Python loops, bit for bit; `paths=8` is the
+    extension named in BASELINE.json configs[3] - it has no counterpart in the reference (nyu.lua:59-64 is 4-path)."""
+    rng = np.random.default_rng(paths + direction)
+    h, w, D = 7, 9, 6
+    x0 = (rng.standard_normal((h, w)) * 0.08).astype(np.float32)
+    x1 = (rng.standard_normal((h, w)) * 0.08).astype(np.float32)
+    vol = rng.standard_normal((h, w, D)).astype(np.float32)
+    assert np.array_equal(po.sgm2(x0, x1, vol, direction, paths=paths), _sgm_python(x0, x1, vol, direction, paths))
+
+
+def test_post_chain_optional_branches_follow_post_lua_order():
+    """cost_agg_2 runs AFTER nyu_cost_agg_2 (post.lua:168-186 then :188-221): the box filter and CBCA do not commute."""
+    rng = np.random.default_rng(3)
+    h, w, D = 24, 40, 12
+    lv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    rv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    ld, rd = lv.argmax(2).astype(np.uint8), rv.argmax(2).astype(np.uint8)
+    base = po.post_chain(lv, rv, ld, rd)
+    ext = po.post_chain(lv, rv, ld, rd, cost_agg=1, cost_agg_2=2)
+    for name in ("nyu_cost_img", "nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2"):
+        assert np.array_equal(base[name], ext[name]), name              # stages before the second box filter
+    l_img, r_img = po.normalise_guide(ld), po.normalise_guide(rd)
+    want = po.box_agg(np.transpose(base["left_vol"], (1, 2, 0)), 5, 5, 2)
+    assert np.array_equal(np.transpose(ext["left_vol"], (1, 2, 0)), want)
+    assert np.array_equal(ext["post_cost_img"], want.argmin(2).astype(np.uint8))
+    assert np.array_equal(ext["cost_img"], po.box_agg(lv, 5, 5, 1).argmax(2).astype(np.uint8))
