@@ -149,6 +149,10 @@ typedef struct stereo_post_params {
     int nyu_cost_agg_1, sgm, nyu_cost_agg_2, post;  /* post.lua:37-40 */
     int cbca_exact;  /* 0: separable CBCA (row sums first; same sum, last-bit differences);
                         1: the original's strictly sequential summation order (slower) */
+    int sgm_paths;   /* 4: the reference (nyu.lua:59-64: -> <- down up, sum / 4).  8: the four diagonal paths
+                        are added (same step, no alpha1 scaling) and the sum is divided by 8 - an extension
+                        named in BASELINE.json configs[3] with NO counterpart in the reference; results of
+                        an 8-path chain are never parity figures */
 } stereo_post_params;
 /* the constants of smooth/nyu.lua:3-22 and the option defaults of post.lua:10-49 */
 int stereo_post_default_params(stereo_post_params *p);
@@ -162,7 +166,10 @@ int stereo_nyu_cross_agg(stereo_ctx *ctx, const float *l_img, const float *r_img
                          float *right_vol, int h, int w, int D, int iters, const stereo_post_params *p);
 
 /* smooth.nyu.sgm(l_img, r_img, vol, direction), smooth/nyu.lua:47-75 (adcensus.sgm2, 4 paths,
- * result = accumulated path costs / 4).  direction -1 for the left volume, +1 for the right. */
+ * result = accumulated path costs / 4; p->sgm_paths == 8: see stereo_post_params).  direction -1 for
+ * the left volume, +1 for the right.  D <= 512.  When D % 4 != 0 the kernels fetch the 16-byte
+ * aligned superset of every [x][d] run: up to 12 bytes before the first and after the last voxel of
+ * the (library-owned) device copy are read, never used; the host array is copied, not touched. */
 int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, float *vol, int h, int w,
                    int D, int direction, const stereo_post_params *p);
 

@@ -53,4 +53,14 @@ full_ms = timed(lambda: ctx.pairs_post_dev(m.net, d_left.data_ptr(), d_right.dat
 d_l4, d_r4 = d_left.unsqueeze(0).repeat(4, 1, 1, 1).contiguous(), d_right.unsqueeze(0).repeat(4, 1, 1, 1).contiguous()
 full4_ms = timed(lambda: ctx.pairs_post_dev(m.net, d_l4.data_ptr(), d_r4.data_ptr(), 4, H, W, D, prec, pp,
                                             d_np.data_ptr()), 3) / 4
-print(json.dumps({"D": D, "post_chain_ms": post_ms, "full_pipeline_ms": full_ms, "full_pipeline_ms_batch4": full4_ms}))
+# kernel classes of one chain, every kernel alone on the GPU (CUDA events around each launch group)
+ctx.profile_enable(True)
+ctx.post_dev(d_lv.data_ptr(), d_rv.data_ptr(), d_ld.data_ptr(), d_rd.data_ptr(), H, W, D, ptrs)
+torch.cuda.synchronize()
+classes = {k: round(v[0], 4) for k, v in ctx.profile_read().items() if v[1]}
+ctx.profile_enable(False)
+p8 = _lib.default_post_params()
+p8.sgm_paths = 8          # not the reference (4-path): BASELINE.json configs[3]'s 8-path chain, labelled apart
+post8_ms = timed(lambda: ctx.post_dev(d_lv.data_ptr(), d_rv.data_ptr(), d_ld.data_ptr(), d_rd.data_ptr(), H, W, D, ptrs,
+                                      params=p8), 3)
+print(json.dumps({"D": D, "post_chain_ms": post_ms, "post_chain_8path_ms": post8_ms, "kernel_class_ms": classes, "full_pipeline_ms": full_ms, "full_pipeline_ms_batch4": full4_ms}))

@@ -31,7 +31,7 @@ class PostParams(ctypes.Structure):
                 ("alpha1", ctypes.c_float), ("sgm_q1", ctypes.c_float), ("sgm_q2", ctypes.c_float),
                 ("occlusion", _i), ("subpixel", _i), ("median", _i), ("bilateral", _i),
                 ("blur_sigma", ctypes.c_double), ("blur_t", ctypes.c_float),
-                ("nyu_cost_agg_1", _i), ("sgm", _i), ("nyu_cost_agg_2", _i), ("post", _i), ("cbca_exact", _i)]
+                ("nyu_cost_agg_1", _i), ("sgm", _i), ("nyu_cost_agg_2", _i), ("post", _i), ("cbca_exact", _i), ("sgm_paths", _i)]
 
 
 _pp = ctypes.POINTER(PostParams)

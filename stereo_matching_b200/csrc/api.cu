@@ -85,18 +85,6 @@ static int check_dims(int n, int h, int w)
     return STEREO_OK;
 }
 
-// Which tensor-core convolution runs trunk layers 2-4.  STEREO_CONV_KERNEL=1: single CTA
-// (conv_tc.cu), 2: CTA pair, one output row at a time (conv_tc2.cu), 3 (default): CTA pair,
-// row-streaming N = 192 (conv_tc3.cu).  Read once.
-static int conv_kernel_mode()
-{
-    static const int mode = [] {
-        const char *e = getenv("STEREO_CONV_KERNEL");
-        return (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 3;
-    }();
-    return mode;
-}
-
 // Planar (hi, lo) feature output of the tensor-core trunk, consumed by the tensor-core correlation.
 struct PlanarOut {
     uint16_t *hi = nullptr, *lo = nullptr;   // already offset by the left margin
@@ -162,32 +150,23 @@ static int trunk_dev(stereo_ctx *ctx, int net, const float *in, int n, int h, in
             }
             return STEREO_OK;
         }
-        // layer 1 on CUDA cores (K = 27) writing chunk-planar bf16 (hi, lo); layers 2-4 on tcgen05
+        // base_model_ws_9: layers 2-4 on tcgen05 (conv_tc3.cu: CTA pair, every input row multiplied once, N = 192)
         const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
-        const int mode = conv_kernel_mode();
-        const int wp = mode >= 2 ? tc2_pitch(w - 2) : tc_pitch(w - 2);
+        const int wp = tc3_pitch(w - 2);
         const size_t plane_elems = (size_t)n * (h - 2) * 8 * wp * 8;
         DevBuf *act = lane ? ctx->act_b + 2 * (lane - 1) : ctx->act;
         STEREO_TRY(act[0].reserve(2 * plane_elems * 2));
         STEREO_TRY(act[1].reserve(2 * plane_elems * 2));
         uint16_t *a_hi = act[0].as<uint16_t>(), *a_lo = a_hi + plane_elems;
         uint16_t *b_hi = act[1].as<uint16_t>(), *b_lo = b_hi + plane_elems;
-        size_t wl = tc_weight_image_elems();
-        if (mode == 3) wl = tc3_weight_image_elems();
-        const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>() + (mode == 1 ? 0 : (mode == 2 ? 3 : 6) * tc_weight_image_elems());
-        auto launch_conv_tc = mode == 3 ? launch_conv_tc3 : (mode == 2 ? launch_conv_tc2 : stereo::launch_conv_tc);
-        if (u8_left) {
-            // STEREO_CONV1_KERNEL=1: CUDA-core layer 1 (conv1_direct.cu); default: tensor cores (conv1_tc.cu)
-            static const bool direct = [] { const char *e = getenv("STEREO_CONV1_KERNEL"); return e && e[0] == '1'; }();
-            if (direct)
-                STEREO_TRY(launch_conv1_direct(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink, ctx->conv1_host,
-                                               a_hi, planes == 2 ? a_lo : nullptr, wp, stats_off));
-            else
-                STEREO_TRY(launch_conv1_tc(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink,
-                                           ctx->wsplit[net].as<uint16_t>() + 6 * tc_weight_image_elems() +
-                                               3 * tc3_weight_image_elems(),
-                                           wts + nd.layer[0].b_off, a_hi, planes == 2 ? a_lo : nullptr, wp, stats_off));
-        }
+        const size_t wl = tc3_weight_image_elems();
+        const uint16_t *wimg = ctx->wsplit[net].as<uint16_t>();
+        auto launch_conv_tc = launch_conv_tc3;
+        if (u8_left)
+            // layer 1 straight from the uint8 images on the tensor cores (conv1_tc.cu)
+            STEREO_TRY(launch_conv1_tc(ctx, u8_left, u8_right, h - nd.shrink, w - nd.shrink,
+                                       ctx->wsplit[net].as<uint16_t>() + 3 * tc3_weight_image_elems(),
+                                       wts + nd.layer[0].b_off, a_hi, planes == 2 ? a_lo : nullptr, wp, stats_off));
         else
             STEREO_TRY(launch_conv_first_split(ctx, nd.layer[0], wts, in, n, h, w, a_hi, planes == 2 ? a_lo : nullptr, wp));
         STEREO_TRY(launch_conv_tc(ctx, a_hi, a_lo, n, h - 2, w - 2, wp, wimg, wts + nd.layer[1].b_off, b_hi, b_lo, wp,
@@ -558,23 +537,14 @@ int stereo_set_weights(stereo_ctx *ctx, int net, const float *packed, size_t n_f
     STEREO_CUDA_CHECK(cudaMemcpyAsync(ctx->weights[net].ptr, packed, sizeof(float) * n_floats,
                                       cudaMemcpyHostToDevice, ctx->stream));
     if (net == STEREO_NET_WIN9) {
-        memcpy(ctx->conv1_host.w, packed + nd.layer[0].w_off, sizeof(ctx->conv1_host.w));
-        memcpy(ctx->conv1_host.b, packed + nd.layer[0].b_off, sizeof(ctx->conv1_host.b));
-        // UMMA B-operand images (bf16 hi/lo) of the three 64->64 layers
-        const size_t wl = tc_weight_image_elems();
-        // (single-CTA layout first, then the per-CTA halves of the two CTA-pair kernels)
+        // UMMA B-operand images (bf16 hi/lo) of the three 64->64 layers (conv_tc3.cu), then layer 1's (conv1_tc.cu)
         const size_t wl3 = tc3_weight_image_elems();
-        STEREO_TRY(ctx->wsplit[net].reserve((6 * wl + 3 * wl3 + conv1_tc_weight_image_elems()) * 2));
+        STEREO_TRY(ctx->wsplit[net].reserve((3 * wl3 + conv1_tc_weight_image_elems()) * 2));
         STEREO_TRY(launch_conv1_weight_image(ctx, ctx->weights[net].as<float>() + nd.layer[0].w_off,
-                                             ctx->wsplit[net].as<uint16_t>() + 6 * wl + 3 * wl3));
-        for (int l = 1; l < 4; ++l) {
-            STEREO_TRY(launch_weight_images(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
-                                            ctx->wsplit[net].as<uint16_t>() + (l - 1) * wl));
-            STEREO_TRY(launch_weight_images2(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
-                                             ctx->wsplit[net].as<uint16_t>() + (l + 2) * wl));
+                                             ctx->wsplit[net].as<uint16_t>() + 3 * wl3));
+        for (int l = 1; l < 4; ++l)
             STEREO_TRY(launch_weight_images3(ctx, ctx->weights[net].as<float>() + nd.layer[l].w_off,
-                                             ctx->wsplit[net].as<uint16_t>() + 6 * wl + (l - 1) * wl3));
-        }
+                                             ctx->wsplit[net].as<uint16_t>() + (l - 1) * wl3));
     }
     if (net == STEREO_NET_WIN37) {
         // streaming units of conv_tcg.cu for layers 2-9, one after the other

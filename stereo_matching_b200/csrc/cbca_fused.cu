@@ -65,15 +65,38 @@ __device__ __forceinline__ void add_if(float &sum, int &cnt, float v, int c, uin
         : "+f"(sum), "+r"(cnt) : "f"(v), "r"(c), "r"(mask), "r"(bit));
 }
 
+// order-preserving integer key of a float (-0 counted as +0): a < b  <=>  key(a) < key(b) as unsigned
+__device__ __forceinline__ uint32_t order_key(float v)
+{
+    const uint32_t u = __float_as_uint(__fadd_rn(v, 0.f));
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+constexpr int kFMaxBandRows = 64;
+
 __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                          int pitch, const float *__restrict__ vol, float *__restrict__ out,
-                                                         int h, int w, int D, int direction, int rows_per_band)
+                                                         int h, int w, int D, int direction, int rows_per_band,
+                                                         double *__restrict__ moments, uint8_t *__restrict__ wta,
+                                                         int take_min)
 {
-    const int d = threadIdx.x;
-    if (d >= D) return;
+    // the lanes past D of the last warp shadow disparity D - 1 (same loads, nothing stored or counted) so that
+    // the warp-wide reductions below see whole warps
+    const bool active = (int)threadIdx.x < D;
+    const int d = active ? (int)threadIdx.x : D - 1;
     const int xb = blockIdx.x * kFB;
     const int y0 = blockIdx.y * rows_per_band, y1 = min(h, y0 + rows_per_band);
     const int shift = d * direction;
+
+    // per (row of the band, pixel): packed (value key, disparity) of the best disparity so far; one 64-bit
+    // atomic per warp and row keeps the warps independent (no barrier on the row loop)
+    __shared__ unsigned long long s_best[kFMaxBandRows][kFB];
+    __shared__ double s_red[2][8];
+    if (wta != nullptr) {
+        for (int i = threadIdx.x; i < kFMaxBandRows * kFB; i += blockDim.x) (&s_best[0][0])[i] = ~0ull;
+        __syncthreads();
+    }
+    double m_s = 0.0, m_ss = 0.0;
 
     int offs[kFN];                           // element offsets of the 12 columns inside a row (clamped: loads stay in the row)
 #pragma unroll
@@ -148,18 +171,73 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                         }
                     }
                     const float centre = hs[(u + 1 + kFR) % kFW][i];
-                    out[obase + offs[kFR + i]] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
+                    const float res = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
+                    if (active) out[obase + offs[kFR + i]] = res;
+                    if (moments != nullptr && active) {
+                        const double rd = (double)res;
+                        m_s += rd;
+                        m_ss = fma(rd, rd, m_ss);
+                    }
+                    if (wta != nullptr) {
+                        // best disparity of the warp's 32: one redux on the keys (arg max: inverted keys), the lowest
+                        // lane holding the winner is the lowest disparity
+                        uint32_t key = order_key(res);
+                        if (!take_min) key = ~key;
+                        if (!active) key = 0xffffffffu;
+                        const uint32_t mn = __reduce_min_sync(0xffffffffu, key);
+                        const unsigned winners = __ballot_sync(0xffffffffu, key == mn);
+                        if ((int)(threadIdx.x & 31) == __ffs(winners) - 1)
+                            atomicMin(&s_best[y - y0][i], ((unsigned long long)mn << 32) | (unsigned)d);
+                    }
                 }
             }
+        }
+    }
+    if (wta != nullptr) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < (y1 - y0) * kFB; i += blockDim.x) {
+            const int row = i / kFB, px = i - row * kFB;
+            if (xb + px < w) wta[(size_t)(y0 + row) * w + xb + px] = (uint8_t)(s_best[row][px] & 0xffu);
+        }
+    }
+    if (moments != nullptr) {
+        // block partials in a fixed order (deterministic): lanes by a shuffle tree, warps one after the other
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m_s += __shfl_down_sync(0xffffffffu, m_s, o);
+            m_ss += __shfl_down_sync(0xffffffffu, m_ss, o);
+        }
+        if ((threadIdx.x & 31) == 0) { s_red[0][threadIdx.x >> 5] = m_s; s_red[1][threadIdx.x >> 5] = m_ss; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0, b = 0.0;
+            for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += s_red[0][i]; b += s_red[1][i]; }
+            const size_t bid = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+            moments[2 * bid] = a;
+            moments[2 * bid + 1] = b;
         }
     }
 }
 
 }  // namespace
 
+static void cbca_fused_grid(int h, int w, int *bands, int *rows_per_band)
+{
+    *bands = std::max(1, (h + 62) / 63);
+    *rows_per_band = (h + *bands - 1) / *bands;
+}
+
+// number of (sum, sum of squares) partial pairs launch_cbca_fused writes into CbcaExtras::moments
+int cbca_fused_blocks(int h, int w)
+{
+    int bands, rows;
+    cbca_fused_grid(h, w, &bands, &rows);
+    return ((w + kFB - 1) / kFB) * bands;
+}
+
 // x0c / x1c: int16 arms [4][h][w] of the two views; rec: scratch for 2 * h * pitch records
 int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
-                      int D, int direction, int L1)
+                      int D, int direction, int L1, const CbcaExtras &ex)
 {
     STEREO_REQUIRE((size_t)h * w * D < (size_t)1 << 31, "volume too large for 32-bit indexing");
     STEREO_REQUIRE(D <= 256 && L1 - 1 <= kFR, "fused CBCA: D <= 256 and L1 <= %d, got D=%d L1=%d", kFR + 1, D, L1);
@@ -172,10 +250,13 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     cbca_pack_arms_kernel<<<pack_blocks, 256, 0, ctx->stream>>>(x0c, h, w, pitch, rec0);
     cbca_pack_arms_kernel<<<pack_blocks, 256, 0, ctx->stream>>>(x1c, h, w, pitch, rec1);
     const int nt = (D + 31) / 32 * 32;
-    const int bands = std::max(1, (h + 62) / 63);
-    const int rows_per_band = (h + bands - 1) / bands;
+    int bands, rows_per_band;
+    cbca_fused_grid(h, w, &bands, &rows_per_band);
+    static_assert(63 <= kFMaxBandRows, "band rows must fit the arg-min table");
     cbca_fused_kernel<<<dim3((w + kFB - 1) / kFB, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D,
-                                                                                direction, rows_per_band);
+                                                                                direction, rows_per_band, ex.moments,
+                                                                                ex.wta, ex.take_min);
+    if (ex.moment_blocks) *ex.moment_blocks = ((w + kFB - 1) / kFB) * bands;
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;

@@ -67,12 +67,6 @@ struct ImageStats {
     float lut[256];
 };
 
-// first-layer weights of base_model_ws_9 as they are passed to conv1_direct_kernel (by value)
-struct Conv1Weights {
-    float w[27 * 64];   // [ky][kx][cin][cout]
-    float b[64];
-};
-
 // CUDA-event timing of kernel classes (stereo_profile_*).
 struct Profiler {
     static constexpr int kMaxPairs = 8192;
@@ -103,7 +97,6 @@ struct stereo_ctx {
     stereo::DevBuf stage_in[2];  // H2D staging of the host-pointer entry points
     stereo::DevBuf stage_out[3];
     stereo::DevBuf stage_vol[2];
-    stereo::Conv1Weights conv1_host;   // host copy of the ws9 first layer (kernel-parameter weights)
     stereo::DevBuf featp;        // chunk-planar bf16 (hi, lo) features with zero margins
     int featp_geom[5] = {0, 0, 0, 0, 0};
     stereo::DevBuf featp_b[3];   // lanes 1..3
@@ -150,9 +143,7 @@ struct ProfScope {
 int launch_normalize_pad(stereo_ctx *ctx, const uint8_t *rgb, int n, int h, int w, int patch, float *out);
 int launch_pad_with_stats(stereo_ctx *ctx, const uint8_t *rgb, int h, int w, int patch, int stats_index, float *out);
 int launch_pair_stats(stereo_ctx *ctx, const uint8_t *left, const uint8_t *right, int n, int h, int w);
-// conv1_direct.cu
-int launch_conv1_direct(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w,
-                        const Conv1Weights &cw, void *out_hi, void *out_lo, int wp_out, int stats_off);
+// conv1_tc.cu
 size_t conv1_tc_weight_image_elems();
 int launch_conv1_weight_image(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv1_tc(stereo_ctx *ctx, const uint8_t *img0, const uint8_t *img1, int h, int w, const void *wimg,
@@ -162,10 +153,7 @@ int launch_conv_ffma(stereo_ctx *ctx, const LayerDesc &L, const float *weights, 
                      int n, int h_in, int w_in, float *out);
 int launch_conv_first_split(stereo_ctx *ctx, const LayerDesc &L, const float *weights, const float *in, int n,
                             int h_in, int w_in, void *out_hi, void *out_lo, int wp_out);
-// conv_tc.cu
-size_t tc_weight_image_elems();
-int tc_pitch(int w);
-int tc2_pitch(int w);
+// conv_tcg.cu
 size_t tcg_weight_image_elems(int ks, int cin, int cout);
 int tcg_pitch(int w);
 int launch_weight_image_g(stereo_ctx *ctx, const float *layer_w, int ks, int cin, int cout, void *img);
@@ -179,25 +167,15 @@ int launch_conv_tcr(stereo_ctx *ctx, int ks, int cin, int cout, const void *in_h
                     int w_in, int wp_in, const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out,
                     float *out_f32, int relu, int planes);
 int corr_sweep_margin();
-int corr_sweep2_row_cols(int w);
-int launch_corr_sweep2(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
-                       int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                       int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
                       uint8_t *left_disp, uint8_t *right_disp);
+int tc3_pitch(int w);
 size_t tc3_weight_image_elems();
 int launch_weight_images3(stereo_ctx *ctx, const float *layer_w, void *img);
 int launch_conv_tc3(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
                     const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
                     int relu, int planes);
-int launch_weight_images2(stereo_ctx *ctx, const float *layer_w, void *img);
-int launch_conv_tc2(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
-                    const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
-                    int relu, int planes);
-int launch_weight_images(stereo_ctx *ctx, const float *layer_w, void *img);
-int launch_conv_tc(stereo_ctx *ctx, const void *in_hi, const void *in_lo, int n, int h_in, int w_in, int wp_in,
-                   const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out, float *out_f32,
-                   int relu, int planes);
 // corr_tc.cu
 int corr_tc_max_disp();
 void corr_tc_geometry(int w, int D, int *wf, int *ml);
@@ -222,17 +200,39 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
 // cbca_fused.cu
+// What the fused CBCA kernel computes besides the aggregated volume (all optional):
+//   moments  per-block partial sums (double: sum, sum of squares) of the OUTPUT volume, combined by
+//            launch_volume_std_final into the unbiased std of post.lua:146 - saves one pass over the volume
+//   wta      uint8 [h][w]: arg max (take_min = 0) / arg min (1) over D of the output (stage images, post.lua:125,178)
+struct CbcaExtras {
+    double *moments = nullptr;
+    int *moment_blocks = nullptr;      // out: number of partial pairs written
+    uint8_t *wta = nullptr;
+    int take_min = 0;
+};
 int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
-                      int D, int direction, int L1);
+                      int D, int direction, int L1, const CbcaExtras &ex = CbcaExtras());
+int cbca_fused_blocks(int h, int w);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
+int launch_volume_std_final(stereo_ctx *ctx, const double *partial, int nblocks, size_t n, float *result);
 int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
-// sgm_ring.cu
-bool sgm_ring_usable(const float *cvol, const float *out, const float *scratch, int D);
+// What the SGM kernels fuse in besides the four paths (all optional):
+//   stdp         costs are read as -(cvol / *stdp)  (post.lua:146,152) instead of pre-scaled by a pass of their own
+//   final_scale  factor of the last path's sum: 0.25 (nyu.lua:61,64 `/ 4`), 0.125 after eight paths
+//   wta          uint8 [h][w]: arg min over D of the final result (the nyu_sgm stage image, post.lua:159); D <= 256
+//   paths        4 (the reference) or 8 (adds the diagonals; no counterpart in the reference)
+struct SgmExtras {
+    const float *stdp = nullptr;
+    float final_scale = 0.25f;
+    uint8_t *wta = nullptr;
+    int paths = 4;
+};
+// sgm_ring.cu: the four paths of the original (-> <- down up); with ex.paths == 8 the sum is left unscaled
 int launch_sgm_ring(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
-                    int h, int w, int D, const SgmParams &p, int direction);
+                    int h, int w, int D, const SgmParams &p, int direction, const SgmExtras &ex);
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
-               int h, int w, int D, const SgmParams &p, int direction);
+               int h, int w, int D, const SgmParams &p, int direction, const SgmExtras &ex = SgmExtras());
 int launch_outlier(stereo_ctx *ctx, const float *d0, const float *d1, int h, int w, int disp_max, float *outlier);
 int launch_interpolate(stereo_ctx *ctx, const float *d0, const float *outlier, int h, int w, float *tmp, float *out);
 int launch_subpixel(stereo_ctx *ctx, const float *d0, const float *vol, int h, int w, int disp_max, float *out);

@@ -298,6 +298,9 @@ __global__ void weight_image3_kernel(const float *__restrict__ w, __nv_bfloat16 
 
 }  // namespace tc3
 
+// row pitch of the chunk-planar activations: a CTA pair covers 256 pixels
+int tc3_pitch(int w) { return (w + 255) / 256 * 256 + 8; }
+
 size_t tc3_weight_image_elems() { return (size_t)2 * tc3::kWBytes / 2; }   // per layer, bf16 elements
 
 int launch_weight_images3(stereo_ctx *ctx, const float *layer_w, void *img)

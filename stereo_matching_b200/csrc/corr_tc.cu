@@ -295,7 +295,10 @@ void corr_tc_geometry(int w, int D, int *wf, int *ml)
     *ml = need > corr_sweep_margin() ? need : corr_sweep_margin();
     const int nb = (w + tcc::kTileM - 1) / tcc::kTileM;
     const int cols = nb * tcc::kTileM + (tcc::kWinN - tcc::kTileM);
-    *wf = *ml + (cols > corr_sweep2_row_cols(w) ? cols : corr_sweep2_row_cols(w));
+    // rows are laid out for whole PAIRS of 128-pixel blocks plus two more blocks (the trunk's CTA pairs store
+    // 256-pixel runs, conv_tc3.cu)
+    const int pair_cols = tcc::kTileM * (2 * ((nb + 1) / 2) + 2);
+    *wf = *ml + (cols > pair_cols ? cols : pair_cols);
 }
 
 int launch_nhwc_to_planar(stereo_ctx *ctx, const float *in, int n, int h, int w, int wf, int ml, void *hi, void *lo)
@@ -318,15 +321,12 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
                    "feature margins too small");
     bool vol = left_vol != nullptr, wta = left_disp != nullptr;
     STEREO_REQUIRE(vol || wta, "nothing to compute");
-    // fused WTA only: the row-sweep kernel (STEREO_CORR_KERNEL=1 keeps the per-tile kernel below)
-    // (STEREO_CORR_KERNEL=3: CTA-pair row sweep, corr_sweep2.cu - measured slower so far, see DESIGN.md;
-    //  default 2: single-CTA row sweep, corr_sweep.cu)
-    static const int mode = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return (e && e[0] >= '1' && e[0] <= '3') ? e[0] - '0' : 2; }();
-    if (mode == 2 && ml >= corr_sweep_margin())
+    // default: the row-sweep kernel (corr_sweep.cu); STEREO_CORR_KERNEL=1 keeps the per-tile kernel below as the
+    // cross-check, which also serves rows whose margins are too small for the sweep
+    static const bool per_tile = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return e && e[0] == '1'; }();
+    if (!per_tile && ml >= corr_sweep_margin())
         return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_vol, right_vol, left_disp,
                                  right_disp);
-    if (!vol && mode == 3 && ml >= corr_sweep_margin() && wf >= ml + corr_sweep2_row_cols(w))
-        return launch_corr_sweep2(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
     tcc::Params p;
     p.l_hi = static_cast<const __nv_bfloat16 *>(l_hi);
     p.l_lo = static_cast<const __nv_bfloat16 *>(l_lo);

@@ -14,6 +14,7 @@
 // original's arithmetic (mean2d) uses an explicit fmaf, everything else is
 // compiled without contraction.
 #include "common.cuh"
+#include "sgm_step.cuh"
 
 namespace stereo {
 
@@ -461,6 +462,16 @@ int launch_volume_std_with(stereo_ctx *ctx, const float *vol, size_t n, double *
     return STEREO_OK;
 }
 
+// the final step alone, over partial sums another kernel produced (the fused CBCA kernel's epilogue)
+int launch_volume_std_final(stereo_ctx *ctx, const double *partial, int nblocks, size_t n, float *result)
+{
+    ProfScope prof(ctx, STEREO_K_VOLSTD);
+    volume_std_final_kernel<<<1, 32, 0, ctx->stream>>>(partial, nblocks, (double)n, result);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 // `slot` (0 or 1) selects one of two partial-sum areas so that two streams can reduce at once
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot)
 {
@@ -547,53 +558,44 @@ int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, 
 }
 
 // ------------------------------------------------------------------------------------------
-// P3  adcensus.sgm2 (nyu.lua:59-60): 4-path semi-global matching with intensity-adaptive
-//     penalties.  The original launches one kernel per scanline STEP (2W+2H launches per
-//     volume) with one thread per disparity.  Here one WARP owns a whole scanline and walks
-//     it: each lane keeps KPL consecutive disparities of the previous step's path costs in
-//     registers, the neighbours d-1 / d+1 across lanes come from two shuffles, the minimum
-//     over D from a shuffle reduction - no shared memory and no block barrier on the
-//     serial chain - and the costs (and running sums) of the next PF steps are already in
-//     flight as 16-byte loads when a step is computed.
-//
-//     Three launches per volume: the two horizontal paths run concurrently in one grid and
-//     write their path costs to two buffers (a = left->right, b = right->left); the downward
-//     pass writes (a + b) + Lr into a; the upward pass writes ((a + Lr) / 4) - the order of
-//     additions of the original's `out +=`, and the division of nyu.lua:61,64.
-//     The input is the cost volume C = -(raw / std) (post.lua:146,152), scaled beforehand.
-//     Arithmetic per voxel is that of the original, operation for operation.
+// P3  adcensus.sgm2 (nyu.lua:59-60): semi-global matching with intensity-adaptive penalties.
+//     The four paths of the original (-> <- down up) run in sgm_ring.cu.  This file holds the
+//     DIAGONAL paths of the 8-path variant, which has no counterpart in the reference (its chain
+//     is 4-path, nyu.lua:59-64; BASELINE.json configs[3] names an 8-path chain): one WARP owns a
+//     diagonal line and walks it, each lane keeps KPL consecutive disparities of the previous
+//     step's path costs in registers, d-1 / d+1 across lanes are two shuffles, the minimum over D
+//     a shuffle reduction, and the costs and running sums of the next PF steps are in flight
+//     while a step is computed.  Every pass adds its path costs to the running sum in place
+//     (same thread reads and writes a voxel); the last one scales by 1/8 and can write the
+//     arg min map.  Step arithmetic: sgm_step() of sgm_step.cuh, the original's, with no alpha1
+//     scaling (the original applies it on the two vertical paths only).
+//     Path order of the sum: -> <- down up, then 4: down-right, 5: down-left, 6: up-right, 7: up-left.
 // ------------------------------------------------------------------------------------------
-template <int SD, int KPL, int PF, bool VEC, int NACC>
-__device__ __forceinline__ void sgm_scan(const float *__restrict__ x0, const float *__restrict__ x1,
-                                         const float *__restrict__ cvol, const float *acc_a, const float *acc_b,
-                                         float *outp, int h, int w, int D, const SgmParams &p, int direction,
-                                         int line, int last)
+template <int SD, int KPL, int PF, bool VEC>
+__global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
+                                                      const float *__restrict__ cvol, float *acc, int h, int w, int D,
+                                                      SgmParams p, int direction, const float *__restrict__ stdp,
+                                                      float final_scale, int last, uint8_t *wta)
 {
-    constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
-    constexpr int dy = SD == 2 ? 1 : (SD == 3 ? -1 : 0);
+    static_assert(SD >= 4 && SD < 8, "diagonal paths only");
+    constexpr int dx = (SD == 4 || SD == 6) ? 1 : -1;
+    constexpr int dy = SD < 6 ? 1 : -1;
     const int lane = threadIdx.x & 31;
-    const int steps = dy == 0 ? w : h;
-    int x = dy == 0 ? (SD == 0 ? 0 : w - 1) : line;
-    int y = dy == 0 ? line : (SD == 2 ? 0 : h - 1);
+    // line -> first pixel: the first row in path order, then the rest of the first column
+    const int line = blockIdx.x;
+    const int y_first = dy > 0 ? 0 : h - 1, x_first = dx > 0 ? 0 : w - 1;
+    int x = line < w ? line : x_first;
+    int y = line < w ? y_first : y_first + dy * (line - w + 1);
+    const int steps = min(dx > 0 ? w - x : x + 1, dy > 0 ? h - y : y + 1);
     const int d0 = lane * KPL;
-    const float kBig = 3.0e38f;          // stands for "no such disparity": never the minimum, kBig + P == kBig
-    const float tau = p.tau_so;
-
-    // the three penalty cases of the original; "P1 / alpha1" applies to the d-1 term on the
-    // downward path and to the d+1 term on the upward one
-    const float P1a = p.pi1, P2a = p.pi2;
-    const float P1b = __fdiv_rn(p.pi1, __fmul_rn(p.q1, p.q2)), P2b = __fdiv_rn(p.pi2, __fmul_rn(p.q1, p.q2));
-    const float P1c = __fdiv_rn(p.pi1, p.q1), P2c = __fdiv_rn(p.pi2, p.q1);
-    const float P1a_m = SD == 2 ? __fdiv_rn(P1a, p.alpha1) : P1a, P1a_p = SD == 3 ? __fdiv_rn(P1a, p.alpha1) : P1a;
-    const float P1b_m = SD == 2 ? __fdiv_rn(P1b, p.alpha1) : P1b, P1b_p = SD == 3 ? __fdiv_rn(P1b, p.alpha1) : P1b;
-    const float P1c_m = SD == 2 ? __fdiv_rn(P1c, p.alpha1) : P1c, P1c_p = SD == 3 ? __fdiv_rn(P1c, p.alpha1) : P1c;
+    const bool scale_on_load = stdp != nullptr;
+    const float sd = scale_on_load ? __ldg(stdp) : 1.f;
+    const SgmPenalties<SD> pen(p);
 
     const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;     // floats between consecutive steps
     const size_t base = ((size_t)y * w + x) * D + d0;
     const float *cptr = cvol + base;
-    const float *aptr = NACC >= 1 ? acc_a + base : nullptr;
-    const float *bptr = NACC >= 2 ? acc_b + base : nullptr;
-    float *optr = outp + base;
+    float *aptr = acc + base;
 
     bool valid[KPL];
 #pragma unroll
@@ -604,28 +606,27 @@ __device__ __forceinline__ void sgm_scan(const float *__restrict__ x0, const flo
 #pragma unroll
             for (int j = 0; j < KPL / 4; ++j) {
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (valid[4 * j]) v = __ldg(reinterpret_cast<const float4 *>(src) + j);
+                if (valid[4 * j]) v = *(reinterpret_cast<const float4 *>(src) + j);
                 dst[4 * j] = v.x; dst[4 * j + 1] = v.y; dst[4 * j + 2] = v.z; dst[4 * j + 3] = v.w;
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < KPL; ++k) dst[k] = valid[k] ? __ldg(src + k) : 0.f;
+            for (int k = 0; k < KPL; ++k) dst[k] = valid[k] ? src[k] : 0.f;
         }
     };
 
-    float cbuf[PF][KPL], abuf[NACC >= 1 ? PF : 1][KPL], bbuf[NACC >= 2 ? PF : 1][KPL];
+    float cbuf[PF][KPL], abuf[PF][KPL];
 #pragma unroll
     for (int i = 0; i < PF; ++i) {
         if (i < steps) {
             load_row(cptr + i * vstride, cbuf[i]);
-            if (NACC >= 1) load_row(aptr + i * vstride, abuf[i]);
-            if (NACC >= 2) load_row(bptr + i * vstride, bbuf[i]);
+            load_row(aptr + i * vstride, abuf[i]);
         }
     }
 
     float prev[KPL], i1p[KPL];
 #pragma unroll
-    for (int k = 0; k < KPL; ++k) { prev[k] = kBig; i1p[k] = 0.f; }
+    for (int k = 0; k < KPL; ++k) { prev[k] = kSgmBig; i1p[k] = 0.f; }
     const bool has_below = lane > 0, has_above = d0 + KPL < D;
 
     for (int g = 0; g < steps; g += PF) {
@@ -633,7 +634,7 @@ __device__ __forceinline__ void sgm_scan(const float *__restrict__ x0, const flo
         for (int i = 0; i < PF; ++i) {
             const int step = g + i;
             if (step >= steps) break;
-            // guide values at the matched pixels of this step (L1-resident rows)
+            // guide values at the matched pixels of this step
             float i1c[KPL];
             const float *g1 = x1 + (size_t)y * w;
             const int xx0 = x + d0 * direction;
@@ -642,132 +643,103 @@ __device__ __forceinline__ void sgm_scan(const float *__restrict__ x0, const flo
                 const int xx = xx0 + k * direction;
                 i1c[k] = (unsigned)xx < (unsigned)w ? __ldg(g1 + xx) : 0.f;
             }
+            float c[KPL];
+#pragma unroll
+            for (int k = 0; k < KPL; ++k) {
+                c[k] = cbuf[i][k];
+                if (scale_on_load) c[k] = __fmul_rn(__fdiv_rn(c[k], sd), -1.f);
+            }
             float val[KPL];
             if (step == 0) {
 #pragma unroll
-                for (int k = 0; k < KPL; ++k) val[k] = valid[k] ? cbuf[i][k] : kBig;
+                for (int k = 0; k < KPL; ++k) val[k] = valid[k] ? c[k] : kSgmBig;
             } else {
-                float pmin = prev[0];
-#pragma unroll
-                for (int k = 1; k < KPL; ++k) pmin = fminf(pmin, prev[k]);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) pmin = fminf(pmin, __shfl_xor_sync(0xffffffffu, pmin, o));
-                float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
-                float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
-                below = has_below ? below : kBig;
-                above = has_above ? above : kBig;
                 const float D1 = fabsf(__ldg(x0 + (size_t)y * w + x) - __ldg(x0 + (size_t)(y - dy) * w + (x - dx)));
-                // D1 is the same for the whole scanline step: pick the candidate penalty set once
-                const bool d1_lt = D1 < tau, d1_gt = D1 > tau;
-                const float P2x = d1_lt ? P2a : P2b, P1mx = d1_lt ? P1a_m : P1b_m, P1px = d1_lt ? P1a_p : P1b_p;
-                const float pmin_p2x = __fadd_rn(pmin, P2x), pmin_p2c = __fadd_rn(pmin, P2c);
-#pragma unroll
-                for (int k = 0; k < KPL; ++k) {
-                    const int xx = xx0 + k * direction;
-                    // the matched pixel of the previous step is (xx - dx, y - dy); its x1 value is i1p[k]
-                    const bool inside = (unsigned)xx < (unsigned)w && (dx == 0 || (unsigned)(xx - dx) < (unsigned)w);
-                    const float D2 = inside ? fabsf(i1c[k] - i1p[k]) : 10.f;
-                    const bool both = d1_lt ? (D2 < tau) : (d1_gt && D2 > tau);
-                    const float P1m = both ? P1mx : P1c_m, P1p = both ? P1px : P1c_p;
-                    float c = fminf(prev[k], both ? pmin_p2x : pmin_p2c);
-                    const float pm = k > 0 ? prev[k > 0 ? k - 1 : 0] : below;
-                    const float pp = k < KPL - 1 ? prev[k < KPL - 1 ? k + 1 : 0] : above;
-                    c = fminf(c, __fadd_rn(pm, P1m));
-                    c = fminf(c, __fadd_rn(pp, P1p));
-                    const float v = __fadd_rn(__fadd_rn(cbuf[i][k], c), -pmin);
-                    val[k] = valid[k] ? v : kBig;
-                }
+                sgm_step<SD, KPL>(pen, D1, c, prev, i1c, i1p, valid, xx0, direction, w, has_below, has_above, val);
             }
-            // accumulate into the output volume
+            // accumulate into the running sum
             float res[KPL];
+            float best = kSgmBig;
+            int best_k = 0;
 #pragma unroll
             for (int k = 0; k < KPL; ++k) {
-                float acc = val[k];
-                if (NACC == 1) acc = __fadd_rn(abuf[i][k], val[k]);
-                if (NACC == 2) acc = __fadd_rn(__fadd_rn(abuf[i][k], bbuf[i][k]), val[k]);
-                res[k] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
+                const float sum = __fadd_rn(abuf[i][k], val[k]);
+                res[k] = last ? __fmul_rn(sum, final_scale) : sum;
+                if (valid[k] && res[k] < best) { best = res[k]; best_k = k; }
             }
             if (VEC) {
 #pragma unroll
                 for (int j = 0; j < KPL / 4; ++j)
                     if (valid[4 * j])
-                        reinterpret_cast<float4 *>(optr)[j] = make_float4(res[4 * j], res[4 * j + 1], res[4 * j + 2], res[4 * j + 3]);
+                        reinterpret_cast<float4 *>(aptr)[j] = make_float4(res[4 * j], res[4 * j + 1], res[4 * j + 2], res[4 * j + 3]);
             } else {
 #pragma unroll
                 for (int k = 0; k < KPL; ++k)
-                    if (valid[k]) optr[k] = res[k];
+                    if (valid[k]) aptr[k] = res[k];
+            }
+            if (last && wta != nullptr) {
+                int key = __float_as_int(__fadd_rn(best, 0.f));
+                key ^= (key >> 31) & 0x7fffffff;
+                const int mn = __reduce_min_sync(0xffffffffu, key);
+                const unsigned winners = __ballot_sync(0xffffffffu, key == mn);
+                if (lane == __ffs(winners) - 1) wta[(size_t)y * w + x] = (uint8_t)(d0 + best_k);
             }
 #pragma unroll
             for (int k = 0; k < KPL; ++k) { prev[k] = val[k]; i1p[k] = i1c[k]; }
             // refill this ring slot with the step PF ahead
             if (step + PF < steps) {
                 load_row(cptr + (ptrdiff_t)PF * vstride, cbuf[i]);
-                if (NACC >= 1) load_row(aptr + (ptrdiff_t)PF * vstride, abuf[i]);
-                if (NACC >= 2) load_row(bptr + (ptrdiff_t)PF * vstride, bbuf[i]);
+                load_row(aptr + (ptrdiff_t)PF * vstride, abuf[i]);
             }
             cptr += vstride;
-            if (NACC >= 1) aptr += vstride;
-            if (NACC >= 2) bptr += vstride;
-            optr += vstride;
+            aptr += vstride;
             x += dx;
             y += dy;
         }
     }
 }
 
-// both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
 template <int KPL, int PF, bool VEC>
-__global__ __launch_bounds__(32) void sgm_h_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
-                                                   const float *__restrict__ cvol, float *out_a, float *out_b, int h,
-                                                   int w, int D, SgmParams p, int direction)
+static int launch_sgm_diagonals(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *acc, int h,
+                                int w, int D, const SgmParams &p, int direction, const SgmExtras &ex)
 {
-    if (blockIdx.y == 0) sgm_scan<0, KPL, PF, VEC, 0>(x0, x1, cvol, nullptr, nullptr, out_a, h, w, D, p, direction, blockIdx.x, 0);
-    else sgm_scan<1, KPL, PF, VEC, 0>(x0, x1, cvol, nullptr, nullptr, out_b, h, w, D, p, direction, blockIdx.x, 0);
-}
-
-template <int SD, int KPL, int PF, bool VEC>
-__global__ __launch_bounds__(32) void sgm_v_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
-                                                   const float *__restrict__ cvol, float *out_a, const float *out_b,
-                                                   int h, int w, int D, SgmParams p, int direction)
-{
-    if (SD == 2) sgm_scan<2, KPL, PF, VEC, 2>(x0, x1, cvol, out_a, out_b, out_a, h, w, D, p, direction, blockIdx.x, 0);
-    else sgm_scan<3, KPL, PF, VEC, 1>(x0, x1, cvol, out_a, nullptr, out_a, h, w, D, p, direction, blockIdx.x, 1);
-}
-
-template <int KPL, int PF, bool VEC>
-static int launch_sgm_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a,
-                        float *out_b, int h, int w, int D, const SgmParams &p, int direction)
-{
-    sgm_h_kernel<KPL, PF, VEC><<<dim3(h, 2), 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
-    sgm_v_kernel<2, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
-    sgm_v_kernel<3, KPL, PF, VEC><<<w, 32, 0, ctx->stream>>>(x0, x1, cvol, out_a, out_b, h, w, D, p, direction);
-    ctx->launches += 3;
+    const int lines = w + h - 1;
+    sgm_diag_kernel<4, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
+    sgm_diag_kernel<5, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
+    sgm_diag_kernel<6, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
+    sgm_diag_kernel<7, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp,
+                                                                    ex.final_scale, 1, ex.wta);
+    ctx->launches += 4;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
 }
 
-// cvol: pre-scaled costs; out: result; scratch: one more volume (the right->left path costs)
+// cvol: costs (pre-scaled, or raw with ex.stdp set); out: result; scratch: one more volume (the right->left path costs)
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
-               int h, int w, int D, const SgmParams &p, int direction)
+               int h, int w, int D, const SgmParams &p, int direction, const SgmExtras &ex)
 {
     if (D > 512) {
         set_error("SGM supports disp_range <= 512 (16 disparities per lane), got %d", D);
         return STEREO_E_LIMIT;
     }
-    // 16-byte loads need every [x][d] row to start 16-byte aligned
-    const bool vec = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
-                     ((uintptr_t)scratch % 16 == 0);
+    STEREO_REQUIRE(ex.paths == 4 || ex.paths == 8, "sgm_paths must be 4 (the reference) or 8, got %d", ex.paths);
+    STEREO_REQUIRE(ex.wta == nullptr || D <= 256, "the arg min map is bytes: D=%d > 256", D);
     ProfScope prof(ctx, STEREO_K_SGM);
-    // default: the shared-memory ring kernels (sgm_ring.cu); STEREO_SGM_KERNEL=1 keeps the register-prefetch ones
-    static const bool ring = [] { const char *e = getenv("STEREO_SGM_KERNEL"); return !(e && atoi(e) == 1); }();
-    if (ring && sgm_ring_usable(cvol, out, scratch, D))
-        return launch_sgm_ring(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
-    if (D <= 128) return vec ? launch_sgm_t<4, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
-                             : launch_sgm_t<4, 4, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
-    if (D <= 256) return vec ? launch_sgm_t<8, 4, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
-                             : launch_sgm_t<8, 4, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
-    return vec ? launch_sgm_t<16, 2, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction)
-               : launch_sgm_t<16, 2, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction);
+    if (ex.paths == 4) return launch_sgm_ring(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction, ex);
+    // eight paths: the four of the original leave their unscaled sum in `out`, the diagonals add to it in place
+    SgmExtras four = ex;
+    four.final_scale = 1.f;
+    four.wta = nullptr;
+    STEREO_TRY(launch_sgm_ring(ctx, x0, x1, cvol, out, scratch, h, w, D, p, direction, four));
+    SgmExtras diag = ex;
+    diag.final_scale = 0.125f;                       // x / 8 == x * 0.125 exactly
+    const bool vec = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0);
+    if (D <= 128) return vec ? launch_sgm_diagonals<4, 4, true>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag)
+                             : launch_sgm_diagonals<4, 4, false>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag);
+    if (D <= 256) return vec ? launch_sgm_diagonals<8, 4, true>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag)
+                             : launch_sgm_diagonals<8, 4, false>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag);
+    return vec ? launch_sgm_diagonals<16, 2, true>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag)
+               : launch_sgm_diagonals<16, 2, false>(ctx, x0, x1, cvol, out, h, w, D, p, direction, diag);
 }
 
 // ------------------------------------------------------------------------------------------

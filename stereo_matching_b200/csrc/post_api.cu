@@ -12,6 +12,7 @@ static int check_params(const stereo_post_params *p, int h, int w, int D)
     STEREO_REQUIRE(p != nullptr, "null post parameters");
     STEREO_REQUIRE(h > 0 && w > 0 && D > 0, "h, w, D must be positive (got %d, %d, %d)", h, w, D);
     STEREO_REQUIRE(p->L1 >= 1 && p->sgm_i >= 1, "L1 and sgm_i must be >= 1");
+    STEREO_REQUIRE(p->sgm_paths == 4 || p->sgm_paths == 8, "sgm_paths must be 4 (the reference) or 8, got %d", p->sgm_paths);
     STEREO_REQUIRE(w < 32768 && h < 32768, "image dimensions must fit the int16 arm encoding");
     return STEREO_OK;
 }
@@ -75,13 +76,19 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 // 12 bytes past the last voxel, which this slack keeps inside the allocation whatever its size.
 static constexpr size_t kVolSlack = 256;
 
+// `ex` (moments of the output, arg max / arg min map) is honoured by the fused kernel only; *ex_done tells the
+// caller whether it was, so that it can fall back to the stand-alone kernels
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
-                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
+                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0,
+                    const CbcaExtras *ex = nullptr, bool *ex_done = nullptr)
 {
+    if (ex_done) *ex_done = false;
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
-    // default: one fused pass (cbca_fused.cu); STEREO_CBCA_KERNEL=1 keeps the two-pass separable kernels
-    static const bool fused = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return !(e && atoi(e) == 1); }();
-    if (fused && D <= 256 && p->L1 <= 5) return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1);
+    if (D <= 256 && p->L1 <= 5) {
+        // one fused pass (cbca_fused.cu)
+        if (ex_done) *ex_done = ex != nullptr;
+        return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1, ex ? *ex : CbcaExtras());
+    }
     STEREO_TRY(ctx->post_cnt[slot].reserve((size_t)h * w * D));
     return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt[slot].as<uint8_t>(), out, h, w, D, direction,
                                  p->L1);
@@ -145,9 +152,16 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
     // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream
     // section would serialise it
-    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
-    for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
-    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * 1184));
+    const bool fused_cbca = !p->cbca_exact && D <= 256 && p->L1 <= 5;
+    // three working volumes per side (result, SGM scratch, spare); the two-pass CBCA needs a fourth and its lengths
+    const int vols_per_side = fused_cbca ? 3 : 4;
+    for (int side = 0; side < 2; ++side)
+        for (int i = 0; i < vols_per_side; ++i) STEREO_TRY(ctx->post_vol[4 * side + i].reserve(sizeof(float) * nvox + kVolSlack));
+    if (!fused_cbca && !p->cbca_exact)
+        for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
+    const int moment_blocks = cbca_fused_blocks(h, w);
+    const size_t moment_doubles = std::max<size_t>(2 * 1184, 2 * (size_t)moment_blocks);
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * moment_doubles));
     if (!ctx->aux_stream) STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
     if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     if (!ctx->ev_join) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
@@ -158,56 +172,80 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     const SgmParams sp = sgm_params(p);
 
     // The left and the right volume are independent until smooth.nyu.post: the left chain is
-    // issued on the context's stream, the right chain on a second stream (the scanline kernels
-    // of SGM leave most of the machine idle on their own).  Four working volumes per side: every
-    // stage reads `cur` and writes a free buffer; the buffer it read goes back to the free list
-    // unless it is the caller's (read-only) input.
+    // issued on the context's stream, the right chain on a second stream.  Every stage reads `cur` and
+    // writes a free buffer; the buffer it read goes back to the free list unless it is the caller's
+    // (read-only) input.  Whatever a later stage needs from a volume besides the volume itself - its
+    // std (post.lua:146), the stage images (post.lua:125,159,178: one arg max / arg min over D each) - is
+    // computed by the kernel that WRITES the volume, and `-(x / std)` (post.lua:146,152) by the SGM
+    // kernels as they load it: per side the chain moves 2 + 11 + 2 volumes through HBM instead of 21.
     STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, ctx->stream));
     STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
     const float *left_final = nullptr;
     for (int side = 0; side < 2; ++side) {
         StreamSwap swap(ctx, side == 0 ? ctx->stream : ctx->aux_stream);
         std::vector<float *> pool;
-        for (int i = 0; i < 4; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
+        for (int i = 0; i < vols_per_side; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
         const int direction = side == 0 ? -1 : 1;
         const float *input = side == 0 ? left_cost : right_cost;
         const float *cur = input;
+        uint8_t *final_map = side == 0 ? m.u8a : m.u8b;
+        bool have_final_map = false;                 // final_map holds the arg min of `cur`
         auto advance = [&](float *dst) {
             if (cur != input) pool.push_back(const_cast<float *>(cur));
             cur = dst;
+            have_final_map = false;
         };
         auto take = [&]() {
             float *dst = pool.back();
             pool.pop_back();
             return dst;
         };
+        auto spare = [&]() -> float * { return fused_cbca || pool.empty() ? nullptr : pool.back(); };
+        double *moments = ctx->scratch.as<double>() + (side ? moment_doubles : 0);
+        float *stdp = m.stdp + side * 2;
+        bool have_std = false;
         // nyu_cost_agg_1 (post.lua:116-133); both volumes are called with (x0c, x1c), nyu.lua:37,39
         for (int i = 0; i < p->nyu_cost_agg_1; ++i) {
+            const bool last_iter = i == p->nyu_cost_agg_1 - 1;
             float *dst = take();
-            float *tmp = take();
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
-            pool.push_back(tmp);
-            advance(dst);
-        }
-        if (p->nyu_cost_agg_1 > 0 && stages[side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
-        // post.lua:146-147: lu = lu / lu:std()  (fused into the SGM cost load when SGM runs)
-        float *stdp = m.stdp + side * 2;
-        STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
-        if (p->sgm == 1) {
-            // post.lua:152-155 + nyu.lua:47-75
-            {   // post.lua:146,152: lu = (lu / lu:std()) * -1
-                float *dst = take();
-                STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 1, dst));
-                advance(dst);
+            CbcaExtras ex;
+            bool ex_done = false;
+            if (last_iter) {
+                ex.moments = moments;                                   // post.lua:146 lu:std() of this output
+                ex.wta = stages[side];                                  // post.lua:125 lu:max(2)
+                ex.take_min = 0;
             }
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
+                                last_iter ? &ex : nullptr, &ex_done));
+            advance(dst);
+            if (last_iter && ex_done) {
+                STEREO_TRY(launch_volume_std_final(ctx, moments, moment_blocks, nvox, stdp));
+                have_std = true;
+            } else if (last_iter && stages[side]) {
+                STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
+            }
+        }
+        // post.lua:146-147: lu = lu / lu:std()
+        if (!have_std) STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
+        if (p->sgm == 1) {
+            // post.lua:152-155 + nyu.lua:47-75; the first sweep reads its costs as -(x / std)
             for (int it = 0; it < p->sgm_i; ++it) {
+                const bool last_iter = it == p->sgm_i - 1;
                 float *dst = take();
                 float *tmp = take();
-                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction));
+                SgmExtras ex;
+                ex.paths = p->sgm_paths == 8 ? 8 : 4;
+                ex.final_scale = ex.paths == 8 ? 0.125f : 0.25f;
+                ex.stdp = it == 0 ? stdp : nullptr;
+                const bool want_map = last_iter && (stages[2 + side] || p->nyu_cost_agg_2 <= 0);
+                ex.wta = want_map ? final_map : nullptr;               // post.lua:159 lu:min(2)
+                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction, ex));
                 pool.push_back(tmp);
                 advance(dst);
+                have_final_map = want_map;
             }
-            if (stages[2 + side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, stages[2 + side]));
+            if (stages[2 + side])
+                STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[2 + side], final_map, hw, cudaMemcpyDeviceToDevice, ctx->stream));
         } else {
             float *dst = take();
             STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 0, dst));
@@ -215,16 +253,21 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         }
         // nyu_cost_agg_2 (post.lua:171-186)
         for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
+            const bool last_iter = i == p->nyu_cost_agg_2 - 1;
             float *dst = take();
-            float *tmp = take();
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
-            pool.push_back(tmp);
+            CbcaExtras ex;
+            bool ex_done = false;
+            ex.wta = final_map;                                         // post.lua:178,226 lu:min(2)
+            ex.take_min = 1;
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
+                                last_iter ? &ex : nullptr, &ex_done));
             advance(dst);
+            have_final_map = last_iter && ex_done;
         }
         // post.lua:226-229: disp = argmin - 1 (0-based here); the stage image of cross_agg 2 is the same map
-        STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, side == 0 ? m.u8a : m.u8b));
+        if (!have_final_map) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, final_map));
         if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
-            STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[4 + side], side == 0 ? m.u8a : m.u8b, hw, cudaMemcpyDeviceToDevice, ctx->stream));
+            STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[4 + side], final_map, hw, cudaMemcpyDeviceToDevice, ctx->stream));
         if (side == 0) left_final = cur;
         else STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->stream));      // still the second stream here
     }
@@ -283,6 +326,7 @@ int stereo_post_default_params(stereo_post_params *p)
     p->nyu_cost_agg_2 = 1;
     p->post = 1;
     p->cbca_exact = 0;
+    p->sgm_paths = 4;
     return STEREO_OK;
 }
 
@@ -389,8 +433,11 @@ int stereo_nyu_sgm(stereo_ctx *ctx, const float *l_img, const float *r_img, floa
     float *a = ctx->post_vol[0].as<float>(), *b = ctx->post_vol[1].as<float>();
     STEREO_TRY(to_dev(ctx, a, vol, sizeof(float) * nvox));
     const SgmParams sp = sgm_params(p);
+    SgmExtras ex;
+    ex.paths = p->sgm_paths == 8 ? 8 : 4;
+    ex.final_scale = ex.paths == 8 ? 0.125f : 0.25f;
     for (int it = 0; it < p->sgm_i; ++it) {
-        STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, a, b, ctx->post_vol[2].as<float>(), h, w, D, sp, direction));
+        STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, a, b, ctx->post_vol[2].as<float>(), h, w, D, sp, direction, ex));
         std::swap(a, b);
     }
     STEREO_TRY(to_host(ctx, vol, a, sizeof(float) * nvox));

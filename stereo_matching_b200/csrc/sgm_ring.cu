@@ -30,6 +30,13 @@ constexpr int kMaxStages = 8;
 struct SgmAux {
     const uint8_t *want, *code;
     int pad, pitch;
+    // costs are read as -(cvol / *stdp) when stdp is set: post.lua:146,152 `lu = (lu / lu:std()) * -1` applied on
+    // load (the same two fp32 operations per voxel, same bits) instead of by an elementwise pass over the volume
+    const float *stdp;
+    // the last pass scales its sum by `final_scale` (0.25: nyu.lua:61,64 `/ 4`; 1: more paths follow) and, when
+    // `wta` is set, writes the arg min over D of every pixel's result (the nyu_sgm stage image, post.lua:159)
+    float final_scale;
+    uint8_t *wta;
 };
 
 // Shared-memory layout of one stage: per array (costs, running sums) a row of SLOTS, one per bulk copy:
@@ -56,6 +63,8 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     constexpr int kArrays = 1 + NACC;
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool scale_on_load = aux.stdp != nullptr;
+    const float sd = scale_on_load ? __ldg(aux.stdp) : 1.f;
     const int steps = kH ? w : h;
     const int n_lines = kH ? h : w;
     const int line0 = group * NW;
@@ -188,6 +197,10 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     if (valid4[j]) {
                         const float4 v = *reinterpret_cast<const float4 *>(base + 16 * j);
                         c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
+                        if (scale_on_load) {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) c[4 * j + e] = __fmul_rn(__fdiv_rn(c[4 * j + e], sd), -1.f);
+                        }
                         if (NACC >= 1) {
                             const float4 u = *reinterpret_cast<const float4 *>(base + array_bytes + 16 * j);
                             a[4 * j] = u.x; a[4 * j + 1] = u.y; a[4 * j + 2] = u.z; a[4 * j + 3] = u.w;
@@ -246,6 +259,10 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     }
                 };
                 gather(0, c, kSgmBig);
+                if (scale_on_load) {
+#pragma unroll
+                    for (int k = 0; k < KPL; ++k) c[k] = d0 + k < D ? __fmul_rn(__fdiv_rn(c[k], sd), -1.f) : c[k];
+                }
                 if constexpr (NACC >= 1) gather(1, a, 0.f);
                 if constexpr (NACC >= 2) gather(2, b, 0.f);
             }
@@ -256,6 +273,8 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
             } else {
                 sgm_step_coded<SD, KPL>(pen, want, c, prev, code, has_below, has_above, val);
             }
+            float best = kSgmBig;         // arg min over this lane's disparities (lowest index wins ties)
+            int best_k = 0;
 #pragma unroll
             for (int j = 0; j < KPL / 4; ++j) {
                 if (valid4[j]) {
@@ -265,13 +284,29 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                         float acc = val[4 * j + e];
                         if (NACC == 1) acc = __fadd_rn(a[4 * j + e], acc);
                         if (NACC == 2) acc = __fadd_rn(__fadd_rn(a[4 * j + e], b[4 * j + e]), acc);
-                        r[e] = last ? __fmul_rn(acc, 0.25f) : acc;        // x / 4 == x * 0.25 exactly
+                        r[e] = last ? __fmul_rn(acc, aux.final_scale) : acc;       // x / 4 == x * 0.25 exactly
+                        if (last && (ALIGNED || d0 + 4 * j + e < D) && r[e] < best) {
+                            best = r[e];
+                            best_k = 4 * j + e;
+                        }
                     }
                     if (ALIGNED) {
                         reinterpret_cast<float4 *>(optr)[j] = make_float4(r[0], r[1], r[2], r[3]);
                     } else {
                         *reinterpret_cast<float4 *>(stg_rows + (step & 1) * Dp + d0 + 4 * j) = make_float4(r[0], r[1], r[2], r[3]);
                     }
+                }
+            }
+            if (last && aux.wta != nullptr) {
+                // warp-wide arg min: one redux on order-preserving keys (-0 counted as +0), lowest lane = lowest d
+                int key = __float_as_int(__fadd_rn(best, 0.f));
+                key ^= (key >> 31) & 0x7fffffff;
+                const int mn = __reduce_min_sync(0xffffffffu, key);
+                const unsigned winners = __ballot_sync(0xffffffffu, key == mn);
+                if (lane == __ffs(winners) - 1) {
+                    const int px = kH ? (SD == 0 ? step : w - 1 - step) : line;
+                    const int py = kH ? line : (SD == 2 ? step : h - 1 - step);
+                    aux.wta[(size_t)py * w + px] = (uint8_t)(d0 + best_k);
                 }
             }
             if (!ALIGNED) {
@@ -363,7 +398,7 @@ RingShape ring_shape(int arrays, int nw, int D, bool horizontal, bool aligned, s
 
 template <int KPL, int NW, int DIR, bool ALIGNED>
 int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a, float *out_b,
-                  int h, int w, int D, const SgmParams &p)
+                  int h, int w, int D, const SgmParams &p, const SgmExtras &ex)
 {
     const RingShape sh_h = ring_shape(1, NW, D, true, ALIGNED, 32 * 1024, 96 * 1024);
     const RingShape sh_v2 = ring_shape(3, NW, D, false, ALIGNED, 24 * 1024, 72 * 1024);
@@ -382,6 +417,9 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     uint8_t *want = buf.as<uint8_t>(), *code = want + want_bytes;
     aux.want = want;
     aux.code = code;
+    aux.stdp = ex.stdp;
+    aux.final_scale = ex.final_scale;
+    aux.wta = ex.wta;
     sgm_prep_kernel<<<std::min<size_t>(((size_t)h * aux.pitch + 255) / 256, 148 * 8), 256, 0, ctx->stream>>>(
         x0, x1, h, w, p.tau_so, aux.pad, aux.pitch, want, code);
 
@@ -402,32 +440,26 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
 
 template <int DIR, bool ALIGNED>
 int launch_ring_dir(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
-                    int h, int w, int D, const SgmParams &p)
+                    int h, int w, int D, const SgmParams &p, const SgmExtras &ex)
 {
-    if (D <= 128) return launch_ring_t<4, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
-    if (D <= 256) return launch_ring_t<8, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
-    return launch_ring_t<16, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+    if (D <= 128) return launch_ring_t<4, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex);
+    if (D <= 256) return launch_ring_t<8, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex);
+    return launch_ring_t<16, 4, DIR, ALIGNED>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex);
 }
 
 }  // namespace
 
-bool sgm_ring_usable(const float *cvol, const float *out, const float *scratch, int D)
-{
-    (void)cvol; (void)out; (void)scratch;
-    return D <= 512;
-}
-
 int launch_sgm_ring(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
-                    int h, int w, int D, const SgmParams &p, int direction)
+                    int h, int w, int D, const SgmParams &p, int direction, const SgmExtras &ex)
 {
     // bulk copies and 16-byte accesses need every [x][d] row to start 16-byte aligned
     const bool aligned = D % 4 == 0 && ((uintptr_t)cvol % 16 == 0) && ((uintptr_t)out % 16 == 0) &&
                          ((uintptr_t)scratch % 16 == 0);
     if (aligned)
-        return direction > 0 ? launch_ring_dir<1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
-                             : launch_ring_dir<-1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
-    return direction > 0 ? launch_ring_dir<1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p)
-                         : launch_ring_dir<-1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p);
+        return direction > 0 ? launch_ring_dir<1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex)
+                             : launch_ring_dir<-1, true>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex);
+    return direction > 0 ? launch_ring_dir<1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex)
+                         : launch_ring_dir<-1, false>(ctx, x0, x1, cvol, out, scratch, h, w, D, p, ex);
 }
 
 }  // namespace stereo

@@ -1,6 +1,6 @@
 // One scanline step of adcensus.sgm2 (smooth/nyu.lua:59-60) for the KPL consecutive disparities a lane owns.
-// Shared by the register-prefetch kernels (post.cu) and the shared-memory ring kernels (sgm_ring.cu) so that both
-// do the original's arithmetic operation for operation.
+// Shared by the shared-memory ring kernels of the four original paths (sgm_ring.cu) and the diagonal-path kernels
+// of the 8-path variant (post.cu) so that both do the original's arithmetic operation for operation.
 #pragma once
 #include "common.cuh"
 
@@ -40,7 +40,8 @@ __device__ __forceinline__ void sgm_step(const SgmPenalties<SD> &pen, float D1, 
                                          const bool (&valid)[KPL], int xx0, int direction, int w, bool has_below,
                                          bool has_above, float (&val)[KPL])
 {
-    constexpr int dx = SD == 0 ? 1 : (SD == 1 ? -1 : 0);
+    // x step of the path: 0 ->, 1 <-, 2 down, 3 up, and the diagonals 4 down-right, 5 down-left, 6 up-right, 7 up-left
+    constexpr int dx = (SD == 0 || SD == 4 || SD == 6) ? 1 : ((SD == 1 || SD == 5 || SD == 7) ? -1 : 0);
     float pmin = prev[0];
 #pragma unroll
     for (int k = 1; k < KPL; ++k) pmin = fminf(pmin, prev[k]);

@@ -168,6 +168,52 @@ def test_full_chain_vs_oracle(ctx, scene, exact):
     assert e_out < so.three_pixel_error(scene["ld"], scene["gt"])
 
 
+@pytest.mark.parametrize("D,h,w", [(33, 6, 40), (201, 7, 23), (228, 9, 45), (64, 37, 13), (4, 5, 9), (512, 3, 18)])
+def test_sgm_eight_paths_bit_exact(ctx, D, h, w):
+    """sgm_paths = 8 (BASELINE.json configs[3]; NOT the reference, whose chain is 4-path, nyu.lua:59-64): the four
+    diagonal paths added to the original four, against the C restatement with the same switch (which
+    tests/test_post_oracle.py ties to plain Python loops).  Wide, tall and tiny images: diagonals of every length."""
+    rng = np.random.default_rng(D + h)
+    l_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    r_img = rng.standard_normal((h, w)).astype(np.float32) * 0.1
+    vol = rng.standard_normal((h, w, D)).astype(np.float32)
+    p8 = _lib.default_post_params()
+    p8.sgm_paths = 8
+    for direction in (-1, 1):
+        ref = po.nyu_sgm(l_img, r_img, np.ascontiguousarray(np.transpose(vol, (2, 0, 1))), direction, paths=8)
+        out = ctx.nyu_sgm(l_img, r_img, vol, direction, p8)
+        assert np.array_equal(np.transpose(out, (2, 0, 1)), ref)
+
+
+def test_full_chain_eight_paths_vs_oracle(ctx, scene):
+    """The whole chain with the 8-path SGM (labelled apart from the parity figures: no reference counterpart)."""
+    ref = po.post_chain(scene["lv"], scene["rv"], scene["ld"], scene["rd"], sgm_paths=8)
+    p8 = _lib.default_post_params()
+    p8.sgm_paths = 8
+    out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"], p8)
+    four = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
+    assert not np.array_equal(out["nyu_sgm_img"], four["nyu_sgm_img"])
+    for name in ("nyu_cost_img", "nyu_sgm_img", "right_nyu_sgm_img", "nyu_cost_img_2", "right_nyu_cost_img_2", "outlier",
+                 "nyu_post"):
+        assert (out[name] == ref[name]).mean() >= 0.999, name
+
+
+def test_stage_maps_and_std_fused_into_the_producing_kernels(ctx, scene):
+    """The chain computes every stage image (arg max / arg min over D) and the volume std inside the kernel that writes
+    the volume, and -(x / std) inside the SGM loads.  Each must equal what the stand-alone entry points give on the
+    same data: WTA of the exported CBCA volume, SGM of the explicitly scaled volume, its arg min."""
+    l_img, r_img = ctx.guide_image(scene["ld"]), ctx.guide_image(scene["rd"])
+    out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
+    lu, ru = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], 1)
+    assert np.array_equal(out["nyu_cost_img"], ctx.wta(lu)[0])
+    assert np.array_equal(out["right_nyu_cost_img"], ctx.wta(ru)[0])
+    for vol, direction, name in ((lu, -1, "nyu_sgm_img"), (ru, 1, "right_nyu_sgm_img")):
+        sd = np.float32(ctx.volume_std(vol))
+        sg = ctx.nyu_sgm(l_img, r_img, (vol / sd) * np.float32(-1), direction)
+        assert np.array_equal(out[name], ctx.wta(sg, take_min=True)[0]), name
+        assert np.array_equal(out[name], np.argmin(sg, axis=2).astype(np.uint8)), name
+
+
 def test_post_error_behaviour(ctx, scene):
     p = _lib.default_post_params()
     assert (p.L1, p.sgm_i, p.nyu_cost_agg_1, p.post) == (5, 1, 1, 1)
