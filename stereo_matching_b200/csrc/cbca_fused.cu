@@ -13,13 +13,25 @@
 // pixel, the matched pixel's arms "x1c[xm] - d*dir - x" are simply ITS relative arms, so the intersection of the two
 // support intervals is the bitwise AND of two records, the segment length a population count, and every
 // conditional addition one bit test - no arm arithmetic is left in the inner loops.
+//
+// RING = true (aligned volumes, the default): the costs do not come through per-thread global loads - 12 of them in
+// flight per thread were all that hid the DRAM latency at 24 warps per SM - but through a ring of shared-memory row
+// slots filled by bulk copies: the 10 pixel columns a block needs from one image row are ONE contiguous run of
+// 10 x D floats ([x][D] layout), one cp.async.bulk per row, up to eight rows ahead, completion on an mbarrier.  A warp
+// reads its 10 values of a row from shared memory (conflict-free: consecutive disparities), releases the slot, and
+// does the same additions as before.  One elected thread of warp 0 refills a slot as soon as every warp has released
+// it; no producer warp (it would cost a third of the occupancy at 80 registers).
 #include <algorithm>
 
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace stereo {
+using namespace tc;
 
 namespace {
+
+constexpr int kRingMaxSlots = 8;
 
 constexpr int kFR = 4;                   // window half width = L1 - 1
 constexpr int kFB = 2;                   // pixels per thread (4: 118 registers, two CTAs per SM, slower; 1: slower still)
@@ -74,11 +86,12 @@ __device__ __forceinline__ uint32_t order_key(float v)
 
 constexpr int kFMaxBandRows = 64;
 
+template <bool RING>
 __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                          int pitch, const float *__restrict__ vol, float *__restrict__ out,
                                                          int h, int w, int D, int direction, int rows_per_band,
                                                          double *__restrict__ moments, uint8_t *__restrict__ wta,
-                                                         int take_min)
+                                                         int take_min, int n_slots)
 {
     // the lanes past D of the last warp shadow disparity D - 1 (same loads, nothing stored or counted) so that
     // the warp-wide reductions below see whole warps
@@ -98,9 +111,34 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
     }
     double m_s = 0.0, m_ss = 0.0;
 
-    int offs[kFN];                           // element offsets of the 12 columns inside a row (clamped: loads stay in the row)
+    int offs[kFN];                           // element offsets of the 10 columns inside a row (clamped: loads stay in the row)
 #pragma unroll
     for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * D + d;
+
+    // ---- ring of row slots (RING): rows r_first .. r_last-1 of columns xlo .. xhi-1, in order ----
+    extern __shared__ __align__(128) uint8_t ring[];
+    const int r_first = max(0, y0 - kFR), n_rows = min(h, y1 + kFR) - r_first;
+    const int xlo = max(0, xb - kFR), xhi = min(w, xb + kFB + kFR);
+    const uint32_t slot_bytes = (uint32_t)kFN * D * 4, run_bytes = (uint32_t)(xhi - xlo) * D * 4;
+    const uint32_t s_ring = smem_u32(ring);
+    const uint32_t bar_full = s_ring + (uint32_t)n_slots * slot_bytes, bar_empty = bar_full + 8 * kRingMaxSlots;
+    auto issue_row = [&](int i) {            // row r_first + i into slot i % n_slots
+        const int sl = i % n_slots;
+        mbar_expect_tx(bar_full + 8 * sl, run_bytes);
+        bulk_g2s(s_ring + (uint32_t)sl * slot_bytes, vol + ((size_t)(r_first + i) * w + xlo) * D, run_bytes, bar_full + 8 * sl);
+    };
+    if (RING) {
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < n_slots; ++i) {
+                mbar_init(bar_full + 8 * i, 1);
+                mbar_init(bar_empty + 8 * i, blockDim.x >> 5);
+            }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int i = 0; i < min(n_slots, n_rows); ++i) issue_row(i);
+    }
     bool pix_ok[kFB], match_ok[kFB];
     int xm[kFB];
 #pragma unroll
@@ -128,8 +166,24 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                 // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
                 const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
                 float v[kFN];
+                if (RING) {
+                    const int i = r - r_first, sl = i % n_slots;
+                    // the slot of the previous row is free once every warp has read it: refill it (one thread)
+                    if (threadIdx.x == 0 && i >= 1 && i - 1 + n_slots < n_rows) {
+                        mbar_wait(bar_empty + 8 * ((i - 1) % n_slots), ((i - 1) / n_slots) & 1);
+                        issue_row(i - 1 + n_slots);
+                    }
+                    __syncwarp();
+                    mbar_wait(bar_full + 8 * sl, (i / n_slots) & 1);
+                    const float *srow = reinterpret_cast<const float *>(ring + (size_t)sl * slot_bytes) - xlo * D;
 #pragma unroll
-                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+                    for (int j = 0; j < kFN; ++j) v[j] = srow[offs[j]];
+                    __syncwarp();
+                    if ((threadIdx.x & 31) == 0) mbar_arrive(bar_empty + 8 * sl);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+                }
                 uint32_t own_r[kFB];
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) own_r[i] = __ldg(rec0 + (rbase + xb + i));
@@ -253,9 +307,24 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     int bands, rows_per_band;
     cbca_fused_grid(h, w, &bands, &rows_per_band);
     static_assert(63 <= kFMaxBandRows, "band rows must fit the arg-min table");
-    cbca_fused_kernel<<<dim3((w + kFB - 1) / kFB, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D,
-                                                                                direction, rows_per_band, ex.moments,
-                                                                                ex.wta, ex.take_min);
+    // bulk copies need 16-byte aligned runs: D % 4 == 0 and an aligned volume; STEREO_CBCA_KERNEL=1 keeps the
+    // per-thread global loads (the cross-check; also what D = 201 takes)
+    static const bool no_ring = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e && atoi(e) == 1; }();
+    const bool ring = !no_ring && D % 4 == 0 && ((uintptr_t)vol % 16 == 0);
+    const dim3 grid((w + kFB - 1) / kFB, bands);
+    if (ring) {
+        // as many row slots as three resident blocks per SM leave room for
+        const size_t slot_bytes = (size_t)kFN * D * 4;
+        const int n_slots = (int)std::min<size_t>(kRingMaxSlots, std::max<size_t>(2, (72 * 1024) / slot_bytes));
+        const size_t smem = n_slots * slot_bytes + 2 * 8 * kRingMaxSlots;
+        auto kern = cbca_fused_kernel<true>;
+        STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<grid, nt, smem, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band, ex.moments,
+                                              ex.wta, ex.take_min, n_slots);
+    } else {
+        cbca_fused_kernel<false><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction,
+                                                                rows_per_band, ex.moments, ex.wta, ex.take_min, 1);
+    }
     if (ex.moment_blocks) *ex.moment_blocks = ((w + kFB - 1) / kFB) * bands;
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());

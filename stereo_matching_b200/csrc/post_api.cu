@@ -152,9 +152,16 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
     // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream
     // section would serialise it
+    // Measurement knobs (scripts/post_chain_ms.py; results are the same bits either way):
+    //   STEREO_POST_SERIAL=1   both sides on one stream, so that kernel-class event times are of kernels running alone
+    //   STEREO_POST_FUSE=mask  1: -(x/std) in the SGM loads  2: volume moments in the CBCA epilogue
+    //                          4: stage arg max/min in the CBCA epilogue  8: stage arg min in the last SGM pass
+    //                          (default 15; a cleared bit runs the stand-alone kernel instead)
+    static const bool serial = [] { const char *e = getenv("STEREO_POST_SERIAL"); return e && atoi(e) == 1; }();
+    static const int fuse = [] { const char *e = getenv("STEREO_POST_FUSE"); return e ? atoi(e) : 15; }();
     const bool fused_cbca = !p->cbca_exact && D <= 256 && p->L1 <= 5;
     // three working volumes per side (result, SGM scratch, spare); the two-pass CBCA needs a fourth and its lengths
-    const int vols_per_side = fused_cbca ? 3 : 4;
+    const int vols_per_side = (fused_cbca && (fuse & 1)) ? 3 : 4;
     for (int side = 0; side < 2; ++side)
         for (int i = 0; i < vols_per_side; ++i) STEREO_TRY(ctx->post_vol[4 * side + i].reserve(sizeof(float) * nvox + kVolSlack));
     if (!fused_cbca && !p->cbca_exact)
@@ -182,7 +189,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
     const float *left_final = nullptr;
     for (int side = 0; side < 2; ++side) {
-        StreamSwap swap(ctx, side == 0 ? ctx->stream : ctx->aux_stream);
+        StreamSwap swap(ctx, side == 0 || serial ? ctx->stream : ctx->aux_stream);
         std::vector<float *> pool;
         for (int i = 0; i < vols_per_side; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
         const int direction = side == 0 ? -1 : 1;
@@ -211,24 +218,28 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             CbcaExtras ex;
             bool ex_done = false;
             if (last_iter) {
-                ex.moments = moments;                                   // post.lua:146 lu:std() of this output
-                ex.wta = stages[side];                                  // post.lua:125 lu:max(2)
+                ex.moments = (fuse & 2) ? moments : nullptr;            // post.lua:146 lu:std() of this output
+                ex.wta = (fuse & 4) ? stages[side] : nullptr;           // post.lua:125 lu:max(2)
                 ex.take_min = 0;
             }
             STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
                                 last_iter ? &ex : nullptr, &ex_done));
             advance(dst);
-            if (last_iter && ex_done) {
+            if (last_iter && ex_done && ex.moments) {
                 STEREO_TRY(launch_volume_std_final(ctx, moments, moment_blocks, nvox, stdp));
                 have_std = true;
-            } else if (last_iter && stages[side]) {
-                STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
             }
+            if (last_iter && stages[side] && !(ex_done && ex.wta)) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
         }
         // post.lua:146-147: lu = lu / lu:std()
         if (!have_std) STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
         if (p->sgm == 1) {
             // post.lua:152-155 + nyu.lua:47-75; the first sweep reads its costs as -(x / std)
+            if (!(fuse & 1)) {
+                float *dst = take();
+                STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 1, dst));
+                advance(dst);
+            }
             for (int it = 0; it < p->sgm_i; ++it) {
                 const bool last_iter = it == p->sgm_i - 1;
                 float *dst = take();
@@ -236,12 +247,13 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
                 SgmExtras ex;
                 ex.paths = p->sgm_paths == 8 ? 8 : 4;
                 ex.final_scale = ex.paths == 8 ? 0.125f : 0.25f;
-                ex.stdp = it == 0 ? stdp : nullptr;
+                ex.stdp = (it == 0 && (fuse & 1)) ? stdp : nullptr;
                 const bool want_map = last_iter && (stages[2 + side] || p->nyu_cost_agg_2 <= 0);
-                ex.wta = want_map ? final_map : nullptr;               // post.lua:159 lu:min(2)
+                ex.wta = (want_map && (fuse & 8)) ? final_map : nullptr;               // post.lua:159 lu:min(2)
                 STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction, ex));
                 pool.push_back(tmp);
                 advance(dst);
+                if (want_map && !ex.wta) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, final_map));
                 have_final_map = want_map;
             }
             if (stages[2 + side])
@@ -257,21 +269,21 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             float *dst = take();
             CbcaExtras ex;
             bool ex_done = false;
-            ex.wta = final_map;                                         // post.lua:178,226 lu:min(2)
+            ex.wta = (fuse & 4) ? final_map : nullptr;                  // post.lua:178,226 lu:min(2)
             ex.take_min = 1;
             STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
                                 last_iter ? &ex : nullptr, &ex_done));
             advance(dst);
-            have_final_map = last_iter && ex_done;
+            have_final_map = last_iter && ex_done && ex.wta;
         }
         // post.lua:226-229: disp = argmin - 1 (0-based here); the stage image of cross_agg 2 is the same map
         if (!have_final_map) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, final_map));
         if (p->nyu_cost_agg_2 > 0 && stages[4 + side])
             STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[4 + side], final_map, hw, cudaMemcpyDeviceToDevice, ctx->stream));
         if (side == 0) left_final = cur;
-        else STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->stream));      // still the second stream here
+        else if (!serial) STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_join, ctx->stream));      // still the second stream here
     }
-    STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    if (!serial) STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     if (p->post == 1) {
         STEREO_TRY(launch_u8_to_float(ctx, m.u8a, (int)hw, m.d0));
         STEREO_TRY(launch_u8_to_float(ctx, m.u8b, (int)hw, m.d1));

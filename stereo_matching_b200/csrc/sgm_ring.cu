@@ -13,6 +13,10 @@
 // (sgm_step_coded() in sgm_step.cuh): results are bit-identical to the register-prefetch kernels.
 // D % 4 != 0 or volumes that are not 16-byte aligned take the same kernels: the bulk copies then fetch the
 // 16-byte aligned superset of each run and the lanes read 4-byte words.
+// When the costs are to be read as -(x / std) (post.lua:146,152; SgmAux::stdp), kScaleWarps more warps turn every
+// landed stage's costs into that IN shared memory (IEEE division, the same two fp32 operations per voxel as the
+// elementwise pass they replace) and hand the stage on through a third barrier: the scanline warps, whose
+// 1 242-step dependent chains bound the kernel, never see the division.
 #include <algorithm>
 
 #include "common.cuh"
@@ -25,6 +29,8 @@ using namespace tc;
 namespace {
 
 constexpr int kMaxStages = 8;
+constexpr int kScaleWarps = 2;           // warps that scale landed stages (idle exit when there is nothing to scale)
+constexpr int kBarBytes = 3 * 8 * kMaxStages;      // full, empty, ready barriers
 
 // Byte images of sgm_prep_kernel: want[path][h][w], code[path][h][pitch] with pitch = w + 2 * pad
 struct SgmAux {
@@ -64,7 +70,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool scale_on_load = aux.stdp != nullptr;
-    const float sd = scale_on_load ? __ldg(aux.stdp) : 1.f;
     const int steps = kH ? w : h;
     const int n_lines = kH ? h : w;
     const int line0 = group * NW;
@@ -75,17 +80,20 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     const uint32_t stage_bytes = kArrays * array_bytes;
     const uint32_t s_data = smem_u32(smem);
     const uint32_t s_bar = s_data + (uint32_t)S * stage_bytes;
-    const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages;
+    const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages, bar_ready = s_bar + 16 * kMaxStages;
+    // consumers start on a stage when it has landed, or - with scaling - when the scale warps are through with it
+    const uint32_t bar_go = scale_on_load ? bar_ready : bar_full;
     const float *src[3] = {cvol, acc_a, acc_b};
     // unaligned volumes: results leave through a per-warp staging row (two of them, used alternately) so that a
     // warp store is a 128-byte run instead of 32 words 32 bytes apart
     const int Dp = (D + 3) & ~3;
-    float *stg_rows = reinterpret_cast<float *>(smem + (size_t)S * stage_bytes + 2 * 8 * kMaxStages) + (size_t)warp * 2 * Dp;
+    float *stg_rows = reinterpret_cast<float *>(smem + (size_t)S * stage_bytes + kBarBytes) + (size_t)warp * 2 * Dp;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < S; ++i) {
             mbar_init(bar_full + 8 * i, 1);
             mbar_init(bar_empty + 8 * i, (uint32_t)lines_here);
+            mbar_init(bar_ready + 8 * i, kScaleWarps);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -126,6 +134,29 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
         }
         return;
     }
+    if (warp > NW) {
+        // ---- scale warps: the cost array of every landed stage becomes -(x / std), 16 bytes per lane and turn ----
+        // (whole array, whichever part of it the runs fill: unused slot tails are never read)
+        if (!scale_on_load) return;
+        const float sd = __ldg(aux.stdp);
+        const int me = (warp - NW - 1) * 32 + lane;
+        for (int t = 0; t < n_stages; ++t) {
+            const int s = t % S;
+            mbar_wait(bar_full + 8 * s, (t / S) & 1);
+            float4 *arr = reinterpret_cast<float4 *>(smem + (size_t)s * stage_bytes);
+            for (uint32_t q = me; q < array_bytes / 16; q += kScaleWarps * 32) {
+                float4 v = arr[q];
+                v.x = __fmul_rn(__fdiv_rn(v.x, sd), -1.f);
+                v.y = __fmul_rn(__fdiv_rn(v.y, sd), -1.f);
+                v.z = __fmul_rn(__fdiv_rn(v.z, sd), -1.f);
+                v.w = __fmul_rn(__fdiv_rn(v.w, sd), -1.f);
+                arr[q] = v;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_ready + 8 * s);
+        }
+        return;
+    }
     if (warp >= lines_here) return;
 
     // ---- consumers: one warp per scanline, KPL consecutive disparities per lane ----
@@ -161,7 +192,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     for (int t = 0; t < n_stages; ++t) {
         const int s = t % S;
         const int g_here = min(G, steps - t * G);
-        mbar_wait(bar_full + 8 * s, (t / S) & 1);
+        mbar_wait(bar_go + 8 * s, (t / S) & 1);
         const uint8_t *stage = smem + (size_t)s * stage_bytes;
         if (!ALIGNED) {
             // byte offset of this lane's first float inside its slot at the first step of the stage: the phase of
@@ -197,10 +228,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     if (valid4[j]) {
                         const float4 v = *reinterpret_cast<const float4 *>(base + 16 * j);
                         c[4 * j] = v.x; c[4 * j + 1] = v.y; c[4 * j + 2] = v.z; c[4 * j + 3] = v.w;
-                        if (scale_on_load) {
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) c[4 * j + e] = __fmul_rn(__fdiv_rn(c[4 * j + e], sd), -1.f);
-                        }
                         if (NACC >= 1) {
                             const float4 u = *reinterpret_cast<const float4 *>(base + array_bytes + 16 * j);
                             a[4 * j] = u.x; a[4 * j + 1] = u.y; a[4 * j + 2] = u.z; a[4 * j + 3] = u.w;
@@ -259,10 +286,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
                     }
                 };
                 gather(0, c, kSgmBig);
-                if (scale_on_load) {
-#pragma unroll
-                    for (int k = 0; k < KPL; ++k) c[k] = d0 + k < D ? __fmul_rn(__fdiv_rn(c[k], sd), -1.f) : c[k];
-                }
                 if constexpr (NACC >= 1) gather(1, a, 0.f);
                 if constexpr (NACC >= 2) gather(2, b, 0.f);
             }
@@ -351,7 +374,7 @@ __global__ void sgm_prep_kernel(const float *__restrict__ x0, const float *__res
 
 // both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
 template <int KPL, int NW, int DIR, bool ALIGNED>
-__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
+__global__ __launch_bounds__((NW + 1 + kScaleWarps) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
@@ -363,7 +386,7 @@ __global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, c
 
 // SD 2: a <- (a + b) + Lr (downward); SD 3: a <- (a + Lr) / 4 (upward)
 template <int SD, int KPL, int NW, int DIR, bool ALIGNED>
-__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
+__global__ __launch_bounds__((NW + 1 + kScaleWarps) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, const float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
@@ -393,7 +416,7 @@ RingShape ring_shape(int arrays, int nw, int D, bool horizontal, bool aligned, s
         S = (int)std::min<size_t>(kMaxStages, budget / stage(G));
     }
     const size_t staging = aligned ? 0 : (size_t)nw * 2 * ((D + 3) & ~3) * 4;      // per-warp output rows
-    return {G, S, (size_t)S * stage(G) + 2 * 8 * kMaxStages + staging};
+    return {G, S, (size_t)S * stage(G) + kBarBytes + staging};
 }
 
 template <int KPL, int NW, int DIR, bool ALIGNED>
@@ -429,7 +452,8 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_h.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v2.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v3.smem));
-    const int threads = (NW + 1) * 32;
+    // the scale warps exist only when there is something to scale
+    const int threads = (NW + 1 + (ex.stdp ? kScaleWarps : 0)) * 32;
     kh<<<dim3((h + NW - 1) / NW, 2), threads, sh_h.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_h.G, sh_h.S);
     kv2<<<(w + NW - 1) / NW, threads, sh_v2.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v2.G, sh_v2.S);
     kv3<<<(w + NW - 1) / NW, threads, sh_v3.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v3.G, sh_v3.S);

@@ -73,6 +73,44 @@ def test_variant_matches_oracle(env, reference_maps, tmp_path):
         assert np.array_equal(got["lr"][i], lab.astype(np.uint8))
 
 
+CBCA_CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib
+ctx = _lib.Context(0)
+out = {}
+for D, h, w in ((228, 150, 61), (64, 70, 130), (4, 9, 5), (256, 5, 37)):
+    rng = np.random.default_rng(D)
+    # piecewise-constant guides: arms of every length; two iterations
+    gl = np.repeat(np.repeat(rng.standard_normal((h // 3 + 1, w // 5 + 1)), 3, 0), 5, 1)[:h, :w].astype(np.float32) * 0.05
+    gr = np.roll(gl, -3, axis=1)
+    lv = rng.standard_normal((h, w, D)).astype(np.float32)
+    rv = rng.standard_normal((h, w, D)).astype(np.float32)
+    out["l_%d" % D], out["r_%d" % D] = ctx.nyu_cross_agg(gl, gr, lv, rv, 2)
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_cbca_ring_and_global_load_kernels_agree_bit_for_bit(tmp_path):
+    """The fused CBCA kernel fed by bulk copies through a shared-memory ring of row slots (default for 16-byte aligned
+    volumes) against the same kernel with per-thread global loads (STEREO_CBCA_KERNEL=1): the same additions in the
+    same order, so the bits must agree; bands of every length, images narrower than a block's window.  Both are
+    checked against the C restatement in test_gpu_post.py."""
+    maps = {}
+    for name, env in (("ring", {}), ("ldg", {"STEREO_CBCA_KERNEL": "1"})):
+        e = dict(os.environ)
+        e.update(env)
+        out = tmp_path / (name + ".npz")
+        r = subprocess.run([sys.executable, "-c", CBCA_CHILD, ROOT, str(out)], env=e, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        maps[name] = np.load(out)
+    assert sorted(maps["ring"].files) == sorted(maps["ldg"].files) and len(maps["ring"].files) == 8
+    for k in maps["ring"].files:
+        assert np.array_equal(maps["ring"][k], maps["ldg"][k]), k
+
+
 BASE_CHILD = r"""
 import os, sys
 import numpy as np
