@@ -20,6 +20,9 @@ CONFIGS = [
     ("serial, only WTA in CBCA", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "4"}),
     ("serial, only WTA in SGM", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "8"}),
     ("serial, all fused, CBCA with global loads", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "1"}),
+    ("serial, nothing fused, CBCA with global loads", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "0", "STEREO_CBCA_KERNEL": "1"}),
+    ("serial, all but scale-on-load", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "14"}),
+    ("two streams, all but scale-on-load", {"STEREO_POST_FUSE": "14"}),
     ("two streams, nothing fused", {"STEREO_POST_FUSE": "0"}),
     ("two streams, all fused, CBCA with global loads", {"STEREO_CBCA_KERNEL": "1"}),
 ]

@@ -85,8 +85,14 @@ __device__ __forceinline__ uint32_t order_key(float v)
 }
 
 constexpr int kFMaxBandRows = 64;
+constexpr int kFMaxWarps = 8;
 
-template <bool RING>
+// RING: costs through the shared-memory ring of row slots.  MODE 0: the volume only; 1: + moments and / or arg MAX
+// map of the output (first CBCA of the chain); 2: + arg MIN map (second CBCA).  The row loop is unrolled nine
+// times (the register window must not move), so everything inside it is kept small: slot and phase of the ring
+// are running counters (no divisions), the extras are compiled in only where they are used - an earlier version
+// with all of it inlined nine times was four times the size and ran out of the instruction cache.
+template <bool RING, int MODE>
 __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                          int pitch, const float *__restrict__ vol, float *__restrict__ out,
                                                          int h, int w, int D, int direction, int rows_per_band,
@@ -94,22 +100,20 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                                                          int take_min, int n_slots)
 {
     // the lanes past D of the last warp shadow disparity D - 1 (same loads, nothing stored or counted) so that
-    // the warp-wide reductions below see whole warps
+    // warp-wide operations see whole warps
     const bool active = (int)threadIdx.x < D;
     const int d = active ? (int)threadIdx.x : D - 1;
     const int xb = blockIdx.x * kFB;
     const int y0 = blockIdx.y * rows_per_band, y1 = min(h, y0 + rows_per_band);
     const int shift = d * direction;
 
-    // per (row of the band, pixel): packed (value key, disparity) of the best disparity so far; one 64-bit
-    // atomic per warp and row keeps the warps independent (no barrier on the row loop)
-    __shared__ unsigned long long s_best[kFMaxBandRows][kFB];
-    __shared__ double s_red[2][8];
-    if (wta != nullptr) {
-        for (int i = threadIdx.x; i < kFMaxBandRows * kFB; i += blockDim.x) (&s_best[0][0])[i] = ~0ull;
-        __syncthreads();
-    }
+    // EXTRAS: per (row of the band, pixel, warp) the packed (value key, disparity) of the warp's best disparity:
+    // plain stores, no barrier on the row loop; merged over the warps at the end of the band
+    constexpr bool EXTRAS = MODE != 0;
+    __shared__ unsigned long long s_best[EXTRAS ? kFMaxBandRows : 1][kFB][kFMaxWarps];
+    __shared__ double s_red[2][kFMaxWarps];
     double m_s = 0.0, m_ss = 0.0;
+    const bool want_wta = EXTRAS && wta != nullptr, want_moments = MODE == 1 && moments != nullptr;
 
     int offs[kFN];                           // element offsets of the 10 columns inside a row (clamped: loads stay in the row)
 #pragma unroll
@@ -121,12 +125,11 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
     const int xlo = max(0, xb - kFR), xhi = min(w, xb + kFB + kFR);
     const uint32_t slot_bytes = (uint32_t)kFN * D * 4, run_bytes = (uint32_t)(xhi - xlo) * D * 4;
     const uint32_t s_ring = smem_u32(ring);
+    const float *ring_src = vol + ((size_t)r_first * w + xlo) * D;      // row i of the block: + i * w * D
     const uint32_t bar_full = s_ring + (uint32_t)n_slots * slot_bytes, bar_empty = bar_full + 8 * kRingMaxSlots;
-    auto issue_row = [&](int i) {            // row r_first + i into slot i % n_slots
-        const int sl = i % n_slots;
-        mbar_expect_tx(bar_full + 8 * sl, run_bytes);
-        bulk_g2s(s_ring + (uint32_t)sl * slot_bytes, vol + ((size_t)(r_first + i) * w + xlo) * D, run_bytes, bar_full + 8 * sl);
-    };
+    // running state of the ring: slot and phase of the row being read, rows issued so far (thread 0)
+    uint32_t cur_slot = 0, cur_phase = 0;
+    int rows_issued = min(n_slots, n_rows);
     if (RING) {
         if (threadIdx.x == 0) {
             for (int i = 0; i < n_slots; ++i) {
@@ -137,7 +140,11 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
         }
         __syncthreads();
         if (threadIdx.x == 0)
-            for (int i = 0; i < min(n_slots, n_rows); ++i) issue_row(i);
+            for (int i = 0; i < rows_issued; ++i) {
+                mbar_expect_tx(bar_full + 8 * i, run_bytes);
+                bulk_g2s(s_ring + (uint32_t)i * slot_bytes, ring_src + (size_t)i * w * D, run_bytes, bar_full + 8 * i);
+            }
+        ring_src += (size_t)rows_issued * w * D;           // next row to issue
     }
     bool pix_ok[kFB], match_ok[kFB];
     int xm[kFB];
@@ -167,19 +174,21 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                 const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
                 float v[kFN];
                 if (RING) {
-                    const int i = r - r_first, sl = i % n_slots;
-                    // the slot of the previous row is free once every warp has read it: refill it (one thread)
-                    if (threadIdx.x == 0 && i >= 1 && i - 1 + n_slots < n_rows) {
-                        mbar_wait(bar_empty + 8 * ((i - 1) % n_slots), ((i - 1) / n_slots) & 1);
-                        issue_row(i - 1 + n_slots);
-                    }
-                    __syncwarp();
-                    mbar_wait(bar_full + 8 * sl, (i / n_slots) & 1);
-                    const float *srow = reinterpret_cast<const float *>(ring + (size_t)sl * slot_bytes) - xlo * D;
+                    mbar_wait(bar_full + 8 * cur_slot, cur_phase);
+                    const float *srow = reinterpret_cast<const float *>(ring + cur_slot * slot_bytes) - xlo * D;
 #pragma unroll
                     for (int j = 0; j < kFN; ++j) v[j] = srow[offs[j]];
                     __syncwarp();
-                    if ((threadIdx.x & 31) == 0) mbar_arrive(bar_empty + 8 * sl);
+                    if ((threadIdx.x & 31) == 0) mbar_arrive(bar_empty + 8 * cur_slot);
+                    // one thread refills the slot as soon as every warp has released it (row rows_issued)
+                    if (threadIdx.x == 0 && rows_issued < n_rows) {
+                        mbar_wait(bar_empty + 8 * cur_slot, cur_phase);
+                        mbar_expect_tx(bar_full + 8 * cur_slot, run_bytes);
+                        bulk_g2s(s_ring + cur_slot * slot_bytes, ring_src, run_bytes, bar_full + 8 * cur_slot);
+                        ring_src += (size_t)w * D;
+                        ++rows_issued;
+                    }
+                    if (++cur_slot == (uint32_t)n_slots) { cur_slot = 0; cur_phase ^= 1; }
                 } else {
 #pragma unroll
                     for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
@@ -227,34 +236,40 @@ __global__ __launch_bounds__(256) void cbca_fused_kernel(const uint32_t *__restr
                     const float centre = hs[(u + 1 + kFR) % kFW][i];
                     const float res = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
                     if (active) out[obase + offs[kFR + i]] = res;
-                    if (moments != nullptr && active) {
-                        const double rd = (double)res;
-                        m_s += rd;
-                        m_ss = fma(rd, rd, m_ss);
-                    }
-                    if (wta != nullptr) {
-                        // best disparity of the warp's 32: one redux on the keys (arg max: inverted keys), the lowest
-                        // lane holding the winner is the lowest disparity
-                        uint32_t key = order_key(res);
-                        if (!take_min) key = ~key;
-                        if (!active) key = 0xffffffffu;
-                        const uint32_t mn = __reduce_min_sync(0xffffffffu, key);
-                        const unsigned winners = __ballot_sync(0xffffffffu, key == mn);
-                        if ((int)(threadIdx.x & 31) == __ffs(winners) - 1)
-                            atomicMin(&s_best[y - y0][i], ((unsigned long long)mn << 32) | (unsigned)d);
+                    if (EXTRAS) {
+                        if (want_moments && active) {
+                            const double rd = (double)res;
+                            m_s += rd;
+                            m_ss = fma(rd, rd, m_ss);
+                        }
+                        if (want_wta) {
+                            // best disparity of the warp's 32: one redux on the keys (arg max: inverted keys), the
+                            // lowest lane holding the winner is the lowest disparity
+                            uint32_t key = order_key(res);
+                            if (MODE == 1) key = ~key;
+                            if (!active) key = 0xffffffffu;
+                            const uint32_t mn = __reduce_min_sync(0xffffffffu, key);
+                            const unsigned winners = __ballot_sync(0xffffffffu, key == mn);
+                            if ((int)(threadIdx.x & 31) == __ffs(winners) - 1)
+                                s_best[y - y0][i][threadIdx.x >> 5] = ((unsigned long long)mn << 32) | (unsigned)d;
+                        }
                     }
                 }
             }
         }
     }
-    if (wta != nullptr) {
+    if (EXTRAS && want_wta) {
         __syncthreads();
+        const int n_warps = blockDim.x >> 5;
         for (int i = threadIdx.x; i < (y1 - y0) * kFB; i += blockDim.x) {
             const int row = i / kFB, px = i - row * kFB;
-            if (xb + px < w) wta[(size_t)(y0 + row) * w + xb + px] = (uint8_t)(s_best[row][px] & 0xffu);
+            if (xb + px >= w) continue;
+            unsigned long long best = s_best[row][px][0];
+            for (int k = 1; k < n_warps; ++k) best = min(best, s_best[row][px][k]);      // lowest key, then lowest disparity
+            wta[(size_t)(y0 + row) * w + xb + px] = (uint8_t)(best & 0xffu);
         }
     }
-    if (moments != nullptr) {
+    if (EXTRAS && want_moments) {
         // block partials in a fixed order (deterministic): lanes by a shuffle tree, warps one after the other
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -312,19 +327,22 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     static const bool no_ring = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e && atoi(e) == 1; }();
     const bool ring = !no_ring && D % 4 == 0 && ((uintptr_t)vol % 16 == 0);
     const dim3 grid((w + kFB - 1) / kFB, bands);
-    if (ring) {
-        // as many row slots as three resident blocks per SM leave room for
-        const size_t slot_bytes = (size_t)kFN * D * 4;
-        const int n_slots = (int)std::min<size_t>(kRingMaxSlots, std::max<size_t>(2, (72 * 1024) / slot_bytes));
-        const size_t smem = n_slots * slot_bytes + 2 * 8 * kRingMaxSlots;
-        auto kern = cbca_fused_kernel<true>;
-        STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool extras = ex.moments != nullptr || ex.wta != nullptr;
+    // as many row slots as three resident blocks per SM leave room for
+    const size_t slot_bytes = (size_t)kFN * D * 4;
+    const int n_slots = ring ? (int)std::min<size_t>(kRingMaxSlots, std::max<size_t>(2, ((extras ? 64 : 72) * 1024) / slot_bytes)) : 1;
+    const size_t smem = ring ? n_slots * slot_bytes + 2 * 8 * kRingMaxSlots : 0;
+    auto launch = [&](auto kern) -> int {
+        if (smem > 48 * 1024) STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<grid, nt, smem, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band, ex.moments,
                                               ex.wta, ex.take_min, n_slots);
-    } else {
-        cbca_fused_kernel<false><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction,
-                                                                rows_per_band, ex.moments, ex.wta, ex.take_min, 1);
-    }
+        return STEREO_OK;
+    };
+    // mode 1: moments and / or arg max; mode 2: arg min only
+    STEREO_REQUIRE(!(ex.moments && ex.wta && ex.take_min), "moments come with the arg MAX map (first CBCA of the chain)");
+    const int mode = !extras ? 0 : ((ex.wta && ex.take_min) ? 2 : 1);
+    if (ring) STEREO_TRY(mode == 0 ? launch(cbca_fused_kernel<true, 0>) : mode == 1 ? launch(cbca_fused_kernel<true, 1>) : launch(cbca_fused_kernel<true, 2>));
+    else STEREO_TRY(mode == 0 ? launch(cbca_fused_kernel<false, 0>) : mode == 1 ? launch(cbca_fused_kernel<false, 1>) : launch(cbca_fused_kernel<false, 2>));
     if (ex.moment_blocks) *ex.moment_blocks = ((w + kFB - 1) / kFB) * bands;
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());

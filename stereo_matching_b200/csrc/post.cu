@@ -14,6 +14,7 @@
 // original's arithmetic (mean2d) uses an explicit fmaf, everything else is
 // compiled without contraction.
 #include "common.cuh"
+#include "exact_div.cuh"
 #include "sgm_step.cuh"
 
 namespace stereo {
@@ -589,7 +590,7 @@ __global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ 
     const int steps = min(dx > 0 ? w - x : x + 1, dy > 0 ? h - y : y + 1);
     const int d0 = lane * KPL;
     const bool scale_on_load = stdp != nullptr;
-    const float sd = scale_on_load ? __ldg(stdp) : 1.f;
+    const ConstDivisor sd = make_divisor(scale_on_load ? __ldg(stdp) : 1.f);
     const SgmPenalties<SD> pen(p);
 
     const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;     // floats between consecutive steps
@@ -647,7 +648,7 @@ __global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ 
 #pragma unroll
             for (int k = 0; k < KPL; ++k) {
                 c[k] = cbuf[i][k];
-                if (scale_on_load) c[k] = __fmul_rn(__fdiv_rn(c[k], sd), -1.f);
+                if (scale_on_load) c[k] = __fmul_rn(div_exact(c[k], sd), -1.f);
             }
             float val[KPL];
             if (step == 0) {

@@ -14,12 +14,13 @@
 // D % 4 != 0 or volumes that are not 16-byte aligned take the same kernels: the bulk copies then fetch the
 // 16-byte aligned superset of each run and the lanes read 4-byte words.
 // When the costs are to be read as -(x / std) (post.lua:146,152; SgmAux::stdp), kScaleWarps more warps turn every
-// landed stage's costs into that IN shared memory (IEEE division, the same two fp32 operations per voxel as the
-// elementwise pass they replace) and hand the stage on through a third barrier: the scanline warps, whose
+// landed stage's costs into that IN shared memory (IEEE-exact division by the one divisor, exact_div.cuh: the same two fp32 results per
+// voxel as the elementwise pass they replace) and hand the stage on through a third barrier: the scanline warps, whose
 // 1 242-step dependent chains bound the kernel, never see the division.
 #include <algorithm>
 
 #include "common.cuh"
+#include "exact_div.cuh"
 #include "sgm_step.cuh"
 #include "tc_common.cuh"
 
@@ -138,7 +139,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
         // ---- scale warps: the cost array of every landed stage becomes -(x / std), 16 bytes per lane and turn ----
         // (whole array, whichever part of it the runs fill: unused slot tails are never read)
         if (!scale_on_load) return;
-        const float sd = __ldg(aux.stdp);
+        const ConstDivisor sd = make_divisor(__ldg(aux.stdp));      // IEEE-exact x / std without a divide per element
         const int me = (warp - NW - 1) * 32 + lane;
         for (int t = 0; t < n_stages; ++t) {
             const int s = t % S;
@@ -146,10 +147,10 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
             float4 *arr = reinterpret_cast<float4 *>(smem + (size_t)s * stage_bytes);
             for (uint32_t q = me; q < array_bytes / 16; q += kScaleWarps * 32) {
                 float4 v = arr[q];
-                v.x = __fmul_rn(__fdiv_rn(v.x, sd), -1.f);
-                v.y = __fmul_rn(__fdiv_rn(v.y, sd), -1.f);
-                v.z = __fmul_rn(__fdiv_rn(v.z, sd), -1.f);
-                v.w = __fmul_rn(__fdiv_rn(v.w, sd), -1.f);
+                v.x = __fmul_rn(div_exact(v.x, sd), -1.f);
+                v.y = __fmul_rn(div_exact(v.y, sd), -1.f);
+                v.z = __fmul_rn(div_exact(v.z, sd), -1.f);
+                v.w = __fmul_rn(div_exact(v.w, sd), -1.f);
                 arr[q] = v;
             }
             __syncwarp();

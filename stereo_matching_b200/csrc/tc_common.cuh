@@ -26,6 +26,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     uint32_t done = 0;
+    // not unrolled: the compiler otherwise emits dozens of try_wait copies per call site, which adds up to tens of
+    // kilobytes of code in kernels that wait inside unrolled loops
+#pragma unroll 1
     for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
