@@ -2,6 +2,13 @@
 """Benchmark of the stereo hot path (BASELINE.json metric: pairs/sec at 375x1242, D=228).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--config ws9_fused|base_model|post_chain|train_dp]
+
+`--config` selects which BASELINE.json configuration is the headline of the ONE JSON line (same contract for each:
+value, e2e, roofline of that configuration's dominant kernel, cpu_baseline): ws9_fused = configs[1] (default, what
+the driver runs), base_model = configs[2], post_chain = configs[3], train_dp = configs[4].  Under torchrun the first
+three shard pairs over the ranks with no collective; train_dp times forward/backward + ONE NCCL all-reduce of the
+gradient array + Adam per step.
 
 A step is one pass of the hot path over one batch of synthetic KITTI-shaped
 stereo pairs: normalise + pad, both trunk forwards (base_model_ws_9, ckpt-1000
@@ -101,6 +108,21 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
+def ncu_metrics(kernel_substr: str):
+    """Per-launch ncu metrics of a kernel from the committed profiles/ncu_metrics.json (written by
+    scripts/ncu_summary.py from `ncu --set full` captures of this round): {"dram_bytes": read + write per launch,
+    "tensor_pipe_active": fraction, "report": file}; None when the kernel has not been captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_metrics.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        table = json.load(f)
+    for name, row in table.items():
+        if kernel_substr in name:
+            return row
+    return None
+
+
 def synthetic_batch(n_pairs: int):
     from stereo_matching_b200 import synth
     base = [synth.make_pair(1000 + i, H, W, D) for i in range(min(DISTINCT_PAIRS, n_pairs))]
@@ -137,10 +159,11 @@ def run_reference(args):
     rank, _, world = dist_env()
     if rank != 0:
         return 0
-    rows = args.cpu_rows
-    total = args.steps + args.warmup
-    times, cores = cpu_pair_seconds(rows, None, repeats=total)
-    timed = times[args.warmup:]
+    rows = args.ref_rows
+    # the CPU path has no caches to warm beyond the first call: one warm-up pair, then K timed pairs
+    # W untimed warm-up steps on a 24-row crop (they only page in torch and the weights), then K timed steps
+    cpu_pair_seconds(min(24, rows), None, repeats=args.warmup)
+    timed, cores = cpu_pair_seconds(rows, None, repeats=args.steps)
     sec = float(np.sum(timed))
     pairs = (rows / H) * len(timed)
     value = pairs / sec
@@ -150,8 +173,10 @@ def run_reference(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, 1),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"oracle/stereo_oracle.infer_pair fp32 on the first {rows} of {H} rows of one "
-                                   f"{H}x{W} pair, D={D}, per step; pairs/s scaled by rows/{H}"},
+                         "sample": (f"oracle/stereo_oracle.infer_pair fp32 on one whole {H}x{W} pair, D={D}, per step"
+                                    if rows == H else
+                                    f"oracle/stereo_oracle.infer_pair fp32 on the first {rows} of {H} rows of one "
+                                    f"{H}x{W} pair, D={D}, per step; pairs/s scaled by rows/{H}")},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -295,7 +320,9 @@ def run_b200(args):
     conv_flops_pair = sum(2.0 * 9 * 64 * 64 * (H + 8 - 2 * k) * (W + 8 - 2 * k) * 2 for k in (2, 3, 4))
     conv_tflops = conv_flops_pair * n * args.steps / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
     corr_ms, corr_launches = prof["corr"]
-    band_flops_pair = 2.0 * 2 * 64 * H * sum(W - d for d in range(D))        # both sides, valid band only
+    # the valid band once: the left and the right volume hold the SAME products (12.35 GFLOP per pair);
+    # the fused kernel computes the band twice (one sweep per side), which the algorithmic count does not credit
+    band_flops_pair = 2.0 * 64 * H * sum(W - d for d in range(D))
     corr_tflops = band_flops_pair * n * args.steps / (corr_ms / 1e3) / 1e12 if corr_ms > 0 else 0.0
     corr_bytes = 2.0 * H * W * 64 * 4 + 2.0 * H * W      # fp32-equivalent feature bytes in, two uint8 maps out
     rooflines = {
@@ -306,9 +333,11 @@ def run_b200(args):
                  # dram__bytes_read.sum + dram__bytes_write.sum per launch of conv3x3_tc3_kernel at 375x1242
                  # (ncu --set full, profiles/r01_ncu_summary.md: 267.4 MB + 191.9 MB); algorithmic bytes per
                  # launch are the bf16 (hi, lo) activations in and out, 2 x 2 x 2 x 64 x 2 B per pixel
-                 "traffic": (459.3e6 if (args.precision != "fp32" and (H, W) == (375, 1242)) else None),
+                 "traffic": ((ncu_metrics("conv3x3_tc3_kernel") or {}).get("dram_bytes")
+                             if (args.precision != "fp32" and (H, W) == (375, 1242)) else None),
                  "algorithmic_bytes_per_launch": 2.0 * 2 * 64 * 2 * 2 * (H + 5) * (W + 5),
-                 "tensor_pipe_active_ncu": 0.85 if args.precision == "bf16x3" else None,
+                 "tensor_pipe_active_ncu": ((ncu_metrics("conv3x3_tc3_kernel") or {}).get("tensor_pipe_active")
+                                            if args.precision == "bf16x3" else None),
                  "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
                  "avg_launch_ms": conv_ms / conv_launches if conv_launches else None,
                  "share_of_step": shares.get("conv"), "mma_passes": split,
@@ -325,7 +354,8 @@ def run_b200(args):
                  "share_of_step": shares.get("corr"), "mma_passes": split,
                  "gdisp_evals_per_s": 2.0 * H * W * D * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None,
                  "algorithmic_gbs": corr_bytes * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None,
-                 "note": "valid-band FLOPs of both volumes (12.35 GFLOP per pair) / CUDA-event time"},
+                 "note": "valid-band FLOPs (12.35 GFLOP per pair, the band counted once although both sweeps compute it) / "
+                         "CUDA-event time"},
     }
     dominant = "conv" if shares.get("conv", 0) >= shares.get("corr", 0) else "corr"
     roofline = rooflines[dominant]
@@ -566,16 +596,27 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--pairs", type=int, default=PAIRS_PER_GPU, help="pairs per GPU per step")
+    ap.add_argument("--config", default="ws9_fused", choices=["ws9_fused", "base_model", "post_chain", "train_dp"],
+                    help="which BASELINE.json configuration is the headline (see the module docstring)")
+    ap.add_argument("--sgm-paths", type=int, default=4, choices=[4, 8],
+                    help="post_chain only: 8 = the 8-path SGM variant (no reference counterpart; labelled in the line)")
+    ap.add_argument("--pairs", type=int, default=None,
+                    help="pairs per GPU per step (default 64 for ws9_fused, 8 for base_model and post_chain)")
     ap.add_argument("--precision", default="bf16x3", choices=["fp32", "bf16x3", "bf16"],
                     help="bf16x3 = tcgen05 with the 3-pass bf16 split (meets the 1e-4 parity gate); fp32 = CUDA cores")
     ap.add_argument("--e2e-pairs", type=int, default=64, help="pairs per host-pointer call in the e2e leg")
-    ap.add_argument("--cpu-rows", type=int, default=96, help="image rows of the bounded CPU sample")
+    ap.add_argument("--cpu-rows", type=int, default=96, help="image rows of the bounded CPU sample (cpu_baseline leg)")
+    ap.add_argument("--ref-rows", type=int, default=H,
+                    help="--impl reference: image rows per step (default: the whole 375-row pair, ~8 s per step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-post", action="store_true", help="skip the secondary post-chain measurement")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    if args.pairs is None:
+        args.pairs = PAIRS_PER_GPU if args.config == "ws9_fused" else 8
+    if args.config != "ws9_fused":
+        return {"base_model": run_base_model, "post_chain": run_post_chain, "train_dp": run_train_dp}[args.config](args)
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)

@@ -2,8 +2,9 @@
 
 Every configuration runs scripts/post_chain_ms.py in its own process (the library reads its measurement knobs once):
 STEREO_POST_SERIAL=1 puts both sides on one stream so that the kernel-class times are of kernels running alone,
-STEREO_POST_FUSE clears single fusions (see csrc/post_api.cu), STEREO_CBCA_KERNEL=1 takes the CBCA kernel with
-per-thread global loads instead of the bulk-copy ring."""
+STEREO_CBCA_OCC=4 takes the CBCA kernel compiled for four resident blocks per SM.  (The fusion knobs this script
+was written for - STEREO_POST_FUSE, the bulk-copy ring CBCA - were measured and removed with the code they
+switched: profiles/r02_post_chain_ab.md.)"""
 import json
 import os
 import subprocess
@@ -12,19 +13,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 D = sys.argv[1] if len(sys.argv) > 1 else "228"
 CONFIGS = [
-    ("default (two streams, all fused)", {}),
-    ("serial, all fused", {"STEREO_POST_SERIAL": "1"}),
-    ("serial, nothing fused (round-1 structure)", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "0"}),
-    ("serial, only scale-on-load", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "1"}),
-    ("serial, only moments in CBCA", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "2"}),
-    ("serial, only WTA in CBCA", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "4"}),
-    ("serial, only WTA in SGM", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "8"}),
-    ("serial, all fused, CBCA with global loads", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "1"}),
-    ("serial, nothing fused, CBCA with global loads", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "0", "STEREO_CBCA_KERNEL": "1"}),
-    ("serial, all but scale-on-load", {"STEREO_POST_SERIAL": "1", "STEREO_POST_FUSE": "14"}),
-    ("two streams, all but scale-on-load", {"STEREO_POST_FUSE": "14"}),
-    ("two streams, nothing fused", {"STEREO_POST_FUSE": "0"}),
-    ("two streams, all fused, CBCA with global loads", {"STEREO_CBCA_KERNEL": "1"}),
+    ("default (two streams)", {}),
+    ("serial", {"STEREO_POST_SERIAL": "1"}),
+    ("serial, CBCA for four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_OCC": "4"}),
+    ("two streams, CBCA for four blocks per SM", {"STEREO_CBCA_OCC": "4"}),
 ]
 for name, env in CONFIGS:
     e = dict(os.environ)

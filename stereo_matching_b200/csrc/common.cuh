@@ -187,6 +187,9 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
 int launch_corr_ffma(stereo_ctx *ctx, const float *lmap, const float *rmap, int n, int h, int w, int c,
                      int D, float *left_vol, float *right_vol, uint8_t *left_disp, uint8_t *right_disp);
 int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp);
+int wta_moments_max_blocks(const stereo_ctx *ctx);
+int launch_wta_moments(stereo_ctx *ctx, const float *vol, size_t npix, int D, int take_min, uint8_t *disp,
+                       double *partial, int *nblocks);
 int launch_lr_check(stereo_ctx *ctx, const uint8_t *d0, const uint8_t *d1, int n, int h, int w, int D,
                     uint8_t *outlier);
 // post.cu
@@ -200,30 +203,18 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
 // cbca_fused.cu
-// What the fused CBCA kernel computes besides the aggregated volume (all optional):
-//   moments  per-block partial sums (double: sum, sum of squares) of the OUTPUT volume, combined by
-//            launch_volume_std_final into the unbiased std of post.lua:146 - saves one pass over the volume
-//   wta      uint8 [h][w]: arg max (take_min = 0) / arg min (1) over D of the output (stage images, post.lua:125,178)
-struct CbcaExtras {
-    double *moments = nullptr;
-    int *moment_blocks = nullptr;      // out: number of partial pairs written
-    uint8_t *wta = nullptr;
-    int take_min = 0;
-};
 int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
-                      int D, int direction, int L1, const CbcaExtras &ex = CbcaExtras());
-int cbca_fused_blocks(int h, int w);
+                      int D, int direction, int L1);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
-int launch_volume_std_final(stereo_ctx *ctx, const double *partial, int nblocks, size_t n, float *result);
+// the same with the arg max over D of every [x][d] row written to `wta` (uint8 [h*w]; D <= 256) in the same pass
+int launch_volume_std_wta(stereo_ctx *ctx, const float *vol, size_t n_pixels, int D, float *result, uint8_t *wta, int slot);
 int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
 // What the SGM kernels fuse in besides the four paths (all optional):
-//   stdp         costs are read as -(cvol / *stdp)  (post.lua:146,152) instead of pre-scaled by a pass of their own
 //   final_scale  factor of the last path's sum: 0.25 (nyu.lua:61,64 `/ 4`), 0.125 after eight paths
 //   wta          uint8 [h][w]: arg min over D of the final result (the nyu_sgm stage image, post.lua:159); D <= 256
 //   paths        4 (the reference) or 8 (adds the diagonals; no counterpart in the reference)
 struct SgmExtras {
-    const float *stdp = nullptr;
     float final_scale = 0.25f;
     uint8_t *wta = nullptr;
     int paths = 4;

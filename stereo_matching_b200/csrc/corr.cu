@@ -216,9 +216,15 @@ __global__ void wta_kernel(const float *__restrict__ vol, size_t npix, int D, in
 
 // Vector variant for D % 4 == 0, D <= 256: half a warp per pixel, four 16-byte loads per lane
 // in flight before any compare, 4 shuffle rounds.  Same result as wta_kernel.
+// MOMENTS: the same pass also accumulates the sum and the sum of squares of every voxel (double; per-block
+// partials in block order, combined by volume_std_final_kernel): the volume std of post.lua:146 and the stage image
+// of post.lua:125 from ONE read of the volume.
+template <bool MOMENTS>
 __global__ __launch_bounds__(256) void wta_vec_kernel(const float4 *__restrict__ vol, size_t npix, int D4,
-                                                      int take_min, uint8_t *__restrict__ disp)
+                                                      int take_min, uint8_t *__restrict__ disp,
+                                                      double *__restrict__ partial)
 {
+    double m_s = 0.0, m_ss = 0.0;
     const int sub = threadIdx.x & 15;
     size_t grp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
     const size_t ngrp = ((size_t)gridDim.x * blockDim.x) >> 4;
@@ -233,6 +239,15 @@ __global__ __launch_bounds__(256) void wta_vec_kernel(const float4 *__restrict__
         for (int j = 0; j < 4; ++j) {
             const int q = sub + 16 * j;
             v[j] = (live && q < D4) ? __ldg(row + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (MOMENTS) {
+            // rows past the end and columns past D were loaded as zeros: they add nothing
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const double a = v[j].x, b = v[j].y, c = v[j].z, d = v[j].w;
+                m_s += (a + b) + (c + d);
+                m_ss += (a * a + b * b) + (c * c + d * d);
+            }
         }
         float best = 0.f;
         int best_d = 0x7fffffff;
@@ -257,6 +272,40 @@ __global__ __launch_bounds__(256) void wta_vec_kernel(const float4 *__restrict__
         }
         if (live && sub == 0) disp[grp] = (uint8_t)(best_d & 255);
     }
+    if (MOMENTS) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            m_s += __shfl_down_sync(0xffffffffu, m_s, o);
+            m_ss += __shfl_down_sync(0xffffffffu, m_ss, o);
+        }
+        __shared__ double sh[2][8];
+        if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = m_s; sh[1][threadIdx.x >> 5] = m_ss; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0, b = 0.0;
+            for (int i = 0; i < 8; ++i) { a += sh[0][i]; b += sh[1][i]; }
+            partial[2 * blockIdx.x] = a;
+            partial[2 * blockIdx.x + 1] = b;
+        }
+    }
+}
+
+// arg max / arg min map and the moment partials of a 16-byte aligned volume with D % 4 == 0, D <= 256, in one pass;
+// *nblocks = number of (sum, sum of squares) pairs written to `partial` (room for 2 * wta_moments_max_blocks())
+int wta_moments_max_blocks(const stereo_ctx *ctx) { return ctx->sm_count * 16; }
+
+int launch_wta_moments(stereo_ctx *ctx, const float *vol, size_t npix, int D, int take_min, uint8_t *disp,
+                       double *partial, int *nblocks)
+{
+    STEREO_REQUIRE(D % 4 == 0 && D <= 256 && (uintptr_t)vol % 16 == 0, "wta + moments pass needs an aligned volume");
+    int vblocks = (int)((npix + 15) / 16);
+    if (vblocks > wta_moments_max_blocks(ctx)) vblocks = wta_moments_max_blocks(ctx);
+    wta_vec_kernel<true><<<vblocks, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(vol), npix, D / 4, take_min,
+                                                           disp, partial);
+    *nblocks = vblocks;
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
 }
 
 int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, int take_min, uint8_t *disp)
@@ -267,8 +316,8 @@ int launch_wta(stereo_ctx *ctx, const float *vol, int n, int h, int w, int D, in
         int vcap = ctx->sm_count * 16;
         if (vblocks > vcap) vblocks = vcap;
         ProfScope prof(ctx, STEREO_K_WTA);
-        wta_vec_kernel<<<vblocks, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(vol), npix, D / 4, take_min,
-                                                         disp);
+        wta_vec_kernel<false><<<vblocks, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(vol), npix, D / 4,
+                                                                take_min, disp, nullptr);
         ctx->launches += 1;
         STEREO_CUDA_CHECK(cudaGetLastError());
         return STEREO_OK;

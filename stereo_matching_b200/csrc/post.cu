@@ -13,6 +13,8 @@
 // bit for bit; the only place where nvcc's FMA contraction is part of the
 // original's arithmetic (mean2d) uses an explicit fmaf, everything else is
 // compiled without contraction.
+#include <algorithm>
+
 #include "common.cuh"
 #include "exact_div.cuh"
 #include "sgm_step.cuh"
@@ -463,11 +465,20 @@ int launch_volume_std_with(stereo_ctx *ctx, const float *vol, size_t n, double *
     return STEREO_OK;
 }
 
-// the final step alone, over partial sums another kernel produced (the fused CBCA kernel's epilogue)
-int launch_volume_std_final(stereo_ctx *ctx, const double *partial, int nblocks, size_t n, float *result)
+// post.lua:125 + :146 from one read of the volume: the arg max map of every pixel and the unbiased std (aligned
+// volumes with D % 4 == 0, D <= 256; the caller falls back to the two stand-alone kernels otherwise)
+int launch_volume_std_wta(stereo_ctx *ctx, const float *vol, size_t n_pixels, int D, float *result, uint8_t *wta, int slot)
 {
+    const size_t area = 2 * (size_t)std::max(kStdBlocks, wta_moments_max_blocks(ctx));
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * area));
+    double *partial = ctx->scratch.as<double>() + (slot ? area : 0);
+    int nblocks = 0;
+    {
+        ProfScope prof(ctx, STEREO_K_WTA);
+        STEREO_TRY(launch_wta_moments(ctx, vol, n_pixels, D, 0, wta, partial, &nblocks));
+    }
     ProfScope prof(ctx, STEREO_K_VOLSTD);
-    volume_std_final_kernel<<<1, 32, 0, ctx->stream>>>(partial, nblocks, (double)n, result);
+    volume_std_final_kernel<<<1, 32, 0, ctx->stream>>>(partial, nblocks, (double)n_pixels * D, result);
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
@@ -476,8 +487,9 @@ int launch_volume_std_final(stereo_ctx *ctx, const double *partial, int nblocks,
 // `slot` (0 or 1) selects one of two partial-sum areas so that two streams can reduce at once
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot)
 {
-    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * kStdBlocks));
-    return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>() + (slot ? 2 * kStdBlocks : 0), result);
+    const size_t area = 2 * (size_t)std::max(kStdBlocks, wta_moments_max_blocks(ctx));
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * area));
+    return launch_volume_std_with(ctx, vol, n, ctx->scratch.as<double>() + (slot ? area : 0), result);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -542,10 +554,27 @@ __global__ void scale_kernel(const float *__restrict__ in, size_t n, const float
                              float *__restrict__ out)
 {
     // mode 0: x / std   mode 1: -(x / std)   mode 2: x / 4
-    float sd = mode == 2 ? 4.f : stdp[0];
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        float v = __fdiv_rn(in[i], sd);
-        out[i] = mode == 1 ? __fmul_rn(v, -1.f) : v;
+    // One divisor for the whole volume: div_exact (exact_div.cuh) gives the bits of IEEE division at five FMA-class
+    // instructions per voxel; with __fdiv_rn (reciprocal approximation, range check, slow-path call per element) this
+    // pass ran at 3.8 TB/s instead of at the speed of a copy.
+    const ConstDivisor sd = make_divisor(mode == 2 ? 4.f : stdp[0]);
+    const size_t stride = (size_t)gridDim.x * blockDim.x, tid0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const float sign = mode == 1 ? -1.f : 1.f;
+    if ((((uintptr_t)in | (uintptr_t)out) & 15) == 0) {
+        const float4 *in4 = reinterpret_cast<const float4 *>(in);
+        float4 *out4 = reinterpret_cast<float4 *>(out);
+        const size_t n4 = n / 4;
+        for (size_t i = tid0; i < n4; i += stride) {
+            float4 v = __ldg(in4 + i);
+            v.x = __fmul_rn(div_exact(v.x, sd), sign);
+            v.y = __fmul_rn(div_exact(v.y, sd), sign);
+            v.z = __fmul_rn(div_exact(v.z, sd), sign);
+            v.w = __fmul_rn(div_exact(v.w, sd), sign);
+            out4[i] = v;
+        }
+        for (size_t i = 4 * n4 + tid0; i < n; i += stride) out[i] = __fmul_rn(div_exact(in[i], sd), sign);
+    } else {
+        for (size_t i = tid0; i < n; i += stride) out[i] = __fmul_rn(div_exact(in[i], sd), sign);
     }
 }
 
@@ -575,8 +604,8 @@ int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, 
 template <int SD, int KPL, int PF, bool VEC>
 __global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ x0, const float *__restrict__ x1,
                                                       const float *__restrict__ cvol, float *acc, int h, int w, int D,
-                                                      SgmParams p, int direction, const float *__restrict__ stdp,
-                                                      float final_scale, int last, uint8_t *wta)
+                                                      SgmParams p, int direction, float final_scale, int last,
+                                                      uint8_t *wta)
 {
     static_assert(SD >= 4 && SD < 8, "diagonal paths only");
     constexpr int dx = (SD == 4 || SD == 6) ? 1 : -1;
@@ -589,8 +618,6 @@ __global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ 
     int y = line < w ? y_first : y_first + dy * (line - w + 1);
     const int steps = min(dx > 0 ? w - x : x + 1, dy > 0 ? h - y : y + 1);
     const int d0 = lane * KPL;
-    const bool scale_on_load = stdp != nullptr;
-    const ConstDivisor sd = make_divisor(scale_on_load ? __ldg(stdp) : 1.f);
     const SgmPenalties<SD> pen(p);
 
     const ptrdiff_t vstride = ((ptrdiff_t)dy * w + dx) * D;     // floats between consecutive steps
@@ -646,10 +673,7 @@ __global__ __launch_bounds__(32) void sgm_diag_kernel(const float *__restrict__ 
             }
             float c[KPL];
 #pragma unroll
-            for (int k = 0; k < KPL; ++k) {
-                c[k] = cbuf[i][k];
-                if (scale_on_load) c[k] = __fmul_rn(div_exact(c[k], sd), -1.f);
-            }
+            for (int k = 0; k < KPL; ++k) c[k] = cbuf[i][k];
             float val[KPL];
             if (step == 0) {
 #pragma unroll
@@ -705,17 +729,17 @@ static int launch_sgm_diagonals(stereo_ctx *ctx, const float *x0, const float *x
                                 int w, int D, const SgmParams &p, int direction, const SgmExtras &ex)
 {
     const int lines = w + h - 1;
-    sgm_diag_kernel<4, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
-    sgm_diag_kernel<5, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
-    sgm_diag_kernel<6, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp, 1.f, 0, nullptr);
-    sgm_diag_kernel<7, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, ex.stdp,
+    sgm_diag_kernel<4, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, 1.f, 0, nullptr);
+    sgm_diag_kernel<5, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, 1.f, 0, nullptr);
+    sgm_diag_kernel<6, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction, 1.f, 0, nullptr);
+    sgm_diag_kernel<7, KPL, PF, VEC><<<lines, 32, 0, ctx->stream>>>(x0, x1, cvol, acc, h, w, D, p, direction,
                                                                     ex.final_scale, 1, ex.wta);
     ctx->launches += 4;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
 }
 
-// cvol: costs (pre-scaled, or raw with ex.stdp set); out: result; scratch: one more volume (the right->left path costs)
+// cvol: pre-scaled costs; out: result; scratch: one more volume (the right->left path costs)
 int launch_sgm(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out, float *scratch,
                int h, int w, int D, const SgmParams &p, int direction, const SgmExtras &ex)
 {

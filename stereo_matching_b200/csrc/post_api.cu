@@ -1,5 +1,6 @@
 // Entry points of the post chain (post.lua + smooth/nyu.lua): parameter defaults, the
 // three smooth.nyu.* functions as host-pointer calls, and the whole per-pair pipeline.
+#include <algorithm>
 #include <cmath>
 #include <vector>
 
@@ -76,19 +77,12 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 // 12 bytes past the last voxel, which this slack keeps inside the allocation whatever its size.
 static constexpr size_t kVolSlack = 256;
 
-// `ex` (moments of the output, arg max / arg min map) is honoured by the fused kernel only; *ex_done tells the
-// caller whether it was, so that it can fall back to the stand-alone kernels
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
-                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0,
-                    const CbcaExtras *ex = nullptr, bool *ex_done = nullptr)
+                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
 {
-    if (ex_done) *ex_done = false;
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
-    if (D <= 256 && p->L1 <= 5) {
-        // one fused pass (cbca_fused.cu)
-        if (ex_done) *ex_done = ex != nullptr;
-        return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1, ex ? *ex : CbcaExtras());
-    }
+    // one fused pass (cbca_fused.cu); arms longer than 5 take the two-pass separable kernels
+    if (D <= 256 && p->L1 <= 5) return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1);
     STEREO_TRY(ctx->post_cnt[slot].reserve((size_t)h * w * D));
     return launch_cbca_separable(ctx, x0c, x1c, vol, tmp, ctx->post_cnt[slot].as<uint8_t>(), out, h, w, D, direction,
                                  p->L1);
@@ -150,25 +144,17 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     const size_t hw = (size_t)h * w, nvox = hw * D;
     PostMaps m;
     STEREO_TRY(carve_maps(ctx, h, w, gauss_count(p), &m));
-    // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream
-    // section would serialise it
-    // Measurement knobs (scripts/post_chain_ms.py; results are the same bits either way):
-    //   STEREO_POST_SERIAL=1   both sides on one stream, so that kernel-class event times are of kernels running alone
-    //   STEREO_POST_FUSE=mask  1: -(x/std) in the SGM loads  2: volume moments in the CBCA epilogue
-    //                          4: stage arg max/min in the CBCA epilogue  8: stage arg min in the last SGM pass
-    //                          (default 15; a cleared bit runs the stand-alone kernel instead)
-    static const bool serial = [] { const char *e = getenv("STEREO_POST_SERIAL"); return e && atoi(e) == 1; }();
-    static const int fuse = [] { const char *e = getenv("STEREO_POST_FUSE"); return e ? atoi(e) : 15; }();
+    // STEREO_POST_SERIAL=1 (measurement knob), or kernel-class profiling switched on: both sides on one stream, so
+    // that event times are of kernels running alone (as stereo_pairs does with its lanes)
+    static const bool serial_env = [] { const char *e = getenv("STEREO_POST_SERIAL"); return e && atoi(e) == 1; }();
+    const bool serial = serial_env || ctx->prof.on;
     const bool fused_cbca = !p->cbca_exact && D <= 256 && p->L1 <= 5;
-    // three working volumes per side (result, SGM scratch, spare); the two-pass CBCA needs a fourth and its lengths
-    const int vols_per_side = (fused_cbca && (fuse & 1)) ? 3 : 4;
-    for (int side = 0; side < 2; ++side)
-        for (int i = 0; i < vols_per_side; ++i) STEREO_TRY(ctx->post_vol[4 * side + i].reserve(sizeof(float) * nvox + kVolSlack));
+    // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream section would
+    // serialise it.  Four working volumes per side: result, SGM scratch, and what they read.
+    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
     if (!fused_cbca && !p->cbca_exact)
         for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
-    const int moment_blocks = cbca_fused_blocks(h, w);
-    const size_t moment_doubles = std::max<size_t>(2 * 1184, 2 * (size_t)moment_blocks);
-    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 2 * moment_doubles));
+    STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * (size_t)std::max(1184, wta_moments_max_blocks(ctx))));
     if (!ctx->aux_stream) STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
     if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
     if (!ctx->ev_join) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
@@ -177,21 +163,22 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     STEREO_TRY(launch_cross(ctx, m.guide_l, h, w, p->L1, p->tau1, m.arms_l));
     STEREO_TRY(launch_cross(ctx, m.guide_r, h, w, p->L1, p->tau1, m.arms_r));
     const SgmParams sp = sgm_params(p);
+    const bool vec_ok = D % 4 == 0;              // working volumes are 256-byte aligned allocations
 
-    // The left and the right volume are independent until smooth.nyu.post: the left chain is
-    // issued on the context's stream, the right chain on a second stream.  Every stage reads `cur` and
-    // writes a free buffer; the buffer it read goes back to the free list unless it is the caller's
-    // (read-only) input.  Whatever a later stage needs from a volume besides the volume itself - its
-    // std (post.lua:146), the stage images (post.lua:125,159,178: one arg max / arg min over D each) - is
-    // computed by the kernel that WRITES the volume, and `-(x / std)` (post.lua:146,152) by the SGM
-    // kernels as they load it: per side the chain moves 2 + 11 + 2 volumes through HBM instead of 21.
+    // The left and the right volume are independent until smooth.nyu.post: the left chain is issued on the
+    // context's stream, the right chain on a second stream.  Every stage reads `cur` and writes a free buffer;
+    // the buffer it read goes back to the free list unless it is the caller's (read-only) input.
+    // Passes over a volume that only exist to look at it are merged where that costs nothing: the stage image
+    // and the std of the first CBCA's output come from ONE read (post.lua:125 + :146), the stage image of the SGM
+    // result is written by the last SGM pass (post.lua:159).  Fusing more into the producers was measured and
+    // dropped - see DESIGN.md section 4 and profiles/r02_post_chain_ab.md.
     STEREO_CUDA_CHECK(cudaEventRecord(ctx->ev_fork, ctx->stream));
-    STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
+    if (!serial) STEREO_CUDA_CHECK(cudaStreamWaitEvent(ctx->aux_stream, ctx->ev_fork, 0));
     const float *left_final = nullptr;
     for (int side = 0; side < 2; ++side) {
         StreamSwap swap(ctx, side == 0 || serial ? ctx->stream : ctx->aux_stream);
         std::vector<float *> pool;
-        for (int i = 0; i < vols_per_side; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
+        for (int i = 0; i < 4; ++i) pool.push_back(ctx->post_vol[4 * side + i].as<float>());
         const int direction = side == 0 ? -1 : 1;
         const float *input = side == 0 ? left_cost : right_cost;
         const float *cur = input;
@@ -207,39 +194,30 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             pool.pop_back();
             return dst;
         };
-        auto spare = [&]() -> float * { return fused_cbca || pool.empty() ? nullptr : pool.back(); };
-        double *moments = ctx->scratch.as<double>() + (side ? moment_doubles : 0);
-        float *stdp = m.stdp + side * 2;
-        bool have_std = false;
         // nyu_cost_agg_1 (post.lua:116-133); both volumes are called with (x0c, x1c), nyu.lua:37,39
         for (int i = 0; i < p->nyu_cost_agg_1; ++i) {
-            const bool last_iter = i == p->nyu_cost_agg_1 - 1;
             float *dst = take();
-            CbcaExtras ex;
-            bool ex_done = false;
-            if (last_iter) {
-                ex.moments = (fuse & 2) ? moments : nullptr;            // post.lua:146 lu:std() of this output
-                ex.wta = (fuse & 4) ? stages[side] : nullptr;           // post.lua:125 lu:max(2)
-                ex.take_min = 0;
-            }
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
-                                last_iter ? &ex : nullptr, &ex_done));
+            float *tmp = take();
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
+            pool.push_back(tmp);
             advance(dst);
-            if (last_iter && ex_done && ex.moments) {
-                STEREO_TRY(launch_volume_std_final(ctx, moments, moment_blocks, nvox, stdp));
-                have_std = true;
-            }
-            if (last_iter && stages[side] && !(ex_done && ex.wta)) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
         }
-        // post.lua:146-147: lu = lu / lu:std()
-        if (!have_std) STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
+        // post.lua:125 stage image (lu:max(2)) and post.lua:146-147 lu:std(): one pass when both are wanted
+        float *stdp = m.stdp + side * 2;
+        const bool aligned_cur = vec_ok && ((uintptr_t)cur % 16 == 0);
+        if (p->nyu_cost_agg_1 > 0 && stages[side] && aligned_cur) {
+            STEREO_TRY(launch_volume_std_wta(ctx, cur, hw, D, stdp, stages[side], side));
+        } else {
+            if (p->nyu_cost_agg_1 > 0 && stages[side]) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 0, stages[side]));
+            STEREO_TRY(launch_volume_std(ctx, cur, nvox, stdp, side));
+        }
+        {   // post.lua:146,152: lu = (lu / lu:std()) * -1   (without SGM: lu / lu:std())
+            float *dst = take();
+            STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, p->sgm == 1 ? 1 : 0, dst));
+            advance(dst);
+        }
         if (p->sgm == 1) {
-            // post.lua:152-155 + nyu.lua:47-75; the first sweep reads its costs as -(x / std)
-            if (!(fuse & 1)) {
-                float *dst = take();
-                STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 1, dst));
-                advance(dst);
-            }
+            // post.lua:152-155 + nyu.lua:47-75
             for (int it = 0; it < p->sgm_i; ++it) {
                 const bool last_iter = it == p->sgm_i - 1;
                 float *dst = take();
@@ -247,34 +225,24 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
                 SgmExtras ex;
                 ex.paths = p->sgm_paths == 8 ? 8 : 4;
                 ex.final_scale = ex.paths == 8 ? 0.125f : 0.25f;
-                ex.stdp = (it == 0 && (fuse & 1)) ? stdp : nullptr;
+                // post.lua:159 lu:min(2): written by the last pass when somebody wants it
                 const bool want_map = last_iter && (stages[2 + side] || p->nyu_cost_agg_2 <= 0);
-                ex.wta = (want_map && (fuse & 8)) ? final_map : nullptr;               // post.lua:159 lu:min(2)
+                ex.wta = want_map ? final_map : nullptr;
                 STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction, ex));
                 pool.push_back(tmp);
                 advance(dst);
-                if (want_map && !ex.wta) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, final_map));
                 have_final_map = want_map;
             }
             if (stages[2 + side])
                 STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[2 + side], final_map, hw, cudaMemcpyDeviceToDevice, ctx->stream));
-        } else {
-            float *dst = take();
-            STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, 0, dst));
-            advance(dst);
         }
         // nyu_cost_agg_2 (post.lua:171-186)
         for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
-            const bool last_iter = i == p->nyu_cost_agg_2 - 1;
             float *dst = take();
-            CbcaExtras ex;
-            bool ex_done = false;
-            ex.wta = (fuse & 4) ? final_map : nullptr;                  // post.lua:178,226 lu:min(2)
-            ex.take_min = 1;
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, spare(), dst, h, w, D, direction, side,
-                                last_iter ? &ex : nullptr, &ex_done));
+            float *tmp = take();
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
+            pool.push_back(tmp);
             advance(dst);
-            have_final_map = last_iter && ex_done && ex.wta;
         }
         // post.lua:226-229: disp = argmin - 1 (0-based here); the stage image of cross_agg 2 is the same map
         if (!have_final_map) STEREO_TRY(launch_wta(ctx, cur, 1, h, w, D, 1, final_map));

@@ -13,14 +13,12 @@
 // (sgm_step_coded() in sgm_step.cuh): results are bit-identical to the register-prefetch kernels.
 // D % 4 != 0 or volumes that are not 16-byte aligned take the same kernels: the bulk copies then fetch the
 // 16-byte aligned superset of each run and the lanes read 4-byte words.
-// When the costs are to be read as -(x / std) (post.lua:146,152; SgmAux::stdp), kScaleWarps more warps turn every
-// landed stage's costs into that IN shared memory (IEEE-exact division by the one divisor, exact_div.cuh: the same two fp32 results per
-// voxel as the elementwise pass they replace) and hand the stage on through a third barrier: the scanline warps, whose
-// 1 242-step dependent chains bound the kernel, never see the division.
+// Measured and dropped (profiles/r02_post_chain_ab.md): -(x / std) of post.lua:146,152 applied to the landed stages
+// by two more warps per CTA instead of by an elementwise pass - the extra hand-over per stage cost the shallow
+// pipelines of these kernels four times what the pass costs.
 #include <algorithm>
 
 #include "common.cuh"
-#include "exact_div.cuh"
 #include "sgm_step.cuh"
 #include "tc_common.cuh"
 
@@ -30,16 +28,12 @@ using namespace tc;
 namespace {
 
 constexpr int kMaxStages = 8;
-constexpr int kScaleWarps = 2;           // warps that scale landed stages (idle exit when there is nothing to scale)
-constexpr int kBarBytes = 3 * 8 * kMaxStages;      // full, empty, ready barriers
+constexpr int kBarBytes = 2 * 8 * kMaxStages;      // full and empty barriers
 
 // Byte images of sgm_prep_kernel: want[path][h][w], code[path][h][pitch] with pitch = w + 2 * pad
 struct SgmAux {
     const uint8_t *want, *code;
     int pad, pitch;
-    // costs are read as -(cvol / *stdp) when stdp is set: post.lua:146,152 `lu = (lu / lu:std()) * -1` applied on
-    // load (the same two fp32 operations per voxel, same bits) instead of by an elementwise pass over the volume
-    const float *stdp;
     // the last pass scales its sum by `final_scale` (0.25: nyu.lua:61,64 `/ 4`; 1: more paths follow) and, when
     // `wta` is set, writes the arg min over D of every pixel's result (the nyu_sgm stage image, post.lua:159)
     float final_scale;
@@ -70,7 +64,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     constexpr int kArrays = 1 + NACC;
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const bool scale_on_load = aux.stdp != nullptr;
     const int steps = kH ? w : h;
     const int n_lines = kH ? h : w;
     const int line0 = group * NW;
@@ -81,9 +74,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     const uint32_t stage_bytes = kArrays * array_bytes;
     const uint32_t s_data = smem_u32(smem);
     const uint32_t s_bar = s_data + (uint32_t)S * stage_bytes;
-    const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages, bar_ready = s_bar + 16 * kMaxStages;
-    // consumers start on a stage when it has landed, or - with scaling - when the scale warps are through with it
-    const uint32_t bar_go = scale_on_load ? bar_ready : bar_full;
+    const uint32_t bar_full = s_bar, bar_empty = s_bar + 8 * kMaxStages;
     const float *src[3] = {cvol, acc_a, acc_b};
     // unaligned volumes: results leave through a per-warp staging row (two of them, used alternately) so that a
     // warp store is a 128-byte run instead of 32 words 32 bytes apart
@@ -94,7 +85,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
         for (int i = 0; i < S; ++i) {
             mbar_init(bar_full + 8 * i, 1);
             mbar_init(bar_empty + 8 * i, (uint32_t)lines_here);
-            mbar_init(bar_ready + 8 * i, kScaleWarps);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -135,29 +125,6 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
         }
         return;
     }
-    if (warp > NW) {
-        // ---- scale warps: the cost array of every landed stage becomes -(x / std), 16 bytes per lane and turn ----
-        // (whole array, whichever part of it the runs fill: unused slot tails are never read)
-        if (!scale_on_load) return;
-        const ConstDivisor sd = make_divisor(__ldg(aux.stdp));      // IEEE-exact x / std without a divide per element
-        const int me = (warp - NW - 1) * 32 + lane;
-        for (int t = 0; t < n_stages; ++t) {
-            const int s = t % S;
-            mbar_wait(bar_full + 8 * s, (t / S) & 1);
-            float4 *arr = reinterpret_cast<float4 *>(smem + (size_t)s * stage_bytes);
-            for (uint32_t q = me; q < array_bytes / 16; q += kScaleWarps * 32) {
-                float4 v = arr[q];
-                v.x = __fmul_rn(div_exact(v.x, sd), -1.f);
-                v.y = __fmul_rn(div_exact(v.y, sd), -1.f);
-                v.z = __fmul_rn(div_exact(v.z, sd), -1.f);
-                v.w = __fmul_rn(div_exact(v.w, sd), -1.f);
-                arr[q] = v;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_ready + 8 * s);
-        }
-        return;
-    }
     if (warp >= lines_here) return;
 
     // ---- consumers: one warp per scanline, KPL consecutive disparities per lane ----
@@ -193,7 +160,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     for (int t = 0; t < n_stages; ++t) {
         const int s = t % S;
         const int g_here = min(G, steps - t * G);
-        mbar_wait(bar_go + 8 * s, (t / S) & 1);
+        mbar_wait(bar_full + 8 * s, (t / S) & 1);
         const uint8_t *stage = smem + (size_t)s * stage_bytes;
         if (!ALIGNED) {
             // byte offset of this lane's first float inside its slot at the first step of the stage: the phase of
@@ -375,7 +342,7 @@ __global__ void sgm_prep_kernel(const float *__restrict__ x0, const float *__res
 
 // both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
 template <int KPL, int NW, int DIR, bool ALIGNED>
-__global__ __launch_bounds__((NW + 1 + kScaleWarps) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
+__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
@@ -387,7 +354,7 @@ __global__ __launch_bounds__((NW + 1 + kScaleWarps) * 32) void sgm_ring_h_kernel
 
 // SD 2: a <- (a + b) + Lr (downward); SD 3: a <- (a + Lr) / 4 (upward)
 template <int SD, int KPL, int NW, int DIR, bool ALIGNED>
-__global__ __launch_bounds__((NW + 1 + kScaleWarps) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
+__global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_v_kernel(SgmAux aux, const float *__restrict__ cvol,
                                                                    float *out_a, const float *out_b, int h, int w, int D,
                                                                    SgmParams p, int G, int S)
 {
@@ -441,7 +408,6 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     uint8_t *want = buf.as<uint8_t>(), *code = want + want_bytes;
     aux.want = want;
     aux.code = code;
-    aux.stdp = ex.stdp;
     aux.final_scale = ex.final_scale;
     aux.wta = ex.wta;
     sgm_prep_kernel<<<std::min<size_t>(((size_t)h * aux.pitch + 255) / 256, 148 * 8), 256, 0, ctx->stream>>>(
@@ -453,8 +419,7 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_h.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v2.smem));
     STEREO_CUDA_CHECK(cudaFuncSetAttribute(kv3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh_v3.smem));
-    // the scale warps exist only when there is something to scale
-    const int threads = (NW + 1 + (ex.stdp ? kScaleWarps : 0)) * 32;
+    const int threads = (NW + 1) * 32;
     kh<<<dim3((h + NW - 1) / NW, 2), threads, sh_h.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_h.G, sh_h.S);
     kv2<<<(w + NW - 1) / NW, threads, sh_v2.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v2.G, sh_v2.S);
     kv3<<<(w + NW - 1) / NW, threads, sh_v3.smem, ctx->stream>>>(aux, cvol, out_a, out_b, h, w, D, p, sh_v3.G, sh_v3.S);

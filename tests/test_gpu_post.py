@@ -198,10 +198,10 @@ def test_full_chain_eight_paths_vs_oracle(ctx, scene):
         assert (out[name] == ref[name]).mean() >= 0.999, name
 
 
-def test_stage_maps_and_std_fused_into_the_producing_kernels(ctx, scene):
-    """The chain computes every stage image (arg max / arg min over D) and the volume std inside the kernel that writes
-    the volume, and -(x / std) inside the SGM loads.  Each must equal what the stand-alone entry points give on the
-    same data: WTA of the exported CBCA volume, SGM of the explicitly scaled volume, its arg min."""
+def test_stage_maps_of_the_merged_passes_equal_the_stand_alone_kernels(ctx, scene):
+    """The chain takes the stage image and the std of the first CBCA's output from ONE pass over the volume and lets
+    the last SGM pass write the arg min map of its result.  Each must equal what the stand-alone entry points give
+    on the same data: WTA of the exported CBCA volume, SGM of the explicitly scaled volume, its arg min."""
     l_img, r_img = ctx.guide_image(scene["ld"]), ctx.guide_image(scene["rd"])
     out = ctx.post(scene["lv"], scene["rv"], scene["ld"], scene["rd"])
     lu, ru = ctx.nyu_cross_agg(l_img, r_img, scene["lv"], scene["rv"], 1)

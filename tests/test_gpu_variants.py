@@ -92,13 +92,12 @@ np.savez(sys.argv[2], **out)
 """
 
 
-def test_cbca_ring_and_global_load_kernels_agree_bit_for_bit(tmp_path):
-    """The fused CBCA kernel fed by bulk copies through a shared-memory ring of row slots (default for 16-byte aligned
-    volumes) against the same kernel with per-thread global loads (STEREO_CBCA_KERNEL=1): the same additions in the
-    same order, so the bits must agree; bands of every length, images narrower than a block's window.  Both are
-    checked against the C restatement in test_gpu_post.py."""
+def test_cbca_occupancy_variants_agree_bit_for_bit(tmp_path):
+    """The fused CBCA kernel compiled for three (default) and four (STEREO_CBCA_OCC=4) resident blocks per SM: the same
+    additions in the same order, so the bits must agree; bands of every length, images narrower than a block's window.
+    The default is checked against the C restatement in test_gpu_post.py."""
     maps = {}
-    for name, env in (("ring", {}), ("ldg", {"STEREO_CBCA_KERNEL": "1"})):
+    for name, env in (("occ3", {}), ("occ4", {"STEREO_CBCA_OCC": "4"})):
         e = dict(os.environ)
         e.update(env)
         out = tmp_path / (name + ".npz")
@@ -106,9 +105,9 @@ def test_cbca_ring_and_global_load_kernels_agree_bit_for_bit(tmp_path):
                            timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         maps[name] = np.load(out)
-    assert sorted(maps["ring"].files) == sorted(maps["ldg"].files) and len(maps["ring"].files) == 8
-    for k in maps["ring"].files:
-        assert np.array_equal(maps["ring"][k], maps["ldg"][k]), k
+    assert sorted(maps["occ3"].files) == sorted(maps["occ4"].files) and len(maps["occ3"].files) == 8
+    for k in maps["occ3"].files:
+        assert np.array_equal(maps["occ3"][k], maps["occ4"][k]), k
 
 
 BASE_CHILD = r"""
