@@ -22,7 +22,7 @@ def run_bench(*args, timeout=900):
 
 def test_reference_arm_on_host_cores():
     """`--impl reference` needs no GPU: the oracle port on a bounded sample of the same workload."""
-    d = run_bench("--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-rows", "12")
+    d = run_bench("--impl", "reference", "--steps", "1", "--warmup", "0", "--ref-rows", "12")
     assert BASE_KEYS <= set(d) and d["impl"] == "reference"
     assert d["unit"] == "pairs/s" and d["higher_is_better"] is True and d["value"] > 0
     assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
