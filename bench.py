@@ -590,6 +590,475 @@ def run_b200(args):
     return 0
 
 
+# =============================================================================================
+# --config base_model | post_chain | train_dp : the other BASELINE.json configurations as the headline
+# =============================================================================================
+class Harness:
+    """One process per GPU: device, stream, barrier and max-over-ranks timing shared by the configurations."""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank, self.local_rank, self.world = dist_env()
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
+        torch.cuda.set_device(self.local_rank)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+        self.dev = torch.device("cuda", self.local_rank)
+        self.stream = torch.cuda.Stream()
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed_steps(self, step, steps, warmup):
+        """W untimed + K timed calls of `step` on self.stream: (ms of the K steps, max over ranks; clock summary)."""
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            for _ in range(warmup):
+                step()
+            self.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with ClockSampler(self.local_rank) as clocks:
+                e0.record(self.stream)
+                for _ in range(steps):
+                    step()
+                e1.record(self.stream)
+                self.barrier()
+        return self.max_over_ranks(e0.elapsed_time(e1)), clocks.summary()
+
+    def timed_host(self, step, steps, warmup):
+        """The same for calls that synchronise themselves (host-pointer entry points): wall clock between barriers."""
+        for _ in range(warmup):
+            step()
+        self.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            step()
+        self.barrier()
+        return self.max_over_ranks(time.perf_counter() - t0)
+
+    def finish(self, line):
+        if self.rank == 0 and line is not None:
+            print(json.dumps(line))
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+        return 0
+
+
+def _line(args, hz, metric, unit, value, ms, dtype, workload, e2e, launches, clocks, roofline, cpu, extra, scaling="weak"):
+    return {"metric": metric, "value": value, "unit": unit, "n_gpus": hz.world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": dtype, "data": "synthetic", "config": workload, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extra": extra}
+
+
+def run_base_model(args):
+    """BASELINE.json configs[2]: base_model (nine 5x5 layers, 37x37 receptive field) on 375x1242 pairs, D=228:
+    trunk on tcgen05 + fused correlation / WTA + LR check, pairs sharded over the ranks, no collective."""
+    from oracle import stereo_oracle as so
+    from stereo_matching_b200 import _lib, synth
+    from stereo_matching_b200.models.model import base_model
+    if args.impl == "reference":
+        return run_reference_generic(args, "base_model")
+    hz = Harness()
+    torch = hz.torch
+    prec = {"fp32": _lib.PREC_FP32, "bf16x3": _lib.PREC_BF16X3, "bf16": _lib.PREC_BF16}[args.precision]
+    model = base_model((None, None, 3), device=hz.local_rank, precision=prec)
+    layers = synth.make_base_model_weights()
+    model.set_layers(layers)
+    ctx = model.context
+    ctx.set_stream(hz.stream.cuda_stream)
+    n = args.pairs
+    left, right, gt = synthetic_batch(n)
+    d_left, d_right = torch.from_numpy(left).to(hz.dev), torch.from_numpy(right).to(hz.dev)
+    d_ld = torch.empty((n, H, W), dtype=torch.uint8, device=hz.dev)
+    d_rd, d_out = torch.empty_like(d_ld), torch.empty_like(d_ld)
+
+    def step():
+        ctx.pairs_dev(model.net, d_left.data_ptr(), d_right.data_ptr(), n, H, W, D, prec, d_ld.data_ptr(), d_rd.data_ptr(),
+                      d_out.data_ptr())
+
+    launches0 = ctx.launch_count
+    ms, clocks = hz.timed_steps(step, args.steps, args.warmup)
+    launches = (ctx.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    value = hz.world * n * args.steps / (ms / 1e3)
+    with torch.cuda.stream(hz.stream):
+        ctx.profile_enable(True)
+        step()
+        torch.cuda.synchronize()
+        prof = ctx.profile_read()
+        ctx.profile_enable(False)
+    # end to end: host images in, maps out
+    p_left, p_right = torch.from_numpy(left).pin_memory(), torch.from_numpy(right).pin_memory()
+    p_maps = [torch.empty((n, H, W), dtype=torch.uint8).pin_memory() for _ in range(3)]
+    lib = _lib.load()
+
+    def step_host():
+        _lib.check(lib.stereo_pairs(ctx._h, model.net, p_left.data_ptr(), p_right.data_ptr(), n, H, W, D, prec,
+                                    p_maps[0].data_ptr(), p_maps[1].data_ptr(), p_maps[2].data_ptr(), None, None))
+
+    e2e_s = hz.timed_host(step_host, args.steps, min(args.warmup, 3))
+    e2e = {"value": hz.world * n * args.steps / e2e_s, "unit": UNIT,
+           "h2d_bytes_per_step": int(hz.world * 2 * n * H * W * 3), "d2h_bytes_per_step": int(hz.world * 3 * n * H * W)}
+    assert np.array_equal(p_maps[0][0].numpy(), d_ld[0].cpu().numpy()), "host and device entry points disagree"
+    if hz.rank != 0:
+        return hz.finish(None)
+    pk = peaks()
+    conv_ms, conv_launches = prof["conv"]
+    flops_pair = 1191.75e9 - 2 * 2.0 * 25 * 3 * 32 * (H + 32) * (W + 32)       # layers 2-9 of both images (layer 1 is the fp32 kernel)
+    tflops = flops_pair * n / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+    total = sum(v[0] for v in prof.values())
+    nm = ncu_metrics("conv_tcr_kernel") or {}
+    roofline = {"kernel": "conv_tcr_kernel<5,*,*> (tcgen05, base_model layers 2-9, every input row multiplied once)",
+                "bound": "tensor", "achieved": tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": tflops / pk["bf16_tflops_sustained"], "traffic": nm.get("dram_bytes"),
+                "tensor_pipe_active_ncu": nm.get("tensor_pipe_active"), "mma_passes": 3 if args.precision == "bf16x3" else 1,
+                "avg_launch_ms": conv_ms / conv_launches if conv_launches else None, "share_of_step": conv_ms / total if total else None,
+                "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
+                "note": "algorithmic FLOPs of the eight 5x5 layers counted once whatever the operand split / CUDA-event "
+                        "time of the kernel class in a pass with the pairs one at a time"}
+    cpu = None
+    if not args.no_cpu_baseline:
+        cpu = cpu_baseline_trunk("win37_dep9", 37, layers, min(args.cpu_rows, 16))
+    extra = {"kernel_ms_per_step": {k: v[0] for k, v in prof.items() if v[1]},
+             "three_px_error_pair0": so.three_pixel_error(d_ld[0].cpu().numpy(), gt[0]),
+             "weights": "seeded synthetic (the reference ships none for base_model)"}
+    workload = {"workload": f"configs[2]: base_model (win37_dep9), {n} synthetic {H}x{W} pairs per GPU per step, fused "
+                            f"correlation+WTA+LR check, D={D}", "pairs_per_gpu": n, "height": H, "width": W, "disp_range": D,
+                "precision": args.precision, "parallelism": f"batch-sharded x{hz.world}, no collective",
+                "l2": "activations of one pair (> 1 GB) exceed the 126 MB L2; no explicit flush"}
+    dtype = {"fp32": "f32", "bf16x3": "bf16x3 (fp32 accumulate)", "bf16": "bf16"}[args.precision]
+    return hz.finish(_line(args, hz, "pairs/sec at 375x1242, D=228 (base_model trunk + fused correlation/WTA + LR check)", UNIT,
+                           value, ms, dtype, workload, e2e, launches, clocks, roofline, cpu, extra))
+
+
+def cpu_baseline_trunk(net, patch, layers, rows):
+    """The oracle port (torch-CPU conv + per-disparity numpy loop) on the first `rows` rows of pair 1000."""
+    import torch
+    from oracle import stereo_oracle as so
+    from stereo_matching_b200 import synth
+    torch.set_num_threads(os.cpu_count() or 1)
+    l, r, _ = synth.make_pair(1000, H, W, D)
+    t0 = time.perf_counter()
+    so.infer_pair(l[:rows], r[:rows], layers, net, patch, D, np.float32)
+    sec = time.perf_counter() - t0
+    return {"value": (rows / H) / sec, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"oracle/stereo_oracle.infer_pair fp32 ({net}) on the first {rows} of {H} rows of one pair, D={D}: {sec:.1f} s; "
+                      f"pairs/s scaled by rows/{H}"}
+
+
+def run_reference_generic(args, which):
+    """--impl reference for the other configurations: the oracle port of that path on the host cores (rank 0)."""
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    if which == "base_model":
+        from stereo_matching_b200 import synth
+        layers = synth.make_base_model_weights()
+        rows = min(args.ref_rows, 32)
+        cpu_baseline_trunk("win37_dep9", 37, layers, 8)
+        runs = [cpu_baseline_trunk("win37_dep9", 37, layers, rows) for _ in range(args.steps)]
+        metric = "pairs/sec at 375x1242, D=228 (base_model trunk + fused correlation/WTA + LR check)"
+        unit = UNIT
+    elif which == "post_chain":
+        runs = [cpu_baseline_post(min(args.ref_rows, 96), args.sgm_paths) for _ in range(args.steps)]
+        metric = "pairs/sec at 375x1242, D=228 (post.lua chain: CBCA -> SGM -> CBCA -> LR/fill/subpixel/median/bilateral)"
+        unit = UNIT
+    else:
+        runs = [cpu_baseline_train() for _ in range(args.steps)]
+        metric = "patches/sec (patch training step, B=128 per GPU, 9x9 patches, D=201)"
+        unit = "patches/s"
+    value = len(runs) / sum(1.0 / r["value"] for r in runs)
+    cb = dict(runs[-1])
+    cb["value"] = value
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 / value * (128 if which == "train_dp" else 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{which}: the CPU restatement of that path on this box's host cores, bounded sample per step"},
+            "cpu_baseline": cb, "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+_POST_VOLUMES = {}
+
+
+def cpu_baseline_post(rows, paths=4, volumes=None):
+    """oracle/post_oracle.post_chain (C, OpenMP) on the first `rows` rows of pair 1000's volumes."""
+    from oracle import post_oracle as po
+    if volumes is None:
+        if "v" not in _POST_VOLUMES:
+            # no GPU on this arm: volumes of the sample rows from the CPU restatement of the inference path
+            from oracle import stereo_oracle as so
+            from stereo_matching_b200 import checkpoint, synth
+            l, r, _ = synth.make_pair(1000, H, W, D)
+            ref = so.infer_pair(l[:rows], r[:rows], checkpoint.load_net_weights(GOLDEN_CKPT), "win9_dep9", 9, D, np.float32,
+                                banded=True)
+            _POST_VOLUMES["v"] = tuple(np.ascontiguousarray(ref[k], dtype=np.float32 if "cost" in k else np.uint8)
+                                       for k in ("left_cost", "right_cost", "left_disp", "right_disp"))
+        volumes = _POST_VOLUMES["v"]
+    lv, rv, ld, rd = (v[:rows] for v in volumes)
+    t0 = time.perf_counter()
+    po.post_chain(lv, rv, ld, rd, sgm_paths=paths)
+    sec = time.perf_counter() - t0
+    return {"value": (rows / H) / sec, "unit": UNIT, "cores": po.num_threads(), "kind": "port",
+            "sample": f"oracle/post_oracle.post_chain (C, OpenMP, {paths}-path SGM) on the first {rows} of {H} rows of one pair's "
+                      f"volumes, D={D}: {sec:.1f} s; pairs/s scaled by rows/{H}"}
+
+
+def run_post_chain(args):
+    """BASELINE.json configs[3]: the post.lua chain (CBCA -> SGM -> CBCA -> LR / fills / sub-pixel / median / bilateral)
+    on full-size volumes resident in HBM, all eight stage images written, pairs sharded over the ranks."""
+    from oracle import stereo_oracle as so
+    from stereo_matching_b200 import _lib
+    from stereo_matching_b200.models.model import base_model_ws_9
+    if args.impl == "reference":
+        return run_reference_generic(args, "post_chain")
+    hz = Harness()
+    torch = hz.torch
+    model = base_model_ws_9((None, None, 3), device=hz.local_rank)
+    model.load_checkpoint(GOLDEN_CKPT, verbose=False)
+    ctx = model.context
+    ctx.set_stream(hz.stream.cuda_stream)
+    n = args.pairs
+    left, right, gt = synthetic_batch(2)
+    params = _lib.default_post_params()
+    params.sgm_paths = args.sgm_paths
+    # two distinct pairs' volumes stay resident (2 x 850 MB); the n pairs of a step alternate between them
+    vols = []
+    with torch.cuda.stream(hz.stream):
+        for i in range(2):
+            lv = torch.empty((H, W, D), dtype=torch.float32, device=hz.dev)
+            rv = torch.empty_like(lv)
+            ld = torch.empty((H, W), dtype=torch.uint8, device=hz.dev)
+            rd = torch.empty_like(ld)
+            dl, dr = torch.from_numpy(left[i]).to(hz.dev), torch.from_numpy(right[i]).to(hz.dev)
+            ctx.pairs_dev(model.net, dl.data_ptr(), dr.data_ptr(), 1, H, W, D, model.precision, ld.data_ptr(), rd.data_ptr(),
+                          None, lv.data_ptr(), rv.data_ptr())
+            vols.append((lv, rv, ld, rd))
+        torch.cuda.synchronize()
+    d_stages = torch.empty((8, H, W), dtype=torch.uint8, device=hz.dev)
+    ptrs = [d_stages[i].data_ptr() for i in range(8)]
+
+    def step():
+        for i in range(n):
+            lv, rv, ld, rd = vols[i & 1]
+            ctx.post_dev(lv.data_ptr(), rv.data_ptr(), ld.data_ptr(), rd.data_ptr(), H, W, D, ptrs, params=params)
+
+    launches0 = ctx.launch_count
+    ms, clocks = hz.timed_steps(step, args.steps, args.warmup)
+    launches = (ctx.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    value = hz.world * n * args.steps / (ms / 1e3)
+    final0 = None
+    with torch.cuda.stream(hz.stream):
+        lv, rv, ld, rd = vols[0]
+        ctx.post_dev(lv.data_ptr(), rv.data_ptr(), ld.data_ptr(), rd.data_ptr(), H, W, D, ptrs, params=params)
+        torch.cuda.synchronize()
+        final0 = d_stages[6].cpu().numpy()
+        ctx.profile_enable(True)                    # kernel classes: both sides on one stream, every kernel alone
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pe0.record(hz.stream)
+        ctx.post_dev(lv.data_ptr(), rv.data_ptr(), ld.data_ptr(), rd.data_ptr(), H, W, D, ptrs, params=params)
+        pe1.record(hz.stream)
+        torch.cuda.synchronize()
+        prof = ctx.profile_read()
+        serial_ms = pe0.elapsed_time(pe1)
+        ctx.profile_enable(False)
+    # end to end through the reference-facing call: the two volumes and the two guide maps come from HOST memory
+    # (post.lua reads them from the .bin / .png files inference.py wrote), the stage maps go back
+    hv = [t.cpu().pin_memory() for t in vols[0]]
+    h_stages = {name: torch.empty((H, W), dtype=torch.uint8).pin_memory() for name in _lib.STAGE_NAMES}
+    h_final = torch.empty((H, W), dtype=torch.float32).pin_memory()
+    import ctypes
+    sp = (ctypes.c_void_p * 8)(*[h_stages[k].data_ptr() for k in _lib.STAGE_NAMES])
+    lib = _lib.load()
+    e2e_pairs = max(1, min(n, 2))
+
+    def step_host():
+        for _ in range(e2e_pairs):
+            _lib.check(lib.stereo_post(ctx._h, hv[0].data_ptr(), hv[1].data_ptr(), hv[2].data_ptr(), hv[3].data_ptr(), H, W, D,
+                                       ctypes.byref(params), sp, h_final.data_ptr()))
+
+    e2e_s = hz.timed_host(step_host, args.steps, 1)
+    vol_bytes = 4.0 * H * W * D
+    e2e = {"value": hz.world * e2e_pairs * args.steps / e2e_s, "unit": UNIT,
+           "h2d_bytes_per_step": int(hz.world * e2e_pairs * (2 * vol_bytes + 2 * H * W)),
+           "d2h_bytes_per_step": int(hz.world * e2e_pairs * (8 * H * W + 4 * H * W)),
+           "note": "stereo_post with host volumes: 850 MB of H2D per pair inside the timed region (what post.lua reads from "
+                   "disk); extra.full_pipeline is the chain fed by the trunk on the device instead"}
+    assert np.array_equal(h_stages["nyu_post"].numpy(), final0), "host and device entry points disagree"
+    if hz.rank != 0:
+        return hz.finish(None)
+    pk = peaks()
+    classes = {k: v[0] for k, v in prof.items() if v[1]}
+    # algorithmic bytes (SURVEY 8(d)): CBCA 2 x vol per call (4 calls), SGM 2 x vol per volume (2 volumes)
+    alg = {"cbca": 2 * vol_bytes * 4, "sgm": 2 * vol_bytes * 2}
+    dom = max(alg, key=lambda k: classes.get(k, 0.0))
+    gbs = alg[dom] / (classes[dom] / 1e3) / 1e9
+    nm = ncu_metrics("sgm_ring_h_kernel" if dom == "sgm" else "cbca_fused_kernel") or {}
+    roofline = {"kernel": {"sgm": "sgm_ring_h_kernel + sgm_ring_v_kernel<2,3> (4-path SGM of one volume: 3 launches)",
+                           "cbca": "cbca_fused_kernel (one adcensus.cbca call)"}[dom] + (" + sgm_diag_kernel x4" if args.sgm_paths == 8 and dom == "sgm" else ""),
+                "bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                "traffic": nm.get("dram_bytes"), "peak_source": pk["source"] + " copy bandwidth",
+                "launch_groups": 2 if dom == "sgm" else 4, "class_ms_per_pair": classes[dom],
+                "algorithmic_bytes_per_launch_group": alg[dom] / (2 if dom == "sgm" else 4),
+                "other": {k: {"gbs_algorithmic": alg[k] / (classes[k] / 1e3) / 1e9, "frac": alg[k] / (classes[k] / 1e3) / 1e9 / pk["hbm_gbs"],
+                              "class_ms_per_pair": classes[k]} for k in alg if k != dom and k in classes},
+                "note": "algorithmic bytes = read + write of the volume per call (SURVEY 8(d)); kernel-class time from a pass with "
+                        "both sides of the chain on one stream (every kernel alone on the GPU)"}
+    cpu = None
+    if not args.no_cpu_baseline:
+        cpu = cpu_baseline_post(48, args.sgm_paths, tuple(t.cpu().numpy() for t in vols[0]))
+    # whole pipeline from images, volumes never leave the device
+    with torch.cuda.stream(hz.stream):
+        n_full = 4
+        d_l4 = torch.from_numpy(np.repeat(left[:1], n_full, 0)).to(hz.dev)
+        d_r4 = torch.from_numpy(np.repeat(right[:1], n_full, 0)).to(hz.dev)
+        d_np = torch.empty((n_full, H, W), dtype=torch.uint8, device=hz.dev)
+        ctx.pairs_post_dev(model.net, d_l4.data_ptr(), d_r4.data_ptr(), 1, H, W, D, model.precision, params, d_np.data_ptr())
+        torch.cuda.synchronize()
+        fe0, fe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fe0.record(hz.stream)
+        ctx.pairs_post_dev(model.net, d_l4.data_ptr(), d_r4.data_ptr(), n_full, H, W, D, model.precision, params, d_np.data_ptr())
+        fe1.record(hz.stream)
+        torch.cuda.synchronize()
+        full_ms = fe0.elapsed_time(fe1) / n_full
+    extra = {"kernel_class_ms_per_pair": classes, "serial_ms_per_pair": serial_ms,
+             "three_px_error_pair0_after_post": so.three_pixel_error(final0, gt[0]),
+             "three_px_error_pair0_raw_wta": so.three_pixel_error(vols[0][2].cpu().numpy(), gt[0]),
+             "full_pipeline": {"workload": "stereo_pairs_post_dev: trunk + materialised volumes + post chain per pair, final maps only",
+                               "ms_per_pair": full_ms, "pairs_per_s": 1e3 / full_ms},
+             "sgm_paths": args.sgm_paths,
+             "sgm_paths_note": ("4-path SGM as in the reference (nyu.lua:59-64)" if args.sgm_paths == 4 else
+                                "8-path SGM: an extension with NO counterpart in the reference; not a parity figure")}
+    workload = {"workload": f"configs[3]: post.lua chain ({args.sgm_paths}-path SGM) on {n} pairs per GPU per step, volumes of two "
+                            f"synthetic {H}x{W} pairs resident in HBM, D={D}, all eight stage images",
+                "pairs_per_gpu": n, "height": H, "width": W, "disp_range": D, "sgm_paths": args.sgm_paths,
+                "parallelism": f"batch-sharded x{hz.world}, no collective",
+                "l2": "the two volumes of a pair (850 MB) exceed the 126 MB L2; no explicit flush"}
+    return hz.finish(_line(args, hz, "pairs/sec at 375x1242, D=228 (post.lua chain: CBCA -> SGM -> CBCA -> LR/fill/subpixel/median/bilateral)",
+                           UNIT, value, ms, "f32", workload, e2e, launches, clocks, roofline, cpu, extra))
+
+
+def cpu_baseline_train(B=128, Dt=201):
+    import torch
+    from oracle import train_oracle as to
+    torch.set_num_threads(os.cpu_count() or 1)
+    rng = np.random.default_rng(0)
+    params, stats = to.init_params("win9_dep9", 0)
+    l = rng.standard_normal((B, 9, 9, 3)).astype(np.float32)
+    r = rng.standard_normal((B, 9, 9 + Dt - 1, 3)).astype(np.float32)
+    t = to.soft_labels(B, Dt)
+    to.forward_backward(params, stats.copy(), l[:8], r[:8], t[:8], dtype=torch.float32)
+    t0 = time.perf_counter()
+    _, _, g, _ = to.forward_backward(params, stats.copy(), l, r, t, dtype=torch.float32)
+    to.adam_step(params.astype(np.float64), g, np.zeros_like(g), np.zeros_like(g), 1, 1e-3)
+    sec = time.perf_counter() - t0
+    return {"value": B / sec, "unit": "patches/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"oracle/train_oracle.forward_backward (torch autograd, float32) + adam_step on one batch of {B} patches, D={Dt}: {sec:.2f} s"}
+
+
+def run_train_dp(args):
+    """BASELINE.json configs[4]: patch training of base_model_ws_9 (9x9 patches, 201-disparity soft-label
+    cross-entropy, Adam), data parallel: every rank runs forward/backward on its own 128 patches, the flat gradient
+    array (113 088 floats) is averaged with ONE NCCL all-reduce, every rank applies the same Adam step."""
+    from stereo_matching_b200 import _lib
+    from stereo_matching_b200 import train as b200train
+    if args.impl == "reference":
+        return run_reference_generic(args, "train_dp")
+    hz = Harness()
+    torch = hz.torch
+    B, Dt = 128, 201
+    ctx = _lib.Context(hz.local_rank)
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, Dt)
+    tr.set_state(*b200train.init_state("win9_dep9", 0))
+    rng = np.random.default_rng(100 + hz.rank)
+    tl = torch.from_numpy(rng.standard_normal((B, 9, 9, 3)).astype(np.float32)).pin_memory()
+    trr = torch.from_numpy(rng.standard_normal((B, 9, 9 + Dt - 1, 3)).astype(np.float32)).pin_memory()
+    tt = torch.from_numpy(b200train.soft_labels(B, Dt)).pin_memory()
+    gview = b200train.DeviceGradView(tr, hz.local_rank).tensor
+    loss = [0.0]
+
+    def step():
+        # the trainer's own entry points: host patches in (H2D inside), loss out (D2H inside), then the all-reduce
+        # of the gradient array in place on the device and Adam
+        loss[0], _, _ = tr.forward_backward(tl.numpy(), trr.numpy(), tt.numpy())
+        if hz.world > 1:
+            b200train.average_gradients(gview, hz.world)
+            torch.cuda.synchronize()
+        tr.apply(1e-3)
+
+    launches0 = ctx.launch_count
+    with ClockSampler(hz.local_rank) as sampler:
+        sec = hz.timed_host(step, args.steps, args.warmup)
+    clocks = sampler.summary()
+    launches = (ctx.launch_count - launches0) * args.steps // (args.steps + args.warmup)
+    value = hz.world * B * args.steps / sec
+    # the all-reduce alone (CUDA events on the current stream, which is the one NCCL is enqueued on)
+    ar_us = None
+    if hz.world > 1:
+        for _ in range(5):
+            hz.dist.all_reduce(gview)
+        torch.cuda.synchronize()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(50):
+            hz.dist.all_reduce(gview)
+        a1.record()
+        torch.cuda.synchronize()
+        ar_us = hz.max_over_ranks(a0.elapsed_time(a1) / 50 * 1e3)
+    st = tr.get_state()
+    chk = torch.tensor([float(np.abs(st["params"]).sum())], dtype=torch.float64, device=hz.dev)
+    same = True
+    if hz.world > 1:
+        lo, hi = chk.clone(), chk.clone()
+        hz.dist.all_reduce(lo, op=hz.dist.ReduceOp.MIN)
+        hz.dist.all_reduce(hi, op=hz.dist.ReduceOp.MAX)
+        same = bool(lo.item() == hi.item())
+    if hz.rank != 0:
+        tr.close()
+        return hz.finish(None)
+    pk = peaks()
+    flops_step = 54.9e9                       # forward + backward of both towers at B = 128 (DESIGN.md section 7)
+    tflops = flops_step * args.steps / sec / 1e12
+    roofline = {"kernel": "train.cu weight-gradient / conv_ffma forward and backward-data kernels (fp32, CUDA cores)",
+                "bound": "tensor", "achieved": tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                "frac": tflops / pk["bf16_tflops_sustained"], "traffic": None,
+                "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
+                "note": "the training contractions run in fp32 on the CUDA cores (not yet on tcgen05): the fraction of the "
+                        "tensor peak says how far that is from what the hardware offers; 54.9 algorithmic GFLOP per step "
+                        "of 128 patches / wall time of the whole step (host patches in, loss out)"}
+    cpu = None if args.no_cpu_baseline else cpu_baseline_train(B, Dt)
+    e2e = {"value": value, "unit": "patches/s",
+           "h2d_bytes_per_step": int(hz.world * 4 * (B * 81 * 3 + B * 9 * (9 + Dt - 1) * 3 + B * Dt)),
+           "d2h_bytes_per_step": int(hz.world * 8),
+           "note": "the trainer is fed from host memory by design (the reference's data handler is host code): value and e2e "
+                   "are the same measurement"}
+    extra = {"loss_last_step": loss[0], "allreduce_us": ar_us, "allreduce_floats": int(tr.n_params),
+             "ranks_hold_identical_parameters": same, "ms_per_step": 1e3 * sec / args.steps}
+    workload = {"workload": f"configs[4]: base_model_ws_9 patch training, B={B} patches per GPU per step, 9x9 / 9x209 patches, "
+                            f"D={Dt} soft labels, Adam; data parallel x{hz.world} with one NCCL all-reduce of {tr.n_params} gradients",
+                "batch_per_gpu": B, "disp_range": Dt, "parallelism": f"data parallel x{hz.world}, gradient all-reduce",
+                "l2": "per-step working set (~60 MB of activations) fits the L2; every step uploads fresh host patches"}
+    tr.close()
+    return hz.finish(_line(args, hz, "patches/sec (patch training step, B=128 per GPU, 9x9 patches, D=201)", "patches/s", value,
+                           1e3 * sec, "f32", workload, e2e, launches, clocks, roofline, cpu, extra))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)

@@ -2,7 +2,7 @@
 
 Every configuration runs scripts/post_chain_ms.py in its own process (the library reads its measurement knobs once):
 STEREO_POST_SERIAL=1 puts both sides on one stream so that the kernel-class times are of kernels running alone,
-STEREO_CBCA_OCC=4 takes the CBCA kernel compiled for four resident blocks per SM.  (The fusion knobs this script
+STEREO_CBCA_KERNEL selects the form of the fused CBCA kernel (csrc/cbca_fused.cu).  (The fusion knobs this script
 was written for - STEREO_POST_FUSE, the bulk-copy ring CBCA - were measured and removed with the code they
 switched: profiles/r02_post_chain_ab.md.)"""
 import json
@@ -15,8 +15,10 @@ D = sys.argv[1] if len(sys.argv) > 1 else "228"
 CONFIGS = [
     ("default (two streams)", {}),
     ("serial", {"STEREO_POST_SERIAL": "1"}),
-    ("serial, CBCA for four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_OCC": "4"}),
-    ("two streams, CBCA for four blocks per SM", {"STEREO_CBCA_OCC": "4"}),
+    ("serial, CBCA round-1 form", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "1"}),
+    ("serial, CBCA round-1 form, four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "2"}),
+    ("serial, CBCA pipelined, four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "3"}),
+    ("two streams, CBCA round-1 form", {"STEREO_CBCA_KERNEL": "1"}),
 ]
 for name, env in CONFIGS:
     e = dict(os.environ)

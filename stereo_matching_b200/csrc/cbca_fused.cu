@@ -65,7 +65,11 @@ __device__ __forceinline__ void add_if(float &sum, int &cnt, float v, int c, uin
         : "+f"(sum), "+r"(cnt) : "f"(v), "r"(c), "r"(mask), "r"(bit));
 }
 
-template <int MIN_BLOCKS>
+// VARIANT 0: the row loop loads a row and uses it at once (round 1).  VARIANT 1 (default): software pipeline - the
+// ten costs and the four arm records of row r + 1 are requested right after the row sums of row r have consumed
+// the registers of the previous request, so their latency runs under the column sums, the division and the store
+// of output row r - 4 instead of in front of the next row sums.  Same additions in the same order.
+template <int MIN_BLOCKS, int VARIANT>
 __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                          int pitch, const float *__restrict__ vol, float *__restrict__ out,
                                                          int h, int w, int D, int direction, int rows_per_band)
@@ -76,7 +80,7 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
     const int y0 = blockIdx.y * rows_per_band, y1 = min(h, y0 + rows_per_band);
     const int shift = d * direction;
 
-    int offs[kFN];                           // element offsets of the 12 columns inside a row (clamped: loads stay in the row)
+    int offs[kFN];                           // element offsets of the 10 columns inside a row (clamped: loads stay in the row)
 #pragma unroll
     for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * D + d;
     bool pix_ok[kFB], match_ok[kFB];
@@ -97,6 +101,22 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
         for (int i = 0; i < kFB; ++i) { hs[u][i] = 0.f; hc[u][i] = 0; }
     const int row_elems = w * D;
 
+    // costs and arm records of the row whose sums come next (VARIANT 1: requested one iteration ahead)
+    float v[kFN];
+    uint32_t own_n[kFB], oth_n[kFB];
+    auto request_row = [&](int r) {
+        const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
+#pragma unroll
+        for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+#pragma unroll
+        for (int i = 0; i < kFB; ++i) {
+            own_n[i] = __ldg(rec0 + (rbase + xb + i));
+            oth_n[i] = __ldg(rec1 + (rbase + xm[i]));
+        }
+    };
+    const int r_first = max(0, y0 - kFR), r_end = min(h, y1 + kFR);       // rows whose sums are formed: [r_first, r_end)
+    if (VARIANT == 1) request_row(r_first);
+
     for (int base = y0 - kFR; base < y1 + kFR; base += kFW) {
 #pragma unroll
         for (int u = 0; u < kFW; ++u) {
@@ -104,16 +124,10 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
             if (r >= y1 + kFR) break;
             if (r >= 0 && r < h) {
                 // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
-                const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
-                float v[kFN];
-#pragma unroll
-                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
-                uint32_t own_r[kFB];
-#pragma unroll
-                for (int i = 0; i < kFB; ++i) own_r[i] = __ldg(rec0 + (rbase + xb + i));
+                if (VARIANT == 0) request_row(r);
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
-                    const uint32_t cm = own_r[i] & __ldg(rec1 + (rbase + xm[i]));   // both arms reach the column
+                    const uint32_t cm = own_n[i] & oth_n[i];         // both arms reach the column
                     float sum = 0.f;
 #pragma unroll
                     for (int jj = -kFR; jj <= kFR; ++jj) {           // columns x-R .. x+R, ascending
@@ -124,6 +138,7 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
                     hs[u][i] = match_ok[i] ? sum : v[kFR + i];
                     hc[u][i] = match_ok[i] ? __popc(cm & 0xffu) + 1 : 0;
                 }
+                if (VARIANT == 1 && r + 1 < r_end) request_row(r + 1);
             }
             const int y = r - kFR;
             if (y >= y0 && y < y1) {
@@ -175,11 +190,14 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     const int nt = (D + 31) / 32 * 32;
     const int bands = std::max(1, (h + 62) / 63);
     const int rows_per_band = (h + bands - 1) / bands;
-    // STEREO_CBCA_OCC=4: the same kernel compiled for four resident blocks per SM (64 registers, a few spills)
-    static const bool occ4 = [] { const char *e = getenv("STEREO_CBCA_OCC"); return e && atoi(e) == 4; }();
+    // STEREO_CBCA_KERNEL=1 keeps the round-1 form (three blocks per SM, every row loaded and used at once) as the
+    // cross-check; STEREO_CBCA_KERNEL=2: that form compiled for four blocks per SM (64 registers, a few spills)
+    static const int variant = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e ? atoi(e) : 0; }();
     const dim3 grid((w + kFB - 1) / kFB, bands);
-    if (occ4) cbca_fused_kernel<4><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
-    else cbca_fused_kernel<3><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    if (variant == 1) cbca_fused_kernel<3, 0><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    else if (variant == 2) cbca_fused_kernel<4, 0><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    else if (variant == 3) cbca_fused_kernel<4, 1><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    else cbca_fused_kernel<3, 1><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;

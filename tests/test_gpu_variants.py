@@ -92,12 +92,13 @@ np.savez(sys.argv[2], **out)
 """
 
 
-def test_cbca_occupancy_variants_agree_bit_for_bit(tmp_path):
-    """The fused CBCA kernel compiled for three (default) and four (STEREO_CBCA_OCC=4) resident blocks per SM: the same
-    additions in the same order, so the bits must agree; bands of every length, images narrower than a block's window.
-    The default is checked against the C restatement in test_gpu_post.py."""
+def test_cbca_kernel_forms_agree_bit_for_bit(tmp_path):
+    """The fused CBCA kernel in its default form (software-pipelined row loads) against the round-1 form
+    (STEREO_CBCA_KERNEL=1: every row loaded and used at once): the same additions in the same order, so the bits must
+    agree; bands of every length, images narrower than a block's window.  The default is checked against the C
+    restatement in test_gpu_post.py."""
     maps = {}
-    for name, env in (("occ3", {}), ("occ4", {"STEREO_CBCA_OCC": "4"})):
+    for name, env in (("pipelined", {}), ("round1", {"STEREO_CBCA_KERNEL": "1"})):
         e = dict(os.environ)
         e.update(env)
         out = tmp_path / (name + ".npz")
@@ -105,9 +106,9 @@ def test_cbca_occupancy_variants_agree_bit_for_bit(tmp_path):
                            timeout=600)
         assert r.returncode == 0, r.stderr[-2000:]
         maps[name] = np.load(out)
-    assert sorted(maps["occ3"].files) == sorted(maps["occ4"].files) and len(maps["occ3"].files) == 8
-    for k in maps["occ3"].files:
-        assert np.array_equal(maps["occ3"][k], maps["occ4"][k]), k
+    assert sorted(maps["pipelined"].files) == sorted(maps["round1"].files) and len(maps["round1"].files) == 8
+    for k in maps["round1"].files:
+        assert np.array_equal(maps["pipelined"][k], maps["round1"][k]), k
 
 
 BASE_CHILD = r"""
