@@ -43,9 +43,18 @@ def rows_of(path):
 
 
 def main():
+    # --json FILE: also write {kernel: {"dram_bytes", "tensor_pipe_active", "time_us", "report"}} (first launch of each
+    # kernel) - the per-launch figures bench.py quotes in its roofline block (profiles/ncu_metrics.json)
+    args = sys.argv[1:]
+    json_path = None
+    if "--json" in args:
+        k = args.index("--json")
+        json_path = args[k + 1]
+        args = args[:k] + args[k + 2:]
+    table = {}
     print("| report | kernel | " + " | ".join(k for k, _ in METRICS) + " |")
     print("|---|---|" + "---|" * len(METRICS))
-    for path in sys.argv[1:]:
+    for path in args:
         hdr, units, rows = rows_of(path)
         idx = {h: i for i, h in enumerate(hdr)}
         for r in rows:
@@ -67,6 +76,22 @@ def main():
                 cells.append(f"{v:.1f}" if abs(v) < 1e6 and v != int(v) else f"{int(v)}")
             name = r[idx["Kernel Name"]].split("(")[0][-48:]
             print(f"| {path.split('/')[-1]} | {name} | " + " | ".join(cells) + " |")
+            full = r[idx["Kernel Name"]]
+            if json_path and full not in table:
+                def num(i):
+                    try:
+                        return float(cells[i])
+                    except ValueError:
+                        return None
+                keys = [k for k, _ in METRICS]
+                rd, wr, tp = num(keys.index("dram_rd_MB")), num(keys.index("dram_wr_MB")), num(keys.index("tensor_pct"))
+                table[full] = {"dram_bytes": (rd + wr) * 1e6 if rd is not None and wr is not None else None,
+                               "tensor_pipe_active": tp / 100.0 if tp is not None else None,
+                               "time_us": num(keys.index("time_us")), "report": path.split("/")[-1]}
+    if json_path:
+        import json
+        with open(json_path, "w") as f:
+            json.dump(table, f, indent=1)
 
 
 if __name__ == "__main__":
