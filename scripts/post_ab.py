@@ -16,8 +16,6 @@ CONFIGS = [
     ("default (two streams)", {}),
     ("serial", {"STEREO_POST_SERIAL": "1"}),
     ("serial, CBCA round-1 form", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "1"}),
-    ("serial, CBCA round-1 form, four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "2"}),
-    ("serial, CBCA pipelined, four blocks per SM", {"STEREO_POST_SERIAL": "1", "STEREO_CBCA_KERNEL": "3"}),
     ("two streams, CBCA round-1 form", {"STEREO_CBCA_KERNEL": "1"}),
 ]
 for name, env in CONFIGS:

@@ -65,14 +65,11 @@ __device__ __forceinline__ void add_if(float &sum, int &cnt, float v, int c, uin
         : "+f"(sum), "+r"(cnt) : "f"(v), "r"(c), "r"(mask), "r"(bit));
 }
 
-// VARIANT 0: the row loop loads a row and uses it at once (round 1).  VARIANT 1 (default): software pipeline - the
-// ten costs and the four arm records of row r + 1 are requested right after the row sums of row r have consumed
-// the registers of the previous request, so their latency runs under the column sums, the division and the store
-// of output row r - 4 instead of in front of the next row sums.  Same additions in the same order.
-template <int MIN_BLOCKS, int VARIANT>
-__global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
-                                                         int pitch, const float *__restrict__ vol, float *__restrict__ out,
-                                                         int h, int w, int D, int direction, int rows_per_band)
+// The round-1 form of the kernel: every row is loaded and used at once, the arm records of an output row are
+// re-read when the row is written.  Kept as the cross-check of the default below (STEREO_CBCA_KERNEL=1).
+__global__ __launch_bounds__(256, 3) void cbca_fused_r1_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
+                                                               int pitch, const float *__restrict__ vol, float *__restrict__ out,
+                                                               int h, int w, int D, int direction, int rows_per_band)
 {
     const int d = threadIdx.x;
     if (d >= D) return;
@@ -101,22 +98,6 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
         for (int i = 0; i < kFB; ++i) { hs[u][i] = 0.f; hc[u][i] = 0; }
     const int row_elems = w * D;
 
-    // costs and arm records of the row whose sums come next (VARIANT 1: requested one iteration ahead)
-    float v[kFN];
-    uint32_t own_n[kFB], oth_n[kFB];
-    auto request_row = [&](int r) {
-        const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
-#pragma unroll
-        for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
-#pragma unroll
-        for (int i = 0; i < kFB; ++i) {
-            own_n[i] = __ldg(rec0 + (rbase + xb + i));
-            oth_n[i] = __ldg(rec1 + (rbase + xm[i]));
-        }
-    };
-    const int r_first = max(0, y0 - kFR), r_end = min(h, y1 + kFR);       // rows whose sums are formed: [r_first, r_end)
-    if (VARIANT == 1) request_row(r_first);
-
     for (int base = y0 - kFR; base < y1 + kFR; base += kFW) {
 #pragma unroll
         for (int u = 0; u < kFW; ++u) {
@@ -124,10 +105,16 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
             if (r >= y1 + kFR) break;
             if (r >= 0 && r < h) {
                 // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
-                if (VARIANT == 0) request_row(r);
+                const int vbase = r * row_elems, rbase = r * pitch;       // 32-bit element indices: one IMAD.WIDE per load
+                float v[kFN];
+#pragma unroll
+                for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+                uint32_t own_r[kFB];
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) own_r[i] = __ldg(rec0 + (rbase + xb + i));
 #pragma unroll
                 for (int i = 0; i < kFB; ++i) {
-                    const uint32_t cm = own_n[i] & oth_n[i];         // both arms reach the column
+                    const uint32_t cm = own_r[i] & __ldg(rec1 + (rbase + xm[i]));   // both arms reach the column
                     float sum = 0.f;
 #pragma unroll
                     for (int jj = -kFR; jj <= kFR; ++jj) {           // columns x-R .. x+R, ascending
@@ -138,7 +125,6 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
                     hs[u][i] = match_ok[i] ? sum : v[kFR + i];
                     hc[u][i] = match_ok[i] ? __popc(cm & 0xffu) + 1 : 0;
                 }
-                if (VARIANT == 1 && r + 1 < r_end) request_row(r + 1);
             }
             const int y = r - kFR;
             if (y >= y0 && y < y1) {
@@ -171,6 +157,142 @@ __global__ __launch_bounds__(256, MIN_BLOCKS) void cbca_fused_kernel(const uint3
     }
 }
 
+// The default form.  What the ncu source page of the round-1 form showed (profiles/r02_ncu_summary.md): 44 % of the
+// stall samples were waits for global loads, 30 % of all samples on ONE instruction per unrolled copy - the arm
+// records of the output row, re-read right before their use - and half of the executed instructions were integer
+// address arithmetic (one IMAD.WIDE per load, D a run-time value).  Here
+//   * the costs and records of row r + 1 are requested right after the row sums of row r have consumed the
+//     registers of the previous request (software pipeline): their latency runs under the column sums, the
+//     division and the store of output row r - 4;
+//   * the column masks of a row are kept from the moment its records are read for the row sums (a ring of nine
+//     16-bit entries in five registers) - the output phase loads nothing;
+//   * blocks whose 10-column window lies inside the image (all but five block columns) address it as
+//     row pointer + j * D with D a compile-time constant for the common ranges, so that the ten loads are one
+//     pointer and ten immediates (EDGE = false; the registers of the ten clamped offsets pay for the mask ring);
+//     edge blocks keep the clamped offsets (EDGE = true, a launch of its own).
+// Same additions in the same order as the round-1 form: bit-identical (tests/test_gpu_variants.py).
+template <int DC, bool EDGE>
+__global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
+                                                                       int pitch, const float *__restrict__ vol, float *__restrict__ out,
+                                                                       int h, int w, int D_rt, int direction, int rows_per_band,
+                                                                       int xb_first, int n_left, int xb_right)
+{
+    const int D = DC ? DC : D_rt;
+    const int d = threadIdx.x;
+    if (d >= D) return;
+    // interior launch: consecutive blocks from xb_first; edge launch: n_left blocks from pixel 0, the rest from xb_right
+    const int xb = EDGE ? ((int)blockIdx.x < n_left ? (int)blockIdx.x * kFB : xb_right + ((int)blockIdx.x - n_left) * kFB)
+                        : xb_first + (int)blockIdx.x * kFB;
+    const int y0 = blockIdx.y * rows_per_band, y1 = min(h, y0 + rows_per_band);
+    const int shift = d * direction;
+
+    int offs[EDGE ? kFN : 1];                // EDGE: element offsets of the 10 columns, clamped into the row
+    if (EDGE) {
+#pragma unroll
+        for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * D + d;
+    }
+    const int col0 = (xb - kFR) * D + d;     // !EDGE: offset of column xb - R; column j is + j * D
+    bool pix_ok[kFB], match_ok[kFB];
+    int xm[kFB];
+#pragma unroll
+    for (int i = 0; i < kFB; ++i) {
+        const int x = xb + i;
+        pix_ok[i] = x < w;
+        match_ok[i] = (unsigned)(x + shift) < (unsigned)w;
+        xm[i] = min(max(x + shift, 0), w - 1);
+    }
+
+    float hs[kFW][kFB];
+    int hc[kFW][kFB];
+    uint32_t vring[(kFW + 1) / 2];           // column masks of the last nine rows: entry u = two pixels x 8 bits
+#pragma unroll
+    for (int u = 0; u < kFW; ++u)
+#pragma unroll
+        for (int i = 0; i < kFB; ++i) { hs[u][i] = 0.f; hc[u][i] = 0; }
+#pragma unroll
+    for (int u = 0; u < (kFW + 1) / 2; ++u) vring[u] = 0;
+    const int row_elems = w * D;
+
+    // costs and arm records of the row whose sums come next, requested one iteration ahead
+    float v[kFN];
+    uint32_t own_n[kFB], oth_n[kFB];
+    auto request_row = [&](int r) {
+        if (EDGE) {
+            const int vbase = r * row_elems;
+#pragma unroll
+            for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
+        } else {
+            const float *prow = vol + ((size_t)r * row_elems + col0);
+#pragma unroll
+            for (int j = 0; j < kFN; ++j) v[j] = __ldg(prow + j * D);
+        }
+        const int rbase = r * pitch;
+#pragma unroll
+        for (int i = 0; i < kFB; ++i) {
+            own_n[i] = __ldg(rec0 + (rbase + xb + i));
+            oth_n[i] = __ldg(rec1 + (rbase + xm[i]));
+        }
+    };
+    const int r_first = max(0, y0 - kFR), r_end = min(h, y1 + kFR);       // rows whose sums are formed: [r_first, r_end)
+    request_row(r_first);
+
+    for (int base = y0 - kFR; base < y1 + kFR; base += kFW) {
+#pragma unroll
+        for (int u = 0; u < kFW; ++u) {
+            const int r = base + u;
+            if (r >= y1 + kFR) break;
+            if (r >= 0 && r < h) {
+                // ---- row-segment sums of image row r (cbca_h4_kernel), into window slot u ----
+                uint32_t vm = 0;
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) {
+                    const uint32_t cm = own_n[i] & oth_n[i];         // both arms reach the column (byte 0) / the row (byte 1)
+                    vm |= ((cm >> 8) & 0xffu) << (8 * i);
+                    float sum = 0.f;
+#pragma unroll
+                    for (int jj = -kFR; jj <= kFR; ++jj) {           // columns x-R .. x+R, ascending
+                        if (jj == 0) sum = __fadd_rn(sum, v[kFR + i]);
+                        else add_if(sum, v[kFR + i + jj], cm, off_bit(jj));
+                    }
+                    // unmatched disparities are copied through: keep the cost itself, length 0
+                    hs[u][i] = match_ok[i] ? sum : v[kFR + i];
+                    hc[u][i] = match_ok[i] ? __popc(cm & 0xffu) + 1 : 0;
+                }
+                // the row's column masks wait in the ring until the row is written, four iterations on
+                vring[u / 2] = (u & 1) ? ((vring[u / 2] & 0xffffu) | (vm << 16)) : ((vring[u / 2] & 0xffff0000u) | vm);
+                if (r + 1 < r_end) request_row(r + 1);
+            }
+            const int y = r - kFR;
+            if (y >= y0 && y < y1) {
+                // ---- output row y: rows y-R .. y+R sit in slots u+1 .. u+9 (mod 9) (cbca_v4_kernel) ----
+                const int uy = (u + kFW - kFR) % kFW;                // ring entry of row y (a constant after unrolling)
+                const uint32_t vm = (vring[uy / 2] >> (16 * (uy & 1))) & 0xffffu;
+                const int obase = y * row_elems;
+#pragma unroll
+                for (int i = 0; i < kFB; ++i) {
+                    if (!pix_ok[i]) continue;
+                    const uint32_t cm = (vm >> (8 * i)) & 0xffu;     // both arms reach the row
+                    float sum = 0.f;
+                    int cnt = 0;
+#pragma unroll
+                    for (int jj = -kFR; jj <= kFR; ++jj) {           // rows y-R .. y+R, ascending
+                        const int slot = (u + 1 + jj + kFR) % kFW;
+                        if (jj == 0) {
+                            sum = __fadd_rn(sum, hs[slot][i]);
+                            cnt += hc[slot][i];
+                        } else {
+                            add_if(sum, cnt, hs[slot][i], hc[slot][i], cm, off_bit(jj));
+                        }
+                    }
+                    const float centre = hs[(u + 1 + kFR) % kFW][i];
+                    const int oidx = EDGE ? obase + offs[kFR + i] : obase + col0 + (kFR + i) * D;
+                    out[oidx] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
+                }
+            }
+        }
+    }
+}
+
 }  // namespace
 
 // x0c / x1c: int16 arms [4][h][w] of the two views; rec: scratch for 2 * h * pitch records
@@ -190,14 +312,31 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     const int nt = (D + 31) / 32 * 32;
     const int bands = std::max(1, (h + 62) / 63);
     const int rows_per_band = (h + bands - 1) / bands;
-    // STEREO_CBCA_KERNEL=1 keeps the round-1 form (three blocks per SM, every row loaded and used at once) as the
-    // cross-check; STEREO_CBCA_KERNEL=2: that form compiled for four blocks per SM (64 registers, a few spills)
-    static const int variant = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e ? atoi(e) : 0; }();
-    const dim3 grid((w + kFB - 1) / kFB, bands);
-    if (variant == 1) cbca_fused_kernel<3, 0><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
-    else if (variant == 2) cbca_fused_kernel<4, 0><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
-    else if (variant == 3) cbca_fused_kernel<4, 1><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
-    else cbca_fused_kernel<3, 1><<<grid, nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    // STEREO_CBCA_KERNEL=1 keeps the round-1 form as the cross-check
+    static const bool round1 = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e && atoi(e) == 1; }();
+    const int nbx = (w + kFB - 1) / kFB;
+    if (round1) {
+        cbca_fused_r1_kernel<<<dim3(nbx, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
+    } else {
+        // interior blocks: the window xb - R .. xb + 1 + R lies inside the image
+        const int n_left = std::min(nbx, (kFR + kFB - 1) / kFB);                       // blocks with xb < R
+        int first_right = n_left;                                                      // first block with xb + kFB + R > w
+        while (first_right < nbx && first_right * kFB + kFB + kFR <= w) ++first_right;
+        const int n_int = first_right - n_left, n_edge = nbx - n_int;
+        auto launch = [&](auto interior, auto edge) {
+            if (n_int > 0)
+                interior<<<dim3(n_int, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band,
+                                                                     n_left * kFB, 0, 0);
+            if (n_edge > 0)
+                edge<<<dim3(n_edge, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band, 0,
+                                                                  n_left, first_right * kFB);
+        };
+        // disparity ranges known at compile time: the benchmark's 228, the reference's default 201; any other at run time
+        if (D == 228) launch(cbca_fused_kernel<228, false>, cbca_fused_kernel<0, true>);
+        else if (D == 201) launch(cbca_fused_kernel<201, false>, cbca_fused_kernel<0, true>);
+        else launch(cbca_fused_kernel<0, false>, cbca_fused_kernel<0, true>);
+        ctx->launches += (n_int > 0 && n_edge > 0) ? 1 : 0;
+    }
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
