@@ -19,6 +19,7 @@
 #include <cuda_bf16.h>
 
 #include <cstdlib>
+#include <type_traits>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -80,7 +81,11 @@ __device__ __forceinline__ Item decode(const Params &p, int item)
     return it;
 }
 
-template <bool VOL, bool WTA>
+// DC: the disparity range as a compile-time constant (0: run-time p.D).  The materialising epilogue stores eight
+// rows of a [x][d] tile per round, one row D +- 1 floats after the other: with D known the eight stores are one
+// pointer and eight immediates, and the range tests compare against a constant - the round-2 ncu source page had
+// 40 % of this kernel's instructions in 64-bit address arithmetic and predicates of these stores.
+template <bool VOL, bool WTA, int DC>
 __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
 {
     using L = Layout<VOL>;
@@ -224,7 +229,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
         // ---- epilogue: warp (q, part) drains columns 32*part.. of every accumulator block, lanes 32q.. ----
         const int q = warp & 3, part = (warp - 4) >> 2;
         const int xi = q * 32 + lane;
-        const int D = p.D;
+        const int D = DC ? DC : p.D;
         float *wta_v = reinterpret_cast<float *>(smem + L::kWtaV);
         uint16_t *wta_d = reinterpret_cast<uint16_t *>(smem + L::kWtaD);
         float *stage = reinterpret_cast<float *>(smem + L::kStage) + (warp - 4) * kStageRows * kStagePitch;
@@ -276,31 +281,41 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                             float *vol = it.side == 0 ? p.left_vol : p.right_vol;
                             float *rowbase = vol + (((size_t)it.img * p.h + it.y) * p.w) * (size_t)D;
                             const int xq = kBlk * k + q * 32;
-                            const int dstep = it.side == 0 ? 1 : -1;
-                            const int stride = D + dstep;                   // 32-bit offsets: a row of a volume is < 2^31 floats
-                            int dd = it.side == 0 ? q * 32 + kMargin - (u0 + lane) : (u0 + lane) - q * 32;   // row 0
-                            int off = xq * D + dd;
                             const int rows_ok = min(32, p.w - xq);
+                            // disparity of this lane's column in row 0 of the chunk; it moves by dstep per row
+                            const int dd0 = it.side == 0 ? q * 32 + kMargin - (u0 + lane) : (u0 + lane) - q * 32;
+                            auto store_rounds = [&](auto dstep_c) {
+                                constexpr int dstep = decltype(dstep_c)::value;
+                                const int stride = D + dstep;               // floats from a row's slot to the next row's
+                                float *p0 = rowbase + (xq * D + dd0);       // 32-bit offset: a row of a volume is < 2^31 floats
 #pragma unroll 1
-                            for (int r0 = 0; r0 < 32; r0 += kStageRows) {
-                                if (lane >= r0 && lane < r0 + kStageRows) {
+                                for (int r0 = 0; r0 < 32; r0 += kStageRows) {
+                                    if (lane >= r0 && lane < r0 + kStageRows) {
 #pragma unroll
-                                    for (int i = 0; i < 8; ++i)
-                                        reinterpret_cast<uint4 *>(stage + (lane - r0) * kStagePitch)[i] =
-                                            make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                                        for (int i = 0; i < 8; ++i)
+                                            reinterpret_cast<uint4 *>(stage + (lane - r0) * kStagePitch)[i] =
+                                                make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                                    }
+                                    __syncwarp();
+                                    float t[kStageRows];
+#pragma unroll
+                                    for (int j = 0; j < kStageRows; ++j) t[j] = stage[j * kStagePitch + lane];
+                                    float *pr = p0 + r0 * stride;
+                                    const int dr = dd0 + r0 * dstep;
+                                    if (r0 + kStageRows <= rows_ok) {
+#pragma unroll
+                                        for (int j = 0; j < kStageRows; ++j)
+                                            if ((unsigned)(dr + j * dstep) < (unsigned)D) pr[j * stride] = t[j];
+                                    } else {
+#pragma unroll
+                                        for (int j = 0; j < kStageRows; ++j)
+                                            if (r0 + j < rows_ok && (unsigned)(dr + j * dstep) < (unsigned)D) pr[j * stride] = t[j];
+                                    }
+                                    __syncwarp();
                                 }
-                                __syncwarp();
-                                float t[kStageRows];
-#pragma unroll
-                                for (int j = 0; j < kStageRows; ++j) t[j] = stage[j * kStagePitch + lane];
-#pragma unroll
-                                for (int j = 0; j < kStageRows; ++j) {
-                                    if (r0 + j < rows_ok && (unsigned)dd < (unsigned)D) rowbase[off] = t[j];
-                                    off += stride;
-                                    dd += dstep;
-                                }
-                                __syncwarp();
-                            }
+                            };
+                            if (it.side == 0) store_rounds(std::integral_constant<int, 1>());
+                            else store_rounds(std::integral_constant<int, -1>());
                         }
                     }
                     tc::tc_fence_before();
@@ -392,9 +407,19 @@ int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const
         STEREO_CUDA_CHECK(cudaGetLastError());
         return STEREO_OK;
     };
-    if (vol && wta) return launch(tcs::corr_sweep_kernel<true, true>, tcs::Layout<true>::kTotal);
-    if (vol) return launch(tcs::corr_sweep_kernel<true, false>, tcs::Layout<true>::kTotal);
-    STEREO_TRY(launch(tcs::corr_sweep_kernel<false, true>, tcs::Layout<false>::kTotal));
+    // the materialising variants exist for the disparity ranges known at compile time too (the benchmark's 228, the
+    // reference's default 201)
+    if (vol && wta) {
+        if (D == 228) return launch(tcs::corr_sweep_kernel<true, true, 228>, tcs::Layout<true>::kTotal);
+        if (D == 201) return launch(tcs::corr_sweep_kernel<true, true, 201>, tcs::Layout<true>::kTotal);
+        return launch(tcs::corr_sweep_kernel<true, true, 0>, tcs::Layout<true>::kTotal);
+    }
+    if (vol) {
+        if (D == 228) return launch(tcs::corr_sweep_kernel<true, false, 228>, tcs::Layout<true>::kTotal);
+        if (D == 201) return launch(tcs::corr_sweep_kernel<true, false, 201>, tcs::Layout<true>::kTotal);
+        return launch(tcs::corr_sweep_kernel<true, false, 0>, tcs::Layout<true>::kTotal);
+    }
+    STEREO_TRY(launch(tcs::corr_sweep_kernel<false, true, 0>, tcs::Layout<false>::kTotal));
     return STEREO_OK;
 }
 
