@@ -73,6 +73,48 @@ def test_variant_matches_oracle(env, reference_maps, tmp_path):
         assert np.array_equal(got["lr"][i], lab.astype(np.uint8))
 
 
+VOL_CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib, checkpoint, synth
+from stereo_matching_b200.models.model import base_model_ws_9
+m = base_model_ws_9((None, None, 3))
+m.set_layers(checkpoint.load_net_weights(os.path.join(sys.argv[1], "tests", "golden", "new_checkpoint")))
+out = {}
+for tag, (h, w, D) in {"a": (40, 300, 64), "b": (9, 1242, 228), "c": (13, 130, 256), "d": (5, 97, 4)}.items():
+    l, r, _ = synth.make_pair(2500 + h, h, w, D)
+    o = m.context.pairs(_lib.NET_WIN9, l, r, D, precision=_lib.PREC_BF16X3, volumes=True)
+    for k in ("left_cost", "right_cost", "left_disp", "right_disp"):
+        out[tag + "_" + k] = o[k][0]
+    lv, rv = m.context.cost_volume(np.random.default_rng(h).standard_normal((1, h, w, 64)).astype(np.float32),
+                                   np.random.default_rng(w).standard_normal((1, h, w, 64)).astype(np.float32), D, _lib.PREC_BF16X3)
+    out[tag + "_lv"], out[tag + "_rv"] = lv[0], rv[0]
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_materialising_store_paths_agree_bit_for_bit(tmp_path):
+    """The materialising correlation writes aligned volumes (D % 4 == 0) through one bulk copy per 32-pixel group of a
+    shared-memory tile; STEREO_CORR_STORE=1 keeps the per-row stores.  The same accumulators leave by two routes: the
+    volumes (with and without the fused WTA) and the maps must be equal bit for bit - image widths that end inside a
+    32-pixel group, the widest range (256) and a tiny one."""
+    outs = {}
+    for name, env in (("bulk", {}), ("rows", {"STEREO_CORR_STORE": "1"})):
+        e = dict(os.environ)
+        e.update(env)
+        out = tmp_path / (name + ".npz")
+        r = subprocess.run([sys.executable, "-c", VOL_CHILD, ROOT, str(out)], env=e, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[name] = np.load(out)
+    assert sorted(outs["bulk"].files) == sorted(outs["rows"].files) and len(outs["bulk"].files) == 24
+    for k in outs["bulk"].files:
+        assert np.array_equal(outs["bulk"][k], outs["rows"][k]), k
+    lv = outs["bulk"]["b_left_cost"]
+    assert np.array_equal(outs["bulk"]["b_left_disp"], np.argmax(lv, axis=2).astype(np.uint8))
+
+
 CBCA_CHILD = r"""
 import os, sys
 import numpy as np
