@@ -32,22 +32,24 @@ constexpr int kBlk = 128;                       // pixels per block
 constexpr int kRun = kBlk * 16;                 // one channel chunk: 2 KB
 constexpr int kPlane = 8 * kRun;                // 16 KB
 constexpr int kBlock = 2 * kPlane;              // hi + lo: 32 KB
-constexpr int kBSlots = 4, kAccBlocks = 4;
+constexpr int kAccBlocks = 4;
 constexpr int kStageRows = 8, kStagePitch = 36;  // materialising epilogue: [8 rows][32 + 4] floats per warp
 // Shared-memory layout.  The materialising variant gives up one of the three own-block slots for the
 // staging buffers in which the epilogue warps transpose 8x32 blocks before they store them.
-// BULK (materialising, 16-byte aligned volumes with D % 4 == 0): the staging area is one [32 pixels][D] fp32 tile, which
-// is ONE contiguous run of the [x][d] volume and leaves for HBM as a single bulk copy.
+// BULK (materialising, 16-byte aligned volumes with D % 4 == 0): the staging area is two [32 pixels][D] fp32 tiles; a
+// tile is ONE contiguous run of the [x][d] volume and leaves for HBM as a single bulk copy while the other one is
+// filled.  The candidate ring gives up a slot for them (three: just the blocks a tile multiplies).
 constexpr int kBulkStageBytes = 32 * 256 * 4;
 template <bool VOL, bool BULK = false>
 struct Layout {
     static constexpr int kASlots = VOL ? 2 : 3;
+    static constexpr int kBSlots = BULK ? 3 : 4;
     static constexpr int kA = 0;
     static constexpr int kB = kA + kASlots * kBlock;
     static constexpr int kWtaV = kB + kBSlots * kBlock;          // [3 parts][128] best value of column parts 1-3
     static constexpr int kWtaD = kWtaV + 3 * 128 * 4;            // [3 parts][128] its disparity (16 bit)
     static constexpr int kStage = kWtaD + 3 * 128 * 2;
-    static constexpr int kBars = kStage + (BULK ? kBulkStageBytes : (VOL ? 16 * kStageRows * kStagePitch * 4 : 0));
+    static constexpr int kBars = kStage + (BULK ? 2 * kBulkStageBytes : (VOL ? 16 * kStageRows * kStagePitch * 4 : 0));
     static constexpr int kTotal = kBars + 256;
     static_assert(kTotal <= 232448, "shared memory budget of one CTA");
 };
@@ -99,6 +101,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
     static_assert(!BULK || VOL, "the bulk store belongs to the materialising variant");
     using L = Layout<VOL, BULK>;
     constexpr int kASlots = L::kASlots;
+    constexpr int kBSlots = L::kBSlots;
     extern __shared__ __align__(128) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t s_base = tc::smem_u32(smem);
@@ -249,11 +252,12 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                 float best = -INFINITY;
                 int best_d = 0x7fffffff;
                 if (BULK) {
-                    float *tile = reinterpret_cast<float *>(smem + L::kStage);
                     float *vol = it.side == 0 ? p.left_vol : p.right_vol;
                     float *rowbase = vol + (((size_t)it.img * p.h + it.y) * p.w) * (size_t)D;
 #pragma unroll 1
                     for (int g = 0; g < 4; ++g) {
+                        // turn g: group g fills tile g & 1 (free: the store thread saw the copy of turn g - 2 read out)
+                        float *tile = reinterpret_cast<float *>(smem + L::kStage + (g & 1) * kBulkStageBytes);
                         if (q == g) {
 #pragma unroll 1
                             for (int o = 0; o < 3; ++o) {
@@ -300,16 +304,17 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         }
                         asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
-                        if (q == g && part == 0 && lane == 0) {
+                        if (warp == 4 && lane == 0) {
+                            // the store thread (one for all groups: bulk groups are tracked per thread) sends the tile off
+                            // and makes sure the copy of the turn before has been read out of the other tile
                             const int xq = kBlk * k + g * 32;
                             const int rows_ok = min(32, p.w - xq);
-                            if (rows_ok > 0) {
+                            if (rows_ok > 0)
                                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(rowbase + (size_t)xq * D),
                                              "r"(tc::smem_u32(tile)), "r"((uint32_t)(rows_ok * D * 4))
                                              : "memory");
-                                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                            }
+                            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
                         }
                         asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
                     }
@@ -432,7 +437,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
         }
         if (WTA && part != 0 && T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
         // the bulk stores this thread issued are complete (not only read out of shared memory) before the block ends
-        if (BULK && part == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        if (BULK && warp == 4 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 
     tc::tc_fence_before();
@@ -497,7 +502,7 @@ int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const
     // 32-pixel group (STEREO_CORR_STORE=1 keeps the per-row stores as the cross-check); the rest take the per-row
     // stores, with the disparity range as a compile-time constant for the reference's default 201.
     static const bool no_bulk = [] { const char *e = getenv("STEREO_CORR_STORE"); return e && atoi(e) == 1; }();
-    const bool bulk = vol && !no_bulk && D % 4 == 0 && D * 128 <= tcs::kBulkStageBytes &&
+    const bool bulk = vol && !no_bulk && D % 4 == 0 && D * 128 <= tcs::kBulkStageBytes &&      // 32 rows x D x 4 bytes
                       ((uintptr_t)left_vol % 16 == 0) && ((uintptr_t)right_vol % 16 == 0);
     if (vol && wta) {
         if (bulk) return launch(tcs::corr_sweep_kernel<true, true, 0, true>, tcs::Layout<true, true>::kTotal);
