@@ -36,10 +36,10 @@ constexpr int kAccBlocks = 4;
 constexpr int kStageRows = 8, kStagePitch = 36;  // materialising epilogue: [8 rows][32 + 4] floats per warp
 // Shared-memory layout.  The materialising variant gives up one of the three own-block slots for the
 // staging buffers in which the epilogue warps transpose 8x32 blocks before they store them.
-// BULK (materialising, 16-byte aligned volumes with D % 4 == 0): the staging area is two [32 pixels][D] fp32 tiles; a
-// tile is ONE contiguous run of the [x][d] volume and leaves for HBM as a single bulk copy while the other one is
-// filled.  The candidate ring gives up a slot for them (three: just the blocks a tile multiplies).
-constexpr int kBulkStageBytes = 32 * 256 * 4;
+// BULK (materialising, 16-byte aligned volumes with D % 4 == 0): the staging area is four [16 pixels][D] fp32 tiles,
+// one per group of epilogue warps; a tile is ONE contiguous run of the [x][d] volume and leaves for HBM as a
+// single bulk copy.  The candidate ring gives up a slot for them (three: just the blocks a tile multiplies).
+constexpr int kBulkStageBytes = 16 * 256 * 4;
 template <bool VOL, bool BULK = false>
 struct Layout {
     static constexpr int kASlots = VOL ? 2 : 3;
@@ -49,7 +49,7 @@ struct Layout {
     static constexpr int kWtaV = kB + kBSlots * kBlock;          // [3 parts][128] best value of column parts 1-3
     static constexpr int kWtaD = kWtaV + 3 * 128 * 4;            // [3 parts][128] its disparity (16 bit)
     static constexpr int kStage = kWtaD + 3 * 128 * 2;
-    static constexpr int kBars = kStage + (BULK ? 2 * kBulkStageBytes : (VOL ? 16 * kStageRows * kStagePitch * 4 : 0));
+    static constexpr int kBars = kStage + (BULK ? 4 * kBulkStageBytes : (VOL ? 16 * kStageRows * kStagePitch * 4 : 0));
     static constexpr int kTotal = kBars + 256;
     static_assert(kTotal <= 232448, "shared memory budget of one CTA");
 };
@@ -90,11 +90,13 @@ __device__ __forceinline__ Item decode(const Params &p, int item)
 // rows of a [x][d] tile per round, one row D +- 1 floats after the other: with D known the eight stores are one
 // pointer and eight immediates, and the range tests compare against a constant - the round-2 ncu source page had
 // 40 % of this kernel's instructions in 64-bit address arithmetic and predicates of these stores.
-// BULK: see Layout.  The four groups of epilogue warps (32 pixels each) take turns: a group copies its rows of the
-// three accumulator blocks of a tile into the staging tile (conflict-free 4-byte shared stores: consecutive lanes
-// are D +- 1 words apart), one thread sends the tile off with cp.async.bulk and waits until the copy engine has
-// read it, then the next group goes.  One store instruction per 32 x D voxels instead of one per 32: the
-// per-store address arithmetic that made the round-1 epilogue instruction bound is gone, and HBM sees 29 KB runs.
+// BULK: see Layout.  Every group of four epilogue warps (32 pixels of the tile) owns a staging tile of 16 pixels: it
+// copies the upper 16 rows of its three accumulator blocks there (conflict-free 4-byte shared stores: consecutive
+// lanes are D +- 1 words apart), one thread of the group sends the tile off with cp.async.bulk, then the same for the
+// lower 16 rows (the accumulators are simply read twice).  One store instruction per 16 x D voxels instead of one
+// per 32: the per-store address arithmetic that made the round-1 epilogue instruction bound is gone, and HBM sees
+// 14 KB runs.  Measured alternatives: the groups taking turns on one 32-row tile (0.55 ms per pair), on two
+// (0.39 ms, like the per-row stores): only four of the sixteen warps work at a time.
 template <bool VOL, bool WTA, int DC, bool BULK = false>
 __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
 {
@@ -254,69 +256,67 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                 if (BULK) {
                     float *vol = it.side == 0 ? p.left_vol : p.right_vol;
                     float *rowbase = vol + (((size_t)it.img * p.h + it.y) * p.w) * (size_t)D;
+                    float *tile = reinterpret_cast<float *>(smem + L::kStage + q * kBulkStageBytes);
+                    const bool store_thread = part == 0 && lane == 0;       // bulk groups are tracked per thread
 #pragma unroll 1
-                    for (int g = 0; g < 4; ++g) {
-                        // turn g: group g fills tile g & 1 (free: the store thread saw the copy of turn g - 2 read out)
-                        float *tile = reinterpret_cast<float *>(smem + L::kStage + (g & 1) * kBulkStageBytes);
-                        if (q == g) {
+                    for (int half = 0; half < 2; ++half) {
+                        // the tile is free once the copy engine has read the previous copy out of it
+                        if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                        asm volatile("bar.sync %0, 128;" ::"r"(3 + q) : "memory");
+                        const bool mine = (lane >> 4) == half;
+                        float *trow = tile + (lane & 15) * D;
 #pragma unroll 1
-                            for (int o = 0; o < 3; ++o) {
-                                const uint32_t Go = G + o, ab = Go % kAccBlocks;
-                                tc::mbar_wait(bar_acc_full + 8 * ab, (Go / kAccBlocks) & 1);
-                                tc::tc_fence_after();
-                                const int u0 = 128 * o + 32 * part;
-                                const int dlo = it.side == 0 ? 32 * q + kMargin - u0 - 31 : u0 - 32 * q - 31;
-                                if (dlo + 62 >= 0 && dlo <= D - 1) {
-                                    uint32_t v[32];
-                                    tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
-                                    // row `lane` of the tile, disparity of column i: dbase -+ i
-                                    float *trow = tile + lane * D;
-                                    if (it.side == 0) {
-                                        const int dbase = xi + kMargin - u0;
+                        for (int o = 0; o < 3; ++o) {
+                            const uint32_t Go = G + o, ab = Go % kAccBlocks;
+                            tc::mbar_wait(bar_acc_full + 8 * ab, (Go / kAccBlocks) & 1);
+                            tc::tc_fence_after();
+                            const int u0 = 128 * o + 32 * part;
+                            const int dlo = it.side == 0 ? 32 * q + kMargin - u0 - 31 : u0 - 32 * q - 31;
+                            if (dlo + 62 >= 0 && dlo <= D - 1) {
+                                uint32_t v[32];
+                                tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
+                                // row `lane` of the group, disparity of column i: dbase -+ i
+                                if (it.side == 0) {
+                                    const int dbase = xi + kMargin - u0;
 #pragma unroll
-                                        for (int i = 0; i < 32; ++i) {
-                                            const int d = dbase - i;
-                                            const float f = __uint_as_float(v[i]);
-                                            if ((unsigned)d < (unsigned)D) trow[d] = f;
-                                            if (WTA) {
-                                                const bool take = (unsigned)d < (unsigned)D && f >= best;
-                                                best = take ? f : best;
-                                                best_d = take ? d : best_d;
-                                            }
+                                    for (int i = 0; i < 32; ++i) {
+                                        const int d = dbase - i;
+                                        const float f = __uint_as_float(v[i]);
+                                        if (mine && (unsigned)d < (unsigned)D) trow[d] = f;
+                                        if (WTA && half == 0) {
+                                            const bool take = (unsigned)d < (unsigned)D && f >= best;
+                                            best = take ? f : best;
+                                            best_d = take ? d : best_d;
                                         }
-                                    } else {
-                                        const int dbase = u0 - xi;
+                                    }
+                                } else {
+                                    const int dbase = u0 - xi;
 #pragma unroll
-                                        for (int i = 0; i < 32; ++i) {
-                                            const int d = dbase + i;
-                                            const float f = __uint_as_float(v[i]);
-                                            if ((unsigned)d < (unsigned)D) trow[d] = f;
-                                            if (WTA) {
-                                                const bool take = (unsigned)d < (unsigned)D && f > best;
-                                                best = take ? f : best;
-                                                best_d = take ? d : best_d;
-                                            }
+                                    for (int i = 0; i < 32; ++i) {
+                                        const int d = dbase + i;
+                                        const float f = __uint_as_float(v[i]);
+                                        if (mine && (unsigned)d < (unsigned)D) trow[d] = f;
+                                        if (WTA && half == 0) {
+                                            const bool take = (unsigned)d < (unsigned)D && f > best;
+                                            best = take ? f : best;
+                                            best_d = take ? d : best_d;
                                         }
                                     }
                                 }
                             }
-                            // generic-proxy writes of this thread become visible to the copy engine
-                            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                         }
-                        asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
-                        if (warp == 4 && lane == 0) {
-                            // the store thread (one for all groups: bulk groups are tracked per thread) sends the tile off
-                            // and makes sure the copy of the turn before has been read out of the other tile
-                            const int xq = kBlk * k + g * 32;
-                            const int rows_ok = min(32, p.w - xq);
+                        // generic-proxy writes of this thread become visible to the copy engine
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        asm volatile("bar.sync %0, 128;" ::"r"(3 + q) : "memory");
+                        if (store_thread) {
+                            const int xq = kBlk * k + q * 32 + 16 * half;
+                            const int rows_ok = min(16, p.w - xq);
                             if (rows_ok > 0)
                                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(rowbase + (size_t)xq * D),
                                              "r"(tc::smem_u32(tile)), "r"((uint32_t)(rows_ok * D * 4))
                                              : "memory");
                             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
                         }
-                        asm volatile("bar.sync 3, %0;" ::"n"(32 * kEpiWarps) : "memory");
                     }
                     // every group has read its rows: the three accumulator blocks go back to the issuer
                     tc::tc_fence_before();
@@ -437,7 +437,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
         }
         if (WTA && part != 0 && T > 0) asm volatile("bar.sync 2, %0;" ::"n"(32 * kEpiWarps) : "memory");
         // the bulk stores this thread issued are complete (not only read out of shared memory) before the block ends
-        if (BULK && warp == 4 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        if (BULK && part == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 
     tc::tc_fence_before();
@@ -502,7 +502,7 @@ int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const
     // 32-pixel group (STEREO_CORR_STORE=1 keeps the per-row stores as the cross-check); the rest take the per-row
     // stores, with the disparity range as a compile-time constant for the reference's default 201.
     static const bool no_bulk = [] { const char *e = getenv("STEREO_CORR_STORE"); return e && atoi(e) == 1; }();
-    const bool bulk = vol && !no_bulk && D % 4 == 0 && D * 128 <= tcs::kBulkStageBytes &&      // 32 rows x D x 4 bytes
+    const bool bulk = vol && !no_bulk && D % 4 == 0 && D * 64 <= tcs::kBulkStageBytes &&      // 16 rows x D x 4 bytes
                       ((uintptr_t)left_vol % 16 == 0) && ((uintptr_t)right_vol % 16 == 0);
     if (vol && wta) {
         if (bulk) return launch(tcs::corr_sweep_kernel<true, true, 0, true>, tcs::Layout<true, true>::kTotal);
