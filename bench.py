@@ -370,6 +370,8 @@ def run_b200(args):
 
     # ---- BASELINE.json metric, second half: "cost-volume GB/s vs HBM peak" (configs[0] shape: one pair,
     #      left + right volumes materialised in the reference's [H][W][D] layout, then standalone WTA) ----------
+    if world > 1:
+        args.no_post = True          # the secondary (configs[0], [2], [3], [4]) figures are single-GPU legs: --config runs them at N > 1
     if not args.no_post:
         # the secondary workloads below are timed alone: give the board a moment to leave the power-capped state the
         # K headline steps put it in (the headline itself is never measured this way)
@@ -483,7 +485,7 @@ def run_b200(args):
         }
 
     # ---- post chain on the host cores: the C/OpenMP restatement on a bounded sample of the same pair ----
-    if not args.no_post and not args.no_cpu_baseline and rank == 0:
+    if not args.no_post and not args.no_cpu_baseline and rank == 0 and world == 1:
         try:
             from oracle import post_oracle as po
             prow = min(48, H)
@@ -568,7 +570,7 @@ def run_b200(args):
 
     # ---- CPU baseline (oracle port) on a bounded sample --------------------------------------------
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:          # the CPU baseline is an N = 1 figure (rank 0's host cores)
         times, cores = cpu_pair_seconds(args.cpu_rows, None, repeats=1)
         cpu_value = (args.cpu_rows / H) / times[0]
         cpu = {"value": cpu_value, "unit": UNIT, "cores": cores, "kind": "port",
@@ -741,7 +743,7 @@ def run_base_model(args):
                 "note": "algorithmic FLOPs of the eight 5x5 layers counted once whatever the operand split / CUDA-event "
                         "time of the kernel class in a pass with the pairs one at a time"}
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and hz.world == 1:
         cpu = cpu_baseline_trunk("win37_dep9", 37, layers, min(args.cpu_rows, 16))
     extra = {"kernel_ms_per_step": {k: v[0] for k, v in prof.items() if v[1]},
              "weights": "seeded synthetic (the reference ships none for base_model): the maps are not meaningful "
@@ -931,7 +933,7 @@ def run_post_chain(args):
                 "note": "algorithmic bytes = read + write of the volume per call (SURVEY 8(d)); kernel-class time from a pass with "
                         "both sides of the chain on one stream (every kernel alone on the GPU)"}
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and hz.world == 1:
         cpu = cpu_baseline_post(48, args.sgm_paths, tuple(t.cpu().numpy() for t in vols[0]))
     # whole pipeline from images, volumes never leave the device
     with torch.cuda.stream(hz.stream):
@@ -1052,7 +1054,7 @@ def run_train_dp(args):
                 "note": "the training contractions run in fp32 on the CUDA cores (not yet on tcgen05): the fraction of the "
                         "tensor peak says how far that is from what the hardware offers; 54.9 algorithmic GFLOP per step "
                         "of 128 patches / wall time of the whole step (host patches in, loss out)"}
-    cpu = None if args.no_cpu_baseline else cpu_baseline_train(B, Dt)
+    cpu = None if (args.no_cpu_baseline or hz.world > 1) else cpu_baseline_train(B, Dt)
     e2e = {"value": value, "unit": "patches/s",
            "h2d_bytes_per_step": int(hz.world * 4 * (B * 81 * 3 + B * 9 * (9 + Dt - 1) * 3 + B * Dt)),
            "d2h_bytes_per_step": int(hz.world * 8),
