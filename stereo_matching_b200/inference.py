@@ -108,9 +108,11 @@ def run(flags) -> float:
     rank, world, local_rank = _world()
     if world > 1:
         import torch.distributed as dist
+        import torch
         if not dist.is_initialized():
             dist.init_process_group("gloo")          # only the per-pair errors travel; no data-path collective
-        flags.device = local_rank
+        # one GPU per rank; ranks beyond the visible GPUs share them (a 2-rank run on a 1-GPU box still works)
+        flags.device = local_rank % max(1, torch.cuda.device_count())
     precision = PRECISIONS[flags.precision]
     if flags.net_type == "win37_dep9":
         model = base_model((None, None, 3), device=flags.device, precision=precision)

@@ -506,3 +506,33 @@ def test_batched_tensor_core_pairs_with_volumes_equal_single_pairs(ctx):
         one = ctx.pairs(_lib.NET_WIN9, left[i], right[i], D, precision=_lib.PREC_BF16X3, volumes=True)
         for name in ("left_disp", "right_disp", "outlier", "left_cost", "right_cost"):
             assert np.array_equal(batch[name][i], one[name][0]), (i, name)
+
+
+def test_inference_cli_sharded_over_two_ranks(tmp_path):
+    """`torchrun --nproc-per-node 2 -m stereo_matching_b200.inference`: the pair list is sharded round-robin over the
+    ranks (shard.py; one GPU per rank, here both on the one GPU of the box), every rank writes the files of its pairs,
+    rank 0 prints the mean over all of them - the same files and the same mean as a single process."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    golden = os.path.join(root, "tests", "golden", "new_checkpoint")
+    common = ["--model_dir", golden, "--synthetic", "3", "--height", "40", "--width", "150", "--disp_range", "32"]
+    outs = {}
+    for name, launcher in (("one", [sys.executable, "-m", "stereo_matching_b200.inference"]),
+                           ("two", [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                                    "--master-addr", "127.0.0.1", "--master-port", "29533", "-m",
+                                    "stereo_matching_b200.inference"])):
+        out_dir = tmp_path / name
+        r = subprocess.run(launcher + common + ["--out_dir", str(out_dir)], capture_output=True, text=True, timeout=600, cwd=root)
+        assert r.returncode == 0, r.stderr[-2000:]
+        means = [float(l.split("Mean Error:")[1]) for l in r.stdout.splitlines() if "Mean Error:" in l]
+        assert len(means) == 1                                   # rank 0 only
+        outs[name] = (out_dir, means[0])
+    assert outs["one"][1] == pytest.approx(outs["two"][1])
+    for fid in range(3):
+        for sub, pat in (("left_disp", "left_%06d_10.png"), ("right_disp", "right_%06d_10.png"), ("gt", "true_%06d_10.png")):
+            a = cv2.imread(str(outs["one"][0] / sub / (pat % fid)), 0)
+            b = cv2.imread(str(outs["two"][0] / sub / (pat % fid)), 0)
+            assert a is not None and b is not None and np.array_equal(a, b), (sub, fid)
+        name = "left_%06d_10_40_150_32.bin" % fid
+        assert (outs["one"][0] / "left_cost" / name).read_bytes() == (outs["two"][0] / "left_cost" / name).read_bytes()
