@@ -171,13 +171,16 @@ __global__ __launch_bounds__(256, 3) void cbca_fused_r1_kernel(const uint32_t *_
 //     pointer and ten immediates (EDGE = false; the registers of the ten clamped offsets pay for the mask ring);
 //     edge blocks keep the clamped offsets (EDGE = true, a launch of its own).
 // Same additions in the same order as the round-1 form: bit-identical (tests/test_gpu_variants.py).
-template <int DC, bool EDGE>
+// DINC / Din_rt: floats between the [d] rows of neighbouring pixels of the INPUT volume (the output always has D):
+// the SGM result of a range that is not a multiple of 4 comes with rows padded to one (post_api.cu).
+template <int DC, int DINC, bool EDGE>
 __global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uint32_t *__restrict__ rec0, const uint32_t *__restrict__ rec1,
                                                                        int pitch, const float *__restrict__ vol, float *__restrict__ out,
-                                                                       int h, int w, int D_rt, int direction, int rows_per_band,
+                                                                       int h, int w, int D_rt, int Din_rt, int direction, int rows_per_band,
                                                                        int xb_first, int n_left, int xb_right)
 {
     const int D = DC ? DC : D_rt;
+    const int Din = DINC ? DINC : Din_rt;
     const int d = threadIdx.x;
     if (d >= D) return;
     // interior launch: consecutive blocks from xb_first; edge launch: n_left blocks from pixel 0, the rest from xb_right
@@ -189,9 +192,9 @@ __global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uin
     int offs[EDGE ? kFN : 1];                // EDGE: element offsets of the 10 columns, clamped into the row
     if (EDGE) {
 #pragma unroll
-        for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * D + d;
+        for (int j = 0; j < kFN; ++j) offs[j] = min(max(xb - kFR + j, 0), w - 1) * Din + d;
     }
-    const int col0 = (xb - kFR) * D + d;     // !EDGE: offset of column xb - R; column j is + j * D
+    const int col0 = (xb - kFR) * Din + d;   // !EDGE: input offset of column xb - R; column j is + j * Din
     bool pix_ok[kFB], match_ok[kFB];
     int xm[kFB];
 #pragma unroll
@@ -211,20 +214,20 @@ __global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uin
         for (int i = 0; i < kFB; ++i) { hs[u][i] = 0.f; hc[u][i] = 0; }
 #pragma unroll
     for (int u = 0; u < (kFW + 1) / 2; ++u) vring[u] = 0;
-    const int row_elems = w * D;
+    const int row_elems = w * D, in_row_elems = w * Din;
 
     // costs and arm records of the row whose sums come next, requested one iteration ahead
     float v[kFN];
     uint32_t own_n[kFB], oth_n[kFB];
     auto request_row = [&](int r) {
         if (EDGE) {
-            const int vbase = r * row_elems;
+            const int vbase = r * in_row_elems;
 #pragma unroll
             for (int j = 0; j < kFN; ++j) v[j] = __ldg(vol + (vbase + offs[j]));
         } else {
-            const float *prow = vol + ((size_t)r * row_elems + col0);
+            const float *prow = vol + ((size_t)r * in_row_elems + col0);
 #pragma unroll
-            for (int j = 0; j < kFN; ++j) v[j] = __ldg(prow + j * D);
+            for (int j = 0; j < kFN; ++j) v[j] = __ldg(prow + j * Din);
         }
         const int rbase = r * pitch;
 #pragma unroll
@@ -285,7 +288,7 @@ __global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uin
                         }
                     }
                     const float centre = hs[(u + 1 + kFR) % kFW][i];
-                    const int oidx = EDGE ? obase + offs[kFR + i] : obase + col0 + (kFR + i) * D;
+                    const int oidx = obase + (xb + i) * D + d;
                     out[oidx] = match_ok[i] ? __fdiv_rn(sum, (float)cnt) : centre;
                 }
             }
@@ -297,9 +300,10 @@ __global__ __launch_bounds__(256, EDGE ? 2 : 3) void cbca_fused_kernel(const uin
 
 // x0c / x1c: int16 arms [4][h][w] of the two views; rec: scratch for 2 * h * pitch records
 int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
-                      int D, int direction, int L1)
+                      int D, int direction, int L1, int in_pitch)
 {
-    STEREO_REQUIRE((size_t)h * w * D < (size_t)1 << 31, "volume too large for 32-bit indexing");
+    STEREO_REQUIRE((size_t)h * w * (size_t)std::max(D, in_pitch) < (size_t)1 << 31, "volume too large for 32-bit indexing");
+    STEREO_REQUIRE(in_pitch == 0 || in_pitch >= D, "input pitch %d smaller than the disparity range %d", in_pitch, D);
     STEREO_REQUIRE(D <= 256 && L1 - 1 <= kFR, "fused CBCA: D <= 256 and L1 <= %d, got D=%d L1=%d", kFR + 1, D, L1);
     const int pitch = (w + 3) / 4 * 4 + 4;
     DevBuf &buf = ctx->cbca_rec[direction > 0];
@@ -315,7 +319,7 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
     // STEREO_CBCA_KERNEL=1 keeps the round-1 form as the cross-check
     static const bool round1 = [] { const char *e = getenv("STEREO_CBCA_KERNEL"); return e && atoi(e) == 1; }();
     const int nbx = (w + kFB - 1) / kFB;
-    if (round1) {
+    if (round1 && (in_pitch == 0 || in_pitch == D)) {
         cbca_fused_r1_kernel<<<dim3(nbx, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band);
     } else {
         // interior blocks: the window xb - R .. xb + 1 + R lies inside the image
@@ -323,18 +327,21 @@ int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const
         int first_right = n_left;                                                      // first block with xb + kFB + R > w
         while (first_right < nbx && first_right * kFB + kFB + kFR <= w) ++first_right;
         const int n_int = first_right - n_left, n_edge = nbx - n_int;
+        const int Din = in_pitch > 0 ? in_pitch : D;
         auto launch = [&](auto interior, auto edge) {
             if (n_int > 0)
-                interior<<<dim3(n_int, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band,
-                                                                     n_left * kFB, 0, 0);
+                interior<<<dim3(n_int, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, Din, direction,
+                                                                     rows_per_band, n_left * kFB, 0, 0);
             if (n_edge > 0)
-                edge<<<dim3(n_edge, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, direction, rows_per_band, 0,
-                                                                  n_left, first_right * kFB);
+                edge<<<dim3(n_edge, bands), nt, 0, ctx->stream>>>(rec0, rec1, pitch, vol, out, h, w, D, Din, direction,
+                                                                  rows_per_band, 0, n_left, first_right * kFB);
         };
-        // disparity ranges known at compile time: the benchmark's 228, the reference's default 201; any other at run time
-        if (D == 228) launch(cbca_fused_kernel<228, false>, cbca_fused_kernel<0, true>);
-        else if (D == 201) launch(cbca_fused_kernel<201, false>, cbca_fused_kernel<0, true>);
-        else launch(cbca_fused_kernel<0, false>, cbca_fused_kernel<0, true>);
+        // disparity ranges known at compile time: the benchmark's 228, the reference's default 201 (whose SGM result
+        // comes with rows of 204 floats); any other at run time
+        if (D == 228 && Din == 228) launch(cbca_fused_kernel<228, 228, false>, cbca_fused_kernel<0, 0, true>);
+        else if (D == 201 && Din == 201) launch(cbca_fused_kernel<201, 201, false>, cbca_fused_kernel<0, 0, true>);
+        else if (D == 201 && Din == 204) launch(cbca_fused_kernel<201, 204, false>, cbca_fused_kernel<0, 0, true>);
+        else launch(cbca_fused_kernel<0, 0, false>, cbca_fused_kernel<0, 0, true>);
         ctx->launches += (n_int > 0 && n_edge > 0) ? 1 : 0;
     }
     ctx->launches += 3;

@@ -203,13 +203,16 @@ int launch_cbca(stereo_ctx *ctx, const short *x0c, const short *x1c, const float
 int launch_cbca_separable(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *hsum,
                           uint8_t *hcnt, float *out, int h, int w, int D, int direction, int L1);
 // cbca_fused.cu
+// in_pitch: floats between the [d] rows of two neighbouring pixels of `vol` (0: D; the output always has pitch D)
 int launch_cbca_fused(stereo_ctx *ctx, const short *x0c, const short *x1c, const float *vol, float *out, int h, int w,
-                      int D, int direction, int L1);
+                      int D, int direction, int L1, int in_pitch = 0);
 int launch_volume_std(stereo_ctx *ctx, const float *vol, size_t n, float *result, int slot = 0);
 // the same with the arg max over D of every [x][d] row written to `wta` (uint8 [h*w]; D <= 256) in the same pass
 int launch_volume_std_wta(stereo_ctx *ctx, const float *vol, size_t n_pixels, int D, float *result, uint8_t *wta, int slot);
 int launch_box_agg(stereo_ctx *ctx, const float *in, int h, int w, int D, int kw, int kh, float *out);
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out);
+int launch_scale_pad(stereo_ctx *ctx, const float *in, size_t n_pixels, int D, int Dp, const float *stdp, int mode,
+                     float *out);
 // What the SGM kernels fuse in besides the four paths (all optional):
 //   final_scale  factor of the last path's sum: 0.25 (nyu.lua:61,64 `/ 4`), 0.125 after eight paths
 //   wta          uint8 [h][w]: arg min over D of the final result (the nyu_sgm stage image, post.lua:159); D <= 256

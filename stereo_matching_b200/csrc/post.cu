@@ -578,6 +578,33 @@ __global__ void scale_kernel(const float *__restrict__ in, size_t n, const float
     }
 }
 
+// The same pass for a volume whose [x][d] rows are not 16-byte aligned (D % 4 != 0, the reference's default 201):
+// the output gets rows of Dp = D rounded up to 4 floats, the Dp - D slots behind every row filled with kSgmBig
+// ("no such disparity": never the minimum of a scanline step, and it stays that way through every addition), so
+// that the aligned SGM kernels can run on it as a volume of Dp disparities.
+__global__ void scale_pad_kernel(const float *__restrict__ in, size_t n_pixels, int D, int Dp,
+                                 const float *__restrict__ stdp, int mode, float *__restrict__ out)
+{
+    const ConstDivisor sd = make_divisor(stdp[0]);
+    const float sign = mode == 1 ? -1.f : 1.f;
+    const size_t total = n_pixels * Dp;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t px = i / Dp;
+        const int d = (int)(i - px * Dp);
+        out[i] = d < D ? __fmul_rn(div_exact(__ldg(in + px * D + d), sd), sign) : kSgmBig;
+    }
+}
+
+int launch_scale_pad(stereo_ctx *ctx, const float *in, size_t n_pixels, int D, int Dp, const float *stdp, int mode,
+                     float *out)
+{
+    ProfScope prof(ctx, STEREO_K_VOLSTD);
+    scale_pad_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(in, n_pixels, D, Dp, stdp, mode, out);
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 int launch_scale(stereo_ctx *ctx, const float *in, size_t n, const float *stdp, int mode, float *out)
 {
     ProfScope prof(ctx, STEREO_K_VOLSTD);

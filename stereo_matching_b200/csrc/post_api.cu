@@ -78,8 +78,12 @@ static int carve_maps(stereo_ctx *ctx, int h, int w, int gauss_n, PostMaps *m)
 static constexpr size_t kVolSlack = 256;
 
 static int cbca_dev(stereo_ctx *ctx, const stereo_post_params *p, const short *x0c, const short *x1c, const float *vol,
-                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0)
+                    float *tmp, float *out, int h, int w, int D, int direction, int slot = 0, int in_pitch = 0)
 {
+    if (in_pitch != 0 && in_pitch != D) {
+        STEREO_REQUIRE(!p->cbca_exact && D <= 256 && p->L1 <= 5, "padded input rows are read by the fused CBCA kernel only");
+        return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1, in_pitch);
+    }
     if (p->cbca_exact || D > 512) return launch_cbca(ctx, x0c, x1c, vol, out, h, w, D, direction);
     // one fused pass (cbca_fused.cu); arms longer than 5 take the two-pass separable kernels
     if (D <= 256 && p->L1 <= 5) return launch_cbca_fused(ctx, x0c, x1c, vol, out, h, w, D, direction, p->L1);
@@ -151,7 +155,17 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
     const bool fused_cbca = !p->cbca_exact && D <= 256 && p->L1 <= 5;
     // everything is reserved up front: a reallocation (cudaFree) in the middle of the two-stream section would
     // serialise it.  Four working volumes per side: result, SGM scratch, and what they read.
-    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox + kVolSlack));
+    // A range that is not a multiple of 4 (the reference's default 201) makes every [x][d] row of a volume start off
+    // the 16-byte grid, which costs the SGM kernels a third of their speed (aligned supersets, 4-byte accesses).  When
+    // SGM sits between two fused CBCA calls, the scale pass in front of it writes rows padded to Dp = 4 * ceil(D / 4)
+    // floats with "no such disparity" in the padding, SGM runs as a range of Dp (the padded slots never win a minimum
+    // and never turn into NaN: kSgmBig, then +inf in the sums), and the CBCA behind it reads rows of Dp.  Same bits
+    // for every real disparity.  STEREO_POST_PAD=0 switches it off (cross-check).
+    static const bool pad_ok = [] { const char *e = getenv("STEREO_POST_PAD"); return !(e && atoi(e) == 0); }();
+    const int Dp = (D + 3) & ~3;
+    const bool padded = pad_ok && Dp != D && p->sgm == 1 && p->nyu_cost_agg_2 > 0 && fused_cbca;
+    const size_t nvox_alloc = hw * (size_t)(padded ? Dp : D);
+    for (int i = 0; i < 8; ++i) STEREO_TRY(ctx->post_vol[i].reserve(sizeof(float) * nvox_alloc + kVolSlack));
     if (!fused_cbca && !p->cbca_exact)
         for (int i = 0; i < 2; ++i) STEREO_TRY(ctx->post_cnt[i].reserve(nvox));
     STEREO_TRY(ctx->scratch.reserve(sizeof(double) * 4 * (size_t)std::max(1184, wta_moments_max_blocks(ctx))));
@@ -213,9 +227,11 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
         }
         {   // post.lua:146,152: lu = (lu / lu:std()) * -1   (without SGM: lu / lu:std())
             float *dst = take();
-            STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, p->sgm == 1 ? 1 : 0, dst));
+            if (padded) STEREO_TRY(launch_scale_pad(ctx, cur, hw, D, Dp, stdp, 1, dst));
+            else STEREO_TRY(launch_scale(ctx, cur, nvox, stdp, p->sgm == 1 ? 1 : 0, dst));
             advance(dst);
         }
+        const int Dsgm = padded ? Dp : D;        // the range the SGM kernels see
         if (p->sgm == 1) {
             // post.lua:152-155 + nyu.lua:47-75
             for (int it = 0; it < p->sgm_i; ++it) {
@@ -228,7 +244,7 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
                 // post.lua:159 lu:min(2): written by the last pass when somebody wants it
                 const bool want_map = last_iter && (stages[2 + side] || p->nyu_cost_agg_2 <= 0);
                 ex.wta = want_map ? final_map : nullptr;
-                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, D, sp, direction, ex));
+                STEREO_TRY(launch_sgm(ctx, m.guide_l, m.guide_r, cur, dst, tmp, h, w, Dsgm, sp, direction, ex));
                 pool.push_back(tmp);
                 advance(dst);
                 have_final_map = want_map;
@@ -236,11 +252,11 @@ static int post_dev(stereo_ctx *ctx, const float *left_cost, const float *right_
             if (stages[2 + side])
                 STEREO_CUDA_CHECK(cudaMemcpyAsync(stages[2 + side], final_map, hw, cudaMemcpyDeviceToDevice, ctx->stream));
         }
-        // nyu_cost_agg_2 (post.lua:171-186)
+        // nyu_cost_agg_2 (post.lua:171-186); the first call reads the SGM result (rows of Dsgm floats)
         for (int i = 0; i < p->nyu_cost_agg_2; ++i) {
             float *dst = take();
             float *tmp = take();
-            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side));
+            STEREO_TRY(cbca_dev(ctx, p, m.arms_l, m.arms_r, cur, tmp, dst, h, w, D, direction, side, i == 0 ? Dsgm : D));
             pool.push_back(tmp);
             advance(dst);
         }

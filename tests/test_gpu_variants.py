@@ -115,6 +115,47 @@ def test_materialising_store_paths_agree_bit_for_bit(tmp_path):
     assert np.array_equal(outs["bulk"]["b_left_disp"], np.argmax(lv, axis=2).astype(np.uint8))
 
 
+PAD_CHILD = r"""
+import os, sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib
+ctx = _lib.Context(0)
+out = {}
+for D, h, w in ((201, 41, 263), (33, 30, 100), (255, 20, 70), (5, 12, 40)):
+    rng = np.random.default_rng(D)
+    lv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    rv = (rng.standard_normal((h, w, D)) * 10 + 20).astype(np.float32)
+    ld, rd = ctx.wta(lv)[0], ctx.wta(rv)[0]
+    for paths in (4, 8):
+        p = _lib.default_post_params()
+        p.sgm_paths = paths
+        st = ctx.post(lv, rv, ld, rd, p)
+        for k, v in st.items():
+            out["%d_%d_%s" % (D, paths, k)] = v
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_padded_sgm_rows_give_the_same_chain_bit_for_bit(tmp_path):
+    """Disparity ranges that are not a multiple of 4 (the reference's default 201): the chain pads the rows of the SGM
+    input to a multiple of 4 floats with "no such disparity" and runs the aligned SGM kernels on it (default) - every
+    stage map and the final float map must equal the chain on unpadded rows (STEREO_POST_PAD=0, the unaligned code
+    path of the same kernels) bit for bit, with 4 and with 8 paths."""
+    outs = {}
+    for name, env in (("padded", {}), ("plain", {"STEREO_POST_PAD": "0"})):
+        e = dict(os.environ)
+        e.update(env)
+        out = tmp_path / (name + ".npz")
+        r = subprocess.run([sys.executable, "-c", PAD_CHILD, ROOT, str(out)], env=e, capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[name] = np.load(out)
+    assert sorted(outs["padded"].files) == sorted(outs["plain"].files) and len(outs["plain"].files) == 4 * 2 * 9
+    for k in outs["plain"].files:
+        assert np.array_equal(outs["padded"][k], outs["plain"][k]), k
+
+
 CBCA_CHILD = r"""
 import os, sys
 import numpy as np
