@@ -585,13 +585,24 @@ __global__ void scale_kernel(const float *__restrict__ in, size_t n, const float
 __global__ void scale_pad_kernel(const float *__restrict__ in, size_t n_pixels, int D, int Dp,
                                  const float *__restrict__ stdp, int mode, float *__restrict__ out)
 {
+    // a warp per pixel: lane q writes float4 q, q + 32, ... of the padded row (16-byte stores), reading four
+    // consecutive 4-byte words of the unpadded one
     const ConstDivisor sd = make_divisor(stdp[0]);
     const float sign = mode == 1 ? -1.f : 1.f;
-    const size_t total = n_pixels * Dp;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const size_t px = i / Dp;
-        const int d = (int)(i - px * Dp);
-        out[i] = d < D ? __fmul_rn(div_exact(__ldg(in + px * D + d), sd), sign) : kSgmBig;
+    const int lane = threadIdx.x & 31, q4 = Dp >> 2;
+    const size_t warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+    for (size_t px = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; px < n_pixels; px += warps) {
+        const float *src = in + px * D;
+        float4 *dst = reinterpret_cast<float4 *>(out + px * Dp);
+        for (int q = lane; q < q4; q += 32) {
+            float v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int d = 4 * q + e;
+                v[e] = d < D ? __fmul_rn(div_exact(__ldg(src + d), sd), sign) : kSgmBig;
+            }
+            dst[q] = make_float4(v[0], v[1], v[2], v[3]);
+        }
     }
 }
 
