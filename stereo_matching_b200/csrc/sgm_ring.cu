@@ -17,6 +17,8 @@
 // by two more warps per CTA instead of by an elementwise pass - the extra hand-over per stage cost the shallow
 // pipelines of these kernels four times what the pass costs.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "sgm_step.cuh"
@@ -376,8 +378,8 @@ RingShape ring_shape(int arrays, int nw, int D, bool horizontal, bool aligned, s
         return horizontal ? (size_t)arrays * nw * ring_slot_bytes(aligned, (uint32_t)G * D)
                           : (size_t)arrays * G * ring_slot_bytes(aligned, (uint32_t)nw * D);
     };
-    int G = horizontal ? 16 : 2;
-    while (G > 1 && stage(G) > stage_target) G = horizontal ? G - 1 : 1;
+    int G = horizontal ? 16 : 4;
+    while (G > 1 && stage(G) > stage_target) --G;
     int S = (int)std::min<size_t>(kMaxStages, budget / stage(G));
     while (S < 2 && G > 1) {
         --G;
@@ -391,9 +393,17 @@ template <int KPL, int NW, int DIR, bool ALIGNED>
 int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float *cvol, float *out_a, float *out_b,
                   int h, int w, int D, const SgmParams &p, const SgmExtras &ex)
 {
-    const RingShape sh_h = ring_shape(1, NW, D, true, ALIGNED, 32 * 1024, 96 * 1024);
-    const RingShape sh_v2 = ring_shape(3, NW, D, false, ALIGNED, 24 * 1024, 72 * 1024);
-    const RingShape sh_v3 = ring_shape(2, NW, D, false, ALIGNED, 16 * 1024, 72 * 1024);
+    // stage size / ring budget in KB per kernel; STEREO_SGM_RING="h_stage,h_budget,v2_stage,v2_budget,v3_stage,v3_budget"
+    // overrides them (tuning sweeps, scripts/sgm_ring_sweep.py)
+    static int cfg[6] = {32, 96, 24, 72, 16, 72};
+    static const bool cfg_read = [] {
+        if (const char *e = getenv("STEREO_SGM_RING")) sscanf(e, "%d,%d,%d,%d,%d,%d", cfg, cfg + 1, cfg + 2, cfg + 3, cfg + 4, cfg + 5);
+        return true;
+    }();
+    (void)cfg_read;
+    const RingShape sh_h = ring_shape(1, NW, D, true, ALIGNED, (size_t)cfg[0] * 1024, (size_t)cfg[1] * 1024);
+    const RingShape sh_v2 = ring_shape(3, NW, D, false, ALIGNED, (size_t)cfg[2] * 1024, (size_t)cfg[3] * 1024);
+    const RingShape sh_v3 = ring_shape(2, NW, D, false, ALIGNED, (size_t)cfg[4] * 1024, (size_t)cfg[5] * 1024);
     if (sh_h.S < 2 || sh_v2.S < 2 || sh_v3.S < 2) {
         set_error("sgm ring: disp_range %d does not fit the shared-memory stages", D);
         return STEREO_E_LIMIT;
