@@ -32,14 +32,9 @@ namespace {
 constexpr int kMaxStages = 8;
 constexpr int kBarBytes = 2 * 8 * kMaxStages;      // full and empty barriers
 
-// Byte images of sgm_prep_kernel: want[path][h][w], code[path][h][pitch] with pitch = w + 2 * pad; from them
-// sgm_bits_kernel builds bits[path][h][w][32 lanes] (KPL <= 8: one byte per lane, bit k = "both" of disparity
-// lane * KPL + k): what a scanline step reads is ONE byte per lane, requested kAhead steps ahead.  (The first ncu
-// source page of the vertical kernels had 29 % of all stall samples on the first use of the eight per-disparity
-// bytes that were requested one step ahead: every step of a vertical path reads another image row of `code`.)
-constexpr int kAhead = 3;
+// Byte images of sgm_prep_kernel: want[path][h][w], code[path][h][pitch] with pitch = w + 2 * pad
 struct SgmAux {
-    const uint8_t *want, *code, *bits;
+    const uint8_t *want, *code;
     int pad, pitch;
     // the last pass scales its sum by `final_scale` (0.25: nyu.lua:61,64 `/ 4`; 1: more paths follow) and, when
     // `wta` is set, writes the arg min over D of every pixel's result (the nyu_sgm stage image, post.lua:159)
@@ -145,27 +140,13 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
     for (int j = 0; j < KPL / 4; ++j) valid4[j] = d0 + 4 * j < D;      // whole float4s when D % 4 == 0
     const bool has_below = lane > 0, has_above = d0 + KPL < D;
 
-    // penalty cases of the coming steps: one byte per lane (kBits) or KPL + 1 bytes (D > 256), requested ahead of use
-    constexpr bool kBits = KPL <= 8;
+    // classified guide differences of the NEXT step (bytes; one step ahead of their use)
     const uint8_t *cptr = aux.code + ((size_t)SD * h + y) * aux.pitch + aux.pad + x + d0 * DIR;
     const uint8_t *wptr = aux.want + ((size_t)SD * h + y) * w + x;
-    const uint8_t *bptr = aux.bits + (((size_t)SD * h + y) * w + x) * 32 + lane;
-    const ptrdiff_t cstep = (ptrdiff_t)dy * aux.pitch + dx, wstep = (ptrdiff_t)dy * w + dx, bstep = wstep * 32;
-    int code_n[kBits ? 1 : KPL], want_n = 3;
+    const ptrdiff_t cstep = (ptrdiff_t)dy * aux.pitch + dx, wstep = (ptrdiff_t)dy * w + dx;
+    int code_n[KPL], want_n = 3;
 #pragma unroll
-    for (int k = 0; k < (kBits ? 1 : KPL); ++k) code_n[k] = 0;
-    // kBits: ring of the next kAhead steps' (bits, want); entry i is for step (current + 1 + i)
-    uint32_t bits_q[kAhead], want_q[kAhead];
-#pragma unroll
-    for (int i = 0; i < kAhead; ++i) {
-        bits_q[i] = 0;
-        want_q[i] = 3;
-        if (kBits && 1 + i < steps) {
-            bits_q[i] = __ldg(bptr + (ptrdiff_t)(1 + i) * bstep);
-            want_q[i] = __ldg(wptr + (ptrdiff_t)(1 + i) * wstep);
-        }
-    }
-    uint32_t bits_cur = 0, want_cur = 3;
+    for (int k = 0; k < KPL; ++k) code_n[k] = 0;
 
     float prev[KPL];
 #pragma unroll
@@ -195,30 +176,16 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
             }
         }
         for (int i = 0; i < g_here; ++i, ++step) {
-            int code[kBits ? 1 : KPL];
-            int want = want_n;
-            if (kBits) {
-                // this step's case came in kAhead steps ago; request the one of step + 1 + kAhead
-                if (step > 0) {
-                    bits_cur = bits_q[0];
-                    want_cur = want_q[0];
+            int code[KPL];
 #pragma unroll
-                    for (int i = 0; i + 1 < kAhead; ++i) { bits_q[i] = bits_q[i + 1]; want_q[i] = want_q[i + 1]; }
-                    if (step + kAhead < steps) {
-                        bits_q[kAhead - 1] = __ldg(bptr + (ptrdiff_t)(step + kAhead) * bstep);
-                        want_q[kAhead - 1] = __ldg(wptr + (ptrdiff_t)(step + kAhead) * wstep);
-                    }
-                }
-            } else {
+            for (int k = 0; k < KPL; ++k) code[k] = code_n[k];
+            const int want = want_n;
+            if (step + 1 < steps) {
+                cptr += cstep;
+                wptr += wstep;
 #pragma unroll
-                for (int k = 0; k < KPL; ++k) code[k] = code_n[k];
-                if (step + 1 < steps) {
-                    cptr += cstep;
-                    wptr += wstep;
-#pragma unroll
-                    for (int k = 0; k < KPL; ++k) code_n[k] = __ldg(cptr + k * DIR);
-                    want_n = __ldg(wptr);
-                }
+                for (int k = 0; k < KPL; ++k) code_n[k] = __ldg(cptr + k * DIR);
+                want_n = __ldg(wptr);
             }
             // costs (and running sums) of this step from the stage
             const int slot = kH ? warp : i;
@@ -297,8 +264,7 @@ __device__ __forceinline__ void sgm_ring_scan(const SgmAux &aux, const float *__
 #pragma unroll
                 for (int k = 0; k < KPL; ++k) val[k] = c[k];
             } else {
-                if constexpr (kBits) sgm_step_bits<SD, KPL>(pen, want_cur == 1, c, prev, bits_cur, has_below, has_above, val);
-                else sgm_step_coded<SD, KPL>(pen, want, c, prev, code, has_below, has_above, val);
+                sgm_step_coded<SD, KPL>(pen, want, c, prev, code, has_below, has_above, val);
             }
             float best = kSgmBig;         // arg min over this lane's disparities (lowest index wins ties)
             int best_k = 0;
@@ -376,27 +342,6 @@ __global__ void sgm_prep_kernel(const float *__restrict__ x0, const float *__res
     }
 }
 
-// bits[sd][y][x][lane]: bit k = (code of disparity lane * KPL + k at the matched pixel == want of (y, x)), i.e. the
-// original's "both steps small" / "both steps large" test of the penalty selection, for all four paths
-template <int KPL, int DIR>
-__global__ void sgm_bits_kernel(const uint8_t *__restrict__ want, const uint8_t *__restrict__ code, int h, int w, int pad,
-                                int pitch, uint8_t *__restrict__ bits)
-{
-    const size_t total = (size_t)4 * h * w * 32;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-        const int lane = (int)(idx & 31);
-        const size_t pix = idx >> 5;                       // (sd * h + y) * w + x
-        const int x = (int)(pix % w);
-        const size_t row = pix / w;                        // sd * h + y
-        const int wv = want[pix];
-        const uint8_t *c = code + row * pitch + pad + x + lane * KPL * DIR;
-        uint32_t b = 0;
-#pragma unroll
-        for (int k = 0; k < KPL; ++k) b |= (uint32_t)(c[k * DIR] == wv) << k;
-        bits[idx] = (uint8_t)b;
-    }
-}
-
 // both horizontal paths in one grid: blockIdx.y = 0 writes a (left->right), 1 writes b (right->left)
 template <int KPL, int NW, int DIR, bool ALIGNED>
 __global__ __launch_bounds__((NW + 1) * 32) void sgm_ring_h_kernel(SgmAux aux, const float *__restrict__ cvol,
@@ -468,21 +413,15 @@ int launch_ring_t(stereo_ctx *ctx, const float *x0, const float *x1, const float
     aux.pad = 32 * KPL + 4;
     aux.pitch = w + 2 * aux.pad;
     DevBuf &buf = ctx->sgm_aux[DIR > 0];
-    const size_t want_bytes = (size_t)4 * h * w, code_bytes = ((size_t)4 * h * aux.pitch + 15) & ~(size_t)15;
-    const size_t bits_bytes = KPL <= 8 ? (size_t)4 * h * w * 32 : 0;
-    STEREO_TRY(buf.reserve(want_bytes + code_bytes + bits_bytes));
-    uint8_t *want = buf.as<uint8_t>(), *code = want + want_bytes, *bits = code + code_bytes;
+    const size_t want_bytes = (size_t)4 * h * w, code_bytes = (size_t)4 * h * aux.pitch;
+    STEREO_TRY(buf.reserve(want_bytes + code_bytes));
+    uint8_t *want = buf.as<uint8_t>(), *code = want + want_bytes;
     aux.want = want;
     aux.code = code;
-    aux.bits = bits;
     aux.final_scale = ex.final_scale;
     aux.wta = ex.wta;
     sgm_prep_kernel<<<std::min<size_t>(((size_t)h * aux.pitch + 255) / 256, 148 * 8), 256, 0, ctx->stream>>>(
         x0, x1, h, w, p.tau_so, aux.pad, aux.pitch, want, code);
-    if constexpr (KPL <= 8) {
-        sgm_bits_kernel<KPL, DIR><<<148 * 16, 256, 0, ctx->stream>>>(want, code, h, w, aux.pad, aux.pitch, bits);
-        ctx->launches += 1;
-    }
 
     auto kh = sgm_ring_h_kernel<KPL, NW, DIR, ALIGNED>;
     auto kv2 = sgm_ring_v_kernel<2, KPL, NW, DIR, ALIGNED>;

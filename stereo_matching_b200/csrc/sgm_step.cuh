@@ -116,41 +116,4 @@ __device__ __forceinline__ void sgm_step_coded(const SgmPenalties<SD> &pen, int 
     }
 }
 
-// The same step with the penalty case of the lane's KPL disparities as ONE value: bit k of `bits` says whether
-// "both" holds for disparity k (code[k] == want, precomputed per pixel and lane by sgm_bits_kernel), `d1_lt` whether
-// D1 < tau for this scanline step.  One small load per lane and step instead of KPL + 1, no compares.
-template <int SD, int KPL>
-__device__ __forceinline__ void sgm_step_bits(const SgmPenalties<SD> &pen, bool d1_lt, const float (&c)[KPL],
-                                              const float (&prev)[KPL], uint32_t bits, bool has_below, bool has_above,
-                                              float (&val)[KPL])
-{
-    float pmin = prev[0];
-#pragma unroll
-    for (int k = 1; k < KPL; ++k) pmin = fminf(pmin, prev[k]);
-    {
-        int key = __float_as_int(pmin);
-        key ^= (key >> 31) & 0x7fffffff;
-        key = __reduce_min_sync(0xffffffffu, key);
-        key ^= (key >> 31) & 0x7fffffff;
-        pmin = __int_as_float(key);
-    }
-    float below = __shfl_up_sync(0xffffffffu, prev[KPL - 1], 1);      // prev[d0 - 1]
-    float above = __shfl_down_sync(0xffffffffu, prev[0], 1);          // prev[d0 + KPL]
-    below = has_below ? below : kSgmBig;
-    above = has_above ? above : kSgmBig;
-    const float P2x = d1_lt ? pen.P2a : pen.P2b, P1mx = d1_lt ? pen.P1a_m : pen.P1b_m, P1px = d1_lt ? pen.P1a_p : pen.P1b_p;
-    const float pmin_p2x = __fadd_rn(pmin, P2x), pmin_p2c = __fadd_rn(pmin, pen.P2c);
-#pragma unroll
-    for (int k = 0; k < KPL; ++k) {
-        const bool both = (bits >> k) & 1u;
-        const float P1m = both ? P1mx : pen.P1c_m, P1p = SD < 2 ? P1m : (both ? P1px : pen.P1c_p);
-        float m = fminf(prev[k], both ? pmin_p2x : pmin_p2c);
-        const float pm = k > 0 ? prev[k > 0 ? k - 1 : 0] : below;
-        const float pp = k < KPL - 1 ? prev[k < KPL - 1 ? k + 1 : 0] : above;
-        m = fminf(m, __fadd_rn(pm, P1m));
-        m = fminf(m, __fadd_rn(pp, P1p));
-        val[k] = __fadd_rn(__fadd_rn(c[k], m), -pmin);
-    }
-}
-
 }  // namespace stereo
