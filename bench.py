@@ -949,7 +949,25 @@ def run_post_chain(args):
         fe1.record(hz.stream)
         torch.cuda.synchronize()
         full_ms = fe0.elapsed_time(fe1) / n_full
-    extra = {"kernel_class_ms_per_pair": classes, "serial_ms_per_pair": serial_ms,
+    # what the SGM kernels really move (ncu dram bytes of one volume's three launches, profiles/ncu_metrics.json): the
+    # four paths need 11 volume transfers where the algorithmic count has 2
+    sgm_traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_metrics.json")) as f:
+            table = json.load(f)
+        per_volume = {}
+        for name, row in table.items():
+            for key in ("sgm_ring_h_kernel", "sgm_ring_v_kernel<2", "sgm_ring_v_kernel<3"):
+                if key in name and key not in per_volume and row.get("dram_bytes"):
+                    per_volume[key] = row["dram_bytes"]
+        if len(per_volume) == 3 and classes.get("sgm"):
+            total = sum(per_volume.values())
+            sgm_traffic = {"dram_bytes_per_volume": total, "gbs": 2 * total / (classes["sgm"] / 1e3) / 1e9,
+                           "frac_of_hbm_peak": 2 * total / (classes["sgm"] / 1e3) / 1e9 / pk["hbm_gbs"],
+                           "note": "DRAM traffic (ncu) / kernel-class time: how busy HBM is, not the algorithmic roofline"}
+    except Exception:
+        pass
+    extra = {"kernel_class_ms_per_pair": classes, "serial_ms_per_pair": serial_ms, "sgm_dram_traffic": sgm_traffic,
              "three_px_error_pair0_after_post": so.three_pixel_error(final0, gt[0]),
              "three_px_error_pair0_raw_wta": so.three_pixel_error(vols[0][2].cpu().numpy(), gt[0]),
              "full_pipeline": {"workload": "stereo_pairs_post_dev: trunk + materialised volumes + post chain per pair, final maps only",
