@@ -17,6 +17,7 @@
 
 #include "common.cuh"
 #include "exact_div.cuh"
+#include "median25.cuh"
 #include "sgm_step.cuh"
 
 namespace stereo {
@@ -939,6 +940,17 @@ __global__ void median2d_kernel(const float *__restrict__ img, int h, int w, int
     int id = blockIdx.x * blockDim.x + threadIdx.x;
     if (id >= h * w) return;
     int x = id % w, y = id / w;
+    if (radius == 2 && x >= 2 && x < w - 2 && y >= 2 && y < h - 2) {
+        // the 5 x 5 window of nyu.lua:107 inside the image: median of 25 by a compare-exchange network in registers
+        // (median25.cuh) instead of an insertion sort in local memory - the same value, whatever the order
+        float v[25];
+#pragma unroll
+        for (int dx = 0; dx < 5; ++dx)
+#pragma unroll
+            for (int dy = 0; dy < 5; ++dy) v[dx * 5 + dy] = __ldg(img + (y - 2 + dy) * w + (x - 2 + dx));
+        out[id] = median25(v);
+        return;
+    }
     float xs[11 * 11];
     int n = 0;
     for (int xx = x - radius; xx <= x + radius; ++xx)
