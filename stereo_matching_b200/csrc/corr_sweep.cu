@@ -86,6 +86,38 @@ __device__ __forceinline__ Item decode(const Params &p, int item)
     return it;
 }
 
+// Running arg max over the 32 columns a lane holds of one accumulator chunk.  SIDE 0 (left volume): the disparity
+// falls as the column rises, ">=" keeps the lowest disparity among equals; SIDE 1: it rises, ">" does.  CHECK = false:
+// the caller knows that every disparity of the chunk, for every lane of the warp, lies inside [0, D) (true for most
+// chunks of the band) - no range test per element.
+template <int SIDE, bool CHECK>
+__device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int dbase, int D, float &best, int &best_d)
+{
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        const int d = SIDE == 0 ? dbase - i : dbase + i;
+        const float f = __uint_as_float(v[i]);
+        const bool in = !CHECK || (unsigned)d < (unsigned)D;
+        const bool take = in && (SIDE == 0 ? f >= best : f > best);
+        best = take ? f : best;
+        best_d = take ? d : best_d;
+    }
+}
+
+// The same 32 values into row `trow` of a [pixel][d] staging tile (bulk-store variant); `mine`: this lane's row
+// belongs to the half of the group that is being staged.
+template <int SIDE, bool CHECK>
+__device__ __forceinline__ void stage_chunk(const uint32_t (&v)[32], int dbase, int D, float *trow, bool mine)
+{
+    if (!mine) return;
+    float *tp = trow + dbase;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        const int d = SIDE == 0 ? dbase - i : dbase + i;
+        if (!CHECK || (unsigned)d < (unsigned)D) tp[SIDE == 0 ? -i : i] = __uint_as_float(v[i]);
+    }
+}
+
 // DC: the disparity range as a compile-time constant (0: run-time p.D).  The materialising epilogue stores eight
 // rows of a [x][d] tile per round, one row D +- 1 floats after the other: with D known the eight stores are one
 // pointer and eight immediates, and the range tests compare against a constant - the round-2 ncu source page had
@@ -275,32 +307,27 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                             if (dlo + 62 >= 0 && dlo <= D - 1) {
                                 uint32_t v[32];
                                 tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
-                                // row `lane` of the group, disparity of column i: dbase -+ i
+                                // row `lane` of the group, disparity of column i: dbase -+ i; chunks whose disparities all
+                                // lie inside the range (for every lane) skip the per-element range tests
+                                const bool all_in = dlo >= 0 && dlo + 62 <= D - 1;
+                                const bool scan = WTA && half == 0;
                                 if (it.side == 0) {
                                     const int dbase = xi + kMargin - u0;
-#pragma unroll
-                                    for (int i = 0; i < 32; ++i) {
-                                        const int d = dbase - i;
-                                        const float f = __uint_as_float(v[i]);
-                                        if (mine && (unsigned)d < (unsigned)D) trow[d] = f;
-                                        if (WTA && half == 0) {
-                                            const bool take = (unsigned)d < (unsigned)D && f >= best;
-                                            best = take ? f : best;
-                                            best_d = take ? d : best_d;
-                                        }
+                                    if (all_in) {
+                                        stage_chunk<0, false>(v, dbase, D, trow, mine);
+                                        if (scan) scan_chunk<0, false>(v, dbase, D, best, best_d);
+                                    } else {
+                                        stage_chunk<0, true>(v, dbase, D, trow, mine);
+                                        if (scan) scan_chunk<0, true>(v, dbase, D, best, best_d);
                                     }
                                 } else {
                                     const int dbase = u0 - xi;
-#pragma unroll
-                                    for (int i = 0; i < 32; ++i) {
-                                        const int d = dbase + i;
-                                        const float f = __uint_as_float(v[i]);
-                                        if (mine && (unsigned)d < (unsigned)D) trow[d] = f;
-                                        if (WTA && half == 0) {
-                                            const bool take = (unsigned)d < (unsigned)D && f > best;
-                                            best = take ? f : best;
-                                            best_d = take ? d : best_d;
-                                        }
+                                    if (all_in) {
+                                        stage_chunk<1, false>(v, dbase, D, trow, mine);
+                                        if (scan) scan_chunk<1, false>(v, dbase, D, best, best_d);
+                                    } else {
+                                        stage_chunk<1, true>(v, dbase, D, trow, mine);
+                                        if (scan) scan_chunk<1, true>(v, dbase, D, best, best_d);
                                     }
                                 }
                             }
@@ -339,27 +366,15 @@ __global__ __launch_bounds__(kThreads, 1) void corr_sweep_kernel(Params p)
                         uint32_t v[32];
                         tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + ab * kBlk + part * 32, v);
                         if (WTA) {
+                            const bool all_in = dlo >= 0 && dlo + 62 <= D - 1;
                             if (it.side == 0) {
-                                // d falls as u rises, so ">=" keeps the lowest d among equals
                                 const int dbase = xi + kMargin - u0;
-#pragma unroll
-                                for (int i = 0; i < 32; ++i) {
-                                    const int d = dbase - i;
-                                    const float f = __uint_as_float(v[i]);
-                                    const bool take = (unsigned)d < (unsigned)D && f >= best;
-                                    best = take ? f : best;
-                                    best_d = take ? d : best_d;
-                                }
+                                if (all_in) scan_chunk<0, false>(v, dbase, D, best, best_d);
+                                else scan_chunk<0, true>(v, dbase, D, best, best_d);
                             } else {
                                 const int dbase = u0 - xi;
-#pragma unroll
-                                for (int i = 0; i < 32; ++i) {
-                                    const int d = dbase + i;
-                                    const float f = __uint_as_float(v[i]);
-                                    const bool take = (unsigned)d < (unsigned)D && f > best;
-                                    best = take ? f : best;
-                                    best_d = take ? d : best_d;
-                                }
+                                if (all_in) scan_chunk<1, false>(v, dbase, D, best, best_d);
+                                else scan_chunk<1, true>(v, dbase, D, best, best_d);
                             }
                         }
                         if (VOL) {
