@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libstereo_b200.so")
+# STEREO_B200_LIB: another build of the library (A/B runs of compile-time variants, scripts/build_variant.py)
+LIB_PATH = os.environ.get("STEREO_B200_LIB") or os.path.join(HERE, "libstereo_b200.so")
 
 NET_WIN9, NET_WIN37 = 0, 1
 PREC_FP32, PREC_BF16X3, PREC_BF16 = 0, 1, 2

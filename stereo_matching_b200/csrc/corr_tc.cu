@@ -324,6 +324,10 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
     // default: the row-sweep kernel (corr_sweep.cu); STEREO_CORR_KERNEL=1 keeps the per-tile kernel below as the
     // cross-check, which also serves rows whose margins are too small for the sweep
     static const bool per_tile = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return e && e[0] == '1'; }();
+    // fused WTA of both maps: one sweep per row serves both (corr_both.cu); STEREO_CORR_SWEEPS=2 keeps the two sweeps
+    static const bool two_sweeps = [] { const char *e = getenv("STEREO_CORR_SWEEPS"); return e && e[0] == '2'; }();
+    if (!per_tile && !two_sweeps && !vol && left_disp && right_disp && ml >= corr_sweep_margin())
+        return launch_corr_both(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
     if (!per_tile && ml >= corr_sweep_margin())
         return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_vol, right_vol, left_disp,
                                  right_disp);

@@ -22,14 +22,27 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Bounded wait: a protocol error traps instead of hanging the GPU.
+// Bounded wait: a protocol error traps instead of hanging the GPU.  STEREO_MBAR_HINT (ns): the suspend-time hint of
+// try_wait - without one a waiting warp comes back about every hundred cycles and spends issue slots on the loop.
+#ifndef STEREO_MBAR_HINT
+#define STEREO_MBAR_HINT 4096
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     uint32_t done = 0;
     // not unrolled: the compiler otherwise emits dozens of try_wait copies per call site, which adds up to tens of
     // kilobytes of code in kernels that wait inside unrolled loops
 #pragma unroll 1
-    for (uint32_t spin = 0; spin < (1u << 26); ++spin) {
+    for (uint32_t spin = 0; spin < (1u << (STEREO_MBAR_HINT ? 22 : 26)); ++spin) {
+#if STEREO_MBAR_HINT
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity), "r"((uint32_t)STEREO_MBAR_HINT)
+            : "memory");
+#else
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
@@ -37,6 +50,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
             : "=r"(done)
             : "r"(bar), "r"(parity)
             : "memory");
+#endif
         if (done) return;
     }
     __trap();

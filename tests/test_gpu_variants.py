@@ -40,8 +40,9 @@ np.savez(sys.argv[2], left=out["left_disp"], right=out["right_disp"], lr=out["ou
 """
 
 VARIANTS = [
-    {},                                       # defaults: conv_tc3, conv1_tc, corr_sweep, two lanes
+    {},                                       # defaults: conv_tc3, conv1_tc, corr_both, two lanes
     {"STEREO_CORR_KERNEL": "1"},              # per-tile correlation (corr_tc.cu)
+    {"STEREO_CORR_SWEEPS": "2"},              # one sweep per volume (corr_sweep.cu) instead of one for both maps
     {"STEREO_PAIR_LANES": "1"},
     {"STEREO_PAIR_LANES": "4"},
 ]
@@ -230,3 +231,55 @@ def test_base_model_conv_kernel_families_agree(tmp_path):
     ref = so.trunk_forward(x, layers, "win37_dep9", np.float64)
     for k in ("row_once", "per_tap"):
         assert np.abs(outs[k]["pair"] - ref).max() / np.abs(ref).max() < 6e-5
+
+
+BOTH_CHILD = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from stereo_matching_b200 import _lib
+ctx = _lib.Context(0)
+out = {}
+cases = {"kitti": (2, 7, 1242, 228), "one_block": (2, 5, 128, 64), "narrow": (1, 4, 97, 4), "two_blocks": (1, 3, 256, 256),
+         "ragged": (2, 6, 130, 201), "d1": (1, 5, 700, 1), "wide": (1, 2, 1500, 256), "tiny": (1, 3, 5, 7)}
+for tag, (n, h, w, D) in cases.items():
+    for kind in ("ties", "normal"):
+        rng = np.random.default_rng(h * 1000 + w)
+        if kind == "ties":       # small integers: exact products, many equal scores -> the tie rule decides
+            l = rng.integers(-1, 2, (n, h, w, 64)).astype(np.float32)
+            r = rng.integers(-1, 2, (n, h, w, 64)).astype(np.float32)
+            l[..., 8:] = 0; r[..., 8:] = 0
+        else:
+            l = rng.standard_normal((n, h, w, 64)).astype(np.float32)
+            r = rng.standard_normal((n, h, w, 64)).astype(np.float32)
+        for prec in (_lib.PREC_BF16X3, _lib.PREC_BF16):
+            ld, rd = ctx.corr_wta(l, r, D, prec)
+            out[f"{tag}_{kind}_{prec}_l"], out[f"{tag}_{kind}_{prec}_r"] = ld, rd
+            if len(sys.argv) > 3:
+                lv, rv = ctx.cost_volume(l, r, D, prec)
+                out[f"{tag}_{kind}_{prec}_la"] = lv.argmax(-1).astype(np.uint8)
+                out[f"{tag}_{kind}_{prec}_ra"] = rv.argmax(-1).astype(np.uint8)
+np.savez(sys.argv[2], **out)
+"""
+
+
+def test_one_sweep_maps_equal_the_arg_max_of_the_volumes(tmp_path):
+    """corr_both.cu reads the accumulators of the LEFT sweep along rows (left map) and along columns (right map).
+    Both maps must equal numpy's argmax (first maximum) of the volumes the materialising kernel writes from the same
+    accumulators, and the maps of the two-sweep kernel (STEREO_CORR_SWEEPS=2), bit for bit: images narrower than a
+    block, ending on and just behind a block edge, D = 1 and D = 256, features with many exactly equal scores, and
+    the right map's zero-filled slots x + d >= w."""
+    runs = {}
+    for tag, env, extra in (("both", {}, ["argmax"]), ("two", {"STEREO_CORR_SWEEPS": "2"}, [])):
+        out = tmp_path / f"{tag}.npz"
+        e = dict(os.environ)
+        e.update(env)
+        r = subprocess.run([sys.executable, "-c", BOTH_CHILD, ROOT, str(out)] + extra, env=e, capture_output=True,
+                           text=True, timeout=900)
+        assert r.returncode == 0, r.stderr[-2000:]
+        runs[tag] = np.load(out)
+    keys = [k for k in runs["two"].files]
+    assert len(keys) == 8 * 2 * 2 * 2
+    for k in keys:
+        assert np.array_equal(runs["both"][k], runs["two"][k]), k
+        assert np.array_equal(runs["both"][k], runs["both"][k + "a"]), k
