@@ -280,11 +280,20 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
     static const int max_lanes = [] { const char *e = getenv("STEREO_PAIR_LANES"); int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > 4 ? 4 : v); }();
     int lanes = (tc_corr && !ctx->prof.on) ? max_lanes : 1;
     if (lanes > n) lanes = n;
+    // Fused path: the features of `group` consecutive pairs stay in the lane's planar buffer and ONE correlation
+    // launch serves them - a single pair is 375 rows for 148 persistent CTAs (the third round runs half empty).
+    // The trunk writes left and right of a pair as neighbouring images: [hi | lo][pair][side][h][8][wf][8].
+    static const int max_group = [] { const char *e = getenv("STEREO_CORR_GROUP"); int v = e ? atoi(e) : 4; return v < 1 ? 1 : (v > 16 ? 16 : v); }();
+    int group = 1;
+    if (tc_corr && !left_vol && !right_vol && corr_both_enabled()) {
+        group = n / lanes < max_group ? n / lanes : max_group;
+        if (group < 1) group = 1;
+    }
     cudaStream_t lane_stream[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
     if (tc_corr) {
         // tensor-core path: only the image statistics (all pairs at once); layer 1 reads the uint8 images itself
         STEREO_TRY(launch_pair_stats(ctx, left_rgb, right_rgb, n, h, w));
-        STEREO_TRY(ensure_planar(ctx, 1, h, w, D, &pf[0], 0));
+        STEREO_TRY(ensure_planar(ctx, group, h, w, D, &pf[0], 0));
         if (lanes > 1) {
             if (!ctx->ev_fork) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
             if (!ctx->ev_join) STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
@@ -300,7 +309,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             for (int l = 1; l < lanes; ++l) {
                 cudaStream_t saved = ctx->stream;
                 ctx->stream = lane_stream[l];                   // the first-use memset of the margins goes to the lane
-                int rc = ensure_planar(ctx, 1, h, w, D, &pf[l], l);
+                int rc = ensure_planar(ctx, group, h, w, D, &pf[l], l);
                 ctx->stream = saved;
                 STEREO_TRY(rc);
             }
@@ -313,7 +322,7 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
         ~LaneStream() { ctx->stream = saved; }
     };
     for (int i = 0; i < n; ++i) {
-        const int lane = i % lanes;
+        const int lane = (i / group) % lanes, slot = i % group;
         LaneStream on_lane(ctx, lane_stream[lane]);
         // left and right of one pair go through the trunk as a batch of two
         float *padded_lane = padded + (size_t)lane * 2 * pad_img;
@@ -331,16 +340,30 @@ static int pairs_dev(stereo_ctx *ctx, int net, const uint8_t *left_rgb, const ui
             // the trunk's last layer writes the chunk-planar bf16 features the correlation reads
             // (image 0 = left, image 1 = right are adjacent sides of one plane)
             const PlanarFeat &f = pf[lane];
-            PlanarOut po;
-            po.hi = f.l_hi + (size_t)f.ml * 8;
-            po.lo = f.l_lo + (size_t)f.ml * 8;
-            po.wf = f.wf;
+            const size_t img_elems = (size_t)h * 8 * f.wf * 8;
             const int planes = precision == STEREO_PREC_BF16X3 ? 2 : 1;
+            PlanarOut po;
+            po.wf = f.wf;
+            if (group == 1) {
+                po.hi = f.l_hi + (size_t)f.ml * 8;
+                po.lo = f.l_lo + (size_t)f.ml * 8;
+            } else {
+                // hi plane = the buffer's two hi regions (2 * group images), lo plane = its two lo regions
+                po.hi = f.l_hi + 2 * slot * img_elems + (size_t)f.ml * 8;
+                po.lo = f.l_lo + 2 * slot * img_elems + (size_t)f.ml * 8;
+            }
             STEREO_TRY(trunk_dev(ctx, net, padded_lane, 2, hp, wp, nullptr, precision, &po,
                                  from_u8 ? left_rgb + i * img_bytes : nullptr, from_u8 ? right_rgb + i * img_bytes : nullptr,
                                  2 * i, lane));
-            STEREO_TRY(launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, 1, h, w, f.wf, f.ml, D, planes, lv, rv,
-                                      left_disp + i * map, right_disp + i * map));
+            if (group == 1) {
+                STEREO_TRY(launch_corr_tc(ctx, f.l_hi, f.l_lo, f.r_hi, f.r_lo, 1, h, w, f.wf, f.ml, D, planes, lv, rv,
+                                          left_disp + i * map, right_disp + i * map));
+            } else if (slot == group - 1 || i == n - 1) {
+                const int first = i - slot;
+                STEREO_TRY(launch_corr_both(ctx, f.l_hi, f.l_lo, f.l_hi + img_elems, f.l_lo + img_elems, slot + 1, h, w, f.wf,
+                                            f.ml, D, planes, left_disp + first * map, right_disp + first * map,
+                                            2 * img_elems));
+            }
         } else {
             STEREO_TRY(trunk_dev(ctx, net, padded_lane, 2, hp, wp, feat, precision));
             STEREO_TRY(corr_dev(ctx, feat, feat + feat_img, 1, h, w, 64, D, precision, lv, rv, left_disp + i * map,

@@ -167,9 +167,12 @@ int launch_conv_tcr(stereo_ctx *ctx, int ks, int cin, int cout, const void *in_h
                     int w_in, int wp_in, const void *wimg, const float *bias, void *out_hi, void *out_lo, int wp_out,
                     float *out_f32, int relu, int planes);
 int corr_sweep_margin();
-// corr_both.cu: both disparity maps from ONE sweep per row (fused WTA only)
+// corr_both.cu: both disparity maps from ONE sweep per row (fused WTA only).  img_stride: elements between consecutive
+// images of one side (0: the images of a side are contiguous); corr_both_enabled(): launch_corr_tc would pick it.
 int launch_corr_both(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
-                     int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp);
+                     int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp,
+                     size_t img_stride = 0);
+bool corr_both_enabled();
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                       int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
                       uint8_t *left_disp, uint8_t *right_disp);

@@ -70,6 +70,7 @@ struct Params {
     int n, h, w, wf, ml, D, planes;
     uint8_t *left_disp, *right_disp;                   // [n][h][w]
     int nb, nitems;                                    // blocks per row, rows
+    size_t img_stride;                                 // elements between consecutive images of one side
 };
 
 // Row scan (left map), as in corr_sweep.cu: running arg max of the lane's pixel over the 32 columns of the chunk,
@@ -190,7 +191,8 @@ __global__ __launch_bounds__(kThreads, 1) void corr_both_kernel(Params p)
             // ---- TMA producer: candidate blocks two tiles ahead, own blocks one tile ahead ----
             uint32_t E = 0, T = 0;                   // running candidate-block and tile counters
             for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
-                const size_t row0 = (size_t)item * 8 * p.wf * 8;          // item = img * h + y
+                const int img = item / p.h;                               // item = img * h + y
+                const size_t row0 = (size_t)img * p.img_stride + (size_t)(item - img * p.h) * 8 * p.wf * 8;
                 const __nv_bfloat16 *own[2] = {p.l_hi, p.l_lo};
                 const __nv_bfloat16 *oth[2] = {p.r_hi, p.r_lo};
                 auto load_block = [&](uint32_t dst, const __nv_bfloat16 *const *src, int col, uint32_t bar) {
@@ -418,7 +420,8 @@ __global__ __launch_bounds__(kThreads, 1) void corr_both_kernel(Params p)
 }  // namespace tcb
 
 int launch_corr_both(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
-                     int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp)
+                     int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp,
+                     size_t img_stride)
 {
     const int nb = (w + tcb::kBlk - 1) / tcb::kBlk;
     STEREO_REQUIRE(D >= 1 && D - 1 <= tcb::kMargin, "one-sweep correlation supports disp_range <= %d, got %d",
@@ -434,6 +437,7 @@ int launch_corr_both(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const 
     p.left_disp = left_disp; p.right_disp = right_disp;
     p.nb = nb;
     p.nitems = n * h;
+    p.img_stride = img_stride ? img_stride : (size_t)h * 8 * wf * 8;
     const int grid = p.nitems < ctx->sm_count ? p.nitems : ctx->sm_count;
     // STEREO_CORR_COLS=0: no column scan (timing only, the right map is wrong)
     static const bool cols = [] { const char *e = getenv("STEREO_CORR_COLS"); return !(e && e[0] == '0'); }();

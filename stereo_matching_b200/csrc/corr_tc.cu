@@ -311,6 +311,15 @@ int launch_nhwc_to_planar(stereo_ctx *ctx, const float *in, int n, int h, int w,
     return STEREO_OK;
 }
 
+bool corr_both_enabled()
+{
+    static const bool on = [] {
+        const char *k = getenv("STEREO_CORR_KERNEL"), *s = getenv("STEREO_CORR_SWEEPS");
+        return !(k && k[0] == '1') && !(s && s[0] == '2');
+    }();
+    return on;
+}
+
 int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                    int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
                    uint8_t *left_disp, uint8_t *right_disp)
@@ -325,8 +334,7 @@ int launch_corr_tc(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const vo
     // cross-check, which also serves rows whose margins are too small for the sweep
     static const bool per_tile = [] { const char *e = getenv("STEREO_CORR_KERNEL"); return e && e[0] == '1'; }();
     // fused WTA of both maps: one sweep per row serves both (corr_both.cu); STEREO_CORR_SWEEPS=2 keeps the two sweeps
-    static const bool two_sweeps = [] { const char *e = getenv("STEREO_CORR_SWEEPS"); return e && e[0] == '2'; }();
-    if (!per_tile && !two_sweeps && !vol && left_disp && right_disp && ml >= corr_sweep_margin())
+    if (corr_both_enabled() && !vol && left_disp && right_disp && ml >= corr_sweep_margin())
         return launch_corr_both(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_disp, right_disp);
     if (!per_tile && ml >= corr_sweep_margin())
         return launch_corr_sweep(ctx, l_hi, l_lo, r_hi, r_lo, n, h, w, wf, ml, D, planes, left_vol, right_vol, left_disp,

@@ -508,6 +508,21 @@ def test_batched_tensor_core_pairs_with_volumes_equal_single_pairs(ctx):
             assert np.array_equal(batch[name][i], one[name][0]), (i, name)
 
 
+@pytest.mark.parametrize("net,n,h,w", [(_lib.NET_WIN9, 9, 21, 300), (_lib.NET_WIN9, 11, 14, 131), (_lib.NET_WIN37, 9, 40, 150)])
+def test_grouped_fused_correlation_equals_single_pairs(ctx, base_layers, net, n, h, w):
+    """Fused path (no volumes): the features of up to four consecutive pairs stay in a lane's planar buffer
+    (left and right of a pair as neighbouring images) and one correlation launch serves them.  Full groups on both
+    lanes and a partial last group: every pair's maps must be those of a call with that pair alone."""
+    D = 40
+    pairs = [synth.make_pair(6100 + i, h, w, D) for i in range(n)]
+    left, right = np.stack([p[0] for p in pairs]), np.stack([p[1] for p in pairs])
+    batch = ctx.pairs(net, left, right, D, precision=_lib.PREC_BF16X3, volumes=False)
+    for i in range(n):
+        one = ctx.pairs(net, left[i], right[i], D, precision=_lib.PREC_BF16X3, volumes=False)
+        for name in ("left_disp", "right_disp", "outlier"):
+            assert np.array_equal(batch[name][i], one[name][0]), (i, name)
+
+
 def test_inference_cli_sharded_over_two_ranks(tmp_path):
     """`torchrun --nproc-per-node 2 -m stereo_matching_b200.inference`: the pair list is sharded round-robin over the
     ranks (shard.py; one GPU per rank, here both on the one GPU of the box), every rank writes the files of its pairs,
