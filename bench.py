@@ -345,7 +345,7 @@ def run_b200(args):
                  "note": "algorithmic FLOPs (2*9*64*64 per output pixel, counted once whatever the operand split) / "
                          "CUDA-event time of the kernel class; the tensor pipe executes mma_passes x these FLOPs "
                          "(executed_frac = that rate / peak; ncu: profiles/)"},
-        "corr": {"kernel": ("corr_sweep_kernel (tcgen05, fused WTA)" if args.precision != "fp32"
+        "corr": {"kernel": ("corr_both_kernel (tcgen05, one sweep per row, fused WTA of both maps)" if args.precision != "fp32"
                             else "corr_ffma_kernel<fused WTA>"),
                  "bound": "tensor", "achieved": corr_tflops, "peak": tensor_peak, "unit": "TFLOP/s",
                  "frac": corr_tflops / tensor_peak, "traffic": None,
@@ -354,8 +354,8 @@ def run_b200(args):
                  "share_of_step": shares.get("corr"), "mma_passes": split,
                  "gdisp_evals_per_s": 2.0 * H * W * D * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None,
                  "algorithmic_gbs": corr_bytes * n * args.steps / (corr_ms / 1e3) / 1e9 if corr_ms else None,
-                 "note": "valid-band FLOPs (12.35 GFLOP per pair, the band counted once although both sweeps compute it) / "
-                         "CUDA-event time"},
+                 "note": "valid-band FLOPs (12.35 GFLOP per pair; the one sweep computes the band once) / CUDA-event time; "
+                         "the kernel is bound by its epilogue scans (ALU pipe), not by the tensor pipe"},
     }
     dominant = "conv" if shares.get("conv", 0) >= shares.get("corr", 0) else "corr"
     roofline = rooflines[dominant]
