@@ -20,6 +20,7 @@ namespace stereo {
 
 constexpr float kBnEps = 1e-3f;        // Keras BatchNormalization default (models/model.py)
 constexpr float kBnMomentum = 0.99f;   // Keras default
+constexpr int kTrainTcMinWidth = 96;   // rows at least this wide go to the tensor-core convolution (256-pixel tiles)
 
 struct TrainLayer {
     int ks, cin, cout, relu;
@@ -48,6 +49,7 @@ struct stereo_trainer {
     stereo::DevBuf logits, dlogits, loss_buf, targets;
     stereo::DevBuf dfeat[2];       // gradient wrt the left / right feature tensors
     stereo::DevBuf d_pad, w_flip, zero_bias;   // backward-data as a forward convolution: padded dz, flipped weights
+    stereo::DevBuf tc_act, tc_wimg;            // tensor-core route: chunk-planar bf16 (hi, lo) input, UMMA weight image
     stereo::Tower tower[2];
     long long step = 0;
 };
@@ -440,11 +442,38 @@ static inline unsigned grid_for(size_t total, int block, int cap)
     return (unsigned)(g < 1 ? 1 : (g > (size_t)cap ? (size_t)cap : g));
 }
 
-// 'valid' convolution + bias (+ ReLU): the tiled fp32 kernels of the inference path (conv_ffma.cu) where one is
+// Wide 3x3 / 64 -> 64 convolutions (the right tower forward, and its backward-data as a forward convolution of the
+// padded dz with the flipped kernel) on the tensor cores: the inference kernel conv_tc3.cu (tcgen05, CTA pair,
+// split-bf16 operands with fp32 accumulation).  The fp32 NHWC input is converted to its chunk-planar (hi, lo) layout,
+// the UMMA weight image is rebuilt from the current weights (they change every step), the output is fp32 NHWC again
+// because BatchNorm and the weight gradient read it.  Columns behind the image width hold whatever an earlier, wider
+// layer left there: they only reach output pixels the kernel does not store.
+static int train_conv_tc(stereo_trainer *tr, int relu, const float *w, const float *bias, const float *in, int n, int h,
+                         int wd, float *out)
+{
+    stereo_ctx *ctx = tr->ctx;
+    const int wp = tc3_pitch(wd);
+    const size_t plane_elems = (size_t)n * h * 8 * wp * 8;
+    const size_t had = tr->tc_act.bytes;
+    STEREO_TRY(tr->tc_act.reserve(2 * plane_elems * sizeof(uint16_t)));
+    if (tr->tc_act.bytes != had) STEREO_CUDA_CHECK(cudaMemsetAsync(tr->tc_act.ptr, 0, tr->tc_act.bytes, ctx->stream));
+    STEREO_TRY(tr->tc_wimg.reserve(tc3_weight_image_elems() * sizeof(uint16_t)));
+    uint16_t *hi = tr->tc_act.as<uint16_t>(), *lo = hi + plane_elems;
+    STEREO_TRY(launch_nhwc_to_planar(ctx, in, n, h, wd, wp, 0, hi, lo));
+    STEREO_TRY(launch_weight_images3(ctx, w, tr->tc_wimg.ptr));
+    return launch_conv_tc3(ctx, hi, lo, n, h, wd, wp, tr->tc_wimg.ptr, bias, nullptr, nullptr, wp, out, relu, 2);
+}
+
+// 'valid' convolution + bias (+ ReLU): the tensor-core route above for wide 64 -> 64 layers (STEREO_TRAIN_CONV=ffma
+// keeps them on the CUDA cores), else the tiled fp32 kernels of the inference path (conv_ffma.cu) where one is
 // instantiated for the shape, the plain kernel above otherwise.  `wbase + w_off` = kernel, `wbase + b_off` = bias.
-static int train_conv(stereo_ctx *ctx, int ks, int cin, int cout, int relu, const float *wbase, size_t w_off,
+static int train_conv(stereo_trainer *tr, int ks, int cin, int cout, int relu, const float *wbase, size_t w_off,
                       size_t b_off, const float *in, int n, int h, int w, float *out)
 {
+    stereo_ctx *ctx = tr->ctx;
+    static const bool no_tc = [] { const char *e = getenv("STEREO_TRAIN_CONV"); return e && (e[0] == 'f' || e[0] == 'p'); }();
+    if (!no_tc && ks == 3 && cin == 64 && cout == 64 && w >= kTrainTcMinWidth && h >= 3)
+        return train_conv_tc(tr, relu, wbase + w_off, wbase + b_off, in, n, h, w, out);
     const bool tiled = (ks == 3 && cout == 64 && (cin == 3 || cin == 64)) ||
                        (ks == 5 && ((cin == 3 && cout == 32) || (cin == 32 && cout == 32) || (cin == 32 && cout == 64) ||
                                     (cin == 64 && cout == 64)));
@@ -483,7 +512,7 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         STEREO_TRY(tw.a[l].reserve(total * sizeof(float)));
         STEREO_TRY(tw.x[l + 1].reserve(total * sizeof(float)));
         STEREO_TRY(tw.bn[l].reserve(2 * L.cout * sizeof(float)));
-        STEREO_TRY(train_conv(ctx, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
+        STEREO_TRY(train_conv(tr, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
                               tw.a[l].as<float>()));
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
         const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
@@ -556,7 +585,7 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
             train_flip_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(P + L.w_off, L.ks, L.cin, L.cout,
                                                                                             tr->w_flip.as<float>());
             STEREO_CUDA_CHECK(cudaMemsetAsync(tr->w_flip.as<float>() + wn, 0, 64 * sizeof(float), ctx->stream));
-            STEREO_TRY(train_conv(ctx, L.ks, L.cout, L.cin, 0, tr->w_flip.as<float>(), 0, wn, tr->d_pad.as<float>(), n, hp, wp, dx));
+            STEREO_TRY(train_conv(tr, L.ks, L.cout, L.cin, 0, tr->w_flip.as<float>(), 0, wn, tr->d_pad.as<float>(), n, hp, wp, dx));
             ctx->launches += 2;
             dy = dx;          // d_act[1] carries the gradient down; d_act[0] is rewritten as the next dz
         }
@@ -635,7 +664,8 @@ int stereo_train_destroy(stereo_trainer *tr)
     cudaSetDevice(tr->ctx->device);
     cudaStreamSynchronize(tr->ctx->stream);
     DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
-                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias};
+                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias,
+                      &tr->tc_act, &tr->tc_wimg};
     for (DevBuf *b : bufs) b->release();
     for (int t = 0; t < 2; ++t) {
         for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();

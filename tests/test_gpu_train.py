@@ -1,7 +1,15 @@
 """GPU parity of the training step (csrc/train.cu through the C ABI) against oracle/train_oracle.py
 (float64 torch autograd).  Tolerances: loss 1e-5 relative; gradients: 99.9 % of the entries within 2e-5 of the
 largest gradient entry and every entry within 1e-3 (fp32 forward/backward with double channel reductions; the
-maximum is set by ReLU-boundary flips that torch's float32 run shows too); Adam trajectories after several steps."""
+maximum is set by ReLU-boundary flips that torch's float32 run shows too); Adam trajectories after several steps.
+Rows of 96 pixels and more (the right tower at the reference's D = 201) run their 64 -> 64 convolutions, forward and
+backward-data, on the tensor cores with split-bf16 operands (products carry ~2^-17 relative error instead of fp32's
+2^-24): there the 99.9 % bound is 4e-5, everything else is unchanged; STEREO_TRAIN_CONV=ffma keeps the fp32 kernels
+and is held to the fp32 bound in a process of its own."""
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
 
@@ -23,7 +31,7 @@ def _batch(rng, B, D, p=9):
             rng.standard_normal((B, p, p + D - 1, 3)).astype(np.float32), to.soft_labels(B, D))
 
 
-@pytest.mark.parametrize("B,D", [(4, 7), (16, 33), (128, 201)])
+@pytest.mark.parametrize("B,D", [(4, 7), (16, 33), (3, 121), (128, 201)])     # the last two: tensor-core convolutions
 def test_forward_backward_matches_oracle(ctx, B, D):
     rng = np.random.default_rng(B)
     params, stats = to.init_params("win9_dep9", seed=B)
@@ -41,7 +49,8 @@ def test_forward_backward_matches_oracle(ctx, B, D):
     # (torch's own float32 run shows the same 3.7e-4 outlier at B = 128), so the bulk and the maximum are
     # bounded separately
     err = np.abs(grads - rgrads) / np.abs(rgrads).max()
-    assert err.max() <= 1e-3 and np.quantile(err, 0.999) <= 2e-5
+    tensor_core_route = 9 + D - 1 >= 96
+    assert err.max() <= 1e-3 and np.quantile(err, 0.999) <= (4e-5 if tensor_core_route else 2e-5)
     layers, _, _ = to.param_layout("win9_dep9")
     for d in layers:                                            # every parameter group on its own scale
         for k in ("kernel", "bias", "gamma", "beta"):
@@ -53,6 +62,53 @@ def test_forward_backward_matches_oracle(ctx, B, D):
     st = tr.get_state()
     assert np.allclose(st["stats"], ref_stats, rtol=1e-4, atol=1e-6)      # moving mean / variance (two passes)
     tr.close()
+
+
+FFMA_CHILD = r"""
+import sys
+import numpy as np
+sys.path.insert(0, sys.argv[1])
+from oracle import train_oracle as to
+from stereo_matching_b200 import _lib
+B, D = 128, 201
+rng = np.random.default_rng(B)
+params, stats = to.init_params("win9_dep9", seed=B)
+params = (params + 0.05 * rng.standard_normal(params.size)).astype(np.float32)
+left = rng.standard_normal((B, 9, 9, 3)).astype(np.float32)
+right = rng.standard_normal((B, 9, 9 + D - 1, 3)).astype(np.float32)
+targets = to.soft_labels(B, D)
+ctx = _lib.Context(0)
+tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+tr.set_state(params, stats)
+loss, correct, grads = tr.forward_backward(left, right, targets, want_grads=True)
+np.savez(sys.argv[2], loss=loss, correct=correct, grads=grads)
+"""
+
+
+def test_fp32_route_of_the_wide_convolutions_keeps_the_fp32_bound(ctx, tmp_path):
+    """STEREO_TRAIN_CONV=ffma (read once per process): the same batch as the (128, 201) case above through the fp32
+    CUDA-core convolutions, against the oracle at the fp32 bound and against the tensor-core route of this process."""
+    B, D = 128, 201
+    out = tmp_path / "ffma.npz"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ, STEREO_TRAIN_CONV="ffma")
+    r = subprocess.run([sys.executable, "-c", FFMA_CHILD, root, str(out)], env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = np.load(out)
+    rng = np.random.default_rng(B)
+    params, stats = to.init_params("win9_dep9", seed=B)
+    params = (params + 0.05 * rng.standard_normal(params.size)).astype(np.float32)
+    left, right, targets = _batch(rng, B, D)
+    rloss, rcorrect, rgrads, _ = to.forward_backward(params.astype(np.float64), stats.copy(), left, right, targets)
+    assert abs(float(got["loss"]) - rloss) <= 1e-5 * max(1.0, abs(rloss)) and int(got["correct"]) == rcorrect
+    err = np.abs(got["grads"] - rgrads) / np.abs(rgrads).max()
+    assert err.max() <= 1e-3 and np.quantile(err, 0.999) <= 2e-5
+    tr = _lib.Trainer(ctx, _lib.NET_WIN9, B, D)
+    tr.set_state(params, stats)
+    loss, correct, grads = tr.forward_backward(left, right, targets, want_grads=True)
+    tr.close()
+    both = np.abs(grads - got["grads"]) / np.abs(rgrads).max()
+    assert abs(loss - float(got["loss"])) <= 1e-5 * max(1.0, abs(rloss)) and np.quantile(both, 0.999) <= 4e-5
 
 
 def test_adam_trajectory_matches_oracle(ctx):
