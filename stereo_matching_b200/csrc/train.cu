@@ -20,6 +20,7 @@ namespace stereo {
 
 constexpr float kBnEps = 1e-3f;        // Keras BatchNormalization default (models/model.py)
 constexpr float kBnMomentum = 0.99f;   // Keras default
+constexpr int kRedW = 256;             // offset of the weight-gradient sums in the double scratch (after the BatchNorm sums)
 constexpr int kTrainTcMinWidth = 96;   // rows at least this wide go to the tensor-core convolution (256-pixel tiles)
 
 struct TrainLayer {
@@ -83,21 +84,6 @@ __global__ void train_conv_fwd_kernel(const float *__restrict__ in, const float 
     }
 }
 
-// per-channel sum and sum of squares (double) of a [m][c] array; red[0..c) += sum, red[c..2c) += sumsq
-__global__ void train_channel_moments_kernel(const float *__restrict__ a, size_t m, int c, double *__restrict__ red)
-{
-    // blockDim.x = c * rows_per_block; thread (r, ch)
-    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
-    double s = 0.0, ss = 0.0;
-    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) {
-        const double v = (double)a[p * c + ch];
-        s += v;
-        ss += v * v;
-    }
-    atomicAdd(red + ch, s);
-    atomicAdd(red + c + ch, ss);
-}
-
 // batch mean / biased variance -> (mean, invstd); moving statistics as Keras updates them
 __global__ void train_bn_finalize_kernel(const double *__restrict__ red, double m, int c, float *__restrict__ bn,
                                          float *__restrict__ moving_mean, float *__restrict__ moving_var)
@@ -113,13 +99,64 @@ __global__ void train_bn_finalize_kernel(const double *__restrict__ red, double 
     moving_var[ch] = moving_var[ch] * kBnMomentum + (float)var * (1.f - kBnMomentum);
 }
 
-__global__ void train_bn_apply_kernel(const float *__restrict__ a, size_t total, int c, const float *__restrict__ bn,
-                                      const float *__restrict__ gamma, const float *__restrict__ beta,
-                                      float *__restrict__ y)
+// ---- vectorised forms (c % 4 == 0: every layer's output has 32 or 64 channels) ----------------------------------
+// A thread owns four consecutive channels (quad q = tid % (c / 4)) of the rows r, r + rows, ... (r = tid / (c / 4)):
+// one 16-byte load per row and tensor, double sums in registers, one shared-memory reduction over the block's row
+// groups and ONE atomicAdd per channel and block.  The scalar forms above issued two double atomics per THREAD on
+// 128 addresses (2 400 per address and launch): 40-80 us for 47 MB.
+template <int NV>      // doubles per thread
+__device__ __forceinline__ void block_reduce_to_red(double (&v)[NV], int c4, double *__restrict__ red, int comp_stride)
 {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int ch = (int)(i % c);
-        y[i] = gamma[ch] * ((a[i] - bn[ch]) * bn[c + ch]) + beta[ch];
+    // v[k]: k = 4 * component + channel-in-quad; component j goes to red[j * comp_stride + channel]
+    __shared__ double sh[256 * NV];
+    const int q = threadIdx.x % c4, r = threadIdx.x / c4, rows = blockDim.x / c4;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) sh[(k * rows + r) * c4 + q] = v[k];
+    __syncthreads();
+    if (r == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            double s = 0.0;
+            for (int rr = 0; rr < rows; ++rr) s += sh[(k * rows + rr) * c4 + q];
+            atomicAdd(red + (k >> 2) * comp_stride + 4 * q + (k & 3), s);
+        }
+    }
+}
+
+__global__ __launch_bounds__(256) void train_moments4_kernel(const float4 *__restrict__ a, size_t m, int c4,
+                                                             double *__restrict__ red)
+{
+    const int q = threadIdx.x % c4, r = threadIdx.x / c4, rows = blockDim.x / c4;
+    double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 2
+    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) {
+        const float4 x = __ldg(a + p * c4 + q);
+        const double d0 = x.x, d1 = x.y, d2 = x.z, d3 = x.w;
+        v[0] += d0; v[1] += d1; v[2] += d2; v[3] += d3;
+        v[4] += d0 * d0; v[5] += d1 * d1; v[6] += d2 * d2; v[7] += d3 * d3;
+    }
+    block_reduce_to_red<8>(v, c4, red, 4 * c4);
+}
+
+__global__ __launch_bounds__(256) void train_bn_apply4_kernel(const float4 *__restrict__ a, size_t total4, int c4,
+                                                              const float *__restrict__ bn, const float *__restrict__ gamma,
+                                                              const float *__restrict__ beta, float4 *__restrict__ y)
+{
+    // the grid stride is a multiple of c4 (host), so a thread keeps its channel quad
+    const size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int ch = (int)(i0 % c4) * 4, c = 4 * c4;
+    float mean[4], scale[4], shift[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { mean[k] = bn[ch + k]; scale[k] = bn[c + ch + k]; shift[k] = beta[ch + k]; }
+    const float g0 = gamma[ch], g1 = gamma[ch + 1], g2 = gamma[ch + 2], g3 = gamma[ch + 3];
+    for (size_t i = i0; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 x = __ldg(a + i);
+        float4 o;
+        o.x = g0 * ((x.x - mean[0]) * scale[0]) + shift[0];
+        o.y = g1 * ((x.y - mean[1]) * scale[1]) + shift[1];
+        o.z = g2 * ((x.z - mean[2]) * scale[2]) + shift[2];
+        o.w = g3 * ((x.w - mean[3]) * scale[3]) + shift[3];
+        y[i] = o;
     }
 }
 
@@ -215,43 +252,91 @@ __global__ void train_loss_bwd_kernel(const float *__restrict__ lf, const float 
 // ------------------------------------------------------------------------------------------
 // backward kernels
 // ------------------------------------------------------------------------------------------
-// BatchNorm backward, reduction part: red[ch] += sum dy, red[c + ch] += sum dy * xhat
-__global__ void train_bn_bwd_reduce_kernel(const float *__restrict__ dy, const float *__restrict__ a, size_t m, int c,
-                                           const float *__restrict__ bn, double *__restrict__ red)
+// red[ch] += sum dy, red[c + ch] += sum dy * xhat (vectorised form of train_bn_bwd_reduce_kernel)
+__global__ __launch_bounds__(256) void train_bn_bwd_reduce4_kernel(const float4 *__restrict__ dy, const float4 *__restrict__ a,
+                                                                   size_t m, int c4, const float *__restrict__ bn,
+                                                                   double *__restrict__ red)
 {
-    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
-    const float mean = bn[ch], invstd = bn[c + ch];
-    double s = 0.0, sx = 0.0;
+    const int q = threadIdx.x % c4, r = threadIdx.x / c4, rows = blockDim.x / c4, c = 4 * c4;
+    float mean[4], invstd[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { mean[k] = bn[4 * q + k]; invstd[k] = bn[c + 4 * q + k]; }
+    double v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 2
     for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) {
-        const float g = dy[p * c + ch];
-        s += (double)g;
-        sx += (double)g * (double)((a[p * c + ch] - mean) * invstd);
+        const float4 g = __ldg(dy + p * c4 + q), x = __ldg(a + p * c4 + q);
+        v[0] += (double)g.x; v[1] += (double)g.y; v[2] += (double)g.z; v[3] += (double)g.w;
+        v[4] += (double)g.x * (double)((x.x - mean[0]) * invstd[0]);
+        v[5] += (double)g.y * (double)((x.y - mean[1]) * invstd[1]);
+        v[6] += (double)g.z * (double)((x.z - mean[2]) * invstd[2]);
+        v[7] += (double)g.w * (double)((x.w - mean[3]) * invstd[3]);
     }
-    atomicAdd(red + ch, s);
-    atomicAdd(red + c + ch, sx);
+    block_reduce_to_red<8>(v, c4, red, c);
 }
 
-// dgamma += red[c + ch], dbeta += red[ch];
-// da = gamma * invstd * (dy - dbeta / M - xhat * dgamma / M), then through the ReLU (a > 0) if the layer has one
-__global__ void train_bn_bwd_apply_kernel(const float *__restrict__ dy, const float *__restrict__ a, size_t total, int c,
-                                          double m, const float *__restrict__ bn, const float *__restrict__ gamma,
-                                          const double *__restrict__ red, int relu, float *__restrict__ dz)
+// da = gamma * invstd * (dy - dbeta / M - xhat * dgamma / M), through the ReLU mask; the same pass sums dz per channel
+// into `red_bias` (the bias gradient), which the scalar path computed in a launch of its own.
+__global__ __launch_bounds__(256) void train_bn_bwd_apply4_kernel(const float4 *__restrict__ dy, const float4 *__restrict__ a,
+                                                                  size_t total4, int c4, double m, const float *__restrict__ bn,
+                                                                  const float *__restrict__ gamma, const double *__restrict__ red,
+                                                                  int relu, float4 *__restrict__ dz, double *__restrict__ red_bias)
 {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int ch = (int)(i % c);
-        const float av = a[i];
-        const float xhat = (av - bn[ch]) * bn[c + ch];
-        const float db = (float)(red[ch] / m), dg = (float)(red[c + ch] / m);
-        float g = gamma[ch] * bn[c + ch] * (dy[i] - db - xhat * dg);
-        if (relu && !(av > 0.f)) g = 0.f;
-        dz[i] = g;
+    const size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;     // grid stride: a multiple of c4
+    const int ch = (int)(i0 % c4) * 4, c = 4 * c4;
+    float mean[4], invstd[4], gs[4], db[4], dg[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        mean[k] = bn[ch + k];
+        invstd[k] = bn[c + ch + k];
+        gs[k] = gamma[ch + k] * invstd[k];
+        db[k] = (float)(red[ch + k] / m);
+        dg[k] = (float)(red[c + ch + k] / m);
     }
+    double v[4] = {0, 0, 0, 0};
+    for (size_t i = i0; i < total4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 g = __ldg(dy + i), x = __ldg(a + i);
+        float4 o;
+        o.x = gs[0] * (g.x - db[0] - ((x.x - mean[0]) * invstd[0]) * dg[0]);
+        o.y = gs[1] * (g.y - db[1] - ((x.y - mean[1]) * invstd[1]) * dg[1]);
+        o.z = gs[2] * (g.z - db[2] - ((x.z - mean[2]) * invstd[2]) * dg[2]);
+        o.w = gs[3] * (g.w - db[3] - ((x.w - mean[3]) * invstd[3]) * dg[3]);
+        if (relu) {
+            if (!(x.x > 0.f)) o.x = 0.f;
+            if (!(x.y > 0.f)) o.y = 0.f;
+            if (!(x.z > 0.f)) o.z = 0.f;
+            if (!(x.w > 0.f)) o.w = 0.f;
+        }
+        dz[i] = o;
+        v[0] += (double)o.x; v[1] += (double)o.y; v[2] += (double)o.z; v[3] += (double)o.w;
+    }
+    block_reduce_to_red<4>(v, c4, red_bias, c);
 }
 
-__global__ void train_accumulate_kernel(const double *__restrict__ red, int n, float *__restrict__ dst)
+// dst[i] += red[i] for two ranges in one launch (BatchNorm: dbeta, dgamma; convolution: dW, db)
+__global__ void train_accumulate2_kernel(const double *__restrict__ red_a, int na, float *__restrict__ dst_a,
+                                         const double *__restrict__ red_b, int nb, float *__restrict__ dst_b)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] += (float)red[i];
+    if (i < na) dst_a[i] += (float)red_a[i];
+    else if (i < na + nb) dst_b[i - na] += (float)red_b[i - na];
+}
+
+// dx[b][yy][xx][ci] = sum_{ky,kx,co} dz[b][yy - ky][xx - kx][co] * w[ky][kx][ci][co] is the 'valid' convolution of
+// dz, zero-padded by ks - 1 on every side, with the flipped and transposed weights
+// w'[ky'][kx'][co][ci] = w[ks-1-ky'][ks-1-kx'][ci][co]: it runs through train_conv.  This kernel makes the zero-padded copy.
+__global__ void train_pad4_kernel(const float4 *__restrict__ dz, int n, int ho, int wo, int c4, int pad, float4 *__restrict__ out)
+{
+    const int hp = ho + 2 * pad, wp = wo + 2 * pad;
+    const size_t total = (size_t)n * hp * wp * c4;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int q = (int)(i % c4);
+        size_t p = i / c4;
+        const int x = (int)(p % wp) - pad;
+        p /= wp;
+        const int y = (int)(p % hp) - pad, b = (int)(p / hp);
+        out[i] = (x >= 0 && x < wo && y >= 0 && y < ho) ? __ldg(dz + (((size_t)b * ho + y) * wo + x) * c4 + q)
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 }
 
 // dW[t][ci][co] += sum_p x[p + t][ci] * dz[p][co].  A shared-memory GEMM per tap: grid = (taps, position
@@ -373,33 +458,6 @@ __global__ __launch_bounds__(256) void train_conv_bwd_w_small_kernel(const float
             if (r0 + i < rows && co0 + j < cout) atomicAdd(red_w + (size_t)(r0 + i) * cout + co0 + j, (double)acc[i][j]);
 }
 
-// db[co] += sum_p dz[p][co]
-__global__ void train_bias_bwd_kernel(const float *__restrict__ dz, size_t m, int c, double *__restrict__ red)
-{
-    const int ch = threadIdx.x % c, r = threadIdx.x / c, rows = blockDim.x / c;
-    double s = 0.0;
-    for (size_t p = (size_t)blockIdx.x * rows + r; p < m; p += (size_t)gridDim.x * rows) s += (double)dz[p * c + ch];
-    atomicAdd(red + ch, s);
-}
-
-// dx[b][yy][xx][ci] = sum_{ky,kx,co} dz[b][yy - ky][xx - kx][co] * w[ky][kx][ci][co] is the 'valid' convolution of
-// dz, zero-padded by ks - 1 on every side, with the flipped and transposed weights
-// w'[ky'][kx'][co][ci] = w[ks-1-ky'][ks-1-kx'][ci][co]: it runs through train_conv_fwd_kernel.
-__global__ void train_pad_kernel(const float *__restrict__ dz, int n, int ho, int wo, int c, int pad,
-                                 float *__restrict__ out)
-{
-    const int hp = ho + 2 * pad, wp = wo + 2 * pad;
-    const size_t total = (size_t)n * hp * wp * c;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int ch = (int)(i % c);
-        size_t p = i / c;
-        const int x = (int)(p % wp) - pad;
-        p /= wp;
-        const int y = (int)(p % hp) - pad, b = (int)(p / hp);
-        out[i] = (x >= 0 && x < wo && y >= 0 && y < ho) ? dz[(((size_t)b * ho + y) * wo + x) * c + ch] : 0.f;
-    }
-}
-
 __global__ void train_flip_weights_kernel(const float *__restrict__ w, int ks, int cin, int cout, float *__restrict__ wt)
 {
     const int total = ks * ks * cin * cout;
@@ -515,13 +573,14 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         STEREO_TRY(train_conv(tr, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
                               tw.a[l].as<float>()));
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
-        const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
-        train_channel_moments_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(
-            tw.a[l].as<float>(), m, L.cout, red);
+        const int c4 = L.cout / 4, rows4 = 256 / c4;
+        train_moments4_kernel<<<grid_for(m, rows4, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
+            reinterpret_cast<const float4 *>(tw.a[l].as<float>()), m, c4, red);
         train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>(),
                                                                 S + L.mean_off, S + L.var_off);
-        train_bn_apply_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-            tw.a[l].as<float>(), total, L.cout, tw.bn[l].as<float>(), P + L.g_off, P + L.be_off, tw.x[l + 1].as<float>());
+        train_bn_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+            reinterpret_cast<const float4 *>(tw.a[l].as<float>()), total / 4, c4, tw.bn[l].as<float>(), P + L.g_off,
+            P + L.be_off, reinterpret_cast<float4 *>(tw.x[l + 1].as<float>()));
         ctx->launches += 3;
         cur = tw.x[l + 1].as<float>();
     }
@@ -545,18 +604,20 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         const float *a = tw.a[l].as<float>();
         const float *xin = l == 0 ? patches : tw.x[l].as<float>();
         float *dz = tr->d_act[0].as<float>();                 // gradient wrt conv output (after the ReLU mask)
-        // BatchNorm: dgamma, dbeta, da
-        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
-        const int rows = 256 / L.cout > 0 ? 256 / L.cout : 1;
-        train_bn_bwd_reduce_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(
-            dy, a, m, L.cout, tw.bn[l].as<float>(), red);
-        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red, L.cout, G + L.be_off);
-        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + L.cout, L.cout, G + L.g_off);
-        train_bn_bwd_apply_kernel<<<grid_for(total, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-            dy, a, total, L.cout, (double)m, tw.bn[l].as<float>(), P + L.g_off, red, L.relu, dz);
-        // conv: dW, db (double accumulation), then dx for the layer below
+        // Scratch: red[0, 2c) BatchNorm sums, red[kRedW, kRedW + wn) dW, then db.  BatchNorm: dgamma, dbeta, da
         const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
-        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (wn + L.cout) * sizeof(double), ctx->stream));
+        double *red_w = red + kRedW, *red_b = red_w + wn;
+        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (kRedW + wn + L.cout) * sizeof(double), ctx->stream));
+        const int c4 = L.cout / 4, rows4 = 256 / c4;
+        train_bn_bwd_reduce4_kernel<<<grid_for(m, rows4, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
+            reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), m, c4, tw.bn[l].as<float>(), red);
+        // (parameter order per layer: kernel, bias, gamma, beta; red[0, c) = dbeta, red[c, 2c) = dgamma)
+        train_accumulate2_kernel<<<1, 2 * L.cout, 0, ctx->stream>>>(red + L.cout, L.cout, G + L.g_off, red, L.cout, G + L.be_off);
+        // da through the ReLU mask = dz; the same pass sums dz per channel (db)
+        train_bn_bwd_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+            reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), total / 4, c4, (double)m,
+            tw.bn[l].as<float>(), P + L.g_off, red, L.relu, reinterpret_cast<float4 *>(dz), red_b);
+        // conv: dW (double accumulation over position chunks)
         // positions per block (accumulated in fp32; the blocks in double): at most kBwdChunk, fewer when that would
         // leave SMs idle (the left tower, the first layer's single product): about eight blocks per SM
         const bool small = L.ks * L.ks * L.cin <= 32 && L.cout <= 64;
@@ -566,22 +627,22 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         const int chunks = (int)((m + chunk - 1) / chunk);
         if (small)
             train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout,
-                                                                           (int)chunk, red);
+                                                                           (int)chunk, red_w);
         else
             train_conv_bwd_w_kernel<<<dim3(L.ks * L.ks, chunks), 256, 0, ctx->stream>>>(
-                xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, (int)chunk, red);
-        train_bias_bwd_kernel<<<grid_for(m, rows, ctx->sm_count * 4), rows * L.cout, 0, ctx->stream>>>(dz, m, L.cout, red + wn);
-        train_accumulate_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(red, (int)wn, G + L.w_off);
-        train_accumulate_kernel<<<1, L.cout, 0, ctx->stream>>>(red + wn, L.cout, G + L.b_off);
-        ctx->launches += 8;
+                xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout, (int)chunk, red_w);
+        // kernel and bias are neighbours in the gradient array, like dW and db in the scratch
+        train_accumulate2_kernel<<<(unsigned)((wn + L.cout + 255) / 256), 256, 0, ctx->stream>>>(red_w, (int)wn, G + L.w_off,
+                                                                                           red_b, L.cout, G + L.b_off);
+        ctx->launches += 5;
         if (l > 0) {
             float *dx = tr->d_act[1].as<float>();
             const int pad = L.ks - 1, hp = ho + 2 * pad, wp = wo + 2 * pad;
             const size_t tpad = (size_t)n * hp * wp * L.cout;
             STEREO_TRY(tr->d_pad.reserve(tpad * sizeof(float)));
             STEREO_TRY(tr->w_flip.reserve((wn + 64) * sizeof(float)));     // flipped kernel, then a zero bias
-            train_pad_kernel<<<grid_for(tpad, 256, ctx->sm_count * 16), 256, 0, ctx->stream>>>(dz, n, ho, wo, L.cout, pad,
-                                                                                             tr->d_pad.as<float>());
+            train_pad4_kernel<<<grid_for(tpad / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+                reinterpret_cast<const float4 *>(dz), n, ho, wo, c4, pad, reinterpret_cast<float4 *>(tr->d_pad.as<float>()));
             train_flip_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(P + L.w_off, L.ks, L.cin, L.cout,
                                                                                             tr->w_flip.as<float>());
             STEREO_CUDA_CHECK(cudaMemsetAsync(tr->w_flip.as<float>() + wn, 0, 64 * sizeof(float), ctx->stream));
