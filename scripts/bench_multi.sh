@@ -1,11 +1,11 @@
 #!/bin/bash
-# Every bench configuration on N GPUs of one box: bash scripts/bench_multi.sh N [tag]  -> gpurun_out/<tag>_bench_<config>_<N>gpu.json
+# Every bench configuration (or those in $CONFIGS) on N GPUs of one box: bash scripts/bench_multi.sh N [tag]  -> gpurun_out/<tag>_bench_<config>_<N>gpu.json
 N=${1:-2}
 TAG=${2:-r02}
 OUT=gpurun_out
 mkdir -p $OUT
 PORT=29540
-for c in ws9_fused base_model post_chain train_dp; do
+for c in ${CONFIGS:-ws9_fused base_model post_chain train_dp}; do
   PORT=$((PORT+1))
   STEPS=10; [ "$c" = "train_dp" ] && STEPS=50
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT \
