@@ -173,6 +173,10 @@ int launch_corr_both(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const 
                      int h, int w, int wf, int ml, int D, int planes, uint8_t *left_disp, uint8_t *right_disp,
                      size_t img_stride = 0);
 bool corr_both_enabled();
+// train_wgrad_tc.cu: weight gradient of a 3x3 / 64 -> 64 layer on the tensor cores, accumulated into red_w (double)
+size_t train_wgrad_tc_scratch_bytes(const stereo_ctx *ctx);
+int launch_train_wgrad_tc(stereo_ctx *ctx, const float *x, const float *dz, int n, int h, int w, float *scratch,
+                          double *red_w);
 int launch_corr_sweep(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const void *r_hi, const void *r_lo, int n,
                       int h, int w, int wf, int ml, int D, int planes, float *left_vol, float *right_vol,
                       uint8_t *left_disp, uint8_t *right_disp);

@@ -51,6 +51,7 @@ struct stereo_trainer {
     stereo::DevBuf dfeat[2];       // gradient wrt the left / right feature tensors
     stereo::DevBuf d_pad, w_flip, zero_bias;   // backward-data as a forward convolution: padded dz, flipped weights
     stereo::DevBuf tc_act, tc_wimg;            // tensor-core route: chunk-planar bf16 (hi, lo) input, UMMA weight image
+    stereo::DevBuf wg_scratch;                 // tensor-core weight gradient: per-CTA partial sums
     stereo::Tower tower[2];
     long long step = 0;
 };
@@ -625,7 +626,12 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         size_t chunk = (m * products / ((size_t)ctx->sm_count * 8) + 31) / 32 * 32;
         chunk = chunk < 128 ? 128 : (chunk > (size_t)kBwdChunk ? (size_t)kBwdChunk : chunk);
         const int chunks = (int)((m + chunk - 1) / chunk);
-        if (small)
+        // 3x3 / 64 -> 64: positions as the K dimension of tcgen05 MMAs (train_wgrad_tc.cu); STEREO_TRAIN_CONV=ffma: fp32
+        static const bool no_tc = [] { const char *e = getenv("STEREO_TRAIN_CONV"); return e && (e[0] == 'f' || e[0] == 'p'); }();
+        if (!no_tc && L.ks == 3 && L.cin == 64 && L.cout == 64) {
+            STEREO_TRY(tr->wg_scratch.reserve(train_wgrad_tc_scratch_bytes(ctx)));
+            STEREO_TRY(launch_train_wgrad_tc(ctx, xin, dz, n, tw.h[l], tw.w[l], tr->wg_scratch.as<float>(), red_w));
+        } else if (small)
             train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout,
                                                                            (int)chunk, red_w);
         else
@@ -726,7 +732,7 @@ int stereo_train_destroy(stereo_trainer *tr)
     cudaStreamSynchronize(tr->ctx->stream);
     DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
                       &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias,
-                      &tr->tc_act, &tr->tc_wimg};
+                      &tr->tc_act, &tr->tc_wimg, &tr->wg_scratch};
     for (DevBuf *b : bufs) b->release();
     for (int t = 0; t < 2; ++t) {
         for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();
