@@ -1065,13 +1065,13 @@ def run_train_dp(args):
     pk = peaks()
     flops_step = 54.9e9                       # forward + backward of both towers at B = 128
     tflops = flops_step * args.steps / sec / 1e12
-    roofline = {"kernel": "conv3x3_tc3_kernel (right tower forward + backward-data, tcgen05 split-bf16) / train.cu weight-gradient "
-                          "and left-tower kernels (fp32, CUDA cores)",
+    roofline = {"kernel": "conv3x3_tc3_kernel (right tower forward + backward-data) and wgrad_tc_kernel (weight gradients), tcgen05 "
+                          "split-bf16; left tower, first layer, BatchNorm passes: fp32 on the CUDA cores",
                 "bound": "tensor", "achieved": tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
                 "frac": tflops / pk["bf16_tflops_sustained"], "traffic": None,
                 "peak_source": pk["source"] + " cuBLAS bf16 dense, sustained",
-                "note": "the wide 64->64 convolutions (forward, backward-data) run on tcgen05, the weight gradient and the left "
-                        "tower in fp32 on the CUDA cores: the fraction of the tensor peak says how far the whole step is from "
+                "note": "the wide 64->64 convolutions (forward, backward-data) and the 64->64 weight gradients run on tcgen05, the "
+                        "left tower in fp32 on the CUDA cores: the fraction of the tensor peak says how far the whole step is from "
                         "what the hardware offers; 54.9 algorithmic GFLOP per step of 128 patches / wall time of the whole "
                         "step (host patches in, loss out)"}
     cpu = None if (args.no_cpu_baseline or hz.world > 1) else cpu_baseline_train(B, Dt)
