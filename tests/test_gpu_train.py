@@ -4,8 +4,10 @@ largest gradient entry and every entry within 1e-3 (fp32 forward/backward with d
 maximum is set by ReLU-boundary flips that torch's float32 run shows too); Adam trajectories after several steps.
 Rows of 96 pixels and more (the right tower at the reference's D = 201) run their 64 -> 64 convolutions, forward and
 backward-data, on the tensor cores with split-bf16 operands (products carry ~2^-17 relative error instead of fp32's
-2^-24): there the 99.9 % bound is 4e-5, everything else is unchanged; STEREO_TRAIN_CONV=ffma keeps the fp32 kernels
-and is held to the fp32 bound in a process of its own."""
+2^-24): there the 99.9 % bound is 4e-5, everything else is unchanged.  The weight gradients of the 64 -> 64 layers come
+from the tensor-core kernel train_wgrad_tc.cu at every size (fp32 accumulation per CTA, double across CTAs) and stay
+inside the fp32 bound on the small cases.  STEREO_TRAIN_CONV=ffma keeps all fp32 kernels and is held to the fp32 bound
+in a process of its own."""
 import os
 import subprocess
 import sys
