@@ -52,6 +52,7 @@ struct stereo_trainer {
     stereo::DevBuf d_pad, w_flip, zero_bias;   // backward-data as a forward convolution: padded dz, flipped weights
     stereo::DevBuf tc_act, tc_wimg;            // tensor-core route: chunk-planar bf16 (hi, lo) input, UMMA weight image
     stereo::DevBuf wg_scratch;                 // tensor-core weight gradient: per-CTA partial sums
+    stereo::DevBuf red_part;                   // per-block partial sums of the channel reductions (double)
     stereo::Tower tower[2];
     long long step = 0;
 };
@@ -103,12 +104,14 @@ __global__ void train_bn_finalize_kernel(const double *__restrict__ red, double 
 // ---- vectorised forms (c % 4 == 0: every layer's output has 32 or 64 channels) ----------------------------------
 // A thread owns four consecutive channels (quad q = tid % (c / 4)) of the rows r, r + rows, ... (r = tid / (c / 4)):
 // one 16-byte load per row and tensor, double sums in registers, one shared-memory reduction over the block's row
-// groups and ONE atomicAdd per channel and block.  The scalar forms above issued two double atomics per THREAD on
-// 128 addresses (2 400 per address and launch): 40-80 us for 47 MB.
+// groups, and the block's sums go to its own row of a partial buffer; train_sum_partials_kernel adds the rows up.
+// No atomics: the scalar forms issued two double atomics per THREAD on 128 addresses (2 400 per address and launch,
+// 40-80 us for 47 MB), and even one per channel and block still serialised at ~30 ns each (20-35 us per launch
+// whatever the tensor size - ncu round 2).
 template <int NV>      // doubles per thread
-__device__ __forceinline__ void block_reduce_to_red(double (&v)[NV], int c4, double *__restrict__ red, int comp_stride)
+__device__ __forceinline__ void block_reduce_to_partial(double (&v)[NV], int c4, double *__restrict__ part, int comp_stride)
 {
-    // v[k]: k = 4 * component + channel-in-quad; component j goes to red[j * comp_stride + channel]
+    // v[k]: k = 4 * component + channel-in-quad; component j goes to part[j * comp_stride + channel]
     __shared__ double sh[256 * NV];
     const int q = threadIdx.x % c4, r = threadIdx.x / c4, rows = blockDim.x / c4;
 #pragma unroll
@@ -119,8 +122,27 @@ __device__ __forceinline__ void block_reduce_to_red(double (&v)[NV], int c4, dou
         for (int k = 0; k < NV; ++k) {
             double s = 0.0;
             for (int rr = 0; rr < rows; ++rr) s += sh[(k * rows + rr) * c4 + q];
-            atomicAdd(red + (k >> 2) * comp_stride + 4 * q + (k & 3), s);
+            part[(k >> 2) * comp_stride + 4 * q + (k & 3)] = s;
         }
+    }
+}
+
+// out[i] (+)= sum over the `parts` rows of partial[part][i], i < n (n <= 128): one block of 1024 threads, thread
+// (g, i) adds the rows g, g + G, ...
+__global__ __launch_bounds__(1024) void train_sum_partials_kernel(const double *__restrict__ partial, int parts, int n,
+                                                                  double *__restrict__ out, int add)
+{
+    __shared__ double sh[1024];
+    const int i = threadIdx.x % n, g = threadIdx.x / n, G = blockDim.x / n;
+    double s = 0.0;
+    if (g < G)
+        for (int pr = g; pr < parts; pr += G) s += partial[(size_t)pr * n + i];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x < n) {
+        double t = 0.0;
+        for (int gg = 0; gg < G; ++gg) t += sh[gg * n + threadIdx.x];
+        out[threadIdx.x] = add ? out[threadIdx.x] + t : t;
     }
 }
 
@@ -136,7 +158,7 @@ __global__ __launch_bounds__(256) void train_moments4_kernel(const float4 *__res
         v[0] += d0; v[1] += d1; v[2] += d2; v[3] += d3;
         v[4] += d0 * d0; v[5] += d1 * d1; v[6] += d2 * d2; v[7] += d3 * d3;
     }
-    block_reduce_to_red<8>(v, c4, red, 4 * c4);
+    block_reduce_to_partial<8>(v, c4, red + (size_t)blockIdx.x * 8 * c4, 4 * c4);
 }
 
 __global__ __launch_bounds__(256) void train_bn_apply4_kernel(const float4 *__restrict__ a, size_t total4, int c4,
@@ -272,7 +294,7 @@ __global__ __launch_bounds__(256) void train_bn_bwd_reduce4_kernel(const float4 
         v[6] += (double)g.z * (double)((x.z - mean[2]) * invstd[2]);
         v[7] += (double)g.w * (double)((x.w - mean[3]) * invstd[3]);
     }
-    block_reduce_to_red<8>(v, c4, red, c);
+    block_reduce_to_partial<8>(v, c4, red + (size_t)blockIdx.x * 2 * c, c);
 }
 
 // da = gamma * invstd * (dy - dbeta / M - xhat * dgamma / M), through the ReLU mask; the same pass sums dz per channel
@@ -310,7 +332,7 @@ __global__ __launch_bounds__(256) void train_bn_bwd_apply4_kernel(const float4 *
         dz[i] = o;
         v[0] += (double)o.x; v[1] += (double)o.y; v[2] += (double)o.z; v[3] += (double)o.w;
     }
-    block_reduce_to_red<4>(v, c4, red_bias, c);
+    block_reduce_to_partial<4>(v, c4, red_bias + (size_t)blockIdx.x * c, c);
 }
 
 // dst[i] += red[i] for two ranges in one launch (BatchNorm: dbeta, dgamma; convolution: dW, db)
@@ -573,16 +595,17 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         STEREO_TRY(tw.bn[l].reserve(2 * L.cout * sizeof(float)));
         STEREO_TRY(train_conv(tr, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
                               tw.a[l].as<float>()));
-        STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, 2 * L.cout * sizeof(double), ctx->stream));
         const int c4 = L.cout / 4, rows4 = 256 / c4;
-        train_moments4_kernel<<<grid_for(m, rows4, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
-            reinterpret_cast<const float4 *>(tw.a[l].as<float>()), m, c4, red);
+        double *part = tr->red_part.as<double>();
+        const unsigned gm = grid_for(m, rows4, ctx->sm_count * 2);
+        train_moments4_kernel<<<gm, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(tw.a[l].as<float>()), m, c4, part);
+        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)gm, 2 * L.cout, red, 0);
         train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>(),
                                                                 S + L.mean_off, S + L.var_off);
         train_bn_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(tw.a[l].as<float>()), total / 4, c4, tw.bn[l].as<float>(), P + L.g_off,
             P + L.be_off, reinterpret_cast<float4 *>(tw.x[l + 1].as<float>()));
-        ctx->launches += 3;
+        ctx->launches += 4;
         cur = tw.x[l + 1].as<float>();
     }
     STEREO_CUDA_CHECK(cudaGetLastError());
@@ -610,14 +633,19 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         double *red_w = red + kRedW, *red_b = red_w + wn;
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (kRedW + wn + L.cout) * sizeof(double), ctx->stream));
         const int c4 = L.cout / 4, rows4 = 256 / c4;
-        train_bn_bwd_reduce4_kernel<<<grid_for(m, rows4, ctx->sm_count * 4), 256, 0, ctx->stream>>>(
-            reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), m, c4, tw.bn[l].as<float>(), red);
+        double *part = tr->red_part.as<double>();
+        const unsigned gr = grid_for(m, rows4, ctx->sm_count * 2);
+        train_bn_bwd_reduce4_kernel<<<gr, 256, 0, ctx->stream>>>(
+            reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), m, c4, tw.bn[l].as<float>(), part);
+        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)gr, 2 * L.cout, red, 0);
         // (parameter order per layer: kernel, bias, gamma, beta; red[0, c) = dbeta, red[c, 2c) = dgamma)
         train_accumulate2_kernel<<<1, 2 * L.cout, 0, ctx->stream>>>(red + L.cout, L.cout, G + L.g_off, red, L.cout, G + L.be_off);
         // da through the ReLU mask = dz; the same pass sums dz per channel (db)
-        train_bn_bwd_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+        const unsigned ga = grid_for(total / 4, 256, ctx->sm_count * 8);
+        train_bn_bwd_apply4_kernel<<<ga, 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), total / 4, c4, (double)m,
-            tw.bn[l].as<float>(), P + L.g_off, red, L.relu, reinterpret_cast<float4 *>(dz), red_b);
+            tw.bn[l].as<float>(), P + L.g_off, red, L.relu, reinterpret_cast<float4 *>(dz), part);
+        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)ga, L.cout, red_b, 0);
         // conv: dW (double accumulation over position chunks)
         // positions per block (accumulated in fp32; the blocks in double): at most kBwdChunk, fewer when that would
         // leave SMs idle (the left tower, the first layer's single product): about eight blocks per SM
@@ -640,7 +668,7 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         // kernel and bias are neighbours in the gradient array, like dW and db in the scratch
         train_accumulate2_kernel<<<(unsigned)((wn + L.cout + 255) / 256), 256, 0, ctx->stream>>>(red_w, (int)wn, G + L.w_off,
                                                                                            red_b, L.cout, G + L.b_off);
-        ctx->launches += 5;
+        ctx->launches += 7;
         if (l > 0) {
             float *dx = tr->d_act[1].as<float>();
             const int pad = L.ks - 1, hp = ho + 2 * pad, wp = wo + 2 * pad;
@@ -703,6 +731,7 @@ int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, ste
     need(tr->adam_v, po * sizeof(float));
     need(tr->stats, so * sizeof(float));
     need(tr->red, (po + 1024) * sizeof(double));
+    need(tr->red_part, (size_t)ctx->sm_count * 8 * 128 * sizeof(double));      // <= 8 blocks per SM x 2 x 64 channels
     const size_t pw = (size_t)tr->patch + disp_range - 1;
     const size_t act = (size_t)batch * (tr->patch - nd.layer[0].ks + 1) * (pw - nd.layer[0].ks + 1) * 64;
     need(tr->d_act[0], act * sizeof(float));
@@ -732,7 +761,7 @@ int stereo_train_destroy(stereo_trainer *tr)
     cudaStreamSynchronize(tr->ctx->stream);
     DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
                       &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias,
-                      &tr->tc_act, &tr->tc_wimg, &tr->wg_scratch};
+                      &tr->tc_act, &tr->tc_wimg, &tr->wg_scratch, &tr->red_part};
     for (DevBuf *b : bufs) b->release();
     for (int t = 0; t < 2; ++t) {
         for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();

@@ -239,7 +239,8 @@ __global__ void wgrad_reduce_kernel(const float *__restrict__ partial, int parts
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= total) return;
     double s = 0.0;
-    for (int c = 0; c < parts; ++c) s += (double)partial[(size_t)c * total + i];
+#pragma unroll 8
+    for (int c = 0; c < parts; ++c) s += (double)__ldg(partial + (size_t)c * total + i);
     red_w[i] += s;
 }
 
