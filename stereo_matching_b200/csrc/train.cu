@@ -127,23 +127,26 @@ __device__ __forceinline__ void block_reduce_to_partial(double (&v)[NV], int c4,
     }
 }
 
-// out[i] (+)= sum over the `parts` rows of partial[part][i], i < n (n <= 128): one block of 1024 threads, thread
-// (g, i) adds the rows g, g + G, ...
+// out[i] (+)= sum over the `parts` rows of partial[part][i], i < n: block b sums the eight values 8 b .. 8 b + 7, thread
+// (g, j) of it adds the rows g, g + 128, ... (a single block took 8 us per call: it waits out the L2 latency of its ~40
+// loads per thread one batch after the other).
 __global__ __launch_bounds__(1024) void train_sum_partials_kernel(const double *__restrict__ partial, int parts, int n,
                                                                   double *__restrict__ out, int add)
 {
     __shared__ double sh[1024];
-    const int i = threadIdx.x % n, g = threadIdx.x / n, G = blockDim.x / n;
+    const int j = threadIdx.x & 7, g = threadIdx.x >> 3, i = 8 * blockIdx.x + j;
     double s = 0.0;
-    if (g < G)
-        for (int pr = g; pr < parts; pr += G) s += partial[(size_t)pr * n + i];
+    if (i < n) {
+#pragma unroll 4
+        for (int pr = g; pr < parts; pr += 128) s += __ldg(partial + (size_t)pr * n + i);
+    }
     sh[threadIdx.x] = s;
     __syncthreads();
-    if (threadIdx.x < n) {
-        double t = 0.0;
-        for (int gg = 0; gg < G; ++gg) t += sh[gg * n + threadIdx.x];
-        out[threadIdx.x] = add ? out[threadIdx.x] + t : t;
+    for (int o = 512; o >= 8; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
     }
+    if (threadIdx.x < 8 && i < n) out[i] = add ? out[i] + sh[threadIdx.x] : sh[threadIdx.x];
 }
 
 __global__ __launch_bounds__(256) void train_moments4_kernel(const float4 *__restrict__ a, size_t m, int c4,
@@ -599,7 +602,7 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         double *part = tr->red_part.as<double>();
         const unsigned gm = grid_for(m, rows4, ctx->sm_count * 2);
         train_moments4_kernel<<<gm, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(tw.a[l].as<float>()), m, c4, part);
-        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)gm, 2 * L.cout, red, 0);
+        train_sum_partials_kernel<<<(2 * L.cout + 7) / 8, 1024, 0, ctx->stream>>>(part, (int)gm, 2 * L.cout, red, 0);
         train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>(),
                                                                 S + L.mean_off, S + L.var_off);
         train_bn_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
@@ -637,15 +640,15 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         const unsigned gr = grid_for(m, rows4, ctx->sm_count * 2);
         train_bn_bwd_reduce4_kernel<<<gr, 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), m, c4, tw.bn[l].as<float>(), part);
-        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)gr, 2 * L.cout, red, 0);
+        train_sum_partials_kernel<<<(2 * L.cout + 7) / 8, 1024, 0, ctx->stream>>>(part, (int)gr, 2 * L.cout, red, 0);
         // (parameter order per layer: kernel, bias, gamma, beta; red[0, c) = dbeta, red[c, 2c) = dgamma)
         train_accumulate2_kernel<<<1, 2 * L.cout, 0, ctx->stream>>>(red + L.cout, L.cout, G + L.g_off, red, L.cout, G + L.be_off);
         // da through the ReLU mask = dz; the same pass sums dz per channel (db)
-        const unsigned ga = grid_for(total / 4, 256, ctx->sm_count * 8);
+        const unsigned ga = grid_for(total / 4, 256, ctx->sm_count * 4);
         train_bn_bwd_apply4_kernel<<<ga, 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), total / 4, c4, (double)m,
             tw.bn[l].as<float>(), P + L.g_off, red, L.relu, reinterpret_cast<float4 *>(dz), part);
-        train_sum_partials_kernel<<<1, 1024, 0, ctx->stream>>>(part, (int)ga, L.cout, red_b, 0);
+        train_sum_partials_kernel<<<(L.cout + 7) / 8, 1024, 0, ctx->stream>>>(part, (int)ga, L.cout, red_b, 0);
         // conv: dW (double accumulation over position chunks)
         // positions per block (accumulated in fp32; the blocks in double): at most kBwdChunk, fewer when that would
         // leave SMs idle (the left tower, the first layer's single product): about eight blocks per SM
