@@ -33,8 +33,16 @@ struct TrainLayer {
 struct Tower {
     DevBuf x[kMaxLayers + 1];      // x[l] = input of layer l (x[0] = patches), x[L] = features
     DevBuf a[kMaxLayers];          // conv + bias (+ ReLU) output, before BatchNorm
-    DevBuf bn[kMaxLayers];         // per channel: batch mean, inverse std  (2 * cout floats)
+    DevBuf bn[kMaxLayers];         // per channel: batch mean, inverse std, batch variance  (3 * cout floats)
     int h[kMaxLayers + 1], w[kMaxLayers + 1];
+    // scratch of this tower's passes (the towers run on two streams at the same time)
+    DevBuf red;                    // double scratch for reductions (>= n_params + 1024)
+    DevBuf red_part;               // per-block partial sums of the channel reductions (double)
+    DevBuf d_act[2];               // ping-pong gradient wrt activations
+    DevBuf d_pad, w_flip;          // backward-data as a forward convolution: padded dz, flipped weights
+    DevBuf tc_act, tc_wimg;        // tensor-core route: chunk-planar bf16 (hi, lo) input, UMMA weight image
+    DevBuf wg_scratch;             // tensor-core weight gradient: per-CTA partial sums
+    DevBuf grads;                  // this tower's share of the gradient (the left tower; the right one adds into tr->grads)
 };
 
 }  // namespace stereo
@@ -45,16 +53,13 @@ struct stereo_trainer {
     stereo::TrainLayer layer[stereo::kMaxLayers];
     size_t n_params = 0, n_stats = 0;
     stereo::DevBuf params, grads, adam_m, adam_v, stats;
-    stereo::DevBuf red;            // double scratch for reductions (>= max(n_params, 4 * 64))
-    stereo::DevBuf d_act[2];       // ping-pong gradient wrt activations
     stereo::DevBuf logits, dlogits, loss_buf, targets;
     stereo::DevBuf dfeat[2];       // gradient wrt the left / right feature tensors
-    stereo::DevBuf d_pad, w_flip, zero_bias;   // backward-data as a forward convolution: padded dz, flipped weights
-    stereo::DevBuf tc_act, tc_wimg;            // tensor-core route: chunk-planar bf16 (hi, lo) input, UMMA weight image
-    stereo::DevBuf wg_scratch;                 // tensor-core weight gradient: per-CTA partial sums
-    stereo::DevBuf red_part;                   // per-block partial sums of the channel reductions (double)
+    stereo::DevBuf zero_bias;
     stereo::Tower tower[2];
     long long step = 0;
+    cudaStream_t side_stream = nullptr;         // the left tower runs here while the right one runs on ctx->stream
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace stereo {
@@ -86,9 +91,8 @@ __global__ void train_conv_fwd_kernel(const float *__restrict__ in, const float 
     }
 }
 
-// batch mean / biased variance -> (mean, invstd); moving statistics as Keras updates them
-__global__ void train_bn_finalize_kernel(const double *__restrict__ red, double m, int c, float *__restrict__ bn,
-                                         float *__restrict__ moving_mean, float *__restrict__ moving_var)
+// batch mean / biased variance -> (mean, invstd, variance)
+__global__ void train_bn_finalize_kernel(const double *__restrict__ red, double m, int c, float *__restrict__ bn)
 {
     const int ch = threadIdx.x;
     if (ch >= c) return;
@@ -97,8 +101,24 @@ __global__ void train_bn_finalize_kernel(const double *__restrict__ red, double 
     if (var < 0.0) var = 0.0;
     bn[ch] = (float)mean;
     bn[c + ch] = (float)(1.0 / sqrt(var + (double)kBnEps));
-    moving_mean[ch] = moving_mean[ch] * kBnMomentum + (float)mean * (1.f - kBnMomentum);
-    moving_var[ch] = moving_var[ch] * kBnMomentum + (float)var * (1.f - kBnMomentum);
+    bn[2 * c + ch] = (float)var;
+}
+
+// Moving statistics as Keras updates them: the model is called on the left batch, then on the right one
+// (train.py:92-95), each call one momentum step.  The towers run at the same time, so the two steps are applied
+// here, in that order, once both batches' statistics are there.
+__global__ void train_update_stats_kernel(const float *__restrict__ bn_left, const float *__restrict__ bn_right, int c,
+                                          float *__restrict__ moving_mean, float *__restrict__ moving_var)
+{
+    const int ch = threadIdx.x;
+    if (ch >= c) return;
+    float mm = moving_mean[ch], mv = moving_var[ch];
+    mm = mm * kBnMomentum + bn_left[ch] * (1.f - kBnMomentum);
+    mv = mv * kBnMomentum + bn_left[2 * c + ch] * (1.f - kBnMomentum);
+    mm = mm * kBnMomentum + bn_right[ch] * (1.f - kBnMomentum);
+    mv = mv * kBnMomentum + bn_right[2 * c + ch] * (1.f - kBnMomentum);
+    moving_mean[ch] = mm;
+    moving_var[ch] = mv;
 }
 
 // ---- vectorised forms (c % 4 == 0: every layer's output has 32 or 64 channels) ----------------------------------
@@ -497,6 +517,12 @@ __global__ void train_flip_weights_kernel(const float *__restrict__ w, int ks, i
     wt[i] = w[(((size_t)(ks - 1 - ky) * ks + (ks - 1 - kx)) * cin + ci) * cout + co];
 }
 
+__global__ void train_add_kernel(const float *__restrict__ src, size_t n, float *__restrict__ dst)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] += src[i];
+}
+
 // Adam as tf.keras.optimizers.Adam applies it (train.py:80,112): lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t)
 __global__ void train_adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m,
                                   float *__restrict__ v, size_t n, float lr_t, float b1, float b2, float eps)
@@ -532,32 +558,32 @@ static inline unsigned grid_for(size_t total, int block, int cap)
 // the UMMA weight image is rebuilt from the current weights (they change every step), the output is fp32 NHWC again
 // because BatchNorm and the weight gradient read it.  Columns behind the image width hold whatever an earlier, wider
 // layer left there: they only reach output pixels the kernel does not store.
-static int train_conv_tc(stereo_trainer *tr, int relu, const float *w, const float *bias, const float *in, int n, int h,
-                         int wd, float *out)
+static int train_conv_tc(stereo_trainer *tr, Tower &tw, int relu, const float *w, const float *bias, const float *in, int n,
+                         int h, int wd, float *out)
 {
     stereo_ctx *ctx = tr->ctx;
     const int wp = tc3_pitch(wd);
     const size_t plane_elems = (size_t)n * h * 8 * wp * 8;
-    const size_t had = tr->tc_act.bytes;
-    STEREO_TRY(tr->tc_act.reserve(2 * plane_elems * sizeof(uint16_t)));
-    if (tr->tc_act.bytes != had) STEREO_CUDA_CHECK(cudaMemsetAsync(tr->tc_act.ptr, 0, tr->tc_act.bytes, ctx->stream));
-    STEREO_TRY(tr->tc_wimg.reserve(tc3_weight_image_elems() * sizeof(uint16_t)));
-    uint16_t *hi = tr->tc_act.as<uint16_t>(), *lo = hi + plane_elems;
+    const size_t had = tw.tc_act.bytes;
+    STEREO_TRY(tw.tc_act.reserve(2 * plane_elems * sizeof(uint16_t)));
+    if (tw.tc_act.bytes != had) STEREO_CUDA_CHECK(cudaMemsetAsync(tw.tc_act.ptr, 0, tw.tc_act.bytes, ctx->stream));
+    STEREO_TRY(tw.tc_wimg.reserve(tc3_weight_image_elems() * sizeof(uint16_t)));
+    uint16_t *hi = tw.tc_act.as<uint16_t>(), *lo = hi + plane_elems;
     STEREO_TRY(launch_nhwc_to_planar(ctx, in, n, h, wd, wp, 0, hi, lo));
-    STEREO_TRY(launch_weight_images3(ctx, w, tr->tc_wimg.ptr));
-    return launch_conv_tc3(ctx, hi, lo, n, h, wd, wp, tr->tc_wimg.ptr, bias, nullptr, nullptr, wp, out, relu, 2);
+    STEREO_TRY(launch_weight_images3(ctx, w, tw.tc_wimg.ptr));
+    return launch_conv_tc3(ctx, hi, lo, n, h, wd, wp, tw.tc_wimg.ptr, bias, nullptr, nullptr, wp, out, relu, 2);
 }
 
 // 'valid' convolution + bias (+ ReLU): the tensor-core route above for wide 64 -> 64 layers (STEREO_TRAIN_CONV=ffma
 // keeps them on the CUDA cores), else the tiled fp32 kernels of the inference path (conv_ffma.cu) where one is
 // instantiated for the shape, the plain kernel above otherwise.  `wbase + w_off` = kernel, `wbase + b_off` = bias.
-static int train_conv(stereo_trainer *tr, int ks, int cin, int cout, int relu, const float *wbase, size_t w_off,
+static int train_conv(stereo_trainer *tr, Tower &tw, int ks, int cin, int cout, int relu, const float *wbase, size_t w_off,
                       size_t b_off, const float *in, int n, int h, int w, float *out)
 {
     stereo_ctx *ctx = tr->ctx;
     static const bool no_tc = [] { const char *e = getenv("STEREO_TRAIN_CONV"); return e && (e[0] == 'f' || e[0] == 'p'); }();
     if (!no_tc && ks == 3 && cin == 64 && cout == 64 && w >= kTrainTcMinWidth && h >= 3)
-        return train_conv_tc(tr, relu, wbase + w_off, wbase + b_off, in, n, h, w, out);
+        return train_conv_tc(tr, tw, relu, wbase + w_off, wbase + b_off, in, n, h, w, out);
     const bool tiled = (ks == 3 && cout == 64 && (cin == 3 || cin == 64)) ||
                        (ks == 5 && ((cin == 3 && cout == 32) || (cin == 32 && cout == 32) || (cin == 32 && cout == 64) ||
                                     (cin == 64 && cout == 64)));
@@ -583,8 +609,7 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
 {
     stereo_ctx *ctx = tr->ctx;
     const float *P = tr->params.as<float>();
-    float *S = tr->stats.as<float>();
-    double *red = tr->red.as<double>();
+    double *red = tw.red.as<double>();
     const int n = tr->batch;
     tw.h[0] = h; tw.w[0] = w;
     const float *cur = patches;
@@ -595,16 +620,15 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
         const size_t m = (size_t)n * ho * wo, total = m * L.cout;
         STEREO_TRY(tw.a[l].reserve(total * sizeof(float)));
         STEREO_TRY(tw.x[l + 1].reserve(total * sizeof(float)));
-        STEREO_TRY(tw.bn[l].reserve(2 * L.cout * sizeof(float)));
-        STEREO_TRY(train_conv(tr, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
+        STEREO_TRY(tw.bn[l].reserve(3 * L.cout * sizeof(float)));
+        STEREO_TRY(train_conv(tr, tw, L.ks, L.cin, L.cout, L.relu, P, L.w_off, L.b_off, cur, n, tw.h[l], tw.w[l],
                               tw.a[l].as<float>()));
         const int c4 = L.cout / 4, rows4 = 256 / c4;
-        double *part = tr->red_part.as<double>();
+        double *part = tw.red_part.as<double>();
         const unsigned gm = grid_for(m, rows4, ctx->sm_count * 2);
         train_moments4_kernel<<<gm, 256, 0, ctx->stream>>>(reinterpret_cast<const float4 *>(tw.a[l].as<float>()), m, c4, part);
         train_sum_partials_kernel<<<(2 * L.cout + 7) / 8, 1024, 0, ctx->stream>>>(part, (int)gm, 2 * L.cout, red, 0);
-        train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>(),
-                                                                S + L.mean_off, S + L.var_off);
+        train_bn_finalize_kernel<<<1, L.cout, 0, ctx->stream>>>(red, (double)m, L.cout, tw.bn[l].as<float>());
         train_bn_apply4_kernel<<<grid_for(total / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(tw.a[l].as<float>()), total / 4, c4, tw.bn[l].as<float>(), P + L.g_off,
             P + L.be_off, reinterpret_cast<float4 *>(tw.x[l + 1].as<float>()));
@@ -615,13 +639,12 @@ static int tower_forward(stereo_trainer *tr, Tower &tw, const float *patches, in
     return STEREO_OK;
 }
 
-// dfeat: gradient wrt the tower's output (same shape as x[L]); gradients are ADDED to tr->grads
-static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, const float *dfeat)
+// dfeat: gradient wrt the tower's output (same shape as x[L]); gradients are ADDED to G
+static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, const float *dfeat, float *G)
 {
     stereo_ctx *ctx = tr->ctx;
     const float *P = tr->params.as<float>();
-    float *G = tr->grads.as<float>();
-    double *red = tr->red.as<double>();
+    double *red = tw.red.as<double>();
     const int n = tr->batch;
     const float *dy = dfeat;
     for (int l = tr->n_layers - 1; l >= 0; --l) {
@@ -630,13 +653,13 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         const size_t m = (size_t)n * ho * wo, total = m * L.cout;
         const float *a = tw.a[l].as<float>();
         const float *xin = l == 0 ? patches : tw.x[l].as<float>();
-        float *dz = tr->d_act[0].as<float>();                 // gradient wrt conv output (after the ReLU mask)
+        float *dz = tw.d_act[0].as<float>();                 // gradient wrt conv output (after the ReLU mask)
         // Scratch: red[0, 2c) BatchNorm sums, red[kRedW, kRedW + wn) dW, then db.  BatchNorm: dgamma, dbeta, da
         const size_t wn = (size_t)L.ks * L.ks * L.cin * L.cout;
         double *red_w = red + kRedW, *red_b = red_w + wn;
         STEREO_CUDA_CHECK(cudaMemsetAsync(red, 0, (kRedW + wn + L.cout) * sizeof(double), ctx->stream));
         const int c4 = L.cout / 4, rows4 = 256 / c4;
-        double *part = tr->red_part.as<double>();
+        double *part = tw.red_part.as<double>();
         const unsigned gr = grid_for(m, rows4, ctx->sm_count * 2);
         train_bn_bwd_reduce4_kernel<<<gr, 256, 0, ctx->stream>>>(
             reinterpret_cast<const float4 *>(dy), reinterpret_cast<const float4 *>(a), m, c4, tw.bn[l].as<float>(), part);
@@ -660,8 +683,8 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
         // 3x3 / 64 -> 64: positions as the K dimension of tcgen05 MMAs (train_wgrad_tc.cu); STEREO_TRAIN_CONV=ffma: fp32
         static const bool no_tc = [] { const char *e = getenv("STEREO_TRAIN_CONV"); return e && (e[0] == 'f' || e[0] == 'p'); }();
         if (!no_tc && L.ks == 3 && L.cin == 64 && L.cout == 64) {
-            STEREO_TRY(tr->wg_scratch.reserve(train_wgrad_tc_scratch_bytes(ctx)));
-            STEREO_TRY(launch_train_wgrad_tc(ctx, xin, dz, n, tw.h[l], tw.w[l], tr->wg_scratch.as<float>(), red_w));
+            STEREO_TRY(tw.wg_scratch.reserve(train_wgrad_tc_scratch_bytes(ctx)));
+            STEREO_TRY(launch_train_wgrad_tc(ctx, xin, dz, n, tw.h[l], tw.w[l], tw.wg_scratch.as<float>(), red_w));
         } else if (small)
             train_conv_bwd_w_small_kernel<<<chunks, 256, 0, ctx->stream>>>(xin, dz, n, tw.h[l], tw.w[l], L.ks, L.cin, L.cout,
                                                                            (int)chunk, red_w);
@@ -673,17 +696,17 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
                                                                                            red_b, L.cout, G + L.b_off);
         ctx->launches += 7;
         if (l > 0) {
-            float *dx = tr->d_act[1].as<float>();
+            float *dx = tw.d_act[1].as<float>();
             const int pad = L.ks - 1, hp = ho + 2 * pad, wp = wo + 2 * pad;
             const size_t tpad = (size_t)n * hp * wp * L.cout;
-            STEREO_TRY(tr->d_pad.reserve(tpad * sizeof(float)));
-            STEREO_TRY(tr->w_flip.reserve((wn + 64) * sizeof(float)));     // flipped kernel, then a zero bias
+            STEREO_TRY(tw.d_pad.reserve(tpad * sizeof(float)));
+            STEREO_TRY(tw.w_flip.reserve((wn + 64) * sizeof(float)));     // flipped kernel, then a zero bias
             train_pad4_kernel<<<grid_for(tpad / 4, 256, ctx->sm_count * 8), 256, 0, ctx->stream>>>(
-                reinterpret_cast<const float4 *>(dz), n, ho, wo, c4, pad, reinterpret_cast<float4 *>(tr->d_pad.as<float>()));
+                reinterpret_cast<const float4 *>(dz), n, ho, wo, c4, pad, reinterpret_cast<float4 *>(tw.d_pad.as<float>()));
             train_flip_weights_kernel<<<(unsigned)((wn + 255) / 256), 256, 0, ctx->stream>>>(P + L.w_off, L.ks, L.cin, L.cout,
-                                                                                            tr->w_flip.as<float>());
-            STEREO_CUDA_CHECK(cudaMemsetAsync(tr->w_flip.as<float>() + wn, 0, 64 * sizeof(float), ctx->stream));
-            STEREO_TRY(train_conv(tr, L.ks, L.cout, L.cin, 0, tr->w_flip.as<float>(), 0, wn, tr->d_pad.as<float>(), n, hp, wp, dx));
+                                                                                            tw.w_flip.as<float>());
+            STEREO_CUDA_CHECK(cudaMemsetAsync(tw.w_flip.as<float>() + wn, 0, 64 * sizeof(float), ctx->stream));
+            STEREO_TRY(train_conv(tr, tw, L.ks, L.cout, L.cin, 0, tw.w_flip.as<float>(), 0, wn, tw.d_pad.as<float>(), n, hp, wp, dx));
             ctx->launches += 2;
             dy = dx;          // d_act[1] carries the gradient down; d_act[0] is rewritten as the next dz
         }
@@ -733,12 +756,17 @@ int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, ste
     need(tr->adam_m, po * sizeof(float));
     need(tr->adam_v, po * sizeof(float));
     need(tr->stats, so * sizeof(float));
-    need(tr->red, (po + 1024) * sizeof(double));
-    need(tr->red_part, (size_t)ctx->sm_count * 8 * 128 * sizeof(double));      // <= 8 blocks per SM x 2 x 64 channels
     const size_t pw = (size_t)tr->patch + disp_range - 1;
     const size_t act = (size_t)batch * (tr->patch - nd.layer[0].ks + 1) * (pw - nd.layer[0].ks + 1) * 64;
-    need(tr->d_act[0], act * sizeof(float));
-    need(tr->d_act[1], act * sizeof(float));
+    for (int t = 0; t < 2; ++t) {
+        Tower &tw = tr->tower[t];
+        const size_t a = t == 0 ? (size_t)batch * (tr->patch - nd.layer[0].ks + 1) * (tr->patch - nd.layer[0].ks + 1) * 64 : act;
+        need(tw.red, (po + 1024) * sizeof(double));
+        need(tw.red_part, (size_t)ctx->sm_count * 8 * 128 * sizeof(double));      // <= 8 blocks per SM x 2 x 64 channels
+        need(tw.d_act[0], a * sizeof(float));
+        need(tw.d_act[1], a * sizeof(float));
+    }
+    need(tr->tower[0].grads, po * sizeof(float));
     need(tr->logits, (size_t)batch * disp_range * sizeof(float));
     need(tr->dlogits, (size_t)batch * disp_range * sizeof(float));
     need(tr->targets, (size_t)batch * disp_range * sizeof(float));
@@ -753,6 +781,9 @@ int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, ste
     cudaMemsetAsync(tr->stats.ptr, 0, so * sizeof(float), ctx->stream);
     cudaMemsetAsync(tr->zero_bias.ptr, 0, 64 * sizeof(float), ctx->stream);
     STEREO_TRY(finish(ctx));
+    STEREO_CUDA_CHECK(cudaStreamCreateWithFlags(&tr->side_stream, cudaStreamNonBlocking));
+    STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&tr->ev_fork, cudaEventDisableTiming));
+    STEREO_CUDA_CHECK(cudaEventCreateWithFlags(&tr->ev_join, cudaEventDisableTiming));
     *out = tr;
     return STEREO_OK;
 }
@@ -762,13 +793,19 @@ int stereo_train_destroy(stereo_trainer *tr)
     if (!tr) return STEREO_OK;
     cudaSetDevice(tr->ctx->device);
     cudaStreamSynchronize(tr->ctx->stream);
-    DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->red, &tr->d_act[0],
-                      &tr->d_act[1], &tr->logits, &tr->dlogits, &tr->loss_buf, &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->d_pad, &tr->w_flip, &tr->zero_bias,
-                      &tr->tc_act, &tr->tc_wimg, &tr->wg_scratch, &tr->red_part};
+    if (tr->side_stream) { cudaStreamSynchronize(tr->side_stream); cudaStreamDestroy(tr->side_stream); }
+    if (tr->ev_fork) cudaEventDestroy(tr->ev_fork);
+    if (tr->ev_join) cudaEventDestroy(tr->ev_join);
+    DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->logits, &tr->dlogits, &tr->loss_buf,
+                      &tr->targets, &tr->dfeat[0], &tr->dfeat[1], &tr->zero_bias};
     for (DevBuf *b : bufs) b->release();
     for (int t = 0; t < 2; ++t) {
-        for (int l = 0; l <= kMaxLayers; ++l) tr->tower[t].x[l].release();
-        for (int l = 0; l < kMaxLayers; ++l) { tr->tower[t].a[l].release(); tr->tower[t].bn[l].release(); }
+        Tower &tw = tr->tower[t];
+        for (int l = 0; l <= kMaxLayers; ++l) tw.x[l].release();
+        for (int l = 0; l < kMaxLayers; ++l) { tw.a[l].release(); tw.bn[l].release(); }
+        DevBuf *tb[] = {&tw.red, &tw.red_part, &tw.d_act[0], &tw.d_act[1], &tw.d_pad, &tw.w_flip, &tw.tc_act, &tw.tc_wimg,
+                        &tw.wg_scratch, &tw.grads};
+        for (DevBuf *b : tb) b->release();
     }
     delete tr;
     return STEREO_OK;
@@ -830,8 +867,41 @@ int stereo_train_forward_backward(stereo_trainer *tr, const float *left, const f
     STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->tower[1].x[0].ptr, right, (size_t)B * p * pw * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
     STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->targets.ptr, targets, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, s));
     STEREO_CUDA_CHECK(cudaMemsetAsync(tr->grads.ptr, 0, tr->n_params * sizeof(float), s));
-    STEREO_TRY(tower_forward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), p, p));
+    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->tower[0].grads.ptr, 0, tr->n_params * sizeof(float), s));
+    // The left tower (9 x 9 patches: small, latency-bound launches) runs on a stream of its own next to the right one;
+    // kernel-class profiling wants every kernel alone on the GPU: one stream while it is on.
+    cudaStream_t side = ctx->prof.on ? s : tr->side_stream;
+    struct OnStream {                        // launches go to ctx->stream
+        stereo_ctx *ctx;
+        cudaStream_t saved;
+        OnStream(stereo_ctx *c, cudaStream_t st) : ctx(c), saved(c->stream) { c->stream = st; }
+        ~OnStream() { ctx->stream = saved; }
+    };
+    auto fork = [&]() -> int {
+        if (side == s) return STEREO_OK;
+        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_fork, s));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(side, tr->ev_fork, 0));
+        return STEREO_OK;
+    };
+    auto join = [&]() -> int {
+        if (side == s) return STEREO_OK;
+        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_join, side));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(s, tr->ev_join, 0));
+        return STEREO_OK;
+    };
+    STEREO_TRY(fork());
+    {
+        OnStream left(ctx, side);
+        STEREO_TRY(tower_forward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), p, p));
+    }
     STEREO_TRY(tower_forward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), p, pw));
+    STEREO_TRY(join());
+    for (int l = 0; l < tr->n_layers; ++l) {
+        const TrainLayer &Ly = tr->layer[l];
+        train_update_stats_kernel<<<1, Ly.cout, 0, s>>>(tr->tower[0].bn[l].as<float>(), tr->tower[1].bn[l].as<float>(), Ly.cout,
+                                                        tr->stats.as<float>() + Ly.mean_off, tr->stats.as<float>() + Ly.var_off);
+    }
+    ctx->launches += tr->n_layers;
     const int L = tr->n_layers, c = tr->layer[L - 1].cout;
     STEREO_REQUIRE(tr->tower[0].h[L] == 1 && tr->tower[0].w[L] == 1 && tr->tower[1].h[L] == 1 && tr->tower[1].w[L] == D,
                    "unexpected feature shape");
@@ -847,8 +917,18 @@ int stereo_train_forward_backward(stereo_trainer *tr, const float *left, const f
     train_loss_bwd_kernel<<<B, c, 0, s>>>(lf, rf, tr->dlogits.as<float>(), D, c, dl.as<float>(), dr.as<float>());
     ctx->launches += 3;
     STEREO_CUDA_CHECK(cudaGetLastError());
-    STEREO_TRY(tower_backward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), dr.as<float>()));
-    STEREO_TRY(tower_backward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), dl.as<float>()));
+    STEREO_TRY(fork());
+    {
+        OnStream left(ctx, side);
+        STEREO_TRY(tower_backward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), dl.as<float>(), tr->tower[0].grads.as<float>()));
+    }
+    STEREO_TRY(tower_backward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), dr.as<float>(), tr->grads.as<float>()));
+    STEREO_TRY(join());
+    // shared weights: the gradient is the sum of the towers' (right + left, the order of the sequential version)
+    train_add_kernel<<<(unsigned)((tr->n_params + 255) / 256), 256, 0, s>>>(tr->tower[0].grads.as<float>(), tr->n_params,
+                                                                         tr->grads.as<float>());
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
     float host[2] = {0.f, 0.f};
     STEREO_CUDA_CHECK(cudaMemcpyAsync(host, tr->loss_buf.as<float>() + 2 * B, sizeof(host), cudaMemcpyDeviceToHost, s));
     if (grads_out)
