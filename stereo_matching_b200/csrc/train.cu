@@ -60,6 +60,9 @@ struct stereo_trainer {
     long long step = 0;
     cudaStream_t side_stream = nullptr;         // the left tower runs here while the right one runs on ctx->stream
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool warm = false;                          // a step has run: every buffer has its size
+    cudaGraphExec_t graph_exec = nullptr;       // the captured step
+    long long graph_launches = 0;               // kernel launches inside it
 };
 
 namespace stereo {
@@ -715,6 +718,78 @@ static int tower_backward(stereo_trainer *tr, Tower &tw, const float *patches, c
     return STEREO_OK;
 }
 
+// Everything of a step between the uploads and the downloads, enqueued on ctx->stream (and the side stream)
+static int enqueue_step(stereo_trainer *tr)
+{
+    stereo_ctx *ctx = tr->ctx;
+    cudaStream_t s = ctx->stream;
+    const int B = tr->batch, D = tr->D, p = tr->patch, pw = p + D - 1;
+    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->grads.ptr, 0, tr->n_params * sizeof(float), s));
+    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->tower[0].grads.ptr, 0, tr->n_params * sizeof(float), s));
+    // The left tower (9 x 9 patches: small, latency-bound launches) runs on a stream of its own next to the right one;
+    // kernel-class profiling wants every kernel alone on the GPU: one stream while it is on.
+    cudaStream_t side = ctx->prof.on ? s : tr->side_stream;
+    struct OnStream {                        // launches go to ctx->stream
+        stereo_ctx *ctx;
+        cudaStream_t saved;
+        OnStream(stereo_ctx *c, cudaStream_t st) : ctx(c), saved(c->stream) { c->stream = st; }
+        ~OnStream() { ctx->stream = saved; }
+    };
+    auto fork = [&]() -> int {
+        if (side == s) return STEREO_OK;
+        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_fork, s));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(side, tr->ev_fork, 0));
+        return STEREO_OK;
+    };
+    auto join = [&]() -> int {
+        if (side == s) return STEREO_OK;
+        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_join, side));
+        STEREO_CUDA_CHECK(cudaStreamWaitEvent(s, tr->ev_join, 0));
+        return STEREO_OK;
+    };
+    STEREO_TRY(fork());
+    {
+        OnStream left(ctx, side);
+        STEREO_TRY(tower_forward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), p, p));
+    }
+    STEREO_TRY(tower_forward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), p, pw));
+    STEREO_TRY(join());
+    for (int l = 0; l < tr->n_layers; ++l) {
+        const TrainLayer &Ly = tr->layer[l];
+        train_update_stats_kernel<<<1, Ly.cout, 0, s>>>(tr->tower[0].bn[l].as<float>(), tr->tower[1].bn[l].as<float>(), Ly.cout,
+                                                        tr->stats.as<float>() + Ly.mean_off, tr->stats.as<float>() + Ly.var_off);
+    }
+    ctx->launches += tr->n_layers;
+    const int L = tr->n_layers, c = tr->layer[L - 1].cout;
+    STEREO_REQUIRE(tr->tower[0].h[L] == 1 && tr->tower[0].w[L] == 1 && tr->tower[1].h[L] == 1 && tr->tower[1].w[L] == D,
+                   "unexpected feature shape");
+    const float *lf = tr->tower[0].x[L].as<float>(), *rf = tr->tower[1].x[L].as<float>();
+    const int nt = 256;
+    const size_t sh = (((size_t)D + 1) & ~(size_t)1) * sizeof(float) + 6 * nt * sizeof(float);
+    train_loss_kernel<<<B, nt, sh, s>>>(lf, rf, tr->targets.as<float>(), D, c, B, tr->logits.as<float>(),
+                                        tr->dlogits.as<float>(), tr->loss_buf.as<float>());
+    train_reduce_loss_kernel<<<1, 32, 0, s>>>(tr->loss_buf.as<float>(), B, tr->loss_buf.as<float>() + 2 * B);
+    DevBuf &dl = tr->dfeat[0], &dr = tr->dfeat[1];
+    STEREO_TRY(dl.reserve((size_t)B * c * sizeof(float)));
+    STEREO_TRY(dr.reserve((size_t)B * D * c * sizeof(float)));
+    train_loss_bwd_kernel<<<B, c, 0, s>>>(lf, rf, tr->dlogits.as<float>(), D, c, dl.as<float>(), dr.as<float>());
+    ctx->launches += 3;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    STEREO_TRY(fork());
+    {
+        OnStream left(ctx, side);
+        STEREO_TRY(tower_backward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), dl.as<float>(), tr->tower[0].grads.as<float>()));
+    }
+    STEREO_TRY(tower_backward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), dr.as<float>(), tr->grads.as<float>()));
+    STEREO_TRY(join());
+    // shared weights: the gradient is the sum of the towers' (right + left, the order of the sequential version)
+    train_add_kernel<<<(unsigned)((tr->n_params + 255) / 256), 256, 0, s>>>(tr->tower[0].grads.as<float>(), tr->n_params,
+                                                                         tr->grads.as<float>());
+    ctx->launches += 1;
+    STEREO_CUDA_CHECK(cudaGetLastError());
+    return STEREO_OK;
+}
+
 }  // namespace stereo
 
 using namespace stereo;
@@ -794,6 +869,7 @@ int stereo_train_destroy(stereo_trainer *tr)
     cudaSetDevice(tr->ctx->device);
     cudaStreamSynchronize(tr->ctx->stream);
     if (tr->side_stream) { cudaStreamSynchronize(tr->side_stream); cudaStreamDestroy(tr->side_stream); }
+    if (tr->graph_exec) cudaGraphExecDestroy(tr->graph_exec);
     if (tr->ev_fork) cudaEventDestroy(tr->ev_fork);
     if (tr->ev_join) cudaEventDestroy(tr->ev_join);
     DevBuf *bufs[] = {&tr->params, &tr->grads, &tr->adam_m, &tr->adam_v, &tr->stats, &tr->logits, &tr->dlogits, &tr->loss_buf,
@@ -866,69 +942,34 @@ int stereo_train_forward_backward(stereo_trainer *tr, const float *left, const f
     STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->tower[0].x[0].ptr, left, (size_t)B * p * p * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
     STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->tower[1].x[0].ptr, right, (size_t)B * p * pw * 3 * sizeof(float), cudaMemcpyHostToDevice, s));
     STEREO_CUDA_CHECK(cudaMemcpyAsync(tr->targets.ptr, targets, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, s));
-    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->grads.ptr, 0, tr->n_params * sizeof(float), s));
-    STEREO_CUDA_CHECK(cudaMemsetAsync(tr->tower[0].grads.ptr, 0, tr->n_params * sizeof(float), s));
-    // The left tower (9 x 9 patches: small, latency-bound launches) runs on a stream of its own next to the right one;
-    // kernel-class profiling wants every kernel alone on the GPU: one stream while it is on.
-    cudaStream_t side = ctx->prof.on ? s : tr->side_stream;
-    struct OnStream {                        // launches go to ctx->stream
-        stereo_ctx *ctx;
-        cudaStream_t saved;
-        OnStream(stereo_ctx *c, cudaStream_t st) : ctx(c), saved(c->stream) { c->stream = st; }
-        ~OnStream() { ctx->stream = saved; }
-    };
-    auto fork = [&]() -> int {
-        if (side == s) return STEREO_OK;
-        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_fork, s));
-        STEREO_CUDA_CHECK(cudaStreamWaitEvent(side, tr->ev_fork, 0));
-        return STEREO_OK;
-    };
-    auto join = [&]() -> int {
-        if (side == s) return STEREO_OK;
-        STEREO_CUDA_CHECK(cudaEventRecord(tr->ev_join, side));
-        STEREO_CUDA_CHECK(cudaStreamWaitEvent(s, tr->ev_join, 0));
-        return STEREO_OK;
-    };
-    STEREO_TRY(fork());
-    {
-        OnStream left(ctx, side);
-        STEREO_TRY(tower_forward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), p, p));
+    // The step is ~150 small launches on two streams with fixed shapes and buffers: from the second call on (every buffer
+    // has its size by then) it is captured once into a CUDA graph and replayed.  STEREO_TRAIN_GRAPH=0 and kernel-class
+    // profiling keep the plain launches.
+    static const bool graphs_on = [] { const char *e = getenv("STEREO_TRAIN_GRAPH"); return !(e && e[0] == '0'); }();
+    if (!graphs_on || ctx->prof.on || !tr->warm) {
+        STEREO_TRY(enqueue_step(tr));
+        tr->warm = true;
+    } else {
+        if (!tr->graph_exec) {
+            const long long launches0 = ctx->launches;
+            STEREO_CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+            const int rc = enqueue_step(tr);
+            cudaGraph_t graph = nullptr;
+            const cudaError_t ce = cudaStreamEndCapture(s, &graph);
+            tr->graph_launches = ctx->launches - launches0;
+            ctx->launches = launches0;
+            if (rc != STEREO_OK || ce != cudaSuccess) {
+                if (graph) cudaGraphDestroy(graph);
+                STEREO_TRY(rc);
+                STEREO_CUDA_CHECK(ce);
+            }
+            const cudaError_t ie = cudaGraphInstantiate(&tr->graph_exec, graph, 0);
+            cudaGraphDestroy(graph);
+            STEREO_CUDA_CHECK(ie);
+        }
+        STEREO_CUDA_CHECK(cudaGraphLaunch(tr->graph_exec, s));
+        ctx->launches += tr->graph_launches;
     }
-    STEREO_TRY(tower_forward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), p, pw));
-    STEREO_TRY(join());
-    for (int l = 0; l < tr->n_layers; ++l) {
-        const TrainLayer &Ly = tr->layer[l];
-        train_update_stats_kernel<<<1, Ly.cout, 0, s>>>(tr->tower[0].bn[l].as<float>(), tr->tower[1].bn[l].as<float>(), Ly.cout,
-                                                        tr->stats.as<float>() + Ly.mean_off, tr->stats.as<float>() + Ly.var_off);
-    }
-    ctx->launches += tr->n_layers;
-    const int L = tr->n_layers, c = tr->layer[L - 1].cout;
-    STEREO_REQUIRE(tr->tower[0].h[L] == 1 && tr->tower[0].w[L] == 1 && tr->tower[1].h[L] == 1 && tr->tower[1].w[L] == D,
-                   "unexpected feature shape");
-    const float *lf = tr->tower[0].x[L].as<float>(), *rf = tr->tower[1].x[L].as<float>();
-    const int nt = 256;
-    const size_t sh = (((size_t)D + 1) & ~(size_t)1) * sizeof(float) + 6 * nt * sizeof(float);
-    train_loss_kernel<<<B, nt, sh, s>>>(lf, rf, tr->targets.as<float>(), D, c, B, tr->logits.as<float>(),
-                                        tr->dlogits.as<float>(), tr->loss_buf.as<float>());
-    train_reduce_loss_kernel<<<1, 32, 0, s>>>(tr->loss_buf.as<float>(), B, tr->loss_buf.as<float>() + 2 * B);
-    DevBuf &dl = tr->dfeat[0], &dr = tr->dfeat[1];
-    STEREO_TRY(dl.reserve((size_t)B * c * sizeof(float)));
-    STEREO_TRY(dr.reserve((size_t)B * D * c * sizeof(float)));
-    train_loss_bwd_kernel<<<B, c, 0, s>>>(lf, rf, tr->dlogits.as<float>(), D, c, dl.as<float>(), dr.as<float>());
-    ctx->launches += 3;
-    STEREO_CUDA_CHECK(cudaGetLastError());
-    STEREO_TRY(fork());
-    {
-        OnStream left(ctx, side);
-        STEREO_TRY(tower_backward(tr, tr->tower[0], tr->tower[0].x[0].as<float>(), dl.as<float>(), tr->tower[0].grads.as<float>()));
-    }
-    STEREO_TRY(tower_backward(tr, tr->tower[1], tr->tower[1].x[0].as<float>(), dr.as<float>(), tr->grads.as<float>()));
-    STEREO_TRY(join());
-    // shared weights: the gradient is the sum of the towers' (right + left, the order of the sequential version)
-    train_add_kernel<<<(unsigned)((tr->n_params + 255) / 256), 256, 0, s>>>(tr->tower[0].grads.as<float>(), tr->n_params,
-                                                                         tr->grads.as<float>());
-    ctx->launches += 1;
-    STEREO_CUDA_CHECK(cudaGetLastError());
     float host[2] = {0.f, 0.f};
     STEREO_CUDA_CHECK(cudaMemcpyAsync(host, tr->loss_buf.as<float>() + 2 * B, sizeof(host), cudaMemcpyDeviceToHost, s));
     if (grads_out)
