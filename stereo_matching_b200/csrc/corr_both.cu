@@ -36,10 +36,10 @@ constexpr int kRun = kBlk * 16;                 // one channel chunk: 2 KB
 constexpr int kPlane = 8 * kRun;                // 16 KB
 constexpr int kBlock = 2 * kPlane;              // hi + lo: 32 KB
 constexpr int kAccBlocks = 4;
-// COL = true: the right map is computed (false: timing experiment, the floor of the sweep).  Measured first for the
-// column maxima: one redux.sync.max.f32 + ballot per column - 139 us per pair, the reductions run at about one per
-// eight cycles and SM.  Eight columns at a time through shared memory (16 KB, leaves room for a third own-block
-// slot): 113 us; sixteen (32 KB, two own-block slots): 102 us.
+// Measured first for the column maxima: one redux.sync.max.f32 + ballot per column - 139 us per pair, the reductions
+// run at about one per eight cycles and SM.  Eight columns at a time through shared memory (16 KB, leaves room for a
+// third own-block slot): 113 us; sixteen (32 KB, two own-block slots): 102 us.  (The sweep without any column scan -
+// a build that existed only for this measurement - took 68 us.)
 #ifndef STEREO_BOTH_NC
 #define STEREO_BOTH_NC 16
 #endif
@@ -137,7 +137,6 @@ __device__ __forceinline__ void scan_cols(const uint32_t (&v)[32], float *xp, in
     }
 }
 
-template <bool COL>
 __global__ __launch_bounds__(kThreads, 1) void corr_both_kernel(Params p)
 {
     using L = Layout;
@@ -353,7 +352,7 @@ __global__ __launch_bounds__(kThreads, 1) void corr_both_kernel(Params p)
                         int cd = kNoDisp;               // column `lane` of the chunk: its maximum over the rows, its disparity
                         if (all_in) scan_rows<false>(v, dbase, D, best, best_d);
                         else scan_rows<true>(v, dbase, D, best, best_d);
-                        if (COL) {
+                        {
                             float *xp = reinterpret_cast<float *>(smem + L::kXpose + (warp - 4) * kXposeWarp);
                             if (all_in) scan_cols<false>(v, xp, lane, 32 * q + kMargin - u0, D, cmax, cd);
                             else scan_cols<true>(v, xp, lane, 32 * q + kMargin - u0, D, cmax, cd);
@@ -439,16 +438,11 @@ int launch_corr_both(stereo_ctx *ctx, const void *l_hi, const void *l_lo, const 
     p.nitems = n * h;
     p.img_stride = img_stride ? img_stride : (size_t)h * 8 * wf * 8;
     const int grid = p.nitems < ctx->sm_count ? p.nitems : ctx->sm_count;
-    // STEREO_CORR_COLS=0: no column scan (timing only, the right map is wrong)
-    static const bool cols = [] { const char *e = getenv("STEREO_CORR_COLS"); return !(e && e[0] == '0'); }();
-    auto launch = [&](auto kern) -> int {
-        STEREO_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::Layout::kTotal));
+    STEREO_CUDA_CHECK(cudaFuncSetAttribute(tcb::corr_both_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::Layout::kTotal));
+    {
         ProfScope prof(ctx, STEREO_K_CORR);
-        kern<<<grid, tcb::kThreads, tcb::Layout::kTotal, ctx->stream>>>(p);
-        return STEREO_OK;
-    };
-    if (cols) STEREO_TRY(launch(tcb::corr_both_kernel<true>));
-    else STEREO_TRY(launch(tcb::corr_both_kernel<false>));
+        tcb::corr_both_kernel<<<grid, tcb::kThreads, tcb::Layout::kTotal, ctx->stream>>>(p);
+    }
     ctx->launches += 1;
     STEREO_CUDA_CHECK(cudaGetLastError());
     return STEREO_OK;
