@@ -261,7 +261,8 @@ int stereo_box_agg_dev(stereo_ctx *ctx, const float *vol, int h, int w, int D, i
  * optimizer.apply_gradients with tf.keras.optimizers.Adam (train.py:80,109-112).
  * Parameters are one flat fp32 array in the order of Keras' trainable_variables: per layer kernel
  * [k][k][Cin][Cout], bias, gamma, beta; the moving statistics (mean, variance per layer) are a second
- * array.  A trainer belongs to the context it was created on and uses its stream.
+ * array.  A trainer belongs to the context it was created on and uses its stream (plus one internal stream on which
+ * the left tower runs next to the right one; both are joined before stereo_train_forward_backward returns).
  * ------------------------------------------------------------------------------------------- */
 typedef struct stereo_trainer stereo_trainer;
 int stereo_train_create(stereo_ctx *ctx, int net, int batch, int disp_range, stereo_trainer **out);
