@@ -140,3 +140,28 @@ def test_banded_cost_volumes_equal_the_reference_loop():
         lb, rb = so.cost_volumes_banded(L, R, D, np.float64)
         assert np.allclose(lb, lref, rtol=0, atol=1e-12) and np.allclose(rb, rref, rtol=0, atol=1e-12)
         assert np.array_equal(lb == 0, lref == 0)
+
+
+def test_right_volume_is_the_sheared_left_volume_and_its_wta_is_a_column_scan():
+    """The identity behind the one-sweep correlation kernel (csrc/corr_both.cu), on the reference loop's own
+    output: right[x][d] = left[x + d][d] wherever x + d < W and 0.0 elsewhere (inference.py:160-183 writes both
+    volumes from the same `inner`), so the right disparity of pixel x is the arg max over the rows x, x + 1, ... of the
+    banded matrix S[xl][xr] = <L[xl], R[xr]> - with the zero-filled slots taking part, lowest disparity on ties."""
+    rng = np.random.default_rng(5)
+    W, D = 23, 9
+    L = rng.integers(-2, 3, (1, 2, W, 3)).astype(np.float64)      # small integers: exact products, many ties
+    R = rng.integers(-2, 3, (1, 2, W, 3)).astype(np.float64)
+    lv, rv = so.cost_volumes(L, R, D)
+    for y in range(2):
+        S = L[0, y] @ R[0, y].T                                   # S[xl][xr]
+        for x in range(W):
+            for d in range(D):
+                assert rv[y, x, d] == (lv[y, x + d, d] if x + d < W else 0.0)
+                assert rv[y, x, d] == (S[x + d, x] if x + d < W else 0.0)
+            # column scan with the running best seeded by nothing, first maximum wins; rows past the image are 0.0
+            best, best_d = -np.inf, 0
+            for d in range(D):
+                v = S[x + d, x] if x + d < W else 0.0
+                if v > best:
+                    best, best_d = v, d
+            assert so.wta(rv)[y, x] == best_d
